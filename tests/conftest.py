@@ -1,0 +1,28 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def small_cases():
+    import numpy as np
+
+    z = np.load(os.path.join(ROOT, "tests", "golden", "small_cases.npz"), allow_pickle=False)
+    return z
+
+
+@pytest.fixture(scope="session")
+def c1():
+    import numpy as np
+
+    return np.load(os.path.join(ROOT, "tests", "golden", "c1_sars20.npz"), allow_pickle=False)

@@ -1,0 +1,83 @@
+"""CPU: pins the plain-C oracle (oracle/pmfs_oracle.c) to the reference.
+
+* against the committed golden fixtures, which were produced by the reference's own fitchSankoff.cpp (oracle/_ref);
+* directly against oracle/_ref on fresh random inputs wherever that library exists (this container; the prebuilt file
+  also travels to the GPU box).
+"""
+import numpy as np
+import pytest
+
+import golden_util as G
+import synth
+from oracle import oracle_api as O
+
+
+def test_port_matches_golden_small(small_cases):
+    z = small_cases
+    for name in z["case_names"]:
+        tree, msa, cons, forced = G.case_inputs(z, str(name))
+        for algo in (0, 1):
+            got = O.run_port(algo, tree, msa, cons, forced, threads=2)
+            assert G.same_muts(got, z[f"{name}/muts{algo}"]), (name, algo)
+            off, nuc = O.pack_port(got, tree.n_nodes)
+            assert (off == z[f"{name}/nuc_off{algo}"]).all(), (name, algo)
+            assert G.same_nuc(nuc, z[f"{name}/nuc{algo}"]), (name, algo)
+
+
+@pytest.mark.parametrize("low,with_ref", [(0, 0), (0, 1), (1, 0), (1, 1)])
+def test_port_matches_golden_c1(c1, low, with_ref):
+    key = f"v{low}{with_ref}_"
+    tree = G.c1_tree(c1)
+    msa = G.unpack_nibbles(c1["msa_nibbles"], int(c1["n_cols"]))
+    forced = None
+    if with_ref:
+        row = list(c1["row_ids"]).index(str(c1[key + "reference"]))
+        # Fitch: refState = 1<<code(ref[i]) (panman.cpp:1409); Sankoff: defaultState = code(ref[i]) (:1573-1580)
+        forced = msa[row]
+    got = O.run_port(low, tree, msa, c1[key + "consensus"], forced, threads=4)
+    assert got.shape[0] == int(c1[key + "n_muts"])
+    assert (np.bincount(got["type"], minlength=3) == c1[key + "type_counts"]).all()
+    assert G.same_muts(got[:512], c1[key + "muts_head"])
+    assert G.digest_muts(got) == str(c1[key + "muts_sha256"])
+    off, nuc = O.pack_port(got, tree.n_nodes)
+    assert nuc.shape[0] == int(c1[key + "n_nuc"])
+    assert G.digest_nuc(off, nuc) == str(c1[key + "nuc_sha256"])
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built and /root/reference absent")
+def test_port_matches_reference_random():
+    rng = np.random.default_rng(7)
+    for trial in range(30):
+        arity = 2 if trial < 10 else int(rng.integers(2, 6))
+        tree = synth.random_tree(int(rng.integers(2, 90)), rng, max_arity=arity, absent_frac=0.0 if trial % 3 else 0.1)
+        L = int(rng.integers(1, 300))
+        msa = synth.simulate_msa(tree, L, rng, p_sub=0.1, p_del=0.05, p_ins=0.2, p_n=0.05, p_amb=0.05)
+        cons = synth.consensus_first_nongap(msa)
+        forced = msa[int(rng.integers(0, msa.shape[0]))] if trial % 2 else None
+        for algo in (0, 1):
+            a = O.run_port(algo, tree, msa, cons, forced, threads=2)
+            b = O.run_ref_columns(algo, tree, O.codes_to_chars(msa), O.codes_to_chars(cons),
+                                  None if forced is None else O.codes_to_chars(forced), threads=2)
+            assert G.same_muts(a, b), (trial, algo)
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref not built and /root/reference absent")
+def test_port_matches_reference_deep_ladder():
+    # the reference recursion needs a big stack here; ref_driver runs it on 64 MB+ threads
+    tree = synth.caterpillar(20000)
+    rng = np.random.default_rng(3)
+    msa = rng.choice(np.array([0, 1, 2, 4, 8, 15], np.uint8), size=(20000, 4), p=[0.05, 0.3, 0.2, 0.2, 0.2, 0.05])
+    msa[0, (msa != 0).sum(0) == 0] = 1
+    cons = synth.consensus_first_nongap(msa)
+    for algo in (0, 1):
+        a = O.run_port(algo, tree, msa, cons, None, threads=2)
+        b = O.run_ref_columns(algo, tree, O.codes_to_chars(msa), O.codes_to_chars(cons), None, threads=2)
+        assert G.same_muts(a, b)
+
+
+def test_sankoff_unforced_invalid_root_is_an_error():
+    tree = synth._flatten([None, None])
+    with pytest.raises(RuntimeError):
+        O.run_port(1, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), None)
+    # Fitch: no records at all (every node has an empty set and is skipped)
+    assert O.run_port(0, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), None).shape[0] == 0
