@@ -1,0 +1,154 @@
+/* libpmfs -- B200 (sm_100a) per-column small parsimony (Fitch / unit-cost Sankoff) for PanMAN's MSA construction path.
+ *
+ * This C ABI replaces, in one batched call, the per-column loop the reference runs on the host while a PanMAT is built
+ * from an MSA and a Newick tree (paths relative to /root/reference):
+ *     Fitch   : src/panman.cpp:1371-1425  -> nucFitch{ForwardPass,BackwardPass,AssignMutations}   src/fitchSankoff.cpp:30,96,131
+ *     Sankoff : src/panman.cpp:1558-1603  -> nucSankoff{ForwardPass,BackwardPass,AssignMutations} src/fitchSankoff.cpp:359,487,676
+ * Everything before the loop (Newick parse, FASTA read, consensus) and after it (per-node sort, <=6-run NucMut packing,
+ * serialisation) stays host C++ (panman_b200/csrc/host/); INTEGRATION.md shows the patch a maintainer would apply.
+ *
+ * Conventions
+ *   - every function returns PMFS_OK (0) or a negative pmfs_status; pmfs_last_error() gives text.  No exceptions, no exit().
+ *   - a context is bound to one CUDA device and must be driven by one host thread at a time.
+ *   - there is NO CPU fallback: without a usable CUDA device pmfs_create fails with PMFS_ERR_CUDA.
+ *   - node ids are the reference's creation order (createTreeFromNewickString, src/panman.cpp:300-440): pre-order,
+ *     id 0 is the root ("node_1"), parent[i] < i.
+ *   - nucleotide codes are the reference's 4-bit codes (src/panman.cpp:83-118): 0 gap/unknown, A1 C2 M3 G4 R5 S6 V7 T8 W9
+ *     Y10 H11 K12 D13 B14 N15; each code is its own unordered state (N is not {A,C,G,T}).
+ *   - an MSA is leaf-major, columns contiguous, two columns per byte: column 2j in the LOW nibble of byte j.
+ */
+#ifndef PMFS_H
+#define PMFS_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    PMFS_OK = 0,
+    PMFS_ERR_ARG = -1,          /* null pointer, bad size, malformed tree */
+    PMFS_ERR_CUDA = -2,         /* CUDA runtime error or no device (there is no CPU path) */
+    PMFS_ERR_NOMEM = -3,        /* device or host allocation failed */
+    PMFS_ERR_ROOT_INVALID = -4, /* Sankoff: a column has no tree leaf present in the MSA and no forced root; the
+                                   reference aborts there (assert, src/fitchSankoff.cpp:505) */
+    PMFS_ERR_STATE = -5         /* call out of order (e.g. run before an MSA is set) */
+} pmfs_status;
+
+enum { PMFS_FITCH = 0, PMFS_SANKOFF = 1 };
+enum { PMFS_NS = 0, PMFS_ND = 1, PMFS_NI = 2 }; /* panmanUtils::NucMutationType, src/panman.hpp:26-41 */
+
+/* Tree in the reference's numbering.  Replaces the Node* graph + allNodes map (src/panman.hpp:307-322, 326-340). */
+typedef struct {
+    int32_t n_nodes;          /* V >= 2; node 0 is the root and must be internal */
+    const int32_t* parent;    /* [V], -1 for the root; parent[i] < i */
+    const int32_t* child_off; /* [V+1] CSR offsets */
+    const int32_t* child_idx; /* children in Newick order (any arity >= 1) */
+    const int32_t* leaf_row;  /* [V]: MSA row of a leaf; -1 for internal nodes; -2 for a leaf with no row in the MSA
+                                 (the reference gives such a leaf the empty set / all-INF vector,
+                                 src/fitchSankoff.cpp:33-36, :363-366) */
+} pmfs_tree;
+
+/* One per-branch annotation: the tuple (pos, type, code) the reference pushes into nonGapMutationsMSA[node]
+ * (src/panman.cpp:1416-1420, :1597-1601), plus the node it belongs to and the parent's state. */
+typedef struct {
+    int32_t node;        /* node id */
+    int32_t pos;         /* column */
+    uint8_t type;        /* PMFS_NS / PMFS_ND / PMFS_NI */
+    uint8_t code;        /* getCodeFromNucleotide(mutation char): the node's state, 0 for ND */
+    uint8_t parent_code; /* the parent's state (the consensus code for the root); not in the reference tuple */
+    uint8_t pad;
+} pmfs_mut;
+
+typedef struct pmfs_ctx pmfs_ctx;
+
+/* Timings of the last pmfs_run* call, CUDA events on the context's stream, milliseconds. */
+typedef struct {
+    float h2d_ms;      /* host->device copies (0 for the device-resident entry points) */
+    float forward_ms;  /* bottom-up set pass (all chunk levels) */
+    float backward_ms; /* top-down assignment + mutation emission */
+    float sort_ms;     /* ordering of the emitted records by (node,pos) */
+    float d2h_ms;      /* record download */
+    float total_ms;
+    int64_t n_launches;     /* kernels of this library launched by the call */
+    int64_t forward_bytes;  /* design-level HBM bytes of the forward pass ("bytes per update") */
+    int64_t backward_bytes; /* same for the backward pass, excluding emitted records */
+} pmfs_timing;
+
+const char* pmfs_last_error(void);
+const char* pmfs_version(void);
+
+/* Builds the per-tree execution plan (chunking + per-chunk walk programs) and uploads it to `device`.
+ * Replaces nothing in the reference one-to-one: it is the flat, device-side stand-in for the Node* graph that
+ * createTreeFromNewickString (src/panman.cpp:300-440) produces. */
+int pmfs_create(pmfs_ctx** ctx, const pmfs_tree* tree, int device);
+void pmfs_destroy(pmfs_ctx* ctx);
+
+/* Optional tuning, call before the first run: target nodes per chunk (0 = automatic) and columns per pass
+ * (0 = automatic from free HBM).  Results never depend on either. */
+int pmfs_set_tuning(pmfs_ctx* ctx, int32_t chunk_nodes, int64_t tile_cols);
+
+/* Run all of the context's work on `cuda_stream` (a cudaStream_t of the context's device; NULL restores the context's
+ * own stream).  Lets a caller order the passes after its own producers and time them with its own events. */
+int pmfs_set_stream(pmfs_ctx* ctx, void* cuda_stream);
+
+/* The reference-facing call: host buffers in, host records out.
+ * Replaces the whole column loop src/panman.cpp:1371-1425 (algo = PMFS_FITCH) or :1558-1603 (PMFS_SANKOFF).
+ *   msa_nibbles       [n_rows][row_stride_bytes]  leaf-major packed codes (see top of file)
+ *   consensus_code    [n_cols]  code compared against the root's state (1<<code(consensusSeq[i]) in :1414-1415,
+ *                               code(consensusSeq[i]) in :1590-1596)
+ *   root_forced_code  [n_cols] or NULL: Fitch refState (src/fitchSankoff.cpp:45-47, passed at src/panman.cpp:1409-1410
+ *                               when --reference is given) / Sankoff defaultValue (:491-492, src/panman.cpp:1573-1594)
+ *   out, n_out        records sorted by (node,pos): exactly the order the per-node std::sort of :1437 produces.
+ *                     Owned by the context until pmfs_result_free or the next run.
+ * Error behaviour: where the reference exit()s or asserts, this returns a status (PMFS_ERR_ROOT_INVALID, PMFS_ERR_ARG). */
+int pmfs_run(pmfs_ctx* ctx, int algo, const uint8_t* msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
+             int64_t n_cols, const uint8_t* consensus_code, const uint8_t* root_forced_code, pmfs_mut** out,
+             int64_t* n_out);
+void pmfs_result_free(pmfs_ctx* ctx, pmfs_mut* out);
+
+/* Device-resident variant (what `value` in bench.py times): every pointer is a DEVICE pointer on the context's
+ * device; msa row stride must be a multiple of 16 bytes and the base 16-byte aligned.  Records stay on the device,
+ * sorted by (node,pos); *d_out is owned by the context and valid until the next run. */
+int pmfs_run_device(pmfs_ctx* ctx, int algo, const uint8_t* d_msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
+                    int64_t n_cols, const uint8_t* d_consensus_code, const uint8_t* d_root_forced_code,
+                    pmfs_mut** d_out, int64_t* n_out);
+/* Copies device records of the last pmfs_run_device to a caller buffer of at least n_out records. */
+int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);
+
+int pmfs_get_timing(pmfs_ctx* ctx, pmfs_timing* t);
+
+/* Plan introspection (tests, DESIGN.md numbers). */
+typedef struct {
+    int32_t n_nodes, n_internal, n_leaves;
+    int32_t n_chunks, n_fwd_levels, n_bwd_levels;
+    int32_t fwd_stack_depth, bwd_stack_depth;
+    int32_t max_arity;
+    int64_t program_words;
+    int64_t edges_leaf;     /* parent->leaf edges */
+    int64_t edges_internal; /* parent->internal edges */
+} pmfs_plan_info;
+int pmfs_get_plan_info(pmfs_ctx* ctx, pmfs_plan_info* info);
+
+/* ---- synthetic alignments, generated on the device (bench and large-size tests) --------------------------
+ * Simulated evolution down the context's tree; a pure function of (seed, node, column), so any column range can be
+ * generated independently (column shards on different GPUs see the same global alignment). */
+typedef struct {
+    uint64_t seed;
+    float p_sub, p_del, p_ins; /* per branch, per column */
+    float p_n_block;           /* per leaf, per 32-column block: whole block becomes N */
+    float p_amb;               /* per leaf cell: one of the 10 two/three-base IUPAC codes */
+    float accessory_frac;      /* fraction of columns whose root state is gap */
+} pmfs_synth_spec;
+
+/* Fills d_msa_nibbles ([n_leaf_rows][row_stride_bytes], device) with columns [col_begin, col_begin+n_cols) of the
+ * synthetic alignment and d_consensus_code ([n_cols], device) with the first non-gap code in row order
+ * (the rule of src/panman.cpp:1326-1340 with rows in id order).  Every column has at least one non-gap cell. */
+int pmfs_synth_msa(pmfs_ctx* ctx, const pmfs_synth_spec* spec, int64_t col_begin, int64_t n_cols,
+                   uint8_t* d_msa_nibbles, int64_t row_stride_bytes, uint8_t* d_consensus_code);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PMFS_H */

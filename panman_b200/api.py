@@ -1,0 +1,218 @@
+"""ctypes bindings for libpmfs.so (include/pmfs.h).  Mirrors the C ABI one to one; no compute happens in Python."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from dataclasses import dataclass
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+FITCH, SANKOFF = 0, 1
+
+MUT_DTYPE = np.dtype([("node", "<i4"), ("pos", "<i4"), ("type", "u1"), ("code", "u1"), ("parent_code", "u1"), ("pad", "u1")])
+NUCMUT_DTYPE = np.dtype(
+    [("nucPosition", "<i4"), ("nucGapPosition", "<i4"), ("primaryBlockId", "<i4"), ("secondaryBlockId", "<i4"),
+     ("mutInfo", "<u4"), ("nucs", "<u4")]
+)
+
+
+class PmfsError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"pmfs status {status}: {msg}")
+        self.status = status
+
+
+def library_path() -> str:
+    return os.path.join(HERE, "libpmfs.so")
+
+
+def build_library(force: bool = False) -> str:
+    """Compile libpmfs.so for sm_100a (nvcc cross-compiles without a GPU)."""
+    # make is incremental: a no-op when the library is newer than its sources (the GPU box runs it on the prebuilt file)
+    subprocess.run(["make", "-C", os.path.join(HERE, "csrc")] + (["-B"] if force else []), check=True,
+                   stdout=subprocess.DEVNULL)
+    return library_path()
+
+
+class _Tree(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("parent", C.POINTER(C.c_int32)), ("child_off", C.POINTER(C.c_int32)),
+                ("child_idx", C.POINTER(C.c_int32)), ("leaf_row", C.POINTER(C.c_int32))]
+
+
+class _Timing(C.Structure):
+    _fields_ = [("h2d_ms", C.c_float), ("forward_ms", C.c_float), ("backward_ms", C.c_float), ("sort_ms", C.c_float),
+                ("d2h_ms", C.c_float), ("total_ms", C.c_float), ("n_launches", C.c_int64), ("forward_bytes", C.c_int64),
+                ("backward_bytes", C.c_int64)]
+
+
+class _PlanInfo(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("n_internal", C.c_int32), ("n_leaves", C.c_int32), ("n_chunks", C.c_int32),
+                ("n_fwd_levels", C.c_int32), ("n_bwd_levels", C.c_int32), ("fwd_stack_depth", C.c_int32),
+                ("bwd_stack_depth", C.c_int32), ("max_arity", C.c_int32), ("program_words", C.c_int64),
+                ("edges_leaf", C.c_int64), ("edges_internal", C.c_int64)]
+
+
+class _Synth(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("p_sub", C.c_float), ("p_del", C.c_float), ("p_ins", C.c_float),
+                ("p_n_block", C.c_float), ("p_amb", C.c_float), ("accessory_frac", C.c_float)]
+
+
+@dataclass
+class SynthSpec:
+    seed: int = 20251106
+    p_sub: float = 2e-5
+    p_del: float = 2e-6
+    p_ins: float = 1e-6
+    p_n_block: float = 1e-2
+    p_amb: float = 1e-4
+    accessory_frac: float = 0.0
+
+
+_lib = None
+
+EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run",
+           "pmfs_result_free", "pmfs_run_device", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
+           "pmfs_synth_msa"]
+
+
+def lib():
+    """Loads libpmfs.so; raises if it has not been built -- there is no fallback of any kind."""
+    global _lib
+    if _lib is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise ImportError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(make -C panman_b200/csrc).  panman_b200 has no CPU implementation.")
+        L = C.CDLL(path)
+        L.pmfs_last_error.restype = C.c_char_p
+        L.pmfs_version.restype = C.c_char_p
+        L.pmfs_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(_Tree), C.c_int]
+        L.pmfs_destroy.argtypes = [C.c_void_p]
+        L.pmfs_destroy.restype = None
+        L.pmfs_set_tuning.argtypes = [C.c_void_p, C.c_int32, C.c_int64]
+        L.pmfs_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.pmfs_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
+                               C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+        L.pmfs_result_free.argtypes = [C.c_void_p, C.c_void_p]
+        L.pmfs_result_free.restype = None
+        L.pmfs_run_device.argtypes = L.pmfs_run.argtypes
+        L.pmfs_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
+        L.pmfs_get_timing.argtypes = [C.c_void_p, C.POINTER(_Timing)]
+        L.pmfs_get_plan_info.argtypes = [C.c_void_p, C.POINTER(_PlanInfo)]
+        L.pmfs_synth_msa.argtypes = [C.c_void_p, C.POINTER(_Synth), C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise PmfsError(rc, lib().pmfs_last_error().decode())
+
+
+def pack_nibbles(codes: np.ndarray, row_stride: int | None = None) -> np.ndarray:
+    """[rows, cols] codes 0..15 -> [rows, row_stride] bytes, column 2j in the low nibble of byte j."""
+    c = np.asarray(codes, dtype=np.uint8)
+    rows, cols = c.shape
+    nb = (cols + 1) // 2
+    stride = nb if row_stride is None else row_stride
+    assert stride >= nb
+    out = np.zeros((rows, stride), dtype=np.uint8)
+    out[:, : cols // 2] = c[:, 0 : cols - (cols % 2) : 2] | (c[:, 1::2] << 4)
+    if cols % 2:
+        out[:, nb - 1] = c[:, cols - 1]
+    return out
+
+
+def unpack_nibbles(packed: np.ndarray, n_cols: int) -> np.ndarray:
+    p = np.asarray(packed, dtype=np.uint8)
+    out = np.empty((p.shape[0], p.shape[1] * 2), np.uint8)
+    out[:, 0::2] = p & 15
+    out[:, 1::2] = p >> 4
+    return out[:, :n_cols]
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+class Context:
+    """One tree on one GPU (pmfs_ctx).  `tree` needs .parent/.child_off/.child_idx/.leaf_row int32 arrays."""
+
+    def __init__(self, tree, device: int = 0):
+        self._L = lib()
+        self._keep = [_i32(tree.parent), _i32(tree.child_off), _i32(tree.child_idx), _i32(tree.leaf_row)]
+        t = _Tree(int(self._keep[0].shape[0]), *[a.ctypes.data_as(C.POINTER(C.c_int32)) for a in self._keep])
+        self._h = C.c_void_p()
+        _check(self._L.pmfs_create(C.byref(self._h), C.byref(t), device))
+        self.n_nodes = t.n_nodes
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._L.pmfs_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_tuning(self, chunk_nodes: int = 0, tile_cols: int = 0):
+        _check(self._L.pmfs_set_tuning(self._h, chunk_nodes, tile_cols))
+
+    def set_stream(self, cuda_stream: int = 0):
+        """Run on the given cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream); 0 = the context's own."""
+        _check(self._L.pmfs_set_stream(self._h, cuda_stream or None))
+
+    def run(self, algo: int, msa_nibbles: np.ndarray, n_cols: int, consensus: np.ndarray, forced=None) -> np.ndarray:
+        """Host buffers in, host records out (pmfs_run).  msa_nibbles: [rows, stride] uint8."""
+        msa = np.ascontiguousarray(msa_nibbles, dtype=np.uint8)
+        cons = np.ascontiguousarray(consensus, dtype=np.uint8)
+        assert cons.shape[0] == n_cols
+        frc = None if forced is None else np.ascontiguousarray(forced, dtype=np.uint8)
+        out, n = C.c_void_p(), C.c_int64()
+        stride = msa.shape[1] if msa.ndim == 2 and msa.shape[0] else (n_cols + 1) // 2
+        _check(self._L.pmfs_run(self._h, algo, msa.ctypes.data, stride, msa.shape[0], n_cols, cons.ctypes.data,
+                                None if frc is None else frc.ctypes.data, C.byref(out), C.byref(n)))
+        if n.value:
+            buf = (C.c_char * (n.value * MUT_DTYPE.itemsize)).from_address(out.value)
+            res = np.frombuffer(buf, dtype=MUT_DTYPE).copy()
+        else:
+            res = np.zeros(0, MUT_DTYPE)
+        self._L.pmfs_result_free(self._h, out)
+        return res
+
+    def run_device(self, algo: int, d_msa: int, row_stride: int, n_rows: int, n_cols: int, d_cons: int, d_forced: int = 0):
+        """Device pointers (ints) in; records stay on the device.  Returns (device pointer, count)."""
+        out, n = C.c_void_p(), C.c_int64()
+        _check(self._L.pmfs_run_device(self._h, algo, d_msa, row_stride, n_rows, n_cols, d_cons, d_forced or None,
+                                       C.byref(out), C.byref(n)))
+        return out.value, n.value
+
+    def download(self, n: int) -> np.ndarray:
+        res = np.zeros(n, MUT_DTYPE)
+        _check(self._L.pmfs_download(self._h, res.ctypes.data, n))
+        return res
+
+    def timing(self) -> dict:
+        t = _Timing()
+        _check(self._L.pmfs_get_timing(self._h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in _Timing._fields_}
+
+    def plan_info(self) -> dict:
+        p = _PlanInfo()
+        _check(self._L.pmfs_get_plan_info(self._h, C.byref(p)))
+        return {k: getattr(p, k) for k, _ in _PlanInfo._fields_}
+
+    def synth_msa(self, spec: SynthSpec, col_begin: int, n_cols: int, d_msa: int, row_stride: int, d_cons: int = 0):
+        s = _Synth(spec.seed, spec.p_sub, spec.p_del, spec.p_ins, spec.p_n_block, spec.p_amb, spec.accessory_frac)
+        _check(self._L.pmfs_synth_msa(self._h, C.byref(s), col_begin, n_cols, d_msa, row_stride, d_cons or None))

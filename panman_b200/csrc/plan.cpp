@@ -1,0 +1,245 @@
+// Plan builder: tree validation, chunking, walk-program emission.  Everything is iterative: ladders of depth 10^5 and
+// more (BASELINE config 5) would overflow the call stack -- the reference's own recursion does.
+#include "plan.hpp"
+
+#include <algorithm>
+#include <numeric>
+
+namespace pmfs {
+namespace {
+
+inline uint32_t op(uint32_t code, uint32_t arg) { return code | (arg << kOpBits); }
+
+}  // namespace
+
+std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
+    const int32_t V = t.n_nodes;
+    if (V < 2) return "tree needs at least a root and one child";
+    if (!t.parent || !t.child_off || !t.child_idx || !t.leaf_row) return "null tree array";
+    if (t.parent[0] != -1) return "node 0 must be the root (parent -1)";
+    if (t.child_off[0] != 0) return "child_off[0] must be 0";
+    if ((int64_t)V >= (int64_t)1 << 28) return "too many nodes";
+    for (int32_t v = 0; v < V; v++) {
+        if (t.child_off[v + 1] < t.child_off[v]) return "child_off not monotone";
+        if (v > 0 && (t.parent[v] < 0 || t.parent[v] >= v)) return "parent[i] must be in [0, i) (pre-order ids)";
+    }
+    if (t.child_off[V] != V - 1) return "child list must name every non-root node exactly once";
+    if (t.child_off[1] == 0) return "root must be an internal node";
+    {
+        std::vector<uint8_t> seen(V, 0);
+        for (int32_t v = 0; v < V; v++)
+            for (int32_t e = t.child_off[v]; e < t.child_off[v + 1]; e++) {
+                int32_t c = t.child_idx[e];
+                if (c <= 0 || c >= V || seen[c] || t.parent[c] != v) return "child_idx inconsistent with parent[]";
+                seen[c] = 1;
+            }
+    }
+
+    P = Plan();
+    P.n_nodes = V;
+    P.int_id.assign(V, -1);
+    int32_t max_row = -1;
+    for (int32_t v = 0; v < V; v++) {
+        int32_t k = t.child_off[v + 1] - t.child_off[v];
+        P.max_arity = std::max(P.max_arity, k);
+        if (k > 0) {
+            if (t.leaf_row[v] != -1) return "leaf_row must be -1 for internal nodes";
+            P.int_id[v] = P.n_internal++;
+            P.int_to_node.push_back(v);
+        } else {
+            if (t.leaf_row[v] < -2 || t.leaf_row[v] == -1) return "leaf_row of a leaf must be a row >= 0 or -2";
+            if ((int64_t)t.leaf_row[v] >= (int64_t)kAbsentLeaf >> 3) return "leaf_row too large";
+            max_row = std::max(max_row, t.leaf_row[v]);
+            P.n_leaves++;
+        }
+    }
+    P.row_to_node.assign((size_t)max_row + 1, -1);
+    for (int32_t v = 0; v < V; v++)
+        if (t.leaf_row[v] >= 0) {
+            // the reference keys every per-column map by NAME, so two leaves sharing a row would alias one entry
+            if (P.row_to_node[t.leaf_row[v]] != -1) return "two leaves map to the same MSA row";
+            P.row_to_node[t.leaf_row[v]] = v;
+            P.n_rows_used++;
+        }
+
+    // ---- chunking: rem[v] = nodes of v's subtree not yet cut off; cut v once rem[v] >= chunk_nodes
+    if (chunk_nodes < 2) chunk_nodes = 2;
+    std::vector<int32_t> rem(V, 1);
+    std::vector<uint8_t> cut(V, 0);
+    for (int32_t v = V - 1; v >= 1; v--) {
+        if (P.int_id[v] >= 0 && rem[v] >= chunk_nodes) {
+            cut[v] = 1;
+            rem[t.parent[v]] += 1;
+        } else {
+            rem[t.parent[v]] += rem[v];
+        }
+    }
+    cut[0] = 1;
+    std::vector<int32_t> chunk_of_root(V, -1);
+    for (int32_t v = 0; v < V; v++)
+        if (cut[v]) {
+            chunk_of_root[v] = (int32_t)P.chunks.size();
+            Chunk c;
+            c.root_node = v;
+            c.root_int = P.int_id[v];
+            P.chunks.push_back(c);
+        }
+    const int32_t NC = (int32_t)P.chunks.size();
+    // owner[v]: chunk whose program visits v as a member (a chunk root is a member of its own chunk)
+    std::vector<int32_t> owner(V, 0);
+    for (int32_t v = 1; v < V; v++) owner[v] = cut[v] ? chunk_of_root[v] : owner[t.parent[v]];
+    for (int32_t c = 1; c < NC; c++) P.chunks[c].depth = P.chunks[owner[t.parent[P.chunks[c].root_node]]].depth + 1;
+    for (int32_t c = NC - 1; c >= 1; c--) {
+        Chunk& par = P.chunks[owner[t.parent[P.chunks[c].root_node]]];
+        par.height = std::max(par.height, P.chunks[c].height + 1);
+    }
+
+    auto is_sub = [&](int32_t c) { return P.int_id[c] >= 0 && !cut[c]; };
+    auto operand = [&](int32_t c) -> uint32_t {
+        if (P.int_id[c] >= 0) return kOperandSet | (uint32_t)P.int_id[c];
+        return t.leaf_row[c] >= 0 ? (uint32_t)t.leaf_row[c] : kAbsentLeaf;
+    };
+
+    // ---- forward (post-order) programs
+    struct Frame {
+        int32_t v;
+        int32_t i;
+        bool pushed;
+        std::vector<int32_t> subs;
+    };
+    std::vector<Frame> st;
+    for (int32_t ci = 0; ci < NC; ci++) {
+        Chunk& ch = P.chunks[ci];
+        ch.fwd_off = (int64_t)P.fwd_prog.size();
+        int32_t depth = 0;
+        st.clear();
+        st.push_back({ch.root_node, -1, false, {}});
+        while (!st.empty()) {
+            Frame& f = st.back();
+            const int32_t v = f.v, b = t.child_off[v], e = t.child_off[v + 1];
+            if (f.i < 0) {
+                for (int32_t k = b; k < e; k++)
+                    if (is_sub(t.child_idx[k])) f.subs.push_back(t.child_idx[k]);
+                std::stable_sort(f.subs.begin(), f.subs.end(), [&](int32_t x, int32_t y) { return rem[x] > rem[y]; });
+                f.i = 0;
+            }
+            const bool binary = (e - b) == 2;
+            const int32_t ns = (int32_t)f.subs.size();
+            if (binary && ns == 2) {
+                if (f.i == 0) {
+                    f.i = 1;
+                    int32_t c = f.subs[0];
+                    st.push_back({c, -1, false, {}});
+                } else if (f.i == 1) {
+                    P.fwd_prog.push_back(op(F_PUSH, 0));
+                    P.fwd_stack_depth = std::max(P.fwd_stack_depth, ++depth);
+                    f.i = 2;
+                    int32_t c = f.subs[1];
+                    st.push_back({c, -1, false, {}});
+                } else {
+                    P.fwd_prog.push_back(op(F_JOIN_POP, (uint32_t)P.int_id[v]));
+                    depth--;
+                    st.pop_back();
+                }
+            } else if (binary && ns == 1) {
+                if (f.i == 0) {
+                    f.i = 1;
+                    int32_t c = f.subs[0];
+                    st.push_back({c, -1, false, {}});
+                } else {
+                    int32_t other = t.child_idx[b] == f.subs[0] ? t.child_idx[b + 1] : t.child_idx[b];
+                    P.fwd_prog.push_back(op(F_JOIN_IMM, (uint32_t)P.int_id[v]));
+                    P.fwd_prog.push_back(operand(other));
+                    st.pop_back();
+                }
+            } else if (binary) {
+                P.fwd_prog.push_back(op(F_JOIN_IMM2, (uint32_t)P.int_id[v]));
+                P.fwd_prog.push_back(operand(t.child_idx[b]));
+                P.fwd_prog.push_back(operand(t.child_idx[b + 1]));
+                st.pop_back();
+            } else {
+                if (f.i < ns) {
+                    int32_t c = f.subs[f.i++];
+                    st.push_back({c, -1, false, {}});
+                } else {
+                    P.fwd_prog.push_back(op(F_POLY, (uint32_t)P.int_id[v]));
+                    P.fwd_prog.push_back((uint32_t)(e - b));
+                    for (int32_t k = b; k < e; k++) P.fwd_prog.push_back(operand(t.child_idx[k]));
+                    st.pop_back();
+                }
+            }
+        }
+        ch.fwd_len = (int32_t)((int64_t)P.fwd_prog.size() - ch.fwd_off);
+    }
+
+    // ---- backward (pre-order) programs
+    for (int32_t ci = 0; ci < NC; ci++) {
+        Chunk& ch = P.chunks[ci];
+        ch.bwd_off = (int64_t)P.bwd_prog.size();
+        int32_t depth = 0;
+        st.clear();
+        st.push_back({ch.root_node, -1, false, {}});
+        while (!st.empty()) {
+            Frame& f = st.back();
+            const int32_t v = f.v, b = t.child_off[v], e = t.child_off[v + 1];
+            if (f.i < 0) {
+                P.bwd_prog.push_back(v == 0 ? op(B_ENTER_ROOT, 0) : op(B_ENTER, (uint32_t)P.int_id[v]));
+                for (int32_t k = b; k < e; k++) {
+                    int32_t c = t.child_idx[k];
+                    if (P.int_id[c] < 0) {
+                        if (t.leaf_row[c] >= 0) P.bwd_prog.push_back(op(B_LEAF, (uint32_t)t.leaf_row[c]));
+                    } else if (cut[c]) {
+                        P.bwd_prog.push_back(op(B_XCHILD, (uint32_t)chunk_of_root[c]));
+                    } else {
+                        f.subs.push_back(c);
+                    }
+                }
+                std::stable_sort(f.subs.begin(), f.subs.end(), [&](int32_t x, int32_t y) { return rem[x] < rem[y]; });
+                f.i = 0;
+            }
+            if (f.pushed) {
+                P.bwd_prog.push_back(op(B_POPP, 0));
+                depth--;
+                f.pushed = false;
+            }
+            if (f.i < (int32_t)f.subs.size()) {
+                int32_t c = f.subs[f.i];
+                bool last = f.i + 1 == (int32_t)f.subs.size();
+                f.i++;
+                if (!last) {
+                    P.bwd_prog.push_back(op(B_PUSHP, 0));
+                    P.bwd_stack_depth = std::max(P.bwd_stack_depth, ++depth);
+                    f.pushed = true;
+                }
+                st.push_back({c, -1, false, {}});  // invalidates f
+            } else {
+                st.pop_back();
+            }
+        }
+        ch.bwd_len = (int32_t)((int64_t)P.bwd_prog.size() - ch.bwd_off);
+    }
+
+    // ---- level lists
+    auto make_levels = [&](bool fwd, std::vector<int32_t>& order, std::vector<int32_t>& off) {
+        int32_t nl = 0;
+        for (auto& c : P.chunks) nl = std::max(nl, (fwd ? c.height : c.depth) + 1);
+        order.resize(NC);
+        std::iota(order.begin(), order.end(), 0);
+        std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
+            int32_t lx = fwd ? P.chunks[x].height : P.chunks[x].depth, ly = fwd ? P.chunks[y].height : P.chunks[y].depth;
+            if (lx != ly) return lx < ly;
+            int32_t wx = fwd ? P.chunks[x].fwd_len : P.chunks[x].bwd_len, wy = fwd ? P.chunks[y].fwd_len : P.chunks[y].bwd_len;
+            return wx > wy;
+        });
+        off.assign(nl + 1, 0);
+        for (auto& c : P.chunks) off[(fwd ? c.height : c.depth) + 1]++;
+        for (int32_t l = 0; l < nl; l++) off[l + 1] += off[l];
+    };
+    make_levels(true, P.fwd_order, P.fwd_lvl_off);
+    make_levels(false, P.bwd_order, P.bwd_lvl_off);
+
+    for (int32_t v = 1; v < V; v++) (P.int_id[v] >= 0 ? P.edges_internal : P.edges_leaf)++;
+    return "";
+}
+
+}  // namespace pmfs

@@ -1,0 +1,71 @@
+// Host-side execution plan for one tree: the flat, device-friendly stand-in for the Node* graph the reference walks
+// recursively (src/fitchSankoff.cpp:30-171, :359-531, :676-703 in /root/reference).
+//
+// The tree is cut into CHUNKS (connected pieces, each rooted at an internal node).  For every chunk the plan holds two
+// straight-line "walk programs" -- one bottom-up (post-order), one top-down (pre-order) -- that every GPU thread
+// executes in lock step on its own 32 alignment columns: the tree is the instruction stream, the columns are the lanes.
+// Chunks whose inputs come from other chunks are ordered by levels (height for the bottom-up pass, depth for the
+// top-down pass); chunks of one level are independent and run as one grid.
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/pmfs.h"
+
+namespace pmfs {
+
+// ---- walk-program encoding: one 32-bit word per op = opcode (low 3 bits) | argument << 3; some ops are followed by
+// operand words.  A forward operand word names a child's state set: bit 31 set -> row `w & 0x7fffffff` of the
+// internal-node set array, else MSA row `w`; kAbsentLeaf is a leaf with no MSA row (empty set).
+constexpr uint32_t kOpBits = 3;
+constexpr uint32_t kOperandSet = 0x80000000u;
+constexpr uint32_t kAbsentLeaf = 0x7fffffffu;
+
+enum FwdOp : uint32_t {
+    F_PUSH = 0,       // push the running set T on the per-thread stack
+    F_JOIN_POP = 1,   // arg = internal id v:  T = join(pop(), T);            store set[v]
+    F_JOIN_IMM = 2,   // arg = v, 1 operand:   T = join(T, operand);          store set[v]
+    F_JOIN_IMM2 = 3,  // arg = v, 2 operands:  T = join(operand0, operand1);  store set[v]
+    F_POLY = 4,       // arg = v, next word = k, then k operands: any arity (1, >=3); children re-read from memory
+};
+
+enum BwdOp : uint32_t {
+    B_ENTER = 0,       // arg = internal id v: resolve v against the parent state P, emit, then P := state(v)
+    B_ENTER_ROOT = 1,  // arg = 0: the tree root (P holds the consensus)
+    B_LEAF = 2,        // arg = MSA row: resolve + emit a present leaf against P
+    B_XCHILD = 3,      // arg = chunk id: publish P for the child chunk rooted below this node
+    B_PUSHP = 4,       // save P before descending into a non-last subtree
+    B_POPP = 5,        // restore P
+};
+
+struct Chunk {
+    int32_t root_node = 0;  // node id of the chunk root (always internal)
+    int32_t root_int = 0;   // its internal id
+    int64_t fwd_off = 0, bwd_off = 0;
+    int32_t fwd_len = 0, bwd_len = 0;
+    int32_t height = 0;  // 0 = no child chunks
+    int32_t depth = 0;   // 0 = contains the tree root
+};
+
+struct Plan {
+    int32_t n_nodes = 0, n_internal = 0, n_leaves = 0, n_rows_used = 0;
+    int32_t max_arity = 0;
+    std::vector<int32_t> int_id;       // [V] internal id or -1
+    std::vector<int32_t> int_to_node;  // [I]
+    std::vector<int32_t> row_to_node;  // [max row + 1] node id or -1
+    std::vector<uint32_t> fwd_prog, bwd_prog;
+    std::vector<Chunk> chunks;
+    // chunk ids grouped by level, heaviest first inside a level; level l spans [lvl_off[l], lvl_off[l+1])
+    std::vector<int32_t> fwd_order, bwd_order;
+    std::vector<int32_t> fwd_lvl_off, bwd_lvl_off;
+    int32_t fwd_stack_depth = 0, bwd_stack_depth = 0;
+    int64_t edges_leaf = 0, edges_internal = 0;
+};
+
+// Validates `tree` and builds the plan.  chunk_nodes: cut a subtree off as its own chunk once it holds at least this
+// many not-yet-cut nodes.  Returns an empty string or an error description.
+std::string build_plan(const pmfs_tree& tree, int32_t chunk_nodes, Plan& plan);
+
+}  // namespace pmfs

@@ -1,0 +1,905 @@
+// libpmfs: CUDA kernels (sm_100a) + C ABI (include/pmfs.h).
+//
+// Kernels
+//   fwd_kernel<ALGO,POLY>   bottom-up walk of one chunk level: grid = chunks of the level x column tiles of kTPB groups
+//   bwd_kernel<ALGO>        top-down walk of one chunk level + mutation emission (warp-aggregated stream compaction)
+//   prep_planes_kernel      consensus / forced-root codes -> bit-sliced code planes in the walk's bit order
+//   assemble_kernel         sorted (key,value) pairs -> pmfs_mut records
+//   synth_* kernels         synthetic alignments
+// HBM layout: MSA rows of packed nibbles (16 B per thread per leaf); set arrays S (and D1 for Sankoff)
+// [internal id][4][G] uint4, i.e. for one node the 4 quarter-sets of all column groups are contiguous, so a warp's
+// 128-bit loads and stores are fully coalesced 512 B segments.
+#include <cuda_runtime.h>
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/pmfs.h"
+#include "plan.hpp"
+#include "walk.cuh"
+
+namespace pmfs {
+
+constexpr int kTPB = 128;  // threads (= column groups) per CTA
+
+static thread_local std::string g_error;
+
+#define PMFS_CUDA(call)                                                                             \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess) {                                                                    \
+            g_error = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+            return e_ == cudaErrorMemoryAllocation ? PMFS_ERR_NOMEM : PMFS_ERR_CUDA;                \
+        }                                                                                           \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------ device environment
+struct WalkParams {
+    const uint32_t* prog;       // fwd or bwd program words
+    const int64_t* chunk_off;   // [NC] offset of each chunk's program
+    const int32_t* chunk_len;   // [NC]
+    const int32_t* order;       // chunk ids of this launch's level
+    int32_t ctas_per_chunk;
+    int32_t stack_depth;
+    const uint4* msa;           // first group of this column tile
+    int64_t msa_stride16;       // uint4 per MSA row
+    uint4* S;                   // [I][4][G]
+    uint4* D;                   // Sankoff only
+    int64_t G;                  // column groups in this tile
+    int64_t tile_cols;          // real columns in this tile
+    int64_t col_base;           // global column of the tile's first column
+    const uint4* cons_planes;   // [G]
+    const uint4* forced_planes; // [G] or null
+    uint4* xcode;               // [NC][G] parent state per chunk root
+    uint32_t* xvalid;           // [NC][G]
+    const int32_t* int_to_node;
+    const int32_t* row_to_node;
+    unsigned long long* out_keys;
+    uint32_t* out_vals;
+    unsigned long long* out_count;
+    unsigned long long out_cap;
+    unsigned int* err_flag;
+};
+
+template <bool READONLY_SETS>
+struct DevEnv {
+    const WalkParams& p;
+    int64_t g;   // clamped column group
+    bool active;
+    uint4* fstk;      // [depth][4][kTPB]
+    uint32_t* bstk;   // [depth][5][kTPB]
+    int sp = 0;
+    int lane;
+
+    __device__ DevEnv(const WalkParams& p_, int64_t g_, bool a, void* smem)
+        : p(p_), g(g_), active(a), fstk((uint4*)smem), bstk((uint32_t*)smem), lane(threadIdx.x & 31) {}
+
+    __device__ __forceinline__ uint32_t word(const uint32_t* prog, int32_t pc) const { return __ldg(prog + pc); }
+    __device__ __forceinline__ uint4 leaf(uint32_t row) const { return __ldg(p.msa + (int64_t)row * p.msa_stride16 + g); }
+
+    __device__ __forceinline__ void load_arr(const uint4* base, uint32_t id, Planes16& s) const {
+        const uint4* q = base + ((int64_t)id * 4) * p.G + g;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            uint4 v = READONLY_SETS ? __ldg(q + (int64_t)i * p.G) : q[(int64_t)i * p.G];
+            s.p[4 * i] = v.x; s.p[4 * i + 1] = v.y; s.p[4 * i + 2] = v.z; s.p[4 * i + 3] = v.w;
+        }
+    }
+    __device__ __forceinline__ void store_arr(uint4* base, uint32_t id, const Planes16& s) const {
+        if (!active) return;
+        uint4* q = base + ((int64_t)id * 4) * p.G + g;
+#pragma unroll
+        for (int i = 0; i < 4; i++) q[(int64_t)i * p.G] = make_uint4(s.p[4 * i], s.p[4 * i + 1], s.p[4 * i + 2], s.p[4 * i + 3]);
+    }
+    __device__ __forceinline__ void load_s(uint32_t id, Planes16& s) const { load_arr(p.S, id, s); }
+    __device__ __forceinline__ void load_d(uint32_t id, Planes16& s) const { load_arr(p.D, id, s); }
+    __device__ __forceinline__ void store_s(uint32_t id, const Planes16& s) const { store_arr(p.S, id, s); }
+    __device__ __forceinline__ void store_d(uint32_t id, const Planes16& s) const { store_arr(p.D, id, s); }
+
+    __device__ __forceinline__ void push(const Planes16& s) {
+        uint4* q = fstk + (sp * 4) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int i = 0; i < 4; i++) q[i * kTPB] = make_uint4(s.p[4 * i], s.p[4 * i + 1], s.p[4 * i + 2], s.p[4 * i + 3]);
+        sp++;
+    }
+    __device__ __forceinline__ void pop(Planes16& s) {
+        sp--;
+        const uint4* q = fstk + (sp * 4) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            uint4 v = q[i * kTPB];
+            s.p[4 * i] = v.x; s.p[4 * i + 1] = v.y; s.p[4 * i + 2] = v.z; s.p[4 * i + 3] = v.w;
+        }
+    }
+    __device__ __forceinline__ void pushp(const Code4& c, uint32_t pv) {
+        uint32_t* q = bstk + (sp * 5) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int i = 0; i < 4; i++) q[i * kTPB] = c.b[i];
+        q[4 * kTPB] = pv;
+        sp++;
+    }
+    __device__ __forceinline__ void popp(Code4& c, uint32_t& pv) {
+        sp--;
+        const uint32_t* q = bstk + (sp * 5) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int i = 0; i < 4; i++) c.b[i] = q[i * kTPB];
+        pv = q[4 * kTPB];
+    }
+    __device__ __forceinline__ void store_x(uint32_t chunk, const Code4& c, uint32_t pv) const {
+        if (!active) return;
+        p.xcode[(int64_t)chunk * p.G + g] = make_uint4(c.b[0], c.b[1], c.b[2], c.b[3]);
+        p.xvalid[(int64_t)chunk * p.G + g] = pv;
+    }
+    __device__ __forceinline__ bool any(bool x) const { return __any_sync(0xffffffffu, x); }
+
+    // Stream compaction of one node's mutations: per-lane counts -> warp prefix sum (shuffles) -> ONE atomic per warp
+    // reserves the slots -> each lane writes its records.  Order inside the buffer is scheduling dependent; the final
+    // radix sort by (node,pos) makes the result deterministic.
+    __device__ void emit(uint32_t node, uint32_t m, const Code4& G, const Code4& P) const {
+        const int cnt = __popc(m);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int x = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += x;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        unsigned long long base = 0;
+        if (lane == 31) base = atomicAdd(p.out_count, (unsigned long long)total);
+        base = __shfl_sync(0xffffffffu, base, 31);
+        unsigned long long idx = base + (unsigned long long)(incl - cnt);
+        while (m) {
+            const int q = __ffs(m) - 1;
+            m &= m - 1;
+            if (idx < p.out_cap) {
+                const uint32_t cg = ((G.b[0] >> q) & 1) | (((G.b[1] >> q) & 1) << 1) | (((G.b[2] >> q) & 1) << 2) | (((G.b[3] >> q) & 1) << 3);
+                const uint32_t cp = ((P.b[0] >> q) & 1) | (((P.b[1] >> q) & 1) << 1) | (((P.b[2] >> q) & 1) << 2) | (((P.b[3] >> q) & 1) << 3);
+                // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
+                const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
+                const unsigned long long pos = (unsigned long long)(p.col_base + g * 32 + column_of_bit(q));
+                p.out_keys[idx] = ((unsigned long long)node << 32) | pos;
+                p.out_vals[idx] = type | (cg << 8) | (cp << 16);
+            }
+            idx++;
+        }
+    }
+    __device__ __forceinline__ void emit_internal(uint32_t id, uint32_t m, const Code4& G, const Code4& P) const {
+        emit((uint32_t)__ldg(p.int_to_node + id), m, G, P);
+    }
+    __device__ __forceinline__ void emit_leaf(uint32_t row, uint32_t m, const Code4& G, const Code4& P) const {
+        emit((uint32_t)__ldg(p.row_to_node + row), m, G, P);
+    }
+};
+
+__device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_cols) {
+    int64_t n = tile_cols - g * 32;
+    if (n >= 32) return ~0u;
+    uint32_t m = 0;
+    for (int q = 0; q < 32; q++)
+        if (column_of_bit(q) < n) m |= 1u << q;
+    return m;
+}
+
+template <int ALGO, bool POLY>
+__global__ void __launch_bounds__(kTPB) fwd_kernel(const WalkParams p) {
+    extern __shared__ uint4 smem[];
+    const int32_t chunk = p.order[blockIdx.x / p.ctas_per_chunk];
+    const int64_t g0 = (int64_t)(blockIdx.x % p.ctas_per_chunk) * kTPB + threadIdx.x;
+    const bool active = g0 < p.G;
+    const int64_t g = active ? g0 : p.G - 1;
+    DevEnv<false> env(p, g, active, smem);
+    Code4 forced;
+    const Code4* fp = nullptr;
+    if (ALGO == kAlgoFitch && p.forced_planes) {
+        uint4 v = __ldg(p.forced_planes + g);
+        forced.b[0] = v.x; forced.b[1] = v.y; forced.b[2] = v.z; forced.b[3] = v.w;
+        fp = &forced;
+    }
+    forward_walk<ALGO, POLY>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], fp);
+}
+
+template <int ALGO>
+__global__ void __launch_bounds__(kTPB) bwd_kernel(const WalkParams p) {
+    extern __shared__ uint4 smem[];
+    const int32_t chunk = p.order[blockIdx.x / p.ctas_per_chunk];
+    const int64_t g0 = (int64_t)(blockIdx.x % p.ctas_per_chunk) * kTPB + threadIdx.x;
+    const bool active = g0 < p.G;
+    const int64_t g = active ? g0 : p.G - 1;
+    DevEnv<true> env(p, g, active, smem);
+    Code4 P, forced;
+    uint32_t pv = ~0u;
+    const Code4* fp = nullptr;
+    if (chunk == 0) {
+        uint4 v = __ldg(p.cons_planes + g);
+        P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
+        if (ALGO == kAlgoSankoff && p.forced_planes) {
+            uint4 f = __ldg(p.forced_planes + g);
+            forced.b[0] = f.x; forced.b[1] = f.y; forced.b[2] = f.z; forced.b[3] = f.w;
+            fp = &forced;
+        }
+    } else {
+        uint4 v = p.xcode[(int64_t)chunk * p.G + g];
+        P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
+        pv = p.xvalid[(int64_t)chunk * p.G + g];
+    }
+    const uint32_t colmask = active ? real_column_mask(g, p.tile_cols) : 0u;
+    const uint32_t err = backward_walk<ALGO>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], P, pv, fp, colmask);
+    if (err) atomicOr(p.err_flag, 1u);
+}
+
+// codes[col_base .. col_base+tile_cols) -> planes[G] in the bit order of transpose_nibbles
+__global__ void prep_planes_kernel(const uint8_t* __restrict__ codes, int64_t tile_cols, int64_t G, uint4* __restrict__ planes) {
+    int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    uint32_t b[4] = {0, 0, 0, 0};
+    for (int q = 0; q < 32; q++) {
+        int64_t col = g * 32 + column_of_bit(q);
+        uint32_t c = col < tile_cols ? (codes[col] & 15u) : 0u;
+#pragma unroll
+        for (int i = 0; i < 4; i++) b[i] |= ((c >> i) & 1u) << q;
+    }
+    planes[g] = make_uint4(b[0], b[1], b[2], b[3]);
+}
+
+__global__ void assemble_kernel(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
+                                pmfs_mut* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long k = keys[i];
+    uint32_t v = vals[i];
+    pmfs_mut m;
+    m.node = (int32_t)(k >> 32);
+    m.pos = (int32_t)(k & 0xffffffffu);
+    m.type = (uint8_t)(v & 0xff);
+    m.code = (uint8_t)((v >> 8) & 0xff);
+    m.parent_code = (uint8_t)((v >> 16) & 0xff);
+    m.pad = 0;
+    out[i] = m;
+}
+
+// ------------------------------------------------------------------------------------------------ synthetic alignments
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {  // splitmix64 finaliser
+    x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
+    x ^= x >> 27; x *= 0x94d049bb133111ebull;
+    x ^= x >> 31;
+    return x;
+}
+__host__ __device__ __forceinline__ uint32_t hash3(uint64_t seed, uint64_t a, uint64_t b) {
+    return (uint32_t)(mix64(seed ^ mix64(a * 0x9e3779b97f4a7c15ull + b)) >> 32);
+}
+
+struct SynthParams {
+    uint64_t seed;
+    uint32_t t_sub, t_del, t_ins, t_nblock, t_amb, t_acc;  // thresholds on a 32-bit hash
+    const int32_t* path_off;   // [rows+1] CSR: nodes on the root->leaf path of each row's leaf (root excluded)
+    const int32_t* path_node;
+    int32_t n_rows;
+    int64_t col_begin, n_cols;
+    uint8_t* msa;
+    int64_t row_stride;
+};
+
+__device__ __forceinline__ uint32_t synth_cell(const SynthParams& s, int32_t row, int64_t col) {
+    const uint32_t base4[4] = {1, 2, 4, 8};
+    uint32_t r = hash3(s.seed, 0x1000000000ull, (uint64_t)col);
+    // root: A .30 C .18 G .20 T .32, or gap in accessory columns
+    uint32_t u = r >> 8, st;
+    if (hash3(s.seed, 0x2000000000ull, (uint64_t)col) < s.t_acc) st = 0;
+    else st = u < 5033165u ? 1 : (u < 8053064u ? 2 : (u < 11408507u ? 4 : 8));
+    for (int32_t e = s.path_off[row]; e < s.path_off[row + 1]; e++) {
+        uint32_t h = hash3(s.seed, (uint64_t)s.path_node[e], (uint64_t)col);
+        if (st != 0) {
+            if (h < s.t_sub) {
+                uint32_t nb = base4[(h >> 3) & 3];
+                st = nb == st ? base4[((h >> 3) + 1) & 3] : nb;
+            } else if (h - s.t_sub < s.t_del) {
+                st = 0;
+            }
+        } else if (h < s.t_ins) {
+            st = base4[(h >> 5) & 3];
+        }
+    }
+    // leaf-only noise
+    if (hash3(s.seed, 0x3000000000ull + (uint64_t)row, (uint64_t)(col >> 5)) < s.t_nblock) st = 15;
+    else {
+        uint32_t h = hash3(s.seed, 0x4000000000ull + (uint64_t)row, (uint64_t)col);
+        if (h < s.t_amb) {
+            const uint32_t amb[10] = {3, 5, 6, 7, 9, 10, 11, 12, 13, 14};
+            st = amb[(h >> 7) % 10];
+        }
+    }
+    // guarantee: one designated row per column is never a gap
+    if (st == 0 && (uint32_t)(hash3(s.seed, 0x5000000000ull, (uint64_t)col) % (uint32_t)s.n_rows) == (uint32_t)row)
+        st = base4[r & 3];
+    return st;
+}
+
+// one thread = one (row, 8-column word)
+__global__ void synth_msa_kernel(const SynthParams s) {
+    const int64_t words_per_row = (s.n_cols + 7) / 8;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= words_per_row * s.n_rows) return;
+    const int32_t row = (int32_t)(i / words_per_row);
+    const int64_t w = i % words_per_row;
+    uint32_t out = 0;
+    for (int k = 0; k < 8; k++) {
+        int64_t c = w * 8 + k;
+        if (c < s.n_cols) out |= synth_cell(s, row, s.col_begin + c) << (4 * k);
+    }
+    *(uint32_t*)(s.msa + (int64_t)row * s.row_stride + w * 4) = out;
+}
+
+// first non-gap code in row order (src/panman.cpp:1326-1340 with rows in id order)
+__global__ void synth_consensus_kernel(const uint8_t* __restrict__ msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                                       uint8_t* __restrict__ cons) {
+    int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_cols) return;
+    uint32_t code = 0;
+    for (int32_t r = 0; r < n_rows && code == 0; r++) code = (msa[(int64_t)r * row_stride + (c >> 1)] >> ((c & 1) * 4)) & 15u;
+    cons[c] = (uint8_t)code;
+}
+
+// ------------------------------------------------------------------------------------------------ context
+template <class T>
+struct DevBuf {
+    T* ptr = nullptr;
+    size_t cap = 0;  // elements
+    int ensure(size_t n) {
+        if (n <= cap) return PMFS_OK;
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&ptr, std::max<size_t>(n, 1) * sizeof(T));
+        if (e != cudaSuccess) {
+            g_error = std::string("cudaMalloc(") + std::to_string(n * sizeof(T)) + " B): " + cudaGetErrorString(e);
+            cudaGetLastError();
+            return PMFS_ERR_NOMEM;
+        }
+        cap = n;
+        return PMFS_OK;
+    }
+    void release() {
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        cap = 0;
+    }
+};
+
+}  // namespace pmfs
+
+using namespace pmfs;
+
+struct pmfs_ctx {
+    int device = 0;
+    Plan plan;
+    bool has_poly = false;
+    int32_t chunk_nodes_used = 0;
+    std::vector<int32_t> parent, child_off, child_idx, leaf_row;  // kept for re-planning and synth
+    int32_t tune_chunk_nodes = 0;
+    int64_t tune_tile_cols = 0;
+    cudaStream_t stream = nullptr;      // stream in use
+    cudaStream_t own_stream = nullptr;  // created by pmfs_create
+    cudaEvent_t ev[8] = {};
+    // plan on device
+    DevBuf<uint32_t> d_fwd_prog, d_bwd_prog;
+    DevBuf<int64_t> d_fwd_off, d_bwd_off;
+    DevBuf<int32_t> d_fwd_len, d_bwd_len, d_fwd_order, d_bwd_order, d_int_to_node, d_row_to_node;
+    // per-run state
+    DevBuf<uint4> d_S, d_D, d_cons_planes, d_forced_planes, d_xcode;
+    DevBuf<uint32_t> d_xvalid;
+    DevBuf<unsigned long long> d_keys, d_keys_alt;
+    DevBuf<uint32_t> d_vals, d_vals_alt;
+    DevBuf<unsigned long long> d_count;
+    DevBuf<unsigned int> d_err;
+    DevBuf<uint8_t> d_sort_tmp;
+    DevBuf<pmfs_mut> d_out;
+    // host-path staging
+    DevBuf<uint8_t> d_msa, d_cons, d_forced;
+    std::vector<pmfs_mut*> host_results;
+    int64_t last_n_out = 0;
+    pmfs_timing timing = {};
+    // synth
+    DevBuf<int32_t> d_path_off, d_path_node;
+    bool synth_ready = false;
+};
+
+static int upload_plan(pmfs_ctx* c) {
+    const Plan& P = c->plan;
+    const size_t NC = P.chunks.size();
+    std::vector<int64_t> foff(NC), boff(NC);
+    std::vector<int32_t> flen(NC), blen(NC);
+    for (size_t i = 0; i < NC; i++) {
+        foff[i] = P.chunks[i].fwd_off; flen[i] = P.chunks[i].fwd_len;
+        boff[i] = P.chunks[i].bwd_off; blen[i] = P.chunks[i].bwd_len;
+    }
+    auto up = [&](auto& buf, const auto& v) -> int {
+        int rc = buf.ensure(v.size());
+        if (rc) return rc;
+        if (!v.empty()) PMFS_CUDA(cudaMemcpy(buf.ptr, v.data(), v.size() * sizeof(v[0]), cudaMemcpyHostToDevice));
+        return PMFS_OK;
+    };
+    int rc;
+    if ((rc = up(c->d_fwd_prog, P.fwd_prog))) return rc;
+    if ((rc = up(c->d_bwd_prog, P.bwd_prog))) return rc;
+    if ((rc = up(c->d_fwd_off, foff))) return rc;
+    if ((rc = up(c->d_bwd_off, boff))) return rc;
+    if ((rc = up(c->d_fwd_len, flen))) return rc;
+    if ((rc = up(c->d_bwd_len, blen))) return rc;
+    if ((rc = up(c->d_fwd_order, P.fwd_order))) return rc;
+    if ((rc = up(c->d_bwd_order, P.bwd_order))) return rc;
+    if ((rc = up(c->d_int_to_node, P.int_to_node))) return rc;
+    if ((rc = up(c->d_row_to_node, P.row_to_node))) return rc;
+    return PMFS_OK;
+}
+
+static int replan(pmfs_ctx* c, int32_t chunk_nodes) {
+    pmfs_tree t;
+    t.n_nodes = (int32_t)c->parent.size();
+    t.parent = c->parent.data();
+    t.child_off = c->child_off.data();
+    t.child_idx = c->child_idx.data();
+    t.leaf_row = c->leaf_row.data();
+    std::string err = build_plan(t, chunk_nodes, c->plan);
+    if (!err.empty()) {
+        g_error = "pmfs_create: " + err;
+        return PMFS_ERR_ARG;
+    }
+    c->has_poly = false;
+    for (int32_t v = 0; v < t.n_nodes; v++)
+        if (t.child_off[v + 1] - t.child_off[v] != 0 && t.child_off[v + 1] - t.child_off[v] != 2) c->has_poly = true;
+    c->chunk_nodes_used = chunk_nodes;
+    return upload_plan(c);
+}
+
+// chunk size such that one chunk level offers a few waves of CTAs (148 SMs) for `groups` column groups
+static int32_t auto_chunk_nodes(int32_t n_nodes, int64_t groups) {
+    int64_t ctas_per_chunk = (groups + kTPB - 1) / kTPB;
+    int64_t want_chunks = std::max<int64_t>(1, (148 * 8 + ctas_per_chunk - 1) / ctas_per_chunk);
+    int64_t cn = n_nodes / (want_chunks * 2);  // chunks end up between cn and 2*cn nodes
+    return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 64), 1 << 16);
+}
+
+extern "C" {
+
+const char* pmfs_last_error(void) { return g_error.c_str(); }
+const char* pmfs_version(void) { return "pmfs 0.1 (sm_100a)"; }
+
+int pmfs_create(pmfs_ctx** out, const pmfs_tree* tree, int device) {
+    if (!out || !tree) {
+        g_error = "pmfs_create: null argument";
+        return PMFS_ERR_ARG;
+    }
+    *out = nullptr;
+    // validate before touching CUDA so that malformed trees are reported even without a device
+    {
+        Plan tmp;
+        std::string err = build_plan(*tree, 1 << 30, tmp);
+        if (!err.empty()) {
+            g_error = "pmfs_create: " + err;
+            return PMFS_ERR_ARG;
+        }
+    }
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) {
+        cudaGetLastError();
+        g_error = "pmfs_create: no CUDA device available (this library has no CPU path)";
+        return PMFS_ERR_CUDA;
+    }
+    if (device < 0 || device >= n_dev) {
+        g_error = "pmfs_create: bad device index";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(device));
+    pmfs_ctx* c = new pmfs_ctx();
+    c->device = device;
+    const int32_t V = tree->n_nodes;
+    c->parent.assign(tree->parent, tree->parent + V);
+    c->child_off.assign(tree->child_off, tree->child_off + V + 1);
+    c->child_idx.assign(tree->child_idx, tree->child_idx + tree->child_off[V]);
+    c->leaf_row.assign(tree->leaf_row, tree->leaf_row + V);
+    cudaError_t se = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (se != cudaSuccess) {
+        g_error = std::string("cudaStreamCreate: ") + cudaGetErrorString(se);
+        delete c;
+        return PMFS_ERR_CUDA;
+    }
+    c->own_stream = c->stream;
+    for (auto& ev : c->ev) cudaEventCreate(&ev);
+    int rc = replan(c, auto_chunk_nodes(V, 1024));
+    if (rc) {
+        pmfs_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return PMFS_OK;
+}
+
+void pmfs_destroy(pmfs_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->d_fwd_prog.release(); c->d_bwd_prog.release(); c->d_fwd_off.release(); c->d_bwd_off.release();
+    c->d_fwd_len.release(); c->d_bwd_len.release(); c->d_fwd_order.release(); c->d_bwd_order.release();
+    c->d_int_to_node.release(); c->d_row_to_node.release();
+    c->d_S.release(); c->d_D.release(); c->d_cons_planes.release(); c->d_forced_planes.release();
+    c->d_xcode.release(); c->d_xvalid.release(); c->d_keys.release(); c->d_keys_alt.release();
+    c->d_vals.release(); c->d_vals_alt.release(); c->d_count.release(); c->d_err.release();
+    c->d_sort_tmp.release(); c->d_out.release(); c->d_msa.release(); c->d_cons.release(); c->d_forced.release();
+    c->d_path_off.release(); c->d_path_node.release();
+    for (auto* p : c->host_results) cudaFreeHost(p);
+    for (auto& ev : c->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+}
+
+int pmfs_set_tuning(pmfs_ctx* c, int32_t chunk_nodes, int64_t tile_cols) {
+    if (!c || chunk_nodes < 0 || tile_cols < 0) {
+        g_error = "pmfs_set_tuning: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    c->tune_chunk_nodes = chunk_nodes;
+    c->tune_tile_cols = tile_cols;
+    return PMFS_OK;
+}
+
+int pmfs_set_stream(pmfs_ctx* c, void* cuda_stream) {
+    if (!c) return PMFS_ERR_ARG;
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return PMFS_OK;
+}
+
+int pmfs_get_plan_info(pmfs_ctx* c, pmfs_plan_info* info) {
+    if (!c || !info) return PMFS_ERR_ARG;
+    const Plan& P = c->plan;
+    info->n_nodes = P.n_nodes; info->n_internal = P.n_internal; info->n_leaves = P.n_leaves;
+    info->n_chunks = (int32_t)P.chunks.size();
+    info->n_fwd_levels = (int32_t)P.fwd_lvl_off.size() - 1;
+    info->n_bwd_levels = (int32_t)P.bwd_lvl_off.size() - 1;
+    info->fwd_stack_depth = P.fwd_stack_depth; info->bwd_stack_depth = P.bwd_stack_depth;
+    info->max_arity = P.max_arity;
+    info->program_words = (int64_t)P.fwd_prog.size() + (int64_t)P.bwd_prog.size();
+    info->edges_leaf = P.edges_leaf; info->edges_internal = P.edges_internal;
+    return PMFS_OK;
+}
+
+int pmfs_get_timing(pmfs_ctx* c, pmfs_timing* t) {
+    if (!c || !t) return PMFS_ERR_ARG;
+    *t = c->timing;
+    return PMFS_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------- the pipeline
+template <int ALGO>
+static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches) {
+    const Plan& P = c->plan;
+    const std::vector<int32_t>& lvl = fwd ? P.fwd_lvl_off : P.bwd_lvl_off;
+    wp.prog = fwd ? c->d_fwd_prog.ptr : c->d_bwd_prog.ptr;
+    wp.chunk_off = fwd ? c->d_fwd_off.ptr : c->d_bwd_off.ptr;
+    wp.chunk_len = fwd ? c->d_fwd_len.ptr : c->d_bwd_len.ptr;
+    const int32_t* order = fwd ? c->d_fwd_order.ptr : c->d_bwd_order.ptr;
+    wp.ctas_per_chunk = (int32_t)((wp.G + kTPB - 1) / kTPB);
+    wp.stack_depth = fwd ? P.fwd_stack_depth : P.bwd_stack_depth;
+    const size_t smem = fwd ? (size_t)std::max(1, P.fwd_stack_depth) * 4 * kTPB * sizeof(uint4)
+                            : (size_t)std::max(1, P.bwd_stack_depth) * 5 * kTPB * sizeof(uint32_t);
+    if (smem > 200 * 1024) {
+        g_error = "walk stack does not fit in shared memory (tree too unbalanced for this chunk size)";
+        return PMFS_ERR_ARG;
+    }
+    for (size_t l = 0; l + 1 < lvl.size(); l++) {
+        const int32_t nchunks = lvl[l + 1] - lvl[l];
+        if (nchunks == 0) continue;
+        wp.order = order + lvl[l];
+        const unsigned grid = (unsigned)((int64_t)nchunks * wp.ctas_per_chunk);
+        if (fwd) {
+            auto k = c->has_poly ? fwd_kernel<ALGO, true> : fwd_kernel<ALGO, false>;
+            if (smem > 48 * 1024) PMFS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k<<<grid, kTPB, smem, c->stream>>>(wp);
+        } else {
+            auto k = bwd_kernel<ALGO>;
+            if (smem > 48 * 1024) PMFS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k<<<grid, kTPB, smem, c->stream>>>(wp);
+        }
+        (*launches)++;
+    }
+    PMFS_CUDA(cudaGetLastError());
+    return PMFS_OK;
+}
+
+static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                           const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut** d_out, int64_t* n_out) {
+    if (!c || (algo != PMFS_FITCH && algo != PMFS_SANKOFF) || !d_msa || !d_cons || !n_out || n_cols <= 0) {
+        g_error = "pmfs_run: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    if (row_stride % 16 != 0 || ((uintptr_t)d_msa & 15) != 0 || row_stride * 2 < n_cols) {
+        g_error = "pmfs_run_device: MSA rows must be 16-byte aligned with a stride that is a multiple of 16 and covers n_cols";
+        return PMFS_ERR_ARG;
+    }
+    if ((int64_t)c->plan.row_to_node.size() > (int64_t)n_rows) {
+        g_error = "pmfs_run: a leaf refers to an MSA row >= n_rows";
+        return PMFS_ERR_ARG;
+    }
+    if (n_cols > 0xffffffffll) {
+        g_error = "pmfs_run: more than 2^32 columns";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    const Plan* P = &c->plan;
+    const int64_t G_all = (n_cols + 31) / 32;
+    const int64_t I = P->n_internal;
+
+    // column tile so that the set arrays fit in HBM
+    size_t free_b = 0, total_b = 0;
+    PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);  // reusable
+    const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64;
+    int64_t tile_groups = std::max<int64_t>(1, (int64_t)(free_b * 0.85) / per_group);
+    if (c->tune_tile_cols > 0) tile_groups = std::min<int64_t>(tile_groups, (c->tune_tile_cols + 31) / 32);
+    tile_groups = std::min(tile_groups, G_all);
+    if (tile_groups < G_all) tile_groups = std::max<int64_t>(kTPB, tile_groups / kTPB * kTPB);
+    tile_groups = std::min(tile_groups, G_all);
+
+    const int32_t want_chunk = c->tune_chunk_nodes > 0 ? c->tune_chunk_nodes : auto_chunk_nodes(P->n_nodes, tile_groups);
+    if (want_chunk != c->chunk_nodes_used) {
+        int rc = replan(c, want_chunk);
+        if (rc) return rc;
+        P = &c->plan;
+    }
+    const int64_t NC = (int64_t)P->chunks.size();
+
+    int rc;
+    if ((rc = c->d_S.ensure((size_t)I * 4 * tile_groups))) return rc;
+    if (algo == PMFS_SANKOFF && (rc = c->d_D.ensure((size_t)I * 4 * tile_groups))) return rc;
+    if ((rc = c->d_cons_planes.ensure(tile_groups))) return rc;
+    if (d_forced && (rc = c->d_forced_planes.ensure(tile_groups))) return rc;
+    if ((rc = c->d_xcode.ensure((size_t)NC * tile_groups))) return rc;
+    if ((rc = c->d_xvalid.ensure((size_t)NC * tile_groups))) return rc;
+    if ((rc = c->d_count.ensure(1))) return rc;
+    if ((rc = c->d_err.ensure(1))) return rc;
+    size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);
+
+    pmfs_timing& tm = c->timing;
+    const float h2d_keep = tm.h2d_ms;
+    tm = pmfs_timing();
+    tm.h2d_ms = h2d_keep;
+    float fwd_ms = 0, bwd_ms = 0;
+    unsigned long long count = 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        if ((rc = c->d_keys.ensure(cap))) return rc;
+        if ((rc = c->d_vals.ensure(cap))) return rc;
+        PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, sizeof(unsigned long long), c->stream));
+        PMFS_CUDA(cudaMemsetAsync(c->d_err.ptr, 0, sizeof(unsigned int), c->stream));
+        fwd_ms = bwd_ms = 0;
+        tm.n_launches = 0;
+        for (int64_t g0 = 0; g0 < G_all; g0 += tile_groups) {
+            WalkParams wp = {};
+            wp.G = std::min(tile_groups, G_all - g0);
+            wp.col_base = g0 * 32;
+            wp.tile_cols = std::min<int64_t>(wp.G * 32, n_cols - wp.col_base);
+            wp.msa = (const uint4*)(d_msa + g0 * 16);
+            wp.msa_stride16 = row_stride / 16;
+            wp.S = c->d_S.ptr;
+            wp.D = c->d_D.ptr;
+            wp.cons_planes = c->d_cons_planes.ptr;
+            wp.forced_planes = d_forced ? c->d_forced_planes.ptr : nullptr;
+            wp.xcode = c->d_xcode.ptr;
+            wp.xvalid = c->d_xvalid.ptr;
+            wp.int_to_node = c->d_int_to_node.ptr;
+            wp.row_to_node = c->d_row_to_node.ptr;
+            wp.out_keys = c->d_keys.ptr;
+            wp.out_vals = c->d_vals.ptr;
+            wp.out_count = c->d_count.ptr;
+            wp.out_cap = c->d_keys.cap;
+            wp.err_flag = c->d_err.ptr;
+            const unsigned pg = (unsigned)((wp.G + 127) / 128);
+            PMFS_CUDA(cudaEventRecord(c->ev[0], c->stream));
+            prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_cons + wp.col_base, wp.tile_cols, wp.G, c->d_cons_planes.ptr);
+            tm.n_launches++;
+            if (d_forced) {
+                prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_forced + wp.col_base, wp.tile_cols, wp.G, c->d_forced_planes.ptr);
+                tm.n_launches++;
+            }
+            rc = algo == PMFS_FITCH ? launch_levels<kAlgoFitch>(c, wp, true, &tm.n_launches)
+                                    : launch_levels<kAlgoSankoff>(c, wp, true, &tm.n_launches);
+            if (rc) return rc;
+            PMFS_CUDA(cudaEventRecord(c->ev[1], c->stream));
+            rc = algo == PMFS_FITCH ? launch_levels<kAlgoFitch>(c, wp, false, &tm.n_launches)
+                                    : launch_levels<kAlgoSankoff>(c, wp, false, &tm.n_launches);
+            if (rc) return rc;
+            PMFS_CUDA(cudaEventRecord(c->ev[2], c->stream));
+            if (g0 + tile_groups < G_all || true) {
+                PMFS_CUDA(cudaEventSynchronize(c->ev[2]));
+                float a = 0, b = 0;
+                cudaEventElapsedTime(&a, c->ev[0], c->ev[1]);
+                cudaEventElapsedTime(&b, c->ev[1], c->ev[2]);
+                fwd_ms += a;
+                bwd_ms += b;
+            }
+        }
+        unsigned int err = 0;
+        PMFS_CUDA(cudaMemcpyAsync(&count, c->d_count.ptr, sizeof(count), cudaMemcpyDeviceToHost, c->stream));
+        PMFS_CUDA(cudaMemcpyAsync(&err, c->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
+        PMFS_CUDA(cudaStreamSynchronize(c->stream));
+        if (err) {
+            g_error = "pmfs_run: Sankoff root has no finite cost in some column and no forced root was given "
+                      "(the reference asserts here, src/fitchSankoff.cpp:505)";
+            return PMFS_ERR_ROOT_INVALID;
+        }
+        if (count <= c->d_keys.cap) break;
+        cap = (size_t)count + (size_t)count / 8 + 1024;  // record buffer was too small: grow and redo the passes
+    }
+    tm.forward_ms = fwd_ms;
+    tm.backward_ms = bwd_ms;
+    {
+        const int64_t Gb = G_all * 16;  // bytes per node row
+        const int64_t sets = (algo == PMFS_SANKOFF) ? 2 : 1;
+        tm.forward_bytes = P->n_rows_used * Gb + I * Gb * 4 * sets;
+        tm.backward_bytes = P->n_rows_used * Gb + I * Gb * 4;
+    }
+
+    // order by (node,pos): radix sort on the key bits that can be non-zero
+    const int64_t n = (int64_t)count;
+    PMFS_CUDA(cudaEventRecord(c->ev[3], c->stream));
+    if (n > 0) {
+        if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
+        if ((rc = c->d_vals_alt.ensure(c->d_vals.cap))) return rc;
+        if ((rc = c->d_out.ensure((size_t)n))) return rc;
+        int node_bits = 1;
+        while ((1ll << node_bits) < P->n_nodes) node_bits++;
+        cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
+        cub::DoubleBuffer<uint32_t> vb(c->d_vals.ptr, c->d_vals_alt.ptr);
+        size_t tmp_bytes = 0;
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, (int)n, 0, 32 + node_bits, c->stream));
+        if ((rc = c->d_sort_tmp.ensure(tmp_bytes))) return rc;
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(c->d_sort_tmp.ptr, tmp_bytes, kb, vb, (int)n, 0, 32 + node_bits, c->stream));
+        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), n, c->d_out.ptr);
+        PMFS_CUDA(cudaGetLastError());
+        tm.n_launches += 1;
+    }
+    PMFS_CUDA(cudaEventRecord(c->ev[4], c->stream));
+    PMFS_CUDA(cudaEventSynchronize(c->ev[4]));
+    cudaEventElapsedTime(&tm.sort_ms, c->ev[3], c->ev[4]);
+    tm.total_ms = tm.h2d_ms + tm.forward_ms + tm.backward_ms + tm.sort_ms;
+    c->last_n_out = n;
+    *n_out = n;
+    if (d_out) *d_out = c->d_out.ptr;
+    return PMFS_OK;
+}
+
+extern "C" {
+
+int pmfs_run_device(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                    const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut** d_out, int64_t* n_out) {
+    if (c) c->timing.h2d_ms = 0;
+    return run_device_impl(c, algo, d_msa, row_stride, n_rows, n_cols, d_cons, d_forced, d_out, n_out);
+}
+
+int pmfs_download(pmfs_ctx* c, pmfs_mut* host_out, int64_t n) {
+    if (!c || (!host_out && n > 0) || n < 0 || n > c->last_n_out) {
+        g_error = "pmfs_download: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    if (n == 0) return PMFS_OK;
+    PMFS_CUDA(cudaSetDevice(c->device));
+    PMFS_CUDA(cudaMemcpyAsync(host_out, c->d_out.ptr, (size_t)n * sizeof(pmfs_mut), cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    return PMFS_OK;
+}
+
+int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+             const uint8_t* cons, const uint8_t* forced, pmfs_mut** out, int64_t* n_out) {
+    if (!c || !msa || !cons || !out || !n_out || n_cols <= 0 || n_rows < 0 || row_stride * 2 < n_cols) {
+        g_error = "pmfs_run: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    const int64_t dstride = ((n_cols + 31) / 32) * 16;
+    int rc;
+    if ((rc = c->d_msa.ensure((size_t)std::max<int64_t>(1, n_rows) * dstride))) return rc;
+    if ((rc = c->d_cons.ensure((size_t)n_cols))) return rc;
+    if (forced && (rc = c->d_forced.ensure((size_t)n_cols))) return rc;
+    PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
+    const int64_t used = (n_cols + 1) / 2;
+    if (dstride > used) PMFS_CUDA(cudaMemsetAsync(c->d_msa.ptr, 0, (size_t)std::max<int64_t>(1, n_rows) * dstride, c->stream));
+    if (n_rows > 0)
+        PMFS_CUDA(cudaMemcpy2DAsync(c->d_msa.ptr, (size_t)dstride, msa, (size_t)row_stride, (size_t)used, (size_t)n_rows,
+                                    cudaMemcpyHostToDevice, c->stream));
+    PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons, (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
+    if (forced) PMFS_CUDA(cudaMemcpyAsync(c->d_forced.ptr, forced, (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
+    PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));
+    PMFS_CUDA(cudaEventSynchronize(c->ev[6]));
+    cudaEventElapsedTime(&c->timing.h2d_ms, c->ev[5], c->ev[6]);
+    // an odd final column shares its byte with a padding nibble that the caller may have left non-zero: it is masked
+    // out of the emission by the real-column mask, and it cannot influence other columns.
+    pmfs_mut* d_out = nullptr;
+    rc = run_device_impl(c, algo, c->d_msa.ptr, dstride, n_rows, n_cols, c->d_cons.ptr, forced ? c->d_forced.ptr : nullptr,
+                         &d_out, n_out);
+    if (rc) return rc;
+    pmfs_mut* h = nullptr;
+    PMFS_CUDA(cudaMallocHost(&h, std::max<size_t>(1, (size_t)*n_out) * sizeof(pmfs_mut)));
+    PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
+    if (*n_out > 0)
+        PMFS_CUDA(cudaMemcpyAsync(h, d_out, (size_t)*n_out * sizeof(pmfs_mut), cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));
+    PMFS_CUDA(cudaEventSynchronize(c->ev[6]));
+    cudaEventElapsedTime(&c->timing.d2h_ms, c->ev[5], c->ev[6]);
+    c->timing.total_ms += c->timing.d2h_ms;
+    c->host_results.push_back(h);
+    *out = h;
+    return PMFS_OK;
+}
+
+void pmfs_result_free(pmfs_ctx* c, pmfs_mut* out) {
+    if (!c || !out) return;
+    auto it = std::find(c->host_results.begin(), c->host_results.end(), out);
+    if (it == c->host_results.end()) return;
+    cudaFreeHost(out);
+    c->host_results.erase(it);
+}
+
+int pmfs_synth_msa(pmfs_ctx* c, const pmfs_synth_spec* spec, int64_t col_begin, int64_t n_cols, uint8_t* d_msa,
+                   int64_t row_stride, uint8_t* d_cons) {
+    if (!c || !spec || !d_msa || n_cols <= 0 || col_begin < 0 || row_stride % 4 != 0 || row_stride * 2 < n_cols) {
+        g_error = "pmfs_synth_msa: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    const int32_t n_rows = (int32_t)c->plan.row_to_node.size();
+    if (n_rows == 0) {
+        g_error = "pmfs_synth_msa: tree has no leaf with an MSA row";
+        return PMFS_ERR_ARG;
+    }
+    if (!c->synth_ready) {
+        // root->leaf paths (root excluded), one CSR row per MSA row
+        std::vector<int32_t> off(n_rows + 1, 0), nodes;
+        std::vector<int32_t> depth(c->parent.size(), 0);
+        for (size_t v = 1; v < c->parent.size(); v++) depth[v] = depth[c->parent[v]] + 1;
+        for (int32_t r = 0; r < n_rows; r++) off[r + 1] = off[r] + (c->plan.row_to_node[r] >= 0 ? depth[c->plan.row_to_node[r]] : 0);
+        nodes.resize(off[n_rows]);
+        for (int32_t r = 0; r < n_rows; r++) {
+            int32_t v = c->plan.row_to_node[r];
+            if (v < 0) continue;
+            int32_t k = off[r + 1];
+            while (v > 0) {
+                nodes[--k] = v;
+                v = c->parent[v];
+            }
+        }
+        int rc;
+        if ((rc = c->d_path_off.ensure(off.size()))) return rc;
+        if ((rc = c->d_path_node.ensure(nodes.size()))) return rc;
+        PMFS_CUDA(cudaMemcpy(c->d_path_off.ptr, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        if (!nodes.empty())
+            PMFS_CUDA(cudaMemcpy(c->d_path_node.ptr, nodes.data(), nodes.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        c->synth_ready = true;
+    }
+    auto thr = [](float p) -> uint32_t {
+        double x = (double)p * 4294967296.0;
+        return x >= 4294967295.0 ? 0xffffffffu : (x <= 0 ? 0u : (uint32_t)x);
+    };
+    SynthParams s;
+    s.seed = spec->seed;
+    s.t_sub = thr(spec->p_sub); s.t_del = thr(spec->p_del); s.t_ins = thr(spec->p_ins);
+    s.t_nblock = thr(spec->p_n_block); s.t_amb = thr(spec->p_amb); s.t_acc = thr(spec->accessory_frac);
+    s.path_off = c->d_path_off.ptr; s.path_node = c->d_path_node.ptr;
+    s.n_rows = n_rows; s.col_begin = col_begin; s.n_cols = n_cols; s.msa = d_msa; s.row_stride = row_stride;
+    PMFS_CUDA(cudaMemsetAsync(d_msa, 0, (size_t)n_rows * row_stride, c->stream));
+    const int64_t total = ((n_cols + 7) / 8) * n_rows;
+    synth_msa_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(s);
+    if (d_cons) synth_consensus_kernel<<<(unsigned)((n_cols + 255) / 256), 256, 0, c->stream>>>(d_msa, row_stride, n_rows, n_cols, d_cons);
+    PMFS_CUDA(cudaGetLastError());
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    return PMFS_OK;
+}
+
+}  // extern "C"

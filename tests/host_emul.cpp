@@ -1,0 +1,186 @@
+// TEST INFRASTRUCTURE ONLY.  Runs the library's own plan builder (panman_b200/csrc/plan.cpp) and walk interpreter
+// (panman_b200/csrc/walk.cuh, the __host__ side of the very code the CUDA kernels execute per thread) on the CPU, one
+// column group at a time, so that program emission and the bit-sliced set algebra can be checked against the oracle
+// without a GPU.  It is built by tests/test_host_emul.py into tests/_build/ and is never loaded by the product.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../panman_b200/csrc/plan.hpp"
+#include "../panman_b200/csrc/walk.cuh"
+
+using namespace pmfs;
+
+namespace {
+
+struct Rec {
+    int32_t node, pos;
+    uint8_t type, code, parent_code, pad;
+};
+
+struct HostEnv {
+    const Plan* plan;
+    const uint8_t* msa;
+    int64_t row_stride;
+    int64_t G, g, col_base;
+    std::vector<uint32_t>*S, *D;       // [I][16][G] words
+    std::vector<uint32_t>*xcode, *xv;  // [NC][4][G], [NC][G]
+    std::vector<Planes16> fstk;
+    std::vector<std::pair<Code4, uint32_t>> bstk;
+    std::vector<Rec>* out;
+
+    uint32_t word(const uint32_t* prog, int32_t pc) const { return prog[pc]; }
+    uint4 leaf(uint32_t row) const {
+        uint4 v;
+        memcpy(&v, msa + (int64_t)row * row_stride + g * 16, 16);
+        return v;
+    }
+    void load(std::vector<uint32_t>* a, uint32_t id, Planes16& s) const {
+        for (int i = 0; i < 16; i++) s.p[i] = (*a)[((int64_t)id * 16 + i) * G + g];
+    }
+    void store(std::vector<uint32_t>* a, uint32_t id, const Planes16& s) const {
+        for (int i = 0; i < 16; i++) (*a)[((int64_t)id * 16 + i) * G + g] = s.p[i];
+    }
+    void load_s(uint32_t id, Planes16& s) const { load(S, id, s); }
+    void load_d(uint32_t id, Planes16& s) const { load(D, id, s); }
+    void store_s(uint32_t id, const Planes16& s) const { store(S, id, s); }
+    void store_d(uint32_t id, const Planes16& s) const { store(D, id, s); }
+    void push(const Planes16& s) { fstk.push_back(s); }
+    void pop(Planes16& s) {
+        s = fstk.back();
+        fstk.pop_back();
+    }
+    void pushp(const Code4& c, uint32_t pv) { bstk.push_back({c, pv}); }
+    void popp(Code4& c, uint32_t& pv) {
+        c = bstk.back().first;
+        pv = bstk.back().second;
+        bstk.pop_back();
+    }
+    void store_x(uint32_t chunk, const Code4& c, uint32_t pv) const {
+        for (int i = 0; i < 4; i++) (*xcode)[((int64_t)chunk * 4 + i) * G + g] = c.b[i];
+        (*xv)[(int64_t)chunk * G + g] = pv;
+    }
+    bool any(bool x) const { return x; }
+    void emit(int32_t node, uint32_t m, const Code4& Gc, const Code4& P) const {
+        for (int q = 0; q < 32; q++)
+            if ((m >> q) & 1) {
+                uint32_t cg = 0, cp = 0;
+                for (int i = 0; i < 4; i++) {
+                    cg |= ((Gc.b[i] >> q) & 1) << i;
+                    cp |= ((P.b[i] >> q) & 1) << i;
+                }
+                Rec r;
+                r.node = node;
+                r.pos = (int32_t)(col_base + g * 32 + column_of_bit(q));
+                r.type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
+                r.code = (uint8_t)cg;
+                r.parent_code = (uint8_t)cp;
+                r.pad = 0;
+                out->push_back(r);
+            }
+    }
+    void emit_internal(uint32_t id, uint32_t m, const Code4& Gc, const Code4& P) const { emit(plan->int_to_node[id], m, Gc, P); }
+    void emit_leaf(uint32_t row, uint32_t m, const Code4& Gc, const Code4& P) const { emit(plan->row_to_node[row], m, Gc, P); }
+};
+
+Code4 planes_of(const uint8_t* codes, int64_t n_cols, int64_t g) {
+    Code4 c = {{0, 0, 0, 0}};
+    for (int q = 0; q < 32; q++) {
+        int64_t col = g * 32 + column_of_bit(q);
+        uint32_t x = col < n_cols ? (codes[col] & 15u) : 0u;
+        for (int i = 0; i < 4; i++) c.b[i] |= ((x >> i) & 1u) << q;
+    }
+    return c;
+}
+
+template <int ALGO>
+int run(const Plan& P, const uint8_t* msa, int64_t row_stride, int64_t n_cols, const uint8_t* cons, const uint8_t* forced,
+        std::vector<Rec>& out) {
+    const int64_t G = (n_cols + 31) / 32;
+    std::vector<uint32_t> S((size_t)P.n_internal * 16 * G), D(ALGO ? S.size() : 0);
+    std::vector<uint32_t> xcode(P.chunks.size() * 4 * G), xv(P.chunks.size() * G);
+    bool has_poly = false;
+    uint32_t err = 0;
+    for (int pass = 0; pass < 2; pass++) {
+        const auto& lvl = pass == 0 ? P.fwd_lvl_off : P.bwd_lvl_off;
+        const auto& order = pass == 0 ? P.fwd_order : P.bwd_order;
+        for (size_t l = 0; l + 1 < lvl.size(); l++)
+            for (int32_t k = lvl[l]; k < lvl[l + 1]; k++) {
+                const Chunk& ch = P.chunks[order[k]];
+                for (int64_t g = 0; g < G; g++) {
+                    HostEnv env{&P, msa, row_stride, G, g, 0, &S, &D, &xcode, &xv, {}, {}, &out};
+                    Code4 fc;
+                    const Code4* fp = nullptr;
+                    if (forced) {
+                        fc = planes_of(forced, n_cols, g);
+                        fp = &fc;
+                    }
+                    if (pass == 0) {
+                        (void)has_poly;
+                        forward_walk<ALGO, true>(env, P.fwd_prog.data() + ch.fwd_off, ch.fwd_len, ALGO == kAlgoFitch ? fp : nullptr);
+                        if (!env.fstk.empty()) return -100;
+                    } else {
+                        Code4 Pc;
+                        uint32_t pv = ~0u;
+                        if (order[k] == 0) {
+                            Pc = planes_of(cons, n_cols, g);
+                        } else {
+                            for (int i = 0; i < 4; i++) Pc.b[i] = xcode[((int64_t)order[k] * 4 + i) * G + g];
+                            pv = xv[(int64_t)order[k] * G + g];
+                        }
+                        uint32_t colmask = 0;
+                        for (int q = 0; q < 32; q++)
+                            if (g * 32 + column_of_bit(q) < n_cols) colmask |= 1u << q;
+                        err |= backward_walk<ALGO>(env, P.bwd_prog.data() + ch.bwd_off, ch.bwd_len, Pc, pv,
+                                                   ALGO == kAlgoSankoff ? fp : nullptr, colmask);
+                        if (!env.bstk.empty()) return -101;
+                    }
+                }
+            }
+    }
+    if (err) return PMFS_ERR_ROOT_INVALID;
+    std::sort(out.begin(), out.end(), [](const Rec& a, const Rec& b) { return a.node != b.node ? a.node < b.node : a.pos < b.pos; });
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+void emul_free(void* p) { free(p); }
+
+// same contract as pmfs_run (include/pmfs.h) + an explicit chunk size; plan_out (optional) receives
+// {n_chunks, fwd_levels, bwd_levels, fwd_stack, bwd_stack, program_words}
+int emul_run(int algo, int32_t n_nodes, const int32_t* parent, const int32_t* child_off, const int32_t* child_idx,
+             const int32_t* leaf_row, const uint8_t* msa, int64_t row_stride, int64_t n_cols, const uint8_t* cons,
+             const uint8_t* forced, int32_t chunk_nodes, void** out, int64_t* n_out, int64_t* plan_out) {
+    pmfs_tree t = {n_nodes, parent, child_off, child_idx, leaf_row};
+    Plan P;
+    std::string e = build_plan(t, chunk_nodes, P);
+    if (!e.empty()) return PMFS_ERR_ARG;
+    if (plan_out) {
+        plan_out[0] = (int64_t)P.chunks.size();
+        plan_out[1] = (int64_t)P.fwd_lvl_off.size() - 1;
+        plan_out[2] = (int64_t)P.bwd_lvl_off.size() - 1;
+        plan_out[3] = P.fwd_stack_depth;
+        plan_out[4] = P.bwd_stack_depth;
+        plan_out[5] = (int64_t)(P.fwd_prog.size() + P.bwd_prog.size());
+    }
+    // rows padded to whole groups, as the library does on upload
+    const int64_t dstride = ((n_cols + 31) / 32) * 16;
+    int32_t n_rows = (int32_t)P.row_to_node.size();
+    std::vector<uint8_t> padded((size_t)std::max(1, n_rows) * dstride, 0);
+    for (int32_t r = 0; r < n_rows; r++) memcpy(padded.data() + (size_t)r * dstride, msa + (size_t)r * row_stride, (size_t)((n_cols + 1) / 2));
+    std::vector<Rec> recs;
+    int rc = algo == 0 ? run<kAlgoFitch>(P, padded.data(), dstride, n_cols, cons, forced, recs)
+                       : run<kAlgoSankoff>(P, padded.data(), dstride, n_cols, cons, forced, recs);
+    if (rc) return rc;
+    Rec* o = (Rec*)malloc(std::max<size_t>(1, recs.size()) * sizeof(Rec));
+    if (!recs.empty()) memcpy(o, recs.data(), recs.size() * sizeof(Rec));
+    *out = o;
+    *n_out = (int64_t)recs.size();
+    return 0;
+}
+}

@@ -1,0 +1,68 @@
+"""CPU: the C-ABI library loads, exports every symbol include/pmfs.h declares, validates trees without a device, and
+fails loudly (no fallback) when no CUDA device is present."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import synth
+from panman_b200 import api
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    api.build_library()
+    return api.lib()
+
+
+def test_exports_match_header(lib):
+    hdr = open(os.path.join(ROOT, "include", "pmfs.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(pmfs_[a-z_0-9]+)\s*\(", hdr))
+    assert declared, "no declarations found"
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in include/pmfs.h but not exported"
+    assert declared == set(api.EXPORTS) | {n for n in declared if n not in api.EXPORTS and hasattr(lib, n)}
+    assert b"sm_100a" in lib.pmfs_version()
+
+
+def _has_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def test_malformed_trees_rejected_without_device(lib):
+    good = synth._flatten([[0, 1], 2])
+    bad = synth._flatten([[0, 1], 2])
+    bad.parent = bad.parent.copy()
+    bad.parent[2] = 3  # parent after child: not a pre-order numbering
+    with pytest.raises(api.PmfsError) as e:
+        api.Context(bad)
+    assert e.value.status == -1
+    dup = synth._flatten([[0, 1], 2])
+    dup.leaf_row = dup.leaf_row.copy()
+    dup.leaf_row[dup.leaf_row == 2] = 1  # two leaves on one MSA row (the reference would alias them by name)
+    with pytest.raises(api.PmfsError) as e:
+        api.Context(dup)
+    assert e.value.status == -1
+    if not _has_gpu():
+        with pytest.raises(api.PmfsError) as e:
+            api.Context(good)
+        assert e.value.status == -2 and "no CPU path" in str(e.value)
+
+
+def test_nibble_packing_roundtrip():
+    rng = np.random.default_rng(0)
+    for cols in (1, 2, 7, 32, 33):
+        codes = rng.integers(0, 16, size=(3, cols), dtype=np.uint8)
+        p = api.pack_nibbles(codes)
+        assert p.shape == (3, (cols + 1) // 2)
+        assert (api.unpack_nibbles(p, cols) == codes).all()
+        assert (p[:, 0] & 15 == codes[:, 0]).all()  # column 0 in the LOW nibble

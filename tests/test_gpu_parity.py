@@ -1,0 +1,110 @@
+"""GPU (B200): the CUDA path, called through the C ABI (include/pmfs.h), against the oracle and the golden fixtures.
+Bit-exact: (node, pos, type, code) records and the packed NucMut arrays must be identical."""
+import numpy as np
+import pytest
+
+import golden_util as G
+import synth
+from oracle import oracle_api as O
+from panman_b200 import api, trees
+
+pytestmark = pytest.mark.gpu
+
+
+def run_gpu(tree, algo, msa_codes, cons, forced=None, chunk_nodes=0, tile_cols=0):
+    with api.Context(tree) as ctx:
+        ctx.set_tuning(chunk_nodes, tile_cols)
+        nib = api.pack_nibbles(msa_codes) if msa_codes.shape[0] else np.zeros((0, 1), np.uint8)
+        return ctx.run(algo, nib, int(cons.shape[0]), cons, forced)
+
+
+def test_golden_small_cases(small_cases):
+    z = small_cases
+    for name in z["case_names"]:
+        tree, msa, cons, forced = G.case_inputs(z, str(name))
+        for algo in (0, 1):
+            for chunk in (0, 4):
+                got = run_gpu(tree, algo, msa, cons, forced, chunk_nodes=chunk)
+                assert G.same_muts(got, z[f"{name}/muts{algo}"]), (name, algo, chunk)
+            off, nuc = O.pack_port(got, tree.n_nodes)
+            assert (off == z[f"{name}/nuc_off{algo}"]).all() and G.same_nuc(nuc, z[f"{name}/nuc{algo}"])
+
+
+@pytest.mark.parametrize("low,with_ref", [(0, 0), (0, 1), (1, 0), (1, 1)])
+def test_golden_c1_sars20(c1, low, with_ref):
+    """BASELINE config 1 (test/sars_20.fa padded + test/sars_20.nwk), all four CLI variants."""
+    key = f"v{low}{with_ref}_"
+    tree = G.c1_tree(c1)
+    msa = G.unpack_nibbles(c1["msa_nibbles"], int(c1["n_cols"]))
+    forced = msa[list(c1["row_ids"]).index(str(c1[key + "reference"]))] if with_ref else None
+    got = run_gpu(tree, low, msa, c1[key + "consensus"], forced)
+    assert got.shape[0] == int(c1[key + "n_muts"])
+    assert (np.bincount(got["type"], minlength=3) == c1[key + "type_counts"]).all()
+    assert G.same_muts(got[:512], c1[key + "muts_head"])
+    assert G.digest_muts(got) == str(c1[key + "muts_sha256"])
+    off, nuc = O.pack_port(got, tree.n_nodes)
+    assert G.digest_nuc(off, nuc) == str(c1[key + "nuc_sha256"])
+
+
+def test_random_trees_vs_oracle():
+    rng = np.random.default_rng(101)
+    for trial in range(24):
+        arity = 2 if trial < 10 else int(rng.integers(2, 7))
+        tree = synth.random_tree(int(rng.integers(2, 400)), rng, max_arity=arity, absent_frac=0.0 if trial % 3 else 0.08)
+        L = int(rng.integers(1, 700))
+        msa = synth.simulate_msa(tree, L, rng, p_sub=0.08, p_del=0.04, p_ins=0.2, p_n=0.04, p_amb=0.04)
+        cons = synth.consensus_first_nongap(msa)
+        forced = msa[int(rng.integers(0, msa.shape[0]))] if trial % 2 else None
+        chunk = int(rng.choice([0, 2, 16, 64]))
+        tile = int(rng.choice([0, 32, 4096]))
+        for algo in (0, 1):
+            want = O.run_port(algo, tree, msa, cons, forced, threads=4)
+            got = run_gpu(tree, algo, msa, cons, forced, chunk_nodes=chunk, tile_cols=tile)
+            assert G.same_muts(got, want), (trial, algo, chunk, tile)
+
+
+def test_medium_binary_tree_many_columns():
+    """2 000 taxa x 20 000 columns: several CTAs per chunk, ragged last group, both algorithms, tiled and untiled."""
+    rng = np.random.default_rng(9)
+    tree = trees.random_binary_tree(2000, seed=5)
+    L = 20011
+    msa = synth.simulate_msa(tree, L, rng, p_sub=0.002, p_del=0.001, p_ins=0.01, p_n=0.01, p_amb=0.001)
+    cons = synth.consensus_first_nongap(msa)
+    for algo in (0, 1):
+        want = O.run_port(algo, tree, msa, cons, None, threads=8)
+        got = run_gpu(tree, algo, msa, cons, None)
+        assert G.same_muts(got, want), algo
+        got2 = run_gpu(tree, algo, msa, cons, msa[3], chunk_nodes=50, tile_cols=8192)
+        want2 = O.run_port(algo, tree, msa, cons, msa[3], threads=8)
+        assert G.same_muts(got2, want2), algo
+
+
+def test_deep_ladder():
+    """Config-5 shape at test size: a 30 000-deep ladder must neither overflow a stack nor lose bit-exactness."""
+    rng = np.random.default_rng(4)
+    tree = trees.caterpillar_tree(30000)
+    L = 96
+    msa = rng.choice(np.array([0, 1, 2, 4, 8, 15], np.uint8), size=(30000, L), p=[0.03, 0.3, 0.2, 0.2, 0.22, 0.05])
+    msa[0, (msa != 0).sum(0) == 0] = 1
+    cons = synth.consensus_first_nongap(msa)
+    for algo in (0, 1):
+        want = O.run_port(algo, tree, msa, cons, None, threads=8)
+        got = run_gpu(tree, algo, msa, cons, None)
+        assert G.same_muts(got, want), algo
+
+
+def test_error_paths():
+    tree = synth._flatten([None, None])
+    cons = np.zeros(5, np.uint8)
+    with api.Context(tree) as ctx:
+        assert ctx.run(api.FITCH, np.zeros((0, 3), np.uint8), 5, cons).shape[0] == 0
+        with pytest.raises(api.PmfsError) as e:
+            ctx.run(api.SANKOFF, np.zeros((0, 3), np.uint8), 5, cons)
+        assert e.value.status == -4
+        got = ctx.run(api.SANKOFF, np.zeros((0, 3), np.uint8), 5, cons, np.array([1, 0, 2, 0, 15], np.uint8))
+        assert got.shape[0] == 3 and (got["node"] == 0).all() and (got["type"] == 2).all()
+    tree = synth._flatten([[0, 1], 2])
+    with api.Context(tree) as ctx:
+        with pytest.raises(api.PmfsError) as e:  # a leaf refers to row 2 but only 2 rows are given
+            ctx.run(api.FITCH, np.zeros((2, 3), np.uint8), 5, cons)
+        assert e.value.status == -1

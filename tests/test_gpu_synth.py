@@ -1,0 +1,87 @@
+"""GPU (B200): device-side synthetic alignments (pmfs_synth_msa) and full-size checks on BASELINE config 2."""
+import numpy as np
+import pytest
+
+import golden_util as G
+from oracle import oracle_api as O
+from panman_b200 import api, trees
+
+pytestmark = pytest.mark.gpu
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def synth_on_device(ctx, spec, n_rows, col_begin, n_cols):
+    torch = _torch()
+    stride = ((n_cols + 31) // 32) * 16
+    d_msa = torch.zeros((n_rows, stride), dtype=torch.uint8, device="cuda")
+    d_cons = torch.zeros(n_cols, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    ctx.synth_msa(spec, col_begin, n_cols, d_msa.data_ptr(), stride, d_cons.data_ptr())
+    return d_msa, d_cons, stride
+
+
+def test_synth_is_a_pure_function_of_seed_node_column():
+    tree = trees.random_binary_tree(500, seed=2)
+    spec = api.SynthSpec(seed=7, p_sub=0.01, p_del=0.01, p_ins=0.05, p_n_block=0.02, p_amb=0.01, accessory_frac=0.3)
+    with api.Context(tree) as ctx:
+        a, ca, _ = synth_on_device(ctx, spec, 500, 0, 4096)
+        b, cb, _ = synth_on_device(ctx, spec, 500, 0, 4096)
+        assert bool((a == b).all()) and bool((ca == cb).all())
+        full = api.unpack_nibbles(a.cpu().numpy(), 4096)
+        part, cp, _ = synth_on_device(ctx, spec, 500, 1024, 512)  # any column range generates the same cells
+        assert (api.unpack_nibbles(part.cpu().numpy(), 512) == full[:, 1024:1536]).all()
+        assert ((full != 0).sum(0) >= 1).all()  # every column has a non-gap cell (SURVEY §8 notes: all-gap is UB upstream)
+        nz = full != 0
+        want_cons = full[nz.argmax(0), np.arange(4096)]
+        assert (ca.cpu().numpy() == want_cons).all()
+        assert (cp.cpu().numpy() == want_cons[1024:1536]).all()
+        spec2 = api.SynthSpec(seed=8, p_sub=0.01, p_del=0.01, p_ins=0.05, p_n_block=0.02, p_amb=0.01, accessory_frac=0.3)
+        c, _, _ = synth_on_device(ctx, spec2, 500, 0, 4096)
+        assert not bool((a == c).all())
+        codes = set(np.unique(full).tolist())
+        assert {0, 1, 2, 4, 8, 15} <= codes
+
+
+@pytest.mark.parametrize("algo", [api.FITCH, api.SANKOFF])
+def test_config2_full_size_properties_and_subsample_parity(algo):
+    """BASELINE config 2 (20 000 taxa x 30 000 columns, random binary tree) at full size:
+    sortedness/uniqueness of the records, tiling- and chunking-invariance, host path == device path,
+    and bit-exactness against the oracle on a 96-column subsample."""
+    torch = _torch()
+    N, L = 20000, 30000
+    tree = trees.random_binary_tree(N)
+    spec = api.SynthSpec()
+    with api.Context(tree) as ctx:
+        d_msa, d_cons, stride = synth_on_device(ctx, spec, N, 0, L)
+        _, n = ctx.run_device(algo, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr())
+        rec = ctx.download(n)
+        key = rec["node"].astype(np.int64) << 32 | rec["pos"].astype(np.int64)
+        assert (np.diff(key) > 0).all(), "records must be strictly sorted by (node,pos)"
+        assert rec["pos"].min() >= 0 and rec["pos"].max() < L and rec["node"].max() < tree.n_nodes
+        assert ((rec["type"] == 1) == (rec["code"] == 0)).all()      # ND <=> state is a gap
+        assert ((rec["type"] == 2) == (rec["parent_code"] == 0)).all()  # NI <=> parent is a gap
+        assert (rec["code"] != rec["parent_code"]).all()
+        digest = G.digest_muts(rec)
+        # tiling / chunking must not change a single record
+        ctx.set_tuning(chunk_nodes=97, tile_cols=7000)
+        _, n2 = ctx.run_device(algo, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr())
+        assert n2 == n and G.digest_muts(ctx.download(n2)) == digest
+        # host-buffer path
+        ctx.set_tuning(0, 0)
+        host = d_msa.cpu().numpy()
+        cons = d_cons.cpu().numpy()
+        got = ctx.run(algo, host, L, cons)
+        assert G.digest_muts(got) == digest
+        # oracle on a column subsample (the CPU reference needs ~0.5 ms per column.node)
+        cols = np.sort(np.random.default_rng(1).choice(L, size=96, replace=False))
+        sub = api.unpack_nibbles(host, L)[:, cols]
+        want = O.run_port(algo, tree, sub, cons[cols], None, threads=8)
+        sel = np.isin(rec["pos"], cols)
+        mine = rec[sel].copy()
+        mine["pos"] = np.searchsorted(cols, mine["pos"])
+        mine = mine[np.lexsort((mine["pos"], mine["node"]))]
+        assert G.same_muts(mine, want)

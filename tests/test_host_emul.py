@@ -1,0 +1,113 @@
+"""CPU: the library's plan builder + walk interpreter (the host side of the code the CUDA kernels run per thread),
+emulated one column group at a time by tests/host_emul.cpp, against the oracle and the golden fixtures."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import golden_util as G
+import synth
+from oracle import oracle_api as O
+from panman_b200.api import MUT_DTYPE, pack_nibbles
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SO = os.path.join(ROOT, "tests", "_build", "libhostemul.so")
+
+
+@pytest.fixture(scope="module")
+def emul():
+    os.makedirs(os.path.dirname(SO), exist_ok=True)
+    srcs = [os.path.join(ROOT, "tests", "host_emul.cpp"), os.path.join(ROOT, "panman_b200", "csrc", "plan.cpp")]
+    deps = srcs + [os.path.join(ROOT, "panman_b200", "csrc", f) for f in ("walk.cuh", "plan.hpp")]
+    if not os.path.exists(SO) or any(os.path.getmtime(d) > os.path.getmtime(SO) for d in deps):
+        subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wno-unknown-pragmas",
+                        "-I/usr/local/cuda/include", "-o", SO] + srcs, check=True)
+    lib = C.CDLL(SO)
+    lib.emul_free.argtypes = [C.c_void_p]
+    return lib
+
+
+def run_emul(lib, algo, tree, msa_codes, cons, forced, chunk_nodes, want_plan=False):
+    nib = pack_nibbles(msa_codes) if msa_codes.shape[0] else np.zeros((0, 1), np.uint8)
+    n_cols = int(cons.shape[0])
+    arrs = [np.ascontiguousarray(a, np.int32) for a in (tree.parent, tree.child_off, tree.child_idx, tree.leaf_row)]
+    cons = np.ascontiguousarray(cons, np.uint8)
+    frc = None if forced is None else np.ascontiguousarray(forced, np.uint8)
+    out, n = C.c_void_p(), C.c_int64()
+    plan = (C.c_int64 * 6)()
+    rc = lib.emul_run(C.c_int(algo), C.c_int32(tree.n_nodes), *[C.c_void_p(a.ctypes.data) for a in arrs],
+                      C.c_void_p(nib.ctypes.data), C.c_int64(nib.shape[1]), C.c_int64(n_cols), C.c_void_p(cons.ctypes.data),
+                      None if frc is None else C.c_void_p(frc.ctypes.data), C.c_int32(chunk_nodes), C.byref(out), C.byref(n), plan)
+    if rc != 0:
+        raise RuntimeError(f"emul_run rc={rc}")
+    res = np.frombuffer((C.c_char * (n.value * MUT_DTYPE.itemsize)).from_address(out.value), MUT_DTYPE).copy() if n.value \
+        else np.zeros(0, MUT_DTYPE)
+    lib.emul_free(out)
+    return (res, list(plan)) if want_plan else res
+
+
+def test_emul_matches_golden_small(emul, small_cases):
+    z = small_cases
+    for name in z["case_names"]:
+        tree, msa, cons, forced = G.case_inputs(z, str(name))
+        for algo in (0, 1):
+            for chunk in (1 << 30, 4):
+                got = run_emul(emul, algo, tree, msa, cons, forced, chunk)
+                assert G.same_muts(got, z[f"{name}/muts{algo}"]), (name, algo, chunk)
+
+
+@pytest.mark.parametrize("low,with_ref", [(0, 0), (0, 1), (1, 0), (1, 1)])
+def test_emul_matches_golden_c1(emul, c1, low, with_ref):
+    key = f"v{low}{with_ref}_"
+    tree = G.c1_tree(c1)
+    msa = G.unpack_nibbles(c1["msa_nibbles"], int(c1["n_cols"]))
+    forced = msa[list(c1["row_ids"]).index(str(c1[key + "reference"]))] if with_ref else None
+    got = run_emul(emul, low, tree, msa, c1[key + "consensus"], forced, 8)
+    assert got.shape[0] == int(c1[key + "n_muts"])
+    assert G.digest_muts(got) == str(c1[key + "muts_sha256"])
+
+
+def test_emul_matches_oracle_random(emul):
+    rng = np.random.default_rng(11)
+    for trial in range(40):
+        arity = 2 if trial < 16 else int(rng.integers(2, 7))
+        tree = synth.random_tree(int(rng.integers(2, 200)), rng, max_arity=arity, absent_frac=0.0 if trial % 3 else 0.1)
+        L = int(rng.integers(1, 150))
+        msa = synth.simulate_msa(tree, L, rng, p_sub=0.1, p_del=0.05, p_ins=0.2, p_n=0.05, p_amb=0.05)
+        cons = synth.consensus_first_nongap(msa)
+        forced = msa[int(rng.integers(0, msa.shape[0]))] if trial % 2 else None
+        chunk = int(rng.choice([2, 3, 8, 32, 1 << 30]))
+        for algo in (0, 1):
+            want = O.run_port(algo, tree, msa, cons, forced, threads=2)
+            got, plan = run_emul(emul, algo, tree, msa, cons, forced, chunk, want_plan=True)
+            assert G.same_muts(got, want), (trial, algo, chunk, plan)
+
+
+def test_emul_ladder_and_balanced_stack_depth(emul):
+    rng = np.random.default_rng(5)
+    ladder = synth.caterpillar(3000)
+    msa = synth.simulate_msa(ladder, 40, rng, p_sub=0.02)
+    cons = synth.consensus_first_nongap(msa)
+    for algo in (0, 1):
+        want = O.run_port(algo, ladder, msa, cons, None)
+        got, plan = run_emul(emul, algo, ladder, msa, cons, None, 1 << 30, want_plan=True)
+        assert G.same_muts(got, want)
+        assert plan[3] <= 1 and plan[4] <= 1  # a ladder needs no stack at all: the heavy child is walked in place
+        got = run_emul(emul, algo, ladder, msa, cons, None, 100)
+        assert G.same_muts(got, want)
+    # perfectly balanced tree: stack depth stays logarithmic
+    def bal(lo, hi):
+        return lo if hi - lo == 1 else [bal(lo, (lo + hi) // 2), bal((lo + hi) // 2, hi)]
+    tree = synth._flatten(bal(0, 256))
+    _, plan = run_emul(emul, 0, tree, synth.simulate_msa(tree, 8, rng), np.ones(8, np.uint8), None, 1 << 30, want_plan=True)
+    assert plan[3] <= 8 and plan[4] <= 8
+
+
+def test_emul_sankoff_invalid_root(emul):
+    tree = synth._flatten([None, None])
+    with pytest.raises(RuntimeError):
+        run_emul(emul, 1, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), None, 1 << 30)
+    assert run_emul(emul, 0, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), None, 1 << 30).shape[0] == 0
+    assert run_emul(emul, 1, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), np.array([1, 0, 2], np.uint8), 1 << 30).shape[0] == 2

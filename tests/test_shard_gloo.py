@@ -1,0 +1,91 @@
+"""CPU, world_size 2 over gloo: the multi-GPU host logic -- column sharding, the variable-length gather of records to
+rank 0, the global (node,pos) order and packing AFTER the gather.  The per-rank compute is stood in for by the oracle
+(allowed in tests only); the result must equal the unsharded oracle run, including <=6-runs that straddle the boundary."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import golden_util as G
+import synth
+from oracle import oracle_api as O
+from panman_b200 import shard
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _to_mut12(rec):
+    out = np.zeros(rec.shape[0], dtype=[("node", "<i4"), ("pos", "<i4"), ("type", "u1"), ("code", "u1"), ("parent_code", "u1"), ("pad", "u1")])
+    for k in ("node", "pos", "type", "code"):
+        out[k] = rec[k]
+    return out
+
+
+def _worker(rank, world, port, seed, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(seed)
+    tree = synth.random_tree(40, rng, max_arity=3)
+    L = 200
+    msa = synth.simulate_msa(tree, L, rng, p_sub=0.02, p_del=0.15, p_ins=0.1)  # long indel runs across the boundary
+    e0 = shard.column_shards(L, world)[0][1]
+    msa[0, e0 - 4:e0 + 4] = 15  # one leaf is N across the shard boundary: a run of 8 consecutive NS records
+    cons = synth.consensus_first_nongap(msa)
+    b, e = shard.column_shards(L, world)[rank]
+    mine = O.run_port(1, tree, np.ascontiguousarray(msa[:, b:e]), cons[b:e], None)
+    merged = shard.gather_records(shard.numpy_to_records(_to_mut12(mine)), b, rank, world)
+    if rank == 0:
+        got = shard.records_to_numpy(merged)
+        want = O.run_port(1, tree, msa, cons, None)
+        ok = G.same_muts(got, want)
+        off_g, nuc_g = O.pack_port(_as_oracle(got), tree.n_nodes)
+        off_w, nuc_w = O.pack_port(want, tree.n_nodes)
+        ok = ok and (off_g == off_w).all() and G.same_nuc(nuc_g, nuc_w)
+        # packing per shard and concatenating would NOT be the same thing: make sure a run really straddles the boundary
+        e0 = shard.column_shards(L, world)[0][1]
+        before = set(want["node"][want["pos"] == e0 - 1].tolist())
+        after = set(want["node"][want["pos"] == e0].tolist())
+        straddle = len(before & after) > 0
+        q.put((ok, straddle))
+    dist.destroy_process_group()
+
+
+def _as_oracle(rec):
+    out = np.zeros(rec.shape[0], dtype=O.MUT_DTYPE)
+    for k in ("node", "pos", "type", "code"):
+        out[k] = rec[k]
+    return out
+
+
+def test_column_shards_cover_and_align():
+    for L, w in ((30000, 8), (29903, 4), (31, 2), (64, 3), (1, 2)):
+        sh = shard.column_shards(L, w)
+        assert sh[0][0] == 0 and sh[-1][1] == L
+        for (b0, e0), (b1, e1) in zip(sh, sh[1:]):
+            assert e0 == b1 and b1 % 32 == 0 or b1 == L
+
+
+def test_gather_merge_pack_world2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, 1234, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    ok, straddle = q.get(timeout=10)
+    assert ok
+    assert straddle, "test input should contain a run of consecutive positions across the shard boundary"
