@@ -101,7 +101,8 @@ int pmfs_set_stream(pmfs_ctx* ctx, void* cuda_stream);
  *   root_forced_code  [n_cols] or NULL: Fitch refState (src/fitchSankoff.cpp:45-47, passed at src/panman.cpp:1409-1410
  *                               when --reference is given) / Sankoff defaultValue (:491-492, src/panman.cpp:1573-1594)
  *   out, n_out        records sorted by (node,pos): exactly the order the per-node std::sort of :1437 produces.
- *                     Owned by the context until pmfs_result_free or the next run.
+ *                     They live in a pinned buffer owned by the context: valid until the next pmfs_run on this context,
+ *                     pmfs_result_free or pmfs_destroy.
  * Error behaviour: where the reference exit()s or asserts, this returns a status (PMFS_ERR_ROOT_INVALID, PMFS_ERR_ARG). */
 int pmfs_run(pmfs_ctx* ctx, int algo, const uint8_t* msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
              int64_t n_cols, const uint8_t* consensus_code, const uint8_t* root_forced_code, pmfs_mut** out,

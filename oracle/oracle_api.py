@@ -178,8 +178,18 @@ def ref_build(msa_path: str, nwk_path: str, reference: str = "", low_mem: bool =
     return res
 
 
+def as_mut(muts: np.ndarray) -> np.ndarray:
+    """Any structured array with node/pos/type/code fields -> MUT_DTYPE (e.g. the product's 12-byte pmfs_mut records)."""
+    if muts.dtype == MUT_DTYPE:
+        return np.ascontiguousarray(muts)
+    out = np.zeros(muts.shape[0], dtype=MUT_DTYPE)
+    for k in ("node", "pos", "type", "code"):
+        out[k] = muts[k]
+    return out
+
+
 def _pack(lib, fn, free, muts: np.ndarray, n_nodes: int):
-    m = np.ascontiguousarray(muts, dtype=MUT_DTYPE)
+    m = as_mut(muts)
     off, out, n = C.c_void_p(), C.c_void_p(), C.c_int64()
     rc = fn(C.c_void_p(m.ctypes.data), C.c_int64(m.shape[0]), C.c_int32(n_nodes), C.byref(off), C.byref(out), C.byref(n))
     assert rc == 0

@@ -173,8 +173,10 @@ class Context:
         """Run on the given cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream); 0 = the context's own."""
         _check(self._L.pmfs_set_stream(self._h, cuda_stream or None))
 
-    def run(self, algo: int, msa_nibbles: np.ndarray, n_cols: int, consensus: np.ndarray, forced=None) -> np.ndarray:
-        """Host buffers in, host records out (pmfs_run).  msa_nibbles: [rows, stride] uint8."""
+    def run(self, algo: int, msa_nibbles: np.ndarray, n_cols: int, consensus: np.ndarray, forced=None,
+            copy: bool = True) -> np.ndarray:
+        """Host buffers in, host records out (pmfs_run).  msa_nibbles: [rows, stride] uint8.
+        copy=False returns a view of the context's pinned result buffer, valid until the next run."""
         msa = np.ascontiguousarray(msa_nibbles, dtype=np.uint8)
         cons = np.ascontiguousarray(consensus, dtype=np.uint8)
         assert cons.shape[0] == n_cols
@@ -185,10 +187,13 @@ class Context:
                                 None if frc is None else frc.ctypes.data, C.byref(out), C.byref(n)))
         if n.value:
             buf = (C.c_char * (n.value * MUT_DTYPE.itemsize)).from_address(out.value)
-            res = np.frombuffer(buf, dtype=MUT_DTYPE).copy()
+            res = np.frombuffer(buf, dtype=MUT_DTYPE)
+            if copy:
+                res = res.copy()
         else:
             res = np.zeros(0, MUT_DTYPE)
-        self._L.pmfs_result_free(self._h, out)
+        if copy:
+            self._L.pmfs_result_free(self._h, out)
         return res
 
     def run_device(self, algo: int, d_msa: int, row_stride: int, n_rows: int, n_cols: int, d_cons: int, d_forced: int = 0):

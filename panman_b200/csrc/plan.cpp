@@ -48,7 +48,7 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
             P.int_to_node.push_back(v);
         } else {
             if (t.leaf_row[v] < -2 || t.leaf_row[v] == -1) return "leaf_row of a leaf must be a row >= 0 or -2";
-            if ((int64_t)t.leaf_row[v] >= (int64_t)kAbsentLeaf >> 3) return "leaf_row too large";
+            if ((int64_t)t.leaf_row[v] >= ((int64_t)1 << 28)) return "leaf_row too large";
             max_row = std::max(max_row, t.leaf_row[v]);
             P.n_leaves++;
         }
@@ -62,18 +62,36 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
             P.n_rows_used++;
         }
 
-    // ---- chunking: rem[v] = nodes of v's subtree not yet cut off; cut v once rem[v] >= chunk_nodes
+    // ---- chunking: rem[v] = nodes of v's subtree not yet cut off; cut v once rem[v] >= threshold.  Round 0 cuts the
+    // whole tree with `chunk_nodes`; every further round re-cuts only the residual top (nodes with a cut descendant)
+    // with a threshold 8x smaller, until the residual is small.
     if (chunk_nodes < 2) chunk_nodes = 2;
     std::vector<int32_t> rem(V, 1);
-    std::vector<uint8_t> cut(V, 0);
-    for (int32_t v = V - 1; v >= 1; v--) {
-        if (P.int_id[v] >= 0 && rem[v] >= chunk_nodes) {
-            cut[v] = 1;
-            rem[t.parent[v]] += 1;
-        } else {
-            rem[t.parent[v]] += rem[v];
+    std::vector<uint8_t> cut(V, 0), hascut(V, 0);
+    int64_t thr = chunk_nodes;
+    for (int round = 0; round < 8; round++) {
+        std::fill(rem.begin(), rem.end(), 1);
+        bool any_new = false;
+        for (int32_t v = V - 1; v >= 1; v--) {
+            const bool candidate = P.int_id[v] >= 0 && !cut[v] && (round == 0 || hascut[v]);
+            if (candidate && rem[v] >= thr) {
+                cut[v] = 1;
+                any_new = true;
+            }
+            if (cut[v]) {
+                rem[t.parent[v]] += 1;
+                hascut[t.parent[v]] = 1;
+            } else {
+                rem[t.parent[v]] += rem[v];
+                if (hascut[v]) hascut[t.parent[v]] = 1;
+            }
         }
+        if (!any_new || rem[0] < 32 || thr <= 8) break;
+        thr = std::max<int64_t>(8, thr / 8);
     }
+    // rem[] must describe the final cut set (the walk orders children by it)
+    std::fill(rem.begin(), rem.end(), 1);
+    for (int32_t v = V - 1; v >= 1; v--) rem[t.parent[v]] += cut[v] ? 1 : rem[v];
     cut[0] = 1;
     std::vector<int32_t> chunk_of_root(V, -1);
     for (int32_t v = 0; v < V; v++)
@@ -96,8 +114,19 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
 
     auto is_sub = [&](int32_t c) { return P.int_id[c] >= 0 && !cut[c]; };
     auto operand = [&](int32_t c) -> uint32_t {
-        if (P.int_id[c] >= 0) return kOperandSet | (uint32_t)P.int_id[c];
+        if (P.int_id[c] >= 0) return kOperandSet | (cut[c] ? kOperandExt : 0u) | (uint32_t)P.int_id[c];
         return t.leaf_row[c] >= 0 ? (uint32_t)t.leaf_row[c] : kAbsentLeaf;
+    };
+    // pushes an operand word on the program and the loads it will consume on the stream
+    auto push_operand = [&](int32_t c) {
+        const uint32_t o = operand(c);
+        P.fwd_prog.push_back(o);
+        if (o & kOperandSet) {
+            if (o & kOperandExt)
+                for (uint32_t q = 0; q < 4; q++) P.fwd_stream.push_back(kStreamSet | ((o & kOperandIdMask) << 2) | q);
+        } else if (o != kAbsentLeaf) {
+            P.fwd_stream.push_back(o);
+        }
     };
 
     // ---- forward (post-order) programs
@@ -111,6 +140,7 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
     for (int32_t ci = 0; ci < NC; ci++) {
         Chunk& ch = P.chunks[ci];
         ch.fwd_off = (int64_t)P.fwd_prog.size();
+        ch.fwd_stream_off = (int64_t)P.fwd_stream.size();
         int32_t depth = 0;
         st.clear();
         st.push_back({ch.root_node, -1, false, {}});
@@ -149,13 +179,13 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
                 } else {
                     int32_t other = t.child_idx[b] == f.subs[0] ? t.child_idx[b + 1] : t.child_idx[b];
                     P.fwd_prog.push_back(op(F_JOIN_IMM, (uint32_t)P.int_id[v]));
-                    P.fwd_prog.push_back(operand(other));
+                    push_operand(other);
                     st.pop_back();
                 }
             } else if (binary) {
                 P.fwd_prog.push_back(op(F_JOIN_IMM2, (uint32_t)P.int_id[v]));
-                P.fwd_prog.push_back(operand(t.child_idx[b]));
-                P.fwd_prog.push_back(operand(t.child_idx[b + 1]));
+                push_operand(t.child_idx[b]);
+                push_operand(t.child_idx[b + 1]);
                 st.pop_back();
             } else {
                 if (f.i < ns) {
@@ -164,18 +194,20 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
                 } else {
                     P.fwd_prog.push_back(op(F_POLY, (uint32_t)P.int_id[v]));
                     P.fwd_prog.push_back((uint32_t)(e - b));
-                    for (int32_t k = b; k < e; k++) P.fwd_prog.push_back(operand(t.child_idx[k]));
+                    for (int32_t k = b; k < e; k++) push_operand(t.child_idx[k]);
                     st.pop_back();
                 }
             }
         }
         ch.fwd_len = (int32_t)((int64_t)P.fwd_prog.size() - ch.fwd_off);
+        ch.fwd_stream_len = (int32_t)((int64_t)P.fwd_stream.size() - ch.fwd_stream_off);
     }
 
     // ---- backward (pre-order) programs
     for (int32_t ci = 0; ci < NC; ci++) {
         Chunk& ch = P.chunks[ci];
         ch.bwd_off = (int64_t)P.bwd_prog.size();
+        ch.bwd_stream_off = (int64_t)P.bwd_stream.size();
         int32_t depth = 0;
         st.clear();
         st.push_back({ch.root_node, -1, false, {}});
@@ -184,10 +216,14 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
             const int32_t v = f.v, b = t.child_off[v], e = t.child_off[v + 1];
             if (f.i < 0) {
                 P.bwd_prog.push_back(v == 0 ? op(B_ENTER_ROOT, 0) : op(B_ENTER, (uint32_t)P.int_id[v]));
+                for (uint32_t q = 0; q < 4; q++) P.bwd_stream.push_back(kStreamSet | ((uint32_t)P.int_id[v] << 2) | q);
                 for (int32_t k = b; k < e; k++) {
                     int32_t c = t.child_idx[k];
                     if (P.int_id[c] < 0) {
-                        if (t.leaf_row[c] >= 0) P.bwd_prog.push_back(op(B_LEAF, (uint32_t)t.leaf_row[c]));
+                        if (t.leaf_row[c] >= 0) {
+                            P.bwd_prog.push_back(op(B_LEAF, (uint32_t)t.leaf_row[c]));
+                            P.bwd_stream.push_back((uint32_t)t.leaf_row[c]);
+                        }
                     } else if (cut[c]) {
                         P.bwd_prog.push_back(op(B_XCHILD, (uint32_t)chunk_of_root[c]));
                     } else {
@@ -217,6 +253,7 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
             }
         }
         ch.bwd_len = (int32_t)((int64_t)P.bwd_prog.size() - ch.bwd_off);
+        ch.bwd_stream_len = (int32_t)((int64_t)P.bwd_stream.size() - ch.bwd_stream_off);
     }
 
     // ---- level lists

@@ -21,7 +21,15 @@ namespace pmfs {
 // internal-node set array, else MSA row `w`; kAbsentLeaf is a leaf with no MSA row (empty set).
 constexpr uint32_t kOpBits = 3;
 constexpr uint32_t kOperandSet = 0x80000000u;
-constexpr uint32_t kAbsentLeaf = 0x7fffffffu;
+constexpr uint32_t kOperandExt = 0x40000000u;  // with kOperandSet: the set was written by an EARLIER launch (root of a child
+                                               // chunk), so it may be prefetched; without it the set belongs to this chunk
+constexpr uint32_t kOperandIdMask = 0x3fffffffu;
+constexpr uint32_t kAbsentLeaf = 0x3fffffffu;
+
+// ---- load streams: next to each walk program, the sequence of 16-byte global loads the program will consume, in
+// consumption order, so the kernels can run them ahead of the walk through a shared-memory ring (cp.async).
+// Entry: bit 31 set -> quarter `e & 3` of set row `(e & 0x7fffffff) >> 2`; else MSA row `e`.
+constexpr uint32_t kStreamSet = 0x80000000u;
 
 enum FwdOp : uint32_t {
     F_PUSH = 0,       // push the running set T on the per-thread stack
@@ -45,6 +53,8 @@ struct Chunk {
     int32_t root_int = 0;   // its internal id
     int64_t fwd_off = 0, bwd_off = 0;
     int32_t fwd_len = 0, bwd_len = 0;
+    int64_t fwd_stream_off = 0, bwd_stream_off = 0;
+    int32_t fwd_stream_len = 0, bwd_stream_len = 0;
     int32_t height = 0;  // 0 = no child chunks
     int32_t depth = 0;   // 0 = contains the tree root
 };
@@ -56,6 +66,7 @@ struct Plan {
     std::vector<int32_t> int_to_node;  // [I]
     std::vector<int32_t> row_to_node;  // [max row + 1] node id or -1
     std::vector<uint32_t> fwd_prog, bwd_prog;
+    std::vector<uint32_t> fwd_stream, bwd_stream;
     std::vector<Chunk> chunks;
     // chunk ids grouped by level, heaviest first inside a level; level l spans [lvl_off[l], lvl_off[l+1])
     std::vector<int32_t> fwd_order, bwd_order;
@@ -65,7 +76,9 @@ struct Plan {
 };
 
 // Validates `tree` and builds the plan.  chunk_nodes: cut a subtree off as its own chunk once it holds at least this
-// many not-yet-cut nodes.  Returns an empty string or an error description.
+// many not-yet-cut nodes.  The part of the tree left above those chunks is cut again with a threshold 8x smaller, and so
+// on: chunks shrink towards the root, where few chunks run side by side and the length of one chunk's walk is the
+// critical path.  Returns an empty string or an error description.
 std::string build_plan(const pmfs_tree& tree, int32_t chunk_nodes, Plan& plan);
 
 }  // namespace pmfs

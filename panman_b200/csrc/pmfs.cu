@@ -45,6 +45,9 @@ struct WalkParams {
     const int64_t* chunk_off;   // [NC] offset of each chunk's program
     const int32_t* chunk_len;   // [NC]
     const int32_t* order;       // chunk ids of this launch's level
+    const uint32_t* stream;     // load streams (plan.hpp)
+    const int64_t* stream_off;  // [NC]
+    const int32_t* stream_len;  // [NC]
     int32_t ctas_per_chunk;
     int32_t stack_depth;
     const uint4* msa;           // first group of this column tile
@@ -67,21 +70,67 @@ struct WalkParams {
     unsigned int* err_flag;
 };
 
-template <bool READONLY_SETS>
+constexpr int kRingFwd = 8;   // 16-byte ring slots per thread: loads run this far ahead of the bottom-up walk
+constexpr int kRingBwd = 16;  // top-down walk: one internal node = 4 slots
+
+// Per-thread view of one (chunk, column group).  Global loads whose addresses are known from the plan (leaf rows, sets
+// written by earlier launches) do not go through registers: they are issued kRing entries ahead as 16-byte cp.async
+// copies into a shared-memory ring private to the thread, in the order of the chunk's load stream, so the walk itself
+// never waits for HBM latency as long as the ring stays ahead.
+template <bool READONLY_SETS, int RING>
 struct DevEnv {
     const WalkParams& p;
-    int64_t g;   // clamped column group
+    int64_t g;      // clamped column group
+    int64_t gwarp;  // (unclamped) column group of this warp's lane 0
     bool active;
+    uint4* ring;      // [RING][kTPB]
     uint4* fstk;      // [depth][4][kTPB]
     uint32_t* bstk;   // [depth][5][kTPB]
     int sp = 0;
     int lane;
+    const uint32_t* strm;
+    int32_t slen;
+    int32_t cons = 0;
 
-    __device__ DevEnv(const WalkParams& p_, int64_t g_, bool a, void* smem)
-        : p(p_), g(g_), active(a), fstk((uint4*)smem), bstk((uint32_t*)smem), lane(threadIdx.x & 31) {}
+    __device__ DevEnv(const WalkParams& p_, int64_t g_, int64_t g_unclamped, bool a, void* smem, int32_t chunk)
+        : p(p_), g(g_), gwarp(g_unclamped - (threadIdx.x & 31)), active(a), ring((uint4*)smem), fstk((uint4*)smem + RING * kTPB),
+          bstk((uint32_t*)((uint4*)smem + RING * kTPB)), lane(threadIdx.x & 31),
+          strm(p_.stream + p_.stream_off[chunk]), slen(p_.stream_len[chunk]) {
+#pragma unroll
+        for (int j = 0; j < RING - 1; j++) issue(j);
+    }
 
     __device__ __forceinline__ uint32_t word(const uint32_t* prog, int32_t pc) const { return __ldg(prog + pc); }
-    __device__ __forceinline__ uint4 leaf(uint32_t row) const { return __ldg(p.msa + (int64_t)row * p.msa_stride16 + g); }
+
+    // stream entry j -> ring slot j % RING (always commits a group, empty past the end, so group counting stays uniform)
+    __device__ __forceinline__ void issue(int32_t j) {
+        if (j < slen) {
+            const uint32_t e = __ldg(strm + j);
+            const uint4* src = (e & kStreamSet) ? p.S + (int64_t)(e & ~kStreamSet) * p.G + g
+                                                : p.msa + (int64_t)e * p.msa_stride16 + g;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(ring + (j % RING) * kTPB + threadIdx.x);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    // next ring entry: wait until it has landed, read it, then refill the slot freed by the PREVIOUS call
+    __device__ __forceinline__ uint4 next() {
+        asm volatile("cp.async.wait_group %0;" ::"n"(RING - 2) : "memory");
+        const uint32_t src = (uint32_t)__cvta_generic_to_shared(ring + (cons % RING) * kTPB + threadIdx.x);
+        uint4 v;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(src) : "memory");
+        issue(cons + RING - 1);
+        cons++;
+        return v;
+    }
+    __device__ __forceinline__ uint4 leaf(uint32_t) { return next(); }
+    __device__ __forceinline__ void load_x(uint32_t, Planes16& s) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            uint4 v = next();
+            s.p[4 * i] = v.x; s.p[4 * i + 1] = v.y; s.p[4 * i + 2] = v.z; s.p[4 * i + 3] = v.w;
+        }
+    }
 
     __device__ __forceinline__ void load_arr(const uint4* base, uint32_t id, Planes16& s) const {
         const uint4* q = base + ((int64_t)id * 4) * p.G + g;
@@ -138,35 +187,39 @@ struct DevEnv {
     }
     __device__ __forceinline__ bool any(bool x) const { return __any_sync(0xffffffffu, x); }
 
-    // Stream compaction of one node's mutations: per-lane counts -> warp prefix sum (shuffles) -> ONE atomic per warp
-    // reserves the slots -> each lane writes its records.  Order inside the buffer is scheduling dependent; the final
-    // radix sort by (node,pos) makes the result deterministic.
+    // Stream compaction of one node's mutations, warp-cooperative.  Called by all 32 lanes (the caller branches on a
+    // warp vote).  One REDUX gives the warp's record count, ONE atomic reserves the slots; then, for every lane that has
+    // mutations, its mask and planes are broadcast and each lane of the warp writes the record of "its" bit -- a block of
+    // 32 N's costs the same ~40 instructions as a single substitution, and the stores are coalesced.  The order inside
+    // the buffer depends on scheduling; the final radix sort by (node,pos) makes the result deterministic.
     __device__ void emit(uint32_t node, uint32_t m, const Code4& G, const Code4& P) const {
-        const int cnt = __popc(m);
-        int incl = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int x = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += x;
-        }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        const unsigned full = 0xffffffffu;
+        const uint32_t total = __reduce_add_sync(full, (uint32_t)__popc(m));
         unsigned long long base = 0;
-        if (lane == 31) base = atomicAdd(p.out_count, (unsigned long long)total);
-        base = __shfl_sync(0xffffffffu, base, 31);
-        unsigned long long idx = base + (unsigned long long)(incl - cnt);
-        while (m) {
-            const int q = __ffs(m) - 1;
-            m &= m - 1;
-            if (idx < p.out_cap) {
-                const uint32_t cg = ((G.b[0] >> q) & 1) | (((G.b[1] >> q) & 1) << 1) | (((G.b[2] >> q) & 1) << 2) | (((G.b[3] >> q) & 1) << 3);
-                const uint32_t cp = ((P.b[0] >> q) & 1) | (((P.b[1] >> q) & 1) << 1) | (((P.b[2] >> q) & 1) << 2) | (((P.b[3] >> q) & 1) << 3);
-                // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
-                const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
-                const unsigned long long pos = (unsigned long long)(p.col_base + g * 32 + column_of_bit(q));
-                p.out_keys[idx] = ((unsigned long long)node << 32) | pos;
-                p.out_vals[idx] = type | (cg << 8) | (cp << 16);
+        if (lane == 0) base = atomicAdd(p.out_count, (unsigned long long)total);
+        base = __shfl_sync(full, base, 0);
+        uint32_t srcs = __ballot_sync(full, m != 0);
+        const unsigned long long pos0 = (unsigned long long)(p.col_base + gwarp * 32 + column_of_bit(lane));
+        while (srcs) {
+            const int src = __ffs(srcs) - 1;
+            srcs &= srcs - 1;
+            const uint32_t mm = __shfl_sync(full, m, src);
+            uint32_t cg = 0, cp = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                cg |= ((__shfl_sync(full, G.b[i], src) >> lane) & 1u) << i;
+                cp |= ((__shfl_sync(full, P.b[i], src) >> lane) & 1u) << i;
             }
-            idx++;
+            if ((mm >> lane) & 1u) {
+                const unsigned long long idx = base + __popc(mm & ((1u << lane) - 1u));
+                if (idx < p.out_cap) {
+                    // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
+                    const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
+                    p.out_keys[idx] = ((unsigned long long)node << 32) | (pos0 + (unsigned long long)src * 32);
+                    p.out_vals[idx] = type | (cg << 8) | (cp << 16);
+                }
+            }
+            base += __popc(mm);
         }
     }
     __device__ __forceinline__ void emit_internal(uint32_t id, uint32_t m, const Code4& G, const Code4& P) const {
@@ -193,7 +246,7 @@ __global__ void __launch_bounds__(kTPB) fwd_kernel(const WalkParams p) {
     const int64_t g0 = (int64_t)(blockIdx.x % p.ctas_per_chunk) * kTPB + threadIdx.x;
     const bool active = g0 < p.G;
     const int64_t g = active ? g0 : p.G - 1;
-    DevEnv<false> env(p, g, active, smem);
+    DevEnv<false, kRingFwd> env(p, g, g0, active, smem, chunk);
     Code4 forced;
     const Code4* fp = nullptr;
     if (ALGO == kAlgoFitch && p.forced_planes) {
@@ -211,7 +264,7 @@ __global__ void __launch_bounds__(kTPB) bwd_kernel(const WalkParams p) {
     const int64_t g0 = (int64_t)(blockIdx.x % p.ctas_per_chunk) * kTPB + threadIdx.x;
     const bool active = g0 < p.G;
     const int64_t g = active ? g0 : p.G - 1;
-    DevEnv<true> env(p, g, active, smem);
+    DevEnv<true, kRingBwd> env(p, g, g0, active, smem, chunk);
     Code4 P, forced;
     uint32_t pv = ~0u;
     const Code4* fp = nullptr;
@@ -387,8 +440,9 @@ struct pmfs_ctx {
     cudaStream_t own_stream = nullptr;  // created by pmfs_create
     cudaEvent_t ev[8] = {};
     // plan on device
-    DevBuf<uint32_t> d_fwd_prog, d_bwd_prog;
-    DevBuf<int64_t> d_fwd_off, d_bwd_off;
+    DevBuf<uint32_t> d_fwd_prog, d_bwd_prog, d_fwd_stream, d_bwd_stream;
+    DevBuf<int64_t> d_fwd_off, d_bwd_off, d_fwd_soff, d_bwd_soff;
+    DevBuf<int32_t> d_fwd_slen, d_bwd_slen;
     DevBuf<int32_t> d_fwd_len, d_bwd_len, d_fwd_order, d_bwd_order, d_int_to_node, d_row_to_node;
     // per-run state
     DevBuf<uint4> d_S, d_D, d_cons_planes, d_forced_planes, d_xcode;
@@ -401,7 +455,8 @@ struct pmfs_ctx {
     DevBuf<pmfs_mut> d_out;
     // host-path staging
     DevBuf<uint8_t> d_msa, d_cons, d_forced;
-    std::vector<pmfs_mut*> host_results;
+    pmfs_mut* h_out = nullptr;  // pinned
+    size_t h_out_cap = 0;
     int64_t last_n_out = 0;
     pmfs_timing timing = {};
     // synth
@@ -412,11 +467,13 @@ struct pmfs_ctx {
 static int upload_plan(pmfs_ctx* c) {
     const Plan& P = c->plan;
     const size_t NC = P.chunks.size();
-    std::vector<int64_t> foff(NC), boff(NC);
-    std::vector<int32_t> flen(NC), blen(NC);
+    std::vector<int64_t> foff(NC), boff(NC), fsoff(NC), bsoff(NC);
+    std::vector<int32_t> flen(NC), blen(NC), fslen(NC), bslen(NC);
     for (size_t i = 0; i < NC; i++) {
         foff[i] = P.chunks[i].fwd_off; flen[i] = P.chunks[i].fwd_len;
         boff[i] = P.chunks[i].bwd_off; blen[i] = P.chunks[i].bwd_len;
+        fsoff[i] = P.chunks[i].fwd_stream_off; fslen[i] = P.chunks[i].fwd_stream_len;
+        bsoff[i] = P.chunks[i].bwd_stream_off; bslen[i] = P.chunks[i].bwd_stream_len;
     }
     auto up = [&](auto& buf, const auto& v) -> int {
         int rc = buf.ensure(v.size());
@@ -427,6 +484,12 @@ static int upload_plan(pmfs_ctx* c) {
     int rc;
     if ((rc = up(c->d_fwd_prog, P.fwd_prog))) return rc;
     if ((rc = up(c->d_bwd_prog, P.bwd_prog))) return rc;
+    if ((rc = up(c->d_fwd_stream, P.fwd_stream))) return rc;
+    if ((rc = up(c->d_bwd_stream, P.bwd_stream))) return rc;
+    if ((rc = up(c->d_fwd_soff, fsoff))) return rc;
+    if ((rc = up(c->d_bwd_soff, bsoff))) return rc;
+    if ((rc = up(c->d_fwd_slen, fslen))) return rc;
+    if ((rc = up(c->d_bwd_slen, bslen))) return rc;
     if ((rc = up(c->d_fwd_off, foff))) return rc;
     if ((rc = up(c->d_bwd_off, boff))) return rc;
     if ((rc = up(c->d_fwd_len, flen))) return rc;
@@ -525,6 +588,8 @@ void pmfs_destroy(pmfs_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    c->d_fwd_stream.release(); c->d_bwd_stream.release(); c->d_fwd_soff.release(); c->d_bwd_soff.release();
+    c->d_fwd_slen.release(); c->d_bwd_slen.release();
     c->d_fwd_prog.release(); c->d_bwd_prog.release(); c->d_fwd_off.release(); c->d_bwd_off.release();
     c->d_fwd_len.release(); c->d_bwd_len.release(); c->d_fwd_order.release(); c->d_bwd_order.release();
     c->d_int_to_node.release(); c->d_row_to_node.release();
@@ -533,7 +598,7 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_vals.release(); c->d_vals_alt.release(); c->d_count.release(); c->d_err.release();
     c->d_sort_tmp.release(); c->d_out.release(); c->d_msa.release(); c->d_cons.release(); c->d_forced.release();
     c->d_path_off.release(); c->d_path_node.release();
-    for (auto* p : c->host_results) cudaFreeHost(p);
+    if (c->h_out) cudaFreeHost(c->h_out);
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -586,11 +651,14 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     wp.prog = fwd ? c->d_fwd_prog.ptr : c->d_bwd_prog.ptr;
     wp.chunk_off = fwd ? c->d_fwd_off.ptr : c->d_bwd_off.ptr;
     wp.chunk_len = fwd ? c->d_fwd_len.ptr : c->d_bwd_len.ptr;
+    wp.stream = fwd ? c->d_fwd_stream.ptr : c->d_bwd_stream.ptr;
+    wp.stream_off = fwd ? c->d_fwd_soff.ptr : c->d_bwd_soff.ptr;
+    wp.stream_len = fwd ? c->d_fwd_slen.ptr : c->d_bwd_slen.ptr;
     const int32_t* order = fwd ? c->d_fwd_order.ptr : c->d_bwd_order.ptr;
     wp.ctas_per_chunk = (int32_t)((wp.G + kTPB - 1) / kTPB);
     wp.stack_depth = fwd ? P.fwd_stack_depth : P.bwd_stack_depth;
-    const size_t smem = fwd ? (size_t)std::max(1, P.fwd_stack_depth) * 4 * kTPB * sizeof(uint4)
-                            : (size_t)std::max(1, P.bwd_stack_depth) * 5 * kTPB * sizeof(uint32_t);
+    const size_t smem = fwd ? ((size_t)kRingFwd + (size_t)P.fwd_stack_depth * 4) * kTPB * sizeof(uint4)
+                            : (size_t)kRingBwd * kTPB * sizeof(uint4) + (size_t)P.bwd_stack_depth * 5 * kTPB * sizeof(uint32_t);
     if (smem > 200 * 1024) {
         g_error = "walk stack does not fit in shared memory (tree too unbalanced for this chunk size)";
         return PMFS_ERR_ARG;
@@ -717,7 +785,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                                     : launch_levels<kAlgoSankoff>(c, wp, false, &tm.n_launches);
             if (rc) return rc;
             PMFS_CUDA(cudaEventRecord(c->ev[2], c->stream));
-            if (g0 + tile_groups < G_all || true) {
+            if (tile_groups < G_all) {  // several tiles reuse the events: read them before the next tile records again
                 PMFS_CUDA(cudaEventSynchronize(c->ev[2]));
                 float a = 0, b = 0;
                 cudaEventElapsedTime(&a, c->ev[0], c->ev[1]);
@@ -730,6 +798,10 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         PMFS_CUDA(cudaMemcpyAsync(&count, c->d_count.ptr, sizeof(count), cudaMemcpyDeviceToHost, c->stream));
         PMFS_CUDA(cudaMemcpyAsync(&err, c->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
+        if (tile_groups >= G_all) {
+            cudaEventElapsedTime(&fwd_ms, c->ev[0], c->ev[1]);
+            cudaEventElapsedTime(&bwd_ms, c->ev[1], c->ev[2]);
+        }
         if (err) {
             g_error = "pmfs_run: Sankoff root has no finite cost in some column and no forced root was given "
                       "(the reference asserts here, src/fitchSankoff.cpp:505)";
@@ -810,8 +882,10 @@ int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int3
     if (forced && (rc = c->d_forced.ensure((size_t)n_cols))) return rc;
     PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
     const int64_t used = (n_cols + 1) / 2;
-    if (dstride > used) PMFS_CUDA(cudaMemsetAsync(c->d_msa.ptr, 0, (size_t)std::max<int64_t>(1, n_rows) * dstride, c->stream));
-    if (n_rows > 0)
+    if (dstride > used && row_stride != dstride) PMFS_CUDA(cudaMemsetAsync(c->d_msa.ptr, 0, (size_t)std::max<int64_t>(1, n_rows) * dstride, c->stream));
+    if (n_rows > 0 && row_stride == dstride)
+        PMFS_CUDA(cudaMemcpyAsync(c->d_msa.ptr, msa, (size_t)n_rows * dstride, cudaMemcpyHostToDevice, c->stream));
+    else if (n_rows > 0)
         PMFS_CUDA(cudaMemcpy2DAsync(c->d_msa.ptr, (size_t)dstride, msa, (size_t)row_stride, (size_t)used, (size_t)n_rows,
                                     cudaMemcpyHostToDevice, c->stream));
     PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons, (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
@@ -825,8 +899,16 @@ int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int3
     rc = run_device_impl(c, algo, c->d_msa.ptr, dstride, n_rows, n_cols, c->d_cons.ptr, forced ? c->d_forced.ptr : nullptr,
                          &d_out, n_out);
     if (rc) return rc;
-    pmfs_mut* h = nullptr;
-    PMFS_CUDA(cudaMallocHost(&h, std::max<size_t>(1, (size_t)*n_out) * sizeof(pmfs_mut)));
+    // one pinned result buffer per context, grown on demand (pinning memory costs far more than the copy itself)
+    if ((size_t)*n_out > c->h_out_cap || !c->h_out) {
+        if (c->h_out) cudaFreeHost(c->h_out);
+        c->h_out = nullptr;
+        c->h_out_cap = 0;
+        const size_t want = std::max<size_t>(1024, (size_t)*n_out + (size_t)*n_out / 4);
+        PMFS_CUDA(cudaMallocHost(&c->h_out, want * sizeof(pmfs_mut)));
+        c->h_out_cap = want;
+    }
+    pmfs_mut* h = c->h_out;
     PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
     if (*n_out > 0)
         PMFS_CUDA(cudaMemcpyAsync(h, d_out, (size_t)*n_out * sizeof(pmfs_mut), cudaMemcpyDeviceToHost, c->stream));
@@ -834,17 +916,19 @@ int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int3
     PMFS_CUDA(cudaEventSynchronize(c->ev[6]));
     cudaEventElapsedTime(&c->timing.d2h_ms, c->ev[5], c->ev[6]);
     c->timing.total_ms += c->timing.d2h_ms;
-    c->host_results.push_back(h);
     *out = h;
     return PMFS_OK;
 }
 
 void pmfs_result_free(pmfs_ctx* c, pmfs_mut* out) {
-    if (!c || !out) return;
-    auto it = std::find(c->host_results.begin(), c->host_results.end(), out);
-    if (it == c->host_results.end()) return;
-    cudaFreeHost(out);
-    c->host_results.erase(it);
+    // results live in the context's pinned buffer, which is reused by the next pmfs_run and released by pmfs_destroy;
+    // releasing early only matters for very large results
+    if (!c || !out || out != c->h_out) return;
+    if (c->h_out_cap > ((size_t)64 << 20) / sizeof(pmfs_mut)) {
+        cudaFreeHost(c->h_out);
+        c->h_out = nullptr;
+        c->h_out_cap = 0;
+    }
 }
 
 int pmfs_synth_msa(pmfs_ctx* c, const pmfs_synth_spec* spec, int64_t col_begin, int64_t n_cols, uint8_t* d_msa,

@@ -148,8 +148,9 @@ constexpr int kPolyBits = 28;  // counter width of the any-arity Sankoff join: a
 // ---------------------------------------------------------------------------------------------------------------------
 // Env concept (device: kernels.cu; host emulation: tests/host_emul.cpp)
 //   uint32_t word(const uint32_t* prog, int32_t pc)          program word, same for every thread
-//   uint4    leaf(uint32_t row)                               this thread's 32 nibbles of MSA row `row`
-//   void     load_s(uint32_t id, Planes16&)  / store_s        set array S (Fitch: the only one)
+//   uint4    leaf(uint32_t row)                               this thread's 32 nibbles of MSA row `row` (next ring entry)
+//   void     load_x(uint32_t id, Planes16&)                   set S[id], prefetched (next 4 ring entries)
+//   void     load_s(uint32_t id, Planes16&)  / store_s        set array S (Fitch: the only one), direct access
 //   void     load_d(uint32_t id, Planes16&)  / store_d        Sankoff D1 array
 //   void     push(const Planes16&) / pop(Planes16&)           forward stack
 //   void     pushp(const Code4&, uint32_t) / popp(...)        backward stack
@@ -162,7 +163,8 @@ constexpr int kPolyBits = 28;  // counter width of the any-arity Sankoff join: a
 template <class Env>
 PMFS_HD void load_operand(Env& env, uint32_t o, Planes16& s) {
     if (o & kOperandSet) {
-        env.load_s(o & ~kOperandSet, s);
+        if (o & kOperandExt) env.load_x(o & kOperandIdMask, s);  // written by an earlier launch: comes through the ring
+        else env.load_s(o & kOperandIdMask, s);                  // written by this thread earlier in this launch
     } else if (o == kAbsentLeaf) {
         zero16(s);
     } else {
@@ -294,7 +296,7 @@ PMFS_HD uint32_t backward_walk(Env& env, const uint32_t* prog, int32_t len, Code
         const uint32_t code = w & ((1u << kOpBits) - 1), arg = w >> kOpBits;
         if (code == B_ENTER) {
             Planes16 S;
-            env.load_s(arg, S);
+            env.load_x(arg, S);
             const uint32_t hit = mux16(S, P);  // parent's state is in this node's set
             const uint32_t nz = or16(S);
             if (ALGO == kAlgoFitch) {
@@ -338,7 +340,7 @@ PMFS_HD uint32_t backward_walk(Env& env, const uint32_t* prog, int32_t len, Code
             env.popp(P, pv);
         } else {  // B_ENTER_ROOT: P holds the consensus
             Planes16 S;
-            env.load_s(0, S);
+            env.load_x(0, S);
             const uint32_t nz = or16(S);
             Code4 G;
             uint32_t nv;

@@ -30,9 +30,21 @@ struct HostEnv {
     std::vector<Planes16> fstk;
     std::vector<std::pair<Code4, uint32_t>> bstk;
     std::vector<Rec>* out;
+    const uint32_t* stream = nullptr;  // the chunk's load stream: every ring-served load must match it, in order
+    int32_t stream_len = 0, consumed = 0;
+    bool stream_ok = true;
 
+    void expect(uint32_t entry) {
+        if (consumed >= stream_len || stream[consumed] != entry) stream_ok = false;
+        consumed++;
+    }
+    void load_x(uint32_t id, Planes16& s) {
+        for (uint32_t q = 0; q < 4; q++) expect(kStreamSet | (id << 2) | q);
+        load(S, id, s);
+    }
     uint32_t word(const uint32_t* prog, int32_t pc) const { return prog[pc]; }
-    uint4 leaf(uint32_t row) const {
+    uint4 leaf(uint32_t row) {
+        expect(row);
         uint4 v;
         memcpy(&v, msa + (int64_t)row * row_stride + g * 16, 16);
         return v;
@@ -111,6 +123,8 @@ int run(const Plan& P, const uint8_t* msa, int64_t row_stride, int64_t n_cols, c
                 const Chunk& ch = P.chunks[order[k]];
                 for (int64_t g = 0; g < G; g++) {
                     HostEnv env{&P, msa, row_stride, G, g, 0, &S, &D, &xcode, &xv, {}, {}, &out};
+                    env.stream = pass == 0 ? P.fwd_stream.data() + ch.fwd_stream_off : P.bwd_stream.data() + ch.bwd_stream_off;
+                    env.stream_len = pass == 0 ? ch.fwd_stream_len : ch.bwd_stream_len;
                     Code4 fc;
                     const Code4* fp = nullptr;
                     if (forced) {
@@ -121,6 +135,7 @@ int run(const Plan& P, const uint8_t* msa, int64_t row_stride, int64_t n_cols, c
                         (void)has_poly;
                         forward_walk<ALGO, true>(env, P.fwd_prog.data() + ch.fwd_off, ch.fwd_len, ALGO == kAlgoFitch ? fp : nullptr);
                         if (!env.fstk.empty()) return -100;
+                        if (!env.stream_ok || env.consumed != env.stream_len) return -102;
                     } else {
                         Code4 Pc;
                         uint32_t pv = ~0u;
@@ -136,6 +151,7 @@ int run(const Plan& P, const uint8_t* msa, int64_t row_stride, int64_t n_cols, c
                         err |= backward_walk<ALGO>(env, P.bwd_prog.data() + ch.bwd_off, ch.bwd_len, Pc, pv,
                                                    ALGO == kAlgoSankoff ? fp : nullptr, colmask);
                         if (!env.bstk.empty()) return -101;
+                        if (!env.stream_ok || env.consumed != env.stream_len) return -103;
                     }
                 }
             }

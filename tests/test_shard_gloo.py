@@ -62,10 +62,7 @@ def _worker(rank, world, port, seed, q):
 
 
 def _as_oracle(rec):
-    out = np.zeros(rec.shape[0], dtype=O.MUT_DTYPE)
-    for k in ("node", "pos", "type", "code"):
-        out[k] = rec[k]
-    return out
+    return O.as_mut(rec)
 
 
 def test_column_shards_cover_and_align():
