@@ -118,6 +118,27 @@ int pmfs_run_device(pmfs_ctx* ctx, int algo, const uint8_t* d_msa_nibbles, int64
 /* Copies device records of the last pmfs_run_device to a caller buffer of at least n_out records. */
 int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);
 
+/* Fitch pass that allocates nothing.  This entry point has no counterpart in the reference.
+ *
+ * It is meant for callers that cannot ask the CUDA allocator for memory when they need a result: a latency-bound service
+ * loop (cudaMalloc and cudaFree stall the whole device), a process whose HBM already belongs to another allocator, or
+ * code running where the allocator must not be called.  It computes exactly what pmfs_run_device(ctx, PMFS_FITCH, ...)
+ * computes, on the plan the context already holds, but every intermediate (the set array shared by the two walk
+ * kernels, parent states, bit-sliced consensus, unsorted record pairs, sort buffers) comes out of one 32 MiB array with
+ * static storage duration in device memory, which every GPU that loads this library keeps until the process exits.
+ *   inputs   device pointers as for pmfs_run_device (all columns are processed in one pass, no tiling)
+ *   outputs  d_out: caller's device buffer of out_capacity records, filled sorted by (node,pos); *n_out: record count
+ * Limits: the call is rejected with PMFS_ERR_ARG and an explanatory pmfs_last_error() when
+ *   256-byte-rounded (n_internal*ceil(n_cols/32)*64 + n_chunks*ceil(n_cols/32)*20 + out_capacity*24 + sort workspace)
+ * exceeds 32 MiB, and when more than out_capacity records are produced (*n_out then holds the number needed).
+ * The first call on a device looks up the array's address on that device; make that first call before any CUDA stream
+ * capture begins.  All calls share the array: it keeps the previous call's contents (the call clears the two words
+ * that must start at zero), and two calls whose GPU work overlaps -- different contexts or streams, same device --
+ * race on it.  No cudaMalloc, cudaFree or other allocating routine is called. */
+int pmfs_run_fitch_static(pmfs_ctx* ctx, const uint8_t* d_msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
+                          int64_t n_cols, const uint8_t* d_consensus_code, const uint8_t* d_root_forced_code,
+                          pmfs_mut* d_out, int64_t out_capacity, int64_t* n_out);
+
 int pmfs_get_timing(pmfs_ctx* ctx, pmfs_timing* t);
 
 /* Plan introspection (tests, DESIGN.md numbers). */

@@ -73,7 +73,7 @@ class SynthSpec:
 _lib = None
 
 EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run",
-           "pmfs_result_free", "pmfs_run_device", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
+           "pmfs_result_free", "pmfs_run_device", "pmfs_run_fitch_static", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
 
@@ -98,6 +98,8 @@ def lib():
         L.pmfs_result_free.argtypes = [C.c_void_p, C.c_void_p]
         L.pmfs_result_free.restype = None
         L.pmfs_run_device.argtypes = L.pmfs_run.argtypes
+        L.pmfs_run_fitch_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
         L.pmfs_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.pmfs_get_timing.argtypes = [C.c_void_p, C.POINTER(_Timing)]
         L.pmfs_get_plan_info.argtypes = [C.c_void_p, C.POINTER(_PlanInfo)]
@@ -202,6 +204,19 @@ class Context:
         _check(self._L.pmfs_run_device(self._h, algo, d_msa, row_stride, n_rows, n_cols, d_cons, d_forced or None,
                                        C.byref(out), C.byref(n)))
         return out.value, n.value
+
+    def run_fitch_static(self, d_msa: int, row_stride: int, n_rows: int, n_cols: int, d_cons: int, d_forced: int,
+                         d_out: int, out_capacity: int) -> int:
+        """pmfs_run_fitch_static: the Fitch pass without any allocation (scratch in the library's static device array).
+        All arguments are device pointers / sizes; returns the number of records written to d_out."""
+        n = C.c_int64()
+        rc = self._L.pmfs_run_fitch_static(self._h, d_msa, row_stride, n_rows, n_cols, d_cons, d_forced or None, d_out,
+                                           out_capacity, C.byref(n))
+        if rc != 0:
+            err = PmfsError(rc, self._L.pmfs_last_error().decode())
+            err.n_out = n.value
+            raise err
+        return n.value
 
     def download(self, n: int) -> np.ndarray:
         res = np.zeros(n, MUT_DTYPE)

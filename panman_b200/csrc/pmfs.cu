@@ -987,3 +987,168 @@ int pmfs_synth_msa(pmfs_ctx* c, const pmfs_synth_spec* spec, int64_t col_begin, 
 }
 
 }  // extern "C"
+
+// =====================================================================================================================
+// Allocation-free Fitch run.
+//
+// Who this is for: code that must not allocate device memory at the moment it needs an answer -- a service loop
+// with a latency budget (cudaMalloc/cudaFree synchronise the whole device and can take milliseconds), a host that has
+// handed all of its HBM to another allocator and has nothing left to ask the driver for, or a region of the program in
+// which the CUDA allocator may simply not be called.  pmfs_run_device grows and reuses buffers on demand and may
+// therefore call cudaMalloc; this entry point never does.  Everything it needs beyond the caller's inputs and outputs
+// (the per-node set array the two walk kernels hand to each other, the per-chunk parent states, the bit-sliced
+// consensus, the unsorted record pairs and the radix sort's double buffers) is carved out of ONE array with static
+// storage duration in device memory.  The price: the array has a fixed size, it is resident on every GPU that loads
+// this library until the process exits, and all calls share it.
+// =====================================================================================================================
+namespace pmfs {
+
+constexpr size_t kStaticScratchBytes = (size_t)32 << 20;  // 32 MiB per GPU that loads the library
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: handing it to a kernel would
+// fault (or quietly touch host memory on systems where the GPU can reach it).  The real address differs per device and
+// is looked up once per device with cudaGetSymbolAddress, with that device current.
+constexpr int kMaxStaticDevices = 64;
+static std::mutex g_static_mu;
+static unsigned char* g_static_dev_ptr[kMaxStaticDevices] = {};
+
+static int static_scratch_on(int device, unsigned char** out) {
+    if (device < 0 || device >= kMaxStaticDevices) {
+        g_error = "pmfs_run_fitch_static: device index out of range";
+        return PMFS_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_dev_ptr[device]) {
+        PMFS_CUDA(cudaSetDevice(device));
+        void* ptr = nullptr;
+        PMFS_CUDA(cudaGetSymbolAddress(&ptr, g_static_scratch));
+        if (!ptr) {
+            g_error = "pmfs_run_fitch_static: cudaGetSymbolAddress returned a null address";
+            return PMFS_ERR_CUDA;
+        }
+        g_static_dev_ptr[device] = (unsigned char*)ptr;
+    }
+    *out = g_static_dev_ptr[device];
+    return PMFS_OK;
+}
+
+struct Carver {  // hands out 256-byte aligned pieces of the static array
+    unsigned char* base;
+    size_t used = 0;
+    template <class T>
+    T* take(size_t n) {
+        T* p = (T*)(base + used);
+        used += (n * sizeof(T) + 255) / 256 * 256;
+        return p;
+    }
+};
+
+}  // namespace pmfs
+
+extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                                     const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut* d_out, int64_t out_capacity,
+                                     int64_t* n_out) {
+    if (!c || !d_msa || !d_cons || !d_out || !n_out || n_cols <= 0 || out_capacity <= 0) {
+        g_error = "pmfs_run_fitch_static: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    if (row_stride % 16 != 0 || ((uintptr_t)d_msa & 15) != 0 || row_stride * 2 < n_cols) {
+        g_error = "pmfs_run_fitch_static: MSA rows must be 16-byte aligned with a stride that is a multiple of 16 and covers n_cols";
+        return PMFS_ERR_ARG;
+    }
+    if ((int64_t)c->plan.row_to_node.size() > (int64_t)n_rows) {
+        g_error = "pmfs_run_fitch_static: a leaf refers to an MSA row >= n_rows";
+        return PMFS_ERR_ARG;
+    }
+    *n_out = 0;
+    unsigned char* scratch = nullptr;
+    int rc = static_scratch_on(c->device, &scratch);  // first call on a device: resolves the array's address there
+    if (rc) return rc;
+    PMFS_CUDA(cudaSetDevice(c->device));
+
+    const Plan& P = c->plan;
+    const int64_t G = (n_cols + 31) / 32;
+    const size_t I = (size_t)P.n_internal, NC = P.chunks.size(), cap = (size_t)out_capacity;
+    int node_bits = 1;
+    while ((1ll << node_bits) < P.n_nodes) node_bits++;
+    size_t sort_tmp = 0;
+    if (out_capacity > 0x7fffffffll) {
+        g_error = "pmfs_run_fitch_static: out_capacity too large";
+        return PMFS_ERR_ARG;
+    }
+    {
+        cub::DoubleBuffer<unsigned long long> kb(nullptr, nullptr);
+        cub::DoubleBuffer<uint32_t> vb(nullptr, nullptr);
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, kb, vb, (int)cap, 0, 32 + node_bits, c->stream));
+    }
+    Carver cv{scratch};
+    uint4* S = cv.take<uint4>(I * 4 * (size_t)G);
+    uint4* xcode = cv.take<uint4>(NC * (size_t)G);
+    uint32_t* xvalid = cv.take<uint32_t>(NC * (size_t)G);
+    uint4* cons_planes = cv.take<uint4>((size_t)G);
+    uint4* forced_planes = cv.take<uint4>((size_t)G);
+    unsigned long long* count = cv.take<unsigned long long>(1);
+    unsigned int* err = cv.take<unsigned int>(1);
+    unsigned long long* keys = cv.take<unsigned long long>(cap);
+    unsigned long long* keys_alt = cv.take<unsigned long long>(cap);
+    uint32_t* vals = cv.take<uint32_t>(cap);
+    uint32_t* vals_alt = cv.take<uint32_t>(cap);
+    uint8_t* tmp = cv.take<uint8_t>(sort_tmp);
+    if (cv.used > kStaticScratchBytes) {
+        g_error = "pmfs_run_fitch_static: this problem needs " + std::to_string(cv.used) + " bytes of scratch (" +
+                  std::to_string(I) + " internal nodes x " + std::to_string(G) + " column groups x 64 B, plus 24 B per record "
+                  "of out_capacity); the static maximum is " + std::to_string(kStaticScratchBytes) +
+                  " bytes.  Use pmfs_run_device, which sizes its buffers to the problem.";
+        return PMFS_ERR_ARG;
+    }
+
+    // the array keeps whatever the previous call left in it: the record counter and the error flag must start at zero;
+    // every set / parent-state entry that is read is written earlier in the same call, so those need no clearing
+    PMFS_CUDA(cudaMemsetAsync(count, 0, sizeof(unsigned long long), c->stream));
+    PMFS_CUDA(cudaMemsetAsync(err, 0, sizeof(unsigned int), c->stream));
+
+    WalkParams wp = {};
+    wp.G = G;
+    wp.col_base = 0;
+    wp.tile_cols = n_cols;
+    wp.msa = (const uint4*)d_msa;
+    wp.msa_stride16 = row_stride / 16;
+    wp.S = S;
+    wp.D = nullptr;
+    wp.cons_planes = cons_planes;
+    wp.forced_planes = d_forced ? forced_planes : nullptr;
+    wp.xcode = xcode;
+    wp.xvalid = xvalid;
+    wp.int_to_node = c->d_int_to_node.ptr;
+    wp.row_to_node = c->d_row_to_node.ptr;
+    wp.out_keys = keys;
+    wp.out_vals = vals;
+    wp.out_count = count;
+    wp.out_cap = cap;
+    wp.err_flag = err;
+    const unsigned pg = (unsigned)((G + 127) / 128);
+    prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_cons, n_cols, G, cons_planes);
+    if (d_forced) prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_forced, n_cols, G, forced_planes);
+    int64_t launches = 0;
+    if ((rc = launch_levels<kAlgoFitch>(c, wp, true, &launches))) return rc;
+    if ((rc = launch_levels<kAlgoFitch>(c, wp, false, &launches))) return rc;
+    unsigned long long n = 0;
+    PMFS_CUDA(cudaMemcpyAsync(&n, count, sizeof(n), cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    *n_out = (int64_t)n;
+    if (n > cap) {
+        g_error = "pmfs_run_fitch_static: " + std::to_string(n) + " records do not fit in out_capacity " + std::to_string(cap);
+        return PMFS_ERR_ARG;
+    }
+    if (n > 0) {
+        cub::DoubleBuffer<unsigned long long> kb(keys, keys_alt);
+        cub::DoubleBuffer<uint32_t> vb(vals, vals_alt);
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(tmp, sort_tmp, kb, vb, (int)n, 0, 32 + node_bits, c->stream));
+        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), (int64_t)n, d_out);
+        PMFS_CUDA(cudaGetLastError());
+    }
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    return PMFS_OK;
+}
