@@ -102,6 +102,8 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--cpu-cols", type=int, default=0, help="columns of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chunk-nodes", type=int, default=0, help="plan tuning: nodes per chunk (0 = automatic)")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (tuning sweeps)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -128,6 +130,8 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     ctx = api.Context(tree, device=local_rank)
+    if args.chunk_nodes:
+        ctx.set_tuning(chunk_nodes=args.chunk_nodes)
     stride = ((N_COLS + 31) // 32) * 16
     d_msa = torch.zeros((N_TAXA, stride), dtype=torch.uint8, device=dev)
     d_cons = torch.zeros(N_COLS, dtype=torch.uint8, device=dev)
@@ -214,7 +218,7 @@ def main():
     ctx.set_stream(0)
     for _ in range(max(1, min(args.warmup, 2))):
         rec = ctx.run(algo, h_msa_np, N_COLS, h_cons_np, copy=False)
-    e2e_steps = max(1, min(args.steps, 10))
+    e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 10))
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
@@ -223,7 +227,7 @@ def main():
     e2e_s = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_val = updates_per_step * e2e_steps / float(e2e_s[0])
+    e2e_val = updates_per_step * e2e_steps / float(e2e_s[0]) if e2e_steps else None
     e2e_phases = ctx.timing()
     h2d = int(N_TAXA * stride + N_COLS)
     d2h = int(rec.shape[0] * 12)
@@ -250,7 +254,7 @@ def main():
                     "steps": e2e_steps, "phases_ms_last_step": {k: e2e_phases[k] for k in
                                                                 ("h2d_ms", "forward_ms", "backward_ms", "sort_ms", "d2h_ms")}},
             "gpu_launches": int(launches), "clocks": clocks,
-            "phases_ms_last_step": {k: tinfo[k] for k in ("forward_ms", "backward_ms", "sort_ms")},
+            "phases_ms_last_step": {k: tinfo[k] for k in ("forward_ms", "backward_ms", "sort_ms", "wall_ms")},
         }
         if world == 1 and not args.no_cpu_baseline:
             cols_n = args.cpu_cols or max(64, min(1024, 16 * ncpu))

@@ -74,6 +74,7 @@ typedef struct {
     int64_t n_launches;     /* kernels of this library launched by the call */
     int64_t forward_bytes;  /* design-level HBM bytes of the forward pass ("bytes per update") */
     int64_t backward_bytes; /* same for the backward pass, excluding emitted records */
+    float wall_ms;          /* host wall clock of the device-resident part of the call (launch + sync overheads included) */
 } pmfs_timing;
 
 const char* pmfs_last_error(void);

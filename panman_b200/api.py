@@ -44,7 +44,7 @@ class _Tree(C.Structure):
 class _Timing(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("forward_ms", C.c_float), ("backward_ms", C.c_float), ("sort_ms", C.c_float),
                 ("d2h_ms", C.c_float), ("total_ms", C.c_float), ("n_launches", C.c_int64), ("forward_bytes", C.c_int64),
-                ("backward_bytes", C.c_int64)]
+                ("backward_bytes", C.c_int64), ("wall_ms", C.c_float)]
 
 
 class _PlanInfo(C.Structure):

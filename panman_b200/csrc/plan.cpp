@@ -106,7 +106,11 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
     // owner[v]: chunk whose program visits v as a member (a chunk root is a member of its own chunk)
     std::vector<int32_t> owner(V, 0);
     for (int32_t v = 1; v < V; v++) owner[v] = cut[v] ? chunk_of_root[v] : owner[t.parent[v]];
-    for (int32_t c = 1; c < NC; c++) P.chunks[c].depth = P.chunks[owner[t.parent[P.chunks[c].root_node]]].depth + 1;
+    for (int32_t c = 1; c < NC; c++) {
+        P.chunks[c].parent = owner[t.parent[P.chunks[c].root_node]];
+        P.chunks[P.chunks[c].parent].n_child++;
+        P.chunks[c].depth = P.chunks[P.chunks[c].parent].depth + 1;
+    }
     for (int32_t c = NC - 1; c >= 1; c--) {
         Chunk& par = P.chunks[owner[t.parent[P.chunks[c].root_node]]];
         par.height = std::max(par.height, P.chunks[c].height + 1);

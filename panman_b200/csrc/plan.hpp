@@ -55,6 +55,8 @@ struct Chunk {
     int32_t fwd_len = 0, bwd_len = 0;
     int64_t fwd_stream_off = 0, bwd_stream_off = 0;
     int32_t fwd_stream_len = 0, bwd_stream_len = 0;
+    int32_t parent = -1;   // chunk that contains the parent of root_node; -1 for the chunk holding the tree root
+    int32_t n_child = 0;   // chunks rooted directly below this one
     int32_t height = 0;  // 0 = no child chunks
     int32_t depth = 0;   // 0 = contains the tree root
 };

@@ -1,8 +1,8 @@
 // libpmfs: CUDA kernels (sm_100a) + C ABI (include/pmfs.h).
 //
 // Kernels
-//   fwd_kernel<ALGO,POLY>   bottom-up walk of one chunk level: grid = chunks of the level x column tiles of kTPB groups
-//   bwd_kernel<ALGO>        top-down walk of one chunk level + mutation emission (warp-aggregated stream compaction)
+//   fwd_kernel<ALGO,POLY>   bottom-up walk, ONE launch: persistent CTAs claim (chunk, column tile) items in dependency order
+//   bwd_kernel<ALGO>        top-down walk + mutation emission (warp-cooperative stream compaction), same scheme
 //   prep_planes_kernel      consensus / forced-root codes -> bit-sliced code planes in the walk's bit order
 //   assemble_kernel         sorted (key,value) pairs -> pmfs_mut records
 //   synth_* kernels         synthetic alignments
@@ -14,6 +14,7 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -44,7 +45,12 @@ struct WalkParams {
     const uint32_t* prog;       // fwd or bwd program words
     const int64_t* chunk_off;   // [NC] offset of each chunk's program
     const int32_t* chunk_len;   // [NC]
-    const int32_t* order;       // chunk ids of this launch's level
+    const int32_t* order;       // chunk ids in execution order of this pass
+    const int32_t* chunk_parent;  // [NC] parent chunk, -1 for the chunk that holds the tree root
+    const int32_t* chunk_nchild;  // [NC] number of child chunks
+    int* ready;                 // [NC][ctas_per_chunk] dependency counters of this pass (zeroed before the launch)
+    int* next_item;             // work-item claim counter of this pass (zeroed before the launch)
+    int32_t n_items;
     const uint32_t* stream;     // load streams (plan.hpp)
     const int64_t* stream_off;  // [NC]
     const int32_t* stream_len;  // [NC]
@@ -68,6 +74,31 @@ struct WalkParams {
     unsigned long long* out_count;
     unsigned long long out_cap;
     unsigned int* err_flag;
+    int pos_bits;               // record key = node << pos_bits | column: only the bits that can be set get sorted
+};
+
+// 64-word sliding window over a word array that every lane of the warp reads at the same, never decreasing index
+// (walk programs, load streams): lane l holds words base+l and base+32+l in two registers, a read is one shuffle, and
+// the next 32 words are fetched (one coalesced load per warp) a whole window before they are needed -- so fetching
+// the "instruction stream" never puts a memory round trip on the walk's critical path.
+struct WarpWords {
+    const uint32_t* base;
+    int32_t len, wbase;
+    uint32_t cur, nxt;
+    __device__ __forceinline__ void init(const uint32_t* b, int32_t n, int lane) {
+        base = b; len = n; wbase = 0;
+        cur = lane < n ? __ldg(b + lane) : 0u;
+        nxt = 32 + lane < n ? __ldg(b + 32 + lane) : 0u;
+    }
+    __device__ __forceinline__ uint32_t get(int32_t i, int lane) {
+        while (i >= wbase + 32) {
+            cur = nxt;
+            wbase += 32;
+            const int32_t j = wbase + 32 + lane;
+            nxt = j < len ? __ldg(base + j) : 0u;
+        }
+        return __shfl_sync(0xffffffffu, cur, i - wbase);
+    }
 };
 
 constexpr int kRingFwd = 8;   // 16-byte ring slots per thread: loads run this far ahead of the bottom-up walk
@@ -88,24 +119,25 @@ struct DevEnv {
     uint32_t* bstk;   // [depth][5][kTPB]
     int sp = 0;
     int lane;
-    const uint32_t* strm;
+    WarpWords progw, strmw;
     int32_t slen;
     int32_t cons = 0;
 
     __device__ DevEnv(const WalkParams& p_, int64_t g_, int64_t g_unclamped, bool a, void* smem, int32_t chunk)
         : p(p_), g(g_), gwarp(g_unclamped - (threadIdx.x & 31)), active(a), ring((uint4*)smem), fstk((uint4*)smem + RING * kTPB),
-          bstk((uint32_t*)((uint4*)smem + RING * kTPB)), lane(threadIdx.x & 31),
-          strm(p_.stream + p_.stream_off[chunk]), slen(p_.stream_len[chunk]) {
+          bstk((uint32_t*)((uint4*)smem + RING * kTPB)), lane(threadIdx.x & 31), slen(p_.stream_len[chunk]) {
+        progw.init(p_.prog + p_.chunk_off[chunk], p_.chunk_len[chunk], lane);
+        strmw.init(p_.stream + p_.stream_off[chunk], slen, lane);
 #pragma unroll
         for (int j = 0; j < RING - 1; j++) issue(j);
     }
 
-    __device__ __forceinline__ uint32_t word(const uint32_t* prog, int32_t pc) const { return __ldg(prog + pc); }
+    __device__ __forceinline__ uint32_t word(const uint32_t*, int32_t pc) { return progw.get(pc, lane); }
 
     // stream entry j -> ring slot j % RING (always commits a group, empty past the end, so group counting stays uniform)
     __device__ __forceinline__ void issue(int32_t j) {
         if (j < slen) {
-            const uint32_t e = __ldg(strm + j);
+            const uint32_t e = strmw.get(j, lane);
             const uint4* src = (e & kStreamSet) ? p.S + (int64_t)(e & ~kStreamSet) * p.G + g
                                                 : p.msa + (int64_t)e * p.msa_stride16 + g;
             const uint32_t dst = (uint32_t)__cvta_generic_to_shared(ring + (j % RING) * kTPB + threadIdx.x);
@@ -215,7 +247,7 @@ struct DevEnv {
                 if (idx < p.out_cap) {
                     // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
                     const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
-                    p.out_keys[idx] = ((unsigned long long)node << 32) | (pos0 + (unsigned long long)src * 32);
+                    p.out_keys[idx] = ((unsigned long long)node << p.pos_bits) | (pos0 + (unsigned long long)src * 32);
                     p.out_vals[idx] = type | (cg << 8) | (cp << 16);
                 }
             }
@@ -239,51 +271,101 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
     return m;
 }
 
+// Work item = (chunk, column tile of kTPB groups).  One launch per pass: CTAs claim items from a global counter in plan
+// order (bottom-up: chunk height ascending; top-down: chunk depth ascending), so everything an item depends on has a
+// smaller index and was claimed earlier by a CTA that is already running -- waiting on it cannot deadlock, whatever the
+// number of resident CTAs.  Dependencies are per column tile (tile t of a chunk needs only tile t of its child chunks /
+// its parent chunk), tracked by one counter per (chunk, tile); there is no grid-wide barrier and no per-level launch,
+// so narrow levels near the root overlap with wide ones instead of leaving the GPU idle.
+__device__ __forceinline__ int claim_item(const WalkParams& p, int* s_item) {
+    if (threadIdx.x == 0) *s_item = atomicAdd(p.next_item, 1);
+    __syncthreads();
+    return *s_item;
+}
+__device__ __forceinline__ void wait_counter(const int* counter, int need) {
+    if (threadIdx.x == 0) {
+        const volatile int* f = counter;
+        while (*f < need) __nanosleep(64);
+        __threadfence();
+    }
+    __syncthreads();  // (also keeps the next claim from overwriting s_item before every thread has read it)
+}
+__device__ __forceinline__ void signal_counter(int* counter) {
+    __syncthreads();  // every thread of the CTA has issued its stores
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1);
+    }
+}
+
 template <int ALGO, bool POLY>
 __global__ void __launch_bounds__(kTPB) fwd_kernel(const WalkParams p) {
     extern __shared__ uint4 smem[];
-    const int32_t chunk = p.order[blockIdx.x / p.ctas_per_chunk];
-    const int64_t g0 = (int64_t)(blockIdx.x % p.ctas_per_chunk) * kTPB + threadIdx.x;
-    const bool active = g0 < p.G;
-    const int64_t g = active ? g0 : p.G - 1;
-    DevEnv<false, kRingFwd> env(p, g, g0, active, smem, chunk);
-    Code4 forced;
-    const Code4* fp = nullptr;
-    if (ALGO == kAlgoFitch && p.forced_planes) {
-        uint4 v = __ldg(p.forced_planes + g);
-        forced.b[0] = v.x; forced.b[1] = v.y; forced.b[2] = v.z; forced.b[3] = v.w;
-        fp = &forced;
+    __shared__ int s_item;
+    for (;;) {
+        const int item = claim_item(p, &s_item);
+        if (item >= p.n_items) return;
+        const int32_t chunk = p.order[item / p.ctas_per_chunk];
+        const int tile = item % p.ctas_per_chunk;
+        wait_counter(p.ready + (int64_t)chunk * p.ctas_per_chunk + tile, p.chunk_nchild[chunk]);
+        const int64_t g0 = (int64_t)tile * kTPB + threadIdx.x;
+        const bool active = g0 < p.G;
+        const int64_t g = active ? g0 : p.G - 1;
+        {
+            DevEnv<false, kRingFwd> env(p, g, g0, active, smem, chunk);
+            Code4 forced;
+            const Code4* fp = nullptr;
+            if (ALGO == kAlgoFitch && p.forced_planes) {
+                uint4 v = __ldg(p.forced_planes + g);
+                forced.b[0] = v.x; forced.b[1] = v.y; forced.b[2] = v.z; forced.b[3] = v.w;
+                fp = &forced;
+            }
+            forward_walk<ALGO, POLY>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], fp);
+        }
+        const int32_t parent = p.chunk_parent[chunk];
+        if (parent >= 0) signal_counter(p.ready + (int64_t)parent * p.ctas_per_chunk + tile);
     }
-    forward_walk<ALGO, POLY>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], fp);
 }
 
 template <int ALGO>
 __global__ void __launch_bounds__(kTPB) bwd_kernel(const WalkParams p) {
     extern __shared__ uint4 smem[];
-    const int32_t chunk = p.order[blockIdx.x / p.ctas_per_chunk];
-    const int64_t g0 = (int64_t)(blockIdx.x % p.ctas_per_chunk) * kTPB + threadIdx.x;
-    const bool active = g0 < p.G;
-    const int64_t g = active ? g0 : p.G - 1;
-    DevEnv<true, kRingBwd> env(p, g, g0, active, smem, chunk);
-    Code4 P, forced;
-    uint32_t pv = ~0u;
-    const Code4* fp = nullptr;
-    if (chunk == 0) {
-        uint4 v = __ldg(p.cons_planes + g);
-        P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
-        if (ALGO == kAlgoSankoff && p.forced_planes) {
-            uint4 f = __ldg(p.forced_planes + g);
-            forced.b[0] = f.x; forced.b[1] = f.y; forced.b[2] = f.z; forced.b[3] = f.w;
-            fp = &forced;
+    __shared__ int s_item;
+    for (;;) {
+        const int item = claim_item(p, &s_item);
+        if (item >= p.n_items) return;
+        const int32_t chunk = p.order[item / p.ctas_per_chunk];
+        const int tile = item % p.ctas_per_chunk;
+        const int32_t parent = p.chunk_parent[chunk];
+        wait_counter(p.ready + (int64_t)(parent < 0 ? chunk : parent) * p.ctas_per_chunk + tile, parent < 0 ? 0 : 1);
+        const int64_t g0 = (int64_t)tile * kTPB + threadIdx.x;
+        const bool active = g0 < p.G;
+        const int64_t g = active ? g0 : p.G - 1;
+        uint32_t err;
+        {
+            DevEnv<true, kRingBwd> env(p, g, g0, active, smem, chunk);
+            Code4 P, forced;
+            uint32_t pv = ~0u;
+            const Code4* fp = nullptr;
+            if (chunk == 0) {
+                uint4 v = __ldg(p.cons_planes + g);
+                P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
+                if (ALGO == kAlgoSankoff && p.forced_planes) {
+                    uint4 f = __ldg(p.forced_planes + g);
+                    forced.b[0] = f.x; forced.b[1] = f.y; forced.b[2] = f.z; forced.b[3] = f.w;
+                    fp = &forced;
+                }
+            } else {  // written by another SM during this launch: read through L2
+                uint4 v = __ldcg(p.xcode + (int64_t)chunk * p.G + g);
+                P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
+                pv = __ldcg(p.xvalid + (int64_t)chunk * p.G + g);
+            }
+            const uint32_t colmask = active ? real_column_mask(g, p.tile_cols) : 0u;
+            err = backward_walk<ALGO>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], P, pv, fp, colmask);
         }
-    } else {
-        uint4 v = p.xcode[(int64_t)chunk * p.G + g];
-        P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
-        pv = p.xvalid[(int64_t)chunk * p.G + g];
+        if (err) atomicOr(p.err_flag, 1u);
+        signal_counter(p.ready + (int64_t)chunk * p.ctas_per_chunk + tile);
     }
-    const uint32_t colmask = active ? real_column_mask(g, p.tile_cols) : 0u;
-    const uint32_t err = backward_walk<ALGO>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], P, pv, fp, colmask);
-    if (err) atomicOr(p.err_flag, 1u);
 }
 
 // codes[col_base .. col_base+tile_cols) -> planes[G] in the bit order of transpose_nibbles
@@ -301,14 +383,14 @@ __global__ void prep_planes_kernel(const uint8_t* __restrict__ codes, int64_t ti
 }
 
 __global__ void assemble_kernel(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
-                                pmfs_mut* __restrict__ out) {
+                                int pos_bits, pmfs_mut* __restrict__ out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     unsigned long long k = keys[i];
     uint32_t v = vals[i];
     pmfs_mut m;
-    m.node = (int32_t)(k >> 32);
-    m.pos = (int32_t)(k & 0xffffffffu);
+    m.node = (int32_t)(k >> pos_bits);
+    m.pos = (int32_t)(k & ((1ull << pos_bits) - 1));
     m.type = (uint8_t)(v & 0xff);
     m.code = (uint8_t)((v >> 8) & 0xff);
     m.parent_code = (uint8_t)((v >> 16) & 0xff);
@@ -442,7 +524,16 @@ struct pmfs_ctx {
     // plan on device
     DevBuf<uint32_t> d_fwd_prog, d_bwd_prog, d_fwd_stream, d_bwd_stream;
     DevBuf<int64_t> d_fwd_off, d_bwd_off, d_fwd_soff, d_bwd_soff;
-    DevBuf<int32_t> d_fwd_slen, d_bwd_slen;
+    DevBuf<int32_t> d_fwd_slen, d_bwd_slen, d_chunk_parent, d_chunk_nchild;
+    DevBuf<int> d_sync;
+    int n_sms = 0;
+    struct Occ {
+        const void* k;
+        size_t smem;
+        int per_sm;
+    };
+    std::vector<Occ> occ_cache;
+    float host_ms = 0;  // wall time of the last run_device_impl call
     DevBuf<int32_t> d_fwd_len, d_bwd_len, d_fwd_order, d_bwd_order, d_int_to_node, d_row_to_node;
     // per-run state
     DevBuf<uint4> d_S, d_D, d_cons_planes, d_forced_planes, d_xcode;
@@ -468,12 +559,13 @@ static int upload_plan(pmfs_ctx* c) {
     const Plan& P = c->plan;
     const size_t NC = P.chunks.size();
     std::vector<int64_t> foff(NC), boff(NC), fsoff(NC), bsoff(NC);
-    std::vector<int32_t> flen(NC), blen(NC), fslen(NC), bslen(NC);
+    std::vector<int32_t> flen(NC), blen(NC), fslen(NC), bslen(NC), cpar(NC), cnch(NC);
     for (size_t i = 0; i < NC; i++) {
         foff[i] = P.chunks[i].fwd_off; flen[i] = P.chunks[i].fwd_len;
         boff[i] = P.chunks[i].bwd_off; blen[i] = P.chunks[i].bwd_len;
         fsoff[i] = P.chunks[i].fwd_stream_off; fslen[i] = P.chunks[i].fwd_stream_len;
         bsoff[i] = P.chunks[i].bwd_stream_off; bslen[i] = P.chunks[i].bwd_stream_len;
+        cpar[i] = P.chunks[i].parent; cnch[i] = P.chunks[i].n_child;
     }
     auto up = [&](auto& buf, const auto& v) -> int {
         int rc = buf.ensure(v.size());
@@ -484,6 +576,8 @@ static int upload_plan(pmfs_ctx* c) {
     int rc;
     if ((rc = up(c->d_fwd_prog, P.fwd_prog))) return rc;
     if ((rc = up(c->d_bwd_prog, P.bwd_prog))) return rc;
+    if ((rc = up(c->d_chunk_parent, cpar))) return rc;
+    if ((rc = up(c->d_chunk_nchild, cnch))) return rc;
     if ((rc = up(c->d_fwd_stream, P.fwd_stream))) return rc;
     if ((rc = up(c->d_bwd_stream, P.bwd_stream))) return rc;
     if ((rc = up(c->d_fwd_soff, fsoff))) return rc;
@@ -589,7 +683,8 @@ void pmfs_destroy(pmfs_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     c->d_fwd_stream.release(); c->d_bwd_stream.release(); c->d_fwd_soff.release(); c->d_bwd_soff.release();
-    c->d_fwd_slen.release(); c->d_bwd_slen.release();
+    c->d_fwd_slen.release(); c->d_bwd_slen.release(); c->d_chunk_parent.release(); c->d_chunk_nchild.release();
+    c->d_sync.release();
     c->d_fwd_prog.release(); c->d_bwd_prog.release(); c->d_fwd_off.release(); c->d_bwd_off.release();
     c->d_fwd_len.release(); c->d_bwd_len.release(); c->d_fwd_order.release(); c->d_bwd_order.release();
     c->d_int_to_node.release(); c->d_row_to_node.release();
@@ -644,42 +739,61 @@ int pmfs_get_timing(pmfs_ctx* c, pmfs_timing* t) {
 }  // extern "C"
 
 // ---------------------------------------------------------------------------------------------------- the pipeline
+// ints of synchronisation scratch a pass needs for `groups` column groups: claim counters + per-(chunk,tile) counters
+static size_t sync_ints(const Plan& P, int64_t groups) {
+    return 64 + 2 * P.chunks.size() * (size_t)((groups + kTPB - 1) / kTPB);
+}
+
+// One launch per pass over all chunks (the name is historical: the first version launched once per chunk level).
+// wp.ready must point to sync_ints() ints of device memory.
 template <int ALGO>
 static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches) {
     const Plan& P = c->plan;
-    const std::vector<int32_t>& lvl = fwd ? P.fwd_lvl_off : P.bwd_lvl_off;
     wp.prog = fwd ? c->d_fwd_prog.ptr : c->d_bwd_prog.ptr;
     wp.chunk_off = fwd ? c->d_fwd_off.ptr : c->d_bwd_off.ptr;
     wp.chunk_len = fwd ? c->d_fwd_len.ptr : c->d_bwd_len.ptr;
     wp.stream = fwd ? c->d_fwd_stream.ptr : c->d_bwd_stream.ptr;
     wp.stream_off = fwd ? c->d_fwd_soff.ptr : c->d_bwd_soff.ptr;
     wp.stream_len = fwd ? c->d_fwd_slen.ptr : c->d_bwd_slen.ptr;
-    const int32_t* order = fwd ? c->d_fwd_order.ptr : c->d_bwd_order.ptr;
+    wp.order = fwd ? c->d_fwd_order.ptr : c->d_bwd_order.ptr;
+    wp.chunk_parent = c->d_chunk_parent.ptr;
+    wp.chunk_nchild = c->d_chunk_nchild.ptr;
     wp.ctas_per_chunk = (int32_t)((wp.G + kTPB - 1) / kTPB);
     wp.stack_depth = fwd ? P.fwd_stack_depth : P.bwd_stack_depth;
+    const int64_t n_items = (int64_t)P.chunks.size() * wp.ctas_per_chunk;
+    if (n_items > 0x7fffffffll) {
+        g_error = "too many (chunk, column tile) work items: use a smaller column tile";
+        return PMFS_ERR_ARG;
+    }
+    wp.n_items = (int32_t)n_items;
+    int* sync = wp.ready;
+    const size_t per_pass = (size_t)n_items;
+    wp.next_item = sync + (fwd ? 0 : 32);
+    wp.ready = sync + 64 + (fwd ? 0 : per_pass);
     const size_t smem = fwd ? ((size_t)kRingFwd + (size_t)P.fwd_stack_depth * 4) * kTPB * sizeof(uint4)
                             : (size_t)kRingBwd * kTPB * sizeof(uint4) + (size_t)P.bwd_stack_depth * 5 * kTPB * sizeof(uint32_t);
     if (smem > 200 * 1024) {
         g_error = "walk stack does not fit in shared memory (tree too unbalanced for this chunk size)";
         return PMFS_ERR_ARG;
     }
-    for (size_t l = 0; l + 1 < lvl.size(); l++) {
-        const int32_t nchunks = lvl[l + 1] - lvl[l];
-        if (nchunks == 0) continue;
-        wp.order = order + lvl[l];
-        const unsigned grid = (unsigned)((int64_t)nchunks * wp.ctas_per_chunk);
-        if (fwd) {
-            auto k = c->has_poly ? fwd_kernel<ALGO, true> : fwd_kernel<ALGO, false>;
-            if (smem > 48 * 1024) PMFS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k<<<grid, kTPB, smem, c->stream>>>(wp);
-        } else {
-            auto k = bwd_kernel<ALGO>;
-            if (smem > 48 * 1024) PMFS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k<<<grid, kTPB, smem, c->stream>>>(wp);
-        }
-        (*launches)++;
+    const void* k = fwd ? (c->has_poly ? (const void*)fwd_kernel<ALGO, true> : (const void*)fwd_kernel<ALGO, false>)
+                        : (const void*)bwd_kernel<ALGO>;
+    if (smem > 40 * 1024) PMFS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    for (auto& e : c->occ_cache)
+        if (e.k == k && e.smem == smem) per_sm = e.per_sm;
+    if (per_sm == 0) {
+        PMFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kTPB, smem));
+        if (per_sm < 1) per_sm = 1;
+        c->occ_cache.push_back({k, smem, per_sm});
     }
-    PMFS_CUDA(cudaGetLastError());
+    if (c->n_sms == 0) PMFS_CUDA(cudaDeviceGetAttribute(&c->n_sms, cudaDevAttrMultiProcessorCount, c->device));
+    const unsigned grid = (unsigned)std::min<int64_t>(n_items, (int64_t)c->n_sms * per_sm);
+    PMFS_CUDA(cudaMemsetAsync(wp.next_item, 0, sizeof(int), c->stream));
+    PMFS_CUDA(cudaMemsetAsync(wp.ready, 0, per_pass * sizeof(int), c->stream));
+    void* args[] = {&wp};
+    PMFS_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kTPB), args, smem, c->stream));
+    (*launches)++;
     return PMFS_OK;
 }
 
@@ -702,16 +816,21 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         return PMFS_ERR_ARG;
     }
     PMFS_CUDA(cudaSetDevice(c->device));
+    const auto host_t0 = std::chrono::steady_clock::now();
     const Plan* P = &c->plan;
     const int64_t G_all = (n_cols + 31) / 32;
     const int64_t I = P->n_internal;
 
     // column tile so that the set arrays fit in HBM
-    size_t free_b = 0, total_b = 0;
-    PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
-    free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);  // reusable
     const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64;
-    int64_t tile_groups = std::max<int64_t>(1, (int64_t)(free_b * 0.85) / per_group);
+    int64_t tile_groups = G_all;
+    const bool fits_already = c->d_S.cap >= (size_t)I * 4 * G_all && (algo != PMFS_SANKOFF || c->d_D.cap >= (size_t)I * 4 * G_all);
+    if (!fits_already) {  // (cudaMemGetInfo costs a fraction of a millisecond: only ask when buffers have to grow)
+        size_t free_b = 0, total_b = 0;
+        PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);  // reusable
+        tile_groups = std::max<int64_t>(1, (int64_t)(free_b * 0.85) / per_group);
+    }
     if (c->tune_tile_cols > 0) tile_groups = std::min<int64_t>(tile_groups, (c->tune_tile_cols + 31) / 32);
     tile_groups = std::min(tile_groups, G_all);
     if (tile_groups < G_all) tile_groups = std::max<int64_t>(kTPB, tile_groups / kTPB * kTPB);
@@ -724,6 +843,9 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         P = &c->plan;
     }
     const int64_t NC = (int64_t)P->chunks.size();
+    int pos_bits = 1, node_bits = 1;
+    while ((1ll << pos_bits) < n_cols) pos_bits++;
+    while ((1ll << node_bits) < P->n_nodes) node_bits++;
 
     int rc;
     if ((rc = c->d_S.ensure((size_t)I * 4 * tile_groups))) return rc;
@@ -734,6 +856,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     if ((rc = c->d_xvalid.ensure((size_t)NC * tile_groups))) return rc;
     if ((rc = c->d_count.ensure(1))) return rc;
     if ((rc = c->d_err.ensure(1))) return rc;
+    if ((rc = c->d_sync.ensure(sync_ints(*P, tile_groups)))) return rc;
     size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);
 
     pmfs_timing& tm = c->timing;
@@ -769,6 +892,8 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             wp.out_count = c->d_count.ptr;
             wp.out_cap = c->d_keys.cap;
             wp.err_flag = c->d_err.ptr;
+            wp.pos_bits = pos_bits;
+            wp.ready = c->d_sync.ptr;
             const unsigned pg = (unsigned)((wp.G + 127) / 128);
             PMFS_CUDA(cudaEventRecord(c->ev[0], c->stream));
             prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_cons + wp.col_base, wp.tile_cols, wp.G, c->d_cons_planes.ptr);
@@ -826,15 +951,13 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
         if ((rc = c->d_vals_alt.ensure(c->d_vals.cap))) return rc;
         if ((rc = c->d_out.ensure((size_t)n))) return rc;
-        int node_bits = 1;
-        while ((1ll << node_bits) < P->n_nodes) node_bits++;
         cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
         cub::DoubleBuffer<uint32_t> vb(c->d_vals.ptr, c->d_vals_alt.ptr);
         size_t tmp_bytes = 0;
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, (int)n, 0, 32 + node_bits, c->stream));
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
         if ((rc = c->d_sort_tmp.ensure(tmp_bytes))) return rc;
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(c->d_sort_tmp.ptr, tmp_bytes, kb, vb, (int)n, 0, 32 + node_bits, c->stream));
-        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), n, c->d_out.ptr);
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(c->d_sort_tmp.ptr, tmp_bytes, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
+        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), n, pos_bits, c->d_out.ptr);
         PMFS_CUDA(cudaGetLastError());
         tm.n_launches += 1;
     }
@@ -843,6 +966,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     cudaEventElapsedTime(&tm.sort_ms, c->ev[3], c->ev[4]);
     tm.total_ms = tm.h2d_ms + tm.forward_ms + tm.backward_ms + tm.sort_ms;
     c->last_n_out = n;
+    tm.wall_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
     *n_out = n;
     if (d_out) *d_out = c->d_out.ptr;
     return PMFS_OK;
@@ -1071,8 +1195,9 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     const Plan& P = c->plan;
     const int64_t G = (n_cols + 31) / 32;
     const size_t I = (size_t)P.n_internal, NC = P.chunks.size(), cap = (size_t)out_capacity;
-    int node_bits = 1;
+    int node_bits = 1, pos_bits = 1;
     while ((1ll << node_bits) < P.n_nodes) node_bits++;
+    while ((1ll << pos_bits) < n_cols) pos_bits++;
     size_t sort_tmp = 0;
     if (out_capacity > 0x7fffffffll) {
         g_error = "pmfs_run_fitch_static: out_capacity too large";
@@ -1081,7 +1206,7 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     {
         cub::DoubleBuffer<unsigned long long> kb(nullptr, nullptr);
         cub::DoubleBuffer<uint32_t> vb(nullptr, nullptr);
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, kb, vb, (int)cap, 0, 32 + node_bits, c->stream));
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, kb, vb, (int)cap, 0, pos_bits + node_bits, c->stream));
     }
     Carver cv{scratch};
     uint4* S = cv.take<uint4>(I * 4 * (size_t)G);
@@ -1096,6 +1221,7 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     uint32_t* vals = cv.take<uint32_t>(cap);
     uint32_t* vals_alt = cv.take<uint32_t>(cap);
     uint8_t* tmp = cv.take<uint8_t>(sort_tmp);
+    int* sync = cv.take<int>(sync_ints(P, G));
     if (cv.used > kStaticScratchBytes) {
         g_error = "pmfs_run_fitch_static: this problem needs " + std::to_string(cv.used) + " bytes of scratch (" +
                   std::to_string(I) + " internal nodes x " + std::to_string(G) + " column groups x 64 B, plus 24 B per record "
@@ -1128,6 +1254,8 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     wp.out_count = count;
     wp.out_cap = cap;
     wp.err_flag = err;
+    wp.pos_bits = pos_bits;
+    wp.ready = sync;  // claim and dependency counters: zeroed by launch_levels before each pass
     const unsigned pg = (unsigned)((G + 127) / 128);
     prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_cons, n_cols, G, cons_planes);
     if (d_forced) prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_forced, n_cols, G, forced_planes);
@@ -1145,8 +1273,8 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     if (n > 0) {
         cub::DoubleBuffer<unsigned long long> kb(keys, keys_alt);
         cub::DoubleBuffer<uint32_t> vb(vals, vals_alt);
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(tmp, sort_tmp, kb, vb, (int)n, 0, 32 + node_bits, c->stream));
-        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), (int64_t)n, d_out);
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(tmp, sort_tmp, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
+        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), (int64_t)n, pos_bits, d_out);
         PMFS_CUDA(cudaGetLastError());
     }
     PMFS_CUDA(cudaStreamSynchronize(c->stream));
