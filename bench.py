@@ -104,6 +104,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk-nodes", type=int, default=0, help="plan tuning: nodes per chunk (0 = automatic)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (tuning sweeps)")
+    ap.add_argument("--p-n-block", type=float, default=None, help="experiment: override the N-block rate of the synthetic MSA")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -136,7 +137,10 @@ def main():
     d_msa = torch.zeros((N_TAXA, stride), dtype=torch.uint8, device=dev)
     d_cons = torch.zeros(N_COLS, dtype=torch.uint8, device=dev)
     torch.cuda.synchronize()
-    ctx.synth_msa(api.SynthSpec(), rank * N_COLS, N_COLS, d_msa.data_ptr(), stride, d_cons.data_ptr())
+    spec = api.SynthSpec()
+    if args.p_n_block is not None:
+        spec.p_n_block = args.p_n_block
+    ctx.synth_msa(spec, rank * N_COLS, N_COLS, d_msa.data_ptr(), stride, d_cons.data_ptr())
 
     # ------------------------------------------------------------------ reference arm: the CPU path on the host cores
     if args.impl == "reference":

@@ -126,8 +126,7 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
         const uint32_t o = operand(c);
         P.fwd_prog.push_back(o);
         if (o & kOperandSet) {
-            if (o & kOperandExt)
-                for (uint32_t q = 0; q < 4; q++) P.fwd_stream.push_back(kStreamSet | ((o & kOperandIdMask) << 2) | q);
+            if (o & kOperandExt) P.fwd_stream.push_back(kStreamSet | (o & kOperandIdMask));
         } else if (o != kAbsentLeaf) {
             P.fwd_stream.push_back(o);
         }
@@ -143,6 +142,7 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
     std::vector<Frame> st;
     for (int32_t ci = 0; ci < NC; ci++) {
         Chunk& ch = P.chunks[ci];
+        while (P.fwd_prog.size() % 4) P.fwd_prog.push_back(0);  // 16-byte aligned: programs are staged by bulk copies
         ch.fwd_off = (int64_t)P.fwd_prog.size();
         ch.fwd_stream_off = (int64_t)P.fwd_stream.size();
         int32_t depth = 0;
@@ -210,6 +210,7 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
     // ---- backward (pre-order) programs
     for (int32_t ci = 0; ci < NC; ci++) {
         Chunk& ch = P.chunks[ci];
+        while (P.bwd_prog.size() % 4) P.bwd_prog.push_back(0);
         ch.bwd_off = (int64_t)P.bwd_prog.size();
         ch.bwd_stream_off = (int64_t)P.bwd_stream.size();
         int32_t depth = 0;
@@ -220,7 +221,7 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
             const int32_t v = f.v, b = t.child_off[v], e = t.child_off[v + 1];
             if (f.i < 0) {
                 P.bwd_prog.push_back(v == 0 ? op(B_ENTER_ROOT, 0) : op(B_ENTER, (uint32_t)P.int_id[v]));
-                for (uint32_t q = 0; q < 4; q++) P.bwd_stream.push_back(kStreamSet | ((uint32_t)P.int_id[v] << 2) | q);
+                P.bwd_stream.push_back(kStreamSet | (uint32_t)P.int_id[v]);
                 for (int32_t k = b; k < e; k++) {
                     int32_t c = t.child_idx[k];
                     if (P.int_id[c] < 0) {
@@ -258,6 +259,11 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
         }
         ch.bwd_len = (int32_t)((int64_t)P.bwd_prog.size() - ch.bwd_off);
         ch.bwd_stream_len = (int32_t)((int64_t)P.bwd_stream.size() - ch.bwd_stream_off);
+    }
+
+    for (int i = 0; i < 4; i++) {  // bulk copies round a program's length up to 16 bytes
+        P.fwd_prog.push_back(0);
+        P.bwd_prog.push_back(0);
     }
 
     // ---- level lists

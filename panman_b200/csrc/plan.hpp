@@ -26,9 +26,9 @@ constexpr uint32_t kOperandExt = 0x40000000u;  // with kOperandSet: the set was 
 constexpr uint32_t kOperandIdMask = 0x3fffffffu;
 constexpr uint32_t kAbsentLeaf = 0x3fffffffu;
 
-// ---- load streams: next to each walk program, the sequence of 16-byte global loads the program will consume, in
-// consumption order, so the kernels can run them ahead of the walk through a shared-memory ring (cp.async).
-// Entry: bit 31 set -> quarter `e & 3` of set row `(e & 0x7fffffff) >> 2`; else MSA row `e`.
+// ---- load streams: next to each walk program, the sequence of operands the program will fetch from global memory,
+// in consumption order, so that a producer warp can run them ahead of the walk through a shared-memory ring (TMA).
+// Entry: bit 31 set -> the whole set row `e & 0x7fffffff` (4 quarter copies); else MSA row `e` (1 copy).
 constexpr uint32_t kStreamSet = 0x80000000u;
 
 enum FwdOp : uint32_t {

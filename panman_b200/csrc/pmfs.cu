@@ -101,66 +101,166 @@ struct WarpWords {
     }
 };
 
-constexpr int kRingFwd = 8;   // 16-byte ring slots per thread: loads run this far ahead of the bottom-up walk
-constexpr int kRingBwd = 16;  // top-down walk: one internal node = 4 slots
+constexpr int kRingFwd = 8;   // ring units (one unit = one 16-byte load per thread = 2 KB per CTA) ahead of the bottom-up walk
+constexpr int kRingBwd = 8;   // top-down walk: a leaf takes 1 unit, an internal node's set 4
+constexpr int kThreads = kTPB + 32;  // 4 consumer warps walk the tree, 1 producer warp feeds them
+constexpr int kProgWords = 1024;     // walk programs up to this many words are staged in shared memory
 
-// Per-thread view of one (chunk, column group).  Global loads whose addresses are known from the plan (leaf rows, sets
-// written by earlier launches) do not go through registers: they are issued kRing entries ahead as 16-byte cp.async
-// copies into a shared-memory ring private to the thread, in the order of the chunk's load stream, so the walk itself
-// never waits for HBM latency as long as the ring stays ahead.
+// ---- mbarrier / bulk-copy (TMA) primitives, sm_90+ PTX ------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// A wait that can never be satisfied (a bug in the producer/consumer bookkeeping) must not hang the GPU: after about
+// ten seconds of spinning the kernel traps and the host sees a CUDA error.
+constexpr long long kSpinLimitCycles = 20000000000ll;  // ~10 s
+__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
+    const long long t0 = clock64();
+    while (!mbar_try(bar, parity))
+        if (clock64() - t0 > kSpinLimitCycles) __trap();
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity);
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// one contiguous global->shared copy by the TMA engine; completion is counted in bytes on `bar`
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
+// Shared-memory ring of one CTA, in UNITS of 2 KB (16 bytes for each of the kTPB column groups of the tile: one
+// contiguous segment of an MSA row or of a quarter-set row).  A load-stream entry takes 1 unit (leaf) or 4 consecutive
+// units modulo RING (the 4 quarters of a set).  full[u] flips when unit u's copy has landed, empty[u] when all 4
+// consumer warps have read it: every unit's two barriers complete exactly once per lap of the ring.  Unit numbers keep counting across the work items of a
+// persistent CTA, so barrier phases never need resetting.
+template <int RING>
+struct RingRefs {
+    uint32_t data, full, empty;  // shared-space addresses
+    uint32_t prog, prog_bar;     // staged walk program + its barrier
+};
+
+// Producer: lane 0 of the 5th warp stages the item's walk program, then walks the chunk's load stream and keeps the
+// ring full.  `unit` and `item_no` advance exactly as on the consumer side.
+template <int RING>
+__device__ __forceinline__ void produce_stream(const WalkParams& p, const RingRefs<RING>& r, int32_t chunk, int tile,
+                                               uint32_t& unit) {
+    const int lane = threadIdx.x & 31;
+    const int32_t plen = p.chunk_len[chunk];
+    if (lane == 0 && plen <= kProgWords) {
+        // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see upload_plan)
+        const uint32_t bytes = (uint32_t)((plen + 3) / 4) * 16u;
+        mbar_arrive_expect_tx(r.prog_bar, bytes);
+        bulk_g2s(r.prog, p.prog + p.chunk_off[chunk], bytes, r.prog_bar);
+    }
+    const int32_t slen = p.stream_len[chunk];
+    WarpWords w;
+    w.init(p.stream + p.stream_off[chunk], slen, lane);
+    const int64_t g0 = (int64_t)tile * kTPB;
+    const uint32_t bytes = (uint32_t)min((int64_t)kTPB, p.G - g0) * 16u;
+    for (int32_t j = 0; j < slen; j++) {
+        const uint32_t e = w.get(j, lane);
+        const uint32_t k = (e & kStreamSet) ? 4u : 1u;
+        if (lane == 0) {
+            const uint4* src = (e & kStreamSet) ? p.S + ((int64_t)(e & ~kStreamSet) * 4) * p.G + g0
+                                                : p.msa + (int64_t)e * p.msa_stride16 + g0;
+            for (uint32_t q = 0; q < k; q++) {
+                const uint32_t u = (unit + q) % RING, lap = (unit + q) / RING;
+                mbar_wait(r.empty + u * 8, (lap & 1u) ^ 1u);  // all consumers are done with the unit's previous content
+                mbar_arrive_expect_tx(r.full + u * 8, bytes);
+                bulk_g2s(r.data + u * (kTPB * 16), src + (int64_t)q * p.G, bytes, r.full + u * 8);
+            }
+        }
+        unit += k;
+    }
+}
+
+// Per-thread view of one (chunk, column group) for the 4 consumer warps.  Global loads whose addresses are known from
+// the plan (leaf rows, sets written by earlier work items) never go through the walking threads: the producer warp
+// streams them through the shared-memory ring with TMA bulk copies, so a walk reads its operands from shared memory
+// and only waits on an mbarrier that has normally completed long before.  The walk program itself is staged in shared
+// memory the same way.
 template <bool READONLY_SETS, int RING>
 struct DevEnv {
     const WalkParams& p;
     int64_t g;      // clamped column group
     int64_t gwarp;  // (unclamped) column group of this warp's lane 0
     bool active;
-    uint4* ring;      // [RING][kTPB]
+    RingRefs<RING> ring;
+    uint32_t& unit;   // running ring-unit number of this CTA (same sequence as the producer's)
     uint4* fstk;      // [depth][4][kTPB]
     uint32_t* bstk;   // [depth][5][kTPB]
     int sp = 0;
     int lane;
-    WarpWords progw, strmw;
-    int32_t slen;
-    int32_t cons = 0;
+    bool prog_staged;
+    const uint32_t* gprog;
 
-    __device__ DevEnv(const WalkParams& p_, int64_t g_, int64_t g_unclamped, bool a, void* smem, int32_t chunk)
-        : p(p_), g(g_), gwarp(g_unclamped - (threadIdx.x & 31)), active(a), ring((uint4*)smem), fstk((uint4*)smem + RING * kTPB),
-          bstk((uint32_t*)((uint4*)smem + RING * kTPB)), lane(threadIdx.x & 31), slen(p_.stream_len[chunk]) {
-        progw.init(p_.prog + p_.chunk_off[chunk], p_.chunk_len[chunk], lane);
-        strmw.init(p_.stream + p_.stream_off[chunk], slen, lane);
-#pragma unroll
-        for (int j = 0; j < RING - 1; j++) issue(j);
+    __device__ DevEnv(const WalkParams& p_, int64_t g_, int64_t g_unclamped, bool a, const RingRefs<RING>& r, uint32_t& unit_,
+                      void* stack, int32_t chunk, uint32_t item_no)
+        : p(p_), g(g_), gwarp(g_unclamped - (threadIdx.x & 31)), active(a), ring(r), unit(unit_), fstk((uint4*)stack),
+          bstk((uint32_t*)stack), lane(threadIdx.x & 31), prog_staged(p_.chunk_len[chunk] <= kProgWords),
+          gprog(p_.prog + p_.chunk_off[chunk]) {
+        if (prog_staged) mbar_wait(ring.prog_bar, item_no & 1u);
     }
 
-    __device__ __forceinline__ uint32_t word(const uint32_t*, int32_t pc) { return progw.get(pc, lane); }
-
-    // stream entry j -> ring slot j % RING (always commits a group, empty past the end, so group counting stays uniform)
-    __device__ __forceinline__ void issue(int32_t j) {
-        if (j < slen) {
-            const uint32_t e = strmw.get(j, lane);
-            const uint4* src = (e & kStreamSet) ? p.S + (int64_t)(e & ~kStreamSet) * p.G + g
-                                                : p.msa + (int64_t)e * p.msa_stride16 + g;
-            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(ring + (j % RING) * kTPB + threadIdx.x);
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+    __device__ __forceinline__ uint32_t word(const uint32_t*, int32_t pc) const {
+        if (prog_staged) {
+            uint32_t w;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(ring.prog + pc * 4));
+            return w;
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+        return __ldg(gprog + pc);  // very long programs (huge polytomies): straight from L1/L2
     }
-    // next ring entry: wait until it has landed, read it, then refill the slot freed by the PREVIOUS call
-    __device__ __forceinline__ uint4 next() {
-        asm volatile("cp.async.wait_group %0;" ::"n"(RING - 2) : "memory");
-        const uint32_t src = (uint32_t)__cvta_generic_to_shared(ring + (cons % RING) * kTPB + threadIdx.x);
-        uint4 v;
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(src) : "memory");
-        issue(cons + RING - 1);
-        cons++;
-        return v;
+
+    // next ring entry of k units: wait until the TMA copies have landed, read this thread's 16 bytes of each unit,
+    // hand the units back
+    template <int K>
+    __device__ __forceinline__ void next(uint4 (&v)[K]) {
+#pragma unroll
+        for (int q = 0; q < K; q++) {
+            const uint32_t u = (unit + q) % RING;
+            mbar_wait(ring.full + u * 8, ((unit + q) / RING) & 1u);
+            v[q] = lds128(ring.data + u * (kTPB * 16) + threadIdx.x * 16);
+        }
+        __syncwarp();
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 0; q < K; q++) mbar_arrive(ring.empty + ((unit + q) % RING) * 8);
+        }
+        unit += K;
     }
-    __device__ __forceinline__ uint4 leaf(uint32_t) { return next(); }
+    __device__ __forceinline__ uint4 leaf(uint32_t) {
+        uint4 v[1];
+        next<1>(v);
+        return v[0];
+    }
     __device__ __forceinline__ void load_x(uint32_t, Planes16& s) {
+        uint4 v[4];
+        next<4>(v);
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            uint4 v = next();
-            s.p[4 * i] = v.x; s.p[4 * i + 1] = v.y; s.p[4 * i + 2] = v.z; s.p[4 * i + 3] = v.w;
+            s.p[4 * i] = v[i].x; s.p[4 * i + 1] = v[i].y; s.p[4 * i + 2] = v[i].z; s.p[4 * i + 3] = v[i].w;
         }
     }
 
@@ -285,7 +385,13 @@ __device__ __forceinline__ int claim_item(const WalkParams& p, int* s_item) {
 __device__ __forceinline__ void wait_counter(const int* counter, int need) {
     if (threadIdx.x == 0) {
         const volatile int* f = counter;
-        while (*f < need) __nanosleep(64);
+        if (*f < need) {
+            const long long t0 = clock64();
+            while (*f < need) {
+                __nanosleep(64);
+                if (clock64() - t0 > kSpinLimitCycles) __trap();
+            }
+        }
         __threadfence();
     }
     __syncthreads();  // (also keeps the next claim from overwriting s_item before every thread has read it)
@@ -298,21 +404,48 @@ __device__ __forceinline__ void signal_counter(int* counter) {
     }
 }
 
+template <int RING>
+__device__ __forceinline__ RingRefs<RING> ring_setup(void* smem, unsigned long long* bars) {
+    RingRefs<RING> r;  // dynamic smem: [program kProgWords words][ring RING x 2 KB][walk stack]
+    r.prog = (uint32_t)__cvta_generic_to_shared(smem);
+    r.data = r.prog + kProgWords * 4;
+    r.full = (uint32_t)__cvta_generic_to_shared(bars);
+    r.empty = r.full + RING * 8;
+    r.prog_bar = r.empty + RING * 8;
+    if (threadIdx.x == 0) {
+        mbar_init(r.prog_bar, 1);
+        for (int i = 0; i < RING; i++) {
+            mbar_init(r.full + i * 8, 1);          // one arrive.expect_tx by the producer
+            mbar_init(r.empty + i * 8, kTPB / 32);  // one arrive per consumer warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    return r;
+}
+
 template <int ALGO, bool POLY>
-__global__ void __launch_bounds__(kTPB) fwd_kernel(const WalkParams p) {
+__global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
     extern __shared__ uint4 smem[];
     __shared__ int s_item;
+    __shared__ __align__(8) unsigned long long bars[2 * kRingFwd + 1];
+    const RingRefs<kRingFwd> ring = ring_setup<kRingFwd>(smem, bars);
+    const bool producer = threadIdx.x >= kTPB;
+    uint32_t entry = 0, staged = 0;  // ring units / staged programs so far: advance identically in producer and consumers
     for (;;) {
         const int item = claim_item(p, &s_item);
         if (item >= p.n_items) return;
         const int32_t chunk = p.order[item / p.ctas_per_chunk];
         const int tile = item % p.ctas_per_chunk;
         wait_counter(p.ready + (int64_t)chunk * p.ctas_per_chunk + tile, p.chunk_nchild[chunk]);
-        const int64_t g0 = (int64_t)tile * kTPB + threadIdx.x;
-        const bool active = g0 < p.G;
-        const int64_t g = active ? g0 : p.G - 1;
-        {
-            DevEnv<false, kRingFwd> env(p, g, g0, active, smem, chunk);
+        if (producer) {
+            asm volatile("fence.proxy.async;" ::: "memory");  // sets written by other CTAs are read by the TMA engine
+            produce_stream<kRingFwd>(p, ring, chunk, tile, entry);
+        } else {
+            const int64_t g0 = (int64_t)tile * kTPB + threadIdx.x;
+            const bool active = g0 < p.G;
+            const int64_t g = active ? g0 : p.G - 1;
+            DevEnv<false, kRingFwd> env(p, g, g0, active, ring, entry, smem + kProgWords / 4 + kRingFwd * kTPB, chunk, staged);
             Code4 forced;
             const Code4* fp = nullptr;
             if (ALGO == kAlgoFitch && p.forced_planes) {
@@ -322,15 +455,20 @@ __global__ void __launch_bounds__(kTPB) fwd_kernel(const WalkParams p) {
             }
             forward_walk<ALGO, POLY>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], fp);
         }
+        if (p.chunk_len[chunk] <= kProgWords) staged++;
         const int32_t parent = p.chunk_parent[chunk];
         if (parent >= 0) signal_counter(p.ready + (int64_t)parent * p.ctas_per_chunk + tile);
     }
 }
 
 template <int ALGO>
-__global__ void __launch_bounds__(kTPB) bwd_kernel(const WalkParams p) {
+__global__ void __launch_bounds__(kThreads) bwd_kernel(const WalkParams p) {
     extern __shared__ uint4 smem[];
     __shared__ int s_item;
+    __shared__ __align__(8) unsigned long long bars[2 * kRingBwd + 1];
+    const RingRefs<kRingBwd> ring = ring_setup<kRingBwd>(smem, bars);
+    const bool producer = threadIdx.x >= kTPB;
+    uint32_t entry = 0, staged = 0;  // ring units / staged programs so far: advance identically in producer and consumers
     for (;;) {
         const int item = claim_item(p, &s_item);
         if (item >= p.n_items) return;
@@ -338,12 +476,14 @@ __global__ void __launch_bounds__(kTPB) bwd_kernel(const WalkParams p) {
         const int tile = item % p.ctas_per_chunk;
         const int32_t parent = p.chunk_parent[chunk];
         wait_counter(p.ready + (int64_t)(parent < 0 ? chunk : parent) * p.ctas_per_chunk + tile, parent < 0 ? 0 : 1);
-        const int64_t g0 = (int64_t)tile * kTPB + threadIdx.x;
-        const bool active = g0 < p.G;
-        const int64_t g = active ? g0 : p.G - 1;
-        uint32_t err;
-        {
-            DevEnv<true, kRingBwd> env(p, g, g0, active, smem, chunk);
+        uint32_t err = 0;
+        if (producer) {
+            produce_stream<kRingBwd>(p, ring, chunk, tile, entry);
+        } else {
+            const int64_t g0 = (int64_t)tile * kTPB + threadIdx.x;
+            const bool active = g0 < p.G;
+            const int64_t g = active ? g0 : p.G - 1;
+            DevEnv<true, kRingBwd> env(p, g, g0, active, ring, entry, smem + kProgWords / 4 + kRingBwd * kTPB, chunk, staged);
             Code4 P, forced;
             uint32_t pv = ~0u;
             const Code4* fp = nullptr;
@@ -364,6 +504,7 @@ __global__ void __launch_bounds__(kTPB) bwd_kernel(const WalkParams p) {
             err = backward_walk<ALGO>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], P, pv, fp, colmask);
         }
         if (err) atomicOr(p.err_flag, 1u);
+        if (p.chunk_len[chunk] <= kProgWords) staged++;
         signal_counter(p.ready + (int64_t)chunk * p.ctas_per_chunk + tile);
     }
 }
@@ -614,12 +755,14 @@ static int replan(pmfs_ctx* c, int32_t chunk_nodes) {
     return upload_plan(c);
 }
 
-// chunk size such that one chunk level offers a few waves of CTAs (148 SMs) for `groups` column groups
+// Chunk size.  The passes are bound by the longest chain of dependent (chunk, tile) items more than by raw throughput,
+// so chunks are kept small (short items, short chains) as long as every item still amortises its fixed cost (claim,
+// dependency check, program staging: a few microseconds) -- measured optimum on BASELINE config 2: 24..64 nodes.
 static int32_t auto_chunk_nodes(int32_t n_nodes, int64_t groups) {
     int64_t ctas_per_chunk = (groups + kTPB - 1) / kTPB;
-    int64_t want_chunks = std::max<int64_t>(1, (148 * 8 + ctas_per_chunk - 1) / ctas_per_chunk);
+    int64_t want_chunks = std::max<int64_t>(1, (148 * 24 + ctas_per_chunk - 1) / ctas_per_chunk);
     int64_t cn = n_nodes / (want_chunks * 2);  // chunks end up between cn and 2*cn nodes
-    return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 64), 1 << 16);
+    return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 24), 1 << 16);
 }
 
 extern "C" {
@@ -770,8 +913,9 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     const size_t per_pass = (size_t)n_items;
     wp.next_item = sync + (fwd ? 0 : 32);
     wp.ready = sync + 64 + (fwd ? 0 : per_pass);
-    const size_t smem = fwd ? ((size_t)kRingFwd + (size_t)P.fwd_stack_depth * 4) * kTPB * sizeof(uint4)
-                            : (size_t)kRingBwd * kTPB * sizeof(uint4) + (size_t)P.bwd_stack_depth * 5 * kTPB * sizeof(uint32_t);
+    const size_t smem = (size_t)kProgWords * 4 +
+                        (fwd ? ((size_t)kRingFwd + (size_t)P.fwd_stack_depth * 4) * kTPB * sizeof(uint4)
+                             : (size_t)kRingBwd * kTPB * sizeof(uint4) + (size_t)P.bwd_stack_depth * 5 * kTPB * sizeof(uint32_t));
     if (smem > 200 * 1024) {
         g_error = "walk stack does not fit in shared memory (tree too unbalanced for this chunk size)";
         return PMFS_ERR_ARG;
@@ -783,7 +927,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     for (auto& e : c->occ_cache)
         if (e.k == k && e.smem == smem) per_sm = e.per_sm;
     if (per_sm == 0) {
-        PMFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kTPB, smem));
+        PMFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kThreads, smem));
         if (per_sm < 1) per_sm = 1;
         c->occ_cache.push_back({k, smem, per_sm});
     }
@@ -792,7 +936,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     PMFS_CUDA(cudaMemsetAsync(wp.next_item, 0, sizeof(int), c->stream));
     PMFS_CUDA(cudaMemsetAsync(wp.ready, 0, per_pass * sizeof(int), c->stream));
     void* args[] = {&wp};
-    PMFS_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kTPB), args, smem, c->stream));
+    PMFS_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kThreads), args, smem, c->stream));
     (*launches)++;
     return PMFS_OK;
 }

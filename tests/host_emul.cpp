@@ -39,7 +39,7 @@ struct HostEnv {
         consumed++;
     }
     void load_x(uint32_t id, Planes16& s) {
-        for (uint32_t q = 0; q < 4; q++) expect(kStreamSet | (id << 2) | q);
+        expect(kStreamSet | id);
         load(S, id, s);
     }
     uint32_t word(const uint32_t* prog, int32_t pc) const { return prog[pc]; }
