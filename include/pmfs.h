@@ -116,7 +116,19 @@ void pmfs_result_free(pmfs_ctx* ctx, pmfs_mut* out);
 int pmfs_run_device(pmfs_ctx* ctx, int algo, const uint8_t* d_msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
                     int64_t n_cols, const uint8_t* d_consensus_code, const uint8_t* d_root_forced_code,
                     pmfs_mut** d_out, int64_t* n_out);
-/* Copies device records of the last pmfs_run_device to a caller buffer of at least n_out records. */
+/* ---- column shards across GPUs (one context per GPU; no counterpart in the reference, which is single-process) ------
+ * pmfs_set_shard puts a context in shard mode: its columns are [pos_offset, pos_offset+n_cols) of a total_cols-wide
+ * alignment, and node ids [node_bounds[r], node_bounds[r+1]) are owned by rank r (n_parts <= 16; n_parts = 0 leaves
+ * shard mode).  In shard mode pmfs_run_device emits global positions, does NOT order the records and returns
+ * *d_out = NULL; instead the (key, value) pairs are grouped by owning rank: pmfs_get_parts gives the device arrays
+ * (u64 keys, u32 values; owner r's pairs are the counts[r] pairs after those of owners < r) for an all-to-all, and the
+ * owner orders everything it received with pmfs_sort_records (d_keys/d_vals are overwritten; result valid until the
+ * next run), which yields its nodes' complete (node,pos)-sorted lists. */
+int pmfs_set_shard(pmfs_ctx* ctx, int64_t pos_offset, int64_t total_cols, int32_t n_parts, const int32_t* node_bounds);
+int pmfs_get_parts(pmfs_ctx* ctx, const void** d_keys, const void** d_vals, int64_t* counts);
+int pmfs_sort_records(pmfs_ctx* ctx, void* d_keys, void* d_vals, int64_t n, pmfs_mut** d_out);
+
+/* Copies device records of the last pmfs_run_device / pmfs_sort_records to a caller buffer of at least n records. */
 int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);
 
 /* Fitch pass that allocates nothing.  This entry point has no counterpart in the reference.

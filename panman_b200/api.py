@@ -73,7 +73,7 @@ class SynthSpec:
 _lib = None
 
 EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run",
-           "pmfs_result_free", "pmfs_run_device", "pmfs_run_fitch_static", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
+           "pmfs_result_free", "pmfs_run_device", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
 
@@ -100,6 +100,9 @@ def lib():
         L.pmfs_run_device.argtypes = L.pmfs_run.argtypes
         L.pmfs_run_fitch_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
+        L.pmfs_set_shard.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
+        L.pmfs_get_parts.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_void_p]
+        L.pmfs_sort_records.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
         L.pmfs_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.pmfs_get_timing.argtypes = [C.c_void_p, C.POINTER(_Timing)]
         L.pmfs_get_plan_info.argtypes = [C.c_void_p, C.POINTER(_PlanInfo)]
@@ -217,6 +220,28 @@ class Context:
             err.n_out = n.value
             raise err
         return n.value
+
+    def set_shard(self, pos_offset: int, total_cols: int, node_bounds=None):
+        """Column-shard mode (pmfs_set_shard); node_bounds: [n_parts+1] node-id boundaries, None leaves shard mode."""
+        if node_bounds is None:
+            _check(self._L.pmfs_set_shard(self._h, 0, 0, 0, None))
+            return
+        b = np.ascontiguousarray(node_bounds, dtype=np.int32)
+        _check(self._L.pmfs_set_shard(self._h, pos_offset, total_cols, b.shape[0] - 1, b.ctypes.data))
+        self._n_parts = b.shape[0] - 1
+
+    def get_parts(self):
+        """-> (d_keys ptr, d_vals ptr, counts list) of the last shard-mode run (records grouped by owning rank)."""
+        k, v = C.c_void_p(), C.c_void_p()
+        counts = np.zeros(16, np.int64)
+        _check(self._L.pmfs_get_parts(self._h, C.byref(k), C.byref(v), counts.ctypes.data))
+        return k.value or 0, v.value or 0, counts[: self._n_parts].tolist()
+
+    def sort_records(self, d_keys: int, d_vals: int, n: int) -> int:
+        """Order `n` received (key, value) pairs by (node, pos) -> device pointer to pmfs_mut records."""
+        out = C.c_void_p()
+        _check(self._L.pmfs_sort_records(self._h, d_keys or None, d_vals or None, n, C.byref(out)))
+        return out.value or 0
 
     def download(self, n: int) -> np.ndarray:
         res = np.zeros(n, MUT_DTYPE)

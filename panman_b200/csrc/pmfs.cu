@@ -74,6 +74,7 @@ struct WalkParams {
     unsigned long long* out_count;
     unsigned long long out_cap;
     unsigned int* err_flag;
+    int64_t pos_offset;         // global column of this context's first column (column shards); 0 otherwise
     int pos_bits;               // record key = node << pos_bits | column: only the bits that can be set get sorted
 };
 
@@ -331,7 +332,7 @@ struct DevEnv {
         if (lane == 0) base = atomicAdd(p.out_count, (unsigned long long)total);
         base = __shfl_sync(full, base, 0);
         uint32_t srcs = __ballot_sync(full, m != 0);
-        const unsigned long long pos0 = (unsigned long long)(p.col_base + gwarp * 32 + column_of_bit(lane));
+        const unsigned long long pos0 = (unsigned long long)(p.pos_offset + p.col_base + gwarp * 32 + column_of_bit(lane));
         while (srcs) {
             const int src = __ffs(srcs) - 1;
             srcs &= srcs - 1;
@@ -530,13 +531,37 @@ __global__ void assemble_kernel(const unsigned long long* __restrict__ keys, con
     unsigned long long k = keys[i];
     uint32_t v = vals[i];
     pmfs_mut m;
-    m.node = (int32_t)(k >> pos_bits);
+    m.node = (int32_t)((k & 0x0fffffffffffffffull) >> pos_bits);  // bits 60..63 may carry a shard owner tag
     m.pos = (int32_t)(k & ((1ull << pos_bits) - 1));
     m.type = (uint8_t)(v & 0xff);
     m.code = (uint8_t)((v >> 8) & 0xff);
     m.parent_code = (uint8_t)((v >> 16) & 0xff);
     m.pad = 0;
     out[i] = m;
+}
+
+// Column shards: tag every record with the rank that owns its node (bits 60..63 of the key) and count records per
+// owner; one radix pass on those 4 bits then makes each owner's records contiguous for the all-to-all.
+struct PartBounds {
+    int32_t n_parts;
+    int32_t bound[17];  // nodes [bound[r], bound[r+1]) belong to part r
+};
+__global__ void tag_parts_kernel(unsigned long long* __restrict__ keys, int64_t n, int pos_bits, const PartBounds pb,
+                                 unsigned long long* __restrict__ hist) {
+    __shared__ unsigned int sh[16];
+    if (threadIdx.x < 16) sh[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const unsigned long long k = keys[i];
+        const int32_t node = (int32_t)(k >> pos_bits);
+        int part = 0;
+        for (int r = 1; r < pb.n_parts; r++) part += node >= pb.bound[r];
+        keys[i] = k | ((unsigned long long)part << 60);
+        atomicAdd(&sh[part], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < pb.n_parts && sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
 }
 
 // ------------------------------------------------------------------------------------------------ synthetic alignments
@@ -675,6 +700,15 @@ struct pmfs_ctx {
     };
     std::vector<Occ> occ_cache;
     float host_ms = 0;  // wall time of the last run_device_impl call
+    // column-shard mode (pmfs_set_shard)
+    int64_t shard_pos_offset = 0, shard_total_cols = 0;
+    PartBounds parts = {};
+    int64_t part_counts[16] = {};
+    unsigned long long* parts_keys = nullptr;
+    uint32_t* parts_vals = nullptr;
+    DevBuf<unsigned long long> d_hist, d_rkeys_alt;
+    DevBuf<uint32_t> d_rvals_alt;
+    DevBuf<uint8_t> d_sort_tmp2;
     DevBuf<int32_t> d_fwd_len, d_bwd_len, d_fwd_order, d_bwd_order, d_int_to_node, d_row_to_node;
     // per-run state
     DevBuf<uint4> d_S, d_D, d_cons_planes, d_forced_planes, d_xcode;
@@ -827,7 +861,7 @@ void pmfs_destroy(pmfs_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->d_fwd_stream.release(); c->d_bwd_stream.release(); c->d_fwd_soff.release(); c->d_bwd_soff.release();
     c->d_fwd_slen.release(); c->d_bwd_slen.release(); c->d_chunk_parent.release(); c->d_chunk_nchild.release();
-    c->d_sync.release();
+    c->d_sync.release(); c->d_hist.release(); c->d_rkeys_alt.release(); c->d_rvals_alt.release(); c->d_sort_tmp2.release();
     c->d_fwd_prog.release(); c->d_bwd_prog.release(); c->d_fwd_off.release(); c->d_bwd_off.release();
     c->d_fwd_len.release(); c->d_bwd_len.release(); c->d_fwd_order.release(); c->d_bwd_order.release();
     c->d_int_to_node.release(); c->d_row_to_node.release();
@@ -988,8 +1022,17 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     }
     const int64_t NC = (int64_t)P->chunks.size();
     int pos_bits = 1, node_bits = 1;
-    while ((1ll << pos_bits) < n_cols) pos_bits++;
+    const int64_t pos_span = c->parts.n_parts > 0 ? c->shard_total_cols : n_cols;
+    if (c->parts.n_parts > 0 && c->shard_pos_offset + n_cols > c->shard_total_cols) {
+        g_error = "pmfs_run: column shard exceeds the total column count given to pmfs_set_shard";
+        return PMFS_ERR_ARG;
+    }
+    while ((1ll << pos_bits) < pos_span) pos_bits++;
     while ((1ll << node_bits) < P->n_nodes) node_bits++;
+    if (pos_bits + node_bits > 60) {
+        g_error = "pmfs_run: node and column counts need more than 60 key bits";
+        return PMFS_ERR_ARG;
+    }
 
     int rc;
     if ((rc = c->d_S.ensure((size_t)I * 4 * tile_groups))) return rc;
@@ -1037,6 +1080,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             wp.out_cap = c->d_keys.cap;
             wp.err_flag = c->d_err.ptr;
             wp.pos_bits = pos_bits;
+            wp.pos_offset = c->parts.n_parts > 0 ? c->shard_pos_offset : 0;
             wp.ready = c->d_sync.ptr;
             const unsigned pg = (unsigned)((wp.G + 127) / 128);
             PMFS_CUDA(cudaEventRecord(c->ev[0], c->stream));
@@ -1091,6 +1135,38 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     // order by (node,pos): radix sort on the key bits that can be non-zero
     const int64_t n = (int64_t)count;
     PMFS_CUDA(cudaEventRecord(c->ev[3], c->stream));
+    if (c->parts.n_parts > 0) {
+        // shard mode: no local ordering -- group the records by owning rank (one radix pass on 4 tag bits); the owner
+        // orders what it receives (pmfs_sort_records)
+        if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
+        if ((rc = c->d_vals_alt.ensure(c->d_vals.cap))) return rc;
+        if ((rc = c->d_hist.ensure(16))) return rc;
+        PMFS_CUDA(cudaMemsetAsync(c->d_hist.ptr, 0, 16 * sizeof(unsigned long long), c->stream));
+        cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
+        cub::DoubleBuffer<uint32_t> vb(c->d_vals.ptr, c->d_vals_alt.ptr);
+        if (n > 0) {
+            tag_parts_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->d_keys.ptr, n, pos_bits, c->parts, c->d_hist.ptr);
+            size_t tmp_bytes = 0;
+            PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, (int)n, 60, 64, c->stream));
+            if ((rc = c->d_sort_tmp.ensure(tmp_bytes))) return rc;
+            PMFS_CUDA(cub::DeviceRadixSort::SortPairs(c->d_sort_tmp.ptr, tmp_bytes, kb, vb, (int)n, 60, 64, c->stream));
+            tm.n_launches += 1;
+        }
+        unsigned long long hist[16] = {};
+        PMFS_CUDA(cudaMemcpyAsync(hist, c->d_hist.ptr, sizeof(hist), cudaMemcpyDeviceToHost, c->stream));
+        PMFS_CUDA(cudaEventRecord(c->ev[4], c->stream));
+        PMFS_CUDA(cudaEventSynchronize(c->ev[4]));
+        for (int r = 0; r < 16; r++) c->part_counts[r] = (int64_t)hist[r];
+        c->parts_keys = kb.Current();
+        c->parts_vals = vb.Current();
+        cudaEventElapsedTime(&tm.sort_ms, c->ev[3], c->ev[4]);
+        tm.total_ms = tm.h2d_ms + tm.forward_ms + tm.backward_ms + tm.sort_ms;
+        c->last_n_out = 0;
+        tm.wall_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
+        *n_out = n;
+        if (d_out) *d_out = nullptr;
+        return PMFS_OK;
+    }
     if (n > 0) {
         if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
         if ((rc = c->d_vals_alt.ensure(c->d_vals.cap))) return rc;
@@ -1122,6 +1198,70 @@ int pmfs_run_device(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
                     const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut** d_out, int64_t* n_out) {
     if (c) c->timing.h2d_ms = 0;
     return run_device_impl(c, algo, d_msa, row_stride, n_rows, n_cols, d_cons, d_forced, d_out, n_out);
+}
+
+int pmfs_set_shard(pmfs_ctx* c, int64_t pos_offset, int64_t total_cols, int32_t n_parts, const int32_t* node_bounds) {
+    if (!c || n_parts < 0 || n_parts > 16 || pos_offset < 0 || (n_parts > 0 && (!node_bounds || total_cols <= 0))) {
+        g_error = "pmfs_set_shard: bad argument (at most 16 parts)";
+        return PMFS_ERR_ARG;
+    }
+    c->parts.n_parts = n_parts;
+    for (int r = 0; r <= n_parts && n_parts > 0; r++) {
+        if (r > 0 && node_bounds[r] < node_bounds[r - 1]) {
+            g_error = "pmfs_set_shard: node_bounds must not decrease";
+            return PMFS_ERR_ARG;
+        }
+        c->parts.bound[r] = node_bounds[r];
+    }
+    c->shard_pos_offset = pos_offset;
+    c->shard_total_cols = total_cols;
+    return PMFS_OK;
+}
+
+int pmfs_get_parts(pmfs_ctx* c, const void** d_keys, const void** d_vals, int64_t* counts) {
+    if (!c || !d_keys || !d_vals || !counts || c->parts.n_parts <= 0) {
+        g_error = "pmfs_get_parts: context is not in shard mode";
+        return PMFS_ERR_STATE;
+    }
+    *d_keys = c->parts_keys;
+    *d_vals = c->parts_vals;
+    for (int r = 0; r < c->parts.n_parts; r++) counts[r] = c->part_counts[r];
+    return PMFS_OK;
+}
+
+int pmfs_sort_records(pmfs_ctx* c, void* d_keys, void* d_vals, int64_t n, pmfs_mut** d_out) {
+    if (!c || n < 0 || (n > 0 && (!d_keys || !d_vals)) || !d_out || n > 0x7fffffffll) {
+        g_error = "pmfs_sort_records: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    const int64_t span = c->parts.n_parts > 0 ? c->shard_total_cols : 0;
+    if (span <= 0) {
+        g_error = "pmfs_sort_records: call pmfs_set_shard first (the key layout depends on the total column count)";
+        return PMFS_ERR_STATE;
+    }
+    int pos_bits = 1, node_bits = 1;
+    while ((1ll << pos_bits) < span) pos_bits++;
+    while ((1ll << node_bits) < c->plan.n_nodes) node_bits++;
+    int rc;
+    if ((rc = c->d_out.ensure((size_t)std::max<int64_t>(1, n)))) return rc;
+    if (n > 0) {
+        if ((rc = c->d_rkeys_alt.ensure((size_t)n))) return rc;
+        if ((rc = c->d_rvals_alt.ensure((size_t)n))) return rc;
+        cub::DoubleBuffer<unsigned long long> kb((unsigned long long*)d_keys, c->d_rkeys_alt.ptr);
+        cub::DoubleBuffer<uint32_t> vb((uint32_t*)d_vals, c->d_rvals_alt.ptr);
+        size_t tmp_bytes = 0;
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
+        if ((rc = c->d_sort_tmp2.ensure(tmp_bytes))) return rc;
+        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(c->d_sort_tmp2.ptr, tmp_bytes, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
+        // (the owner tag in bits 60..63 is above the sorted bits and is masked off here)
+        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), n, pos_bits, c->d_out.ptr);
+        PMFS_CUDA(cudaGetLastError());
+    }
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    c->last_n_out = n;
+    *d_out = c->d_out.ptr;
+    return PMFS_OK;
 }
 
 int pmfs_download(pmfs_ctx* c, pmfs_mut* host_out, int64_t n) {

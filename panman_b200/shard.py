@@ -66,6 +66,92 @@ def gather_records(rec, col_offset: int, rank: int, world: int, group=None):
     return allrec.index_select(0, order)
 
 
+def node_ranges(n_nodes: int, world: int):
+    """Contiguous node-id ranges, one per rank: rank r owns the mutation lists of nodes [b, e)."""
+    return [((n_nodes * r) // world, (n_nodes * (r + 1)) // world) for r in range(world)]
+
+
+def exchange_by_node(rec, col_offset: int, rank: int, world: int, n_nodes: int, group=None):
+    """Scalable form of the gather: an all-to-all that leaves every rank with the COMPLETE mutation lists (all column
+    shards, sorted by (node, global pos)) of its own node range -- per-rank traffic and merge work stay constant as ranks
+    are added, instead of piling everything on rank 0.  rec: int32 [n,3] sorted by (node,pos), positions shard-local.
+
+    One host synchronisation (the split sizes); the merge is a scatter, not a sort: parts arrive sorted and shard
+    ranges are rank-ordered, so a record's slot is  start(node) + records of that node from lower ranks + its index
+    inside its own part's run of that node."""
+    import torch
+    import torch.distributed as dist
+
+    dev = rec.device
+    bounds = torch.tensor([b for b, _ in node_ranges(n_nodes, world)] + [n_nodes], dtype=torch.int32, device=dev)
+    nodes = rec[:, 0].contiguous()
+    cuts = torch.searchsorted(nodes, bounds).to(torch.int64)          # [world+1] split points of my list
+    all_cuts = [torch.empty_like(cuts) for _ in range(world)]
+    dist.all_gather(all_cuts, cuts, group=group)
+    all_cuts = torch.stack(all_cuts).cpu()                            # the one host sync
+    send = (all_cuts[rank, 1:] - all_cuts[rank, :-1]).tolist()
+    recv = (all_cuts[:, rank + 1] - all_cuts[:, rank]).tolist()
+    local = rec.clone()
+    local[:, 1] += col_offset
+    inbox = torch.empty((sum(recv), 3), dtype=torch.int32, device=dev)
+    dist.all_to_all_single(inbox, local, output_split_sizes=recv, input_split_sizes=send, group=group)
+    # scatter-merge of the `world` sorted parts
+    b, e = node_ranges(n_nodes, world)[rank]
+    nloc = max(1, e - b)
+    node_l = (inbox[:, 0] - b).to(torch.int64)
+    part = torch.repeat_interleave(torch.arange(world, device=dev), torch.tensor(recv, device=dev))
+    counts = torch.zeros((world, nloc), dtype=torch.int64, device=dev)
+    counts.view(-1).index_add_(0, part * nloc + node_l, torch.ones_like(node_l))
+    per_node = counts.sum(0)
+    node_start = torch.cumsum(per_node, 0) - per_node                 # first slot of each node
+    before = torch.cumsum(counts, 0) - counts                         # records of that node from lower ranks
+    run_start = torch.cumsum(counts, 1) - counts                      # index of the node's run inside its part
+    part_start = torch.tensor([0] + recv[:-1], device=dev).cumsum(0)
+    idx_in_part = torch.arange(inbox.shape[0], device=dev) - part_start[part]
+    dest = node_start[node_l] + before[part, node_l] + (idx_in_part - run_start[part, node_l])
+    out = torch.empty_like(inbox)
+    out[dest] = inbox
+    return out
+
+
+def _as_tensor(ptr: int, n: int, dtype_str: str, device):
+    import torch
+
+    tdt = {"<i8": torch.int64, "<i4": torch.int32}[dtype_str]
+    if n == 0:
+        return torch.zeros(0, dtype=tdt, device=device)
+
+    class _Wrap:
+        __cuda_array_interface__ = {"shape": (n,), "typestr": dtype_str, "data": (ptr, False), "version": 3}
+
+    return torch.as_tensor(_Wrap(), device=device)
+
+
+def exchange_parts(ctx, rank: int, world: int, device, group=None):
+    """The data path's single exchange on GPUs, after a shard-mode pmfs_run_device on every rank: all-to-all of the
+    owner-grouped (key, value) pairs over NCCL, then each rank orders what it received with the library's radix sort.
+    Returns (device pointer to this rank's pmfs_mut records, count)."""
+    import torch
+    import torch.distributed as dist
+
+    d_keys, d_vals, send = ctx.get_parts()
+    n = sum(send)
+    keys = _as_tensor(d_keys, n, "<i8", device)
+    vals = _as_tensor(d_vals, n, "<i4", device)
+    mine = torch.tensor(send, dtype=torch.int64, device=device)
+    table = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(table, mine, group=group)
+    recv = torch.stack(table)[:, rank].tolist()  # the one host synchronisation of the exchange
+    total = sum(recv)
+    in_keys = torch.empty(total, dtype=torch.int64, device=device)
+    in_vals = torch.empty(total, dtype=torch.int32, device=device)
+    dist.all_to_all_single(in_keys, keys, output_split_sizes=recv, input_split_sizes=send, group=group)
+    dist.all_to_all_single(in_vals, vals, output_split_sizes=recv, input_split_sizes=send, group=group)
+    torch.cuda.current_stream(device).synchronize()
+    out = ctx.sort_records(in_keys.data_ptr(), in_vals.data_ptr(), total)
+    return out, total
+
+
 def gather_device_records(ptr: int, n: int, rank: int, world: int, device, col_offset: int | None = None, cols_per_rank: int = 0):
     """bench.py helper: gather the records of the last pmfs_run_device call of every rank to rank 0."""
     rec = records_as_tensor(ptr, n, device)

@@ -85,3 +85,47 @@ def test_config2_full_size_properties_and_subsample_parity(algo):
         mine["pos"] = np.searchsorted(cols, mine["pos"])
         mine = mine[np.lexsort((mine["pos"], mine["node"]))]
         assert G.same_muts(mine, want)
+
+
+def test_shard_mode_two_contexts_equal_unsharded():
+    """Column shards on ONE GPU (two contexts stand in for two ranks): shard-mode runs, the all-to-all emulated by
+    slicing, pmfs_sort_records on each owner -> every owner holds exactly its node range of the unsharded result."""
+    torch = _torch()
+    from panman_b200 import shard
+
+    N, L = 1500, 8000
+    tree = trees.random_binary_tree(N, seed=9)
+    spec = api.SynthSpec(p_sub=0.003, p_del=0.002, p_ins=0.01, p_n_block=0.01, p_amb=0.001)
+    world = 2
+    cols = shard.column_shards(L, world)
+    nodes = shard.node_ranges(tree.n_nodes, world)
+    bounds = [b for b, _ in nodes] + [tree.n_nodes]
+    with api.Context(tree) as full:
+        d_msa, d_cons, stride = synth_on_device(full, spec, N, 0, L)
+        _, n = full.run_device(api.FITCH, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr())
+        want = full.download(n)
+    ctxs, keys, vals, counts, keep = [], [], [], [], []
+    for r in range(world):
+        ctx = api.Context(tree)
+        b, e = cols[r]
+        m, c, st = synth_on_device(ctx, spec, N, b, e - b)
+        assert bool((api.unpack_nibbles(m.cpu().numpy(), e - b) == api.unpack_nibbles(d_msa.cpu().numpy(), L)[:, b:e]).all())
+        ctx.set_shard(b, L, bounds)
+        _, n_r = ctx.run_device(api.FITCH, m.data_ptr(), st, N, e - b, c.data_ptr())
+        dk, dv, cnt = ctx.get_parts()
+        assert sum(cnt) == n_r
+        keys.append(shard._as_tensor(dk, n_r, "<i8", "cuda").clone())
+        vals.append(shard._as_tensor(dv, n_r, "<i4", "cuda").clone())
+        counts.append(cnt)
+        ctxs.append(ctx)
+        keep.append((m, c))
+    for r in range(world):  # what rank r would receive
+        offs = [np.concatenate([[0], np.cumsum(counts[s])]) for s in range(world)]
+        in_k = torch.cat([keys[s][offs[s][r]: offs[s][r + 1]] for s in range(world)])
+        in_v = torch.cat([vals[s][offs[s][r]: offs[s][r + 1]] for s in range(world)])
+        ctxs[r].sort_records(in_k.data_ptr(), in_v.data_ptr(), int(in_k.shape[0]))
+        got = ctxs[r].download(int(in_k.shape[0]))
+        sel = (want["node"] >= nodes[r][0]) & (want["node"] < nodes[r][1])
+        assert G.same_muts(got, want[sel]) and (got["parent_code"] == want[sel]["parent_code"]).all(), r
+    for ctx in ctxs:
+        ctx.close()

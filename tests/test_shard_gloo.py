@@ -44,6 +44,11 @@ def _worker(rank, world, port, seed, q):
     cons = synth.consensus_first_nongap(msa)
     b, e = shard.column_shards(L, world)[rank]
     mine = O.run_port(1, tree, np.ascontiguousarray(msa[:, b:e]), cons[b:e], None)
+    want_all = O.run_port(1, tree, msa, cons, None)
+    owned = shard.exchange_by_node(shard.numpy_to_records(_to_mut12(mine)), b, rank, world, tree.n_nodes)
+    nb, ne = shard.node_ranges(tree.n_nodes, world)[rank]
+    sel = (want_all["node"] >= nb) & (want_all["node"] < ne)
+    q.put(("x", rank, G.same_muts(shard.records_to_numpy(owned), want_all[sel]), int(sel.sum())))
     merged = shard.gather_records(shard.numpy_to_records(_to_mut12(mine)), b, rank, world)
     if rank == 0:
         got = shard.records_to_numpy(merged)
@@ -83,6 +88,9 @@ def test_gather_merge_pack_world2():
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
-    ok, straddle = q.get(timeout=10)
+    got = [q.get(timeout=10) for _ in range(3)]
+    ex = [g for g in got if g[0] == "x"]
+    assert len(ex) == 2 and all(g[2] for g in ex) and all(g[3] > 0 for g in ex), ex  # all-to-all by node range
+    ok, straddle = [g for g in got if g[0] != "x"][0]
     assert ok
     assert straddle, "test input should contain a run of consecutive positions across the shard boundary"
