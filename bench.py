@@ -21,6 +21,9 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# NCCL_DEBUG=VERSION makes NCCL print its version banner on STDOUT, next to the one JSON line the driver parses
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+    del os.environ["NCCL_DEBUG"]
 
 N_TAXA = 20000
 N_COLS = 30000

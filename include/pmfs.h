@@ -120,13 +120,14 @@ int pmfs_run_device(pmfs_ctx* ctx, int algo, const uint8_t* d_msa_nibbles, int64
  * pmfs_set_shard puts a context in shard mode: its columns are [pos_offset, pos_offset+n_cols) of a total_cols-wide
  * alignment, and node ids [node_bounds[r], node_bounds[r+1]) are owned by rank r (n_parts <= 16; n_parts = 0 leaves
  * shard mode).  In shard mode pmfs_run_device emits global positions, does NOT order the records and returns
- * *d_out = NULL; instead the (key, value) pairs are grouped by owning rank: pmfs_get_parts gives the device arrays
- * (u64 keys, u32 values; owner r's pairs are the counts[r] pairs after those of owners < r) for an all-to-all, and the
- * owner orders everything it received with pmfs_sort_records (d_keys/d_vals are overwritten; result valid until the
- * next run), which yields its nodes' complete (node,pos)-sorted lists. */
+ * *d_out = NULL.  The records (one opaque 64-bit word each) are written straight into one region per owning rank:
+ * pmfs_get_parts gives the base device pointer, the region stride in records and the counts (owner r's records are
+ * d_records[r*region_stride .. +counts[r])) for an all-to-all, and the owner orders everything it received with
+ * pmfs_sort_records (d_records is overwritten; the result is valid until the next run), which yields its nodes'
+ * complete (node,pos)-sorted lists. */
 int pmfs_set_shard(pmfs_ctx* ctx, int64_t pos_offset, int64_t total_cols, int32_t n_parts, const int32_t* node_bounds);
-int pmfs_get_parts(pmfs_ctx* ctx, const void** d_keys, const void** d_vals, int64_t* counts);
-int pmfs_sort_records(pmfs_ctx* ctx, void* d_keys, void* d_vals, int64_t n, pmfs_mut** d_out);
+int pmfs_get_parts(pmfs_ctx* ctx, const void** d_records, int64_t* region_stride, int64_t* counts);
+int pmfs_sort_records(pmfs_ctx* ctx, void* d_records, int64_t n, pmfs_mut** d_out);
 
 /* Copies device records of the last pmfs_run_device / pmfs_sort_records to a caller buffer of at least n records. */
 int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);
@@ -137,12 +138,12 @@ int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);
  * loop (cudaMalloc and cudaFree stall the whole device), a process whose HBM already belongs to another allocator, or
  * code running where the allocator must not be called.  It computes exactly what pmfs_run_device(ctx, PMFS_FITCH, ...)
  * computes, on the plan the context already holds, but every intermediate (the set array shared by the two walk
- * kernels, parent states, bit-sliced consensus, unsorted record pairs, sort buffers) comes out of one 32 MiB array with
+ * kernels, parent states, bit-sliced consensus, unsorted records, sort buffers) comes out of one 32 MiB array with
  * static storage duration in device memory, which every GPU that loads this library keeps until the process exits.
  *   inputs   device pointers as for pmfs_run_device (all columns are processed in one pass, no tiling)
  *   outputs  d_out: caller's device buffer of out_capacity records, filled sorted by (node,pos); *n_out: record count
  * Limits: the call is rejected with PMFS_ERR_ARG and an explanatory pmfs_last_error() when
- *   256-byte-rounded (n_internal*ceil(n_cols/32)*64 + n_chunks*ceil(n_cols/32)*20 + out_capacity*24 + sort workspace)
+ *   256-byte-rounded (n_internal*ceil(n_cols/32)*64 + n_chunks*ceil(n_cols/32)*20 + out_capacity*16 + sort workspace)
  * exceeds 32 MiB, and when more than out_capacity records are produced (*n_out then holds the number needed).
  * The first call on a device looks up the array's address on that device; make that first call before any CUDA stream
  * capture begins.  All calls share the array: it keeps the previous call's contents (the call clears the two words

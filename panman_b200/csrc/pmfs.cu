@@ -28,6 +28,10 @@
 namespace pmfs {
 
 constexpr int kTPB = 128;  // threads (= column groups) per CTA
+// A mutation record is ONE 64-bit word: sort key (node, column) in the high bits, payload in the low 10 bits
+// (type 2 bits, node state 4, parent state 4), so ordering the records is a keys-only radix sort over exactly the
+// key bits that can be set, and the multi-GPU exchange moves 8 bytes per record.
+constexpr int kPayloadBits = 10;
 
 static thread_local std::string g_error;
 
@@ -69,13 +73,14 @@ struct WalkParams {
     uint32_t* xvalid;           // [NC][G]
     const int32_t* int_to_node;
     const int32_t* row_to_node;
-    unsigned long long* out_keys;
-    uint32_t* out_vals;
-    unsigned long long* out_count;
-    unsigned long long out_cap;
+    unsigned long long* out_keys;   // [n_owners][out_cap] packed records (see kPayloadBits)
+    unsigned long long* out_count;  // [n_owners]
+    unsigned long long out_cap;     // capacity of one owner's region
+    int32_t n_owners;               // 1, or the number of ranks in column-shard mode
+    int32_t owner_bound[17];        // nodes [owner_bound[r], owner_bound[r+1]) are owned by rank r
     unsigned int* err_flag;
     int64_t pos_offset;         // global column of this context's first column (column shards); 0 otherwise
-    int pos_bits;               // record key = node << pos_bits | column: only the bits that can be set get sorted
+    int pos_bits;               // record = ((node << pos_bits | column) << kPayloadBits) | payload
 };
 
 // 64-word sliding window over a word array that every lane of the warp reads at the same, never decreasing index
@@ -328,9 +333,12 @@ struct DevEnv {
     __device__ void emit(uint32_t node, uint32_t m, const Code4& G, const Code4& P) const {
         const unsigned full = 0xffffffffu;
         const uint32_t total = __reduce_add_sync(full, (uint32_t)__popc(m));
+        int own = 0;  // owner of this node's list (column shards); uniform across the warp
+        for (int r = 1; r < p.n_owners; r++) own += (int32_t)node >= p.owner_bound[r];
         unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(p.out_count, (unsigned long long)total);
+        if (lane == 0) base = atomicAdd(p.out_count + own, (unsigned long long)total);
         base = __shfl_sync(full, base, 0);
+        unsigned long long* out = p.out_keys + (unsigned long long)own * p.out_cap;
         uint32_t srcs = __ballot_sync(full, m != 0);
         const unsigned long long pos0 = (unsigned long long)(p.pos_offset + p.col_base + gwarp * 32 + column_of_bit(lane));
         while (srcs) {
@@ -348,8 +356,8 @@ struct DevEnv {
                 if (idx < p.out_cap) {
                     // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
                     const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
-                    p.out_keys[idx] = ((unsigned long long)node << p.pos_bits) | (pos0 + (unsigned long long)src * 32);
-                    p.out_vals[idx] = type | (cg << 8) | (cp << 16);
+                    const unsigned long long key = ((unsigned long long)node << p.pos_bits) | (pos0 + (unsigned long long)src * 32);
+                    out[idx] = (key << kPayloadBits) | type | (cg << 2) | (cp << 6);
                 }
             }
             base += __popc(mm);
@@ -524,44 +532,18 @@ __global__ void prep_planes_kernel(const uint8_t* __restrict__ codes, int64_t ti
     planes[g] = make_uint4(b[0], b[1], b[2], b[3]);
 }
 
-__global__ void assemble_kernel(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ vals, int64_t n,
-                                int pos_bits, pmfs_mut* __restrict__ out) {
+__global__ void assemble_kernel(const unsigned long long* __restrict__ recs, int64_t n, int pos_bits, pmfs_mut* __restrict__ out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    unsigned long long k = keys[i];
-    uint32_t v = vals[i];
+    const unsigned long long r = recs[i], k = r >> kPayloadBits;
     pmfs_mut m;
-    m.node = (int32_t)((k & 0x0fffffffffffffffull) >> pos_bits);  // bits 60..63 may carry a shard owner tag
+    m.node = (int32_t)(k >> pos_bits);
     m.pos = (int32_t)(k & ((1ull << pos_bits) - 1));
-    m.type = (uint8_t)(v & 0xff);
-    m.code = (uint8_t)((v >> 8) & 0xff);
-    m.parent_code = (uint8_t)((v >> 16) & 0xff);
+    m.type = (uint8_t)(r & 3);
+    m.code = (uint8_t)((r >> 2) & 15);
+    m.parent_code = (uint8_t)((r >> 6) & 15);
     m.pad = 0;
     out[i] = m;
-}
-
-// Column shards: tag every record with the rank that owns its node (bits 60..63 of the key) and count records per
-// owner; one radix pass on those 4 bits then makes each owner's records contiguous for the all-to-all.
-struct PartBounds {
-    int32_t n_parts;
-    int32_t bound[17];  // nodes [bound[r], bound[r+1]) belong to part r
-};
-__global__ void tag_parts_kernel(unsigned long long* __restrict__ keys, int64_t n, int pos_bits, const PartBounds pb,
-                                 unsigned long long* __restrict__ hist) {
-    __shared__ unsigned int sh[16];
-    if (threadIdx.x < 16) sh[threadIdx.x] = 0;
-    __syncthreads();
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) {
-        const unsigned long long k = keys[i];
-        const int32_t node = (int32_t)(k >> pos_bits);
-        int part = 0;
-        for (int r = 1; r < pb.n_parts; r++) part += node >= pb.bound[r];
-        keys[i] = k | ((unsigned long long)part << 60);
-        atomicAdd(&sh[part], 1u);
-    }
-    __syncthreads();
-    if (threadIdx.x < pb.n_parts && sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
 }
 
 // ------------------------------------------------------------------------------------------------ synthetic alignments
@@ -676,6 +658,11 @@ struct DevBuf {
 
 using namespace pmfs;
 
+struct PartBounds {
+    int32_t n_parts;
+    int32_t bound[17];  // nodes [bound[r], bound[r+1]) belong to rank r
+};
+
 struct pmfs_ctx {
     int device = 0;
     Plan plan;
@@ -705,16 +692,15 @@ struct pmfs_ctx {
     PartBounds parts = {};
     int64_t part_counts[16] = {};
     unsigned long long* parts_keys = nullptr;
-    uint32_t* parts_vals = nullptr;
-    DevBuf<unsigned long long> d_hist, d_rkeys_alt;
-    DevBuf<uint32_t> d_rvals_alt;
+    int64_t parts_stride = 0;
+    DevBuf<unsigned long long> d_rkeys_alt;
     DevBuf<uint8_t> d_sort_tmp2;
     DevBuf<int32_t> d_fwd_len, d_bwd_len, d_fwd_order, d_bwd_order, d_int_to_node, d_row_to_node;
     // per-run state
     DevBuf<uint4> d_S, d_D, d_cons_planes, d_forced_planes, d_xcode;
     DevBuf<uint32_t> d_xvalid;
     DevBuf<unsigned long long> d_keys, d_keys_alt;
-    DevBuf<uint32_t> d_vals, d_vals_alt;
+
     DevBuf<unsigned long long> d_count;
     DevBuf<unsigned int> d_err;
     DevBuf<uint8_t> d_sort_tmp;
@@ -861,13 +847,13 @@ void pmfs_destroy(pmfs_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->d_fwd_stream.release(); c->d_bwd_stream.release(); c->d_fwd_soff.release(); c->d_bwd_soff.release();
     c->d_fwd_slen.release(); c->d_bwd_slen.release(); c->d_chunk_parent.release(); c->d_chunk_nchild.release();
-    c->d_sync.release(); c->d_hist.release(); c->d_rkeys_alt.release(); c->d_rvals_alt.release(); c->d_sort_tmp2.release();
+    c->d_sync.release(); c->d_rkeys_alt.release(); c->d_sort_tmp2.release();
     c->d_fwd_prog.release(); c->d_bwd_prog.release(); c->d_fwd_off.release(); c->d_bwd_off.release();
     c->d_fwd_len.release(); c->d_bwd_len.release(); c->d_fwd_order.release(); c->d_bwd_order.release();
     c->d_int_to_node.release(); c->d_row_to_node.release();
     c->d_S.release(); c->d_D.release(); c->d_cons_planes.release(); c->d_forced_planes.release();
     c->d_xcode.release(); c->d_xvalid.release(); c->d_keys.release(); c->d_keys_alt.release();
-    c->d_vals.release(); c->d_vals_alt.release(); c->d_count.release(); c->d_err.release();
+    c->d_count.release(); c->d_err.release();
     c->d_sort_tmp.release(); c->d_out.release(); c->d_msa.release(); c->d_cons.release(); c->d_forced.release();
     c->d_path_off.release(); c->d_path_node.release();
     if (c->h_out) cudaFreeHost(c->h_out);
@@ -1029,8 +1015,8 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     }
     while ((1ll << pos_bits) < pos_span) pos_bits++;
     while ((1ll << node_bits) < P->n_nodes) node_bits++;
-    if (pos_bits + node_bits > 60) {
-        g_error = "pmfs_run: node and column counts need more than 60 key bits";
+    if (pos_bits + node_bits + kPayloadBits > 64) {
+        g_error = "pmfs_run: log2(nodes) + log2(columns) must not exceed 54 (a record is one 64-bit word)";
         return PMFS_ERR_ARG;
     }
 
@@ -1041,21 +1027,23 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     if (d_forced && (rc = c->d_forced_planes.ensure(tile_groups))) return rc;
     if ((rc = c->d_xcode.ensure((size_t)NC * tile_groups))) return rc;
     if ((rc = c->d_xvalid.ensure((size_t)NC * tile_groups))) return rc;
-    if ((rc = c->d_count.ensure(1))) return rc;
+    if ((rc = c->d_count.ensure(16))) return rc;
     if ((rc = c->d_err.ensure(1))) return rc;
     if ((rc = c->d_sync.ensure(sync_ints(*P, tile_groups)))) return rc;
-    size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);
+    const int n_owners = std::max(1, c->parts.n_parts);
+    size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);  // total records; one owner's region is cap / n_owners
 
     pmfs_timing& tm = c->timing;
     const float h2d_keep = tm.h2d_ms;
     tm = pmfs_timing();
     tm.h2d_ms = h2d_keep;
     float fwd_ms = 0, bwd_ms = 0;
-    unsigned long long count = 0;
+    unsigned long long count = 0, counts[16] = {};
+    size_t region = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
         if ((rc = c->d_keys.ensure(cap))) return rc;
-        if ((rc = c->d_vals.ensure(cap))) return rc;
-        PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, sizeof(unsigned long long), c->stream));
+        region = c->d_keys.cap / (size_t)n_owners;
+        PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, 16 * sizeof(unsigned long long), c->stream));
         PMFS_CUDA(cudaMemsetAsync(c->d_err.ptr, 0, sizeof(unsigned int), c->stream));
         fwd_ms = bwd_ms = 0;
         tm.n_launches = 0;
@@ -1075,9 +1063,10 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             wp.int_to_node = c->d_int_to_node.ptr;
             wp.row_to_node = c->d_row_to_node.ptr;
             wp.out_keys = c->d_keys.ptr;
-            wp.out_vals = c->d_vals.ptr;
             wp.out_count = c->d_count.ptr;
-            wp.out_cap = c->d_keys.cap;
+            wp.out_cap = region;
+            wp.n_owners = n_owners;
+            for (int r = 0; r <= c->parts.n_parts; r++) wp.owner_bound[r] = c->parts.bound[r];
             wp.err_flag = c->d_err.ptr;
             wp.pos_bits = pos_bits;
             wp.pos_offset = c->parts.n_parts > 0 ? c->shard_pos_offset : 0;
@@ -1108,7 +1097,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             }
         }
         unsigned int err = 0;
-        PMFS_CUDA(cudaMemcpyAsync(&count, c->d_count.ptr, sizeof(count), cudaMemcpyDeviceToHost, c->stream));
+        PMFS_CUDA(cudaMemcpyAsync(counts, c->d_count.ptr, sizeof(counts), cudaMemcpyDeviceToHost, c->stream));
         PMFS_CUDA(cudaMemcpyAsync(&err, c->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
         if (tile_groups >= G_all) {
@@ -1120,8 +1109,18 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                       "(the reference asserts here, src/fitchSankoff.cpp:505)";
             return PMFS_ERR_ROOT_INVALID;
         }
-        if (count <= c->d_keys.cap) break;
-        cap = (size_t)count + (size_t)count / 8 + 1024;  // record buffer was too small: grow and redo the passes
+        count = 0;
+        unsigned long long worst = 0;
+        for (int r = 0; r < n_owners; r++) {
+            count += counts[r];
+            worst = std::max(worst, counts[r]);
+        }
+        if (worst <= region) break;
+        if (attempt == 1) {
+            g_error = "pmfs_run: record buffer overflow after regrowth";
+            return PMFS_ERR_NOMEM;
+        }
+        cap = (size_t)n_owners * ((size_t)worst + (size_t)worst / 8 + 1024);  // too small: grow and redo the passes
     }
     tm.forward_ms = fwd_ms;
     tm.backward_ms = bwd_ms;
@@ -1132,52 +1131,37 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         tm.backward_bytes = P->n_rows_used * Gb + I * Gb * 4;
     }
 
-    // order by (node,pos): radix sort on the key bits that can be non-zero
     const int64_t n = (int64_t)count;
+    if (n > 0x7fffffffll) {
+        g_error = "pmfs_run: more than 2^31 records in one call: run fewer columns per call";
+        return PMFS_ERR_ARG;
+    }
     PMFS_CUDA(cudaEventRecord(c->ev[3], c->stream));
     if (c->parts.n_parts > 0) {
-        // shard mode: no local ordering -- group the records by owning rank (one radix pass on 4 tag bits); the owner
+        // shard mode: records were emitted straight into one region per owning rank and stay unordered; the owner
         // orders what it receives (pmfs_sort_records)
-        if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
-        if ((rc = c->d_vals_alt.ensure(c->d_vals.cap))) return rc;
-        if ((rc = c->d_hist.ensure(16))) return rc;
-        PMFS_CUDA(cudaMemsetAsync(c->d_hist.ptr, 0, 16 * sizeof(unsigned long long), c->stream));
-        cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
-        cub::DoubleBuffer<uint32_t> vb(c->d_vals.ptr, c->d_vals_alt.ptr);
-        if (n > 0) {
-            tag_parts_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(c->d_keys.ptr, n, pos_bits, c->parts, c->d_hist.ptr);
-            size_t tmp_bytes = 0;
-            PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, (int)n, 60, 64, c->stream));
-            if ((rc = c->d_sort_tmp.ensure(tmp_bytes))) return rc;
-            PMFS_CUDA(cub::DeviceRadixSort::SortPairs(c->d_sort_tmp.ptr, tmp_bytes, kb, vb, (int)n, 60, 64, c->stream));
-            tm.n_launches += 1;
-        }
-        unsigned long long hist[16] = {};
-        PMFS_CUDA(cudaMemcpyAsync(hist, c->d_hist.ptr, sizeof(hist), cudaMemcpyDeviceToHost, c->stream));
-        PMFS_CUDA(cudaEventRecord(c->ev[4], c->stream));
-        PMFS_CUDA(cudaEventSynchronize(c->ev[4]));
-        for (int r = 0; r < 16; r++) c->part_counts[r] = (int64_t)hist[r];
-        c->parts_keys = kb.Current();
-        c->parts_vals = vb.Current();
-        cudaEventElapsedTime(&tm.sort_ms, c->ev[3], c->ev[4]);
-        tm.total_ms = tm.h2d_ms + tm.forward_ms + tm.backward_ms + tm.sort_ms;
+        for (int r = 0; r < 16; r++) c->part_counts[r] = r < n_owners ? (int64_t)counts[r] : 0;
+        c->parts_keys = c->d_keys.ptr;
+        c->parts_stride = (int64_t)region;
+        tm.sort_ms = 0;
+        tm.total_ms = tm.h2d_ms + tm.forward_ms + tm.backward_ms;
         c->last_n_out = 0;
         tm.wall_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
         *n_out = n;
         if (d_out) *d_out = nullptr;
         return PMFS_OK;
     }
+    // order by (node,pos): keys-only radix sort over exactly the key bits that can be set
     if (n > 0) {
         if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
-        if ((rc = c->d_vals_alt.ensure(c->d_vals.cap))) return rc;
         if ((rc = c->d_out.ensure((size_t)n))) return rc;
         cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
-        cub::DoubleBuffer<uint32_t> vb(c->d_vals.ptr, c->d_vals_alt.ptr);
         size_t tmp_bytes = 0;
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
+        const int lo = kPayloadBits, hi = kPayloadBits + pos_bits + node_bits;
+        PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
         if ((rc = c->d_sort_tmp.ensure(tmp_bytes))) return rc;
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(c->d_sort_tmp.ptr, tmp_bytes, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
-        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), n, pos_bits, c->d_out.ptr);
+        PMFS_CUDA(cub::DeviceRadixSort::SortKeys(c->d_sort_tmp.ptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
+        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), n, pos_bits, c->d_out.ptr);
         PMFS_CUDA(cudaGetLastError());
         tm.n_launches += 1;
     }
@@ -1218,26 +1202,26 @@ int pmfs_set_shard(pmfs_ctx* c, int64_t pos_offset, int64_t total_cols, int32_t 
     return PMFS_OK;
 }
 
-int pmfs_get_parts(pmfs_ctx* c, const void** d_keys, const void** d_vals, int64_t* counts) {
-    if (!c || !d_keys || !d_vals || !counts || c->parts.n_parts <= 0) {
+int pmfs_get_parts(pmfs_ctx* c, const void** d_records, int64_t* region_stride, int64_t* counts) {
+    if (!c || !d_records || !region_stride || !counts || c->parts.n_parts <= 0) {
         g_error = "pmfs_get_parts: context is not in shard mode";
         return PMFS_ERR_STATE;
     }
-    *d_keys = c->parts_keys;
-    *d_vals = c->parts_vals;
+    *d_records = c->parts_keys;
+    *region_stride = c->parts_stride;
     for (int r = 0; r < c->parts.n_parts; r++) counts[r] = c->part_counts[r];
     return PMFS_OK;
 }
 
-int pmfs_sort_records(pmfs_ctx* c, void* d_keys, void* d_vals, int64_t n, pmfs_mut** d_out) {
-    if (!c || n < 0 || (n > 0 && (!d_keys || !d_vals)) || !d_out || n > 0x7fffffffll) {
+int pmfs_sort_records(pmfs_ctx* c, void* d_records, int64_t n, pmfs_mut** d_out) {
+    if (!c || n < 0 || (n > 0 && !d_records) || !d_out || n > 0x7fffffffll) {
         g_error = "pmfs_sort_records: bad argument";
         return PMFS_ERR_ARG;
     }
     PMFS_CUDA(cudaSetDevice(c->device));
     const int64_t span = c->parts.n_parts > 0 ? c->shard_total_cols : 0;
     if (span <= 0) {
-        g_error = "pmfs_sort_records: call pmfs_set_shard first (the key layout depends on the total column count)";
+        g_error = "pmfs_sort_records: call pmfs_set_shard first (the record layout depends on the total column count)";
         return PMFS_ERR_STATE;
     }
     int pos_bits = 1, node_bits = 1;
@@ -1247,15 +1231,13 @@ int pmfs_sort_records(pmfs_ctx* c, void* d_keys, void* d_vals, int64_t n, pmfs_m
     if ((rc = c->d_out.ensure((size_t)std::max<int64_t>(1, n)))) return rc;
     if (n > 0) {
         if ((rc = c->d_rkeys_alt.ensure((size_t)n))) return rc;
-        if ((rc = c->d_rvals_alt.ensure((size_t)n))) return rc;
-        cub::DoubleBuffer<unsigned long long> kb((unsigned long long*)d_keys, c->d_rkeys_alt.ptr);
-        cub::DoubleBuffer<uint32_t> vb((uint32_t*)d_vals, c->d_rvals_alt.ptr);
+        cub::DoubleBuffer<unsigned long long> kb((unsigned long long*)d_records, c->d_rkeys_alt.ptr);
         size_t tmp_bytes = 0;
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
+        const int lo = kPayloadBits, hi = kPayloadBits + pos_bits + node_bits;
+        PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
         if ((rc = c->d_sort_tmp2.ensure(tmp_bytes))) return rc;
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(c->d_sort_tmp2.ptr, tmp_bytes, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
-        // (the owner tag in bits 60..63 is above the sorted bits and is masked off here)
-        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), n, pos_bits, c->d_out.ptr);
+        PMFS_CUDA(cub::DeviceRadixSort::SortKeys(c->d_sort_tmp2.ptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
+        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), n, pos_bits, c->d_out.ptr);
         PMFS_CUDA(cudaGetLastError());
     }
     PMFS_CUDA(cudaStreamSynchronize(c->stream));
@@ -1487,10 +1469,13 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
         g_error = "pmfs_run_fitch_static: out_capacity too large";
         return PMFS_ERR_ARG;
     }
+    if (pos_bits + node_bits + kPayloadBits > 64) {
+        g_error = "pmfs_run_fitch_static: log2(nodes) + log2(columns) must not exceed 54";
+        return PMFS_ERR_ARG;
+    }
     {
         cub::DoubleBuffer<unsigned long long> kb(nullptr, nullptr);
-        cub::DoubleBuffer<uint32_t> vb(nullptr, nullptr);
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, kb, vb, (int)cap, 0, pos_bits + node_bits, c->stream));
+        PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, sort_tmp, kb, (int)cap, kPayloadBits, kPayloadBits + pos_bits + node_bits, c->stream));
     }
     Carver cv{scratch};
     uint4* S = cv.take<uint4>(I * 4 * (size_t)G);
@@ -1502,13 +1487,11 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     unsigned int* err = cv.take<unsigned int>(1);
     unsigned long long* keys = cv.take<unsigned long long>(cap);
     unsigned long long* keys_alt = cv.take<unsigned long long>(cap);
-    uint32_t* vals = cv.take<uint32_t>(cap);
-    uint32_t* vals_alt = cv.take<uint32_t>(cap);
     uint8_t* tmp = cv.take<uint8_t>(sort_tmp);
     int* sync = cv.take<int>(sync_ints(P, G));
     if (cv.used > kStaticScratchBytes) {
         g_error = "pmfs_run_fitch_static: this problem needs " + std::to_string(cv.used) + " bytes of scratch (" +
-                  std::to_string(I) + " internal nodes x " + std::to_string(G) + " column groups x 64 B, plus 24 B per record "
+                  std::to_string(I) + " internal nodes x " + std::to_string(G) + " column groups x 64 B, plus 16 B per record "
                   "of out_capacity); the static maximum is " + std::to_string(kStaticScratchBytes) +
                   " bytes.  Use pmfs_run_device, which sizes its buffers to the problem.";
         return PMFS_ERR_ARG;
@@ -1534,7 +1517,7 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     wp.int_to_node = c->d_int_to_node.ptr;
     wp.row_to_node = c->d_row_to_node.ptr;
     wp.out_keys = keys;
-    wp.out_vals = vals;
+    wp.n_owners = 1;
     wp.out_count = count;
     wp.out_cap = cap;
     wp.err_flag = err;
@@ -1556,9 +1539,8 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     }
     if (n > 0) {
         cub::DoubleBuffer<unsigned long long> kb(keys, keys_alt);
-        cub::DoubleBuffer<uint32_t> vb(vals, vals_alt);
-        PMFS_CUDA(cub::DeviceRadixSort::SortPairs(tmp, sort_tmp, kb, vb, (int)n, 0, pos_bits + node_bits, c->stream));
-        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), vb.Current(), (int64_t)n, pos_bits, d_out);
+        PMFS_CUDA(cub::DeviceRadixSort::SortKeys(tmp, sort_tmp, kb, (int)n, kPayloadBits, kPayloadBits + pos_bits + node_bits, c->stream));
+        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), (int64_t)n, pos_bits, d_out);
         PMFS_CUDA(cudaGetLastError());
     }
     PMFS_CUDA(cudaStreamSynchronize(c->stream));

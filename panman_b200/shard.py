@@ -129,26 +129,23 @@ def _as_tensor(ptr: int, n: int, dtype_str: str, device):
 
 def exchange_parts(ctx, rank: int, world: int, device, group=None):
     """The data path's single exchange on GPUs, after a shard-mode pmfs_run_device on every rank: all-to-all of the
-    owner-grouped (key, value) pairs over NCCL, then each rank orders what it received with the library's radix sort.
-    Returns (device pointer to this rank's pmfs_mut records, count)."""
+    64-bit records (already grouped by owning rank when they were emitted) over NCCL, then each rank orders what it
+    received with the library's radix sort.  Returns (device pointer to this rank's pmfs_mut records, count)."""
     import torch
     import torch.distributed as dist
 
-    d_keys, d_vals, send = ctx.get_parts()
-    n = sum(send)
-    keys = _as_tensor(d_keys, n, "<i8", device)
-    vals = _as_tensor(d_vals, n, "<i4", device)
+    base, stride, send = ctx.get_parts()
     mine = torch.tensor(send, dtype=torch.int64, device=device)
     table = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(table, mine, group=group)
     recv = torch.stack(table)[:, rank].tolist()  # the one host synchronisation of the exchange
     total = sum(recv)
-    in_keys = torch.empty(total, dtype=torch.int64, device=device)
-    in_vals = torch.empty(total, dtype=torch.int32, device=device)
-    dist.all_to_all_single(in_keys, keys, output_split_sizes=recv, input_split_sizes=send, group=group)
-    dist.all_to_all_single(in_vals, vals, output_split_sizes=recv, input_split_sizes=send, group=group)
+    inbox = torch.empty(total, dtype=torch.int64, device=device)
+    outs = [_as_tensor(base + 8 * stride * r, send[r], "<i8", device) for r in range(world)]
+    ins = list(torch.split(inbox, recv))
+    dist.all_to_all(ins, outs, group=group)
     torch.cuda.current_stream(device).synchronize()
-    out = ctx.sort_records(in_keys.data_ptr(), in_vals.data_ptr(), total)
+    out = ctx.sort_records(inbox.data_ptr(), total)
     return out, total
 
 

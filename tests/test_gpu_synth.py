@@ -104,7 +104,7 @@ def test_shard_mode_two_contexts_equal_unsharded():
         d_msa, d_cons, stride = synth_on_device(full, spec, N, 0, L)
         _, n = full.run_device(api.FITCH, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr())
         want = full.download(n)
-    ctxs, keys, vals, counts, keep = [], [], [], [], []
+    ctxs, parts, keep = [], [], []
     for r in range(world):
         ctx = api.Context(tree)
         b, e = cols[r]
@@ -112,19 +112,15 @@ def test_shard_mode_two_contexts_equal_unsharded():
         assert bool((api.unpack_nibbles(m.cpu().numpy(), e - b) == api.unpack_nibbles(d_msa.cpu().numpy(), L)[:, b:e]).all())
         ctx.set_shard(b, L, bounds)
         _, n_r = ctx.run_device(api.FITCH, m.data_ptr(), st, N, e - b, c.data_ptr())
-        dk, dv, cnt = ctx.get_parts()
+        base, stride, cnt = ctx.get_parts()
         assert sum(cnt) == n_r
-        keys.append(shard._as_tensor(dk, n_r, "<i8", "cuda").clone())
-        vals.append(shard._as_tensor(dv, n_r, "<i4", "cuda").clone())
-        counts.append(cnt)
+        parts.append([shard._as_tensor(base + 8 * stride * o, cnt[o], "<i8", "cuda").clone() for o in range(world)])
         ctxs.append(ctx)
         keep.append((m, c))
-    for r in range(world):  # what rank r would receive
-        offs = [np.concatenate([[0], np.cumsum(counts[s])]) for s in range(world)]
-        in_k = torch.cat([keys[s][offs[s][r]: offs[s][r + 1]] for s in range(world)])
-        in_v = torch.cat([vals[s][offs[s][r]: offs[s][r + 1]] for s in range(world)])
-        ctxs[r].sort_records(in_k.data_ptr(), in_v.data_ptr(), int(in_k.shape[0]))
-        got = ctxs[r].download(int(in_k.shape[0]))
+    for r in range(world):  # what rank r would receive from everybody
+        inbox = torch.cat([parts[s][r] for s in range(world)])
+        ctxs[r].sort_records(inbox.data_ptr(), int(inbox.shape[0]))
+        got = ctxs[r].download(int(inbox.shape[0]))
         sel = (want["node"] >= nodes[r][0]) & (want["node"] < nodes[r][1])
         assert G.same_muts(got, want[sel]) and (got["parent_code"] == want[sel]["parent_code"]).all(), r
     for ctx in ctxs:
