@@ -27,7 +27,7 @@
 
 namespace pmfs {
 
-constexpr int kTPB = 128;  // threads (= column groups) per CTA
+constexpr int kTPB = 256;  // threads (= column groups) per CTA
 // A mutation record is ONE 64-bit word: sort key (node, column) in the high bits, payload in the low 10 bits
 // (type 2 bits, node state 4, parent state 4), so ordering the records is a keys-only radix sort over exactly the
 // key bits that can be set, and the multi-GPU exchange moves 8 bytes per record.
@@ -164,21 +164,29 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 template <int RING>
 struct RingRefs {
     uint32_t data, full, empty;  // shared-space addresses
-    uint32_t prog, prog_bar;     // staged walk program + its barrier
+    uint32_t prog, prog_bar;     // 2 staged walk programs (kProgWords words each) + their barriers
+    uint32_t desc, desc_full, desc_empty;  // 2 item descriptors (int4) + their barriers
 };
 
-// Producer: lane 0 of the 5th warp stages the item's walk program, then walks the chunk's load stream and keeps the
-// ring full.  `unit` and `item_no` advance exactly as on the consumer side.
+// What the producer tells the consumers about a work item (one int4 in shared memory).
+struct ItemDesc {
+    int32_t chunk;   // -1: no more items
+    int32_t tile;
+    int32_t plen;    // program length in words
+    int32_t parent;  // parent chunk (-1 for the chunk with the tree root)
+};
+
+// Producer side of one item: stage the walk program into program buffer `slot`, then walk the chunk's load stream and
+// keep the ring full.  Called by the whole producer warp (the stream words are read warp-wide); lane 0 drives TMA.
 template <int RING>
 __device__ __forceinline__ void produce_stream(const WalkParams& p, const RingRefs<RING>& r, int32_t chunk, int tile,
-                                               uint32_t& unit) {
+                                               int32_t plen, uint32_t slot, uint32_t& unit) {
     const int lane = threadIdx.x & 31;
-    const int32_t plen = p.chunk_len[chunk];
     if (lane == 0 && plen <= kProgWords) {
-        // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see upload_plan)
+        // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
         const uint32_t bytes = (uint32_t)((plen + 3) / 4) * 16u;
-        mbar_arrive_expect_tx(r.prog_bar, bytes);
-        bulk_g2s(r.prog, p.prog + p.chunk_off[chunk], bytes, r.prog_bar);
+        mbar_arrive_expect_tx(r.prog_bar + slot * 8, bytes);
+        bulk_g2s(r.prog + slot * (kProgWords * 4), p.prog + p.chunk_off[chunk], bytes, r.prog_bar + slot * 8);
     }
     const int32_t slen = p.stream_len[chunk];
     WarpWords w;
@@ -222,18 +230,21 @@ struct DevEnv {
     bool prog_staged;
     const uint32_t* gprog;
 
+    uint32_t sprog;  // shared address of this item's staged program
+
     __device__ DevEnv(const WalkParams& p_, int64_t g_, int64_t g_unclamped, bool a, const RingRefs<RING>& r, uint32_t& unit_,
-                      void* stack, int32_t chunk, uint32_t item_no)
+                      void* stack, const ItemDesc& d, uint32_t slot, uint32_t prog_parity)
         : p(p_), g(g_), gwarp(g_unclamped - (threadIdx.x & 31)), active(a), ring(r), unit(unit_), fstk((uint4*)stack),
-          bstk((uint32_t*)stack), lane(threadIdx.x & 31), prog_staged(p_.chunk_len[chunk] <= kProgWords),
-          gprog(p_.prog + p_.chunk_off[chunk]) {
-        if (prog_staged) mbar_wait(ring.prog_bar, item_no & 1u);
+          bstk((uint32_t*)stack), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords), gprog(nullptr),
+          sprog(r.prog + slot * (kProgWords * 4)) {
+        if (prog_staged) mbar_wait(ring.prog_bar + slot * 8, prog_parity);
+        else gprog = p_.prog + p_.chunk_off[d.chunk];
     }
 
     __device__ __forceinline__ uint32_t word(const uint32_t*, int32_t pc) const {
         if (prog_staged) {
             uint32_t w;
-            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(ring.prog + pc * 4));
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(sprog + pc * 4));
             return w;
         }
         return __ldg(gprog + pc);  // very long programs (huge polytomies): straight from L1/L2
@@ -279,6 +290,9 @@ struct DevEnv {
         }
     }
     __device__ __forceinline__ void store_arr(uint4* base, uint32_t id, const Planes16& s) const {
+#ifdef PMFS_EXP_NOSTORE
+        if (s.p[0] != 0x12345678u) return;  // timing experiment only: keeps the computation alive, drops the stores
+#endif
         if (!active) return;
         uint4* q = base + ((int64_t)id * 4) * p.G + g;
 #pragma unroll
@@ -380,81 +394,127 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
     return m;
 }
 
-// Work item = (chunk, column tile of kTPB groups).  One launch per pass: CTAs claim items from a global counter in plan
-// order (bottom-up: chunk height ascending; top-down: chunk depth ascending), so everything an item depends on has a
-// smaller index and was claimed earlier by a CTA that is already running -- waiting on it cannot deadlock, whatever the
-// number of resident CTAs.  Dependencies are per column tile (tile t of a chunk needs only tile t of its child chunks /
-// its parent chunk), tracked by one counter per (chunk, tile); there is no grid-wide barrier and no per-level launch,
-// so narrow levels near the root overlap with wide ones instead of leaving the GPU idle.
-__device__ __forceinline__ int claim_item(const WalkParams& p, int* s_item) {
-    if (threadIdx.x == 0) *s_item = atomicAdd(p.next_item, 1);
-    __syncthreads();
-    return *s_item;
-}
-__device__ __forceinline__ void wait_counter(const int* counter, int need) {
-    if (threadIdx.x == 0) {
-        const volatile int* f = counter;
-        if (*f < need) {
-            const long long t0 = clock64();
-            while (*f < need) {
-                __nanosleep(64);
-                if (clock64() - t0 > kSpinLimitCycles) __trap();
-            }
-        }
-        __threadfence();
-    }
-    __syncthreads();  // (also keeps the next claim from overwriting s_item before every thread has read it)
-}
-__device__ __forceinline__ void signal_counter(int* counter) {
-    __syncthreads();  // every thread of the CTA has issued its stores
-    if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(counter, 1);
-    }
-}
+// Work item = (chunk, column tile of kTPB groups).  One launch per pass: persistent CTAs claim items from a global
+// counter in plan order (bottom-up: chunk height ascending; top-down: chunk depth ascending), so everything an item
+// depends on has a smaller index and was claimed earlier by a CTA that is already running -- waiting on it cannot
+// deadlock, whatever the number of resident CTAs.  Dependencies are per column tile (tile t of a chunk needs only tile
+// t of its child chunks / its parent chunk), tracked by one counter per (chunk, tile); there is no grid-wide barrier
+// and no per-level launch, so narrow levels near the root overlap with wide ones instead of leaving the GPU idle.
+//
+// Inside a CTA the producer warp runs AHEAD of the four walking warps, across item boundaries: while they finish item
+// n it has already claimed item n+1, waited for its dependencies, staged its program and started filling the ring
+// with its operands, so the walkers go from one item to the next without seeing the claim / dependency / staging
+// latencies (a few microseconds, as much as a small item itself takes).  Item descriptors and programs are double
+// buffered; all hand-overs are mbarriers, the kernels contain no CTA-wide barrier after set-up.
+constexpr int kPassFwd = 0, kPassBwd = 1;
 
 template <int RING>
 __device__ __forceinline__ RingRefs<RING> ring_setup(void* smem, unsigned long long* bars) {
-    RingRefs<RING> r;  // dynamic smem: [program kProgWords words][ring RING x 2 KB][walk stack]
+    RingRefs<RING> r;  // dynamic smem: [2 programs of kProgWords words][2 descriptors][ring RING x 2 KB][walk stack]
     r.prog = (uint32_t)__cvta_generic_to_shared(smem);
-    r.data = r.prog + kProgWords * 4;
+    r.desc = r.prog + 2 * kProgWords * 4;
+    r.data = r.desc + 64;
     r.full = (uint32_t)__cvta_generic_to_shared(bars);
     r.empty = r.full + RING * 8;
     r.prog_bar = r.empty + RING * 8;
+    r.desc_full = r.prog_bar + 16;
+    r.desc_empty = r.desc_full + 16;
     if (threadIdx.x == 0) {
-        mbar_init(r.prog_bar, 1);
         for (int i = 0; i < RING; i++) {
             mbar_init(r.full + i * 8, 1);          // one arrive.expect_tx by the producer
             mbar_init(r.empty + i * 8, kTPB / 32);  // one arrive per consumer warp
+        }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(r.prog_bar + i * 8, 1);
+            mbar_init(r.desc_full + i * 8, 1);
+            mbar_init(r.desc_empty + i * 8, kTPB / 32);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     return r;
 }
+constexpr int kSmemHeadWords = 2 * kProgWords + 16;  // programs + descriptors, in 32-bit words (multiple of 4)
+constexpr int kNumBars(int ring) { return 2 * ring + 6; }
+
+// Producer warp: claim -> dependency -> descriptor -> program + operand stream, item after item.
+template <int PASS, int RING>
+__device__ __forceinline__ void producer_loop(const WalkParams& p, const RingRefs<RING>& r) {
+    const int lane = threadIdx.x & 31;
+    uint32_t unit = 0;
+    for (uint32_t n = 0;; n++) {
+        const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
+        int32_t chunk = -1, tile = 0, plen = 0, parent = -1;
+        if (lane == 0) {
+            mbar_wait(r.desc_empty + slot * 8, phase ^ 1u);  // the walkers are done with item n-2 (descriptor + program)
+            const int item = atomicAdd(p.next_item, 1);
+            if (item < p.n_items) {
+                chunk = p.order[item / p.ctas_per_chunk];
+                tile = item % p.ctas_per_chunk;
+                plen = p.chunk_len[chunk];
+                parent = p.chunk_parent[chunk];
+                // dependencies: all child chunks (bottom-up) / the parent chunk (top-down), same column tile
+                const int need = PASS == kPassFwd ? p.chunk_nchild[chunk] : (parent < 0 ? 0 : 1);
+                const volatile int* f = p.ready + (int64_t)(PASS == kPassFwd || parent < 0 ? chunk : parent) * p.ctas_per_chunk + tile;
+                if (*f < need) {
+                    const long long t0 = clock64();
+                    while (*f < need) {
+                        __nanosleep(32);
+                        if (clock64() - t0 > kSpinLimitCycles) __trap();
+                    }
+                }
+                __threadfence();
+                asm volatile("fence.proxy.async;" ::: "memory");  // data written by other CTAs is read by the TMA engine
+            }
+            asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.desc + slot * 16), "r"(chunk), "r"(tile), "r"(plen), "r"(parent)
+                         : "memory");
+            mbar_arrive(r.desc_full + slot * 8);
+        }
+        chunk = __shfl_sync(0xffffffffu, chunk, 0);
+        if (chunk < 0) return;
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        plen = __shfl_sync(0xffffffffu, plen, 0);
+        produce_stream<RING>(p, r, chunk, tile, plen, slot, unit);
+    }
+}
+
+// Walking warps: take the next descriptor; returns false when there is no more work.
+template <int RING>
+__device__ __forceinline__ bool next_item(const RingRefs<RING>& r, uint32_t n, ItemDesc& d) {
+    const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
+    mbar_wait(r.desc_full + slot * 8, phase);
+    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(d.chunk), "=r"(d.tile), "=r"(d.plen), "=r"(d.parent) : "r"(r.desc + slot * 16) : "memory");
+    return d.chunk >= 0;
+}
+// Item finished: publish it to dependants (all walkers' stores first), then free the descriptor/program slot.
+__device__ __forceinline__ void finish_item(int* counter, uint32_t desc_empty_bar) {
+    asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // the four walking warps only
+    if (threadIdx.x == 0 && counter) {
+        __threadfence();
+        atomicAdd(counter, 1);
+    }
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(desc_empty_bar);
+}
 
 template <int ALGO, bool POLY>
 __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
     extern __shared__ uint4 smem[];
-    __shared__ int s_item;
-    __shared__ __align__(8) unsigned long long bars[2 * kRingFwd + 1];
+    __shared__ __align__(8) unsigned long long bars[kNumBars(kRingFwd)];
     const RingRefs<kRingFwd> ring = ring_setup<kRingFwd>(smem, bars);
-    const bool producer = threadIdx.x >= kTPB;
-    uint32_t entry = 0, staged = 0;  // ring units / staged programs so far: advance identically in producer and consumers
-    for (;;) {
-        const int item = claim_item(p, &s_item);
-        if (item >= p.n_items) return;
-        const int32_t chunk = p.order[item / p.ctas_per_chunk];
-        const int tile = item % p.ctas_per_chunk;
-        wait_counter(p.ready + (int64_t)chunk * p.ctas_per_chunk + tile, p.chunk_nchild[chunk]);
-        if (producer) {
-            asm volatile("fence.proxy.async;" ::: "memory");  // sets written by other CTAs are read by the TMA engine
-            produce_stream<kRingFwd>(p, ring, chunk, tile, entry);
-        } else {
-            const int64_t g0 = (int64_t)tile * kTPB + threadIdx.x;
-            const bool active = g0 < p.G;
-            const int64_t g = active ? g0 : p.G - 1;
-            DevEnv<false, kRingFwd> env(p, g, g0, active, ring, entry, smem + kProgWords / 4 + kRingFwd * kTPB, chunk, staged);
+    if (threadIdx.x >= kTPB) {
+        producer_loop<kPassFwd, kRingFwd>(p, ring);
+        return;
+    }
+    uint32_t unit = 0, staged[2] = {0, 0};
+    ItemDesc d;
+    for (uint32_t n = 0; next_item(ring, n, d); n++) {
+        const uint32_t slot = n & 1u;
+        const int64_t g0 = (int64_t)d.tile * kTPB + threadIdx.x;
+        const bool active = g0 < p.G;
+        const int64_t g = active ? g0 : p.G - 1;
+        {
+            DevEnv<false, kRingFwd> env(p, g, g0, active, ring, unit, smem + kSmemHeadWords / 4 + kRingFwd * kTPB, d, slot, staged[slot] & 1u);
             Code4 forced;
             const Code4* fp = nullptr;
             if (ALGO == kAlgoFitch && p.forced_planes) {
@@ -462,41 +522,36 @@ __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
                 forced.b[0] = v.x; forced.b[1] = v.y; forced.b[2] = v.z; forced.b[3] = v.w;
                 fp = &forced;
             }
-            forward_walk<ALGO, POLY>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], fp);
+            forward_walk<ALGO, POLY>(env, nullptr, d.plen, fp);
         }
-        if (p.chunk_len[chunk] <= kProgWords) staged++;
-        const int32_t parent = p.chunk_parent[chunk];
-        if (parent >= 0) signal_counter(p.ready + (int64_t)parent * p.ctas_per_chunk + tile);
+        if (d.plen <= kProgWords) staged[slot]++;
+        finish_item(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr, ring.desc_empty + slot * 8);
     }
 }
 
 template <int ALGO>
 __global__ void __launch_bounds__(kThreads) bwd_kernel(const WalkParams p) {
     extern __shared__ uint4 smem[];
-    __shared__ int s_item;
-    __shared__ __align__(8) unsigned long long bars[2 * kRingBwd + 1];
+    __shared__ __align__(8) unsigned long long bars[kNumBars(kRingBwd)];
     const RingRefs<kRingBwd> ring = ring_setup<kRingBwd>(smem, bars);
-    const bool producer = threadIdx.x >= kTPB;
-    uint32_t entry = 0, staged = 0;  // ring units / staged programs so far: advance identically in producer and consumers
-    for (;;) {
-        const int item = claim_item(p, &s_item);
-        if (item >= p.n_items) return;
-        const int32_t chunk = p.order[item / p.ctas_per_chunk];
-        const int tile = item % p.ctas_per_chunk;
-        const int32_t parent = p.chunk_parent[chunk];
-        wait_counter(p.ready + (int64_t)(parent < 0 ? chunk : parent) * p.ctas_per_chunk + tile, parent < 0 ? 0 : 1);
-        uint32_t err = 0;
-        if (producer) {
-            produce_stream<kRingBwd>(p, ring, chunk, tile, entry);
-        } else {
-            const int64_t g0 = (int64_t)tile * kTPB + threadIdx.x;
-            const bool active = g0 < p.G;
-            const int64_t g = active ? g0 : p.G - 1;
-            DevEnv<true, kRingBwd> env(p, g, g0, active, ring, entry, smem + kProgWords / 4 + kRingBwd * kTPB, chunk, staged);
+    if (threadIdx.x >= kTPB) {
+        producer_loop<kPassBwd, kRingBwd>(p, ring);
+        return;
+    }
+    uint32_t unit = 0, staged[2] = {0, 0};
+    ItemDesc d;
+    for (uint32_t n = 0; next_item(ring, n, d); n++) {
+        const uint32_t slot = n & 1u;
+        const int64_t g0 = (int64_t)d.tile * kTPB + threadIdx.x;
+        const bool active = g0 < p.G;
+        const int64_t g = active ? g0 : p.G - 1;
+        uint32_t err;
+        {
+            DevEnv<true, kRingBwd> env(p, g, g0, active, ring, unit, smem + kSmemHeadWords / 4 + kRingBwd * kTPB, d, slot, staged[slot] & 1u);
             Code4 P, forced;
             uint32_t pv = ~0u;
             const Code4* fp = nullptr;
-            if (chunk == 0) {
+            if (d.chunk == 0) {
                 uint4 v = __ldg(p.cons_planes + g);
                 P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
                 if (ALGO == kAlgoSankoff && p.forced_planes) {
@@ -505,16 +560,16 @@ __global__ void __launch_bounds__(kThreads) bwd_kernel(const WalkParams p) {
                     fp = &forced;
                 }
             } else {  // written by another SM during this launch: read through L2
-                uint4 v = __ldcg(p.xcode + (int64_t)chunk * p.G + g);
+                uint4 v = __ldcg(p.xcode + (int64_t)d.chunk * p.G + g);
                 P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
-                pv = __ldcg(p.xvalid + (int64_t)chunk * p.G + g);
+                pv = __ldcg(p.xvalid + (int64_t)d.chunk * p.G + g);
             }
             const uint32_t colmask = active ? real_column_mask(g, p.tile_cols) : 0u;
-            err = backward_walk<ALGO>(env, p.prog + p.chunk_off[chunk], p.chunk_len[chunk], P, pv, fp, colmask);
+            err = backward_walk<ALGO>(env, nullptr, d.plen, P, pv, fp, colmask);
         }
         if (err) atomicOr(p.err_flag, 1u);
-        if (p.chunk_len[chunk] <= kProgWords) staged++;
-        signal_counter(p.ready + (int64_t)chunk * p.ctas_per_chunk + tile);
+        if (d.plen <= kProgWords) staged[slot]++;
+        finish_item(p.ready + (int64_t)d.chunk * p.ctas_per_chunk + d.tile, ring.desc_empty + slot * 8);
     }
 }
 
@@ -933,7 +988,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     const size_t per_pass = (size_t)n_items;
     wp.next_item = sync + (fwd ? 0 : 32);
     wp.ready = sync + 64 + (fwd ? 0 : per_pass);
-    const size_t smem = (size_t)kProgWords * 4 +
+    const size_t smem = (size_t)kSmemHeadWords * 4 +
                         (fwd ? ((size_t)kRingFwd + (size_t)P.fwd_stack_depth * 4) * kTPB * sizeof(uint4)
                              : (size_t)kRingBwd * kTPB * sizeof(uint4) + (size_t)P.bwd_stack_depth * 5 * kTPB * sizeof(uint32_t));
     if (smem > 200 * 1024) {
