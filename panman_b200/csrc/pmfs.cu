@@ -130,10 +130,22 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
 // A wait that can never be satisfied (a bug in the producer/consumer bookkeeping) must not hang the GPU: after about
 // ten seconds of spinning the kernel traps and the host sees a CUDA error.
 constexpr long long kSpinLimitCycles = 20000000000ll;  // ~10 s
+// slow path: let the hardware park the thread (suspend-time hint) instead of burning issue slots the producer needs
+__device__ __forceinline__ bool mbar_try_park(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(20000u)
+        : "memory");
+    return ok != 0;
+}
 __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
     const long long t0 = clock64();
-    while (!mbar_try(bar, parity))
-        if (clock64() - t0 > kSpinLimitCycles) __trap();
+    for (uint32_t it = 1; !mbar_try_park(bar, parity); it++)
+        if ((it & 255u) == 0 && clock64() - t0 > kSpinLimitCycles) __trap();
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity);
@@ -254,10 +266,14 @@ struct DevEnv {
     // hand the units back
     template <int K>
     __device__ __forceinline__ void next(uint4 (&v)[K]) {
+        bool ok[K];
+#pragma unroll
+        for (int q = 0; q < K; q++)  // all K barrier tests in flight at once (a test takes ~90 cycles to answer)
+            ok[q] = mbar_try(ring.full + ((unit + q) % RING) * 8, ((unit + q) / RING) & 1u);
 #pragma unroll
         for (int q = 0; q < K; q++) {
             const uint32_t u = (unit + q) % RING;
-            mbar_wait(ring.full + u * 8, ((unit + q) / RING) & 1u);
+            if (!ok[q]) mbar_wait_slow(ring.full + u * 8, ((unit + q) / RING) & 1u);
             v[q] = lds128(ring.data + u * (kTPB * 16) + threadIdx.x * 16);
         }
         __syncwarp();
@@ -612,41 +628,54 @@ __host__ __device__ __forceinline__ uint32_t hash3(uint64_t seed, uint64_t a, ui
     return (uint32_t)(mix64(seed ^ mix64(a * 0x9e3779b97f4a7c15ull + b)) >> 32);
 }
 
+// The alignment is simulated level by level down the tree (one launch per tree depth): a node's state is its parent's
+// state after the branch events hash3(seed, node, column) decides, so every cell is a pure function of
+// (seed, node, column) and any column range can be generated on its own.  Only the previous level's internal-node
+// states are kept (packed nibbles, ping-pong buffers).
 struct SynthParams {
     uint64_t seed;
     uint32_t t_sub, t_del, t_ins, t_nblock, t_amb, t_acc;  // thresholds on a 32-bit hash
-    const int32_t* path_off;   // [rows+1] CSR: nodes on the root->leaf path of each row's leaf (root excluded)
-    const int32_t* path_node;
+    const int32_t* node;         // [n_level] node ids of this depth
+    const int32_t* parent_slot;  // [n_level] slot of the parent in `prev`
+    const int32_t* my_slot;      // [n_level] slot in `cur` (internal node) or -(row+1) (leaf with an MSA row), 0x7fffffff: absent leaf
+    int32_t n_level;
+    int32_t is_root;
+    const uint32_t* prev;
+    uint32_t* cur;
+    int64_t words;               // 8-column words per row
     int32_t n_rows;
     int64_t col_begin, n_cols;
     uint8_t* msa;
     int64_t row_stride;
 };
 
-__device__ __forceinline__ uint32_t synth_cell(const SynthParams& s, int32_t row, int64_t col) {
-    const uint32_t base4[4] = {1, 2, 4, 8};
-    uint32_t r = hash3(s.seed, 0x1000000000ull, (uint64_t)col);
+__device__ __forceinline__ uint32_t synth_root(const SynthParams& s, int64_t col, uint32_t& r) {
+    r = hash3(s.seed, 0x1000000000ull, (uint64_t)col);
     // root: A .30 C .18 G .20 T .32, or gap in accessory columns
-    uint32_t u = r >> 8, st;
-    if (hash3(s.seed, 0x2000000000ull, (uint64_t)col) < s.t_acc) st = 0;
-    else st = u < 5033165u ? 1 : (u < 8053064u ? 2 : (u < 11408507u ? 4 : 8));
-    for (int32_t e = s.path_off[row]; e < s.path_off[row + 1]; e++) {
-        uint32_t h = hash3(s.seed, (uint64_t)s.path_node[e], (uint64_t)col);
-        if (st != 0) {
-            if (h < s.t_sub) {
-                uint32_t nb = base4[(h >> 3) & 3];
-                st = nb == st ? base4[((h >> 3) + 1) & 3] : nb;
-            } else if (h - s.t_sub < s.t_del) {
-                st = 0;
-            }
-        } else if (h < s.t_ins) {
-            st = base4[(h >> 5) & 3];
+    const uint32_t u = r >> 8;
+    if (hash3(s.seed, 0x2000000000ull, (uint64_t)col) < s.t_acc) return 0;
+    return u < 5033165u ? 1 : (u < 8053064u ? 2 : (u < 11408507u ? 4 : 8));
+}
+__device__ __forceinline__ uint32_t synth_branch(const SynthParams& s, uint32_t st, int32_t node, int64_t col) {
+    const uint32_t base4[4] = {1, 2, 4, 8};
+    const uint32_t h = hash3(s.seed, (uint64_t)node, (uint64_t)col);
+    if (st != 0) {
+        if (h < s.t_sub) {
+            const uint32_t nb = base4[(h >> 3) & 3];
+            st = nb == st ? base4[((h >> 3) + 1) & 3] : nb;
+        } else if (h - s.t_sub < s.t_del) {
+            st = 0;
         }
+    } else if (h < s.t_ins) {
+        st = base4[(h >> 5) & 3];
     }
-    // leaf-only noise
+    return st;
+}
+__device__ __forceinline__ uint32_t synth_leaf(const SynthParams& s, uint32_t st, int32_t row, int64_t col) {
+    const uint32_t base4[4] = {1, 2, 4, 8};
     if (hash3(s.seed, 0x3000000000ull + (uint64_t)row, (uint64_t)(col >> 5)) < s.t_nblock) st = 15;
     else {
-        uint32_t h = hash3(s.seed, 0x4000000000ull + (uint64_t)row, (uint64_t)col);
+        const uint32_t h = hash3(s.seed, 0x4000000000ull + (uint64_t)row, (uint64_t)col);
         if (h < s.t_amb) {
             const uint32_t amb[10] = {3, 5, 6, 7, 9, 10, 11, 12, 13, 14};
             st = amb[(h >> 7) % 10];
@@ -654,23 +683,32 @@ __device__ __forceinline__ uint32_t synth_cell(const SynthParams& s, int32_t row
     }
     // guarantee: one designated row per column is never a gap
     if (st == 0 && (uint32_t)(hash3(s.seed, 0x5000000000ull, (uint64_t)col) % (uint32_t)s.n_rows) == (uint32_t)row)
-        st = base4[r & 3];
+        st = base4[hash3(s.seed, 0x1000000000ull, (uint64_t)col) & 3];
     return st;
 }
 
-// one thread = one (row, 8-column word)
-__global__ void synth_msa_kernel(const SynthParams s) {
-    const int64_t words_per_row = (s.n_cols + 7) / 8;
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= words_per_row * s.n_rows) return;
-    const int32_t row = (int32_t)(i / words_per_row);
-    const int64_t w = i % words_per_row;
+// one thread = one (node of this depth, 8-column word)
+__global__ void synth_level_kernel(const SynthParams s) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= s.words * s.n_level) return;
+    const int32_t k = (int32_t)(i / s.words);
+    const int64_t w = i % s.words;
+    const int32_t node = s.node[k], slot = s.my_slot[k];
+    if (slot == 0x7fffffff) return;
+    const uint32_t parent = s.is_root ? 0u : s.prev[(int64_t)s.parent_slot[k] * s.words + w];
     uint32_t out = 0;
-    for (int k = 0; k < 8; k++) {
-        int64_t c = w * 8 + k;
-        if (c < s.n_cols) out |= synth_cell(s, row, s.col_begin + c) << (4 * k);
+    for (int j = 0; j < 8; j++) {
+        const int64_t c = w * 8 + j;
+        if (c >= s.n_cols) break;
+        const int64_t col = s.col_begin + c;
+        uint32_t st, r;
+        if (s.is_root) st = synth_root(s, col, r);
+        else st = synth_branch(s, (parent >> (4 * j)) & 15u, node, col);
+        if (slot < 0) st = synth_leaf(s, st, -slot - 1, col);
+        out |= st << (4 * j);
     }
-    *(uint32_t*)(s.msa + (int64_t)row * s.row_stride + w * 4) = out;
+    if (slot >= 0) s.cur[(int64_t)slot * s.words + w] = out;
+    else *(uint32_t*)(s.msa + (int64_t)(-slot - 1) * s.row_stride + w * 4) = out;
 }
 
 // first non-gap code in row order (src/panman.cpp:1326-1340 with rows in id order)
@@ -767,7 +805,10 @@ struct pmfs_ctx {
     int64_t last_n_out = 0;
     pmfs_timing timing = {};
     // synth
-    DevBuf<int32_t> d_path_off, d_path_node;
+    DevBuf<int32_t> d_synth_node, d_synth_pslot, d_synth_mslot;
+    DevBuf<uint32_t> d_synth_state[2];
+    std::vector<int64_t> synth_lvl_off;
+    int64_t synth_max_slots = 1;
     bool synth_ready = false;
 };
 
@@ -910,7 +951,8 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_xcode.release(); c->d_xvalid.release(); c->d_keys.release(); c->d_keys_alt.release();
     c->d_count.release(); c->d_err.release();
     c->d_sort_tmp.release(); c->d_out.release(); c->d_msa.release(); c->d_cons.release(); c->d_forced.release();
-    c->d_path_off.release(); c->d_path_node.release();
+    c->d_synth_node.release(); c->d_synth_pslot.release(); c->d_synth_mslot.release();
+    c->d_synth_state[0].release(); c->d_synth_state[1].release();
     if (c->h_out) cudaFreeHost(c->h_out);
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);
@@ -1378,7 +1420,7 @@ void pmfs_result_free(pmfs_ctx* c, pmfs_mut* out) {
 
 int pmfs_synth_msa(pmfs_ctx* c, const pmfs_synth_spec* spec, int64_t col_begin, int64_t n_cols, uint8_t* d_msa,
                    int64_t row_stride, uint8_t* d_cons) {
-    if (!c || !spec || !d_msa || n_cols <= 0 || col_begin < 0 || row_stride % 4 != 0 || row_stride * 2 < n_cols) {
+    if (!c || !spec || !d_msa || n_cols <= 0 || col_begin < 0 || col_begin % 8 != 0 || row_stride % 4 != 0 || row_stride * 2 < n_cols) {
         g_error = "pmfs_synth_msa: bad argument";
         return PMFS_ERR_ARG;
     }
@@ -1389,27 +1431,38 @@ int pmfs_synth_msa(pmfs_ctx* c, const pmfs_synth_spec* spec, int64_t col_begin, 
         return PMFS_ERR_ARG;
     }
     if (!c->synth_ready) {
-        // root->leaf paths (root excluded), one CSR row per MSA row
-        std::vector<int32_t> off(n_rows + 1, 0), nodes;
-        std::vector<int32_t> depth(c->parent.size(), 0);
-        for (size_t v = 1; v < c->parent.size(); v++) depth[v] = depth[c->parent[v]] + 1;
-        for (int32_t r = 0; r < n_rows; r++) off[r + 1] = off[r] + (c->plan.row_to_node[r] >= 0 ? depth[c->plan.row_to_node[r]] : 0);
-        nodes.resize(off[n_rows]);
-        for (int32_t r = 0; r < n_rows; r++) {
-            int32_t v = c->plan.row_to_node[r];
-            if (v < 0) continue;
-            int32_t k = off[r + 1];
-            while (v > 0) {
-                nodes[--k] = v;
-                v = c->parent[v];
+        // nodes grouped by depth; internal nodes get a slot in their level's state buffer
+        const size_t V = c->parent.size();
+        std::vector<int32_t> depth(V, 0);
+        int32_t maxd = 0;
+        for (size_t v = 1; v < V; v++) maxd = std::max(maxd, depth[v] = depth[c->parent[v]] + 1);
+        std::vector<int64_t>& off = c->synth_lvl_off;
+        off.assign((size_t)maxd + 2, 0);
+        for (size_t v = 0; v < V; v++) off[depth[v] + 1]++;
+        for (int32_t d = 0; d <= maxd; d++) off[d + 1] += off[d];
+        std::vector<int32_t> node(V), pslot(V), mslot(V), slot_of(V, -1);
+        std::vector<int64_t> fill(off.begin(), off.end() - 1), n_int((size_t)maxd + 1, 0);
+        c->synth_max_slots = 1;
+        for (size_t v = 0; v < V; v++) {  // ascending ids: parents get their slots before their children
+            const int32_t d = depth[v];
+            const int64_t k = fill[d]++;
+            node[k] = (int32_t)v;
+            pslot[k] = v == 0 ? 0 : slot_of[c->parent[v]];
+            if (c->leaf_row[v] == -1) {
+                slot_of[v] = (int32_t)n_int[d]++;
+                mslot[k] = slot_of[v];
+                c->synth_max_slots = std::max<int64_t>(c->synth_max_slots, n_int[d]);
+            } else {
+                mslot[k] = c->leaf_row[v] >= 0 ? -(c->leaf_row[v] + 1) : 0x7fffffff;
             }
         }
         int rc;
-        if ((rc = c->d_path_off.ensure(off.size()))) return rc;
-        if ((rc = c->d_path_node.ensure(nodes.size()))) return rc;
-        PMFS_CUDA(cudaMemcpy(c->d_path_off.ptr, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
-        if (!nodes.empty())
-            PMFS_CUDA(cudaMemcpy(c->d_path_node.ptr, nodes.data(), nodes.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        if ((rc = c->d_synth_node.ensure(V))) return rc;
+        if ((rc = c->d_synth_pslot.ensure(V))) return rc;
+        if ((rc = c->d_synth_mslot.ensure(V))) return rc;
+        PMFS_CUDA(cudaMemcpy(c->d_synth_node.ptr, node.data(), V * sizeof(int32_t), cudaMemcpyHostToDevice));
+        PMFS_CUDA(cudaMemcpy(c->d_synth_pslot.ptr, pslot.data(), V * sizeof(int32_t), cudaMemcpyHostToDevice));
+        PMFS_CUDA(cudaMemcpy(c->d_synth_mslot.ptr, mslot.data(), V * sizeof(int32_t), cudaMemcpyHostToDevice));
         c->synth_ready = true;
     }
     auto thr = [](float p) -> uint32_t {
@@ -1420,11 +1473,26 @@ int pmfs_synth_msa(pmfs_ctx* c, const pmfs_synth_spec* spec, int64_t col_begin, 
     s.seed = spec->seed;
     s.t_sub = thr(spec->p_sub); s.t_del = thr(spec->p_del); s.t_ins = thr(spec->p_ins);
     s.t_nblock = thr(spec->p_n_block); s.t_amb = thr(spec->p_amb); s.t_acc = thr(spec->accessory_frac);
-    s.path_off = c->d_path_off.ptr; s.path_node = c->d_path_node.ptr;
+    s.words = (n_cols + 7) / 8;
     s.n_rows = n_rows; s.col_begin = col_begin; s.n_cols = n_cols; s.msa = d_msa; s.row_stride = row_stride;
+    {
+        int rc;
+        if ((rc = c->d_synth_state[0].ensure((size_t)c->synth_max_slots * s.words))) return rc;
+        if ((rc = c->d_synth_state[1].ensure((size_t)c->synth_max_slots * s.words))) return rc;
+    }
     PMFS_CUDA(cudaMemsetAsync(d_msa, 0, (size_t)n_rows * row_stride, c->stream));
-    const int64_t total = ((n_cols + 7) / 8) * n_rows;
-    synth_msa_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(s);
+    for (size_t d = 0; d + 1 < c->synth_lvl_off.size(); d++) {
+        const int64_t b0 = c->synth_lvl_off[d], e0 = c->synth_lvl_off[d + 1];
+        s.node = c->d_synth_node.ptr + b0;
+        s.parent_slot = c->d_synth_pslot.ptr + b0;
+        s.my_slot = c->d_synth_mslot.ptr + b0;
+        s.n_level = (int32_t)(e0 - b0);
+        s.is_root = d == 0;
+        s.prev = c->d_synth_state[(d + 1) & 1].ptr;
+        s.cur = c->d_synth_state[d & 1].ptr;
+        const int64_t total = s.words * s.n_level;
+        synth_level_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(s);
+    }
     if (d_cons) synth_consensus_kernel<<<(unsigned)((n_cols + 255) / 256), 256, 0, c->stream>>>(d_msa, row_stride, n_rows, n_cols, d_cons);
     PMFS_CUDA(cudaGetLastError());
     PMFS_CUDA(cudaStreamSynchronize(c->stream));
