@@ -30,6 +30,15 @@ N_COLS = 30000
 B_CONTRACT = {"fitch": 4.25, "sankoff": 6.25}  # level-sweep bytes per column.node update
 
 
+def ncu_traffic(algo):
+    """DRAM bytes per step of fwd_kernel + bwd_kernel from the committed `ncu --set full` capture (profiles/)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic_r1.json")))
+        return float(t[algo]["traffic_bytes_per_step"])
+    except Exception:
+        return None
+
+
 def peaks():
     try:
         p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -50,7 +59,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+                                          "--format=csv,noheader,nounits", "-lms", "20"], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=lambda: [self.rows.append(l) for l in self.proc.stdout], daemon=True).start()
         except Exception:
             self.proc = None
@@ -100,8 +109,8 @@ def cpu_reference_sample(tree, host_codes, cons, algo, threads):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--algo", choices=["fitch", "sankoff"], default="fitch")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--cpu-cols", type=int, default=0, help="columns of the CPU baseline sample (0 = auto)")
@@ -259,9 +268,13 @@ def main():
                                        "per rank") if world > 1 else "1 GPU",
                        "records_per_step": int(n_rec), "plan": plan},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         "traffic": None, "peak_source": peak_src,
+                         "traffic": ncu_traffic(args.algo), "peak_source": peak_src,
+                         "traffic_note": "dram__bytes_read+write of fwd_kernel+bwd_kernel per step, ncu --set full capture of "
+                                         "this workload (profiles/traffic_r1.json); algorithmic bytes at the contract "
+                                         "figure: %.3e" % (V * N_COLS * b),
                          "kernel": "fwd_kernel + bwd_kernel (all chunk levels of one step)",
                          "bytes_per_update_contract": b, "pass_ms_per_step": 1e3 * per_step_pass_s,
+                         "frac_whole_step": V * N_COLS * b / (total_ms * 1e-3 / args.steps) / 1e9 / hbm_peak / world,
                          "bytes_per_update_design": design_bytes / (V * N_COLS),
                          "achieved_design_gbs": design_bytes / per_step_pass_s / 1e9},
             "e2e": {"value": e2e_val, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
