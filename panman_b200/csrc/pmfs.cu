@@ -27,7 +27,7 @@
 
 namespace pmfs {
 
-constexpr int kTPB = 256;  // threads (= column groups) per CTA
+constexpr int kTPB = 128;  // walking threads per CTA; each walks 2 column groups (kNG), so a CTA tile is 256 groups
 // A mutation record is ONE 64-bit word: sort key (node, column) in the high bits, payload in the low 10 bits
 // (type 2 bits, node state 4, parent state 4), so ordering the records is a keys-only radix sort over exactly the
 // key bits that can be set, and the multi-GPU exchange moves 8 bytes per record.
@@ -84,9 +84,8 @@ struct WalkParams {
 };
 
 // 64-word sliding window over a word array that every lane of the warp reads at the same, never decreasing index
-// (walk programs, load streams): lane l holds words base+l and base+32+l in two registers, a read is one shuffle, and
-// the next 32 words are fetched (one coalesced load per warp) a whole window before they are needed -- so fetching
-// the "instruction stream" never puts a memory round trip on the walk's critical path.
+// (load streams): lane l holds words base+l and base+32+l in two registers, a read is one shuffle, and the next 32
+// words are fetched (one coalesced load per warp) a whole window before they are needed.
 struct WarpWords {
     const uint32_t* base;
     int32_t len, wbase;
@@ -107,10 +106,15 @@ struct WarpWords {
     }
 };
 
-constexpr int kRingFwd = 8;   // ring units (one unit = one 16-byte load per thread = 2 KB per CTA) ahead of the bottom-up walk
-constexpr int kRingBwd = 8;   // top-down walk: a leaf takes 1 unit, an internal node's set 4
-constexpr int kThreads = kTPB + 32;  // 4 consumer warps walk the tree, 1 producer warp feeds them
-constexpr int kProgWords = 1024;     // walk programs up to this many words are staged in shared memory
+constexpr int kNG = 2;                    // column groups per walking thread (walk.cuh: Env::kGroups)
+constexpr int kTileGroups = kTPB * kNG;   // column groups per work item (256 groups = 8 192 columns)
+constexpr int kThreads = kTPB + 32;       // 4 walking warps + 1 producer warp
+constexpr int kLeafRing = 4;              // leaf-row units in flight (4 KB each: 16 B for each group of the tile)
+constexpr int kSetRingFwd = 1;            // set slots in flight (16 KB each: 64 B for each group), bottom-up pass
+constexpr int kSetRingBwd = 2;            // top-down pass: every internal node is one set
+constexpr int kProgWords = 256;           // walk programs up to this many words are staged in shared memory
+constexpr int kUnitBytes = kTileGroups * 16;
+constexpr int kSetBytes = kTileGroups * 64;
 
 // ---- mbarrier / bulk-copy (TMA) primitives, sm_90+ PTX ------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -127,9 +131,6 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// A wait that can never be satisfied (a bug in the producer/consumer bookkeeping) must not hang the GPU: after about
-// ten seconds of spinning the kernel traps and the host sees a CUDA error.
-constexpr long long kSpinLimitCycles = 20000000000ll;  // ~10 s
 // slow path: let the hardware park the thread (suspend-time hint) instead of burning issue slots the producer needs
 __device__ __forceinline__ bool mbar_try_park(uint32_t bar, uint32_t parity) {
     uint32_t ok;
@@ -142,6 +143,9 @@ __device__ __forceinline__ bool mbar_try_park(uint32_t bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// A wait that can never be satisfied (a bug in the producer/consumer bookkeeping) must not hang the GPU: after about
+// ten seconds of spinning the kernel traps and the host sees a CUDA error.
+constexpr long long kSpinLimitCycles = 20000000000ll;  // ~10 s
 __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
     const long long t0 = clock64();
     for (uint32_t it = 1; !mbar_try_park(bar, parity); it++)
@@ -168,19 +172,29 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
     return v;
 }
 
-// Shared-memory ring of one CTA, in UNITS of 2 KB (16 bytes for each of the kTPB column groups of the tile: one
-// contiguous segment of an MSA row or of a quarter-set row).  A load-stream entry takes 1 unit (leaf) or 4 consecutive
-// units modulo RING (the 4 quarters of a set).  full[u] flips when unit u's copy has landed, empty[u] when all 4
-// consumer warps have read it: every unit's two barriers complete exactly once per lap of the ring.  Unit numbers keep counting across the work items of a
-// persistent CTA, so barrier phases never need resetting.
-template <int RING>
-struct RingRefs {
-    uint32_t data, full, empty;  // shared-space addresses
-    uint32_t prog, prog_bar;     // 2 staged walk programs (kProgWords words each) + their barriers
-    uint32_t desc, desc_full, desc_empty;  // 2 item descriptors (int4) + their barriers
+// Shared-memory layout of one CTA (addresses in the shared window).  Two operand rings, both filled by the producer
+// warp with TMA bulk copies and drained by the 4 walking warps: LEAF units (one 4 KB segment of an MSA row: 16 bytes
+// for each of the tile's 256 column groups) and SET slots (one 16 KB block of the tile-major set array: the 4
+// quarter-sets of all 256 groups, a single contiguous copy).  Per ring entry: `full` flips when its bytes have
+// landed, `empty` when all 4 walking warps have read it.  Entry numbers keep counting across the work items of a
+// persistent CTA, so phases never need resetting.
+template <int SETS>
+struct SmemMap {
+    static constexpr int kProg = 0;                                 // 2 staged programs
+    static constexpr int kDesc = 2 * kProgWords * 4;                // 2 item descriptors (16 B each, 64 B reserved)
+    static constexpr int kLeaf = kDesc + 64;                        // leaf ring
+    static constexpr int kSet = kLeaf + kLeafRing * kUnitBytes;     // set ring
+    static constexpr int kStack = kSet + SETS * kSetBytes;          // walk stack (dynamic size)
+    // barriers (static shared array), 8 bytes each
+    static constexpr int bLeafFull = 0, bLeafEmpty = kLeafRing, bSetFull = 2 * kLeafRing, bSetEmpty = 2 * kLeafRing + SETS,
+                         bProg = 2 * kLeafRing + 2 * SETS, bDescFull = bProg + 2, bDescEmpty = bProg + 4, kBars = bProg + 6;
+};
+struct Ring {
+    uint32_t smem;  // shared address of the dynamic shared memory
+    uint32_t bars;  // shared address of the barrier array
 };
 
-// What the producer tells the consumers about a work item (one int4 in shared memory).
+// What the producer tells the walkers about a work item (one int4 in shared memory).
 struct ItemDesc {
     int32_t chunk;   // -1: no more items
     int32_t tile;
@@ -189,67 +203,88 @@ struct ItemDesc {
 };
 
 // Producer side of one item: stage the walk program into program buffer `slot`, then walk the chunk's load stream and
-// keep the ring full.  Called by the whole producer warp (the stream words are read warp-wide); lane 0 drives TMA.
-template <int RING>
-__device__ __forceinline__ void produce_stream(const WalkParams& p, const RingRefs<RING>& r, int32_t chunk, int tile,
-                                               int32_t plen, uint32_t slot, uint32_t& unit) {
+// keep both rings full.  Called by the whole producer warp (the stream words are read warp-wide); lane 0 drives TMA.
+template <int SETS>
+__device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& r, int32_t chunk, int tile, int32_t plen,
+                                               uint32_t slot, uint32_t& n_leaf, uint32_t& n_set) {
+    using M = SmemMap<SETS>;
     const int lane = threadIdx.x & 31;
     if (lane == 0 && plen <= kProgWords) {
         // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
         const uint32_t bytes = (uint32_t)((plen + 3) / 4) * 16u;
-        mbar_arrive_expect_tx(r.prog_bar + slot * 8, bytes);
-        bulk_g2s(r.prog + slot * (kProgWords * 4), p.prog + p.chunk_off[chunk], bytes, r.prog_bar + slot * 8);
+        mbar_arrive_expect_tx(r.bars + (M::bProg + slot) * 8, bytes);
+        bulk_g2s(r.smem + M::kProg + slot * (kProgWords * 4), p.prog + p.chunk_off[chunk], bytes, r.bars + (M::bProg + slot) * 8);
     }
     const int32_t slen = p.stream_len[chunk];
     WarpWords w;
     w.init(p.stream + p.stream_off[chunk], slen, lane);
-    const int64_t g0 = (int64_t)tile * kTPB;
-    const uint32_t bytes = (uint32_t)min((int64_t)kTPB, p.G - g0) * 16u;
+    const int64_t g0 = (int64_t)tile * kTileGroups;
+    const uint32_t leaf_bytes = (uint32_t)min((int64_t)kTileGroups, p.G - g0) * 16u;
     for (int32_t j = 0; j < slen; j++) {
         const uint32_t e = w.get(j, lane);
-        const uint32_t k = (e & kStreamSet) ? 4u : 1u;
-        if (lane == 0) {
-            const uint4* src = (e & kStreamSet) ? p.S + ((int64_t)(e & ~kStreamSet) * 4) * p.G + g0
-                                                : p.msa + (int64_t)e * p.msa_stride16 + g0;
-            for (uint32_t q = 0; q < k; q++) {
-                const uint32_t u = (unit + q) % RING, lap = (unit + q) / RING;
-                mbar_wait(r.empty + u * 8, (lap & 1u) ^ 1u);  // all consumers are done with the unit's previous content
-                mbar_arrive_expect_tx(r.full + u * 8, bytes);
-                bulk_g2s(r.data + u * (kTPB * 16), src + (int64_t)q * p.G, bytes, r.full + u * 8);
+        if (e & kStreamSet) {
+            if (lane == 0) {
+                const uint32_t u = n_set % SETS, par = (n_set / SETS) & 1u;
+                mbar_wait(r.bars + (M::bSetEmpty + u) * 8, par ^ 1u);  // all walkers are done with the slot's previous set
+                mbar_arrive_expect_tx(r.bars + (M::bSetFull + u) * 8, kSetBytes);
+                bulk_g2s(r.smem + M::kSet + u * kSetBytes,
+                         p.S + ((int64_t)(e & ~kStreamSet) * p.ctas_per_chunk + tile) * (kSetBytes / 16), kSetBytes,
+                         r.bars + (M::bSetFull + u) * 8);
             }
+            n_set++;
+        } else {
+            if (lane == 0) {
+                const uint32_t u = n_leaf % kLeafRing, par = (n_leaf / kLeafRing) & 1u;
+                mbar_wait(r.bars + (M::bLeafEmpty + u) * 8, par ^ 1u);
+                mbar_arrive_expect_tx(r.bars + (M::bLeafFull + u) * 8, leaf_bytes);
+                bulk_g2s(r.smem + M::kLeaf + u * kUnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
+                         r.bars + (M::bLeafFull + u) * 8);
+            }
+            n_leaf++;
         }
-        unit += k;
     }
 }
 
-// Per-thread view of one (chunk, column group) for the 4 consumer warps.  Global loads whose addresses are known from
-// the plan (leaf rows, sets written by earlier work items) never go through the walking threads: the producer warp
-// streams them through the shared-memory ring with TMA bulk copies, so a walk reads its operands from shared memory
-// and only waits on an mbarrier that has normally completed long before.  The walk program itself is staged in shared
-// memory the same way.
-template <bool READONLY_SETS, int RING>
+// Per-thread view of one work item for the 4 walking warps: thread t walks column groups tile*256 + t and
+// tile*256 + 128 + t.  Operands whose addresses are known from the plan (leaf rows, sets written by earlier work
+// items) never go through the walking threads: the producer warp streams them through the shared-memory rings with TMA
+// bulk copies, so a walk reads its operands from shared memory and only waits on an mbarrier that has normally
+// completed long before.  The walk program itself is staged in shared memory the same way.
+// Set arrays are TILE-MAJOR: S[internal id][tile][quarter][256 groups] (uint4), so one node's set for one tile is a
+// single contiguous 16 KB block (one TMA copy) and a warp's 128-bit stores are 512-byte segments.
+template <bool READONLY_SETS, int SETS>
 struct DevEnv {
+    static constexpr int kGroups = kNG;
+    using M = SmemMap<SETS>;
     const WalkParams& p;
-    int64_t g;      // clamped column group
-    int64_t gwarp;  // (unclamped) column group of this warp's lane 0
-    bool active;
-    RingRefs<RING> ring;
-    uint32_t& unit;   // running ring-unit number of this CTA (same sequence as the producer's)
-    uint4* fstk;      // [depth][4][kTPB]
-    uint32_t* bstk;   // [depth][5][kTPB]
+    const Ring& ring;
+    int64_t g[kNG];      // clamped column groups
+    bool active[kNG];
+    int64_t gwarp;       // (unclamped) column group of this warp's lane 0, first group slot
+    int64_t set_tile;    // uint4 offset of this tile inside one node's set rows: tile * 1024
+    uint32_t& n_leaf;    // running ring entry numbers of this CTA (same sequences as the producer's)
+    uint32_t& n_set;
+    uint4* fstk;         // [depth][kNG][4][kTPB]
+    uint32_t* bstk;      // [depth][kNG][5][kTPB]
     int sp = 0;
     int lane;
     bool prog_staged;
     const uint32_t* gprog;
+    uint32_t sprog;      // shared address of this item's staged program
 
-    uint32_t sprog;  // shared address of this item's staged program
-
-    __device__ DevEnv(const WalkParams& p_, int64_t g_, int64_t g_unclamped, bool a, const RingRefs<RING>& r, uint32_t& unit_,
-                      void* stack, const ItemDesc& d, uint32_t slot, uint32_t prog_parity)
-        : p(p_), g(g_), gwarp(g_unclamped - (threadIdx.x & 31)), active(a), ring(r), unit(unit_), fstk((uint4*)stack),
-          bstk((uint32_t*)stack), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords), gprog(nullptr),
-          sprog(r.prog + slot * (kProgWords * 4)) {
-        if (prog_staged) mbar_wait(ring.prog_bar + slot * 8, prog_parity);
+    __device__ DevEnv(const WalkParams& p_, const Ring& r, const ItemDesc& d, uint32_t slot, uint32_t prog_parity,
+                      uint32_t& n_leaf_, uint32_t& n_set_, void* smem_generic)
+        : p(p_), ring(r), gwarp((int64_t)d.tile * kTileGroups + (threadIdx.x & ~31)), set_tile((int64_t)d.tile * (kSetBytes / 16)),
+          n_leaf(n_leaf_), n_set(n_set_), fstk((uint4*)((char*)smem_generic + M::kStack)),
+          bstk((uint32_t*)((char*)smem_generic + M::kStack)), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords),
+          gprog(nullptr), sprog(r.smem + M::kProg + slot * (kProgWords * 4)) {
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            const int64_t gj = (int64_t)d.tile * kTileGroups + j * kTPB + threadIdx.x;
+            active[j] = gj < p_.G;
+            g[j] = active[j] ? gj : p_.G - 1;
+        }
+        if (prog_staged) mbar_wait(r.bars + (M::bProg + slot) * 8, prog_parity);
         else gprog = p_.prog + p_.chunk_off[d.chunk];
     }
 
@@ -262,96 +297,109 @@ struct DevEnv {
         return __ldg(gprog + pc);  // very long programs (huge polytomies): straight from L1/L2
     }
 
-    // next ring entry of k units: wait until the TMA copies have landed, read this thread's 16 bytes of each unit,
-    // hand the units back
-    template <int K>
-    __device__ __forceinline__ void next(uint4 (&v)[K]) {
-        bool ok[K];
+    // next leaf unit: wait until the TMA copy has landed, read this thread's 16 bytes per group, hand the unit back
+    __device__ __forceinline__ void leaf(uint32_t, uint4 (&w)[kNG]) {
+        const uint32_t u = n_leaf % kLeafRing, par = (n_leaf / kLeafRing) & 1u;
+        mbar_wait(ring.bars + (M::bLeafFull + u) * 8, par);
+        const uint32_t base = ring.smem + M::kLeaf + u * kUnitBytes + threadIdx.x * 16;
 #pragma unroll
-        for (int q = 0; q < K; q++)  // all K barrier tests in flight at once (a test takes ~90 cycles to answer)
-            ok[q] = mbar_try(ring.full + ((unit + q) % RING) * 8, ((unit + q) / RING) & 1u);
-#pragma unroll
-        for (int q = 0; q < K; q++) {
-            const uint32_t u = (unit + q) % RING;
-            if (!ok[q]) mbar_wait_slow(ring.full + u * 8, ((unit + q) / RING) & 1u);
-            v[q] = lds128(ring.data + u * (kTPB * 16) + threadIdx.x * 16);
-        }
+        for (int j = 0; j < kNG; j++) w[j] = lds128(base + j * (kTPB * 16));
         __syncwarp();
-        if (lane == 0) {
-#pragma unroll
-            for (int q = 0; q < K; q++) mbar_arrive(ring.empty + ((unit + q) % RING) * 8);
-        }
-        unit += K;
+        if (lane == 0) mbar_arrive(ring.bars + (M::bLeafEmpty + u) * 8);
+        n_leaf++;
     }
-    __device__ __forceinline__ uint4 leaf(uint32_t) {
-        uint4 v[1];
-        next<1>(v);
-        return v[0];
-    }
-    __device__ __forceinline__ void load_x(uint32_t, Planes16& s) {
-        uint4 v[4];
-        next<4>(v);
+    // next set slot (a set written by an earlier work item): 4 quarters x kNG groups
+    __device__ __forceinline__ void load_x(uint32_t, Planes16 (&s)[kNG]) {
+        const uint32_t u = n_set % SETS, par = (n_set / SETS) & 1u;
+        mbar_wait(ring.bars + (M::bSetFull + u) * 8, par);
+        const uint32_t base = ring.smem + M::kSet + u * kSetBytes + threadIdx.x * 16;
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            s.p[4 * i] = v[i].x; s.p[4 * i + 1] = v[i].y; s.p[4 * i + 2] = v[i].z; s.p[4 * i + 3] = v[i].w;
-        }
+        for (int j = 0; j < kNG; j++)
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint4 v = lds128(base + (i * kTileGroups + j * kTPB) * 16);
+                s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
+            }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(ring.bars + (M::bSetEmpty + u) * 8);
+        n_set++;
     }
 
-    __device__ __forceinline__ void load_arr(const uint4* base, uint32_t id, Planes16& s) const {
-        const uint4* q = base + ((int64_t)id * 4) * p.G + g;
+    // direct access to the set arrays (sets of this work item itself; Sankoff D1 on the slow path)
+    __device__ __forceinline__ int64_t set_index(uint32_t id, int j, int i) const {
+        return ((int64_t)id * p.ctas_per_chunk) * (kSetBytes / 16) + set_tile + i * kTileGroups + j * kTPB + threadIdx.x;
+    }
+    __device__ __forceinline__ void load_arr(const uint4* base, uint32_t id, Planes16 (&s)[kNG]) const {
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            uint4 v = READONLY_SETS ? __ldg(q + (int64_t)i * p.G) : q[(int64_t)i * p.G];
-            s.p[4 * i] = v.x; s.p[4 * i + 1] = v.y; s.p[4 * i + 2] = v.z; s.p[4 * i + 3] = v.w;
+        for (int j = 0; j < kNG; j++)
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint4* q = base + set_index(id, j, i);
+                const uint4 v = READONLY_SETS ? __ldg(q) : *q;
+                s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
+            }
+    }
+    __device__ __forceinline__ void store_arr(uint4* base, uint32_t id, const Planes16 (&s)[kNG]) const {
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            if (!active[j]) continue;
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                base[set_index(id, j, i)] = make_uint4(s[j].p[4 * i], s[j].p[4 * i + 1], s[j].p[4 * i + 2], s[j].p[4 * i + 3]);
         }
     }
-    __device__ __forceinline__ void store_arr(uint4* base, uint32_t id, const Planes16& s) const {
-#ifdef PMFS_EXP_NOSTORE
-        if (s.p[0] != 0x12345678u) return;  // timing experiment only: keeps the computation alive, drops the stores
-#endif
-        if (!active) return;
-        uint4* q = base + ((int64_t)id * 4) * p.G + g;
-#pragma unroll
-        for (int i = 0; i < 4; i++) q[(int64_t)i * p.G] = make_uint4(s.p[4 * i], s.p[4 * i + 1], s.p[4 * i + 2], s.p[4 * i + 3]);
-    }
-    __device__ __forceinline__ void load_s(uint32_t id, Planes16& s) const { load_arr(p.S, id, s); }
-    __device__ __forceinline__ void load_d(uint32_t id, Planes16& s) const { load_arr(p.D, id, s); }
-    __device__ __forceinline__ void store_s(uint32_t id, const Planes16& s) const { store_arr(p.S, id, s); }
-    __device__ __forceinline__ void store_d(uint32_t id, const Planes16& s) const { store_arr(p.D, id, s); }
+    __device__ __forceinline__ void load_s(uint32_t id, Planes16 (&s)[kNG]) const { load_arr(p.S, id, s); }
+    __device__ __forceinline__ void load_d(uint32_t id, Planes16 (&s)[kNG]) const { load_arr(p.D, id, s); }
+    __device__ __forceinline__ void store_s(uint32_t id, const Planes16 (&s)[kNG]) const { store_arr(p.S, id, s); }
+    __device__ __forceinline__ void store_d(uint32_t id, const Planes16 (&s)[kNG]) const { store_arr(p.D, id, s); }
 
-    __device__ __forceinline__ void push(const Planes16& s) {
-        uint4* q = fstk + (sp * 4) * kTPB + threadIdx.x;
+    __device__ __forceinline__ void push(const Planes16 (&s)[kNG]) {
+        uint4* q = fstk + (sp * kNG * 4) * kTPB + threadIdx.x;
 #pragma unroll
-        for (int i = 0; i < 4; i++) q[i * kTPB] = make_uint4(s.p[4 * i], s.p[4 * i + 1], s.p[4 * i + 2], s.p[4 * i + 3]);
+        for (int j = 0; j < kNG; j++)
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                q[(j * 4 + i) * kTPB] = make_uint4(s[j].p[4 * i], s[j].p[4 * i + 1], s[j].p[4 * i + 2], s[j].p[4 * i + 3]);
         sp++;
     }
-    __device__ __forceinline__ void pop(Planes16& s) {
+    __device__ __forceinline__ void pop(Planes16 (&s)[kNG]) {
         sp--;
-        const uint4* q = fstk + (sp * 4) * kTPB + threadIdx.x;
+        const uint4* q = fstk + (sp * kNG * 4) * kTPB + threadIdx.x;
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            uint4 v = q[i * kTPB];
-            s.p[4 * i] = v.x; s.p[4 * i + 1] = v.y; s.p[4 * i + 2] = v.z; s.p[4 * i + 3] = v.w;
+        for (int j = 0; j < kNG; j++)
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint4 v = q[(j * 4 + i) * kTPB];
+                s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
+            }
+    }
+    __device__ __forceinline__ void pushp(const Code4 (&c)[kNG], const uint32_t (&pv)[kNG]) {
+        uint32_t* q = bstk + (sp * kNG * 5) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) q[(j * 5 + i) * kTPB] = c[j].b[i];
+            q[(j * 5 + 4) * kTPB] = pv[j];
+        }
+        sp++;
+    }
+    __device__ __forceinline__ void popp(Code4 (&c)[kNG], uint32_t (&pv)[kNG]) {
+        sp--;
+        const uint32_t* q = bstk + (sp * kNG * 5) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) c[j].b[i] = q[(j * 5 + i) * kTPB];
+            pv[j] = q[(j * 5 + 4) * kTPB];
         }
     }
-    __device__ __forceinline__ void pushp(const Code4& c, uint32_t pv) {
-        uint32_t* q = bstk + (sp * 5) * kTPB + threadIdx.x;
+    __device__ __forceinline__ void store_x(uint32_t chunk, const Code4 (&c)[kNG], const uint32_t (&pv)[kNG]) const {
 #pragma unroll
-        for (int i = 0; i < 4; i++) q[i * kTPB] = c.b[i];
-        q[4 * kTPB] = pv;
-        sp++;
-    }
-    __device__ __forceinline__ void popp(Code4& c, uint32_t& pv) {
-        sp--;
-        const uint32_t* q = bstk + (sp * 5) * kTPB + threadIdx.x;
-#pragma unroll
-        for (int i = 0; i < 4; i++) c.b[i] = q[i * kTPB];
-        pv = q[4 * kTPB];
-    }
-    __device__ __forceinline__ void store_x(uint32_t chunk, const Code4& c, uint32_t pv) const {
-        if (!active) return;
-        p.xcode[(int64_t)chunk * p.G + g] = make_uint4(c.b[0], c.b[1], c.b[2], c.b[3]);
-        p.xvalid[(int64_t)chunk * p.G + g] = pv;
+        for (int j = 0; j < kNG; j++) {
+            if (!active[j]) continue;
+            p.xcode[(int64_t)chunk * p.G + g[j]] = make_uint4(c[j].b[0], c[j].b[1], c[j].b[2], c[j].b[3]);
+            p.xvalid[(int64_t)chunk * p.G + g[j]] = pv[j];
+        }
     }
     __device__ __forceinline__ bool any(bool x) const { return __any_sync(0xffffffffu, x); }
 
@@ -360,17 +408,11 @@ struct DevEnv {
     // mutations, its mask and planes are broadcast and each lane of the warp writes the record of "its" bit -- a block of
     // 32 N's costs the same ~40 instructions as a single substitution, and the stores are coalesced.  The order inside
     // the buffer depends on scheduling; the final radix sort by (node,pos) makes the result deterministic.
-    __device__ void emit(uint32_t node, uint32_t m, const Code4& G, const Code4& P) const {
+    __device__ void emit1(uint32_t node, unsigned long long* out, unsigned long long& base, uint32_t m, const Code4& G,
+                          const Code4& P, int64_t gw) const {
         const unsigned full = 0xffffffffu;
-        const uint32_t total = __reduce_add_sync(full, (uint32_t)__popc(m));
-        int own = 0;  // owner of this node's list (column shards); uniform across the warp
-        for (int r = 1; r < p.n_owners; r++) own += (int32_t)node >= p.owner_bound[r];
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(p.out_count + own, (unsigned long long)total);
-        base = __shfl_sync(full, base, 0);
-        unsigned long long* out = p.out_keys + (unsigned long long)own * p.out_cap;
         uint32_t srcs = __ballot_sync(full, m != 0);
-        const unsigned long long pos0 = (unsigned long long)(p.pos_offset + p.col_base + gwarp * 32 + column_of_bit(lane));
+        const unsigned long long pos0 = (unsigned long long)(p.pos_offset + p.col_base + gw * 32 + column_of_bit(lane));
         while (srcs) {
             const int src = __ffs(srcs) - 1;
             srcs &= srcs - 1;
@@ -393,10 +435,24 @@ struct DevEnv {
             base += __popc(mm);
         }
     }
-    __device__ __forceinline__ void emit_internal(uint32_t id, uint32_t m, const Code4& G, const Code4& P) const {
+    __device__ void emit(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+        uint32_t cnt = 0;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) cnt += __popc(m[j]);
+        const uint32_t total = __reduce_add_sync(0xffffffffu, cnt);
+        int own = 0;  // owner of this node's list (column shards); uniform across the warp
+        for (int r = 1; r < p.n_owners; r++) own += (int32_t)node >= p.owner_bound[r];
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(p.out_count + own, (unsigned long long)total);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        unsigned long long* out = p.out_keys + (unsigned long long)own * p.out_cap;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) emit1(node, out, base, m[j], G[j], P[j], gwarp + j * kTPB);
+    }
+    __device__ __forceinline__ void emit_internal(uint32_t id, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
         emit((uint32_t)__ldg(p.int_to_node + id), m, G, P);
     }
-    __device__ __forceinline__ void emit_leaf(uint32_t row, uint32_t m, const Code4& G, const Code4& P) const {
+    __device__ __forceinline__ void emit_leaf(uint32_t row, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
         emit((uint32_t)__ldg(p.row_to_node + row), m, G, P);
     }
 };
@@ -410,7 +466,7 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
     return m;
 }
 
-// Work item = (chunk, column tile of kTPB groups).  One launch per pass: persistent CTAs claim items from a global
+// Work item = (chunk, column tile of 256 groups).  One launch per pass: persistent CTAs claim items from a global
 // counter in plan order (bottom-up: chunk height ascending; top-down: chunk depth ascending), so everything an item
 // depends on has a smaller index and was claimed earlier by a CTA that is already running -- waiting on it cannot
 // deadlock, whatever the number of resident CTAs.  Dependencies are per column tile (tile t of a chunk needs only tile
@@ -418,51 +474,49 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
 // and no per-level launch, so narrow levels near the root overlap with wide ones instead of leaving the GPU idle.
 //
 // Inside a CTA the producer warp runs AHEAD of the four walking warps, across item boundaries: while they finish item
-// n it has already claimed item n+1, waited for its dependencies, staged its program and started filling the ring
+// n it has already claimed item n+1, waited for its dependencies, staged its program and started filling the rings
 // with its operands, so the walkers go from one item to the next without seeing the claim / dependency / staging
-// latencies (a few microseconds, as much as a small item itself takes).  Item descriptors and programs are double
-// buffered; all hand-overs are mbarriers, the kernels contain no CTA-wide barrier after set-up.
+// latencies.  Item descriptors and programs are double buffered; all hand-overs are mbarriers, the kernels contain no
+// CTA-wide barrier after set-up.
 constexpr int kPassFwd = 0, kPassBwd = 1;
 
-template <int RING>
-__device__ __forceinline__ RingRefs<RING> ring_setup(void* smem, unsigned long long* bars) {
-    RingRefs<RING> r;  // dynamic smem: [2 programs of kProgWords words][2 descriptors][ring RING x 2 KB][walk stack]
-    r.prog = (uint32_t)__cvta_generic_to_shared(smem);
-    r.desc = r.prog + 2 * kProgWords * 4;
-    r.data = r.desc + 64;
-    r.full = (uint32_t)__cvta_generic_to_shared(bars);
-    r.empty = r.full + RING * 8;
-    r.prog_bar = r.empty + RING * 8;
-    r.desc_full = r.prog_bar + 16;
-    r.desc_empty = r.desc_full + 16;
+template <int SETS>
+__device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars) {
+    using M = SmemMap<SETS>;
+    Ring r;
+    r.smem = (uint32_t)__cvta_generic_to_shared(smem);
+    r.bars = (uint32_t)__cvta_generic_to_shared(bars);
     if (threadIdx.x == 0) {
-        for (int i = 0; i < RING; i++) {
-            mbar_init(r.full + i * 8, 1);          // one arrive.expect_tx by the producer
-            mbar_init(r.empty + i * 8, kTPB / 32);  // one arrive per consumer warp
+        for (int i = 0; i < kLeafRing; i++) {
+            mbar_init(r.bars + (M::bLeafFull + i) * 8, 1);           // one arrive.expect_tx by the producer
+            mbar_init(r.bars + (M::bLeafEmpty + i) * 8, kTPB / 32);  // one arrive per walking warp
+        }
+        for (int i = 0; i < SETS; i++) {
+            mbar_init(r.bars + (M::bSetFull + i) * 8, 1);
+            mbar_init(r.bars + (M::bSetEmpty + i) * 8, kTPB / 32);
         }
         for (int i = 0; i < 2; i++) {
-            mbar_init(r.prog_bar + i * 8, 1);
-            mbar_init(r.desc_full + i * 8, 1);
-            mbar_init(r.desc_empty + i * 8, kTPB / 32);
+            mbar_init(r.bars + (M::bProg + i) * 8, 1);
+            mbar_init(r.bars + (M::bDescFull + i) * 8, 1);
+            mbar_init(r.bars + (M::bDescEmpty + i) * 8, kTPB / 32);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     return r;
 }
-constexpr int kSmemHeadWords = 2 * kProgWords + 16;  // programs + descriptors, in 32-bit words (multiple of 4)
-constexpr int kNumBars(int ring) { return 2 * ring + 6; }
 
 // Producer warp: claim -> dependency -> descriptor -> program + operand stream, item after item.
-template <int PASS, int RING>
-__device__ __forceinline__ void producer_loop(const WalkParams& p, const RingRefs<RING>& r) {
+template <int PASS, int SETS>
+__device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r) {
+    using M = SmemMap<SETS>;
     const int lane = threadIdx.x & 31;
-    uint32_t unit = 0;
+    uint32_t n_leaf = 0, n_set = 0;
     for (uint32_t n = 0;; n++) {
         const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
         int32_t chunk = -1, tile = 0, plen = 0, parent = -1;
         if (lane == 0) {
-            mbar_wait(r.desc_empty + slot * 8, phase ^ 1u);  // the walkers are done with item n-2 (descriptor + program)
+            mbar_wait(r.bars + (M::bDescEmpty + slot) * 8, phase ^ 1u);  // the walkers are done with item n-2
             const int item = atomicAdd(p.next_item, 1);
             if (item < p.n_items) {
                 chunk = p.order[item / p.ctas_per_chunk];
@@ -482,24 +536,29 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const RingRef
                 __threadfence();
                 asm volatile("fence.proxy.async;" ::: "memory");  // data written by other CTAs is read by the TMA engine
             }
-            asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.desc + slot * 16), "r"(chunk), "r"(tile), "r"(plen), "r"(parent)
+            asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.smem + M::kDesc + slot * 16), "r"(chunk), "r"(tile), "r"(plen),
+                         "r"(parent)
                          : "memory");
-            mbar_arrive(r.desc_full + slot * 8);
+            mbar_arrive(r.bars + (M::bDescFull + slot) * 8);
         }
         chunk = __shfl_sync(0xffffffffu, chunk, 0);
         if (chunk < 0) return;
         tile = __shfl_sync(0xffffffffu, tile, 0);
         plen = __shfl_sync(0xffffffffu, plen, 0);
-        produce_stream<RING>(p, r, chunk, tile, plen, slot, unit);
+        produce_stream<SETS>(p, r, chunk, tile, plen, slot, n_leaf, n_set);
     }
 }
 
 // Walking warps: take the next descriptor; returns false when there is no more work.
-template <int RING>
-__device__ __forceinline__ bool next_item(const RingRefs<RING>& r, uint32_t n, ItemDesc& d) {
+template <int SETS>
+__device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d) {
+    using M = SmemMap<SETS>;
     const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
-    mbar_wait(r.desc_full + slot * 8, phase);
-    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(d.chunk), "=r"(d.tile), "=r"(d.plen), "=r"(d.parent) : "r"(r.desc + slot * 16) : "memory");
+    mbar_wait(r.bars + (M::bDescFull + slot) * 8, phase);
+    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(d.chunk), "=r"(d.tile), "=r"(d.plen), "=r"(d.parent)
+                 : "r"(r.smem + M::kDesc + slot * 16)
+                 : "memory");
     return d.chunk >= 0;
 }
 // Item finished: publish it to dependants (all walkers' stores first), then free the descriptor/program slot.
@@ -515,77 +574,81 @@ __device__ __forceinline__ void finish_item(int* counter, uint32_t desc_empty_ba
 
 template <int ALGO, bool POLY>
 __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
+    using M = SmemMap<kSetRingFwd>;
     extern __shared__ uint4 smem[];
-    __shared__ __align__(8) unsigned long long bars[kNumBars(kRingFwd)];
-    const RingRefs<kRingFwd> ring = ring_setup<kRingFwd>(smem, bars);
+    __shared__ __align__(8) unsigned long long bars[M::kBars];
+    const Ring ring = ring_setup<kSetRingFwd>(smem, bars);
     if (threadIdx.x >= kTPB) {
-        producer_loop<kPassFwd, kRingFwd>(p, ring);
+        producer_loop<kPassFwd, kSetRingFwd>(p, ring);
         return;
     }
-    uint32_t unit = 0, staged[2] = {0, 0};
+    uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
     ItemDesc d;
-    for (uint32_t n = 0; next_item(ring, n, d); n++) {
+    for (uint32_t n = 0; next_item<kSetRingFwd>(ring, n, d); n++) {
         const uint32_t slot = n & 1u;
-        const int64_t g0 = (int64_t)d.tile * kTPB + threadIdx.x;
-        const bool active = g0 < p.G;
-        const int64_t g = active ? g0 : p.G - 1;
         {
-            DevEnv<false, kRingFwd> env(p, g, g0, active, ring, unit, smem + kSmemHeadWords / 4 + kRingFwd * kTPB, d, slot, staged[slot] & 1u);
-            Code4 forced;
+            DevEnv<false, kSetRingFwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            Code4 forced[kNG];
             const Code4* fp = nullptr;
             if (ALGO == kAlgoFitch && p.forced_planes) {
-                uint4 v = __ldg(p.forced_planes + g);
-                forced.b[0] = v.x; forced.b[1] = v.y; forced.b[2] = v.z; forced.b[3] = v.w;
-                fp = &forced;
+#pragma unroll
+                for (int j = 0; j < kNG; j++) {
+                    const uint4 v = __ldg(p.forced_planes + env.g[j]);
+                    forced[j].b[0] = v.x; forced[j].b[1] = v.y; forced[j].b[2] = v.z; forced[j].b[3] = v.w;
+                }
+                fp = forced;
             }
             forward_walk<ALGO, POLY>(env, nullptr, d.plen, fp);
         }
         if (d.plen <= kProgWords) staged[slot]++;
-        finish_item(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr, ring.desc_empty + slot * 8);
+        finish_item(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr,
+                    ring.bars + (M::bDescEmpty + slot) * 8);
     }
 }
 
 template <int ALGO>
 __global__ void __launch_bounds__(kThreads) bwd_kernel(const WalkParams p) {
+    using M = SmemMap<kSetRingBwd>;
     extern __shared__ uint4 smem[];
-    __shared__ __align__(8) unsigned long long bars[kNumBars(kRingBwd)];
-    const RingRefs<kRingBwd> ring = ring_setup<kRingBwd>(smem, bars);
+    __shared__ __align__(8) unsigned long long bars[M::kBars];
+    const Ring ring = ring_setup<kSetRingBwd>(smem, bars);
     if (threadIdx.x >= kTPB) {
-        producer_loop<kPassBwd, kRingBwd>(p, ring);
+        producer_loop<kPassBwd, kSetRingBwd>(p, ring);
         return;
     }
-    uint32_t unit = 0, staged[2] = {0, 0};
+    uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
     ItemDesc d;
-    for (uint32_t n = 0; next_item(ring, n, d); n++) {
+    for (uint32_t n = 0; next_item<kSetRingBwd>(ring, n, d); n++) {
         const uint32_t slot = n & 1u;
-        const int64_t g0 = (int64_t)d.tile * kTPB + threadIdx.x;
-        const bool active = g0 < p.G;
-        const int64_t g = active ? g0 : p.G - 1;
         uint32_t err;
         {
-            DevEnv<true, kRingBwd> env(p, g, g0, active, ring, unit, smem + kSmemHeadWords / 4 + kRingBwd * kTPB, d, slot, staged[slot] & 1u);
-            Code4 P, forced;
-            uint32_t pv = ~0u;
+            DevEnv<true, kSetRingBwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            Code4 P[kNG], forced[kNG];
+            uint32_t pv[kNG], colmask[kNG];
             const Code4* fp = nullptr;
-            if (d.chunk == 0) {
-                uint4 v = __ldg(p.cons_planes + g);
-                P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
-                if (ALGO == kAlgoSankoff && p.forced_planes) {
-                    uint4 f = __ldg(p.forced_planes + g);
-                    forced.b[0] = f.x; forced.b[1] = f.y; forced.b[2] = f.z; forced.b[3] = f.w;
-                    fp = &forced;
+#pragma unroll
+            for (int j = 0; j < kNG; j++) {
+                pv[j] = ~0u;
+                if (d.chunk == 0) {
+                    const uint4 v = __ldg(p.cons_planes + env.g[j]);
+                    P[j].b[0] = v.x; P[j].b[1] = v.y; P[j].b[2] = v.z; P[j].b[3] = v.w;
+                    if (ALGO == kAlgoSankoff && p.forced_planes) {
+                        const uint4 f = __ldg(p.forced_planes + env.g[j]);
+                        forced[j].b[0] = f.x; forced[j].b[1] = f.y; forced[j].b[2] = f.z; forced[j].b[3] = f.w;
+                        fp = forced;
+                    }
+                } else {  // written by another SM during this launch: read through L2
+                    const uint4 v = __ldcg(p.xcode + (int64_t)d.chunk * p.G + env.g[j]);
+                    P[j].b[0] = v.x; P[j].b[1] = v.y; P[j].b[2] = v.z; P[j].b[3] = v.w;
+                    pv[j] = __ldcg(p.xvalid + (int64_t)d.chunk * p.G + env.g[j]);
                 }
-            } else {  // written by another SM during this launch: read through L2
-                uint4 v = __ldcg(p.xcode + (int64_t)d.chunk * p.G + g);
-                P.b[0] = v.x; P.b[1] = v.y; P.b[2] = v.z; P.b[3] = v.w;
-                pv = __ldcg(p.xvalid + (int64_t)d.chunk * p.G + g);
+                colmask[j] = env.active[j] ? real_column_mask(env.g[j], p.tile_cols) : 0u;
             }
-            const uint32_t colmask = active ? real_column_mask(g, p.tile_cols) : 0u;
             err = backward_walk<ALGO>(env, nullptr, d.plen, P, pv, fp, colmask);
         }
         if (err) atomicOr(p.err_flag, 1u);
         if (d.plen <= kProgWords) staged[slot]++;
-        finish_item(p.ready + (int64_t)d.chunk * p.ctas_per_chunk + d.tile, ring.desc_empty + slot * 8);
+        finish_item(p.ready + (int64_t)d.chunk * p.ctas_per_chunk + d.tile, ring.bars + (M::bDescEmpty + slot) * 8);
     }
 }
 
@@ -875,7 +938,7 @@ static int replan(pmfs_ctx* c, int32_t chunk_nodes) {
 // so chunks are kept small (short items, short chains) as long as every item still amortises its fixed cost (claim,
 // dependency check, program staging: a few microseconds) -- measured optimum on BASELINE config 2: 24..64 nodes.
 static int32_t auto_chunk_nodes(int32_t n_nodes, int64_t groups) {
-    int64_t ctas_per_chunk = (groups + kTPB - 1) / kTPB;
+    int64_t ctas_per_chunk = (groups + kTileGroups - 1) / kTileGroups;
     int64_t want_chunks = std::max<int64_t>(1, (148 * 24 + ctas_per_chunk - 1) / ctas_per_chunk);
     int64_t cn = n_nodes / (want_chunks * 2);  // chunks end up between cn and 2*cn nodes
     return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 24), 1 << 16);
@@ -1001,7 +1064,7 @@ int pmfs_get_timing(pmfs_ctx* c, pmfs_timing* t) {
 // ---------------------------------------------------------------------------------------------------- the pipeline
 // ints of synchronisation scratch a pass needs for `groups` column groups: claim counters + per-(chunk,tile) counters
 static size_t sync_ints(const Plan& P, int64_t groups) {
-    return 64 + 2 * P.chunks.size() * (size_t)((groups + kTPB - 1) / kTPB);
+    return 64 + 2 * P.chunks.size() * (size_t)((groups + kTileGroups - 1) / kTileGroups);
 }
 
 // One launch per pass over all chunks (the name is historical: the first version launched once per chunk level).
@@ -1018,7 +1081,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     wp.order = fwd ? c->d_fwd_order.ptr : c->d_bwd_order.ptr;
     wp.chunk_parent = c->d_chunk_parent.ptr;
     wp.chunk_nchild = c->d_chunk_nchild.ptr;
-    wp.ctas_per_chunk = (int32_t)((wp.G + kTPB - 1) / kTPB);
+    wp.ctas_per_chunk = (int32_t)((wp.G + kTileGroups - 1) / kTileGroups);
     wp.stack_depth = fwd ? P.fwd_stack_depth : P.bwd_stack_depth;
     const int64_t n_items = (int64_t)P.chunks.size() * wp.ctas_per_chunk;
     if (n_items > 0x7fffffffll) {
@@ -1030,9 +1093,8 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     const size_t per_pass = (size_t)n_items;
     wp.next_item = sync + (fwd ? 0 : 32);
     wp.ready = sync + 64 + (fwd ? 0 : per_pass);
-    const size_t smem = (size_t)kSmemHeadWords * 4 +
-                        (fwd ? ((size_t)kRingFwd + (size_t)P.fwd_stack_depth * 4) * kTPB * sizeof(uint4)
-                             : (size_t)kRingBwd * kTPB * sizeof(uint4) + (size_t)P.bwd_stack_depth * 5 * kTPB * sizeof(uint32_t));
+    const size_t smem = fwd ? (size_t)SmemMap<kSetRingFwd>::kStack + (size_t)P.fwd_stack_depth * kNG * 4 * kTPB * sizeof(uint4)
+                            : (size_t)SmemMap<kSetRingBwd>::kStack + (size_t)P.bwd_stack_depth * kNG * 5 * kTPB * sizeof(uint32_t);
     if (smem > 200 * 1024) {
         g_error = "walk stack does not fit in shared memory (tree too unbalanced for this chunk size)";
         return PMFS_ERR_ARG;
@@ -1085,7 +1147,10 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     // column tile so that the set arrays fit in HBM
     const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64;
     int64_t tile_groups = G_all;
-    const bool fits_already = c->d_S.cap >= (size_t)I * 4 * G_all && (algo != PMFS_SANKOFF || c->d_D.cap >= (size_t)I * 4 * G_all);
+    auto set_elems = [&](int64_t groups) {  // uint4 elements of one tile-major set array for `groups` column groups
+        return (size_t)I * (size_t)((groups + kTileGroups - 1) / kTileGroups) * (kSetBytes / 16);
+    };
+    const bool fits_already = c->d_S.cap >= set_elems(G_all) && (algo != PMFS_SANKOFF || c->d_D.cap >= set_elems(G_all));
     if (!fits_already) {  // (cudaMemGetInfo costs a fraction of a millisecond: only ask when buffers have to grow)
         size_t free_b = 0, total_b = 0;
         PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
@@ -1094,7 +1159,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     }
     if (c->tune_tile_cols > 0) tile_groups = std::min<int64_t>(tile_groups, (c->tune_tile_cols + 31) / 32);
     tile_groups = std::min(tile_groups, G_all);
-    if (tile_groups < G_all) tile_groups = std::max<int64_t>(kTPB, tile_groups / kTPB * kTPB);
+    if (tile_groups < G_all) tile_groups = std::max<int64_t>(kTileGroups, tile_groups / kTileGroups * kTileGroups);
     tile_groups = std::min(tile_groups, G_all);
 
     const int32_t want_chunk = c->tune_chunk_nodes > 0 ? c->tune_chunk_nodes : auto_chunk_nodes(P->n_nodes, tile_groups);
@@ -1118,8 +1183,8 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     }
 
     int rc;
-    if ((rc = c->d_S.ensure((size_t)I * 4 * tile_groups))) return rc;
-    if (algo == PMFS_SANKOFF && (rc = c->d_D.ensure((size_t)I * 4 * tile_groups))) return rc;
+    if ((rc = c->d_S.ensure(set_elems(tile_groups)))) return rc;
+    if (algo == PMFS_SANKOFF && (rc = c->d_D.ensure(set_elems(tile_groups)))) return rc;
     if ((rc = c->d_cons_planes.ensure(tile_groups))) return rc;
     if (d_forced && (rc = c->d_forced_planes.ensure(tile_groups))) return rc;
     if ((rc = c->d_xcode.ensure((size_t)NC * tile_groups))) return rc;
@@ -1601,7 +1666,7 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
         PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, sort_tmp, kb, (int)cap, kPayloadBits, kPayloadBits + pos_bits + node_bits, c->stream));
     }
     Carver cv{scratch};
-    uint4* S = cv.take<uint4>(I * 4 * (size_t)G);
+    uint4* S = cv.take<uint4>(I * (size_t)((G + kTileGroups - 1) / kTileGroups) * (kSetBytes / 16));
     uint4* xcode = cv.take<uint4>(NC * (size_t)G);
     uint32_t* xvalid = cv.take<uint32_t>(NC * (size_t)G);
     uint4* cons_planes = cv.take<uint4>((size_t)G);

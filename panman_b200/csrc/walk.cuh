@@ -63,11 +63,10 @@ PMFS_HD void onehot(const Code4& c, Planes16& s) {
     for (int s_ = 0; s_ < 16; s_++) s.p[s_] = hi[s_ >> 2] & lo[s_ & 3];
 }
 
-PMFS_HD uint32_t or16(const Planes16& s) {
-    uint32_t r = 0;
-#pragma unroll
-    for (int i = 0; i < 16; i++) r |= s.p[i];
-    return r;
+PMFS_HD uint32_t or16(const Planes16& s) {  // tree shaped: short dependency chain
+    const uint32_t a = s.p[0] | s.p[1] | s.p[2], b = s.p[3] | s.p[4] | s.p[5], c = s.p[6] | s.p[7] | s.p[8];
+    const uint32_t d = s.p[9] | s.p[10] | s.p[11], e = s.p[12] | s.p[13] | s.p[14];
+    return (a | b | c) | (d | e | s.p[15]);
 }
 
 PMFS_HD void zero16(Planes16& s) {
@@ -127,9 +126,10 @@ PMFS_HD void code_select(uint32_t m, const Code4& a, const Code4& b, Code4& out)
 
 // Fitch: and ? and : or (src/fitchSankoff.cpp:48-55).  Also the S part of the binary Sankoff join.
 PMFS_HD void join_sets(const Planes16& a, const Planes16& b, Planes16& out, uint32_t& any_and) {
-    uint32_t any = 0;
+    uint32_t t[4] = {0, 0, 0, 0};  // four short OR chains instead of one of length 16
 #pragma unroll
-    for (int i = 0; i < 16; i++) any |= a.p[i] & b.p[i];
+    for (int i = 0; i < 16; i++) t[i & 3] |= a.p[i] & b.p[i];
+    const uint32_t any = (t[0] | t[1]) | (t[2] | t[3]);
 #pragma unroll
     for (int i = 0; i < 16; i++) out.p[i] = (a.p[i] & b.p[i]) | ((a.p[i] | b.p[i]) & ~any);
     any_and = any;
@@ -146,104 +146,137 @@ constexpr int kAlgoSankoff = 1;
 constexpr int kPolyBits = 28;  // counter width of the any-arity Sankoff join: arity < 2^28 (node ids are < 2^28)
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Env concept (device: kernels.cu; host emulation: tests/host_emul.cpp)
-//   uint32_t word(const uint32_t* prog, int32_t pc)          program word, same for every thread
-//   uint4    leaf(uint32_t row)                               this thread's 32 nibbles of MSA row `row` (next ring entry)
-//   void     load_x(uint32_t id, Planes16&)                   set S[id], prefetched (next 4 ring entries)
-//   void     load_s(uint32_t id, Planes16&)  / store_s        set array S (Fitch: the only one), direct access
-//   void     load_d(uint32_t id, Planes16&)  / store_d        Sankoff D1 array
-//   void     push(const Planes16&) / pop(Planes16&)           forward stack
-//   void     pushp(const Code4&, uint32_t) / popp(...)        backward stack
-//   void     store_x(uint32_t chunk, const Code4&, uint32_t)  parent state for a child chunk
-//   bool     any(bool)                                        warp-wide OR (host: identity)
-//   void     emit_internal(uint32_t id, uint32_t m, const Code4& g, const Code4& p)
-//   void     emit_leaf(uint32_t row, uint32_t m, const Code4& g, const Code4& p)
+// One thread walks NG column groups at once (NG x 32 columns): the per-op bookkeeping (program fetch, dispatch, operand
+// hand-over, addressing) is paid once per NG groups, and the NG independent dependency chains interleave in the
+// pipeline.  On the B200 this code is bound by integer-ALU issue, so instructions per column are what counts.
+//
+// Env concept (device: pmfs.cu; host emulation: tests/host_emul.cpp), NG = Env::kGroups
+//   uint32_t word(const uint32_t* prog, int32_t pc)            program word, same for every thread
+//   void     leaf(uint32_t row, uint4 (&w)[NG])                this thread's 32 nibbles per group of MSA row `row`
+//   void     load_x(uint32_t id, Planes16 (&s)[NG])            set S[id] written by an earlier work item (prefetched)
+//   void     load_s / store_s(uint32_t id, Planes16 (&s)[NG])  set array S (Fitch: the only one), direct access
+//   void     load_d / store_d                                  Sankoff D1 array
+//   void     push / pop(Planes16 (&s)[NG])                     forward stack
+//   void     pushp / popp(Code4 (&c)[NG], uint32_t (&pv)[NG])  backward stack
+//   void     store_x(uint32_t chunk, const Code4 (&c)[NG], const uint32_t (&pv)[NG])   parent state for a child chunk
+//   bool     any(bool)                                         warp-wide OR (host: identity)
+//   void     emit_internal(uint32_t id, const uint32_t (&m)[NG], const Code4 (&g)[NG], const Code4 (&p)[NG])
+//   void     emit_leaf(uint32_t row, ...same...)
 // ---------------------------------------------------------------------------------------------------------------------
 
 template <class Env>
-PMFS_HD void load_operand(Env& env, uint32_t o, Planes16& s) {
+PMFS_HD void load_operand(Env& env, uint32_t o, Planes16 (&s)[Env::kGroups]) {
+    constexpr int NG = Env::kGroups;
     if (o & kOperandSet) {
-        if (o & kOperandExt) env.load_x(o & kOperandIdMask, s);  // written by an earlier launch: comes through the ring
-        else env.load_s(o & kOperandIdMask, s);                  // written by this thread earlier in this launch
+        if (o & kOperandExt) env.load_x(o & kOperandIdMask, s);  // written by an earlier work item: comes through the ring
+        else env.load_s(o & kOperandIdMask, s);                  // written by this thread earlier in this work item
     } else if (o == kAbsentLeaf) {
-        zero16(s);
+#pragma unroll
+        for (int j = 0; j < NG; j++) zero16(s[j]);
     } else {
-        Code4 c;
-        transpose_nibbles(env.leaf(o), c);
-        onehot(c, s);
+        uint4 w[NG];
+        env.leaf(o, w);
+#pragma unroll
+        for (int j = 0; j < NG; j++) {
+            Code4 c;
+            transpose_nibbles(w[j], c);
+            onehot(c, s[j]);
+        }
     }
 }
 
 template <int ALGO, class Env>
-PMFS_HD void finish_node(Env& env, uint32_t id, Planes16& S, const Code4* forced) {
-    if (ALGO == kAlgoFitch && id == 0 && forced) onehot(*forced, S);  // refState overwrites the root (:45-47)
+PMFS_HD void finish_node(Env& env, uint32_t id, Planes16 (&S)[Env::kGroups], const Code4* forced) {
+    if (ALGO == kAlgoFitch && id == 0 && forced) {  // refState overwrites the root (:45-47)
+#pragma unroll
+        for (int j = 0; j < Env::kGroups; j++) onehot(forced[j], S[j]);
+    }
     env.store_s(id, S);
 }
 
 // Any-arity join (unary nodes and polytomies); children are re-read from memory, so nothing is live across them.
 template <int ALGO, class Env>
-PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, Planes16& S, Planes16& D1) {
+PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, Planes16 (&S)[Env::kGroups],
+                       Planes16 (&D1)[Env::kGroups]) {
+    constexpr int NG = Env::kGroups;
     if (ALGO == kAlgoFitch) {
-        Planes16 A, O;
+        Planes16 A[NG], O[NG];
 #pragma unroll
-        for (int i = 0; i < 16; i++) { A.p[i] = ~0u; O.p[i] = 0; }
-        for (uint32_t j = 0; j < k; j++) {
-            Planes16 B;
-            load_operand(env, env.word(prog, pc + (int32_t)j), B);
+        for (int j = 0; j < NG; j++)
 #pragma unroll
-            for (int i = 0; i < 16; i++) { A.p[i] &= B.p[i]; O.p[i] |= B.p[i]; }
+            for (int i = 0; i < 16; i++) { A[j].p[i] = ~0u; O[j].p[i] = 0; }
+        for (uint32_t c = 0; c < k; c++) {
+            Planes16 B[NG];
+            load_operand(env, env.word(prog, pc + (int32_t)c), B);
+#pragma unroll
+            for (int j = 0; j < NG; j++)
+#pragma unroll
+                for (int i = 0; i < 16; i++) { A[j].p[i] &= B[j].p[i]; O[j].p[i] |= B[j].p[i]; }
         }
-        uint32_t any = or16(A);
 #pragma unroll
-        for (int i = 0; i < 16; i++) S.p[i] = A.p[i] | (O.p[i] & ~any);
+        for (int j = 0; j < NG; j++) {
+            const uint32_t any = or16(A[j]);
+#pragma unroll
+            for (int i = 0; i < 16; i++) S[j].p[i] = A[j].p[i] | (O[j].p[i] & ~any);
+        }
     } else {
         // h[s] = number of valid children whose S contains s, as bit-sliced counters; S = argmax h, D1 = {h = max-1}
         int nb = 1;
         while ((k >> nb) != 0) nb++;
-        uint32_t h[16][kPolyBits];
-        for (int s = 0; s < 16; s++)
-            for (int b = 0; b < nb; b++) h[s][b] = 0;
-        uint32_t any_valid = 0;
-        for (uint32_t j = 0; j < k; j++) {
-            Planes16 B;
-            load_operand(env, env.word(prog, pc + (int32_t)j), B);
-            any_valid |= or16(B);
-            for (int s = 0; s < 16; s++) {
-                uint32_t carry = B.p[s];
-                for (int b = 0; b < nb && carry; b++) {
-                    uint32_t x = h[s][b];
-                    h[s][b] = x ^ carry;
-                    carry &= x;
+        uint32_t h[NG][16][kPolyBits];
+        uint32_t any_valid[NG];
+        for (int j = 0; j < NG; j++) {
+            any_valid[j] = 0;
+            for (int s = 0; s < 16; s++)
+                for (int b = 0; b < nb; b++) h[j][s][b] = 0;
+        }
+        for (uint32_t c = 0; c < k; c++) {
+            Planes16 B[NG];
+            load_operand(env, env.word(prog, pc + (int32_t)c), B);
+            for (int j = 0; j < NG; j++) {
+                any_valid[j] |= or16(B[j]);
+                for (int s = 0; s < 16; s++) {
+                    uint32_t carry = B[j].p[s];
+                    for (int b = 0; b < nb && carry; b++) {
+                        const uint32_t x = h[j][s][b];
+                        h[j][s][b] = x ^ carry;
+                        carry &= x;
+                    }
                 }
             }
         }
-        uint32_t cand[16], mx[kPolyBits];
-        for (int s = 0; s < 16; s++) cand[s] = ~0u;
-        for (int b = nb - 1; b >= 0; b--) {
-            uint32_t one = 0;
-            for (int s = 0; s < 16; s++) one |= cand[s] & h[s][b];
-            for (int s = 0; s < 16; s++) cand[s] &= ~(one & ~h[s][b]);
-            mx[b] = one;
-        }
-        uint32_t borrow = ~0u;  // mx - 1
-        for (int b = 0; b < nb; b++) {
-            uint32_t x = mx[b];
-            mx[b] = x ^ borrow;
-            borrow &= ~x;
-        }
-        for (int s = 0; s < 16; s++) {
-            uint32_t eq = ~borrow;  // borrow out set <=> max was 0 (no valid child): D1 is irrelevant there
-            for (int b = 0; b < nb; b++) eq &= ~(h[s][b] ^ mx[b]);
-            S.p[s] = cand[s] & any_valid;
-            D1.p[s] = eq;
+        for (int j = 0; j < NG; j++) {
+            uint32_t cand[16], mx[kPolyBits];
+            for (int s = 0; s < 16; s++) cand[s] = ~0u;
+            for (int b = nb - 1; b >= 0; b--) {
+                uint32_t one = 0;
+                for (int s = 0; s < 16; s++) one |= cand[s] & h[j][s][b];
+                for (int s = 0; s < 16; s++) cand[s] &= ~(one & ~h[j][s][b]);
+                mx[b] = one;
+            }
+            uint32_t borrow = ~0u;  // mx - 1
+            for (int b = 0; b < nb; b++) {
+                const uint32_t x = mx[b];
+                mx[b] = x ^ borrow;
+                borrow &= ~x;
+            }
+            for (int s = 0; s < 16; s++) {
+                uint32_t eq = ~borrow;  // borrow out set <=> max was 0 (no valid child): D1 is irrelevant there
+                for (int b = 0; b < nb; b++) eq &= ~(h[j][s][b] ^ mx[b]);
+                S[j].p[s] = cand[s] & any_valid[j];
+                D1[j].p[s] = eq;
+            }
         }
     }
 }
 
+// forced: NG code planes (Fitch refState) or nullptr
 template <int ALGO, bool POLY, class Env>
 PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Code4* forced) {
-    Planes16 T;
-    zero16(T);
+    constexpr int NG = Env::kGroups;
+    Planes16 T[NG];
+#pragma unroll
+    for (int j = 0; j < NG; j++) zero16(T[j]);
     int32_t pc = 0;
     while (pc < len) {
         const uint32_t w = env.word(prog, pc++);
@@ -252,7 +285,7 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
             env.push(T);
             continue;
         }
-        Planes16 D1;
+        Planes16 D1[NG];
         if (code == F_POLY) {
             if (POLY) {
                 const uint32_t k = env.word(prog, pc++);
@@ -260,8 +293,7 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
                 pc += (int32_t)k;
             }
         } else {
-            Planes16 A;
-            uint32_t any;
+            Planes16 A[NG];
             if (code == F_JOIN_POP) {
                 env.pop(A);
             } else if (code == F_JOIN_IMM) {
@@ -270,13 +302,17 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
                 load_operand(env, env.word(prog, pc++), A);
                 load_operand(env, env.word(prog, pc++), T);
             }
-            if (ALGO == kAlgoSankoff) {
-                Planes16 S;
-                join_sets(A, T, S, any);
-                join_d1(A, T, any, D1);
-                T = S;
-            } else {
-                join_sets(A, T, T, any);
+#pragma unroll
+            for (int j = 0; j < NG; j++) {
+                uint32_t any;
+                if (ALGO == kAlgoSankoff) {
+                    Planes16 S;
+                    join_sets(A[j], T[j], S, any);
+                    join_d1(A[j], T[j], any, D1[j]);
+                    T[j] = S;
+                } else {
+                    join_sets(A[j], T[j], T[j], any);
+                }
             }
         }
         finish_node<ALGO>(env, id, T, forced);
@@ -284,54 +320,68 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
     }
 }
 
-// P/pv: state of the chunk root's parent (consensus planes and all-ones for the tree root).  colmask: real columns of
-// this group.  Returns the mask of real columns whose Sankoff root has no finite cost and is not forced (an error).
+// P/pv: state of the chunk root's parent (consensus planes and all-ones for the tree root), per group.  colmask: real
+// columns of each group.  Returns the mask of real columns whose Sankoff root has no finite cost and is not forced.
 template <int ALGO, class Env>
-PMFS_HD uint32_t backward_walk(Env& env, const uint32_t* prog, int32_t len, Code4 P, uint32_t pv, const Code4* forced,
-                               uint32_t colmask) {
+PMFS_HD uint32_t backward_walk(Env& env, const uint32_t* prog, int32_t len, Code4 (&P)[Env::kGroups],
+                               uint32_t (&pv)[Env::kGroups], const Code4* forced, const uint32_t (&colmask)[Env::kGroups]) {
+    constexpr int NG = Env::kGroups;
     uint32_t err = 0;
     int32_t pc = 0;
     while (pc < len) {
         const uint32_t w = env.word(prog, pc++);
         const uint32_t code = w & ((1u << kOpBits) - 1), arg = w >> kOpBits;
         if (code == B_ENTER) {
-            Planes16 S;
+            Planes16 S[NG];
             env.load_x(arg, S);
-            const uint32_t hit = mux16(S, P);  // parent's state is in this node's set
-            const uint32_t nz = or16(S);
-            if (ALGO == kAlgoFitch) {
-                // a node with an empty set is skipped with its whole subtree (:101-103); below it every set is empty too
-                const uint32_t m = nz & ~hit & colmask;
-                if (env.any(m != 0)) {
-                    Code4 l, G;
-                    lowest(S, nz, l);
-                    code_select(hit, P, l, G);
-                    env.emit_internal(arg, m, G, P);
-                    P = G;
+            uint32_t hit[NG], nz[NG], slow = 0;
+#pragma unroll
+            for (int j = 0; j < NG; j++) {
+                hit[j] = mux16(S[j], P[j]);  // parent's state is in this node's set
+                nz[j] = or16(S[j]);
+                // Fitch: a node with an empty set is skipped with its whole subtree (:101-103); below it every set is
+                // empty too.  Sankoff: includes invalid nodes (an empty S never hits).
+                slow |= (ALGO == kAlgoFitch ? nz[j] : pv[j]) & ~hit[j] & colmask[j];
+            }
+            if (env.any(slow != 0)) {
+                Planes16 D1[NG];
+                if (ALGO == kAlgoSankoff) env.load_d(arg, D1);
+                Code4 G[NG];
+                uint32_t m[NG];
+#pragma unroll
+                for (int j = 0; j < NG; j++) {
+                    Code4 l;
+                    lowest(S[j], nz[j], l);
+                    if (ALGO == kAlgoFitch) {
+                        code_select(hit[j], P[j], l, G[j]);
+                        m[j] = nz[j] & ~hit[j] & colmask[j];
+                    } else {
+                        const uint32_t ind = mux16(D1[j], P[j]);
+                        const uint32_t keep = hit[j] | (ind & ~code_lt(l, P[j]));  // d[p]==1: first index of {p} U S wins
+                        code_select(keep, P[j], l, G[j]);
+                        const uint32_t nv = pv[j] & nz[j];
+                        m[j] = nv & code_ne(G[j], P[j]) & colmask[j];
+                        pv[j] = nv;
+                    }
                 }
-            } else {
-                const uint32_t slow = pv & ~hit & colmask;  // includes invalid nodes (empty S never hits)
-                if (env.any(slow != 0)) {
-                    Planes16 D1;
-                    env.load_d(arg, D1);
-                    const uint32_t ind = mux16(D1, P);
-                    Code4 l, G;
-                    lowest(S, nz, l);
-                    const uint32_t keep = hit | (ind & ~code_lt(l, P));  // d[p]==1: first index of {p} U S wins
-                    code_select(keep, P, l, G);
-                    const uint32_t nv = pv & nz;
-                    env.emit_internal(arg, nv & code_ne(G, P) & colmask, G, P);
-                    P = G;
-                    pv = nv;
-                }
+                env.emit_internal(arg, m, G, P);
+#pragma unroll
+                for (int j = 0; j < NG; j++) P[j] = G[j];
             }
         } else if (code == B_LEAF) {
-            Code4 c;
-            transpose_nibbles(env.leaf(arg), c);
-            // Fitch: parent & {c} ? parent : c == c.  Sankoff: S = {c}, D1 = {} -> c.  Either way the leaf keeps its code.
-            uint32_t m = code_ne(c, P) & colmask;
-            if (ALGO == kAlgoSankoff) m &= pv;
-            if (env.any(m != 0)) env.emit_leaf(arg, m, c, P);
+            uint4 wv[NG];
+            env.leaf(arg, wv);
+            Code4 c[NG];
+            uint32_t m[NG], anym = 0;
+#pragma unroll
+            for (int j = 0; j < NG; j++) {
+                transpose_nibbles(wv[j], c[j]);
+                // Fitch: parent & {c} ? parent : c == c.  Sankoff: S = {c}, D1 = {} -> c.  The leaf keeps its code.
+                m[j] = code_ne(c[j], P[j]) & colmask[j];
+                if (ALGO == kAlgoSankoff) m[j] &= pv[j];
+                anym |= m[j];
+            }
+            if (env.any(anym != 0)) env.emit_leaf(arg, m, c, P);
         } else if (code == B_XCHILD) {
             env.store_x(arg, P, pv);
         } else if (code == B_PUSHP) {
@@ -339,23 +389,29 @@ PMFS_HD uint32_t backward_walk(Env& env, const uint32_t* prog, int32_t len, Code
         } else if (code == B_POPP) {
             env.popp(P, pv);
         } else {  // B_ENTER_ROOT: P holds the consensus
-            Planes16 S;
+            Planes16 S[NG];
             env.load_x(0, S);
-            const uint32_t nz = or16(S);
-            Code4 G;
-            uint32_t nv;
-            if (ALGO == kAlgoSankoff && forced) {
-                G = *forced;  // defaultValue (:491-492)
-                nv = ~0u;
-            } else {
-                lowest(S, nz, G);  // Fitch: lowest set bit (:104-116); Sankoff: first-index argmin (:493-507)
-                nv = nz;
-                if (ALGO == kAlgoSankoff) err |= ~nz & colmask;
+            Code4 G[NG];
+            uint32_t m[NG], anym = 0;
+#pragma unroll
+            for (int j = 0; j < NG; j++) {
+                const uint32_t nz = or16(S[j]);
+                uint32_t nv;
+                if (ALGO == kAlgoSankoff && forced) {
+                    G[j] = forced[j];  // defaultValue (:491-492)
+                    nv = ~0u;
+                } else {
+                    lowest(S[j], nz, G[j]);  // Fitch: lowest set bit (:104-116); Sankoff: first-index argmin (:493-507)
+                    nv = nz;
+                    if (ALGO == kAlgoSankoff) err |= ~nz & colmask[j];
+                }
+                m[j] = nv & code_ne(G[j], P[j]) & colmask[j];
+                anym |= m[j];
+                pv[j] = nv;
             }
-            const uint32_t m = nv & code_ne(G, P) & colmask;
-            if (env.any(m != 0)) env.emit_internal(0, m, G, P);
-            P = G;
-            pv = nv;
+            if (env.any(anym != 0)) env.emit_internal(0, m, G, P);
+#pragma unroll
+            for (int j = 0; j < NG; j++) P[j] = G[j];
         }
     }
     return err;

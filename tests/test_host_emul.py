@@ -29,7 +29,7 @@ def emul():
     return lib
 
 
-def run_emul(lib, algo, tree, msa_codes, cons, forced, chunk_nodes, want_plan=False):
+def run_emul(lib, algo, tree, msa_codes, cons, forced, chunk_nodes, want_plan=False, groups=2):
     nib = pack_nibbles(msa_codes) if msa_codes.shape[0] else np.zeros((0, 1), np.uint8)
     n_cols = int(cons.shape[0])
     arrs = [np.ascontiguousarray(a, np.int32) for a in (tree.parent, tree.child_off, tree.child_idx, tree.leaf_row)]
@@ -39,7 +39,7 @@ def run_emul(lib, algo, tree, msa_codes, cons, forced, chunk_nodes, want_plan=Fa
     plan = (C.c_int64 * 6)()
     rc = lib.emul_run(C.c_int(algo), C.c_int32(tree.n_nodes), *[C.c_void_p(a.ctypes.data) for a in arrs],
                       C.c_void_p(nib.ctypes.data), C.c_int64(nib.shape[1]), C.c_int64(n_cols), C.c_void_p(cons.ctypes.data),
-                      None if frc is None else C.c_void_p(frc.ctypes.data), C.c_int32(chunk_nodes), C.byref(out), C.byref(n), plan)
+                      None if frc is None else C.c_void_p(frc.ctypes.data), C.c_int32(chunk_nodes), C.c_int32(groups), C.byref(out), C.byref(n), plan)
     if rc != 0:
         raise RuntimeError(f"emul_run rc={rc}")
     res = np.frombuffer((C.c_char * (n.value * MUT_DTYPE.itemsize)).from_address(out.value), MUT_DTYPE).copy() if n.value \
@@ -53,9 +53,9 @@ def test_emul_matches_golden_small(emul, small_cases):
     for name in z["case_names"]:
         tree, msa, cons, forced = G.case_inputs(z, str(name))
         for algo in (0, 1):
-            for chunk in (1 << 30, 4):
-                got = run_emul(emul, algo, tree, msa, cons, forced, chunk)
-                assert G.same_muts(got, z[f"{name}/muts{algo}"]), (name, algo, chunk)
+            for chunk, groups in ((1 << 30, 1), (4, 2)):
+                got = run_emul(emul, algo, tree, msa, cons, forced, chunk, groups=groups)
+                assert G.same_muts(got, z[f"{name}/muts{algo}"]), (name, algo, chunk, groups)
 
 
 @pytest.mark.parametrize("low,with_ref", [(0, 0), (0, 1), (1, 0), (1, 1)])
@@ -81,7 +81,7 @@ def test_emul_matches_oracle_random(emul):
         chunk = int(rng.choice([2, 3, 8, 32, 1 << 30]))
         for algo in (0, 1):
             want = O.run_port(algo, tree, msa, cons, forced, threads=2)
-            got, plan = run_emul(emul, algo, tree, msa, cons, forced, chunk, want_plan=True)
+            got, plan = run_emul(emul, algo, tree, msa, cons, forced, chunk, want_plan=True, groups=1 + trial % 2)
             assert G.same_muts(got, want), (trial, algo, chunk, plan)
 
 
