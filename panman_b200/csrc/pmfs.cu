@@ -50,6 +50,7 @@ struct WalkParams {
     const int64_t* chunk_off;   // [NC] offset of each chunk's program
     const int32_t* chunk_len;   // [NC]
     const int32_t* order;       // chunk ids in execution order of this pass
+    const int4* items;          // [2*NC] per chunk IN EXECUTION ORDER: {chunk, parent, plen, slen}, {prog_off/4, stream_off, need, dep chunk}
     const int32_t* chunk_parent;  // [NC] parent chunk, -1 for the chunk that holds the tree root
     const int32_t* chunk_nchild;  // [NC] number of child chunks
     int* ready;                 // [NC][ctas_per_chunk] dependency counters of this pass (zeroed before the launch)
@@ -205,19 +206,10 @@ struct ItemDesc {
 // Producer side of one item: stage the walk program into program buffer `slot`, then walk the chunk's load stream and
 // keep both rings full.  Called by the whole producer warp (the stream words are read warp-wide); lane 0 drives TMA.
 template <int SETS>
-__device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& r, int32_t chunk, int tile, int32_t plen,
-                                               uint32_t slot, uint32_t& n_leaf, uint32_t& n_set) {
+__device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& r, WarpWords& w, int32_t slen, int tile,
+                                               uint32_t& n_leaf, uint32_t& n_set) {
     using M = SmemMap<SETS>;
     const int lane = threadIdx.x & 31;
-    if (lane == 0 && plen <= kProgWords) {
-        // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
-        const uint32_t bytes = (uint32_t)((plen + 3) / 4) * 16u;
-        mbar_arrive_expect_tx(r.bars + (M::bProg + slot) * 8, bytes);
-        bulk_g2s(r.smem + M::kProg + slot * (kProgWords * 4), p.prog + p.chunk_off[chunk], bytes, r.bars + (M::bProg + slot) * 8);
-    }
-    const int32_t slen = p.stream_len[chunk];
-    WarpWords w;
-    w.init(p.stream + p.stream_off[chunk], slen, lane);
     const int64_t g0 = (int64_t)tile * kTileGroups;
     const uint32_t leaf_bytes = (uint32_t)min((int64_t)kTileGroups, p.G - g0) * 16u;
     for (int32_t j = 0; j < slen; j++) {
@@ -506,35 +498,48 @@ __device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars)
     return r;
 }
 
-// Producer warp: claim -> dependency -> descriptor -> program + operand stream, item after item.
+// Producer warp: claim -> item record -> (program copy, stream window) -> dependency -> descriptor -> operand stream,
+// item after item.  Everything that does not need the dependency is started before it is polled, the item record is
+// one 32-byte load, and the claim for the NEXT item is issued before this one is produced, so that per item only the
+// record load and the dependency poll remain on the producer's critical path.
 template <int PASS, int SETS>
 __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r) {
     using M = SmemMap<SETS>;
     const int lane = threadIdx.x & 31;
     uint32_t n_leaf = 0, n_set = 0;
+    int item = 0;
+    if (lane == 0) item = atomicAdd(p.next_item, 1);
     for (uint32_t n = 0;; n++) {
         const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
-        int32_t chunk = -1, tile = 0, plen = 0, parent = -1;
+        int32_t chunk = -1, tile = 0, slen = 0, stream_off = 0, next = 0;
         if (lane == 0) {
-            mbar_wait(r.bars + (M::bDescEmpty + slot) * 8, phase ^ 1u);  // the walkers are done with item n-2
-            const int item = atomicAdd(p.next_item, 1);
+            int32_t plen = 0, parent = -1;
             if (item < p.n_items) {
-                chunk = p.order[item / p.ctas_per_chunk];
+                const int pos = item / p.ctas_per_chunk;
                 tile = item % p.ctas_per_chunk;
-                plen = p.chunk_len[chunk];
-                parent = p.chunk_parent[chunk];
+                const int4 a = __ldg(p.items + 2 * pos), b = __ldg(p.items + 2 * pos + 1);
+                next = atomicAdd(p.next_item, 1);  // claim ahead: its latency hides behind this item
+                chunk = a.x; parent = a.y; plen = a.z; slen = a.w; stream_off = b.y;
+                mbar_wait(r.bars + (M::bDescEmpty + slot) * 8, phase ^ 1u);  // the walkers are done with item n-2
+                if (plen <= kProgWords) {
+                    // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
+                    const uint32_t bytes = (uint32_t)((plen + 3) / 4) * 16u;
+                    mbar_arrive_expect_tx(r.bars + (M::bProg + slot) * 8, bytes);
+                    bulk_g2s(r.smem + M::kProg + slot * (kProgWords * 4), p.prog + (int64_t)b.x * 4, bytes, r.bars + (M::bProg + slot) * 8);
+                }
                 // dependencies: all child chunks (bottom-up) / the parent chunk (top-down), same column tile
-                const int need = PASS == kPassFwd ? p.chunk_nchild[chunk] : (parent < 0 ? 0 : 1);
-                const volatile int* f = p.ready + (int64_t)(PASS == kPassFwd || parent < 0 ? chunk : parent) * p.ctas_per_chunk + tile;
-                if (*f < need) {
+                const volatile int* f = p.ready + (int64_t)b.w * p.ctas_per_chunk + tile;
+                if (*f < b.z) {
                     const long long t0 = clock64();
-                    while (*f < need) {
+                    while (*f < b.z) {
                         __nanosleep(32);
                         if (clock64() - t0 > kSpinLimitCycles) __trap();
                     }
                 }
                 __threadfence();
                 asm volatile("fence.proxy.async;" ::: "memory");  // data written by other CTAs is read by the TMA engine
+            } else {
+                mbar_wait(r.bars + (M::bDescEmpty + slot) * 8, phase ^ 1u);
             }
             asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.smem + M::kDesc + slot * 16), "r"(chunk), "r"(tile), "r"(plen),
                          "r"(parent)
@@ -544,8 +549,12 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
         chunk = __shfl_sync(0xffffffffu, chunk, 0);
         if (chunk < 0) return;
         tile = __shfl_sync(0xffffffffu, tile, 0);
-        plen = __shfl_sync(0xffffffffu, plen, 0);
-        produce_stream<SETS>(p, r, chunk, tile, plen, slot, n_leaf, n_set);
+        slen = __shfl_sync(0xffffffffu, slen, 0);
+        stream_off = __shfl_sync(0xffffffffu, stream_off, 0);
+        WarpWords w;
+        w.init(p.stream + stream_off, slen, lane);
+        produce_stream<SETS>(p, r, w, slen, tile, n_leaf, n_set);
+        item = next;
     }
 }
 
@@ -834,6 +843,7 @@ struct pmfs_ctx {
     DevBuf<uint32_t> d_fwd_prog, d_bwd_prog, d_fwd_stream, d_bwd_stream;
     DevBuf<int64_t> d_fwd_off, d_bwd_off, d_fwd_soff, d_bwd_soff;
     DevBuf<int32_t> d_fwd_slen, d_bwd_slen, d_chunk_parent, d_chunk_nchild;
+    DevBuf<int4> d_fwd_items, d_bwd_items;
     DevBuf<int> d_sync;
     int n_sms = 0;
     struct Occ {
@@ -896,6 +906,25 @@ static int upload_plan(pmfs_ctx* c) {
     int rc;
     if ((rc = up(c->d_fwd_prog, P.fwd_prog))) return rc;
     if ((rc = up(c->d_bwd_prog, P.bwd_prog))) return rc;
+    for (int pass = 0; pass < 2; pass++) {  // packed per-item records in execution order (see WalkParams::items)
+        const std::vector<int32_t>& order = pass == 0 ? P.fwd_order : P.bwd_order;
+        std::vector<int4> items(2 * NC);
+        for (size_t k = 0; k < NC; k++) {
+            const Chunk& ch = P.chunks[order[k]];
+            const int64_t poff = pass == 0 ? ch.fwd_off : ch.bwd_off, soff = pass == 0 ? ch.fwd_stream_off : ch.bwd_stream_off;
+            if (poff / 4 > 0x7fffffffll || soff > 0x7fffffffll) {
+                g_error = "walk programs exceed 2^31 words";
+                return PMFS_ERR_ARG;
+            }
+            items[2 * k] = make_int4(order[k], ch.parent, pass == 0 ? ch.fwd_len : ch.bwd_len,
+                                     pass == 0 ? ch.fwd_stream_len : ch.bwd_stream_len);
+            // bottom-up: wait for all child chunks on my own counter; top-down: for the parent chunk on its counter
+            const int need = pass == 0 ? ch.n_child : (ch.parent < 0 ? 0 : 1);
+            const int dep = (pass == 0 || ch.parent < 0) ? order[k] : ch.parent;
+            items[2 * k + 1] = make_int4((int)(poff / 4), (int)soff, need, dep);
+        }
+        if ((rc = up(pass == 0 ? c->d_fwd_items : c->d_bwd_items, items))) return rc;
+    }
     if ((rc = up(c->d_chunk_parent, cpar))) return rc;
     if ((rc = up(c->d_chunk_nchild, cnch))) return rc;
     if ((rc = up(c->d_fwd_stream, P.fwd_stream))) return rc;
@@ -1006,7 +1035,7 @@ void pmfs_destroy(pmfs_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->d_fwd_stream.release(); c->d_bwd_stream.release(); c->d_fwd_soff.release(); c->d_bwd_soff.release();
     c->d_fwd_slen.release(); c->d_bwd_slen.release(); c->d_chunk_parent.release(); c->d_chunk_nchild.release();
-    c->d_sync.release(); c->d_rkeys_alt.release(); c->d_sort_tmp2.release();
+    c->d_sync.release(); c->d_fwd_items.release(); c->d_bwd_items.release(); c->d_rkeys_alt.release(); c->d_sort_tmp2.release();
     c->d_fwd_prog.release(); c->d_bwd_prog.release(); c->d_fwd_off.release(); c->d_bwd_off.release();
     c->d_fwd_len.release(); c->d_bwd_len.release(); c->d_fwd_order.release(); c->d_bwd_order.release();
     c->d_int_to_node.release(); c->d_row_to_node.release();
@@ -1079,6 +1108,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     wp.stream_off = fwd ? c->d_fwd_soff.ptr : c->d_bwd_soff.ptr;
     wp.stream_len = fwd ? c->d_fwd_slen.ptr : c->d_bwd_slen.ptr;
     wp.order = fwd ? c->d_fwd_order.ptr : c->d_bwd_order.ptr;
+    wp.items = fwd ? c->d_fwd_items.ptr : c->d_bwd_items.ptr;
     wp.chunk_parent = c->d_chunk_parent.ptr;
     wp.chunk_nchild = c->d_chunk_nchild.ptr;
     wp.ctas_per_chunk = (int32_t)((wp.G + kTileGroups - 1) / kTileGroups);

@@ -1,5 +1,5 @@
 """Minimal driver for ncu captures: BASELINE config 2, `--steps` device-resident passes, nothing else.
-usage: python profiles/prof_run.py [fitch|sankoff] [steps]"""
+usage: python profiles/prof_run.py [fitch|sankoff] [steps] [taxa] [columns]"""
 import os
 import sys
 
@@ -10,7 +10,8 @@ from panman_b200 import api, trees
 
 algo = api.SANKOFF if len(sys.argv) > 1 and sys.argv[1] == "sankoff" else api.FITCH
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
-N, L = 20000, 30000
+N = int(sys.argv[3]) if len(sys.argv) > 3 else 20000
+L = int(sys.argv[4]) if len(sys.argv) > 4 else 30000
 tree = trees.random_binary_tree(N)
 ctx = api.Context(tree)
 stride = ((L + 31) // 32) * 16
