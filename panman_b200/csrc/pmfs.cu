@@ -77,6 +77,8 @@ struct WalkParams {
     unsigned long long* out_keys;   // [n_owners][out_cap] packed records (see kPayloadBits)
     unsigned long long* out_count;  // [n_owners]
     unsigned long long out_cap;     // capacity of one owner's region
+    int32_t n_regions;              // > 0: one output region per 32 column groups (see emit); 0: regions per owner
+    int64_t region_base;            // region index of this column tile's first 32 groups
     int32_t n_owners;               // 1, or the number of ranks in column-shard mode
     int32_t owner_bound[17];        // nodes [owner_bound[r], owner_bound[r+1]) are owned by rank r
     unsigned int* err_flag;
@@ -263,6 +265,7 @@ struct DevEnv {
     bool prog_staged;
     const uint32_t* gprog;
     uint32_t sprog;      // shared address of this item's staged program
+    uint32_t ltmask;     // bits of a group word whose column is smaller than the column of bit `lane`
 
     __device__ DevEnv(const WalkParams& p_, const Ring& r, const ItemDesc& d, uint32_t slot, uint32_t prog_parity,
                       uint32_t& n_leaf_, uint32_t& n_set_, void* smem_generic)
@@ -276,6 +279,9 @@ struct DevEnv {
             active[j] = gj < p_.G;
             g[j] = active[j] ? gj : p_.G - 1;
         }
+        ltmask = 0;
+        for (int q = 0; q < 32; q++)
+            if (column_of_bit(q) < column_of_bit(lane)) ltmask |= 1u << q;
         if (prog_staged) mbar_wait(r.bars + (M::bProg + slot) * 8, prog_parity);
         else gprog = p_.prog + p_.chunk_off[d.chunk];
     }
@@ -416,7 +422,7 @@ struct DevEnv {
                 cp |= ((__shfl_sync(full, P.b[i], src) >> lane) & 1u) << i;
             }
             if ((mm >> lane) & 1u) {
-                const unsigned long long idx = base + __popc(mm & ((1u << lane) - 1u));
+                const unsigned long long idx = base + __popc(mm & ltmask);  // rank in COLUMN order
                 if (idx < p.out_cap) {
                     // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
                     const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
@@ -427,7 +433,24 @@ struct DevEnv {
             base += __popc(mm);
         }
     }
+    // Two output layouts.  Regions per 32 column groups (single-GPU runs): the records of one (node, region) pair come
+    // from exactly one call, are written contiguously in column order, and regions are laid out in column order -- so a
+    // STABLE sort on the node bits alone (2 radix passes instead of 4) yields the (node,pos) order.  Regions per owning
+    // rank (column shards): see pmfs_set_shard.
     __device__ void emit(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+        if (p.n_regions > 0) {
+#pragma unroll
+            for (int j = 0; j < kNG; j++) {
+                if (!__any_sync(0xffffffffu, m[j] != 0)) continue;
+                const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
+                const int64_t region = p.region_base + ((gwarp + j * kTPB) >> 5);
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(p.out_count + region, (unsigned long long)total);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * kTPB);
+            }
+            return;
+        }
         uint32_t cnt = 0;
 #pragma unroll
         for (int j = 0; j < kNG; j++) cnt += __popc(m[j]);
@@ -689,6 +712,16 @@ __global__ void assemble_kernel(const unsigned long long* __restrict__ recs, int
     out[i] = m;
 }
 
+// region r's records (count[r] of them at src + r*cap) -> dst + offset[r]: makes the per-region output contiguous
+__global__ void compact_regions_kernel(const unsigned long long* __restrict__ src, unsigned long long cap,
+                                       const unsigned long long* __restrict__ count, const unsigned long long* __restrict__ offset,
+                                       unsigned long long* __restrict__ dst) {
+    const unsigned long long n = count[blockIdx.y], o = offset[blockIdx.y];
+    const unsigned long long* s = src + (unsigned long long)blockIdx.y * cap;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x)
+        dst[o + i] = s[i];
+}
+
 // ------------------------------------------------------------------------------------------------ synthetic alignments
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {  // splitmix64 finaliser
     x ^= x >> 30; x *= 0xbf58476d1ce4e5b9ull;
@@ -873,6 +906,7 @@ struct pmfs_ctx {
     DevBuf<pmfs_mut> d_out;
     // host-path staging
     DevBuf<uint8_t> d_msa, d_cons, d_forced;
+    std::vector<unsigned long long> h_counts, h_offsets;
     pmfs_mut* h_out = nullptr;  // pinned
     size_t h_out_cap = 0;
     int64_t last_n_out = 0;
@@ -963,14 +997,14 @@ static int replan(pmfs_ctx* c, int32_t chunk_nodes) {
     return upload_plan(c);
 }
 
-// Chunk size.  The passes are bound by the longest chain of dependent (chunk, tile) items more than by raw throughput,
-// so chunks are kept small (short items, short chains) as long as every item still amortises its fixed cost (claim,
-// dependency check, program staging: a few microseconds) -- measured optimum on BASELINE config 2: 24..64 nodes.
+// Chunk size.  At BASELINE-config-2 scale a pass is (chain of dependent items near the root) + (bulk throughput); the
+// chain costs about 6 us per chunk level plus 0.4 us per node on the longest path, so chunks are kept small as long as
+// an item still amortises its fixed cost -- measured optimum on config 2: about 12 nodes (sweeps in profiles/).
 static int32_t auto_chunk_nodes(int32_t n_nodes, int64_t groups) {
     int64_t ctas_per_chunk = (groups + kTileGroups - 1) / kTileGroups;
-    int64_t want_chunks = std::max<int64_t>(1, (148 * 24 + ctas_per_chunk - 1) / ctas_per_chunk);
+    int64_t want_chunks = std::max<int64_t>(1, (148 * 48 + ctas_per_chunk - 1) / ctas_per_chunk);
     int64_t cn = n_nodes / (want_chunks * 2);  // chunks end up between cn and 2*cn nodes
-    return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 24), 1 << 16);
+    return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 12), 1 << 16);
 }
 
 extern "C" {
@@ -1219,23 +1253,28 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     if (d_forced && (rc = c->d_forced_planes.ensure(tile_groups))) return rc;
     if ((rc = c->d_xcode.ensure((size_t)NC * tile_groups))) return rc;
     if ((rc = c->d_xvalid.ensure((size_t)NC * tile_groups))) return rc;
-    if ((rc = c->d_count.ensure(16))) return rc;
     if ((rc = c->d_err.ensure(1))) return rc;
     if ((rc = c->d_sync.ensure(sync_ints(*P, tile_groups)))) return rc;
-    const int n_owners = std::max(1, c->parts.n_parts);
-    size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);  // total records; one owner's region is cap / n_owners
+    // output regions: per owning rank in shard mode, else one per 32 column groups (see DevEnv::emit)
+    const int64_t W = (G_all + 31) / 32;
+    const bool by_columns = c->parts.n_parts == 0 && W <= 65535;
+    const int n_owners = by_columns ? (int)W : std::max(1, c->parts.n_parts);
+    if ((rc = c->d_count.ensure(2 * (size_t)std::max(16, n_owners)))) return rc;
+    size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);  // total records; one region is cap / n_owners
 
     pmfs_timing& tm = c->timing;
     const float h2d_keep = tm.h2d_ms;
     tm = pmfs_timing();
     tm.h2d_ms = h2d_keep;
     float fwd_ms = 0, bwd_ms = 0;
-    unsigned long long count = 0, counts[16] = {};
+    unsigned long long count = 0;
+    std::vector<unsigned long long>& counts = c->h_counts;
+    counts.assign((size_t)std::max(16, n_owners), 0);
     size_t region = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
         if ((rc = c->d_keys.ensure(cap))) return rc;
         region = c->d_keys.cap / (size_t)n_owners;
-        PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, 16 * sizeof(unsigned long long), c->stream));
+        PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, counts.size() * sizeof(unsigned long long), c->stream));
         PMFS_CUDA(cudaMemsetAsync(c->d_err.ptr, 0, sizeof(unsigned int), c->stream));
         fwd_ms = bwd_ms = 0;
         tm.n_launches = 0;
@@ -1257,7 +1296,9 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             wp.out_keys = c->d_keys.ptr;
             wp.out_count = c->d_count.ptr;
             wp.out_cap = region;
-            wp.n_owners = n_owners;
+            wp.n_owners = by_columns ? 1 : n_owners;
+            wp.n_regions = by_columns ? (int32_t)W : 0;
+            wp.region_base = g0 / 32;
             for (int r = 0; r <= c->parts.n_parts; r++) wp.owner_bound[r] = c->parts.bound[r];
             wp.err_flag = c->d_err.ptr;
             wp.pos_bits = pos_bits;
@@ -1289,7 +1330,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             }
         }
         unsigned int err = 0;
-        PMFS_CUDA(cudaMemcpyAsync(counts, c->d_count.ptr, sizeof(counts), cudaMemcpyDeviceToHost, c->stream));
+        PMFS_CUDA(cudaMemcpyAsync(counts.data(), c->d_count.ptr, counts.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
         PMFS_CUDA(cudaMemcpyAsync(&err, c->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
         if (tile_groups >= G_all) {
@@ -1348,8 +1389,24 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
         if ((rc = c->d_out.ensure((size_t)n))) return rc;
         cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
+        int lo = kPayloadBits;
+        const int hi = kPayloadBits + pos_bits + node_bits;
+        if (by_columns) {
+            // regions are in column order and every node's records inside a region are contiguous and column-ordered:
+            // pack the regions, then a stable sort on the NODE bits alone gives the (node,pos) order
+            std::vector<unsigned long long>& off = c->h_offsets;
+            off.assign(counts.size(), 0);
+            for (int r = 1; r < n_owners; r++) off[r] = off[r - 1] + counts[r - 1];
+            unsigned long long* d_off = c->d_count.ptr + counts.size();
+            PMFS_CUDA(cudaMemcpyAsync(d_off, off.data(), (size_t)n_owners * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+            const unsigned bx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, ((size_t)n / n_owners + 255) / 256));
+            compact_regions_kernel<<<dim3(bx, (unsigned)n_owners), 256, 0, c->stream>>>(c->d_keys.ptr, region, c->d_count.ptr, d_off,
+                                                                                       c->d_keys_alt.ptr);
+            tm.n_launches += 1;
+            kb = cub::DoubleBuffer<unsigned long long>(c->d_keys_alt.ptr, c->d_keys.ptr);
+            lo = kPayloadBits + pos_bits;
+        }
         size_t tmp_bytes = 0;
-        const int lo = kPayloadBits, hi = kPayloadBits + pos_bits + node_bits;
         PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
         if ((rc = c->d_sort_tmp.ensure(tmp_bytes))) return rc;
         PMFS_CUDA(cub::DeviceRadixSort::SortKeys(c->d_sort_tmp.ptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
