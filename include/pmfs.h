@@ -153,6 +153,18 @@ int pmfs_run_fitch_static(pmfs_ctx* ctx, const uint8_t* d_msa_nibbles, int64_t r
                           int64_t n_cols, const uint8_t* d_consensus_code, const uint8_t* d_root_forced_code,
                           pmfs_mut* d_out, int64_t out_capacity, int64_t* n_out);
 
+/* Greedy <=6-run packing of the last result (pmfs_run / pmfs_run_device / pmfs_sort_records) ON THE DEVICE, followed by
+ * the download of the packed lists.  Replaces the per-node loop of src/panman.cpp:1439-1455 with the NucMut range
+ * constructor src/panman.hpp:86-128: only 24 bytes per up-to-6 records cross PCIe instead of 12 per
+ * record.  *out: n_out packed records, all nodes concatenated; node v's list is out[node_off[v] .. node_off[v+1]).
+ * Both arrays live in pinned buffers owned by the context, valid until the next call. */
+typedef struct {
+    int32_t nucPosition, nucGapPosition, primaryBlockId, secondaryBlockId;
+    uint32_t mutInfo; /* uint8_t in the reference's NucMut (src/panman.hpp:55-61); widened for a padding-free layout */
+    uint32_t nucs;
+} pmfs_host_nucmut_t;
+int pmfs_pack_last(pmfs_ctx* ctx, const pmfs_host_nucmut_t** out, int64_t* n_out, const int64_t** node_off);
+
 int pmfs_get_timing(pmfs_ctx* ctx, pmfs_timing* t);
 
 /* Plan introspection (tests, DESIGN.md numbers). */

@@ -13,10 +13,7 @@ extern "C" {
 #endif
 
 /* NucMut (src/panman.hpp:55-61) with mutInfo widened to 32 bits so the C layout has no padding. */
-typedef struct {
-    int32_t nucPosition, nucGapPosition, primaryBlockId, secondaryBlockId;
-    uint32_t mutInfo, nucs;
-} pmfs_host_nucmut;
+typedef pmfs_host_nucmut_t pmfs_host_nucmut;
 
 const char* pmfs_host_last_error(void);
 void pmfs_host_free(void* p);

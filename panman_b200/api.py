@@ -73,7 +73,7 @@ class SynthSpec:
 _lib = None
 
 EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run",
-           "pmfs_result_free", "pmfs_run_device", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
+           "pmfs_result_free", "pmfs_run_device", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
 
@@ -103,6 +103,7 @@ def lib():
         L.pmfs_set_shard.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
         L.pmfs_get_parts.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_void_p]
         L.pmfs_sort_records.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
+        L.pmfs_pack_last.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_void_p)]
         L.pmfs_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.pmfs_get_timing.argtypes = [C.c_void_p, C.POINTER(_Timing)]
         L.pmfs_get_plan_info.argtypes = [C.c_void_p, C.POINTER(_PlanInfo)]
@@ -243,6 +244,17 @@ class Context:
         out = C.c_void_p()
         _check(self._L.pmfs_sort_records(self._h, d_records or None, n, C.byref(out)))
         return out.value or 0
+
+    def pack_last(self):
+        """Device-side <=6-run packing of the last result -> (node_off int64[V+1], packed NUCMUT_DTYPE array)."""
+        out, off, n = C.c_void_p(), C.c_void_p(), C.c_int64()
+        _check(self._L.pmfs_pack_last(self._h, C.byref(out), C.byref(n), C.byref(off)))
+        node_off = np.frombuffer((C.c_char * ((self.n_nodes + 1) * 8)).from_address(off.value), dtype="<i8").copy()
+        if n.value:
+            nuc = np.frombuffer((C.c_char * (n.value * NUCMUT_DTYPE.itemsize)).from_address(out.value), dtype=NUCMUT_DTYPE).copy()
+        else:
+            nuc = np.zeros(0, NUCMUT_DTYPE)
+        return node_off, nuc
 
     def download(self, n: int) -> np.ndarray:
         res = np.zeros(n, MUT_DTYPE)

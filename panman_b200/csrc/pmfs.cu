@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include <algorithm>
 #include <chrono>
@@ -712,6 +713,58 @@ __global__ void assemble_kernel(const unsigned long long* __restrict__ recs, int
     out[i] = m;
 }
 
+// ---- device-side <=6-run packing (src/panman.cpp:1439-1455 + NucMut range ctor src/panman.hpp:86-128) ---------------------
+// Records are sorted by (node,pos).  A RUN is a maximal stretch of one node with consecutive positions and one type;
+// the greedy rule of the reference cuts every run into pieces of 6 from its start, so a packed record starts at every
+// record whose index inside its run is a multiple of 6.  run_start[i] = index of the first record of i's run
+// (max-scan of "i if a run starts here"), starts are counted by a prefix sum, and each start packs up to 6 records.
+struct PackedNucMut {  // pmfs_host_nucmut (include/pmfs_host.h)
+    int32_t nucPosition, nucGapPosition, primaryBlockId, secondaryBlockId;
+    uint32_t mutInfo, nucs;
+};
+__global__ void pack_runstart_kernel(const pmfs_mut* __restrict__ m, int64_t n, int32_t* __restrict__ run_start) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    bool brk = i == 0;
+    if (!brk) {
+        const pmfs_mut a = m[i - 1], b = m[i];
+        brk = a.node != b.node || b.pos != a.pos + 1 || a.type != b.type;
+    }
+    run_start[i] = brk ? (int32_t)i : 0;
+}
+__global__ void pack_isstart_kernel(const int32_t* __restrict__ run_start, int64_t n, int32_t* __restrict__ is_start) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) is_start[i] = ((int32_t)i - run_start[i]) % 6 == 0;
+}
+__global__ void pack_emit_kernel(const pmfs_mut* __restrict__ m, const int32_t* __restrict__ run_start,
+                                 const int32_t* __restrict__ out_idx, int64_t n, PackedNucMut* __restrict__ out,
+                                 int32_t* __restrict__ out_node) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int32_t rs = run_start[i];
+    if (((int32_t)i - rs) % 6 != 0) return;
+    int len = 1;
+    while (len < 6 && i + len < n && run_start[i + len] == rs) len++;
+    PackedNucMut r;
+    r.nucPosition = m[i].pos;
+    r.nucGapPosition = -1;
+    r.primaryBlockId = 0;
+    r.secondaryBlockId = -1;
+    r.mutInfo = (uint32_t)(uint8_t)((len << 4) + m[i].type);
+    r.nucs = 0;
+    for (int k = 0; k < len; k++) r.nucs += (uint32_t)m[i + k].code << (4 * (5 - k));
+    out[out_idx[i]] = r;
+    out_node[out_idx[i]] = m[i].node;
+}
+// node_off[v] = first packed record of node >= v; node_off[n_nodes] = n_packed
+__global__ void pack_offsets_kernel(const int32_t* __restrict__ out_node, int64_t n_packed, int32_t n_nodes, int64_t* __restrict__ node_off) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > n_packed) return;
+    const int32_t lo = k == 0 ? 0 : out_node[k - 1] + 1;
+    const int32_t hi = k == n_packed ? n_nodes : out_node[k];
+    for (int32_t v = lo; v <= hi; v++) node_off[v] = k;
+}
+
 // region r's records (count[r] of them at src + r*cap) -> dst + offset[r]: makes the per-region output contiguous
 __global__ void compact_regions_kernel(const unsigned long long* __restrict__ src, unsigned long long cap,
                                        const unsigned long long* __restrict__ count, const unsigned long long* __restrict__ offset,
@@ -907,6 +960,14 @@ struct pmfs_ctx {
     // host-path staging
     DevBuf<uint8_t> d_msa, d_cons, d_forced;
     std::vector<unsigned long long> h_counts, h_offsets;
+    // device-side packing (pmfs_pack_last)
+    DevBuf<int32_t> d_pk_run, d_pk_idx, d_pk_node;
+    DevBuf<PackedNucMut> d_pk_out;
+    DevBuf<int64_t> d_pk_off;
+    DevBuf<uint8_t> d_pk_tmp;
+    PackedNucMut* h_pk_out = nullptr;  // pinned
+    int64_t* h_pk_off = nullptr;       // pinned
+    size_t h_pk_out_cap = 0, h_pk_off_cap = 0;
     pmfs_mut* h_out = nullptr;  // pinned
     size_t h_out_cap = 0;
     int64_t last_n_out = 0;
@@ -1080,6 +1141,10 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_synth_node.release(); c->d_synth_pslot.release(); c->d_synth_mslot.release();
     c->d_synth_state[0].release(); c->d_synth_state[1].release();
     if (c->h_out) cudaFreeHost(c->h_out);
+    if (c->h_pk_out) cudaFreeHost(c->h_pk_out);
+    if (c->h_pk_off) cudaFreeHost(c->h_pk_off);
+    c->d_pk_run.release(); c->d_pk_idx.release(); c->d_pk_node.release(); c->d_pk_out.release(); c->d_pk_off.release();
+    c->d_pk_tmp.release();
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -1492,6 +1557,68 @@ int pmfs_sort_records(pmfs_ctx* c, void* d_records, int64_t n, pmfs_mut** d_out)
     PMFS_CUDA(cudaStreamSynchronize(c->stream));
     c->last_n_out = n;
     *d_out = c->d_out.ptr;
+    return PMFS_OK;
+}
+
+// Greedy <=6-run packing of the last result ON THE DEVICE, then download of the packed NucMut lists.
+int pmfs_pack_last(pmfs_ctx* c, const pmfs_host_nucmut_t** out, int64_t* n_out, const int64_t** node_off) {
+    if (!c || !out || !n_out || !node_off) {
+        g_error = "pmfs_pack_last: null argument";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    const int64_t n = c->last_n_out;
+    const int32_t V = c->plan.n_nodes;
+    int rc;
+    if ((rc = c->d_pk_off.ensure((size_t)V + 1))) return rc;
+    if (c->h_pk_off_cap < (size_t)V + 1) {
+        if (c->h_pk_off) cudaFreeHost(c->h_pk_off);
+        c->h_pk_off = nullptr;
+        PMFS_CUDA(cudaMallocHost(&c->h_pk_off, ((size_t)V + 1) * sizeof(int64_t)));
+        c->h_pk_off_cap = (size_t)V + 1;
+    }
+    int64_t n_packed = 0;
+    if (n > 0) {
+        if (n > 0x7fffffffll) {
+            g_error = "pmfs_pack_last: too many records";
+            return PMFS_ERR_ARG;
+        }
+        if ((rc = c->d_pk_run.ensure((size_t)n))) return rc;
+        if ((rc = c->d_pk_idx.ensure((size_t)n + 1))) return rc;
+        const unsigned nb = (unsigned)((n + 255) / 256);
+        pack_runstart_kernel<<<nb, 256, 0, c->stream>>>(c->d_out.ptr, n, c->d_pk_run.ptr);
+        size_t t1 = 0, t2 = 0;
+        PMFS_CUDA(cub::DeviceScan::InclusiveScan(nullptr, t1, c->d_pk_run.ptr, c->d_pk_run.ptr, cub::Max(), (int)n, c->stream));
+        PMFS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, t2, c->d_pk_idx.ptr, c->d_pk_idx.ptr, (int)n + 1, c->stream));
+        if ((rc = c->d_pk_tmp.ensure(std::max(t1, t2)))) return rc;
+        PMFS_CUDA(cub::DeviceScan::InclusiveScan(c->d_pk_tmp.ptr, t1, c->d_pk_run.ptr, c->d_pk_run.ptr, cub::Max(), (int)n, c->stream));
+        pack_isstart_kernel<<<nb, 256, 0, c->stream>>>(c->d_pk_run.ptr, n, c->d_pk_idx.ptr);
+        PMFS_CUDA(cudaMemsetAsync(c->d_pk_idx.ptr + n, 0, sizeof(int32_t), c->stream));
+        PMFS_CUDA(cub::DeviceScan::ExclusiveSum(c->d_pk_tmp.ptr, t2, c->d_pk_idx.ptr, c->d_pk_idx.ptr, (int)n + 1, c->stream));
+        int32_t total = 0;
+        PMFS_CUDA(cudaMemcpyAsync(&total, c->d_pk_idx.ptr + n, sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        PMFS_CUDA(cudaStreamSynchronize(c->stream));
+        n_packed = total;
+        if ((rc = c->d_pk_out.ensure((size_t)n_packed))) return rc;
+        if ((rc = c->d_pk_node.ensure((size_t)n_packed))) return rc;
+        pack_emit_kernel<<<nb, 256, 0, c->stream>>>(c->d_out.ptr, c->d_pk_run.ptr, c->d_pk_idx.ptr, n, c->d_pk_out.ptr, c->d_pk_node.ptr);
+    }
+    pack_offsets_kernel<<<(unsigned)((n_packed + 256) / 256), 256, 0, c->stream>>>(c->d_pk_node.ptr, n_packed, V, c->d_pk_off.ptr);
+    PMFS_CUDA(cudaGetLastError());
+    if (c->h_pk_out_cap < (size_t)std::max<int64_t>(1, n_packed)) {
+        if (c->h_pk_out) cudaFreeHost(c->h_pk_out);
+        c->h_pk_out = nullptr;
+        const size_t want = (size_t)n_packed + (size_t)n_packed / 4 + 1024;
+        PMFS_CUDA(cudaMallocHost(&c->h_pk_out, want * sizeof(PackedNucMut)));
+        c->h_pk_out_cap = want;
+    }
+    if (n_packed > 0)
+        PMFS_CUDA(cudaMemcpyAsync(c->h_pk_out, c->d_pk_out.ptr, (size_t)n_packed * sizeof(PackedNucMut), cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaMemcpyAsync(c->h_pk_off, c->d_pk_off.ptr, ((size_t)V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    *out = (const pmfs_host_nucmut_t*)c->h_pk_out;
+    *n_out = n_packed;
+    *node_off = c->h_pk_off;
     return PMFS_OK;
 }
 

@@ -18,6 +18,33 @@ def run_gpu(tree, algo, msa_codes, cons, forced=None, chunk_nodes=0, tile_cols=0
         return ctx.run(algo, nib, int(cons.shape[0]), cons, forced)
 
 
+def test_device_side_packing(small_cases, c1):
+    """pmfs_pack_last: greedy <=6-run packing on the device == the reference rule (golden NucMut arrays)."""
+    z = small_cases
+    for name in z["case_names"]:
+        tree, msa, cons, forced = G.case_inputs(z, str(name))
+        for algo in (0, 1):
+            with api.Context(tree) as ctx:
+                ctx.run(algo, api.pack_nibbles(msa), int(cons.shape[0]), cons, forced)
+                off, nuc = ctx.pack_last()
+            assert (off == z[f"{name}/nuc_off{algo}"]).all(), (name, algo)
+            assert G.same_nuc(nuc, z[f"{name}/nuc{algo}"]), (name, algo)
+    key = "v00_"
+    tree = G.c1_tree(c1)
+    msa = G.unpack_nibbles(c1["msa_nibbles"], int(c1["n_cols"]))
+    with api.Context(tree) as ctx:
+        ctx.run(api.FITCH, api.pack_nibbles(msa), int(c1["n_cols"]), c1[key + "consensus"], None)
+        off, nuc = ctx.pack_last()
+    assert nuc.shape[0] == int(c1[key + "n_nuc"])
+    assert G.digest_nuc(off, nuc) == str(c1[key + "nuc_sha256"])
+    # no records at all: every list is empty
+    tree = synth._flatten([None, None])
+    with api.Context(tree) as ctx:
+        ctx.run(api.FITCH, np.zeros((0, 3), np.uint8), 5, np.zeros(5, np.uint8))
+        off, nuc = ctx.pack_last()
+    assert nuc.shape[0] == 0 and (off == 0).all()
+
+
 def test_golden_small_cases(small_cases):
     z = small_cases
     for name in z["case_names"]:
