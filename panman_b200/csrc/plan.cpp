@@ -266,15 +266,27 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
         P.bwd_prog.push_back(0);
     }
 
-    // ---- level lists
+    // ---- execution order: critical-path list scheduling.  Any order in which dependencies come first is valid (the
+    // kernels claim items in this order and wait for unfinished dependencies).  Bottom-up: a chunk's longest remaining
+    // chain is its distance to the root chunk, so DEEPEST chunks go first -- the long chains get going at once and the
+    // many shallow leaf chunks are the filler that keeps the SMs busy while the chains climb.  Top-down: the longest
+    // remaining chain is the chunk's height, so TALLEST first.  (Plain level order leaves the whole chain of narrow
+    // levels near the root exposed at the end / start of a pass.)  lvl_off only counts chunks per height / depth.
+    // remaining chain length in program words: up[c] = own + up[parent] (bottom-up pass), down[c] = own + max down[child]
+    std::vector<int64_t> up(NC, 0), down(NC, 0);
+    for (int32_t c = 0; c < NC; c++) up[c] = P.chunks[c].fwd_len + (P.chunks[c].parent >= 0 ? up[P.chunks[c].parent] : 0);
+    for (int32_t c = NC - 1; c >= 0; c--) {
+        down[c] += P.chunks[c].bwd_len;
+        if (P.chunks[c].parent >= 0) down[P.chunks[c].parent] = std::max(down[P.chunks[c].parent], down[c]);
+    }
     auto make_levels = [&](bool fwd, std::vector<int32_t>& order, std::vector<int32_t>& off) {
         int32_t nl = 0;
         for (auto& c : P.chunks) nl = std::max(nl, (fwd ? c.height : c.depth) + 1);
         order.resize(NC);
         std::iota(order.begin(), order.end(), 0);
         std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
-            int32_t lx = fwd ? P.chunks[x].height : P.chunks[x].depth, ly = fwd ? P.chunks[y].height : P.chunks[y].depth;
-            if (lx != ly) return lx < ly;
+            const int64_t px = fwd ? up[x] : down[x], py = fwd ? up[y] : down[y];
+            if (px != py) return px > py;
             int32_t wx = fwd ? P.chunks[x].fwd_len : P.chunks[x].bwd_len, wy = fwd ? P.chunks[y].fwd_len : P.chunks[y].bwd_len;
             return wx > wy;
         });

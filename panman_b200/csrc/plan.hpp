@@ -70,7 +70,7 @@ struct Plan {
     std::vector<uint32_t> fwd_prog, bwd_prog;
     std::vector<uint32_t> fwd_stream, bwd_stream;
     std::vector<Chunk> chunks;
-    // chunk ids grouped by level, heaviest first inside a level; level l spans [lvl_off[l], lvl_off[l+1])
+    // chunk ids in execution order (dependencies first, longest remaining chain first); lvl_off: chunks per height / depth
     std::vector<int32_t> fwd_order, bwd_order;
     std::vector<int32_t> fwd_lvl_off, bwd_lvl_off;
     int32_t fwd_stack_depth = 0, bwd_stack_depth = 0;
