@@ -120,14 +120,16 @@ int pmfs_run_device(pmfs_ctx* ctx, int algo, const uint8_t* d_msa_nibbles, int64
  * pmfs_set_shard puts a context in shard mode: its columns are [pos_offset, pos_offset+n_cols) of a total_cols-wide
  * alignment, and node ids [node_bounds[r], node_bounds[r+1]) are owned by rank r (n_parts <= 16; n_parts = 0 leaves
  * shard mode).  In shard mode pmfs_run_device emits global positions, does NOT order the records and returns
- * *d_out = NULL.  The records (one opaque 64-bit word each) are written straight into one region per owning rank:
- * pmfs_get_parts gives the base device pointer, the region stride in records and the counts (owner r's records are
- * d_records[r*region_stride .. +counts[r])) for an all-to-all, and the owner orders everything it received with
- * pmfs_sort_records (d_records is overwritten; the result is valid until the next run), which yields its nodes'
- * complete (node,pos)-sorted lists. */
+ * *d_out = NULL.  The records (one opaque 64-bit word each) are grouped by owning rank: pmfs_get_parts gives the base
+ * device pointer and, per owner r, offsets[r] and counts[r] in records (owner r's block is
+ * d_records[offsets[r] .. offsets[r]+counts[r])) for an all-to-all.  *column_ordered is 1 when every block is laid out
+ * in column-region order (always, unless ranks x column count is enormous).  The owner concatenates the blocks it
+ * received IN SOURCE-RANK ORDER and orders them with pmfs_sort_records (d_records is overwritten; the result is valid
+ * until the next run): with column_ordered = 1 on every source a stable sort on the node bits suffices, pass 0 to force
+ * a full sort.  The result is the owner's nodes' complete (node,pos)-sorted lists. */
 int pmfs_set_shard(pmfs_ctx* ctx, int64_t pos_offset, int64_t total_cols, int32_t n_parts, const int32_t* node_bounds);
-int pmfs_get_parts(pmfs_ctx* ctx, const void** d_records, int64_t* region_stride, int64_t* counts);
-int pmfs_sort_records(pmfs_ctx* ctx, void* d_records, int64_t n, pmfs_mut** d_out);
+int pmfs_get_parts(pmfs_ctx* ctx, const void** d_records, int64_t* offsets, int64_t* counts, int* column_ordered);
+int pmfs_sort_records(pmfs_ctx* ctx, void* d_records, int64_t n, int column_ordered, pmfs_mut** d_out);
 
 /* Copies device records of the last pmfs_run_device / pmfs_sort_records to a caller buffer of at least n records. */
 int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);

@@ -101,8 +101,8 @@ def lib():
         L.pmfs_run_fitch_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
         L.pmfs_set_shard.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
-        L.pmfs_get_parts.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_void_p]
-        L.pmfs_sort_records.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
+        L.pmfs_get_parts.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
+        L.pmfs_sort_records.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.POINTER(C.c_void_p)]
         L.pmfs_pack_last.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_void_p)]
         L.pmfs_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.pmfs_get_timing.argtypes = [C.c_void_p, C.POINTER(_Timing)]
@@ -232,17 +232,19 @@ class Context:
         self._n_parts = b.shape[0] - 1
 
     def get_parts(self):
-        """-> (device base pointer, region stride in records, counts list) of the last shard-mode run: owner r's
-        64-bit records are base[r*stride : r*stride + counts[r]]."""
-        base, stride = C.c_void_p(), C.c_int64()
+        """-> (device base pointer, offsets list, counts list, column_ordered) of the last shard-mode run: owner r's
+        64-bit records are base[offsets[r] : offsets[r] + counts[r]]."""
+        base, flag = C.c_void_p(), C.c_int()
+        offsets = np.zeros(16, np.int64)
         counts = np.zeros(16, np.int64)
-        _check(self._L.pmfs_get_parts(self._h, C.byref(base), C.byref(stride), counts.ctypes.data))
-        return base.value or 0, stride.value, counts[: self._n_parts].tolist()
+        _check(self._L.pmfs_get_parts(self._h, C.byref(base), offsets.ctypes.data, counts.ctypes.data, C.byref(flag)))
+        return base.value or 0, offsets[: self._n_parts].tolist(), counts[: self._n_parts].tolist(), bool(flag.value)
 
-    def sort_records(self, d_records: int, n: int) -> int:
-        """Order `n` received 64-bit records by (node, pos) -> device pointer to pmfs_mut records."""
+    def sort_records(self, d_records: int, n: int, column_ordered: bool = False) -> int:
+        """Order `n` received 64-bit records (blocks concatenated in source-rank order) by (node, pos) -> device
+        pointer to pmfs_mut records."""
         out = C.c_void_p()
-        _check(self._L.pmfs_sort_records(self._h, d_records or None, n, C.byref(out)))
+        _check(self._L.pmfs_sort_records(self._h, d_records or None, n, int(column_ordered), C.byref(out)))
         return out.value or 0
 
     def pack_last(self):

@@ -440,11 +440,13 @@ struct DevEnv {
     // rank (column shards): see pmfs_set_shard.
     __device__ void emit(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
         if (p.n_regions > 0) {
+            int64_t own_base = 0;  // column shards: regions are owner-major (owner of this node's list, uniform in the warp)
+            for (int r = 1; r < p.n_owners; r++) own_base += (int32_t)node >= p.owner_bound[r] ? p.n_regions : 0;
 #pragma unroll
             for (int j = 0; j < kNG; j++) {
                 if (!__any_sync(0xffffffffu, m[j] != 0)) continue;
                 const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
-                const int64_t region = p.region_base + ((gwarp + j * kTPB) >> 5);
+                const int64_t region = own_base + p.region_base + ((gwarp + j * kTPB) >> 5);
                 unsigned long long base = 0;
                 if (lane == 0) base = atomicAdd(p.out_count + region, (unsigned long long)total);
                 base = __shfl_sync(0xffffffffu, base, 0);
@@ -944,7 +946,8 @@ struct pmfs_ctx {
     PartBounds parts = {};
     int64_t part_counts[16] = {};
     unsigned long long* parts_keys = nullptr;
-    int64_t parts_stride = 0;
+    int64_t part_offsets[16] = {};
+    bool parts_by_columns = false;
     DevBuf<unsigned long long> d_rkeys_alt;
     DevBuf<uint8_t> d_sort_tmp2;
     DevBuf<int32_t> d_fwd_len, d_bwd_len, d_fwd_order, d_bwd_order, d_int_to_node, d_row_to_node;
@@ -1322,8 +1325,9 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     if ((rc = c->d_sync.ensure(sync_ints(*P, tile_groups)))) return rc;
     // output regions: per owning rank in shard mode, else one per 32 column groups (see DevEnv::emit)
     const int64_t W = (G_all + 31) / 32;
-    const bool by_columns = c->parts.n_parts == 0 && W <= 65535;
-    const int n_owners = by_columns ? (int)W : std::max(1, c->parts.n_parts);
+    const int n_parts = std::max(1, c->parts.n_parts);
+    const bool by_columns = W * n_parts <= 65535;
+    const int n_owners = by_columns ? (int)(W * n_parts) : n_parts;  // number of output regions
     if ((rc = c->d_count.ensure(2 * (size_t)std::max(16, n_owners)))) return rc;
     size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);  // total records; one region is cap / n_owners
 
@@ -1361,7 +1365,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             wp.out_keys = c->d_keys.ptr;
             wp.out_count = c->d_count.ptr;
             wp.out_cap = region;
-            wp.n_owners = by_columns ? 1 : n_owners;
+            wp.n_owners = n_parts;
             wp.n_regions = by_columns ? (int32_t)W : 0;
             wp.region_base = g0 / 32;
             for (int r = 0; r <= c->parts.n_parts; r++) wp.owner_bound[r] = c->parts.bound[r];
@@ -1438,9 +1442,36 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     if (c->parts.n_parts > 0) {
         // shard mode: records were emitted straight into one region per owning rank and stay unordered; the owner
         // orders what it receives (pmfs_sort_records)
-        for (int r = 0; r < 16; r++) c->part_counts[r] = r < n_owners ? (int64_t)counts[r] : 0;
-        c->parts_keys = c->d_keys.ptr;
-        c->parts_stride = (int64_t)region;
+        c->parts_by_columns = by_columns;
+        if (by_columns) {
+            // pack the (owner, column region) regions: every owner's records become one contiguous block whose regions
+            // are in column order, which is what lets the owner order its inbox with a stable sort on the node bits
+            if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
+            std::vector<unsigned long long>& off = c->h_offsets;
+            off.assign(counts.size(), 0);
+            for (int r = 1; r < n_owners; r++) off[r] = off[r - 1] + counts[r - 1];
+            for (int o = 0; o < 16; o++) {
+                c->part_counts[o] = 0;
+                c->part_offsets[o] = o < n_parts ? (int64_t)off[(size_t)o * W] : n;
+                for (int64_t w = 0; o < n_parts && w < W; w++) c->part_counts[o] += (int64_t)counts[(size_t)o * W + w];
+            }
+            if (n > 0) {
+                unsigned long long* d_off = c->d_count.ptr + counts.size();
+                PMFS_CUDA(cudaMemcpyAsync(d_off, off.data(), (size_t)n_owners * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+                const unsigned bx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, ((size_t)n / n_owners + 255) / 256));
+                compact_regions_kernel<<<dim3(bx, (unsigned)n_owners), 256, 0, c->stream>>>(c->d_keys.ptr, region, c->d_count.ptr, d_off,
+                                                                                           c->d_keys_alt.ptr);
+                PMFS_CUDA(cudaStreamSynchronize(c->stream));
+                tm.n_launches += 1;
+            }
+            c->parts_keys = c->d_keys_alt.ptr;
+        } else {
+            for (int o = 0; o < 16; o++) {
+                c->part_counts[o] = o < n_parts ? (int64_t)counts[o] : 0;
+                c->part_offsets[o] = (int64_t)region * o;
+            }
+            c->parts_keys = c->d_keys.ptr;
+        }
         tm.sort_ms = 0;
         tm.total_ms = tm.h2d_ms + tm.forward_ms + tm.backward_ms;
         c->last_n_out = 0;
@@ -1516,18 +1547,21 @@ int pmfs_set_shard(pmfs_ctx* c, int64_t pos_offset, int64_t total_cols, int32_t 
     return PMFS_OK;
 }
 
-int pmfs_get_parts(pmfs_ctx* c, const void** d_records, int64_t* region_stride, int64_t* counts) {
-    if (!c || !d_records || !region_stride || !counts || c->parts.n_parts <= 0) {
+int pmfs_get_parts(pmfs_ctx* c, const void** d_records, int64_t* offsets, int64_t* counts, int* column_ordered) {
+    if (!c || !d_records || !offsets || !counts || !column_ordered || c->parts.n_parts <= 0) {
         g_error = "pmfs_get_parts: context is not in shard mode";
         return PMFS_ERR_STATE;
     }
     *d_records = c->parts_keys;
-    *region_stride = c->parts_stride;
-    for (int r = 0; r < c->parts.n_parts; r++) counts[r] = c->part_counts[r];
+    *column_ordered = c->parts_by_columns ? 1 : 0;
+    for (int r = 0; r < c->parts.n_parts; r++) {
+        offsets[r] = c->part_offsets[r];
+        counts[r] = c->part_counts[r];
+    }
     return PMFS_OK;
 }
 
-int pmfs_sort_records(pmfs_ctx* c, void* d_records, int64_t n, pmfs_mut** d_out) {
+int pmfs_sort_records(pmfs_ctx* c, void* d_records, int64_t n, int column_ordered, pmfs_mut** d_out) {
     if (!c || n < 0 || (n > 0 && !d_records) || !d_out || n > 0x7fffffffll) {
         g_error = "pmfs_sort_records: bad argument";
         return PMFS_ERR_ARG;
@@ -1547,7 +1581,9 @@ int pmfs_sort_records(pmfs_ctx* c, void* d_records, int64_t n, pmfs_mut** d_out)
         if ((rc = c->d_rkeys_alt.ensure((size_t)n))) return rc;
         cub::DoubleBuffer<unsigned long long> kb((unsigned long long*)d_records, c->d_rkeys_alt.ptr);
         size_t tmp_bytes = 0;
-        const int lo = kPayloadBits, hi = kPayloadBits + pos_bits + node_bits;
+        // blocks in source-rank order, each in column-region order with every node's records contiguous and
+        // column-ordered inside a region: a STABLE sort on the node bits alone is enough (2 radix passes, not 4)
+        const int lo = column_ordered ? kPayloadBits + pos_bits : kPayloadBits, hi = kPayloadBits + pos_bits + node_bits;
         PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
         if ((rc = c->d_sort_tmp2.ensure(tmp_bytes))) return rc;
         PMFS_CUDA(cub::DeviceRadixSort::SortKeys(c->d_sort_tmp2.ptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));

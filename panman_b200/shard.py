@@ -127,25 +127,49 @@ def _as_tensor(ptr: int, n: int, dtype_str: str, device):
     return torch.as_tensor(_Wrap(), device=device)
 
 
-def exchange_parts(ctx, rank: int, world: int, device, group=None):
+_xbuf = {}
+
+
+def exchange_parts(ctx, rank: int, world: int, device, group=None, same_stream: bool = True):
     """The data path's single exchange on GPUs, after a shard-mode pmfs_run_device on every rank: all-to-all of the
     64-bit records (already grouped by owning rank when they were emitted) over NCCL, then each rank orders what it
-    received with the library's radix sort.  Returns (device pointer to this rank's pmfs_mut records, count)."""
+    received with the library's radix sort.  Returns (device pointer to this rank's pmfs_mut records, count).
+
+    same_stream: the context runs on torch's current stream (pmfs_set_stream), so the sort is ordered after the
+    all-to-all without a host synchronisation.  Small tensors and the inbox are reused across calls."""
     import torch
     import torch.distributed as dist
 
-    base, stride, send = ctx.get_parts()
-    mine = torch.tensor(send, dtype=torch.int64, device=device)
-    table = [torch.empty_like(mine) for _ in range(world)]
-    dist.all_gather(table, mine, group=group)
-    recv = torch.stack(table)[:, rank].tolist()  # the one host synchronisation of the exchange
+    base, offsets, send, col_ordered = ctx.get_parts()
+    key = (str(device), world)
+    if key not in _xbuf:
+        _xbuf[key] = {"h": torch.empty(world + 1, dtype=torch.int64).pin_memory(),
+                      "d": torch.empty(world + 1, dtype=torch.int64, device=device),
+                      "t": torch.empty((world, world + 1), dtype=torch.int64, device=device),
+                      "th": torch.empty((world, world + 1), dtype=torch.int64).pin_memory(),
+                      "inbox": torch.empty(0, dtype=torch.int64, device=device)}
+    B = _xbuf[key]
+    B["h"][:world] = torch.tensor(send, dtype=torch.int64)
+    B["h"][world] = int(col_ordered)
+    B["d"].copy_(B["h"], non_blocking=True)
+    dist.all_gather_into_tensor(B["t"].view(-1), B["d"], group=group)
+    B["th"].copy_(B["t"], non_blocking=True)
+    torch.cuda.current_stream(device).synchronize()  # the one host synchronisation of the exchange
+    recv = B["th"][:, rank].tolist()
+    all_ordered = bool(B["th"][:, world].min().item())
     total = sum(recv)
-    inbox = torch.empty(total, dtype=torch.int64, device=device)
-    outs = [_as_tensor(base + 8 * stride * r, send[r], "<i8", device) for r in range(world)]
-    ins = list(torch.split(inbox, recv))
-    dist.all_to_all(ins, outs, group=group)
-    torch.cuda.current_stream(device).synchronize()
-    out = ctx.sort_records(inbox.data_ptr(), total)
+    if B["inbox"].shape[0] < total:
+        B["inbox"] = torch.empty(int(total * 1.25) + 1024, dtype=torch.int64, device=device)
+    inbox = B["inbox"][:total]
+    if all_ordered:  # every owner's block is contiguous and the blocks follow each other: one all_to_all_single
+        outbox = _as_tensor(base + 8 * offsets[0], sum(send), "<i8", device)
+        dist.all_to_all_single(inbox, outbox, output_split_sizes=recv, input_split_sizes=send, group=group)
+    else:
+        outs = [_as_tensor(base + 8 * offsets[r], send[r], "<i8", device) for r in range(world)]
+        dist.all_to_all(list(torch.split(inbox, recv)), outs, group=group)
+    if not same_stream:
+        torch.cuda.current_stream(device).synchronize()
+    out = ctx.sort_records(inbox.data_ptr(), total, column_ordered=all_ordered)
     return out, total
 
 

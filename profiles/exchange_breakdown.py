@@ -22,14 +22,14 @@ def T():
 for it in range(6):
     dist.barrier(); t0 = T()
     ctx.run_device(api.FITCH, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr()); t1 = T()
-    base, stride, send = ctx.get_parts(); t2 = T()
+    base, offsets, send, col_ordered = ctx.get_parts(); t2 = T()
     mine = torch.tensor(send, dtype=torch.int64, device=dev); table = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(table, mine); recv = torch.stack(table)[:, rank].tolist(); t3 = T()
     total = sum(recv)
     inbox = torch.empty(total, dtype=torch.int64, device=dev)
-    outs = [shard._as_tensor(base + 8 * stride * r, send[r], "<i8", dev) for r in range(world)]
-    dist.all_to_all(list(torch.split(inbox, recv)), outs); t4 = T()
-    ctx.sort_records(inbox.data_ptr(), total); t5 = T()
+    outbox = shard._as_tensor(base + 8 * offsets[0], sum(send), "<i8", dev)
+    dist.all_to_all_single(inbox, outbox, output_split_sizes=recv, input_split_sizes=send); t4 = T()
+    ctx.sort_records(inbox.data_ptr(), total, column_ordered=col_ordered); t5 = T()
     if rank == 0:
         print(f"it{it}: run {1e3*(t1-t0):.3f} wrap {1e3*(t2-t1):.3f} counts {1e3*(t3-t2):.3f} a2a {1e3*(t4-t3):.3f} sort {1e3*(t5-t4):.3f} ms; timing {ctx.timing()}")
 dist.destroy_process_group()

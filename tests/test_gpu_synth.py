@@ -112,16 +112,18 @@ def test_shard_mode_two_contexts_equal_unsharded():
         assert bool((api.unpack_nibbles(m.cpu().numpy(), e - b) == api.unpack_nibbles(d_msa.cpu().numpy(), L)[:, b:e]).all())
         ctx.set_shard(b, L, bounds)
         _, n_r = ctx.run_device(api.FITCH, m.data_ptr(), st, N, e - b, c.data_ptr())
-        base, stride, cnt = ctx.get_parts()
-        assert sum(cnt) == n_r
-        parts.append([shard._as_tensor(base + 8 * stride * o, cnt[o], "<i8", "cuda").clone() for o in range(world)])
+        base, offs, cnt, col_ordered = ctx.get_parts()
+        assert sum(cnt) == n_r and col_ordered
+        parts.append([shard._as_tensor(base + 8 * offs[o], cnt[o], "<i8", "cuda").clone() for o in range(world)])
         ctxs.append(ctx)
         keep.append((m, c))
     for r in range(world):  # what rank r would receive from everybody
         inbox = torch.cat([parts[s][r] for s in range(world)])
-        ctxs[r].sort_records(inbox.data_ptr(), int(inbox.shape[0]))
-        got = ctxs[r].download(int(inbox.shape[0]))
         sel = (want["node"] >= nodes[r][0]) & (want["node"] < nodes[r][1])
-        assert G.same_muts(got, want[sel]) and (got["parent_code"] == want[sel]["parent_code"]).all(), r
+        for ordered in (True, False):  # stable sort on the node bits alone, and the full sort
+            box = inbox.clone()
+            ctxs[r].sort_records(box.data_ptr(), int(box.shape[0]), column_ordered=ordered)
+            got = ctxs[r].download(int(box.shape[0]))
+            assert G.same_muts(got, want[sel]) and (got["parent_code"] == want[sel]["parent_code"]).all(), (r, ordered)
     for ctx in ctxs:
         ctx.close()
