@@ -64,13 +64,18 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def mark(self):
+        """Samples taken before this call (warm-up) are dropped, unless nothing else arrives."""
+        self.skip = len(self.rows)
+
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
         sm, mx, reasons = [], [], set()
-        for l in self.rows:
+        rows = self.rows[getattr(self, "skip", 0):] or self.rows
+        for l in rows:
             f = [x.strip() for x in l.split(",")]
             if len(f) < 6:
                 continue
@@ -203,11 +208,12 @@ def main():
             shard.exchange_parts(ctx, rank, world, dev)
         return n
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()  # started before the warm-up so that nvidia-smi is already sampling when the timed region begins
     for _ in range(args.warmup):
         n_rec = step()
-    sampler = ClockSampler(local_rank)
     barrier()
-    sampler.start()
+    sampler.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     pass_ms, launches = 0.0, 0
     e0.record()

@@ -221,9 +221,9 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
             if (lane == 0) {
                 const uint32_t u = n_set % SETS, par = (n_set / SETS) & 1u;
                 mbar_wait(r.bars + (M::bSetEmpty + u) * 8, par ^ 1u);  // all walkers are done with the slot's previous set
-                mbar_arrive_expect_tx(r.bars + (M::bSetFull + u) * 8, kSetBytes);
-                bulk_g2s(r.smem + M::kSet + u * kSetBytes,
-                         p.S + ((int64_t)(e & ~kStreamSet) * p.ctas_per_chunk + tile) * (kSetBytes / 16), kSetBytes,
+                // one node's set for this tile: 4 quarters of `tile_w` groups, contiguous (leaf_bytes = tile_w * 16)
+                mbar_arrive_expect_tx(r.bars + (M::bSetFull + u) * 8, 4 * leaf_bytes);
+                bulk_g2s(r.smem + M::kSet + u * kSetBytes, p.S + (int64_t)(e & ~kStreamSet) * (4 * p.G) + g0 * 4, 4 * leaf_bytes,
                          r.bars + (M::bSetFull + u) * 8);
             }
             n_set++;
@@ -245,8 +245,9 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
 // items) never go through the walking threads: the producer warp streams them through the shared-memory rings with TMA
 // bulk copies, so a walk reads its operands from shared memory and only waits on an mbarrier that has normally
 // completed long before.  The walk program itself is staged in shared memory the same way.
-// Set arrays are TILE-MAJOR: S[internal id][tile][quarter][256 groups] (uint4), so one node's set for one tile is a
-// single contiguous 16 KB block (one TMA copy) and a warp's 128-bit stores are 512-byte segments.
+// Set arrays are TILE-MAJOR: S[internal id][tile][quarter][groups of the tile] (uint4; 256 groups per tile, fewer in
+// the last one), so one node's set for one tile is a single contiguous block of up to 16 KB (one TMA copy) and a
+// warp's 128-bit stores are 512-byte segments.  A node's row is exactly 4*G uint4: no padding.
 template <bool READONLY_SETS, int SETS>
 struct DevEnv {
     static constexpr int kGroups = kNG;
@@ -256,7 +257,8 @@ struct DevEnv {
     int64_t g[kNG];      // clamped column groups
     bool active[kNG];
     int64_t gwarp;       // (unclamped) column group of this warp's lane 0, first group slot
-    int64_t set_tile;    // uint4 offset of this tile inside one node's set rows: tile * 1024
+    int64_t set_tile;    // uint4 offset of this tile inside one node's set row: tile * 1024
+    int32_t tile_w;      // column groups of this tile (256, less for the last tile): stride between the 4 quarters
     uint32_t& n_leaf;    // running ring entry numbers of this CTA (same sequences as the producer's)
     uint32_t& n_set;
     uint4* fstk;         // [depth][kNG][4][kTPB]
@@ -271,6 +273,7 @@ struct DevEnv {
     __device__ DevEnv(const WalkParams& p_, const Ring& r, const ItemDesc& d, uint32_t slot, uint32_t prog_parity,
                       uint32_t& n_leaf_, uint32_t& n_set_, void* smem_generic)
         : p(p_), ring(r), gwarp((int64_t)d.tile * kTileGroups + (threadIdx.x & ~31)), set_tile((int64_t)d.tile * (kSetBytes / 16)),
+          tile_w((int32_t)min((int64_t)kTileGroups, p_.G - (int64_t)d.tile * kTileGroups)),
           n_leaf(n_leaf_), n_set(n_set_), fstk((uint4*)((char*)smem_generic + M::kStack)),
           bstk((uint32_t*)((char*)smem_generic + M::kStack)), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords),
           gprog(nullptr), sprog(r.smem + M::kProg + slot * (kProgWords * 4)) {
@@ -316,7 +319,7 @@ struct DevEnv {
         for (int j = 0; j < kNG; j++)
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const uint4 v = lds128(base + (i * kTileGroups + j * kTPB) * 16);
+                const uint4 v = lds128(base + (i * tile_w + j * kTPB) * 16);
                 s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
             }
         __syncwarp();
@@ -326,17 +329,22 @@ struct DevEnv {
 
     // direct access to the set arrays (sets of this work item itself; Sankoff D1 on the slow path)
     __device__ __forceinline__ int64_t set_index(uint32_t id, int j, int i) const {
-        return ((int64_t)id * p.ctas_per_chunk) * (kSetBytes / 16) + set_tile + i * kTileGroups + j * kTPB + threadIdx.x;
+        return (int64_t)id * (4 * p.G) + set_tile + i * tile_w + j * kTPB + threadIdx.x;
     }
     __device__ __forceinline__ void load_arr(const uint4* base, uint32_t id, Planes16 (&s)[kNG]) const {
 #pragma unroll
-        for (int j = 0; j < kNG; j++)
+        for (int j = 0; j < kNG; j++) {
+            if (!active[j]) {  // padding lane of the last tile: its slot lies outside this tile's block
+                zero16(s[j]);
+                continue;
+            }
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 const uint4* q = base + set_index(id, j, i);
                 const uint4 v = READONLY_SETS ? __ldg(q) : *q;
                 s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
             }
+        }
     }
     __device__ __forceinline__ void store_arr(uint4* base, uint32_t id, const Planes16 (&s)[kNG]) const {
 #pragma unroll
@@ -1280,7 +1288,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64;
     int64_t tile_groups = G_all;
     auto set_elems = [&](int64_t groups) {  // uint4 elements of one tile-major set array for `groups` column groups
-        return (size_t)I * (size_t)((groups + kTileGroups - 1) / kTileGroups) * (kSetBytes / 16);
+        return (size_t)I * 4 * (size_t)groups;
     };
     const bool fits_already = c->d_S.cap >= set_elems(G_all) && (algo != PMFS_SANKOFF || c->d_D.cap >= set_elems(G_all));
     if (!fits_already) {  // (cudaMemGetInfo costs a fraction of a millisecond: only ask when buffers have to grow)
@@ -1916,7 +1924,7 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
         PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, sort_tmp, kb, (int)cap, kPayloadBits, kPayloadBits + pos_bits + node_bits, c->stream));
     }
     Carver cv{scratch};
-    uint4* S = cv.take<uint4>(I * (size_t)((G + kTileGroups - 1) / kTileGroups) * (kSetBytes / 16));
+    uint4* S = cv.take<uint4>(I * 4 * (size_t)G);
     uint4* xcode = cv.take<uint4>(NC * (size_t)G);
     uint32_t* xvalid = cv.take<uint32_t>(NC * (size_t)G);
     uint4* cons_planes = cv.take<uint4>((size_t)G);
