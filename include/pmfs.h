@@ -110,6 +110,14 @@ int pmfs_run(pmfs_ctx* ctx, int algo, const uint8_t* msa_nibbles, int64_t row_st
              int64_t* n_out);
 void pmfs_result_free(pmfs_ctx* ctx, pmfs_mut* out);
 
+/* Same call on CHARACTERS, as the reference holds them (std::string rows, src/panman.cpp:1271-1315): rows of n_cols
+ * alignment characters, consensus and (optional) forced-root characters.  The characters are uploaded and converted to
+ * packed codes on the device with the reference's table getCodeFromNucleotide (src/panman.cpp:83-118; case-sensitive:
+ * '-', lower case and anything else is code 0), replacing the per-cell conversions of :1398-1406 / :1565-1571. */
+int pmfs_run_chars(pmfs_ctx* ctx, int algo, const char* msa_chars, int64_t row_stride_bytes, int32_t n_rows,
+                   int64_t n_cols, const char* consensus_chars, const char* root_forced_chars, pmfs_mut** out,
+                   int64_t* n_out);
+
 /* Device-resident variant (what `value` in bench.py times): every pointer is a DEVICE pointer on the context's
  * device; msa row stride must be a multiple of 16 bytes and the base 16-byte aligned.  Records stay on the device,
  * sorted by (node,pos); *d_out is owned by the context and valid until the next run. */

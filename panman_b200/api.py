@@ -72,7 +72,7 @@ class SynthSpec:
 
 _lib = None
 
-EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run",
+EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars",
            "pmfs_result_free", "pmfs_run_device", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
@@ -95,6 +95,7 @@ def lib():
         L.pmfs_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.pmfs_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+        L.pmfs_run_chars.argtypes = L.pmfs_run.argtypes
         L.pmfs_result_free.argtypes = [C.c_void_p, C.c_void_p]
         L.pmfs_result_free.restype = None
         L.pmfs_run_device.argtypes = L.pmfs_run.argtypes
@@ -201,6 +202,20 @@ class Context:
         if copy:
             self._L.pmfs_result_free(self._h, out)
         return res
+
+    def run_chars(self, algo: int, msa_chars: np.ndarray, consensus_chars: np.ndarray, forced_chars=None) -> np.ndarray:
+        """pmfs_run_chars: [rows, cols] uint8 alignment CHARACTERS in, host records out (conversion on the device)."""
+        msa = np.ascontiguousarray(msa_chars, dtype=np.uint8)
+        cons = np.ascontiguousarray(consensus_chars, dtype=np.uint8)
+        frc = None if forced_chars is None else np.ascontiguousarray(forced_chars, dtype=np.uint8)
+        n_cols = int(cons.shape[0])
+        out, n = C.c_void_p(), C.c_int64()
+        stride = msa.shape[1] if msa.ndim == 2 and msa.shape[0] else n_cols
+        _check(self._L.pmfs_run_chars(self._h, algo, msa.ctypes.data, stride, msa.shape[0], n_cols, cons.ctypes.data,
+                                      None if frc is None else frc.ctypes.data, C.byref(out), C.byref(n)))
+        if not n.value:
+            return np.zeros(0, MUT_DTYPE)
+        return np.frombuffer((C.c_char * (n.value * MUT_DTYPE.itemsize)).from_address(out.value), dtype=MUT_DTYPE).copy()
 
     def run_device(self, algo: int, d_msa: int, row_stride: int, n_rows: int, n_cols: int, d_cons: int, d_forced: int = 0):
         """Device pointers (ints) in; records stay on the device.  Returns (device pointer, count)."""

@@ -296,27 +296,21 @@ Tree::Tree(std::istream& fin, std::istream& secondFin, FILE_TYPE ftype, std::str
         }
     }
     if (L > 0) {
-        const int64_t stride = (L + 1) / 2;
-        std::vector<uint8_t> nib((size_t)std::max<size_t>(1, seqs.size()) * stride, 0), cons(L), forced;
+        // rows as contiguous characters, in map order; the character -> code conversion of :1398-1406 / :1565-1571 and
+        // the nibble packing happen on the device (pmfs_run_chars)
+        std::vector<char> chars((size_t)std::max<size_t>(1, seqs.size()) * (size_t)L);
         size_t row = 0;
-        for (const auto& u : seqs) {
-            uint8_t* dst = nib.data() + row++ * stride;
-            for (int64_t i = 0; i < L; i++) dst[i >> 1] |= (uint8_t)(getCodeFromNucleotide(u.second[i]) << ((i & 1) * 4));
-        }
-        for (int64_t i = 0; i < L; i++) cons[i] = (uint8_t)getCodeFromNucleotide(consensusSeq[i]);
-        if (!reference.empty()) {  // refState (src/panman.cpp:1409) / defaultState (:1573-1580): code of the reference row
-            const std::string& ref = seqs.at(reference);
-            forced.resize(L);
-            for (int64_t i = 0; i < L; i++) forced[i] = (uint8_t)getCodeFromNucleotide(ref[i]);
-        }
+        for (const auto& u : seqs) memcpy(chars.data() + row++ * (size_t)L, u.second.data(), (size_t)L);
+        const char* forcedChars = nullptr;
+        if (!reference.empty()) forcedChars = seqs.at(reference).data();  // refState (:1409) / defaultState (:1573-1580)
         pmfs_tree t = {V, parent.data(), childOff.data(), childIdx.data(), leafRow.data()};
         pmfs_ctx* ctx = nullptr;
         int rc = pmfs_create(&ctx, &t, device);
         if (rc) throw BuildError(rc, pmfs_last_error());
         pmfs_mut* out = nullptr;
         int64_t n = 0;
-        rc = pmfs_run(ctx, ftype == FILE_TYPE::MSA ? PMFS_FITCH : PMFS_SANKOFF, nib.data(), stride, (int32_t)seqs.size(), L,
-                      cons.data(), forced.empty() ? nullptr : forced.data(), &out, &n);
+        rc = pmfs_run_chars(ctx, ftype == FILE_TYPE::MSA ? PMFS_FITCH : PMFS_SANKOFF, chars.data(), L, (int32_t)seqs.size(), L,
+                            consensusSeq.data(), forcedChars, &out, &n);
         if (rc) {
             std::string msg = pmfs_last_error();
             pmfs_destroy(ctx);

@@ -775,6 +775,32 @@ __global__ void pack_offsets_kernel(const int32_t* __restrict__ out_node, int64_
     for (int32_t v = lo; v <= hi; v++) node_off[v] = k;
 }
 
+// ---- FASTA characters -> packed 4-bit codes on the device -------------------------------------------------
+// getCodeFromNucleotide (src/panman.cpp:83-118): case-sensitive, everything that is not one of the 15 upper-case IUPAC
+// letters (including '-', lower case and '\0') is code 0.
+__device__ __forceinline__ uint32_t code_of_char(uint32_t ch) {
+    switch (ch) {
+        case 'A': return 1;  case 'C': return 2;  case 'M': return 3;  case 'G': return 4;
+        case 'R': return 5;  case 'S': return 6;  case 'V': return 7;  case 'T': return 8;
+        case 'W': return 9;  case 'Y': return 10; case 'H': return 11; case 'K': return 12;
+        case 'D': return 13; case 'B': return 14; case 'N': return 15;
+        default: return 0;
+    }
+}
+// one thread = 8 columns of one row: 8 characters in, one 32-bit word of nibbles out (column 2j in the low nibble of byte j)
+__global__ void pack_chars_kernel(const uint8_t* __restrict__ chars, int64_t in_stride, int32_t n_rows, int64_t n_cols,
+                                  uint8_t* __restrict__ out, int64_t out_stride) {
+    const int64_t words = out_stride / 4;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= words * n_rows) return;
+    const int64_t row = i / words, w = i % words;
+    const uint8_t* src = chars + row * in_stride + w * 8;
+    uint32_t v = 0;
+    for (int k = 0; k < 8; k++)
+        if (w * 8 + k < n_cols) v |= code_of_char(src[k]) << (4 * k);
+    *(uint32_t*)(out + row * out_stride + w * 4) = v;
+}
+
 // region r's records (count[r] of them at src + r*cap) -> dst + offset[r]: makes the per-region output contiguous
 __global__ void compact_regions_kernel(const unsigned long long* __restrict__ src, unsigned long long cap,
                                        const unsigned long long* __restrict__ count, const unsigned long long* __restrict__ offset,
@@ -969,7 +995,7 @@ struct pmfs_ctx {
     DevBuf<uint8_t> d_sort_tmp;
     DevBuf<pmfs_mut> d_out;
     // host-path staging
-    DevBuf<uint8_t> d_msa, d_cons, d_forced;
+    DevBuf<uint8_t> d_msa, d_cons, d_forced, d_chars;
     std::vector<unsigned long long> h_counts, h_offsets;
     // device-side packing (pmfs_pack_last)
     DevBuf<int32_t> d_pk_run, d_pk_idx, d_pk_node;
@@ -1149,6 +1175,7 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_xcode.release(); c->d_xvalid.release(); c->d_keys.release(); c->d_keys_alt.release();
     c->d_count.release(); c->d_err.release();
     c->d_sort_tmp.release(); c->d_out.release(); c->d_msa.release(); c->d_cons.release(); c->d_forced.release();
+    c->d_chars.release();
     c->d_synth_node.release(); c->d_synth_pslot.release(); c->d_synth_mslot.release();
     c->d_synth_state[0].release(); c->d_synth_state[1].release();
     if (c->h_out) cudaFreeHost(c->h_out);
@@ -1727,6 +1754,65 @@ int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int3
     cudaEventElapsedTime(&c->timing.d2h_ms, c->ev[5], c->ev[6]);
     c->timing.total_ms += c->timing.d2h_ms;
     *out = h;
+    return PMFS_OK;
+}
+
+static uint8_t host_code_of_char(char ch) {  // src/panman.cpp:83-118
+    switch (ch) {
+        case 'A': return 1;  case 'C': return 2;  case 'M': return 3;  case 'G': return 4;
+        case 'R': return 5;  case 'S': return 6;  case 'V': return 7;  case 'T': return 8;
+        case 'W': return 9;  case 'Y': return 10; case 'H': return 11; case 'K': return 12;
+        case 'D': return 13; case 'B': return 14; case 'N': return 15;
+        default: return 0;
+    }
+}
+
+int pmfs_run_chars(pmfs_ctx* c, int algo, const char* msa_chars, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                   const char* consensus_chars, const char* forced_chars, pmfs_mut** out, int64_t* n_out) {
+    if (!c || !msa_chars || !consensus_chars || !out || !n_out || n_cols <= 0 || n_rows < 0 || row_stride < n_cols) {
+        g_error = "pmfs_run_chars: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    const int64_t dstride = ((n_cols + 31) / 32) * 16;
+    const int64_t cstride = ((n_cols + 15) / 16) * 16;  // device character rows, 16-byte aligned
+    int rc;
+    if ((rc = c->d_msa.ensure((size_t)std::max<int64_t>(1, n_rows) * dstride))) return rc;
+    if ((rc = c->d_chars.ensure((size_t)std::max<int64_t>(1, n_rows) * cstride + 16))) return rc;
+    if ((rc = c->d_cons.ensure((size_t)n_cols))) return rc;
+    if (forced_chars && (rc = c->d_forced.ensure((size_t)n_cols))) return rc;
+    std::vector<uint8_t> cons((size_t)n_cols), forced(forced_chars ? (size_t)n_cols : 0);
+    for (int64_t i = 0; i < n_cols; i++) cons[i] = host_code_of_char(consensus_chars[i]);
+    for (size_t i = 0; i < forced.size(); i++) forced[i] = host_code_of_char(forced_chars[i]);
+    PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
+    if (n_rows > 0) {
+        PMFS_CUDA(cudaMemcpy2DAsync(c->d_chars.ptr, (size_t)cstride, msa_chars, (size_t)row_stride, (size_t)n_cols, (size_t)n_rows,
+                                    cudaMemcpyHostToDevice, c->stream));
+        const int64_t total = (dstride / 4) * n_rows;
+        pack_chars_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(c->d_chars.ptr, cstride, n_rows, n_cols, c->d_msa.ptr, dstride);
+        PMFS_CUDA(cudaGetLastError());
+    }
+    PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons.data(), (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
+    if (forced_chars) PMFS_CUDA(cudaMemcpyAsync(c->d_forced.ptr, forced.data(), (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
+    PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));
+    PMFS_CUDA(cudaEventSynchronize(c->ev[6]));
+    cudaEventElapsedTime(&c->timing.h2d_ms, c->ev[5], c->ev[6]);
+    pmfs_mut* d_out = nullptr;
+    rc = run_device_impl(c, algo, c->d_msa.ptr, dstride, n_rows, n_cols, c->d_cons.ptr, forced_chars ? c->d_forced.ptr : nullptr,
+                         &d_out, n_out);
+    if (rc) return rc;
+    if ((size_t)*n_out > c->h_out_cap || !c->h_out) {
+        if (c->h_out) cudaFreeHost(c->h_out);
+        c->h_out = nullptr;
+        c->h_out_cap = 0;
+        const size_t want = std::max<size_t>(1024, (size_t)*n_out + (size_t)*n_out / 4);
+        PMFS_CUDA(cudaMallocHost(&c->h_out, want * sizeof(pmfs_mut)));
+        c->h_out_cap = want;
+    }
+    if (*n_out > 0)
+        PMFS_CUDA(cudaMemcpyAsync(c->h_out, d_out, (size_t)*n_out * sizeof(pmfs_mut), cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    *out = c->h_out;
     return PMFS_OK;
 }
 

@@ -135,3 +135,35 @@ def test_error_paths():
         with pytest.raises(api.PmfsError) as e:  # a leaf refers to row 2 but only 2 rows are given
             ctx.run(api.FITCH, np.zeros((2, 3), np.uint8), 5, cons)
         assert e.value.status == -1
+
+
+# getCodeFromNucleotide (src/panman.cpp:83-118) as a 256-entry table: the 15 upper-case IUPAC letters, all else 0
+_CODE = np.zeros(256, np.uint8)
+for _i, _ch in enumerate("ACMGRSVTWYHKDBN"):
+    _CODE[ord(_ch)] = _i + 1
+
+
+def test_run_chars_matches_codes_path():
+    """pmfs_run_chars (characters in, conversion on the device) == pmfs_run on host-converted codes == oracle,
+    on alignments that hold every byte value (lower case, '-', '\\0', >127 all map to the gap code)."""
+    rng = np.random.default_rng(77)
+    letters = np.frombuffer(b"ACGTACGTACGTNRYKMSWBDHV--", np.uint8)
+    for trial, L in enumerate((1, 7, 8, 31, 33, 600, 4099)):
+        tree = synth.random_tree(int(rng.integers(2, 120)), rng, max_arity=3, absent_frac=0.05 if trial % 2 else 0.0)
+        rows = synth.n_rows(tree)
+        chars = letters[rng.integers(0, len(letters), (rows, L))].copy()
+        junk = rng.random((rows, L)) < 0.05
+        chars[junk] = rng.integers(0, 256, int(junk.sum()), dtype=np.uint8)  # any byte value at all
+        if L >= 600:
+            chars[0, :256] = np.arange(256, dtype=np.uint8)
+        codes = _CODE[chars]
+        cons_chars = np.where(codes.max(axis=0) > 0, np.frombuffer(b"A", np.uint8)[0], np.uint8(ord("-"))).astype(np.uint8)
+        cons = _CODE[cons_chars]
+        forced_chars = chars[int(rng.integers(0, rows))] if trial % 2 else None
+        forced = None if forced_chars is None else _CODE[forced_chars]
+        for algo in (0, 1):
+            want = O.run_port(algo, tree, codes, cons, forced, threads=2)
+            with api.Context(tree) as ctx:
+                got = ctx.run_chars(algo, chars, cons_chars, forced_chars)
+            assert G.same_muts(got, want), (trial, algo)
+            assert G.same_muts(got, run_gpu(tree, algo, codes, cons, forced))
