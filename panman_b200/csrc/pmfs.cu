@@ -79,6 +79,7 @@ struct WalkParams {
     unsigned long long* out_count;  // [n_owners]
     unsigned long long out_cap;     // capacity of one owner's region
     int32_t n_regions;              // > 0: one output region per 32 column groups (see emit); 0: regions per owner
+    uint32_t bucket_mask;           // single-GPU runs: regions are further split by (node & bucket_mask), bucket-major
     int64_t region_base;            // region index of this column tile's first 32 groups
     int32_t n_owners;               // 1, or the number of ranks in column-shard mode
     int32_t owner_bound[17];        // nodes [owner_bound[r], owner_bound[r+1]) are owned by rank r
@@ -158,6 +159,23 @@ __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity);
 }
+// -DPMFS_WAITPROF (never in the shipped library): cycles spent per wait kind, summed over warps, printed per launch
+#ifdef PMFS_WAITPROF
+__device__ unsigned long long g_waitprof[16];
+__device__ __forceinline__ long long wp_now() { return clock64(); }
+__device__ __forceinline__ void wp_add(int k, long long t0) {
+    if ((threadIdx.x & 31) == 0) atomicAdd(&g_waitprof[k], (unsigned long long)(clock64() - t0));
+}
+struct WaitProf {
+    long long t0;
+    int k;
+    __device__ __forceinline__ explicit WaitProf(int kind) : t0(wp_now()), k(kind) {}
+    __device__ __forceinline__ ~WaitProf() { wp_add(k, t0); }
+};
+#define PMFS_WP(kind) WaitProf wp_##kind(kind)
+#else
+#define PMFS_WP(kind)
+#endif
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
@@ -220,6 +238,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
         if (e & kStreamSet) {
             if (lane == 0) {
                 const uint32_t u = n_set % SETS, par = (n_set / SETS) & 1u;
+                PMFS_WP(9);
                 mbar_wait(r.bars + (M::bSetEmpty + u) * 8, par ^ 1u);  // all walkers are done with the slot's previous set
                 // one node's set for this tile: 4 quarters of `tile_w` groups, contiguous (leaf_bytes = tile_w * 16)
                 mbar_arrive_expect_tx(r.bars + (M::bSetFull + u) * 8, 4 * leaf_bytes);
@@ -230,6 +249,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
         } else {
             if (lane == 0) {
                 const uint32_t u = n_leaf % kLeafRing, par = (n_leaf / kLeafRing) & 1u;
+                PMFS_WP(8);
                 mbar_wait(r.bars + (M::bLeafEmpty + u) * 8, par ^ 1u);
                 mbar_arrive_expect_tx(r.bars + (M::bLeafFull + u) * 8, leaf_bytes);
                 bulk_g2s(r.smem + M::kLeaf + u * kUnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
@@ -286,6 +306,7 @@ struct DevEnv {
         ltmask = 0;
         for (int q = 0; q < 32; q++)
             if (column_of_bit(q) < column_of_bit(lane)) ltmask |= 1u << q;
+        PMFS_WP(1);
         if (prog_staged) mbar_wait(r.bars + (M::bProg + slot) * 8, prog_parity);
         else gprog = p_.prog + p_.chunk_off[d.chunk];
     }
@@ -302,6 +323,7 @@ struct DevEnv {
     // next leaf unit: wait until the TMA copy has landed, read this thread's 16 bytes per group, hand the unit back
     __device__ __forceinline__ void leaf(uint32_t, uint4 (&w)[kNG]) {
         const uint32_t u = n_leaf % kLeafRing, par = (n_leaf / kLeafRing) & 1u;
+        PMFS_WP(2);
         mbar_wait(ring.bars + (M::bLeafFull + u) * 8, par);
         const uint32_t base = ring.smem + M::kLeaf + u * kUnitBytes + threadIdx.x * 16;
 #pragma unroll
@@ -313,6 +335,7 @@ struct DevEnv {
     // next set slot (a set written by an earlier work item): 4 quarters x kNG groups
     __device__ __forceinline__ void load_x(uint32_t, Planes16 (&s)[kNG]) {
         const uint32_t u = n_set % SETS, par = (n_set / SETS) & 1u;
+        PMFS_WP(3);
         mbar_wait(ring.bars + (M::bSetFull + u) * 8, par);
         const uint32_t base = ring.smem + M::kSet + u * kSetBytes + threadIdx.x * 16;
 #pragma unroll
@@ -444,8 +467,10 @@ struct DevEnv {
     }
     // Two output layouts.  Regions per 32 column groups (single-GPU runs): the records of one (node, region) pair come
     // from exactly one call, are written contiguously in column order, and regions are laid out in column order -- so a
-    // STABLE sort on the node bits alone (2 radix passes instead of 4) yields the (node,pos) order.  Regions per owning
-    // rank (column shards): see pmfs_set_shard.
+    // STABLE sort on the node bits alone yields the (node,pos) order.  The regions are further split by the LOW node bits
+    // (bucket-major layout): that is the first pass of an LSD radix sort done for free while emitting, and the stable
+    // sort only has to cover the remaining high node bits (one radix pass for up to 2^16 nodes instead of four on the
+    // whole key).  Regions per owning rank (column shards): see pmfs_set_shard.
     __device__ void emit(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
         if (p.n_regions > 0) {
             int64_t own_base = 0;  // column shards: regions are owner-major (owner of this node's list, uniform in the warp)
@@ -454,7 +479,7 @@ struct DevEnv {
             for (int j = 0; j < kNG; j++) {
                 if (!__any_sync(0xffffffffu, m[j] != 0)) continue;
                 const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
-                const int64_t region = own_base + p.region_base + ((gwarp + j * kTPB) >> 5);
+                const int64_t region = own_base + (int64_t)(node & p.bucket_mask) * p.n_regions + p.region_base + ((gwarp + j * kTPB) >> 5);
                 unsigned long long base = 0;
                 if (lane == 0) base = atomicAdd(p.out_count + region, (unsigned long long)total);
                 base = __shfl_sync(0xffffffffu, base, 0);
@@ -554,7 +579,10 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
                 const int4 a = __ldg(p.items + 2 * pos), b = __ldg(p.items + 2 * pos + 1);
                 next = atomicAdd(p.next_item, 1);  // claim ahead: its latency hides behind this item
                 chunk = a.x; parent = a.y; plen = a.z; slen = a.w; stream_off = b.y;
-                mbar_wait(r.bars + (M::bDescEmpty + slot) * 8, phase ^ 1u);  // the walkers are done with item n-2
+                {
+                    PMFS_WP(7);
+                    mbar_wait(r.bars + (M::bDescEmpty + slot) * 8, phase ^ 1u);  // the walkers are done with item n-2
+                }
                 if (plen <= kProgWords) {
                     // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
                     const uint32_t bytes = (uint32_t)((plen + 3) / 4) * 16u;
@@ -564,6 +592,7 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
                 // dependencies: all child chunks (bottom-up) / the parent chunk (top-down), same column tile
                 const volatile int* f = p.ready + (int64_t)b.w * p.ctas_per_chunk + tile;
                 if (*f < b.z) {
+                    PMFS_WP(6);
                     const long long t0 = clock64();
                     while (*f < b.z) {
                         __nanosleep(32);
@@ -597,7 +626,10 @@ template <int SETS>
 __device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d) {
     using M = SmemMap<SETS>;
     const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
-    mbar_wait(r.bars + (M::bDescFull + slot) * 8, phase);
+    {
+        PMFS_WP(0);
+        mbar_wait(r.bars + (M::bDescFull + slot) * 8, phase);
+    }
     asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(d.chunk), "=r"(d.tile), "=r"(d.plen), "=r"(d.parent)
                  : "r"(r.smem + M::kDesc + slot * 16)
@@ -606,7 +638,10 @@ __device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d
 }
 // Item finished: publish it to dependants (all walkers' stores first), then free the descriptor/program slot.
 __device__ __forceinline__ void finish_item(int* counter, uint32_t desc_empty_bar) {
-    asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // the four walking warps only
+    {
+        PMFS_WP(4);
+        asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // the four walking warps only
+    }
     if (threadIdx.x == 0 && counter) {
         __threadfence();
         atomicAdd(counter, 1);
@@ -622,9 +657,11 @@ __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
     __shared__ __align__(8) unsigned long long bars[M::kBars];
     const Ring ring = ring_setup<kSetRingFwd>(smem, bars);
     if (threadIdx.x >= kTPB) {
+        PMFS_WP(10);
         producer_loop<kPassFwd, kSetRingFwd>(p, ring);
         return;
     }
+    PMFS_WP(5);
     uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
     ItemDesc d;
     for (uint32_t n = 0; next_item<kSetRingFwd>(ring, n, d); n++) {
@@ -656,9 +693,11 @@ __global__ void __launch_bounds__(kThreads) bwd_kernel(const WalkParams p) {
     __shared__ __align__(8) unsigned long long bars[M::kBars];
     const Ring ring = ring_setup<kSetRingBwd>(smem, bars);
     if (threadIdx.x >= kTPB) {
+        PMFS_WP(10);
         producer_loop<kPassBwd, kSetRingBwd>(p, ring);
         return;
     }
+    PMFS_WP(5);
     uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
     ItemDesc d;
     for (uint32_t n = 0; next_item<kSetRingBwd>(ring, n, d); n++) {
@@ -799,6 +838,45 @@ __global__ void pack_chars_kernel(const uint8_t* __restrict__ chars, int64_t in_
     for (int k = 0; k < 8; k++)
         if (w * 8 + k < n_cols) v |= code_of_char(src[k]) << (4 * k);
     *(uint32_t*)(out + row * out_stride + w * 4) = v;
+}
+
+// sum and maximum of the output-area counters (overflow check and record count without copying the counters to the host)
+__global__ void area_stats_kernel(const unsigned long long* __restrict__ count, int64_t n_areas, unsigned long long* __restrict__ stats) {
+    unsigned long long sum = 0, mx = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_areas; i += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long v = count[i];
+        sum += v;
+        mx = mx > v ? mx : v;
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, d);
+        const unsigned long long o = __shfl_xor_sync(0xffffffffu, mx, d);
+        mx = mx > o ? mx : o;
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (sum) atomicAdd(stats, sum);
+        if (mx) atomicMax(stats + 1, mx);
+    }
+}
+// one warp per output area (grid-stride): count[a] records at src + a*cap -> dst + offset[a]
+__global__ void compact_areas_kernel(const unsigned long long* __restrict__ src, unsigned long long cap,
+                                     const unsigned long long* __restrict__ count, const unsigned long long* __restrict__ offset,
+                                     int64_t n_areas, const unsigned long long* __restrict__ max_count,
+                                     unsigned long long* __restrict__ dst) {
+    if (*max_count > cap) return;  // some area overflowed: the host grows the buffer and runs the passes again
+    const int lane = threadIdx.x & 31;
+    const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t a = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; a < n_areas; a += n_warps) {
+        const unsigned long long n = count[a];
+        const unsigned long long* s = src + (unsigned long long)a * cap;
+        unsigned long long* d = dst + offset[a];
+        unsigned long long i = lane;
+        for (; i + 96 < n; i += 128) {  // four loads in flight per lane
+            const unsigned long long v0 = s[i], v1 = s[i + 32], v2 = s[i + 64], v3 = s[i + 96];
+            d[i] = v0; d[i + 32] = v1; d[i + 64] = v2; d[i + 96] = v3;
+        }
+        for (; i < n; i += 32) d[i] = s[i];
+    }
 }
 
 // region r's records (count[r] of them at src + r*cap) -> dst + offset[r]: makes the per-region output contiguous
@@ -992,7 +1070,8 @@ struct pmfs_ctx {
 
     DevBuf<unsigned long long> d_count;
     DevBuf<unsigned int> d_err;
-    DevBuf<uint8_t> d_sort_tmp;
+    DevBuf<uint8_t> d_sort_tmp, d_scan_tmp;
+    unsigned long long* h_stats = nullptr;  // pinned: {records, largest area, error flag} of the last run
     DevBuf<pmfs_mut> d_out;
     // host-path staging
     DevBuf<uint8_t> d_msa, d_cons, d_forced, d_chars;
@@ -1174,6 +1253,8 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_S.release(); c->d_D.release(); c->d_cons_planes.release(); c->d_forced_planes.release();
     c->d_xcode.release(); c->d_xvalid.release(); c->d_keys.release(); c->d_keys_alt.release();
     c->d_count.release(); c->d_err.release();
+    c->d_scan_tmp.release();
+    if (c->h_stats) cudaFreeHost(c->h_stats);
     c->d_sort_tmp.release(); c->d_out.release(); c->d_msa.release(); c->d_cons.release(); c->d_forced.release();
     c->d_chars.release();
     c->d_synth_node.release(); c->d_synth_pslot.release(); c->d_synth_mslot.release();
@@ -1279,10 +1360,29 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     }
     if (c->n_sms == 0) PMFS_CUDA(cudaDeviceGetAttribute(&c->n_sms, cudaDevAttrMultiProcessorCount, c->device));
     const unsigned grid = (unsigned)std::min<int64_t>(n_items, (int64_t)c->n_sms * per_sm);
-    PMFS_CUDA(cudaMemsetAsync(wp.next_item, 0, sizeof(int), c->stream));
-    PMFS_CUDA(cudaMemsetAsync(wp.ready, 0, per_pass * sizeof(int), c->stream));
+    // claim counters and dependency counters of BOTH passes are cleared once, ahead of the bottom-up pass
+    if (fwd) PMFS_CUDA(cudaMemsetAsync(sync, 0, (64 + 2 * per_pass) * sizeof(int), c->stream));
     void* args[] = {&wp};
+#ifdef PMFS_WAITPROF
+    {
+        unsigned long long z[16] = {0};
+        PMFS_CUDA(cudaStreamSynchronize(c->stream));
+        PMFS_CUDA(cudaMemcpyToSymbol(g_waitprof, z, sizeof(z)));
+    }
+#endif
     PMFS_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kThreads), args, smem, c->stream));
+#ifdef PMFS_WAITPROF
+    {
+        unsigned long long z[16];
+        PMFS_CUDA(cudaStreamSynchronize(c->stream));
+        PMFS_CUDA(cudaMemcpyFromSymbol(z, g_waitprof, sizeof(z)));
+        const double W = (double)z[5], Pr = (double)z[10];
+        fprintf(stderr, "[waitprof %s grid %u per_sm %d items %d] walkers: desc %.1f%% prog %.1f%% leaf %.1f%% set %.1f%% barsync %.1f%% | "
+                "producer: dep %.1f%% desc_empty %.1f%% leaf_empty %.1f%% set_empty %.1f%% | walker warp-cycles %.3g\n",
+                fwd ? "fwd" : "bwd", grid, per_sm, wp.n_items, 100 * z[0] / W, 100 * z[1] / W, 100 * z[2] / W, 100 * z[3] / W, 100 * z[4] / W,
+                100 * z[6] / Pr, 100 * z[7] / Pr, 100 * z[8] / Pr, 100 * z[9] / Pr, W);
+    }
+#endif
     (*launches)++;
     return PMFS_OK;
 }
@@ -1356,14 +1456,29 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     if (d_forced && (rc = c->d_forced_planes.ensure(tile_groups))) return rc;
     if ((rc = c->d_xcode.ensure((size_t)NC * tile_groups))) return rc;
     if ((rc = c->d_xvalid.ensure((size_t)NC * tile_groups))) return rc;
-    if ((rc = c->d_err.ensure(1))) return rc;
     if ((rc = c->d_sync.ensure(sync_ints(*P, tile_groups)))) return rc;
     // output regions: per owning rank in shard mode, else one per 32 column groups (see DevEnv::emit)
     const int64_t W = (G_all + 31) / 32;
     const int n_parts = std::max(1, c->parts.n_parts);
-    const bool by_columns = W * n_parts <= 65535;
-    const int n_owners = by_columns ? (int)(W * n_parts) : n_parts;  // number of output regions
-    if ((rc = c->d_count.ensure(2 * (size_t)std::max(16, n_owners)))) return rc;
+    const bool shard = c->parts.n_parts > 0;
+    const bool by_columns = shard ? W * n_parts <= 65535 : W <= (1 << 20);
+    // single-GPU runs: low node bits that select the output bucket (see DevEnv::emit) -- as few as make the remaining
+    // node bits fit the smallest number of 8-bit radix passes, with at most 2^20 output areas
+    int bucket_bits = 0;
+    if (!shard && by_columns) {
+        int max_bits = 10;
+        while (max_bits > 0 && (W << max_bits) > (1 << 20)) max_bits--;
+        max_bits = std::min(max_bits, node_bits);
+        const int passes = (node_bits - max_bits + 7) / 8;
+        bucket_bits = std::max(0, node_bits - 8 * passes);
+    }
+    const int64_t n_owners = !by_columns ? n_parts : shard ? W * n_parts : (W << bucket_bits);  // number of output areas
+    const size_t n_ctr = (size_t)std::max<int64_t>(16, n_owners);
+    if ((rc = c->d_count.ensure(2 * n_ctr + 16))) return rc;
+    // [n_ctr area counters][16: sum, max of the counters, error flag][n_ctr area offsets]
+    unsigned long long* const d_stats = c->d_count.ptr + n_ctr;
+    unsigned long long* const d_off = d_stats + 16;
+    if (!c->h_stats) PMFS_CUDA(cudaMallocHost(&c->h_stats, 16 * sizeof(unsigned long long)));
     size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);  // total records; one region is cap / n_owners
 
     pmfs_timing& tm = c->timing;
@@ -1373,13 +1488,12 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     float fwd_ms = 0, bwd_ms = 0;
     unsigned long long count = 0;
     std::vector<unsigned long long>& counts = c->h_counts;
-    counts.assign((size_t)std::max(16, n_owners), 0);
+    counts.assign(shard ? n_ctr : 16, 0);
     size_t region = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
         if ((rc = c->d_keys.ensure(cap))) return rc;
         region = c->d_keys.cap / (size_t)n_owners;
-        PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, counts.size() * sizeof(unsigned long long), c->stream));
-        PMFS_CUDA(cudaMemsetAsync(c->d_err.ptr, 0, sizeof(unsigned int), c->stream));
+        PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, (n_ctr + 16) * sizeof(unsigned long long), c->stream));
         fwd_ms = bwd_ms = 0;
         tm.n_launches = 0;
         for (int64_t g0 = 0; g0 < G_all; g0 += tile_groups) {
@@ -1402,9 +1516,10 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             wp.out_cap = region;
             wp.n_owners = n_parts;
             wp.n_regions = by_columns ? (int32_t)W : 0;
+            wp.bucket_mask = (1u << bucket_bits) - 1u;
             wp.region_base = g0 / 32;
             for (int r = 0; r <= c->parts.n_parts; r++) wp.owner_bound[r] = c->parts.bound[r];
-            wp.err_flag = c->d_err.ptr;
+            wp.err_flag = (unsigned int*)(d_stats + 2);
             wp.pos_bits = pos_bits;
             wp.pos_offset = c->parts.n_parts > 0 ? c->shard_pos_offset : 0;
             wp.ready = c->d_sync.ptr;
@@ -1433,10 +1548,33 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                 bwd_ms += b;
             }
         }
-        unsigned int err = 0;
-        PMFS_CUDA(cudaMemcpyAsync(counts.data(), c->d_count.ptr, counts.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-        PMFS_CUDA(cudaMemcpyAsync(&err, c->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost, c->stream));
+        PMFS_CUDA(cudaEventRecord(c->ev[3], c->stream));
+        unsigned long long* const stats = c->h_stats;
+        if (shard) {
+            PMFS_CUDA(cudaMemcpyAsync(counts.data(), c->d_count.ptr, counts.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+            PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+        } else {
+            area_stats_kernel<<<(unsigned)std::min<int64_t>(296, (n_owners + 255) / 256), 256, 0, c->stream>>>(c->d_count.ptr, n_owners, d_stats);
+            tm.n_launches++;
+            PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+            if (by_columns) {
+                // Areas are laid out (low node bits, column region)-major and every node's records inside an area are
+                // contiguous and column-ordered: pack the areas; a stable sort on the remaining HIGH node bits alone then
+                // gives the (node,pos) order.  Queued before the host knows the record count (the device checks for
+                // overflow itself), so the GPU packs while the host waits for the count the sort call needs.
+                size_t scan_bytes = 0;
+                PMFS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, c->d_count.ptr, d_off, (int)n_owners, c->stream));
+                if ((rc = c->d_scan_tmp.ensure(scan_bytes + 16))) return rc;
+                if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
+                PMFS_CUDA(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.ptr, scan_bytes, c->d_count.ptr, d_off, (int)n_owners, c->stream));
+                const unsigned cg = (unsigned)std::max<int64_t>(1, std::min<int64_t>(148 * 8, (n_owners + 7) / 8));
+                compact_areas_kernel<<<cg, 256, 0, c->stream>>>(c->d_keys.ptr, region, c->d_count.ptr, d_off, n_owners, d_stats + 1,
+                                                                c->d_keys_alt.ptr);
+                tm.n_launches++;
+            }
+        }
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
+        const unsigned int err = (unsigned int)stats[2];
         if (tile_groups >= G_all) {
             cudaEventElapsedTime(&fwd_ms, c->ev[0], c->ev[1]);
             cudaEventElapsedTime(&bwd_ms, c->ev[1], c->ev[2]);
@@ -1446,9 +1584,9 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                       "(the reference asserts here, src/fitchSankoff.cpp:505)";
             return PMFS_ERR_ROOT_INVALID;
         }
-        count = 0;
-        unsigned long long worst = 0;
-        for (int r = 0; r < n_owners; r++) {
+        count = shard ? 0 : stats[0];
+        unsigned long long worst = shard ? 0 : stats[1];
+        for (int64_t r = 0; shard && r < n_owners; r++) {
             count += counts[r];
             worst = std::max(worst, counts[r]);
         }
@@ -1457,7 +1595,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             g_error = "pmfs_run: record buffer overflow after regrowth";
             return PMFS_ERR_NOMEM;
         }
-        cap = (size_t)n_owners * ((size_t)worst + (size_t)worst / 8 + 1024);  // too small: grow and redo the passes
+        cap = (size_t)n_owners * ((size_t)worst + (size_t)worst / 4 + 64);  // too small: grow and redo the passes
     }
     tm.forward_ms = fwd_ms;
     tm.backward_ms = bwd_ms;
@@ -1473,7 +1611,6 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         g_error = "pmfs_run: more than 2^31 records in one call: run fewer columns per call";
         return PMFS_ERR_ARG;
     }
-    PMFS_CUDA(cudaEventRecord(c->ev[3], c->stream));
     if (c->parts.n_parts > 0) {
         // shard mode: records were emitted straight into one region per owning rank and stay unordered; the owner
         // orders what it receives (pmfs_sort_records)
@@ -1491,7 +1628,6 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                 for (int64_t w = 0; o < n_parts && w < W; w++) c->part_counts[o] += (int64_t)counts[(size_t)o * W + w];
             }
             if (n > 0) {
-                unsigned long long* d_off = c->d_count.ptr + counts.size();
                 PMFS_CUDA(cudaMemcpyAsync(d_off, off.data(), (size_t)n_owners * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
                 const unsigned bx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, ((size_t)n / n_owners + 255) / 256));
                 compact_regions_kernel<<<dim3(bx, (unsigned)n_owners), 256, 0, c->stream>>>(c->d_keys.ptr, region, c->d_count.ptr, d_off,
@@ -1520,27 +1656,15 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
         if ((rc = c->d_out.ensure((size_t)n))) return rc;
         cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
-        int lo = kPayloadBits;
+        const int lo = by_columns ? kPayloadBits + pos_bits + bucket_bits : kPayloadBits;
         const int hi = kPayloadBits + pos_bits + node_bits;
-        if (by_columns) {
-            // regions are in column order and every node's records inside a region are contiguous and column-ordered:
-            // pack the regions, then a stable sort on the NODE bits alone gives the (node,pos) order
-            std::vector<unsigned long long>& off = c->h_offsets;
-            off.assign(counts.size(), 0);
-            for (int r = 1; r < n_owners; r++) off[r] = off[r - 1] + counts[r - 1];
-            unsigned long long* d_off = c->d_count.ptr + counts.size();
-            PMFS_CUDA(cudaMemcpyAsync(d_off, off.data(), (size_t)n_owners * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
-            const unsigned bx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, ((size_t)n / n_owners + 255) / 256));
-            compact_regions_kernel<<<dim3(bx, (unsigned)n_owners), 256, 0, c->stream>>>(c->d_keys.ptr, region, c->d_count.ptr, d_off,
-                                                                                       c->d_keys_alt.ptr);
-            tm.n_launches += 1;
-            kb = cub::DoubleBuffer<unsigned long long>(c->d_keys_alt.ptr, c->d_keys.ptr);
-            lo = kPayloadBits + pos_bits;
-        }
         size_t tmp_bytes = 0;
-        PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
-        if ((rc = c->d_sort_tmp.ensure(tmp_bytes))) return rc;
-        PMFS_CUDA(cub::DeviceRadixSort::SortKeys(c->d_sort_tmp.ptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
+        if (lo < hi) PMFS_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
+        if ((rc = c->d_sort_tmp.ensure(tmp_bytes + 16))) return rc;
+        // (the areas were packed into d_keys_alt above; no node bits are left to sort on when the tree has at most
+        // 2^bucket_bits nodes)
+        if (by_columns) kb = cub::DoubleBuffer<unsigned long long>(c->d_keys_alt.ptr, c->d_keys.ptr);
+        if (lo < hi) PMFS_CUDA(cub::DeviceRadixSort::SortKeys(c->d_sort_tmp.ptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
         assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), n, pos_bits, c->d_out.ptr);
         PMFS_CUDA(cudaGetLastError());
         tm.n_launches += 1;
