@@ -62,6 +62,7 @@ struct WalkParams {
     const int32_t* stream_len;  // [NC]
     int32_t ctas_per_chunk;
     int32_t stack_depth;
+    int32_t claim_lead;         // stream entries before the end of an item at which the producer claims the next one
     const uint4* msa;           // first group of this column tile
     int64_t msa_stride16;       // uint4 per MSA row
     uint4* S;                   // [I][4][G]
@@ -136,6 +137,17 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {  // never suspends
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 // slow path: let the hardware park the thread (suspend-time hint) instead of burning issue slots the producer needs
 __device__ __forceinline__ bool mbar_try_park(uint32_t bar, uint32_t parity) {
     uint32_t ok;
@@ -172,8 +184,32 @@ struct WaitProf {
     __device__ __forceinline__ explicit WaitProf(int kind) : t0(wp_now()), k(kind) {}
     __device__ __forceinline__ ~WaitProf() { wp_add(k, t0); }
 };
-#define PMFS_WP(kind) WaitProf wp_##kind(kind)
+#ifdef PMFS_TRACE_ONLY
+#define PMFS_WP(kind)
 #else
+#define PMFS_WP(kind) WaitProf wp_##kind(kind)
+#endif
+// per-item timeline: {start ns, end ns, chunk, tile | smid << 16}
+constexpr int kTraceCap = 1 << 17;
+__device__ ulonglong4 g_trace[kTraceCap];
+__device__ unsigned int g_trace_n;
+__device__ __forceinline__ unsigned long long trace_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void trace_item(unsigned long long t0, int chunk, int tile) {
+    if (threadIdx.x != 0) return;
+    unsigned int smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    const unsigned int i = atomicAdd(&g_trace_n, 1u);
+    if (i < kTraceCap) g_trace[i] = make_ulonglong4(t0, trace_now(), (unsigned long long)chunk, (unsigned long long)tile | ((unsigned long long)smid << 16));
+}
+#define PMFS_TRACE_BEGIN const unsigned long long trace_t0 = trace_now();
+#define PMFS_TRACE_END(chunk, tile) trace_item(trace_t0, chunk, tile);
+#else
+#define PMFS_TRACE_BEGIN
+#define PMFS_TRACE_END(chunk, tile)
 #define PMFS_WP(kind)
 #endif
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
@@ -224,11 +260,91 @@ struct ItemDesc {
     int32_t parent;  // parent chunk (-1 for the chunk with the tree root)
 };
 
-// Producer side of one item: stage the walk program into program buffer `slot`, then walk the chunk's load stream and
-// keep both rings full.  Called by the whole producer warp (the stream words are read warp-wide); lane 0 drives TMA.
+// Lane 0 of the producer warp: the work item AFTER the one whose operands are being streamed.  Its header work (free
+// descriptor slot -> program copy -> dependencies met -> descriptor posted) is attempted, without blocking, between
+// the ring entries of the current item and only finished with blocking waits once the current stream is done, so the
+// walkers normally find the next descriptor and program already there.
+struct NextItem {
+    int4 a, b;        // packed item records: {chunk, parent, plen, slen}, {prog_off/4, stream_off, need, dep chunk}
+    int32_t tile;
+    uint32_t ordinal; // how many items this CTA has taken before it (selects descriptor slot and barrier phase)
+    bool valid;       // false: no more items, the descriptor only tells the walkers to stop
+    bool slot_free, dep_ok, posted, claimed, fetched;
+    int32_t item;     // claimed index into the pass's item order
+    int32_t t_claim, t_fetch;  // stream entries left when the claim / the record fetch are issued
+    __device__ __forceinline__ void begin(uint32_t ord, int32_t slen, int32_t lead) {
+        ordinal = ord;
+        valid = slot_free = dep_ok = posted = claimed = fetched = false;
+        t_claim = min(lead, slen - 1);
+        t_fetch = max(t_claim - 2, -1);
+    }
+    __device__ __forceinline__ void claim(const WalkParams& p) {
+        item = atomicAdd(p.next_item, 1);
+        claimed = true;
+    }
+    __device__ __forceinline__ void fetch(const WalkParams& p) {
+        if (!claimed) claim(p);
+        valid = item < p.n_items;
+        tile = 0;
+        a = make_int4(-1, -1, 0, 0);
+        b = make_int4(0, 0, 0, 0);
+        if (valid) {
+            const int pos = item / p.ctas_per_chunk;
+            tile = item % p.ctas_per_chunk;
+            a = __ldg(p.items + 2 * pos);
+            b = __ldg(p.items + 2 * pos + 1);
+        }
+        fetched = true;
+    }
+};
+template <int SETS>
+__device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, NextItem& h, bool block) {
+    using M = SmemMap<SETS>;
+    const uint32_t slot = h.ordinal & 1u, phase = (h.ordinal >> 1) & 1u;
+    if (!h.slot_free) {  // the walkers are done with the item two before this one
+        const uint32_t bar = r.bars + (M::bDescEmpty + slot) * 8;
+        if (block) {
+            PMFS_WP(7);
+            mbar_wait(bar, phase ^ 1u);
+        } else if (!mbar_test(bar, phase ^ 1u)) {
+            return;
+        }
+        h.slot_free = true;
+        if (h.valid && h.a.z <= kProgWords) {
+            // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
+            const uint32_t bytes = (uint32_t)((h.a.z + 3) / 4) * 16u;
+            mbar_arrive_expect_tx(r.bars + (M::bProg + slot) * 8, bytes);
+            bulk_g2s(r.smem + M::kProg + slot * (kProgWords * 4), p.prog + (int64_t)h.b.x * 4, bytes, r.bars + (M::bProg + slot) * 8);
+        }
+    }
+    if (h.valid && !h.dep_ok) {
+        // dependencies: all child chunks (bottom-up) / the parent chunk (top-down), same column tile
+        const volatile int* f = p.ready + (int64_t)h.b.w * p.ctas_per_chunk + h.tile;
+        if (*f < h.b.z) {
+            if (!block) return;
+            PMFS_WP(6);
+            const long long t0 = clock64();
+            while (*f < h.b.z) {
+                __nanosleep(32);
+                if (clock64() - t0 > kSpinLimitCycles) __trap();
+            }
+        }
+        __threadfence();
+        asm volatile("fence.proxy.async;" ::: "memory");  // data written by other CTAs is read by the TMA engine
+        h.dep_ok = true;
+    }
+    asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.smem + M::kDesc + slot * 16), "r"(h.valid ? h.a.x : -1), "r"(h.tile),
+                 "r"(h.a.z), "r"(h.a.y)
+                 : "memory");
+    mbar_arrive(r.bars + (M::bDescFull + slot) * 8);
+    h.posted = true;
+}
+
+// Producer side of one item: walk the chunk's load stream and keep both rings full.  Called by the whole producer warp
+// (the stream words are read warp-wide); lane 0 drives TMA and, in passing, the header of the next item.
 template <int SETS>
 __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& r, WarpWords& w, int32_t slen, int tile,
-                                               uint32_t& n_leaf, uint32_t& n_set) {
+                                               uint32_t& n_leaf, uint32_t& n_set, NextItem& h) {
     using M = SmemMap<SETS>;
     const int lane = threadIdx.x & 31;
     const int64_t g0 = (int64_t)tile * kTileGroups;
@@ -256,6 +372,15 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
                          r.bars + (M::bLeafFull + u) * 8);
             }
             n_leaf++;
+        }
+        if (lane == 0) {
+            // the next item: claimed `claim_lead` entries before the end of this stream (late, so that an item that
+            // is ready is not held by a busy CTA while others idle), its records fetched two entries later, then its
+            // header attempted every other entry
+            const int32_t left = slen - 1 - j;
+            if (left == h.t_claim) h.claim(p);
+            else if (left == h.t_fetch) h.fetch(p);
+            else if (left < h.t_fetch && !h.posted && (left & 1) == 0) header_step<SETS>(p, r, h, false);
         }
     }
 }
@@ -474,6 +599,7 @@ struct DevEnv {
     __device__ void emit(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
         if (p.n_regions > 0) {
             int64_t own_base = 0;  // column shards: regions are owner-major (owner of this node's list, uniform in the warp)
+#pragma unroll 1  // (unrolled 16-fold this loop was a fifth of the kernel's code)
             for (int r = 1; r < p.n_owners; r++) own_base += (int32_t)node >= p.owner_bound[r] ? p.n_regions : 0;
 #pragma unroll
             for (int j = 0; j < kNG; j++) {
@@ -492,6 +618,7 @@ struct DevEnv {
         for (int j = 0; j < kNG; j++) cnt += __popc(m[j]);
         const uint32_t total = __reduce_add_sync(0xffffffffu, cnt);
         int own = 0;  // owner of this node's list (column shards); uniform across the warp
+#pragma unroll 1
         for (int r = 1; r < p.n_owners; r++) own += (int32_t)node >= p.owner_bound[r];
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(p.out_count + own, (unsigned long long)total);
@@ -512,6 +639,7 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
     int64_t n = tile_cols - g * 32;
     if (n >= 32) return ~0u;
     uint32_t m = 0;
+#pragma unroll 1  // once per work item and only in the last column group: keep it out of the instruction cache
     for (int q = 0; q < 32; q++)
         if (column_of_bit(q) < n) m |= 1u << q;
     return m;
@@ -563,61 +691,29 @@ __device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars)
 // record load and the dependency poll remain on the producer's critical path.
 template <int PASS, int SETS>
 __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r) {
-    using M = SmemMap<SETS>;
     const int lane = threadIdx.x & 31;
     uint32_t n_leaf = 0, n_set = 0;
-    int item = 0;
-    if (lane == 0) item = atomicAdd(p.next_item, 1);
+    NextItem h = {};
+    if (lane == 0) {
+        h.begin(0, 1, 0);
+        h.fetch(p);
+        header_step<SETS>(p, r, h, true);
+    }
     for (uint32_t n = 0;; n++) {
-        const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
-        int32_t chunk = -1, tile = 0, slen = 0, stream_off = 0, next = 0;
-        if (lane == 0) {
-            int32_t plen = 0, parent = -1;
-            if (item < p.n_items) {
-                const int pos = item / p.ctas_per_chunk;
-                tile = item % p.ctas_per_chunk;
-                const int4 a = __ldg(p.items + 2 * pos), b = __ldg(p.items + 2 * pos + 1);
-                next = atomicAdd(p.next_item, 1);  // claim ahead: its latency hides behind this item
-                chunk = a.x; parent = a.y; plen = a.z; slen = a.w; stream_off = b.y;
-                {
-                    PMFS_WP(7);
-                    mbar_wait(r.bars + (M::bDescEmpty + slot) * 8, phase ^ 1u);  // the walkers are done with item n-2
-                }
-                if (plen <= kProgWords) {
-                    // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
-                    const uint32_t bytes = (uint32_t)((plen + 3) / 4) * 16u;
-                    mbar_arrive_expect_tx(r.bars + (M::bProg + slot) * 8, bytes);
-                    bulk_g2s(r.smem + M::kProg + slot * (kProgWords * 4), p.prog + (int64_t)b.x * 4, bytes, r.bars + (M::bProg + slot) * 8);
-                }
-                // dependencies: all child chunks (bottom-up) / the parent chunk (top-down), same column tile
-                const volatile int* f = p.ready + (int64_t)b.w * p.ctas_per_chunk + tile;
-                if (*f < b.z) {
-                    PMFS_WP(6);
-                    const long long t0 = clock64();
-                    while (*f < b.z) {
-                        __nanosleep(32);
-                        if (clock64() - t0 > kSpinLimitCycles) __trap();
-                    }
-                }
-                __threadfence();
-                asm volatile("fence.proxy.async;" ::: "memory");  // data written by other CTAs is read by the TMA engine
-            } else {
-                mbar_wait(r.bars + (M::bDescEmpty + slot) * 8, phase ^ 1u);
-            }
-            asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.smem + M::kDesc + slot * 16), "r"(chunk), "r"(tile), "r"(plen),
-                         "r"(parent)
-                         : "memory");
-            mbar_arrive(r.bars + (M::bDescFull + slot) * 8);
-        }
-        chunk = __shfl_sync(0xffffffffu, chunk, 0);
+        // item n: descriptor posted; broadcast what the stream needs
+        const int32_t chunk = __shfl_sync(0xffffffffu, h.valid ? h.a.x : -1, 0);
         if (chunk < 0) return;
-        tile = __shfl_sync(0xffffffffu, tile, 0);
-        slen = __shfl_sync(0xffffffffu, slen, 0);
-        stream_off = __shfl_sync(0xffffffffu, stream_off, 0);
+        const int32_t tile = __shfl_sync(0xffffffffu, h.tile, 0);
+        const int32_t slen = __shfl_sync(0xffffffffu, h.a.w, 0);
+        const int32_t stream_off = __shfl_sync(0xffffffffu, h.b.y, 0);
         WarpWords w;
         w.init(p.stream + stream_off, slen, lane);
-        produce_stream<SETS>(p, r, w, slen, tile, n_leaf, n_set);
-        item = next;
+        if (lane == 0) h.begin(n + 1, slen, p.claim_lead);
+        produce_stream<SETS>(p, r, w, slen, tile, n_leaf, n_set, h);
+        if (lane == 0 && !h.posted) {
+            if (!h.fetched) h.fetch(p);
+            header_step<SETS>(p, r, h, true);
+        }
     }
 }
 
@@ -666,6 +762,7 @@ __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
     ItemDesc d;
     for (uint32_t n = 0; next_item<kSetRingFwd>(ring, n, d); n++) {
         const uint32_t slot = n & 1u;
+        PMFS_TRACE_BEGIN
         {
             DevEnv<false, kSetRingFwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
             Code4 forced[kNG];
@@ -683,6 +780,7 @@ __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
         if (d.plen <= kProgWords) staged[slot]++;
         finish_item(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr,
                     ring.bars + (M::bDescEmpty + slot) * 8);
+        PMFS_TRACE_END(d.chunk, d.tile)
     }
 }
 
@@ -703,6 +801,7 @@ __global__ void __launch_bounds__(kThreads) bwd_kernel(const WalkParams p) {
     for (uint32_t n = 0; next_item<kSetRingBwd>(ring, n, d); n++) {
         const uint32_t slot = n & 1u;
         uint32_t err;
+        PMFS_TRACE_BEGIN
         {
             DevEnv<true, kSetRingBwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
             Code4 P[kNG], forced[kNG];
@@ -731,6 +830,7 @@ __global__ void __launch_bounds__(kThreads) bwd_kernel(const WalkParams p) {
         if (err) atomicOr(p.err_flag, 1u);
         if (d.plen <= kProgWords) staged[slot]++;
         finish_item(p.ready + (int64_t)d.chunk * p.ctas_per_chunk + d.tile, ring.bars + (M::bDescEmpty + slot) * 8);
+        PMFS_TRACE_END(d.chunk, d.tile)
     }
 }
 
@@ -1331,6 +1431,10 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     wp.chunk_nchild = c->d_chunk_nchild.ptr;
     wp.ctas_per_chunk = (int32_t)((wp.G + kTileGroups - 1) / kTileGroups);
     wp.stack_depth = fwd ? P.fwd_stack_depth : P.bwd_stack_depth;
+    {
+        static const int lead = getenv("PMFS_CLAIM_LEAD") ? atoi(getenv("PMFS_CLAIM_LEAD")) : 4;
+        wp.claim_lead = lead;
+    }
     const int64_t n_items = (int64_t)P.chunks.size() * wp.ctas_per_chunk;
     if (n_items > 0x7fffffffll) {
         g_error = "too many (chunk, column tile) work items: use a smaller column tile";
@@ -1368,6 +1472,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
         unsigned long long z[16] = {0};
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
         PMFS_CUDA(cudaMemcpyToSymbol(g_waitprof, z, sizeof(z)));
+        PMFS_CUDA(cudaMemcpyToSymbol(g_trace_n, z, sizeof(unsigned int)));
     }
 #endif
     PMFS_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kThreads), args, smem, c->stream));
@@ -1381,6 +1486,18 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
                 "producer: dep %.1f%% desc_empty %.1f%% leaf_empty %.1f%% set_empty %.1f%% | walker warp-cycles %.3g\n",
                 fwd ? "fwd" : "bwd", grid, per_sm, wp.n_items, 100 * z[0] / W, 100 * z[1] / W, 100 * z[2] / W, 100 * z[3] / W, 100 * z[4] / W,
                 100 * z[6] / Pr, 100 * z[7] / Pr, 100 * z[8] / Pr, 100 * z[9] / Pr, W);
+        if (const char* dir = getenv("PMFS_TRACE_DIR")) {
+            unsigned int tn = 0;
+            PMFS_CUDA(cudaMemcpyFromSymbol(&tn, g_trace_n, sizeof(tn)));
+            tn = std::min<unsigned int>(tn, kTraceCap);
+            std::vector<ulonglong4> tr(tn);
+            if (tn) PMFS_CUDA(cudaMemcpyFromSymbol(tr.data(), g_trace, (size_t)tn * sizeof(ulonglong4)));
+            const std::string path = std::string(dir) + (fwd ? "/trace_fwd.bin" : "/trace_bwd.bin");
+            if (FILE* fp = fopen(path.c_str(), "wb")) {
+                fwrite(tr.data(), sizeof(ulonglong4), tn, fp);
+                fclose(fp);
+            }
+        }
     }
 #endif
     (*launches)++;
