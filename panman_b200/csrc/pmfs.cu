@@ -81,6 +81,8 @@ struct WalkParams {
     unsigned long long out_cap;     // capacity of one owner's region
     int32_t n_regions;              // > 0: one output region per 32 column groups (see emit); 0: regions per owner
     uint32_t bucket_mask;           // single-GPU runs: regions are further split by (node & bucket_mask), bucket-major
+    uint32_t* cell_count;           // [n_nodes][n_regions] or null: records of (node, region) -- see order_cells_kernel
+    uint32_t* cell_start;           // [n_nodes][n_regions]: where they start inside the region
     int64_t region_base;            // region index of this column tile's first 32 groups
     int32_t n_owners;               // 1, or the number of ranks in column-shard mode
     int32_t owner_bound[17];        // nodes [owner_bound[r], owner_bound[r+1]) are owned by rank r
@@ -607,7 +609,14 @@ struct DevEnv {
                 const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
                 const int64_t region = own_base + (int64_t)(node & p.bucket_mask) * p.n_regions + p.region_base + ((gwarp + j * kTPB) >> 5);
                 unsigned long long base = 0;
-                if (lane == 0) base = atomicAdd(p.out_count + region, (unsigned long long)total);
+                if (lane == 0) {
+                    base = atomicAdd(p.out_count + region, (unsigned long long)total);
+                    if (p.cell_count) {  // (a (node, region) pair is emitted at most once per run)
+                        const int64_t cell = (int64_t)node * p.n_regions + region;
+                        p.cell_count[cell] = total;
+                        p.cell_start[cell] = (uint32_t)base;
+                    }
+                }
                 base = __shfl_sync(0xffffffffu, base, 0);
                 emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * kTPB);
             }
@@ -979,6 +988,92 @@ __global__ void compact_areas_kernel(const unsigned long long* __restrict__ src,
     }
 }
 
+// Ordering without a sort (single-GPU runs).  The top-down pass leaves, for every (node, column region) CELL, how many
+// records it emitted and where they start inside the region's buffer; inside a cell the records are contiguous and in
+// column order.  The (node,pos) order is therefore cell order, node-major: an exclusive prefix sum over the cell counts
+// gives every cell its place in the output and this kernel copies the cells there, turning the packed 8-byte records
+// into pmfs_mut on the way.  One warp per 32 consecutive cells: their output range is contiguous, so the warp walks it
+// 32 records at a time and each lane finds the cell its record belongs to from a mask of the cell starts in the window.
+// stats = {records, largest region count}: on overflow of a region or of `out` nothing is written (the host redoes it).
+__device__ __forceinline__ int kth_set_bit(uint32_t mask, uint32_t k) {  // position of the k-th (from 0) set bit
+    int pos = 0;
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+        const uint32_t c = __popc((mask >> pos) & ((1u << step) - 1u));
+        if (k >= c) {
+            pos += step;
+            k -= c;
+        }
+    }
+    return pos;
+}
+__global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, unsigned long long cap, const uint32_t* __restrict__ cnt,
+                                   const uint32_t* __restrict__ start, const uint32_t* __restrict__ prefix, int64_t cells, int32_t W,
+                                   int pos_bits, const unsigned long long* __restrict__ stats, unsigned long long out_cap,
+                                   pmfs_mut* __restrict__ out) {
+    if (stats[1] > cap || stats[0] > out_cap) return;
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int64_t stride = (((int64_t)gridDim.x * blockDim.x) >> 5) * 32;
+    const unsigned long long pos_mask = (1ull << pos_bits) - 1;
+    uint32_t* const out32 = (uint32_t*)out;
+    int64_t c0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32;
+    // the three per-cell words of the NEXT block are fetched while the current one is copied
+    uint32_t n_nx = 0, s_nx = 0, e_nx = 0;
+    if (c0 + lane < cells) {
+        n_nx = cnt[c0 + lane];
+        s_nx = start[c0 + lane];
+        e_nx = prefix[c0 + lane];
+    }
+    for (; c0 < cells; c0 += stride) {
+        const uint32_t n_l = n_nx, s_l = s_nx, e_l = e_nx;
+        n_nx = 0;
+        if (c0 + stride + lane < cells) {
+            n_nx = cnt[c0 + stride + lane];
+            s_nx = start[c0 + stride + lane];
+            e_nx = prefix[c0 + stride + lane];
+        }
+        const uint32_t nonempty = __ballot_sync(full, n_l != 0);
+        if (nonempty == 0) continue;
+        const int32_t region = (int32_t)((c0 + lane) % W);
+        const unsigned long long* src = keys + (unsigned long long)region * cap + s_l;
+        const uint32_t longest = __reduce_max_sync(full, n_l);
+        if (longest <= 24) {
+            // the usual case, a handful of records per cell: every lane copies its own cell
+            uint32_t* o = out32 + (size_t)e_l * 3;
+            for (uint32_t i = 0; i < n_l; i++, o += 3) {
+                const unsigned long long r = src[i], key = r >> kPayloadBits;
+                o[0] = (uint32_t)(key >> pos_bits);
+                o[1] = (uint32_t)(key & pos_mask);
+                o[2] = (uint32_t)(r & 3) | ((uint32_t)((r >> 2) & 15) << 8) | ((uint32_t)((r >> 6) & 15) << 16);
+            }
+            continue;
+        }
+        // some cell is long (a block of N's, an insertion): the warp walks the block's output range 32 records at a time
+        const uint32_t e0 = __shfl_sync(full, e_l, 0);
+        const uint32_t rel_l = e_l - e0;  // (lanes past the last cell are empty and never looked at)
+        const uint32_t total = __reduce_add_sync(full, n_l);
+        for (uint32_t t0 = 0; t0 < total; t0 += 32) {
+            const bool here = n_l != 0 && rel_l >= t0 && rel_l < t0 + 32;
+            const uint32_t marks = __reduce_or_sync(full, here ? 1u << (rel_l - t0) : 0u);
+            const uint32_t before = __popc(__ballot_sync(full, n_l != 0 && rel_l < t0));
+            const uint32_t t = t0 + lane;
+            // the record at output slot t belongs to the k-th non-empty cell of the block (k counted from 0)
+            const uint32_t k = before + __popc(marks & ((2u << lane) - 1u)) - 1u;
+            const int src_lane = t < total ? kth_set_bit(nonempty, k) : 0;
+            const unsigned long long* src_t = (const unsigned long long*)__shfl_sync(full, (unsigned long long)src, src_lane);
+            const uint32_t rel_src = __shfl_sync(full, rel_l, src_lane);
+            if (t < total) {
+                const unsigned long long r = src_t[t - rel_src], key = r >> kPayloadBits;
+                uint32_t* o = out32 + ((size_t)e0 + t) * 3;
+                o[0] = (uint32_t)(key >> pos_bits);
+                o[1] = (uint32_t)(key & pos_mask);
+                o[2] = (uint32_t)(r & 3) | ((uint32_t)((r >> 2) & 15) << 8) | ((uint32_t)((r >> 6) & 15) << 16);
+            }
+        }
+    }
+}
+
 // region r's records (count[r] of them at src + r*cap) -> dst + offset[r]: makes the per-region output contiguous
 __global__ void compact_regions_kernel(const unsigned long long* __restrict__ src, unsigned long long cap,
                                        const unsigned long long* __restrict__ count, const unsigned long long* __restrict__ offset,
@@ -1171,6 +1266,7 @@ struct pmfs_ctx {
     DevBuf<unsigned long long> d_count;
     DevBuf<unsigned int> d_err;
     DevBuf<uint8_t> d_sort_tmp, d_scan_tmp;
+    DevBuf<uint32_t> d_cell_count, d_cell_start, d_cell_prefix;  // per (node, column region), see order_cells_kernel
     unsigned long long* h_stats = nullptr;  // pinned: {records, largest area, error flag} of the last run
     DevBuf<pmfs_mut> d_out;
     // host-path staging
@@ -1353,7 +1449,7 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_S.release(); c->d_D.release(); c->d_cons_planes.release(); c->d_forced_planes.release();
     c->d_xcode.release(); c->d_xvalid.release(); c->d_keys.release(); c->d_keys_alt.release();
     c->d_count.release(); c->d_err.release();
-    c->d_scan_tmp.release();
+    c->d_scan_tmp.release(); c->d_cell_count.release(); c->d_cell_start.release(); c->d_cell_prefix.release();
     if (c->h_stats) cudaFreeHost(c->h_stats);
     c->d_sort_tmp.release(); c->d_out.release(); c->d_msa.release(); c->d_cons.release(); c->d_forced.release();
     c->d_chars.release();
@@ -1504,6 +1600,15 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     return PMFS_OK;
 }
 
+static int launch_order_cells(pmfs_ctx* c, size_t region_cap, int64_t cells, int64_t W, int pos_bits, const unsigned long long* d_stats,
+                              size_t out_cap) {
+    const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>((int64_t)c->n_sms * 8, (cells + 255) / 256));
+    order_cells_kernel<<<grid, 256, 0, c->stream>>>(c->d_keys.ptr, region_cap, c->d_cell_count.ptr, c->d_cell_start.ptr, c->d_cell_prefix.ptr,
+                                                    cells, (int32_t)W, pos_bits, d_stats, out_cap, c->d_out.ptr);
+    PMFS_CUDA(cudaGetLastError());
+    return PMFS_OK;
+}
+
 static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
                            const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut** d_out, int64_t* n_out) {
     if (!c || (algo != PMFS_FITCH && algo != PMFS_SANKOFF) || !d_msa || !d_cons || !n_out || n_cols <= 0) {
@@ -1589,6 +1694,16 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         const int passes = (node_bits - max_bits + 7) / 8;
         bucket_bits = std::max(0, node_bits - 8 * passes);
     }
+    // ... unless the (node, region) cell matrix fits: then the records are ordered without any sort (order_cells_kernel)
+    static const bool force_radix = getenv("PMFS_ORDER") && std::string(getenv("PMFS_ORDER")) == "radix";  // test hook
+    const int64_t cells = (int64_t)P->n_nodes * W;
+    const bool use_cells = !shard && by_columns && !force_radix && cells <= (1ll << 30);
+    if (use_cells) {
+        bucket_bits = 0;
+        if ((rc = c->d_cell_count.ensure((size_t)cells))) return rc;
+        if ((rc = c->d_cell_start.ensure((size_t)cells))) return rc;
+        if ((rc = c->d_cell_prefix.ensure((size_t)cells))) return rc;
+    }
     const int64_t n_owners = !by_columns ? n_parts : shard ? W * n_parts : (W << bucket_bits);  // number of output areas
     const size_t n_ctr = (size_t)std::max<int64_t>(16, n_owners);
     if ((rc = c->d_count.ensure(2 * n_ctr + 16))) return rc;
@@ -1606,11 +1721,12 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     unsigned long long count = 0;
     std::vector<unsigned long long>& counts = c->h_counts;
     counts.assign(shard ? n_ctr : 16, 0);
-    size_t region = 0;
+    size_t region = 0, ordered_cap = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
         if ((rc = c->d_keys.ensure(cap))) return rc;
         region = c->d_keys.cap / (size_t)n_owners;
         PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, (n_ctr + 16) * sizeof(unsigned long long), c->stream));
+        if (use_cells) PMFS_CUDA(cudaMemsetAsync(c->d_cell_count.ptr, 0, (size_t)cells * sizeof(uint32_t), c->stream));
         fwd_ms = bwd_ms = 0;
         tm.n_launches = 0;
         for (int64_t g0 = 0; g0 < G_all; g0 += tile_groups) {
@@ -1634,6 +1750,8 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             wp.n_owners = n_parts;
             wp.n_regions = by_columns ? (int32_t)W : 0;
             wp.bucket_mask = (1u << bucket_bits) - 1u;
+            wp.cell_count = use_cells ? c->d_cell_count.ptr : nullptr;
+            wp.cell_start = use_cells ? c->d_cell_start.ptr : nullptr;
             wp.region_base = g0 / 32;
             for (int r = 0; r <= c->parts.n_parts; r++) wp.owner_bound[r] = c->parts.bound[r];
             wp.err_flag = (unsigned int*)(d_stats + 2);
@@ -1674,7 +1792,21 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             area_stats_kernel<<<(unsigned)std::min<int64_t>(296, (n_owners + 255) / 256), 256, 0, c->stream>>>(c->d_count.ptr, n_owners, d_stats);
             tm.n_launches++;
             PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-            if (by_columns) {
+            if (use_cells) {
+                // exclusive prefix sum over the cell counts = every cell's place in the (node,pos) order; the copy into
+                // that order is queued right away when the output buffer of the previous run is still there (the kernel
+                // checks on the device that nothing overflowed), so the GPU does not wait for the host to learn the count
+                size_t scan_bytes = 0;
+                PMFS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, c->d_cell_count.ptr, c->d_cell_prefix.ptr, (int)cells, c->stream));
+                if ((rc = c->d_scan_tmp.ensure(scan_bytes + 16))) return rc;
+                PMFS_CUDA(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.ptr, scan_bytes, c->d_cell_count.ptr, c->d_cell_prefix.ptr, (int)cells, c->stream));
+                ordered_cap = c->d_out.cap;
+                if (ordered_cap > 0) {
+                    rc = launch_order_cells(c, region, cells, W, pos_bits, d_stats, ordered_cap);
+                    if (rc) return rc;
+                    tm.n_launches++;
+                }
+            } else if (by_columns) {
                 // Areas are laid out (low node bits, column region)-major and every node's records inside an area are
                 // contiguous and column-ordered: pack the areas; a stable sort on the remaining HIGH node bits alone then
                 // gives the (node,pos) order.  Queued before the host knows the record count (the device checks for
@@ -1768,8 +1900,14 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         if (d_out) *d_out = nullptr;
         return PMFS_OK;
     }
-    // order by (node,pos): keys-only radix sort over exactly the key bits that can be set
-    if (n > 0) {
+    if (n > 0 && use_cells) {
+        if ((size_t)n > ordered_cap) {  // first run, or more records than ever before: now the count is known
+            if ((rc = c->d_out.ensure((size_t)n + (size_t)n / 8))) return rc;
+            rc = launch_order_cells(c, region, cells, W, pos_bits, d_stats, c->d_out.cap);
+            if (rc) return rc;
+            tm.n_launches++;
+        }
+    } else if (n > 0) {  // order by (node,pos): keys-only radix sort over exactly the key bits that can be set
         if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
         if ((rc = c->d_out.ensure((size_t)n))) return rc;
         cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
