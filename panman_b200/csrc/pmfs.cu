@@ -117,9 +117,16 @@ struct WarpWords {
 constexpr int kNG = 2;                    // column groups per walking thread (walk.cuh: Env::kGroups)
 constexpr int kTileGroups = kTPB * kNG;   // column groups per work item (256 groups = 8 192 columns)
 constexpr int kThreads = kTPB + 32;       // 4 walking warps + 1 producer warp
-constexpr int kLeafRing = 4;              // leaf-row units in flight (4 KB each: 16 B for each group of the tile)
-constexpr int kSetRingFwd = 1;            // set slots in flight (16 KB each: 64 B for each group), bottom-up pass
-constexpr int kSetRingBwd = 2;            // top-down pass: every internal node is one set
+// Operand rings of a CTA, per pass: leaf-row units in flight (4 KB each: 16 B for each group of the tile) and set slots in
+// flight (16 KB each: 64 B for each group).  One int encodes both (leaf * 16 + sets) so that it can be a template argument.
+// Bottom-up: mostly leaves, and its 32 KB walk stack + 128 registers cap it at 3 CTAs per SM anyway.  Top-down: every
+// internal node is one set; 2 + 2 keeps a CTA under 57 KB, which lets 4 CTAs share an SM (measured: 0.41 -> 0.36 ms).
+#ifndef PMFS_RING_FWD
+#define PMFS_RING_FWD (4 * 16 + 1)
+#define PMFS_RING_BWD (2 * 16 + 2)
+#endif
+constexpr int kSetRingFwd = PMFS_RING_FWD;
+constexpr int kSetRingBwd = PMFS_RING_BWD;
 constexpr int kProgWords = 256;           // walk programs up to this many words are staged in shared memory
 constexpr int kUnitBytes = kTileGroups * 16;
 constexpr int kSetBytes = kTileGroups * 64;
@@ -238,8 +245,9 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 // quarter-sets of all 256 groups, a single contiguous copy).  Per ring entry: `full` flips when its bytes have
 // landed, `empty` when all 4 walking warps have read it.  Entry numbers keep counting across the work items of a
 // persistent CTA, so phases never need resetting.
-template <int SETS>
+template <int RING>
 struct SmemMap {
+    static constexpr int kLeafRing = RING >> 4, SETS = RING & 15;
     static constexpr int kProg = 0;                                 // 2 staged programs
     static constexpr int kDesc = 2 * kProgWords * 4;                // 2 item descriptors (16 B each, 64 B reserved)
     static constexpr int kLeaf = kDesc + 64;                        // leaf ring
@@ -299,9 +307,9 @@ struct NextItem {
         fetched = true;
     }
 };
-template <int SETS>
+template <int RING>
 __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, NextItem& h, bool block) {
-    using M = SmemMap<SETS>;
+    using M = SmemMap<RING>;
     const uint32_t slot = h.ordinal & 1u, phase = (h.ordinal >> 1) & 1u;
     if (!h.slot_free) {  // the walkers are done with the item two before this one
         const uint32_t bar = r.bars + (M::bDescEmpty + slot) * 8;
@@ -344,10 +352,10 @@ __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, 
 
 // Producer side of one item: walk the chunk's load stream and keep both rings full.  Called by the whole producer warp
 // (the stream words are read warp-wide); lane 0 drives TMA and, in passing, the header of the next item.
-template <int SETS>
+template <int RING>
 __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& r, WarpWords& w, int32_t slen, int tile,
                                                uint32_t& n_leaf, uint32_t& n_set, NextItem& h) {
-    using M = SmemMap<SETS>;
+    using M = SmemMap<RING>;
     const int lane = threadIdx.x & 31;
     const int64_t g0 = (int64_t)tile * kTileGroups;
     const uint32_t leaf_bytes = (uint32_t)min((int64_t)kTileGroups, p.G - g0) * 16u;
@@ -355,7 +363,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
         const uint32_t e = w.get(j, lane);
         if (e & kStreamSet) {
             if (lane == 0) {
-                const uint32_t u = n_set % SETS, par = (n_set / SETS) & 1u;
+                const uint32_t u = n_set % M::SETS, par = (n_set / M::SETS) & 1u;
                 PMFS_WP(9);
                 mbar_wait(r.bars + (M::bSetEmpty + u) * 8, par ^ 1u);  // all walkers are done with the slot's previous set
                 // one node's set for this tile: 4 quarters of `tile_w` groups, contiguous (leaf_bytes = tile_w * 16)
@@ -366,7 +374,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
             n_set++;
         } else {
             if (lane == 0) {
-                const uint32_t u = n_leaf % kLeafRing, par = (n_leaf / kLeafRing) & 1u;
+                const uint32_t u = n_leaf % M::kLeafRing, par = (n_leaf / M::kLeafRing) & 1u;
                 PMFS_WP(8);
                 mbar_wait(r.bars + (M::bLeafEmpty + u) * 8, par ^ 1u);
                 mbar_arrive_expect_tx(r.bars + (M::bLeafFull + u) * 8, leaf_bytes);
@@ -382,7 +390,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
             const int32_t left = slen - 1 - j;
             if (left == h.t_claim) h.claim(p);
             else if (left == h.t_fetch) h.fetch(p);
-            else if (left < h.t_fetch && !h.posted && (left & 1) == 0) header_step<SETS>(p, r, h, false);
+            else if (left < h.t_fetch && !h.posted && (left & 1) == 0) header_step<RING>(p, r, h, false);
         }
     }
 }
@@ -395,10 +403,10 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
 // Set arrays are TILE-MAJOR: S[internal id][tile][quarter][groups of the tile] (uint4; 256 groups per tile, fewer in
 // the last one), so one node's set for one tile is a single contiguous block of up to 16 KB (one TMA copy) and a
 // warp's 128-bit stores are 512-byte segments.  A node's row is exactly 4*G uint4: no padding.
-template <bool READONLY_SETS, int SETS>
+template <bool READONLY_SETS, int RING>
 struct DevEnv {
     static constexpr int kGroups = kNG;
-    using M = SmemMap<SETS>;
+    using M = SmemMap<RING>;
     const WalkParams& p;
     const Ring& ring;
     int64_t g[kNG];      // clamped column groups
@@ -449,7 +457,7 @@ struct DevEnv {
 
     // next leaf unit: wait until the TMA copy has landed, read this thread's 16 bytes per group, hand the unit back
     __device__ __forceinline__ void leaf(uint32_t, uint4 (&w)[kNG]) {
-        const uint32_t u = n_leaf % kLeafRing, par = (n_leaf / kLeafRing) & 1u;
+        const uint32_t u = n_leaf % M::kLeafRing, par = (n_leaf / M::kLeafRing) & 1u;
         PMFS_WP(2);
         mbar_wait(ring.bars + (M::bLeafFull + u) * 8, par);
         const uint32_t base = ring.smem + M::kLeaf + u * kUnitBytes + threadIdx.x * 16;
@@ -461,7 +469,7 @@ struct DevEnv {
     }
     // next set slot (a set written by an earlier work item): 4 quarters x kNG groups
     __device__ __forceinline__ void load_x(uint32_t, Planes16 (&s)[kNG]) {
-        const uint32_t u = n_set % SETS, par = (n_set / SETS) & 1u;
+        const uint32_t u = n_set % M::SETS, par = (n_set / M::SETS) & 1u;
         PMFS_WP(3);
         mbar_wait(ring.bars + (M::bSetFull + u) * 8, par);
         const uint32_t base = ring.smem + M::kSet + u * kSetBytes + threadIdx.x * 16;
@@ -668,18 +676,18 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
 // CTA-wide barrier after set-up.
 constexpr int kPassFwd = 0, kPassBwd = 1;
 
-template <int SETS>
+template <int RING>
 __device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars) {
-    using M = SmemMap<SETS>;
+    using M = SmemMap<RING>;
     Ring r;
     r.smem = (uint32_t)__cvta_generic_to_shared(smem);
     r.bars = (uint32_t)__cvta_generic_to_shared(bars);
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kLeafRing; i++) {
+        for (int i = 0; i < M::kLeafRing; i++) {
             mbar_init(r.bars + (M::bLeafFull + i) * 8, 1);           // one arrive.expect_tx by the producer
             mbar_init(r.bars + (M::bLeafEmpty + i) * 8, kTPB / 32);  // one arrive per walking warp
         }
-        for (int i = 0; i < SETS; i++) {
+        for (int i = 0; i < M::SETS; i++) {
             mbar_init(r.bars + (M::bSetFull + i) * 8, 1);
             mbar_init(r.bars + (M::bSetEmpty + i) * 8, kTPB / 32);
         }
@@ -698,7 +706,7 @@ __device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars)
 // item after item.  Everything that does not need the dependency is started before it is polled, the item record is
 // one 32-byte load, and the claim for the NEXT item is issued before this one is produced, so that per item only the
 // record load and the dependency poll remain on the producer's critical path.
-template <int PASS, int SETS>
+template <int PASS, int RING>
 __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r) {
     const int lane = threadIdx.x & 31;
     uint32_t n_leaf = 0, n_set = 0;
@@ -706,7 +714,7 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
     if (lane == 0) {
         h.begin(0, 1, 0);
         h.fetch(p);
-        header_step<SETS>(p, r, h, true);
+        header_step<RING>(p, r, h, true);
     }
     for (uint32_t n = 0;; n++) {
         // item n: descriptor posted; broadcast what the stream needs
@@ -718,18 +726,18 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
         WarpWords w;
         w.init(p.stream + stream_off, slen, lane);
         if (lane == 0) h.begin(n + 1, slen, p.claim_lead);
-        produce_stream<SETS>(p, r, w, slen, tile, n_leaf, n_set, h);
+        produce_stream<RING>(p, r, w, slen, tile, n_leaf, n_set, h);
         if (lane == 0 && !h.posted) {
             if (!h.fetched) h.fetch(p);
-            header_step<SETS>(p, r, h, true);
+            header_step<RING>(p, r, h, true);
         }
     }
 }
 
 // Walking warps: take the next descriptor; returns false when there is no more work.
-template <int SETS>
+template <int RING>
 __device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d) {
-    using M = SmemMap<SETS>;
+    using M = SmemMap<RING>;
     const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
     {
         PMFS_WP(0);
@@ -794,7 +802,7 @@ __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
 }
 
 template <int ALGO>
-__global__ void __launch_bounds__(kThreads) bwd_kernel(const WalkParams p) {
+__global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 1) bwd_kernel(const WalkParams p) {
     using M = SmemMap<kSetRingBwd>;
     extern __shared__ uint4 smem[];
     __shared__ __align__(8) unsigned long long bars[M::kBars];

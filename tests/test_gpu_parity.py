@@ -167,3 +167,19 @@ def test_run_chars_matches_codes_path():
                 got = ctx.run_chars(algo, chars, cons_chars, forced_chars)
             assert G.same_muts(got, want), (trial, algo)
             assert G.same_muts(got, run_gpu(tree, algo, codes, cons, forced))
+
+
+def test_radix_ordering_path_in_subprocess():
+    """Single-GPU runs order their records through the (node, region) cell matrix; the radix-sort path (bucketed
+    emission + stable sort on the high node bits) is what column shards and very large cell matrices use.  Run a few of
+    the parity tests above with that path forced (PMFS_ORDER is read once per process)."""
+    import os
+    import subprocess
+    import sys
+
+    env = dict(os.environ, PMFS_ORDER="radix")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(here, "test_gpu_parity.py"), "-q", "-x", "-m", "gpu", "-k",
+                        "golden_small_cases or random_trees or deep_ladder or device_side_packing"],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
