@@ -424,6 +424,8 @@ struct DevEnv {
     const uint32_t* gprog;
     uint32_t sprog;      // shared address of this item's staged program
     uint32_t ltmask;     // bits of a group word whose column is smaller than the column of bit `lane`
+    mutable unsigned long long blk_base[kNG];  // lane 0, cell mode: the warp's current output block per group slot
+    mutable uint32_t blk_used[kNG], blk_size[kNG];
 
     __device__ DevEnv(const WalkParams& p_, const Ring& r, const ItemDesc& d, uint32_t slot, uint32_t prog_parity,
                       uint32_t& n_leaf_, uint32_t& n_set_, void* smem_generic)
@@ -606,7 +608,52 @@ struct DevEnv {
     // (bucket-major layout): that is the first pass of an LSD radix sort done for free while emitting, and the stable
     // sort only has to cover the remaining high node bits (one radix pass for up to 2^16 nodes instead of four on the
     // whole key).  Regions per owning rank (column shards): see pmfs_set_shard.
+    //
+    // Cell mode (single-GPU runs, see order_cells_kernel): the ordering kernel is told where every (node, region) cell
+    // starts, so a region need not be dense.  Each warp therefore reserves space in BLOCKS of kEmitBlock records -- one
+    // atomic per work item and column-group slot, issued when the item starts and not waited for until the first node
+    // that has mutations -- and hands out the block to its nodes from a register.  The round trip of a per-node atomic
+    // was the longest latency on the top-down path, which is what the chain of chunks below the root is made of.
+    static constexpr uint32_t kEmitBlock = 256;
+    __device__ __forceinline__ void reserve_blocks() const {
+        if (lane != 0) return;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            blk_used[j] = blk_size[j] = 0;
+            if (gwarp + j * kTPB < p.G) {
+                blk_base[j] = atomicAdd(p.out_count + p.region_base + ((gwarp + j * kTPB) >> 5), (unsigned long long)kEmitBlock);
+                blk_size[j] = kEmitBlock;
+            }
+        }
+    }
+    __device__ void emit_cells(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            if (!__any_sync(0xffffffffu, m[j] != 0)) continue;
+            const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
+            const int64_t region = p.region_base + ((gwarp + j * kTPB) >> 5);
+            unsigned long long base = 0;
+            if (lane == 0) {
+                if (total > blk_size[j] - blk_used[j]) {  // block used up (or a node with more records than a block holds)
+                    blk_size[j] = total > kEmitBlock ? total : kEmitBlock;
+                    blk_base[j] = atomicAdd(p.out_count + region, (unsigned long long)blk_size[j]);
+                    blk_used[j] = 0;
+                }
+                base = blk_base[j] + blk_used[j];
+                blk_used[j] += total;
+                const int64_t cell = (int64_t)node * p.n_regions + region;  // (a cell is emitted at most once per run)
+                p.cell_count[cell] = total;
+                p.cell_start[cell] = (uint32_t)base;
+            }
+            base = __shfl_sync(0xffffffffu, base, 0);
+            emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * kTPB);
+        }
+    }
     __device__ void emit(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+        if (p.cell_count) {
+            emit_cells(node, m, G, P);
+            return;
+        }
         if (p.n_regions > 0) {
             int64_t own_base = 0;  // column shards: regions are owner-major (owner of this node's list, uniform in the warp)
 #pragma unroll 1  // (unrolled 16-fold this loop was a fifth of the kernel's code)
@@ -617,14 +664,7 @@ struct DevEnv {
                 const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
                 const int64_t region = own_base + (int64_t)(node & p.bucket_mask) * p.n_regions + p.region_base + ((gwarp + j * kTPB) >> 5);
                 unsigned long long base = 0;
-                if (lane == 0) {
-                    base = atomicAdd(p.out_count + region, (unsigned long long)total);
-                    if (p.cell_count) {  // (a (node, region) pair is emitted at most once per run)
-                        const int64_t cell = (int64_t)node * p.n_regions + region;
-                        p.cell_count[cell] = total;
-                        p.cell_start[cell] = (uint32_t)base;
-                    }
-                }
+                if (lane == 0) base = atomicAdd(p.out_count + region, (unsigned long long)total);
                 base = __shfl_sync(0xffffffffu, base, 0);
                 emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * kTPB);
             }
@@ -802,7 +842,7 @@ __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
 }
 
 template <int ALGO>
-__global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 1) bwd_kernel(const WalkParams p) {
+__global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 3) bwd_kernel(const WalkParams p) {
     using M = SmemMap<kSetRingBwd>;
     extern __shared__ uint4 smem[];
     __shared__ __align__(8) unsigned long long bars[M::kBars];
@@ -821,6 +861,7 @@ __global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 1) bwd_kern
         PMFS_TRACE_BEGIN
         {
             DevEnv<true, kSetRingBwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            if (p.cell_count) env.reserve_blocks();
             Code4 P[kNG], forced[kNG];
             uint32_t pv[kNG], colmask[kNG];
             const Code4* fp = nullptr;
@@ -1003,6 +1044,10 @@ __global__ void compact_areas_kernel(const unsigned long long* __restrict__ src,
 // into pmfs_mut on the way.  One warp per 32 consecutive cells: their output range is contiguous, so the warp walks it
 // 32 records at a time and each lane finds the cell its record belongs to from a mask of the cell starts in the window.
 // stats = {records, largest region count}: on overflow of a region or of `out` nothing is written (the host redoes it).
+__global__ void cells_total_kernel(const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ prefix, int64_t cells,
+                                   unsigned long long* __restrict__ stats) {
+    stats[0] = (unsigned long long)prefix[cells - 1] + cnt[cells - 1];
+}
 __device__ __forceinline__ int kth_set_bit(uint32_t mask, uint32_t k) {  // position of the k-th (from 0) set bit
     int pos = 0;
 #pragma unroll
@@ -1799,7 +1844,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         } else {
             area_stats_kernel<<<(unsigned)std::min<int64_t>(296, (n_owners + 255) / 256), 256, 0, c->stream>>>(c->d_count.ptr, n_owners, d_stats);
             tm.n_launches++;
-            PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+            if (!use_cells) PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
             if (use_cells) {
                 // exclusive prefix sum over the cell counts = every cell's place in the (node,pos) order; the copy into
                 // that order is queued right away when the output buffer of the previous run is still there (the kernel
@@ -1808,6 +1853,10 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                 PMFS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, c->d_cell_count.ptr, c->d_cell_prefix.ptr, (int)cells, c->stream));
                 if ((rc = c->d_scan_tmp.ensure(scan_bytes + 16))) return rc;
                 PMFS_CUDA(cub::DeviceScan::ExclusiveSum(c->d_scan_tmp.ptr, scan_bytes, c->d_cell_count.ptr, c->d_cell_prefix.ptr, (int)cells, c->stream));
+                // (the region counters include the unused ends of the warps' output blocks: the record count is the cells')
+                cells_total_kernel<<<1, 1, 0, c->stream>>>(c->d_cell_count.ptr, c->d_cell_prefix.ptr, cells, d_stats);
+                tm.n_launches++;
+                PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
                 ordered_cap = c->d_out.cap;
                 if (ordered_cap > 0) {
                     rc = launch_order_cells(c, region, cells, W, pos_bits, d_stats, ordered_cap);
