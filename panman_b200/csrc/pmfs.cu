@@ -440,9 +440,8 @@ struct DevEnv {
             active[j] = gj < p_.G;
             g[j] = active[j] ? gj : p_.G - 1;
         }
-        ltmask = 0;
-        for (int q = 0; q < 32; q++)
-            if (column_of_bit(q) < column_of_bit(lane)) ltmask |= 1u << q;
+        // bit q is column 8*(q&3) + (q>>2): smaller residues q&3 come first as a whole, then smaller q>>2 of this lane's own
+        ltmask = 0x11111111u * ((1u << (lane & 3)) - 1u) | ((0x11111111u << (lane & 3)) & ((1u << (4 * (lane >> 2))) - 1u));
         PMFS_WP(1);
         if (prog_staged) mbar_wait(r.bars + (M::bProg + slot) * 8, prog_parity);
         else gprog = p_.prog + p_.chunk_off[d.chunk];
@@ -1088,17 +1087,20 @@ __global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, 
         }
         const uint32_t nonempty = __ballot_sync(full, n_l != 0);
         if (nonempty == 0) continue;
-        const int32_t region = (int32_t)((c0 + lane) % W);
+        const int32_t region = (int32_t)((uint32_t)(c0 + lane) % (uint32_t)W);  // (cells < 2^31)
         const unsigned long long* src = keys + (unsigned long long)region * cap + s_l;
         const uint32_t longest = __reduce_max_sync(full, n_l);
         if (longest <= 24) {
             // the usual case, a handful of records per cell: every lane copies its own cell
             uint32_t* o = out32 + (size_t)e_l * 3;
+            unsigned long long r = n_l ? src[0] : 0ull;
             for (uint32_t i = 0; i < n_l; i++, o += 3) {
-                const unsigned long long r = src[i], key = r >> kPayloadBits;
+                const unsigned long long key = r >> kPayloadBits;
+                const uint32_t pay = (uint32_t)r;
+                if (i + 1 < n_l) r = src[i + 1];  // next record in flight while this one is stored
                 o[0] = (uint32_t)(key >> pos_bits);
                 o[1] = (uint32_t)(key & pos_mask);
-                o[2] = (uint32_t)(r & 3) | ((uint32_t)((r >> 2) & 15) << 8) | ((uint32_t)((r >> 6) & 15) << 16);
+                o[2] = (pay & 3) | (((pay >> 2) & 15) << 8) | (((pay >> 6) & 15) << 16);
             }
             continue;
         }
