@@ -6,8 +6,10 @@
 A step = one full pass of the hot path (bottom-up sets, top-down assignment, mutation emission, ordering by (node,pos))
 over one synthetic SARS-CoV-2-shaped alignment of 20 000 taxa x 30 000 columns on a random binary tree (39 999 nodes),
 already resident in HBM.  With N GPUs every rank owns its own 30 000-column shard of a 20 000 x (30 000*N) alignment
-(weak scaling; columns are independent, the only exchange is an all-to-all of the sparse records that leaves every
-rank with the complete per-node mutation lists of its node range).
+(weak scaling; columns are independent: every rank runs the whole step on its shard and keeps its (node,pos)-ordered
+records with global positions -- no data-path collective; a node's complete list is the concatenation of the ranks'
+slices, panman_b200/shard.py stitch_by_node).  The variant in which an NCCL all-to-all leaves every rank with the
+complete lists of a node range ON THE DEVICE is timed after the main loop and reported as config.gathered_by_node.
 `value` counts all ranks' updates over the max-over-ranks device time; `e2e` is the same metric through the
 host-buffer C-ABI call (pmfs_run: H2D of the nibble-packed MSA and D2H of the records inside the timed region).
 """
@@ -122,6 +124,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk-nodes", type=int, default=0, help="plan tuning: nodes per chunk (0 = automatic)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (tuning sweeps)")
+    ap.add_argument("--no-exchange", action="store_true", help="N > 1: skip the extra gathered-by-node leg")
     ap.add_argument("--p-n-block", type=float, default=None, help="experiment: override the N-block rate of the synthetic MSA")
     args = ap.parse_args()
 
@@ -192,8 +195,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     if world > 1:
-        from panman_b200 import shard as _sh
-        ctx.set_shard(rank * N_COLS, world * N_COLS, [b for b, _ in _sh.node_ranges(V, world)] + [V])
+        ctx.set_shard(rank * N_COLS, world * N_COLS, None)  # a column shard that keeps its output: global positions
 
     def barrier():
         if world > 1:
@@ -202,9 +204,9 @@ def main():
 
     from panman_b200 import shard
 
-    def step():
+    def step(exchange=False):
         ptr, n = ctx.run_device(algo, d_msa.data_ptr(), stride, N_TAXA, N_COLS, d_cons.data_ptr())
-        if world > 1:  # the one exchange of the path: every rank ends up owning the complete lists of its node range
+        if exchange:  # every rank ends up owning the complete, ordered lists of its node range
             shard.exchange_parts(ctx, rank, world, dev)
         return n
 
@@ -234,6 +236,26 @@ def main():
     tinfo = ctx.timing()
     plan = ctx.plan_info()
 
+    # the same step followed by the all-to-all by node range (lists complete on the device of the owning rank)
+    gathered = None
+    if world > 1 and not args.no_exchange:
+        ctx.set_shard(rank * N_COLS, world * N_COLS, [b for b, _ in shard.node_ranges(V, world)] + [V])
+        xsteps = max(1, min(args.steps, 50))
+        for _ in range(3):
+            step(True)
+        barrier()
+        x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        x0.record()
+        for _ in range(xsteps):
+            step(True)
+        x1.record()
+        barrier()
+        xms = torch.tensor([x0.elapsed_time(x1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(xms, op=dist.ReduceOp.MAX)
+        gathered = {"ms_per_step": float(xms[0]) / xsteps, "value": updates_per_step * xsteps / (float(xms[0]) * 1e-3),
+                    "steps": xsteps, "what": "step + NCCL all-to-all of the 8-byte records by node range + owner-side ordering"}
+        ctx.set_shard(0, 0, None)
+
     # end to end: pinned host buffers through pmfs_run (H2D + passes + sort + D2H of the records), every step
     h_msa = torch.empty((N_TAXA, stride), dtype=torch.uint8, pin_memory=True)
     h_msa.copy_(d_msa)
@@ -243,7 +265,7 @@ def main():
     h_msa_np, h_cons_np = h_msa.numpy(), h_cons.numpy()
     ctx.set_stream(0)
     if world > 1:
-        ctx.set_shard(0, 0, None)  # the host-buffer leg measures the plain per-GPU call
+        ctx.set_shard(rank * N_COLS, world * N_COLS, None)
     for _ in range(max(1, min(args.warmup, 2))):
         rec = ctx.run(algo, h_msa_np, N_COLS, h_cons_np, copy=False)
     e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 10))
@@ -270,8 +292,10 @@ def main():
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32 bit-planes (16-state sets, 4-bit codes)", "data": "synthetic",
             "config": {"workload": workload, "l2": "inputs larger than L2 (MSA 300 MB + set array 1.2 GB touched per step)",
-                       "parallelism": (f"column shards x{world}; all-to-all of the sparse records by node range (NCCL), merged "
-                                       "per rank") if world > 1 else "1 GPU",
+                       "parallelism": (f"column shards x{world}, no data-path collective: every rank keeps the (node,pos)-ordered "
+                                       "records of its own columns (global positions); a node's list is the concatenation "
+                                       "over ranks") if world > 1 else "1 GPU",
+                       "gathered_by_node": gathered,
                        "records_per_step": int(n_rec), "plan": plan},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                          "traffic": ncu_traffic(args.algo), "peak_source": peak_src,

@@ -134,7 +134,11 @@ int pmfs_run_device(pmfs_ctx* ctx, int algo, const uint8_t* d_msa_nibbles, int64
  * in column-region order (always, unless ranks x column count is enormous).  The owner concatenates the blocks it
  * received IN SOURCE-RANK ORDER and orders them with pmfs_sort_records (d_records is overwritten; the result is valid
  * until the next run): with column_ordered = 1 on every source a stable sort on the node bits suffices, pass 0 to force
- * a full sort.  The result is the owner's nodes' complete (node,pos)-sorted lists. */
+ * a full sort.  The result is the owner's nodes' complete (node,pos)-sorted lists.
+ * With n_parts = 0 and total_cols > 0 the context is a column shard that keeps its output: the run orders its own
+ * records by (node,pos) as usual, positions are global (pos_offset added), and nothing needs exchanging -- a node's
+ * complete list is the concatenation of the shards' slices for that node in column order (pmfs_pack_last gives the
+ * per-node offsets).  total_cols = 0 leaves shard mode altogether. */
 int pmfs_set_shard(pmfs_ctx* ctx, int64_t pos_offset, int64_t total_cols, int32_t n_parts, const int32_t* node_bounds);
 int pmfs_get_parts(pmfs_ctx* ctx, const void** d_records, int64_t* offsets, int64_t* counts, int* column_ordered);
 int pmfs_sort_records(pmfs_ctx* ctx, void* d_records, int64_t n, int column_ordered, pmfs_mut** d_out);

@@ -240,7 +240,9 @@ class Context:
     def set_shard(self, pos_offset: int, total_cols: int, node_bounds=None):
         """Column-shard mode (pmfs_set_shard); node_bounds: [n_parts+1] node-id boundaries, None leaves shard mode."""
         if node_bounds is None:
-            _check(self._L.pmfs_set_shard(self._h, 0, 0, 0, None))
+            # total_cols > 0: a column shard that orders and keeps its own records (global positions, no exchange)
+            _check(self._L.pmfs_set_shard(self._h, pos_offset if total_cols else 0, total_cols, 0, None))
+            self._n_parts = 0
             return
         b = np.ascontiguousarray(node_bounds, dtype=np.int32)
         _check(self._L.pmfs_set_shard(self._h, pos_offset, total_cols, b.shape[0] - 1, b.ctypes.data))

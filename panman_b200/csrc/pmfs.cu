@@ -1714,8 +1714,8 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     }
     const int64_t NC = (int64_t)P->chunks.size();
     int pos_bits = 1, node_bits = 1;
-    const int64_t pos_span = c->parts.n_parts > 0 ? c->shard_total_cols : n_cols;
-    if (c->parts.n_parts > 0 && c->shard_pos_offset + n_cols > c->shard_total_cols) {
+    const int64_t pos_span = c->shard_total_cols > 0 ? c->shard_total_cols : n_cols;
+    if (c->shard_total_cols > 0 && c->shard_pos_offset + n_cols > c->shard_total_cols) {
         g_error = "pmfs_run: column shard exceeds the total column count given to pmfs_set_shard";
         return PMFS_ERR_ARG;
     }
@@ -1811,7 +1811,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             for (int r = 0; r <= c->parts.n_parts; r++) wp.owner_bound[r] = c->parts.bound[r];
             wp.err_flag = (unsigned int*)(d_stats + 2);
             wp.pos_bits = pos_bits;
-            wp.pos_offset = c->parts.n_parts > 0 ? c->shard_pos_offset : 0;
+            wp.pos_offset = c->shard_total_cols > 0 ? c->shard_pos_offset : 0;
             wp.ready = c->d_sync.ptr;
             const unsigned pg = (unsigned)((wp.G + 127) / 128);
             PMFS_CUDA(cudaEventRecord(c->ev[0], c->stream));
@@ -2003,7 +2003,8 @@ int pmfs_run_device(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
 }
 
 int pmfs_set_shard(pmfs_ctx* c, int64_t pos_offset, int64_t total_cols, int32_t n_parts, const int32_t* node_bounds) {
-    if (!c || n_parts < 0 || n_parts > 16 || pos_offset < 0 || (n_parts > 0 && (!node_bounds || total_cols <= 0))) {
+    if (!c || n_parts < 0 || n_parts > 16 || pos_offset < 0 || total_cols < 0 || (n_parts > 0 && (!node_bounds || total_cols <= 0)) ||
+        (total_cols == 0 && pos_offset != 0)) {
         g_error = "pmfs_set_shard: bad argument (at most 16 parts)";
         return PMFS_ERR_ARG;
     }

@@ -191,3 +191,27 @@ def numpy_to_records(rec: np.ndarray):
 
     a = np.ascontiguousarray(rec).view(np.uint8).reshape(-1, 12).copy().view("<i4").reshape(-1, 3)
     return torch.from_numpy(a.copy())
+
+
+def stitch_by_node(shards, n_nodes: int) -> np.ndarray:
+    """Per-node mutation lists from column shards that kept their output (pmfs_set_shard with n_parts = 0): `shards` is
+    the list, in column order, of each shard's (node,pos)-ordered record array (api.MUT_DTYPE, global positions).  A
+    node's list is the concatenation of the shards' slices for that node; the result is the array an unsharded run over
+    all columns returns.  Host-side pointer arithmetic on per-node counts -- this is all the "gather" a consumer of
+    per-node lists needs when no rank has to own complete lists on the device."""
+    counts = np.zeros((len(shards), n_nodes + 1), np.int64)
+    for s, rec in enumerate(shards):
+        counts[s, 1:] = np.bincount(rec["node"], minlength=n_nodes)[:n_nodes]
+    per_node = counts.sum(axis=0)
+    node_off = np.cumsum(per_node)                     # start of node v's list in the result: node_off[v]
+    within = np.cumsum(counts[:, 1:], axis=0) - counts[:, 1:]  # [s, v]: records of v in shards before s
+    total = int(node_off[-1])
+    out = np.zeros(total, shards[0].dtype if shards else None)
+    for s, rec in enumerate(shards):
+        if rec.shape[0] == 0:
+            continue
+        src_off = np.cumsum(counts[s]) [:-1]            # start of node v inside shard s
+        nodes = rec["node"].astype(np.int64)
+        dst = node_off[nodes] + within[s, nodes] + (np.arange(rec.shape[0]) - src_off[nodes])
+        out[dst] = rec
+    return out

@@ -94,3 +94,22 @@ def test_gather_merge_pack_world2():
     ok, straddle = [g for g in got if g[0] != "x"][0]
     assert ok
     assert straddle, "test input should contain a run of consecutive positions across the shard boundary"
+
+
+def test_stitch_by_node_matches_unsharded_oracle():
+    """shard.stitch_by_node: per-shard (node,pos)-ordered outputs with global positions -> the unsharded record array."""
+    rng = np.random.default_rng(5)
+    tree = synth.random_tree(60, rng, max_arity=3, absent_frac=0.05)
+    L = 500
+    msa = synth.simulate_msa(tree, L, rng, p_sub=0.05, p_del=0.03, p_ins=0.1, p_n=0.03, p_amb=0.02)
+    cons = synth.consensus_first_nongap(msa)
+    want = O.run_port(0, tree, msa, cons, None, threads=2)
+    for world in (1, 2, 4):
+        parts = []
+        for b, e in shard.column_shards(L, world):
+            rec = O.run_port(0, tree, np.ascontiguousarray(msa[:, b:e]), cons[b:e], None, threads=2)
+            rec = _to_mut12(rec) if rec.dtype.itemsize != 12 else rec.copy()
+            rec["pos"] += b
+            parts.append(rec)
+        got = shard.stitch_by_node(parts, tree.n_nodes)
+        assert G.same_muts(got, want), world
