@@ -66,14 +66,22 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
     // whole tree with `chunk_nodes`; every further round re-cuts only the residual top (nodes with a cut descendant)
     // with a threshold 8x smaller, until the residual is small.
     if (chunk_nodes < 2) chunk_nodes = 2;
+    // A re-cut only pays where the residual top BRANCHES (the pieces below a branching node run in parallel); along a
+    // path it would just chop a serial chain into more hand-overs -- a ladder tree stays in round-0 chunks.
     std::vector<int32_t> rem(V, 1);
-    std::vector<uint8_t> cut(V, 0), hascut(V, 0);
+    std::vector<uint8_t> cut(V, 0), hascut(V, 0), fork(V, 0);
     int64_t thr = chunk_nodes;
     for (int round = 0; round < 8; round++) {
         std::fill(rem.begin(), rem.end(), 1);
+        if (round > 0) {  // fork[v]: at least two children of v lead to cuts of earlier rounds
+            std::vector<uint8_t> n_hc(V, 0);
+            for (int32_t v = 1; v < V; v++)
+                if ((cut[v] || hascut[v]) && n_hc[t.parent[v]] < 2) n_hc[t.parent[v]]++;
+            for (int32_t v = 0; v < V; v++) fork[v] = n_hc[v] >= 2;
+        }
         bool any_new = false;
         for (int32_t v = V - 1; v >= 1; v--) {
-            const bool candidate = P.int_id[v] >= 0 && !cut[v] && (round == 0 || hascut[v]);
+            const bool candidate = P.int_id[v] >= 0 && !cut[v] && (round == 0 || (hascut[v] && fork[t.parent[v]]));
             if (candidate && rem[v] >= thr) {
                 cut[v] = 1;
                 any_new = true;
