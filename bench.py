@@ -314,7 +314,7 @@ def main():
             "phases_ms_last_step": {k: tinfo[k] for k in ("forward_ms", "backward_ms", "sort_ms", "wall_ms")},
         }
         if world == 1 and not args.no_cpu_baseline:
-            cols_n = args.cpu_cols or max(64, min(1024, 16 * ncpu))
+            cols_n = args.cpu_cols or 8192  # about 10 s (Fitch) to 30 s (Sankoff) of CPU work on 16 cores
             cols = np.sort(np.random.default_rng(0).choice(N_COLS, size=cols_n, replace=False))
             full = api.unpack_nibbles(h_msa_np, N_COLS)
             sub = np.ascontiguousarray(full[:, cols])
