@@ -1289,6 +1289,9 @@ struct pmfs_ctx {
     cudaStream_t stream = nullptr;      // stream in use
     cudaStream_t own_stream = nullptr;  // created by pmfs_create
     cudaEvent_t ev[8] = {};
+    cudaEvent_t ev_slab[2] = {};        // pmfs_run: upload slab 0 / 1 complete (recorded on copy_stream)
+    cudaStream_t copy_stream = nullptr;
+    int64_t slab_split = 0;             // > 0 while pmfs_run pipelines: first column group of the second slab
     // plan on device
     DevBuf<uint32_t> d_fwd_prog, d_bwd_prog, d_fwd_stream, d_bwd_stream;
     DevBuf<int64_t> d_fwd_off, d_bwd_off, d_fwd_soff, d_bwd_soff;
@@ -1482,6 +1485,8 @@ int pmfs_create(pmfs_ctx** out, const pmfs_tree* tree, int device) {
     }
     c->own_stream = c->stream;
     for (auto& ev : c->ev) cudaEventCreate(&ev);
+    for (auto& ev : c->ev_slab) cudaEventCreate(&ev);
+    cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
     int rc = replan(c, auto_chunk_nodes(V, 1024));
     if (rc) {
         pmfs_destroy(c);
@@ -1517,6 +1522,9 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_pk_tmp.release();
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);
+    for (auto& ev : c->ev_slab)
+        if (ev) cudaEventDestroy(ev);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
@@ -1784,9 +1792,16 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         if (use_cells) PMFS_CUDA(cudaMemsetAsync(c->d_cell_count.ptr, 0, (size_t)cells * sizeof(uint32_t), c->stream));
         fwd_ms = bwd_ms = 0;
         tm.n_launches = 0;
-        for (int64_t g0 = 0; g0 < G_all; g0 += tile_groups) {
+        // column segments: the memory tiles, cut once more where pmfs_run's second upload slab begins
+        const int64_t split = c->slab_split > 0 && c->slab_split < G_all ? c->slab_split : 0;
+        const bool multi = tile_groups < G_all || split > 0;
+        for (int64_t g0 = 0, g1; g0 < G_all; g0 = g1) {
+            g1 = std::min(g0 + tile_groups, G_all);
+            if (g0 < split && split < g1) g1 = split;
+            if (split > 0 && (g0 == 0 || g0 == split))  // the slab's bytes have arrived (copy stream of pmfs_run)
+                PMFS_CUDA(cudaStreamWaitEvent(c->stream, c->ev_slab[g0 == 0 ? 0 : 1], 0));
             WalkParams wp = {};
-            wp.G = std::min(tile_groups, G_all - g0);
+            wp.G = g1 - g0;
             wp.col_base = g0 * 32;
             wp.tile_cols = std::min<int64_t>(wp.G * 32, n_cols - wp.col_base);
             wp.msa = (const uint4*)(d_msa + g0 * 16);
@@ -1829,7 +1844,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                                     : launch_levels<kAlgoSankoff>(c, wp, false, &tm.n_launches);
             if (rc) return rc;
             PMFS_CUDA(cudaEventRecord(c->ev[2], c->stream));
-            if (tile_groups < G_all) {  // several tiles reuse the events: read them before the next tile records again
+            if (multi) {  // several segments reuse the events: read them before the next one records again
                 PMFS_CUDA(cudaEventSynchronize(c->ev[2]));
                 float a = 0, b = 0;
                 cudaEventElapsedTime(&a, c->ev[0], c->ev[1]);
@@ -1883,7 +1898,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         }
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
         const unsigned int err = (unsigned int)stats[2];
-        if (tile_groups >= G_all) {
+        if (!multi) {
             cudaEventElapsedTime(&fwd_ms, c->ev[0], c->ev[1]);
             cudaEventElapsedTime(&bwd_ms, c->ev[1], c->ev[2]);
         }
@@ -2156,24 +2171,55 @@ int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int3
     if ((rc = c->d_msa.ensure((size_t)std::max<int64_t>(1, n_rows) * dstride))) return rc;
     if ((rc = c->d_cons.ensure((size_t)n_cols))) return rc;
     if (forced && (rc = c->d_forced.ensure((size_t)n_cols))) return rc;
-    PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
     const int64_t used = (n_cols + 1) / 2;
-    if (dstride > used && row_stride != dstride) PMFS_CUDA(cudaMemsetAsync(c->d_msa.ptr, 0, (size_t)std::max<int64_t>(1, n_rows) * dstride, c->stream));
-    if (n_rows > 0 && row_stride == dstride)
-        PMFS_CUDA(cudaMemcpyAsync(c->d_msa.ptr, msa, (size_t)n_rows * dstride, cudaMemcpyHostToDevice, c->stream));
-    else if (n_rows > 0)
-        PMFS_CUDA(cudaMemcpy2DAsync(c->d_msa.ptr, (size_t)dstride, msa, (size_t)row_stride, (size_t)used, (size_t)n_rows,
-                                    cudaMemcpyHostToDevice, c->stream));
-    PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons, (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
-    if (forced) PMFS_CUDA(cudaMemcpyAsync(c->d_forced.ptr, forced, (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
-    PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));
-    PMFS_CUDA(cudaEventSynchronize(c->ev[6]));
-    cudaEventElapsedTime(&c->timing.h2d_ms, c->ev[5], c->ev[6]);
-    // an odd final column shares its byte with a padding nibble that the caller may have left non-zero: it is masked
-    // out of the emission by the real-column mask, and it cannot influence other columns.
+    // Wide alignments go up in two column slabs on a copy stream and the passes of the first slab (all column tiles but
+    // the last) run while the second is still on the bus: only the last tile's passes are left after the upload.
+    const int64_t G_all = (n_cols + 31) / 32, tiles = (G_all + kTileGroups - 1) / kTileGroups;
+    const bool slabs = n_rows > 0 && tiles >= 2 && (size_t)n_rows * (size_t)used >= ((size_t)32 << 20);
     pmfs_mut* d_out = nullptr;
-    rc = run_device_impl(c, algo, c->d_msa.ptr, dstride, n_rows, n_cols, c->d_cons.ptr, forced ? c->d_forced.ptr : nullptr,
-                         &d_out, n_out);
+    if (slabs) {
+        const int64_t split = (tiles - 1) * kTileGroups;  // column groups in slab 0
+        const size_t w0 = (size_t)split * 16, w1 = (size_t)(row_stride >= dstride ? dstride : used) - w0;
+        cudaStream_t cs = c->copy_stream;
+        PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));  // whatever the caller's stream still does with these buffers
+        PMFS_CUDA(cudaStreamWaitEvent(cs, c->ev[6], 0));
+        PMFS_CUDA(cudaEventRecord(c->ev[5], cs));
+        if (dstride > used && row_stride < dstride) PMFS_CUDA(cudaMemsetAsync(c->d_msa.ptr, 0, (size_t)n_rows * dstride, cs));
+        PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons, (size_t)n_cols, cudaMemcpyHostToDevice, cs));
+        if (forced) PMFS_CUDA(cudaMemcpyAsync(c->d_forced.ptr, forced, (size_t)n_cols, cudaMemcpyHostToDevice, cs));
+        PMFS_CUDA(cudaMemcpy2DAsync(c->d_msa.ptr, (size_t)dstride, msa, (size_t)row_stride, w0, (size_t)n_rows, cudaMemcpyHostToDevice, cs));
+        PMFS_CUDA(cudaEventRecord(c->ev_slab[0], cs));
+        PMFS_CUDA(cudaMemcpy2DAsync(c->d_msa.ptr + w0, (size_t)dstride, msa + w0, (size_t)row_stride, w1, (size_t)n_rows,
+                                    cudaMemcpyHostToDevice, cs));
+        PMFS_CUDA(cudaEventRecord(c->ev_slab[1], cs));
+        c->slab_split = split;
+        rc = run_device_impl(c, algo, c->d_msa.ptr, dstride, n_rows, n_cols, c->d_cons.ptr, forced ? c->d_forced.ptr : nullptr,
+                             &d_out, n_out);
+        c->slab_split = 0;
+        if (rc) {
+            cudaStreamSynchronize(cs);
+            return rc;
+        }
+        cudaEventElapsedTime(&c->timing.h2d_ms, c->ev[5], c->ev_slab[1]);  // (overlaps forward_ms / backward_ms)
+        c->timing.total_ms = c->timing.wall_ms;
+    } else {
+        PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
+        if (dstride > used && row_stride != dstride) PMFS_CUDA(cudaMemsetAsync(c->d_msa.ptr, 0, (size_t)std::max<int64_t>(1, n_rows) * dstride, c->stream));
+        if (n_rows > 0 && row_stride == dstride)
+            PMFS_CUDA(cudaMemcpyAsync(c->d_msa.ptr, msa, (size_t)n_rows * dstride, cudaMemcpyHostToDevice, c->stream));
+        else if (n_rows > 0)
+            PMFS_CUDA(cudaMemcpy2DAsync(c->d_msa.ptr, (size_t)dstride, msa, (size_t)row_stride, (size_t)used, (size_t)n_rows,
+                                        cudaMemcpyHostToDevice, c->stream));
+        PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons, (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
+        if (forced) PMFS_CUDA(cudaMemcpyAsync(c->d_forced.ptr, forced, (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
+        PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));
+        PMFS_CUDA(cudaEventSynchronize(c->ev[6]));
+        cudaEventElapsedTime(&c->timing.h2d_ms, c->ev[5], c->ev[6]);
+        // an odd final column shares its byte with a padding nibble that the caller may have left non-zero: it is masked
+        // out of the emission by the real-column mask, and it cannot influence other columns.
+        rc = run_device_impl(c, algo, c->d_msa.ptr, dstride, n_rows, n_cols, c->d_cons.ptr, forced ? c->d_forced.ptr : nullptr,
+                             &d_out, n_out);
+    }
     if (rc) return rc;
     // one pinned result buffer per context, grown on demand (pinning memory costs far more than the copy itself)
     if ((size_t)*n_out > c->h_out_cap || !c->h_out) {

@@ -160,3 +160,28 @@ def test_local_column_shards_stitch_to_unsharded():
                 _, n = full.run_device(api.SANKOFF, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr())
                 want_s = full.download(n)
             assert G.same_muts(shard.stitch_by_node(got, tree.n_nodes), want_s)
+
+
+def test_host_buffer_call_pipelines_two_slabs():
+    """pmfs_run on an alignment wide and big enough for the two-slab upload (>= 2 column tiles, >= 32 MB): same records
+    as the device-resident call, for a row stride equal to and larger than the device stride."""
+    N, L = 3000, 24000 + 40
+    tree = trees.random_binary_tree(N, seed=4)
+    spec = api.SynthSpec(p_sub=0.002, p_del=0.001, p_ins=0.004, p_n_block=0.004, p_amb=0.001)
+    with api.Context(tree) as ctx:
+        d_msa, d_cons, stride = synth_on_device(ctx, spec, N, 0, L)
+        _, n = ctx.run_device(api.FITCH, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr())
+        want = ctx.download(n)
+        h_msa, h_cons = d_msa.cpu().numpy(), d_cons.cpu().numpy()
+        assert h_msa.nbytes >= 32 << 20
+        for pad in (0, 48):
+            h = np.zeros((N, stride + pad), np.uint8)
+            h[:, :stride] = h_msa
+            h[:, stride:] = 0xff  # bytes beyond the row must never be looked at
+            for algo in (api.FITCH, api.SANKOFF):
+                got = ctx.run(algo, h, L, h_cons)
+                if algo == api.FITCH:
+                    assert G.same_muts(got, want) and (got["parent_code"] == want["parent_code"]).all(), pad
+                else:
+                    _, n_s = ctx.run_device(api.SANKOFF, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr())
+                    assert G.same_muts(got, ctx.download(n_s)), pad
