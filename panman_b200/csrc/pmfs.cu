@@ -713,7 +713,6 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
 // with its operands, so the walkers go from one item to the next without seeing the claim / dependency / staging
 // latencies.  Item descriptors and programs are double buffered; all hand-overs are mbarriers, the kernels contain no
 // CTA-wide barrier after set-up.
-constexpr int kPassFwd = 0, kPassBwd = 1;
 
 template <int RING>
 __device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars) {
@@ -745,7 +744,7 @@ __device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars)
 // item after item.  Everything that does not need the dependency is started before it is polled, the item record is
 // one 32-byte load, and the claim for the NEXT item is issued before this one is produced, so that per item only the
 // record load and the dependency poll remain on the producer's critical path.
-template <int PASS, int RING>
+template <int RING>
 __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r) {
     const int lane = threadIdx.x & 31;
     uint32_t n_leaf = 0, n_set = 0;
@@ -810,7 +809,7 @@ __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
     const Ring ring = ring_setup<kSetRingFwd>(smem, bars);
     if (threadIdx.x >= kTPB) {
         PMFS_WP(10);
-        producer_loop<kPassFwd, kSetRingFwd>(p, ring);
+        producer_loop<kSetRingFwd>(p, ring);
         return;
     }
     PMFS_WP(5);
@@ -848,7 +847,7 @@ __global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 3) bwd_kern
     const Ring ring = ring_setup<kSetRingBwd>(smem, bars);
     if (threadIdx.x >= kTPB) {
         PMFS_WP(10);
-        producer_loop<kPassBwd, kSetRingBwd>(p, ring);
+        producer_loop<kSetRingBwd>(p, ring);
         return;
     }
     PMFS_WP(5);
@@ -1322,7 +1321,6 @@ struct pmfs_ctx {
     DevBuf<unsigned long long> d_keys, d_keys_alt;
 
     DevBuf<unsigned long long> d_count;
-    DevBuf<unsigned int> d_err;
     DevBuf<uint8_t> d_sort_tmp, d_scan_tmp;
     DevBuf<uint32_t> d_cell_count, d_cell_start, d_cell_prefix;  // per (node, column region), see order_cells_kernel
     unsigned long long* h_stats = nullptr;  // pinned: {records, largest area, error flag} of the last run
@@ -1508,7 +1506,7 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_int_to_node.release(); c->d_row_to_node.release();
     c->d_S.release(); c->d_D.release(); c->d_cons_planes.release(); c->d_forced_planes.release();
     c->d_xcode.release(); c->d_xvalid.release(); c->d_keys.release(); c->d_keys_alt.release();
-    c->d_count.release(); c->d_err.release();
+    c->d_count.release();
     c->d_scan_tmp.release(); c->d_cell_count.release(); c->d_cell_start.release(); c->d_cell_prefix.release();
     if (c->h_stats) cudaFreeHost(c->h_stats);
     c->d_sort_tmp.release(); c->d_out.release(); c->d_msa.release(); c->d_cons.release(); c->d_forced.release();
