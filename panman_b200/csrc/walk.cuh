@@ -220,51 +220,114 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
             for (int i = 0; i < 16; i++) S[j].p[i] = A[j].p[i] | (O[j].p[i] & ~any);
         }
     } else {
-        // h[s] = number of valid children whose S contains s, as bit-sliced counters; S = argmax h, D1 = {h = max-1}
+        // h[s] = number of valid children whose S contains s, as bit-sliced counters; S = argmax h, D1 = {h = max-1}.
+        // The two low counter bits of every state live in registers (statically indexed: everything over the 16 states
+        // is unrolled); the higher bits sit in a per-thread array and are touched only when the low pair overflows --
+        // once per four increments, and then the whole warp takes the branch together on real data.  Arity <= 3 never
+        // touches the array at all.
         int nb = 1;
         while ((k >> nb) != 0) nb++;
-        uint32_t h[NG][16][kPolyBits];
+        const int nhi = nb > 2 ? nb - 2 : 0;
+        uint32_t lo0[NG][16], lo1[NG][16], hi[NG][16][kPolyBits - 2];
         uint32_t any_valid[NG];
+#pragma unroll
         for (int j = 0; j < NG; j++) {
             any_valid[j] = 0;
-            for (int s = 0; s < 16; s++)
-                for (int b = 0; b < nb; b++) h[j][s][b] = 0;
+#pragma unroll
+            for (int s_ = 0; s_ < 16; s_++) lo0[j][s_] = lo1[j][s_] = 0;
+            if (nhi > 0) {
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++)
+                    for (int b_ = 0; b_ < nhi; b_++) hi[j][s_][b_] = 0;
+            }
         }
         for (uint32_t c = 0; c < k; c++) {
             Planes16 B[NG];
             load_operand(env, env.word(prog, pc + (int32_t)c), B);
+#pragma unroll
             for (int j = 0; j < NG; j++) {
                 any_valid[j] |= or16(B[j]);
-                for (int s = 0; s < 16; s++) {
-                    uint32_t carry = B[j].p[s];
-                    for (int b = 0; b < nb && carry; b++) {
-                        const uint32_t x = h[j][s][b];
-                        h[j][s][b] = x ^ carry;
-                        carry &= x;
+                uint32_t overflow = 0;
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) {  // 16 independent chains, no control flow: the carries replace B
+                    uint32_t carry = B[j].p[s_], x = lo0[j][s_];
+                    lo0[j][s_] = x ^ carry;
+                    carry &= x;
+                    x = lo1[j][s_];
+                    lo1[j][s_] = x ^ carry;
+                    carry &= x;
+                    B[j].p[s_] = carry;
+                    overflow |= carry;
+                }
+                if (env.any(overflow != 0)) {
+#pragma unroll
+                    for (int s_ = 0; s_ < 16; s_++) {
+                        uint32_t carry = B[j].p[s_];
+                        if (env.any(carry != 0))
+                            for (int b_ = 0; b_ < nhi; b_++) {
+                                const uint32_t x = hi[j][s_][b_];
+                                hi[j][s_][b_] = x ^ carry;
+                                carry &= x;
+                            }
                     }
                 }
             }
         }
+#pragma unroll
         for (int j = 0; j < NG; j++) {
-            uint32_t cand[16], mx[kPolyBits];
-            for (int s = 0; s < 16; s++) cand[s] = ~0u;
-            for (int b = nb - 1; b >= 0; b--) {
+            // argmax over the 16 counters, most significant bit first: `cand` keeps the states that can still be maximal,
+            // mx collects the maximum's bits.  The two register-resident bits are straight-line code; the loop over the
+            // high bits does not run for arity <= 3.
+            uint32_t cand[16], mxhi[kPolyBits - 2], mx0, mx1;
+#pragma unroll
+            for (int s_ = 0; s_ < 16; s_++) cand[s_] = ~0u;
+            for (int b_ = nhi - 1; b_ >= 0; b_--) {
                 uint32_t one = 0;
-                for (int s = 0; s < 16; s++) one |= cand[s] & h[j][s][b];
-                for (int s = 0; s < 16; s++) cand[s] &= ~(one & ~h[j][s][b]);
-                mx[b] = one;
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) one |= cand[s_] & hi[j][s_][b_];
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) cand[s_] &= ~(one & ~hi[j][s_][b_]);
+                mxhi[b_] = one;
             }
-            uint32_t borrow = ~0u;  // mx - 1
-            for (int b = 0; b < nb; b++) {
-                const uint32_t x = mx[b];
-                mx[b] = x ^ borrow;
+            {
+                uint32_t one = 0;
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) one |= cand[s_] & lo1[j][s_];
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) cand[s_] &= ~(one & ~lo1[j][s_]);
+                mx1 = one;
+                one = 0;
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) one |= cand[s_] & lo0[j][s_];
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) cand[s_] &= ~(one & ~lo0[j][s_]);
+                mx0 = one;
+            }
+            // mx - 1 (borrow chain from bit 0); a borrow out of the top bit <=> max was 0 (no valid child): D1 is
+            // irrelevant there
+            uint32_t borrow = ~mx0;
+            mx0 = ~mx0;
+            {
+                const uint32_t x = mx1;
+                mx1 = x ^ borrow;
                 borrow &= ~x;
             }
-            for (int s = 0; s < 16; s++) {
-                uint32_t eq = ~borrow;  // borrow out set <=> max was 0 (no valid child): D1 is irrelevant there
-                for (int b = 0; b < nb; b++) eq &= ~(h[j][s][b] ^ mx[b]);
-                S[j].p[s] = cand[s] & any_valid[j];
-                D1[j].p[s] = eq;
+            for (int b_ = 0; b_ < nhi; b_++) {
+                const uint32_t x = mxhi[b_];
+                mxhi[b_] = x ^ borrow;
+                borrow &= ~x;
+            }
+            uint32_t eq[16];
+#pragma unroll
+            for (int s_ = 0; s_ < 16; s_++) eq[s_] = ~borrow & ~(lo0[j][s_] ^ mx0) & ~(lo1[j][s_] ^ mx1);
+            for (int b_ = 0; b_ < nhi; b_++) {
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) eq[s_] &= ~(hi[j][s_][b_] ^ mxhi[b_]);
+            }
+#pragma unroll
+            for (int s_ = 0; s_ < 16; s_++) {
+                S[j].p[s_] = cand[s_] & any_valid[j];
+                D1[j].p[s_] = eq[s_];
             }
         }
     }

@@ -115,3 +115,31 @@ def to_newick(tree: FlatTree, leaf_names=None) -> str:
         else:
             out.append(")")
     return "".join(out) + ";"
+
+
+def collapse_edges(tree: FlatTree, frac: float, seed: int = 1) -> FlatTree:
+    """Polytomies out of a binary tree: a fraction `frac` of the internal non-root nodes is contracted into its parent
+    (its children become children of the nearest surviving ancestor, in place).  Mutation-annotated trees of outbreak
+    data look like this: most branches have no mutation and are collapsed, some nodes have hundreds of children."""
+    rng = np.random.default_rng(seed)
+    V = tree.n_nodes
+    internal = tree.leaf_row == -1
+    drop = internal & (rng.random(V) < frac)
+    drop[0] = False
+    keep = ~drop
+    new_id = np.cumsum(keep) - 1  # pre-order is preserved by contraction
+    anc = np.arange(V)            # nearest surviving ancestor-or-self, resolved top-down (parents have smaller ids)
+    par = tree.parent
+    for v in range(1, V):
+        if drop[v]:
+            anc[v] = anc[par[v]]
+    kept = np.nonzero(keep)[0]
+    parent = np.full(kept.shape[0], -1, np.int32)
+    parent[1:] = new_id[anc[par[kept[1:]]]]
+    leaf_row = tree.leaf_row[kept].astype(np.int32)
+    n = kept.shape[0]
+    child_off = np.zeros(n + 1, np.int32)
+    np.add.at(child_off, parent[1:] + 1, 1)
+    child_off = np.cumsum(child_off).astype(np.int32)
+    child_idx = (np.argsort(parent[1:], kind="stable") + 1).astype(np.int32)  # pre-order = Newick order inside a parent
+    return FlatTree(parent, child_off, child_idx, leaf_row)

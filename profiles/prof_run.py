@@ -1,5 +1,5 @@
 """Minimal driver for ncu captures: BASELINE config 2, `--steps` device-resident passes, nothing else.
-usage: python profiles/prof_run.py [fitch|sankoff] [steps] [taxa] [columns]"""
+usage: python profiles/prof_run.py [fitch|sankoff] [steps] [taxa] [columns] [fraction of internal edges collapsed]"""
 import os
 import sys
 
@@ -13,6 +13,8 @@ steps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 N = int(sys.argv[3]) if len(sys.argv) > 3 else 20000
 L = int(sys.argv[4]) if len(sys.argv) > 4 else 30000
 tree = trees.random_binary_tree(N)
+if len(sys.argv) > 5 and float(sys.argv[5]) > 0:
+    tree = trees.collapse_edges(tree, float(sys.argv[5]))  # polytomies
 ctx = api.Context(tree)
 stride = ((L + 31) // 32) * 16
 d_msa = torch.zeros((N, stride), dtype=torch.uint8, device="cuda")
