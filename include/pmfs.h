@@ -118,6 +118,25 @@ int pmfs_run_chars(pmfs_ctx* ctx, int algo, const char* msa_chars, int64_t row_s
                    int64_t n_cols, const char* consensus_chars, const char* root_forced_chars, pmfs_mut** out,
                    int64_t* n_out);
 
+/* Same call on unpacked STATE CODES, one byte per cell (low 4 bits used): for the callers of the path that do not come
+ * from alignment characters.  The reference's block-level passes are this call on three states:
+ * blockFitchForwardPassNew / BackwardPassNew / AssignMutationsNew (src/fitchSankoff.cpp:224-308, driven per block at
+ * src/panman.cpp:865-904 and src/reroot.cpp:80-82) with PMFS_FITCH, blockSankoffForwardPass / BackwardPass /
+ * AssignMutations (:707-818, driven at src/panman.cpp:906-949) with PMFS_SANKOFF, on codes 0 = block absent,
+ * 1 = forward strand, 2 = reverse strand, one column per block, consensus_code = all zeros (the root's parent state is
+ * "absent"), root_forced_code = the reference sequence's states (defaultState) or NULL.  Records translate with
+ * pmfs_block_type / pmfs_block_inverted below.  One difference to mind: the block Sankoff pass gives a leaf without a
+ * sequence the state "absent" (src/fitchSankoff.cpp:711-714), so such leaves need an all-zero row rather than
+ * leaf_row = -2; block Fitch treats them like the nucleotide pass (empty set).  tests/test_oracle.py pins this against
+ * the reference's own block members. */
+int pmfs_run_codes(pmfs_ctx* ctx, int algo, const uint8_t* codes, int64_t row_stride_bytes, int32_t n_rows,
+                   int64_t n_cols, const uint8_t* consensus_code, const uint8_t* root_forced_code, pmfs_mut** out,
+                   int64_t* n_out);
+/* BlockMutationType of a record computed on block states (src/panman.hpp:43-52): 1 = BI (insertion), 0 = BD
+ * (deletion, or inversion when pmfs_block_inverted is set) -- the pair blockFitchAssignMutationsNew stores. */
+static inline int pmfs_block_type(const pmfs_mut* m) { return m->type == 2 /* PMFS_NI */ ? 1 : 0; }
+static inline int pmfs_block_inverted(const pmfs_mut* m) { return m->type == 2 ? m->code == 2 : m->type == 0 /* PMFS_NS */; }
+
 /* Device-resident variant (what `value` in bench.py times): every pointer is a DEVICE pointer on the context's
  * device; msa row stride must be a multiple of 16 bytes and the base 16-byte aligned.  Records stay on the device,
  * sorted by (node,pos); *d_out is owned by the context and valid until the next run. */

@@ -148,6 +148,34 @@ def run_ref_columns(algo: int, tree: FlatTree, msa_chars: np.ndarray, consensus_
     return _take(lib.pmref_free, out, n.value, MUT_DTYPE)
 
 
+def run_ref_blocks(algo: int, tree: FlatTree, states: np.ndarray, forced=None):
+    """The reference's block-level members (blockFitch*New / blockSankoff*) driven per block as the PanGraph branch does
+    (oracle/ref_driver.cpp: pmref_block_columns).  states: [rows, blocks] uint8, 0 absent / 1 forward / 2 reverse;
+    forced: [blocks] uint8 or None.  Records: node, pos = block, type = BlockMutationType (BI 1, BD 0), code = inverted."""
+    lib = ref_lib()
+    st = np.ascontiguousarray(states, dtype=np.uint8)
+    frc = None if forced is None else np.ascontiguousarray(forced, dtype=np.uint8)
+    par, coff, cidx, lrow = _i32(tree.parent), _i32(tree.child_off), _i32(tree.child_idx), _i32(tree.leaf_row)
+    out = C.c_void_p()
+    n = C.c_int64()
+    rc = lib.pmref_block_columns(
+        C.c_int(algo), C.c_int32(tree.n_nodes), _ptr(par, C.c_int32), _ptr(coff, C.c_int32), _ptr(cidx, C.c_int32),
+        _ptr(lrow, C.c_int32), C.c_int32(st.shape[0]), C.c_int64(st.shape[1]), _ptr(st, C.c_uint8),
+        None if frc is None else _ptr(frc, C.c_uint8), C.byref(out), C.byref(n))
+    if rc != 0:
+        raise RuntimeError(f"pmref_block_columns rc={rc}")
+    return _take(lib.pmref_free, out, n.value, MUT_DTYPE)
+
+
+def blocks_from_nuc(rec: np.ndarray) -> np.ndarray:
+    """Block view of nucleotide-pass records computed on state codes 0/1/2 (include/pmfs.h: pmfs_block_type /
+    pmfs_block_inverted): NI -> (BI, code == 2), ND -> (BD, false), NS -> (BD, true)."""
+    out = rec.copy()
+    out["type"] = np.where(rec["type"] == 2, 1, 0)
+    out["code"] = np.where(rec["type"] == 2, rec["code"] == 2, rec["type"] == 0)
+    return out
+
+
 def ref_build(msa_path: str, nwk_path: str, reference: str = "", low_mem: bool = False, threads: int = 1) -> dict:
     """Whole `panmanUtils -M .. -N ..` construction path up to serialisation (oracle/ref_driver.cpp: pmref_build)."""
     lib = ref_lib()

@@ -472,6 +472,72 @@ int pmref_columns(int algo, int32_t n_nodes, const int32_t* parent, const int32_
     return 0;
 }
 
+// Block-level passes (the per-block loop of the PanGraph branch, src/panman.cpp:865-950, restated; its callers build
+// `alignedSequences` from a GFA / PanGraph, which is out of scope): one "column" per block, one state per sequence --
+// 0 block absent, 1 forward strand, 2 reverse strand.  algo 0 = blockFitch*New (:898-904; a leaf without a row has the
+// empty set), algo 1 = blockSankoff* (:943-949; a leaf without a row gets the blank state {0,INF,INF}).  forced: the
+// reference sequence's states per block (defaultState) or nullptr.  Same tree/row naming as pmref_columns.
+// Output records: node, pos = block, type = BlockMutationType (BI = 1, BD = 0), code = the inversion flag.
+int pmref_block_columns(int algo, int32_t n_nodes, const int32_t* parent, const int32_t* child_off, const int32_t* child_idx,
+                        const int32_t* leaf_row, int32_t n_rows, int64_t n_blocks, const uint8_t* states_in,
+                        const uint8_t* forced, pmref_mut** out, int64_t* n_out) {
+    NodeGraph g;
+    g.nodes.resize(n_nodes);
+    int internal = 0;
+    for (int i = 0; i < n_nodes; i++) {
+        Node* n = new Node();
+        bool isLeaf = child_off[i + 1] == child_off[i];
+        if (!isLeaf) n->identifier = "node_" + std::to_string(++internal);
+        else if (leaf_row[i] >= 0) n->identifier = "r" + std::to_string(leaf_row[i]);
+        else n->identifier = "absent_" + std::to_string(i);
+        g.nodes[i] = n;
+        g.index[n->identifier] = i;
+    }
+    for (int i = 0; i < n_nodes; i++) {
+        Node* n = g.nodes[i];
+        n->parent = parent[i] >= 0 ? g.nodes[parent[i]] : nullptr;
+        for (int e = child_off[i]; e < child_off[i + 1]; e++) n->children.push_back(g.nodes[child_idx[e]]);
+    }
+    Tree tree;
+    tree.root = g.nodes[0];
+    std::vector<RefMut> muts;
+    for (int64_t b = 0; b < n_blocks; b++) {
+        std::unordered_map<std::string, std::pair<panmanUtils::BlockMutationType, bool>> mutations;
+        if (algo == 0) {
+            std::unordered_map<std::string, int> states;
+            for (int r = 0; r < n_rows; r++) states["r" + std::to_string(r)] = 1 << states_in[(size_t)r * n_blocks + b];  // :888-896
+            tree.blockFitchForwardPassNew(tree.root, states);
+            if (forced) tree.blockFitchBackwardPassNew(tree.root, states, 1, 1 << forced[b]);  // :899-903
+            else tree.blockFitchBackwardPassNew(tree.root, states, 1);
+            tree.blockFitchAssignMutationsNew(tree.root, states, mutations, 1);
+        } else {
+            std::unordered_map<std::string, std::vector<int>> stateSets;
+            std::unordered_map<std::string, int> states;
+            for (int r = 0; r < n_rows; r++) {  // :931-941
+                std::vector<int> cur(3, SANKOFF_INF);
+                cur[states_in[(size_t)r * n_blocks + b]] = 0;
+                stateSets["r" + std::to_string(r)] = cur;
+            }
+            tree.blockSankoffForwardPass(tree.root, stateSets);
+            if (forced) tree.blockSankoffBackwardPass(tree.root, stateSets, states, 0, forced[b]);  // :944-948
+            else tree.blockSankoffBackwardPass(tree.root, stateSets, states, 0);
+            tree.blockSankoffAssignMutations(tree.root, states, mutations, 0);
+        }
+        for (const auto& m : mutations) {
+            RefMut r = {};
+            r.node = g.index.at(m.first);
+            r.pos = (int32_t)b;
+            r.type = (uint8_t)m.second.first;
+            r.code = m.second.second ? 1 : 0;
+            muts.push_back(r);
+        }
+    }
+    std::sort(muts.begin(), muts.end(), [](const RefMut& a, const RefMut& b) { return a.node != b.node ? a.node < b.node : a.pos < b.pos; });
+    *out = dupArray(muts);
+    *n_out = (int64_t)muts.size();
+    return 0;
+}
+
 // Whole construction path from files, as `panmanUtils -M msa -N nwk [--reference id] [--low-mem-mode]` runs it up to
 // (not including) serialisation.  Outputs (malloc'd; release with pmref_free):
 //   tree in pre-order (parent, child CSR, names as one '\n'-joined string), consensus characters,

@@ -72,7 +72,7 @@ class SynthSpec:
 
 _lib = None
 
-EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars",
+EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_codes",
            "pmfs_result_free", "pmfs_run_device", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
@@ -96,6 +96,7 @@ def lib():
         L.pmfs_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
         L.pmfs_run_chars.argtypes = L.pmfs_run.argtypes
+        L.pmfs_run_codes.argtypes = L.pmfs_run.argtypes
         L.pmfs_result_free.argtypes = [C.c_void_p, C.c_void_p]
         L.pmfs_result_free.restype = None
         L.pmfs_run_device.argtypes = L.pmfs_run.argtypes
@@ -203,7 +204,12 @@ class Context:
             self._L.pmfs_result_free(self._h, out)
         return res
 
-    def run_chars(self, algo: int, msa_chars: np.ndarray, consensus_chars: np.ndarray, forced_chars=None) -> np.ndarray:
+    def run_codes(self, algo: int, codes: np.ndarray, consensus_codes: np.ndarray, forced_codes=None) -> np.ndarray:
+        """pmfs_run_codes: [rows, cols] uint8 state codes (one byte per cell) in, host records out."""
+        return self.run_chars(algo, codes, consensus_codes, forced_codes, _entry="pmfs_run_codes")
+
+    def run_chars(self, algo: int, msa_chars: np.ndarray, consensus_chars: np.ndarray, forced_chars=None,
+                  _entry: str = "pmfs_run_chars") -> np.ndarray:
         """pmfs_run_chars: [rows, cols] uint8 alignment CHARACTERS in, host records out (conversion on the device)."""
         msa = np.ascontiguousarray(msa_chars, dtype=np.uint8)
         cons = np.ascontiguousarray(consensus_chars, dtype=np.uint8)
@@ -211,7 +217,7 @@ class Context:
         n_cols = int(cons.shape[0])
         out, n = C.c_void_p(), C.c_int64()
         stride = msa.shape[1] if msa.ndim == 2 and msa.shape[0] else n_cols
-        _check(self._L.pmfs_run_chars(self._h, algo, msa.ctypes.data, stride, msa.shape[0], n_cols, cons.ctypes.data,
+        _check(getattr(self._L, _entry)(self._h, algo, msa.ctypes.data, stride, msa.shape[0], n_cols, cons.ctypes.data,
                                       None if frc is None else frc.ctypes.data, C.byref(out), C.byref(n)))
         if not n.value:
             return np.zeros(0, MUT_DTYPE)

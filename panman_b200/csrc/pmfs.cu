@@ -983,6 +983,7 @@ __device__ __forceinline__ uint32_t code_of_char(uint32_t ch) {
     }
 }
 // one thread = 8 columns of one row: 8 characters in, one 32-bit word of nibbles out (column 2j in the low nibble of byte j)
+template <bool RAW>  // RAW: the bytes are state codes already (low 4 bits), not alignment characters
 __global__ void pack_chars_kernel(const uint8_t* __restrict__ chars, int64_t in_stride, int32_t n_rows, int64_t n_cols,
                                   uint8_t* __restrict__ out, int64_t out_stride) {
     const int64_t words = out_stride / 4;
@@ -992,7 +993,7 @@ __global__ void pack_chars_kernel(const uint8_t* __restrict__ chars, int64_t in_
     const uint8_t* src = chars + row * in_stride + w * 8;
     uint32_t v = 0;
     for (int k = 0; k < 8; k++)
-        if (w * 8 + k < n_cols) v |= code_of_char(src[k]) << (4 * k);
+        if (w * 8 + k < n_cols) v |= (RAW ? (uint32_t)src[k] & 15u : code_of_char(src[k])) << (4 * k);
     *(uint32_t*)(out + row * out_stride + w * 4) = v;
 }
 
@@ -2250,10 +2251,24 @@ static uint8_t host_code_of_char(char ch) {  // src/panman.cpp:83-118
     }
 }
 
+static int run_bytes(pmfs_ctx* c, int algo, bool raw, const char* msa_chars, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                     const char* consensus_chars, const char* forced_chars, pmfs_mut** out, int64_t* n_out);
+
 int pmfs_run_chars(pmfs_ctx* c, int algo, const char* msa_chars, int64_t row_stride, int32_t n_rows, int64_t n_cols,
                    const char* consensus_chars, const char* forced_chars, pmfs_mut** out, int64_t* n_out) {
+    return run_bytes(c, algo, false, msa_chars, row_stride, n_rows, n_cols, consensus_chars, forced_chars, out, n_out);
+}
+
+int pmfs_run_codes(pmfs_ctx* c, int algo, const uint8_t* codes, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                   const uint8_t* consensus_codes, const uint8_t* forced_codes, pmfs_mut** out, int64_t* n_out) {
+    return run_bytes(c, algo, true, (const char*)codes, row_stride, n_rows, n_cols, (const char*)consensus_codes,
+                     (const char*)forced_codes, out, n_out);
+}
+
+static int run_bytes(pmfs_ctx* c, int algo, bool raw, const char* msa_chars, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                     const char* consensus_chars, const char* forced_chars, pmfs_mut** out, int64_t* n_out) {
     if (!c || !msa_chars || !consensus_chars || !out || !n_out || n_cols <= 0 || n_rows < 0 || row_stride < n_cols) {
-        g_error = "pmfs_run_chars: bad argument";
+        g_error = "pmfs_run_chars / pmfs_run_codes: bad argument";
         return PMFS_ERR_ARG;
     }
     PMFS_CUDA(cudaSetDevice(c->device));
@@ -2265,14 +2280,15 @@ int pmfs_run_chars(pmfs_ctx* c, int algo, const char* msa_chars, int64_t row_str
     if ((rc = c->d_cons.ensure((size_t)n_cols))) return rc;
     if (forced_chars && (rc = c->d_forced.ensure((size_t)n_cols))) return rc;
     std::vector<uint8_t> cons((size_t)n_cols), forced(forced_chars ? (size_t)n_cols : 0);
-    for (int64_t i = 0; i < n_cols; i++) cons[i] = host_code_of_char(consensus_chars[i]);
-    for (size_t i = 0; i < forced.size(); i++) forced[i] = host_code_of_char(forced_chars[i]);
+    for (int64_t i = 0; i < n_cols; i++) cons[i] = raw ? (uint8_t)consensus_chars[i] & 15 : host_code_of_char(consensus_chars[i]);
+    for (size_t i = 0; i < forced.size(); i++) forced[i] = raw ? (uint8_t)forced_chars[i] & 15 : host_code_of_char(forced_chars[i]);
     PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
     if (n_rows > 0) {
         PMFS_CUDA(cudaMemcpy2DAsync(c->d_chars.ptr, (size_t)cstride, msa_chars, (size_t)row_stride, (size_t)n_cols, (size_t)n_rows,
                                     cudaMemcpyHostToDevice, c->stream));
         const int64_t total = (dstride / 4) * n_rows;
-        pack_chars_kernel<<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(c->d_chars.ptr, cstride, n_rows, n_cols, c->d_msa.ptr, dstride);
+        if (raw) pack_chars_kernel<true><<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(c->d_chars.ptr, cstride, n_rows, n_cols, c->d_msa.ptr, dstride);
+        else pack_chars_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(c->d_chars.ptr, cstride, n_rows, n_cols, c->d_msa.ptr, dstride);
         PMFS_CUDA(cudaGetLastError());
     }
     PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons.data(), (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));

@@ -183,3 +183,33 @@ def test_radix_ordering_path_in_subprocess():
                         "golden_small_cases or random_trees or deep_ladder or device_side_packing"],
                        env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_block_level_passes_through_run_codes():
+    """the reference's block-level Fitch / Sankoff (3 states, one column per block) through pmfs_run_codes,
+    against the reference's own blockFitch*New / blockSankoff* members.  Leaves without a sequence: empty set for Fitch
+    (leaf_row = -2), an all-zero row for Sankoff (the block pass gives them the state "absent")."""
+    rng = np.random.default_rng(41)
+    for trial in range(10):
+        arity = 2 if trial < 4 else int(rng.integers(2, 7))
+        tree = synth.random_tree(int(rng.integers(2, 300)), rng, max_arity=arity, absent_frac=0.1 if trial % 3 == 0 else 0.0)
+        rows, B = synth.n_rows(tree), int(rng.integers(1, 900))
+        anc = rng.integers(0, 3, B)
+        states = np.where(rng.random((rows, B)) < 0.8, anc[None, :], rng.integers(0, 3, (rows, B))).astype(np.uint8)
+        forced = states[int(rng.integers(0, rows))] if trial % 2 else None
+        cons = np.zeros(B, np.uint8)
+        # Fitch: absent leaves stay absent
+        want = O.run_ref_blocks(0, tree, states, forced)
+        with api.Context(tree) as ctx:
+            got = O.blocks_from_nuc(ctx.run_codes(api.FITCH, states, cons, forced))
+        assert G.same_muts(got, want), (trial, "fitch")
+        # Sankoff: absent leaves read an extra all-zero row
+        lr = tree.leaf_row.copy()
+        n_abs = int((lr == -2).sum())
+        lr[lr == -2] = rows + np.arange(n_abs)  # (one row each: the library refuses two leaves on one row)
+        t2 = type(tree)(tree.parent, tree.child_off, tree.child_idx, lr)
+        st2 = np.vstack([states, np.zeros((n_abs, B), np.uint8)])
+        want = O.run_ref_blocks(1, tree, states, forced)
+        with api.Context(t2) as ctx:
+            got = O.blocks_from_nuc(ctx.run_codes(api.SANKOFF, st2, cons, forced))
+        assert G.same_muts(got, want), (trial, "sankoff")

@@ -81,3 +81,30 @@ def test_sankoff_unforced_invalid_root_is_an_error():
         O.run_port(1, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), None)
     # Fitch: no records at all (every node has an empty set and is skipped)
     assert O.run_port(0, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), None).shape[0] == 0
+
+
+def test_block_passes_are_the_nucleotide_passes_on_three_states():
+    """the reference's block-level passes (blockFitch*New, blockSankoff*; 3 states) give exactly what its
+    nucleotide passes -- hence the library -- give on the state codes 0/1/2 with an all-absent parent of the root, after
+    relabelling the mutation types.  Checked against the reference's own block members."""
+    rng = np.random.default_rng(31)
+    for trial in range(12):
+        arity = 2 if trial < 6 else int(rng.integers(2, 6))
+        tree = synth.random_tree(int(rng.integers(2, 90)), rng, max_arity=arity, absent_frac=0.1 if trial % 3 == 0 else 0.0)
+        rows, B = synth.n_rows(tree), int(rng.integers(1, 120))
+        anc = rng.integers(0, 3, B)
+        states = np.where(rng.random((rows, B)) < 0.7, anc[None, :], rng.integers(0, 3, (rows, B))).astype(np.uint8)
+        forced = states[int(rng.integers(0, rows))] if trial % 2 else None
+        cons = np.zeros(B, np.uint8)  # parentState of the root: block absent
+        for algo in (0, 1):
+            want = O.run_ref_blocks(algo, tree, states, forced)
+            t2, st2 = tree, states
+            if algo == 1 and (tree.leaf_row == -2).any():
+                # the block Sankoff pass gives a leaf without a sequence the state "absent": an all-zero row
+                lr = tree.leaf_row.copy()
+                n_abs = int((lr == -2).sum())
+                lr[lr == -2] = rows + np.arange(n_abs)
+                t2 = type(tree)(tree.parent, tree.child_off, tree.child_idx, lr)
+                st2 = np.vstack([states, np.zeros((n_abs, B), np.uint8)])
+            got = O.blocks_from_nuc(O.run_port(algo, t2, st2, cons, forced, threads=1))
+            assert G.same_muts(got, want), (trial, algo)
