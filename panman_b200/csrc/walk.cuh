@@ -221,14 +221,15 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
         }
     } else {
         // h[s] = number of valid children whose S contains s, as bit-sliced counters; S = argmax h, D1 = {h = max-1}.
-        // The two low counter bits of every state live in registers (statically indexed: everything over the 16 states
-        // is unrolled); the higher bits sit in a per-thread array and are touched only when the low pair overflows --
-        // once per four increments, and then the whole warp takes the branch together on real data.  Arity <= 3 never
-        // touches the array at all.
+        // Children are counted three at a time into a 2-bit counter per state that lives in registers (statically
+        // indexed: everything over the 16 states is unrolled, 16 independent chains, no control flow) -- three
+        // increments cannot overflow it.  Arity <= 3 needs nothing else.  For larger arities the register counters are
+        // added into full-width counters in a per-thread array after every third child (only the states some column of
+        // the warp has seen; the carry ripples two bits on average), and read back from there at the end.
         int nb = 1;
         while ((k >> nb) != 0) nb++;
         const int nhi = nb > 2 ? nb - 2 : 0;
-        uint32_t lo0[NG][16], lo1[NG][16], hi[NG][16][kPolyBits - 2];
+        uint32_t lo0[NG][16], lo1[NG][16], full[NG][16][kPolyBits];
         uint32_t any_valid[NG];
 #pragma unroll
         for (int j = 0; j < NG; j++) {
@@ -238,40 +239,55 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
             if (nhi > 0) {
 #pragma unroll
                 for (int s_ = 0; s_ < 16; s_++)
-                    for (int b_ = 0; b_ < nhi; b_++) hi[j][s_][b_] = 0;
+                    for (int b_ = 0; b_ < nb; b_++) full[j][s_][b_] = 0;
             }
         }
+        uint32_t pending = 0;  // children counted in lo0/lo1 since the last flush
         for (uint32_t c = 0; c < k; c++) {
             Planes16 B[NG];
             load_operand(env, env.word(prog, pc + (int32_t)c), B);
 #pragma unroll
             for (int j = 0; j < NG; j++) {
                 any_valid[j] |= or16(B[j]);
-                uint32_t overflow = 0;
 #pragma unroll
-                for (int s_ = 0; s_ < 16; s_++) {  // 16 independent chains, no control flow: the carries replace B
-                    uint32_t carry = B[j].p[s_], x = lo0[j][s_];
-                    lo0[j][s_] = x ^ carry;
-                    carry &= x;
-                    x = lo1[j][s_];
-                    lo1[j][s_] = x ^ carry;
-                    carry &= x;
-                    B[j].p[s_] = carry;
-                    overflow |= carry;
-                }
-                if (env.any(overflow != 0)) {
-#pragma unroll
-                    for (int s_ = 0; s_ < 16; s_++) {
-                        uint32_t carry = B[j].p[s_];
-                        if (env.any(carry != 0))
-                            for (int b_ = 0; b_ < nhi; b_++) {
-                                const uint32_t x = hi[j][s_][b_];
-                                hi[j][s_][b_] = x ^ carry;
-                                carry &= x;
-                            }
-                    }
+                for (int s_ = 0; s_ < 16; s_++) {
+                    const uint32_t x = lo0[j][s_], carry = B[j].p[s_] & x;
+                    lo0[j][s_] = x ^ B[j].p[s_];
+                    lo1[j][s_] ^= carry;
                 }
             }
+            pending++;
+            if (nhi > 0 && (pending == 3 || c + 1 == k)) {
+                pending = 0;
+#pragma unroll
+                for (int j = 0; j < NG; j++)
+#pragma unroll
+                    for (int s_ = 0; s_ < 16; s_++) {
+                        const uint32_t a0 = lo0[j][s_], a1 = lo1[j][s_];
+                        if (!env.any((a0 | a1) != 0)) continue;
+                        uint32_t x = full[j][s_][0];
+                        full[j][s_][0] = x ^ a0;
+                        uint32_t carry = x & a0;
+                        x = full[j][s_][1];
+                        full[j][s_][1] = x ^ a1 ^ carry;
+                        carry = (x & a1) | (carry & (x ^ a1));
+                        for (int b_ = 2; b_ < nb && env.any(carry != 0); b_++) {
+                            x = full[j][s_][b_];
+                            full[j][s_][b_] = x ^ carry;
+                            carry &= x;
+                        }
+                        lo0[j][s_] = lo1[j][s_] = 0;
+                    }
+            }
+        }
+        if (nhi > 0) {  // the two low bits back into registers: the code below reads (lo0, lo1, full[2..])
+#pragma unroll
+            for (int j = 0; j < NG; j++)
+#pragma unroll
+                for (int s_ = 0; s_ < 16; s_++) {
+                    lo0[j][s_] = full[j][s_][0];
+                    lo1[j][s_] = full[j][s_][1];
+                }
         }
 #pragma unroll
         for (int j = 0; j < NG; j++) {
@@ -284,9 +300,9 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
             for (int b_ = nhi - 1; b_ >= 0; b_--) {
                 uint32_t one = 0;
 #pragma unroll
-                for (int s_ = 0; s_ < 16; s_++) one |= cand[s_] & hi[j][s_][b_];
+                for (int s_ = 0; s_ < 16; s_++) one |= cand[s_] & full[j][s_][b_ + 2];
 #pragma unroll
-                for (int s_ = 0; s_ < 16; s_++) cand[s_] &= ~(one & ~hi[j][s_][b_]);
+                for (int s_ = 0; s_ < 16; s_++) cand[s_] &= ~(one & ~full[j][s_][b_ + 2]);
                 mxhi[b_] = one;
             }
             {
@@ -322,7 +338,7 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
             for (int s_ = 0; s_ < 16; s_++) eq[s_] = ~borrow & ~(lo0[j][s_] ^ mx0) & ~(lo1[j][s_] ^ mx1);
             for (int b_ = 0; b_ < nhi; b_++) {
 #pragma unroll
-                for (int s_ = 0; s_ < 16; s_++) eq[s_] &= ~(hi[j][s_][b_] ^ mxhi[b_]);
+                for (int s_ = 0; s_ < 16; s_++) eq[s_] &= ~(full[j][s_][b_ + 2] ^ mxhi[b_]);
             }
 #pragma unroll
             for (int s_ = 0; s_ < 16; s_++) {
