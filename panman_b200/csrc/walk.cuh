@@ -150,7 +150,7 @@ constexpr int kPolyBits = 28;  // counter width of the any-arity Sankoff join: a
 // hand-over, addressing) is paid once per NG groups, and the NG independent dependency chains interleave in the
 // pipeline.  On the B200 this code is bound by integer-ALU issue, so instructions per column are what counts.
 //
-// Env concept (device: pmfs.cu; host emulation: tests/host_emul.cpp), NG = Env::kGroups
+// Env concept (device: walk_kernels.cuh DevEnv; host emulation: tests/host_emul.cpp), NG = Env::kGroups
 //   uint32_t word(const uint32_t* prog, int32_t pc)            program word, same for every thread
 //   void     leaf(uint32_t row, uint4 (&w)[NG])                this thread's 32 nibbles per group of MSA row `row`
 //   void     load_x(uint32_t id, Planes16 (&s)[NG])            set S[id] written by an earlier work item (prefetched)

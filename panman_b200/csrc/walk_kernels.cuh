@@ -1,0 +1,853 @@
+// libpmfs device code, part 1: the two walk kernels and everything they are made of -- work-item scheduling, the producer
+// warp with its TMA rings, the per-thread view of an item (DevEnv) that walk.cuh's interpreter runs on, emission.
+// Included by pmfs.cu only (after its constants, WalkParams comes first here).
+#pragma once
+
+namespace pmfs {
+
+// ------------------------------------------------------------------------------------------------ device environment
+struct WalkParams {
+    const uint32_t* prog;       // fwd or bwd program words
+    const int64_t* chunk_off;   // [NC] offset of each chunk's program
+    const int32_t* chunk_len;   // [NC]
+    const int32_t* order;       // chunk ids in execution order of this pass
+    const int4* items;          // [2*NC] per chunk IN EXECUTION ORDER: {chunk, parent, plen, slen}, {prog_off/4, stream_off, need, dep chunk}
+    const int32_t* chunk_parent;  // [NC] parent chunk, -1 for the chunk that holds the tree root
+    const int32_t* chunk_nchild;  // [NC] number of child chunks
+    int* ready;                 // [NC][ctas_per_chunk] dependency counters of this pass (zeroed before the launch)
+    int* next_item;             // work-item claim counter of this pass (zeroed before the launch)
+    int32_t n_items;
+    const uint32_t* stream;     // load streams (plan.hpp)
+    const int64_t* stream_off;  // [NC]
+    const int32_t* stream_len;  // [NC]
+    int32_t ctas_per_chunk;
+    int32_t stack_depth;
+    int32_t claim_lead;         // stream entries before the end of an item at which the producer claims the next one
+    const uint4* msa;           // first group of this column tile
+    int64_t msa_stride16;       // uint4 per MSA row
+    uint4* S;                   // [I][4][G]
+    uint4* D;                   // Sankoff only
+    int64_t G;                  // column groups in this tile
+    int64_t tile_cols;          // real columns in this tile
+    int64_t col_base;           // global column of the tile's first column
+    const uint4* cons_planes;   // [G]
+    const uint4* forced_planes; // [G] or null
+    uint4* xcode;               // [NC][G] parent state per chunk root
+    uint32_t* xvalid;           // [NC][G]
+    const int32_t* int_to_node;
+    const int32_t* row_to_node;
+    unsigned long long* out_keys;   // [n_owners][out_cap] packed records (see kPayloadBits)
+    unsigned long long* out_count;  // [n_owners]
+    unsigned long long out_cap;     // capacity of one owner's region
+    int32_t n_regions;              // > 0: one output region per 32 column groups (see emit); 0: regions per owner
+    uint32_t bucket_mask;           // single-GPU runs: regions are further split by (node & bucket_mask), bucket-major
+    uint32_t* cell_count;           // [n_nodes][n_regions] or null: records of (node, region) -- see order_cells_kernel
+    uint32_t* cell_start;           // [n_nodes][n_regions]: where they start inside the region
+    int64_t region_base;            // region index of this column tile's first 32 groups
+    int32_t n_owners;               // 1, or the number of ranks in column-shard mode
+    int32_t owner_bound[17];        // nodes [owner_bound[r], owner_bound[r+1]) are owned by rank r
+    unsigned int* err_flag;
+    int64_t pos_offset;         // global column of this context's first column (column shards); 0 otherwise
+    int pos_bits;               // record = ((node << pos_bits | column) << kPayloadBits) | payload
+};
+
+// 64-word sliding window over a word array that every lane of the warp reads at the same, never decreasing index
+// (load streams): lane l holds words base+l and base+32+l in two registers, a read is one shuffle, and the next 32
+// words are fetched (one coalesced load per warp) a whole window before they are needed.
+struct WarpWords {
+    const uint32_t* base;
+    int32_t len, wbase;
+    uint32_t cur, nxt;
+    __device__ __forceinline__ void init(const uint32_t* b, int32_t n, int lane) {
+        base = b; len = n; wbase = 0;
+        cur = lane < n ? __ldg(b + lane) : 0u;
+        nxt = 32 + lane < n ? __ldg(b + 32 + lane) : 0u;
+    }
+    __device__ __forceinline__ uint32_t get(int32_t i, int lane) {
+        while (i >= wbase + 32) {
+            cur = nxt;
+            wbase += 32;
+            const int32_t j = wbase + 32 + lane;
+            nxt = j < len ? __ldg(base + j) : 0u;
+        }
+        return __shfl_sync(0xffffffffu, cur, i - wbase);
+    }
+};
+
+constexpr int kNG = 2;                    // column groups per walking thread (walk.cuh: Env::kGroups)
+constexpr int kTileGroups = kTPB * kNG;   // column groups per work item (256 groups = 8 192 columns)
+constexpr int kThreads = kTPB + 32;       // 4 walking warps + 1 producer warp
+// Operand rings of a CTA, per pass: leaf-row units in flight (4 KB each: 16 B for each group of the tile) and set slots in
+// flight (16 KB each: 64 B for each group).  One int encodes both (leaf * 16 + sets) so that it can be a template argument.
+// Bottom-up: mostly leaves, and its 32 KB walk stack + 128 registers cap it at 3 CTAs per SM anyway.  Top-down: every
+// internal node is one set; 2 + 2 keeps a CTA under 57 KB, which lets 4 CTAs share an SM (measured: 0.41 -> 0.36 ms).
+#ifndef PMFS_RING_FWD
+#define PMFS_RING_FWD (4 * 16 + 1)
+#define PMFS_RING_BWD (2 * 16 + 2)
+#endif
+constexpr int kSetRingFwd = PMFS_RING_FWD;
+constexpr int kSetRingBwd = PMFS_RING_BWD;
+constexpr int kProgWords = 256;           // walk programs up to this many words are staged in shared memory
+constexpr int kUnitBytes = kTileGroups * 16;
+constexpr int kSetBytes = kTileGroups * 64;
+
+// ---- mbarrier / bulk-copy (TMA) primitives, sm_90+ PTX ------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ bool mbar_test(uint32_t bar, uint32_t parity) {  // never suspends
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// slow path: let the hardware park the thread (suspend-time hint) instead of burning issue slots the producer needs
+__device__ __forceinline__ bool mbar_try_park(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(20000u)
+        : "memory");
+    return ok != 0;
+}
+// A wait that can never be satisfied (a bug in the producer/consumer bookkeeping) must not hang the GPU: after about
+// ten seconds of spinning the kernel traps and the host sees a CUDA error.
+constexpr long long kSpinLimitCycles = 20000000000ll;  // ~10 s
+__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
+    const long long t0 = clock64();
+    for (uint32_t it = 1; !mbar_try_park(bar, parity); it++)
+        if ((it & 255u) == 0 && clock64() - t0 > kSpinLimitCycles) __trap();
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity);
+}
+// -DPMFS_WAITPROF (never in the shipped library): cycles spent per wait kind, summed over warps, printed per launch
+#ifdef PMFS_WAITPROF
+__device__ unsigned long long g_waitprof[16];
+__device__ __forceinline__ long long wp_now() { return clock64(); }
+__device__ __forceinline__ void wp_add(int k, long long t0) {
+    if ((threadIdx.x & 31) == 0) atomicAdd(&g_waitprof[k], (unsigned long long)(clock64() - t0));
+}
+struct WaitProf {
+    long long t0;
+    int k;
+    __device__ __forceinline__ explicit WaitProf(int kind) : t0(wp_now()), k(kind) {}
+    __device__ __forceinline__ ~WaitProf() { wp_add(k, t0); }
+};
+#ifdef PMFS_TRACE_ONLY
+#define PMFS_WP(kind)
+#else
+#define PMFS_WP(kind) WaitProf wp_##kind(kind)
+#endif
+// per-item timeline: {start ns, end ns, chunk, tile | smid << 16}
+constexpr int kTraceCap = 1 << 17;
+__device__ ulonglong4 g_trace[kTraceCap];
+__device__ unsigned int g_trace_n;
+__device__ __forceinline__ unsigned long long trace_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void trace_item(unsigned long long t0, int chunk, int tile) {
+    if (threadIdx.x != 0) return;
+    unsigned int smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    const unsigned int i = atomicAdd(&g_trace_n, 1u);
+    if (i < kTraceCap) g_trace[i] = make_ulonglong4(t0, trace_now(), (unsigned long long)chunk, (unsigned long long)tile | ((unsigned long long)smid << 16));
+}
+#define PMFS_TRACE_BEGIN const unsigned long long trace_t0 = trace_now();
+#define PMFS_TRACE_END(chunk, tile) trace_item(trace_t0, chunk, tile);
+#else
+#define PMFS_TRACE_BEGIN
+#define PMFS_TRACE_END(chunk, tile)
+#define PMFS_WP(kind)
+#endif
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// one contiguous global->shared copy by the TMA engine; completion is counted in bytes on `bar`
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
+// Shared-memory layout of one CTA (addresses in the shared window).  Two operand rings, both filled by the producer
+// warp with TMA bulk copies and drained by the 4 walking warps: LEAF units (one 4 KB segment of an MSA row: 16 bytes
+// for each of the tile's 256 column groups) and SET slots (one 16 KB block of the tile-major set array: the 4
+// quarter-sets of all 256 groups, a single contiguous copy).  Per ring entry: `full` flips when its bytes have
+// landed, `empty` when all 4 walking warps have read it.  Entry numbers keep counting across the work items of a
+// persistent CTA, so phases never need resetting.
+template <int RING>
+struct SmemMap {
+    static constexpr int kLeafRing = RING >> 4, SETS = RING & 15;
+    static constexpr int kProg = 0;                                 // 2 staged programs
+    static constexpr int kDesc = 2 * kProgWords * 4;                // 2 item descriptors (16 B each, 64 B reserved)
+    static constexpr int kLeaf = kDesc + 64;                        // leaf ring
+    static constexpr int kSet = kLeaf + kLeafRing * kUnitBytes;     // set ring
+    static constexpr int kStack = kSet + SETS * kSetBytes;          // walk stack (dynamic size)
+    // barriers (static shared array), 8 bytes each
+    static constexpr int bLeafFull = 0, bLeafEmpty = kLeafRing, bSetFull = 2 * kLeafRing, bSetEmpty = 2 * kLeafRing + SETS,
+                         bProg = 2 * kLeafRing + 2 * SETS, bDescFull = bProg + 2, bDescEmpty = bProg + 4, kBars = bProg + 6;
+};
+struct Ring {
+    uint32_t smem;  // shared address of the dynamic shared memory
+    uint32_t bars;  // shared address of the barrier array
+};
+
+// What the producer tells the walkers about a work item (one int4 in shared memory).
+struct ItemDesc {
+    int32_t chunk;   // -1: no more items
+    int32_t tile;
+    int32_t plen;    // program length in words
+    int32_t parent;  // parent chunk (-1 for the chunk with the tree root)
+};
+
+// Lane 0 of the producer warp: the work item AFTER the one whose operands are being streamed.  Its header work (free
+// descriptor slot -> program copy -> dependencies met -> descriptor posted) is attempted, without blocking, between
+// the ring entries of the current item and only finished with blocking waits once the current stream is done, so the
+// walkers normally find the next descriptor and program already there.
+struct NextItem {
+    int4 a, b;        // packed item records: {chunk, parent, plen, slen}, {prog_off/4, stream_off, need, dep chunk}
+    int32_t tile;
+    uint32_t ordinal; // how many items this CTA has taken before it (selects descriptor slot and barrier phase)
+    bool valid;       // false: no more items, the descriptor only tells the walkers to stop
+    bool slot_free, dep_ok, posted, claimed, fetched;
+    int32_t item;     // claimed index into the pass's item order
+    int32_t t_claim, t_fetch;  // stream entries left when the claim / the record fetch are issued
+    __device__ __forceinline__ void begin(uint32_t ord, int32_t slen, int32_t lead) {
+        ordinal = ord;
+        valid = slot_free = dep_ok = posted = claimed = fetched = false;
+        t_claim = min(lead, slen - 1);
+        t_fetch = max(t_claim - 2, -1);
+    }
+    __device__ __forceinline__ void claim(const WalkParams& p) {
+        item = atomicAdd(p.next_item, 1);
+        claimed = true;
+    }
+    __device__ __forceinline__ void fetch(const WalkParams& p) {
+        if (!claimed) claim(p);
+        valid = item < p.n_items;
+        tile = 0;
+        a = make_int4(-1, -1, 0, 0);
+        b = make_int4(0, 0, 0, 0);
+        if (valid) {
+            const int pos = item / p.ctas_per_chunk;
+            tile = item % p.ctas_per_chunk;
+            a = __ldg(p.items + 2 * pos);
+            b = __ldg(p.items + 2 * pos + 1);
+        }
+        fetched = true;
+    }
+};
+template <int RING>
+__device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, NextItem& h, bool block) {
+    using M = SmemMap<RING>;
+    const uint32_t slot = h.ordinal & 1u, phase = (h.ordinal >> 1) & 1u;
+    if (!h.slot_free) {  // the walkers are done with the item two before this one
+        const uint32_t bar = r.bars + (M::bDescEmpty + slot) * 8;
+        if (block) {
+            PMFS_WP(7);
+            mbar_wait(bar, phase ^ 1u);
+        } else if (!mbar_test(bar, phase ^ 1u)) {
+            return;
+        }
+        h.slot_free = true;
+        if (h.valid && h.a.z <= kProgWords) {
+            // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
+            const uint32_t bytes = (uint32_t)((h.a.z + 3) / 4) * 16u;
+            mbar_arrive_expect_tx(r.bars + (M::bProg + slot) * 8, bytes);
+            bulk_g2s(r.smem + M::kProg + slot * (kProgWords * 4), p.prog + (int64_t)h.b.x * 4, bytes, r.bars + (M::bProg + slot) * 8);
+        }
+    }
+    if (h.valid && !h.dep_ok) {
+        // dependencies: all child chunks (bottom-up) / the parent chunk (top-down), same column tile
+        const volatile int* f = p.ready + (int64_t)h.b.w * p.ctas_per_chunk + h.tile;
+        if (*f < h.b.z) {
+            if (!block) return;
+            PMFS_WP(6);
+            const long long t0 = clock64();
+            while (*f < h.b.z) {
+                __nanosleep(32);
+                if (clock64() - t0 > kSpinLimitCycles) __trap();
+            }
+        }
+        __threadfence();
+        asm volatile("fence.proxy.async;" ::: "memory");  // data written by other CTAs is read by the TMA engine
+        h.dep_ok = true;
+    }
+    asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.smem + M::kDesc + slot * 16), "r"(h.valid ? h.a.x : -1), "r"(h.tile),
+                 "r"(h.a.z), "r"(h.a.y)
+                 : "memory");
+    mbar_arrive(r.bars + (M::bDescFull + slot) * 8);
+    h.posted = true;
+}
+
+// Producer side of one item: walk the chunk's load stream and keep both rings full.  Called by the whole producer warp
+// (the stream words are read warp-wide); lane 0 drives TMA and, in passing, the header of the next item.
+template <int RING>
+__device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& r, WarpWords& w, int32_t slen, int tile,
+                                               uint32_t& n_leaf, uint32_t& n_set, NextItem& h) {
+    using M = SmemMap<RING>;
+    const int lane = threadIdx.x & 31;
+    const int64_t g0 = (int64_t)tile * kTileGroups;
+    const uint32_t leaf_bytes = (uint32_t)min((int64_t)kTileGroups, p.G - g0) * 16u;
+    for (int32_t j = 0; j < slen; j++) {
+        const uint32_t e = w.get(j, lane);
+        if (e & kStreamSet) {
+            if (lane == 0) {
+                const uint32_t u = n_set % M::SETS, par = (n_set / M::SETS) & 1u;
+                PMFS_WP(9);
+                mbar_wait(r.bars + (M::bSetEmpty + u) * 8, par ^ 1u);  // all walkers are done with the slot's previous set
+                // one node's set for this tile: 4 quarters of `tile_w` groups, contiguous (leaf_bytes = tile_w * 16)
+                mbar_arrive_expect_tx(r.bars + (M::bSetFull + u) * 8, 4 * leaf_bytes);
+                bulk_g2s(r.smem + M::kSet + u * kSetBytes, p.S + (int64_t)(e & ~kStreamSet) * (4 * p.G) + g0 * 4, 4 * leaf_bytes,
+                         r.bars + (M::bSetFull + u) * 8);
+            }
+            n_set++;
+        } else {
+            if (lane == 0) {
+                const uint32_t u = n_leaf % M::kLeafRing, par = (n_leaf / M::kLeafRing) & 1u;
+                PMFS_WP(8);
+                mbar_wait(r.bars + (M::bLeafEmpty + u) * 8, par ^ 1u);
+                mbar_arrive_expect_tx(r.bars + (M::bLeafFull + u) * 8, leaf_bytes);
+                bulk_g2s(r.smem + M::kLeaf + u * kUnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
+                         r.bars + (M::bLeafFull + u) * 8);
+            }
+            n_leaf++;
+        }
+        if (lane == 0) {
+            // the next item: claimed `claim_lead` entries before the end of this stream (late, so that an item that
+            // is ready is not held by a busy CTA while others idle), its records fetched two entries later, then its
+            // header attempted every other entry
+            const int32_t left = slen - 1 - j;
+            if (left == h.t_claim) h.claim(p);
+            else if (left == h.t_fetch) h.fetch(p);
+            else if (left < h.t_fetch && !h.posted && (left & 1) == 0) header_step<RING>(p, r, h, false);
+        }
+    }
+}
+
+// Per-thread view of one work item for the 4 walking warps: thread t walks column groups tile*256 + t and
+// tile*256 + 128 + t.  Operands whose addresses are known from the plan (leaf rows, sets written by earlier work
+// items) never go through the walking threads: the producer warp streams them through the shared-memory rings with TMA
+// bulk copies, so a walk reads its operands from shared memory and only waits on an mbarrier that has normally
+// completed long before.  The walk program itself is staged in shared memory the same way.
+// Set arrays are TILE-MAJOR: S[internal id][tile][quarter][groups of the tile] (uint4; 256 groups per tile, fewer in
+// the last one), so one node's set for one tile is a single contiguous block of up to 16 KB (one TMA copy) and a
+// warp's 128-bit stores are 512-byte segments.  A node's row is exactly 4*G uint4: no padding.
+template <bool READONLY_SETS, int RING>
+struct DevEnv {
+    static constexpr int kGroups = kNG;
+    using M = SmemMap<RING>;
+    const WalkParams& p;
+    const Ring& ring;
+    int64_t g[kNG];      // clamped column groups
+    bool active[kNG];
+    int64_t gwarp;       // (unclamped) column group of this warp's lane 0, first group slot
+    int64_t set_tile;    // uint4 offset of this tile inside one node's set row: tile * 1024
+    int32_t tile_w;      // column groups of this tile (256, less for the last tile): stride between the 4 quarters
+    uint32_t& n_leaf;    // running ring entry numbers of this CTA (same sequences as the producer's)
+    uint32_t& n_set;
+    uint4* fstk;         // [depth][kNG][4][kTPB]
+    uint32_t* bstk;      // [depth][kNG][5][kTPB]
+    int sp = 0;
+    int lane;
+    bool prog_staged;
+    const uint32_t* gprog;
+    uint32_t sprog;      // shared address of this item's staged program
+    uint32_t ltmask;     // bits of a group word whose column is smaller than the column of bit `lane`
+    mutable unsigned long long blk_base[kNG];  // lane 0, cell mode: the warp's current output block per group slot
+    mutable uint32_t blk_used[kNG], blk_size[kNG];
+
+    __device__ DevEnv(const WalkParams& p_, const Ring& r, const ItemDesc& d, uint32_t slot, uint32_t prog_parity,
+                      uint32_t& n_leaf_, uint32_t& n_set_, void* smem_generic)
+        : p(p_), ring(r), gwarp((int64_t)d.tile * kTileGroups + (threadIdx.x & ~31)), set_tile((int64_t)d.tile * (kSetBytes / 16)),
+          tile_w((int32_t)min((int64_t)kTileGroups, p_.G - (int64_t)d.tile * kTileGroups)),
+          n_leaf(n_leaf_), n_set(n_set_), fstk((uint4*)((char*)smem_generic + M::kStack)),
+          bstk((uint32_t*)((char*)smem_generic + M::kStack)), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords),
+          gprog(nullptr), sprog(r.smem + M::kProg + slot * (kProgWords * 4)) {
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            const int64_t gj = (int64_t)d.tile * kTileGroups + j * kTPB + threadIdx.x;
+            active[j] = gj < p_.G;
+            g[j] = active[j] ? gj : p_.G - 1;
+        }
+        // bit q is column 8*(q&3) + (q>>2): smaller residues q&3 come first as a whole, then smaller q>>2 of this lane's own
+        ltmask = 0x11111111u * ((1u << (lane & 3)) - 1u) | ((0x11111111u << (lane & 3)) & ((1u << (4 * (lane >> 2))) - 1u));
+        PMFS_WP(1);
+        if (prog_staged) mbar_wait(r.bars + (M::bProg + slot) * 8, prog_parity);
+        else gprog = p_.prog + p_.chunk_off[d.chunk];
+    }
+
+    __device__ __forceinline__ uint32_t word(const uint32_t*, int32_t pc) const {
+        if (prog_staged) {
+            uint32_t w;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(sprog + pc * 4));
+            return w;
+        }
+        return __ldg(gprog + pc);  // very long programs (huge polytomies): straight from L1/L2
+    }
+
+    // next leaf unit: wait until the TMA copy has landed, read this thread's 16 bytes per group, hand the unit back
+    __device__ __forceinline__ void leaf(uint32_t, uint4 (&w)[kNG]) {
+        const uint32_t u = n_leaf % M::kLeafRing, par = (n_leaf / M::kLeafRing) & 1u;
+        PMFS_WP(2);
+        mbar_wait(ring.bars + (M::bLeafFull + u) * 8, par);
+        const uint32_t base = ring.smem + M::kLeaf + u * kUnitBytes + threadIdx.x * 16;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) w[j] = lds128(base + j * (kTPB * 16));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(ring.bars + (M::bLeafEmpty + u) * 8);
+        n_leaf++;
+    }
+    // next set slot (a set written by an earlier work item): 4 quarters x kNG groups
+    __device__ __forceinline__ void load_x(uint32_t, Planes16 (&s)[kNG]) {
+        const uint32_t u = n_set % M::SETS, par = (n_set / M::SETS) & 1u;
+        PMFS_WP(3);
+        mbar_wait(ring.bars + (M::bSetFull + u) * 8, par);
+        const uint32_t base = ring.smem + M::kSet + u * kSetBytes + threadIdx.x * 16;
+#pragma unroll
+        for (int j = 0; j < kNG; j++)
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint4 v = lds128(base + (i * tile_w + j * kTPB) * 16);
+                s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
+            }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(ring.bars + (M::bSetEmpty + u) * 8);
+        n_set++;
+    }
+
+    // direct access to the set arrays (sets of this work item itself; Sankoff D1 on the slow path)
+    __device__ __forceinline__ int64_t set_index(uint32_t id, int j, int i) const {
+        return (int64_t)id * (4 * p.G) + set_tile + i * tile_w + j * kTPB + threadIdx.x;
+    }
+    __device__ __forceinline__ void load_arr(const uint4* base, uint32_t id, Planes16 (&s)[kNG]) const {
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            if (!active[j]) {  // padding lane of the last tile: its slot lies outside this tile's block
+                zero16(s[j]);
+                continue;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint4* q = base + set_index(id, j, i);
+                const uint4 v = READONLY_SETS ? __ldg(q) : *q;
+                s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
+            }
+        }
+    }
+    __device__ __forceinline__ void store_arr(uint4* base, uint32_t id, const Planes16 (&s)[kNG]) const {
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            if (!active[j]) continue;
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                base[set_index(id, j, i)] = make_uint4(s[j].p[4 * i], s[j].p[4 * i + 1], s[j].p[4 * i + 2], s[j].p[4 * i + 3]);
+        }
+    }
+    __device__ __forceinline__ void load_s(uint32_t id, Planes16 (&s)[kNG]) const { load_arr(p.S, id, s); }
+    __device__ __forceinline__ void load_d(uint32_t id, Planes16 (&s)[kNG]) const { load_arr(p.D, id, s); }
+    __device__ __forceinline__ void store_s(uint32_t id, const Planes16 (&s)[kNG]) const { store_arr(p.S, id, s); }
+    __device__ __forceinline__ void store_d(uint32_t id, const Planes16 (&s)[kNG]) const { store_arr(p.D, id, s); }
+
+    __device__ __forceinline__ void push(const Planes16 (&s)[kNG]) {
+        uint4* q = fstk + (sp * kNG * 4) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int j = 0; j < kNG; j++)
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                q[(j * 4 + i) * kTPB] = make_uint4(s[j].p[4 * i], s[j].p[4 * i + 1], s[j].p[4 * i + 2], s[j].p[4 * i + 3]);
+        sp++;
+    }
+    __device__ __forceinline__ void pop(Planes16 (&s)[kNG]) {
+        sp--;
+        const uint4* q = fstk + (sp * kNG * 4) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int j = 0; j < kNG; j++)
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint4 v = q[(j * 4 + i) * kTPB];
+                s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
+            }
+    }
+    __device__ __forceinline__ void pushp(const Code4 (&c)[kNG], const uint32_t (&pv)[kNG]) {
+        uint32_t* q = bstk + (sp * kNG * 5) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) q[(j * 5 + i) * kTPB] = c[j].b[i];
+            q[(j * 5 + 4) * kTPB] = pv[j];
+        }
+        sp++;
+    }
+    __device__ __forceinline__ void popp(Code4 (&c)[kNG], uint32_t (&pv)[kNG]) {
+        sp--;
+        const uint32_t* q = bstk + (sp * kNG * 5) * kTPB + threadIdx.x;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) c[j].b[i] = q[(j * 5 + i) * kTPB];
+            pv[j] = q[(j * 5 + 4) * kTPB];
+        }
+    }
+    __device__ __forceinline__ void store_x(uint32_t chunk, const Code4 (&c)[kNG], const uint32_t (&pv)[kNG]) const {
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            if (!active[j]) continue;
+            p.xcode[(int64_t)chunk * p.G + g[j]] = make_uint4(c[j].b[0], c[j].b[1], c[j].b[2], c[j].b[3]);
+            p.xvalid[(int64_t)chunk * p.G + g[j]] = pv[j];
+        }
+    }
+    __device__ __forceinline__ bool any(bool x) const { return __any_sync(0xffffffffu, x); }
+
+    // Stream compaction of one node's mutations, warp-cooperative.  Called by all 32 lanes (the caller branches on a
+    // warp vote).  One REDUX gives the warp's record count, ONE atomic reserves the slots; then, for every lane that has
+    // mutations, its mask and planes are broadcast and each lane of the warp writes the record of "its" bit -- a block of
+    // 32 N's costs the same ~40 instructions as a single substitution, and the stores are coalesced.  The order inside
+    // the buffer depends on scheduling; the final radix sort by (node,pos) makes the result deterministic.
+    __device__ void emit1(uint32_t node, unsigned long long* out, unsigned long long& base, uint32_t m, const Code4& G,
+                          const Code4& P, int64_t gw) const {
+        const unsigned full = 0xffffffffu;
+        uint32_t srcs = __ballot_sync(full, m != 0);
+        const unsigned long long pos0 = (unsigned long long)(p.pos_offset + p.col_base + gw * 32 + column_of_bit(lane));
+        while (srcs) {
+            const int src = __ffs(srcs) - 1;
+            srcs &= srcs - 1;
+            const uint32_t mm = __shfl_sync(full, m, src);
+            uint32_t cg = 0, cp = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                cg |= ((__shfl_sync(full, G.b[i], src) >> lane) & 1u) << i;
+                cp |= ((__shfl_sync(full, P.b[i], src) >> lane) & 1u) << i;
+            }
+            if ((mm >> lane) & 1u) {
+                const unsigned long long idx = base + __popc(mm & ltmask);  // rank in COLUMN order
+                if (idx < p.out_cap) {
+                    // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
+                    const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
+                    const unsigned long long key = ((unsigned long long)node << p.pos_bits) | (pos0 + (unsigned long long)src * 32);
+                    out[idx] = (key << kPayloadBits) | type | (cg << 2) | (cp << 6);
+                }
+            }
+            base += __popc(mm);
+        }
+    }
+    // Two output layouts.  Regions per 32 column groups (single-GPU runs): the records of one (node, region) pair come
+    // from exactly one call, are written contiguously in column order, and regions are laid out in column order -- so a
+    // STABLE sort on the node bits alone yields the (node,pos) order.  The regions are further split by the LOW node bits
+    // (bucket-major layout): that is the first pass of an LSD radix sort done for free while emitting, and the stable
+    // sort only has to cover the remaining high node bits (one radix pass for up to 2^16 nodes instead of four on the
+    // whole key).  Regions per owning rank (column shards): see pmfs_set_shard.
+    //
+    // Cell mode (single-GPU runs, see order_cells_kernel): the ordering kernel is told where every (node, region) cell
+    // starts, so a region need not be dense.  Each warp therefore reserves space in BLOCKS of kEmitBlock records -- one
+    // atomic per work item and column-group slot, issued when the item starts and not waited for until the first node
+    // that has mutations -- and hands out the block to its nodes from a register.  The round trip of a per-node atomic
+    // was the longest latency on the top-down path, which is what the chain of chunks below the root is made of.
+    static constexpr uint32_t kEmitBlock = 256;
+    __device__ __forceinline__ void reserve_blocks() const {
+        if (lane != 0) return;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            blk_used[j] = blk_size[j] = 0;
+            if (gwarp + j * kTPB < p.G) {
+                blk_base[j] = atomicAdd(p.out_count + p.region_base + ((gwarp + j * kTPB) >> 5), (unsigned long long)kEmitBlock);
+                blk_size[j] = kEmitBlock;
+            }
+        }
+    }
+    __device__ void emit_cells(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+#pragma unroll
+        for (int j = 0; j < kNG; j++) {
+            if (!__any_sync(0xffffffffu, m[j] != 0)) continue;
+            const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
+            const int64_t region = p.region_base + ((gwarp + j * kTPB) >> 5);
+            unsigned long long base = 0;
+            if (lane == 0) {
+                if (total > blk_size[j] - blk_used[j]) {  // block used up (or a node with more records than a block holds)
+                    blk_size[j] = total > kEmitBlock ? total : kEmitBlock;
+                    blk_base[j] = atomicAdd(p.out_count + region, (unsigned long long)blk_size[j]);
+                    blk_used[j] = 0;
+                }
+                base = blk_base[j] + blk_used[j];
+                blk_used[j] += total;
+                const int64_t cell = (int64_t)node * p.n_regions + region;  // (a cell is emitted at most once per run)
+                p.cell_count[cell] = total;
+                p.cell_start[cell] = (uint32_t)base;
+            }
+            base = __shfl_sync(0xffffffffu, base, 0);
+            emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * kTPB);
+        }
+    }
+    __device__ void emit(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+        if (p.cell_count) {
+            emit_cells(node, m, G, P);
+            return;
+        }
+        if (p.n_regions > 0) {
+            int64_t own_base = 0;  // column shards: regions are owner-major (owner of this node's list, uniform in the warp)
+#pragma unroll 1  // (unrolled 16-fold this loop was a fifth of the kernel's code)
+            for (int r = 1; r < p.n_owners; r++) own_base += (int32_t)node >= p.owner_bound[r] ? p.n_regions : 0;
+#pragma unroll
+            for (int j = 0; j < kNG; j++) {
+                if (!__any_sync(0xffffffffu, m[j] != 0)) continue;
+                const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
+                const int64_t region = own_base + (int64_t)(node & p.bucket_mask) * p.n_regions + p.region_base + ((gwarp + j * kTPB) >> 5);
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(p.out_count + region, (unsigned long long)total);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * kTPB);
+            }
+            return;
+        }
+        uint32_t cnt = 0;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) cnt += __popc(m[j]);
+        const uint32_t total = __reduce_add_sync(0xffffffffu, cnt);
+        int own = 0;  // owner of this node's list (column shards); uniform across the warp
+#pragma unroll 1
+        for (int r = 1; r < p.n_owners; r++) own += (int32_t)node >= p.owner_bound[r];
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(p.out_count + own, (unsigned long long)total);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        unsigned long long* out = p.out_keys + (unsigned long long)own * p.out_cap;
+#pragma unroll
+        for (int j = 0; j < kNG; j++) emit1(node, out, base, m[j], G[j], P[j], gwarp + j * kTPB);
+    }
+    __device__ __forceinline__ void emit_internal(uint32_t id, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+        emit((uint32_t)__ldg(p.int_to_node + id), m, G, P);
+    }
+    __device__ __forceinline__ void emit_leaf(uint32_t row, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+        emit((uint32_t)__ldg(p.row_to_node + row), m, G, P);
+    }
+};
+
+__device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_cols) {
+    int64_t n = tile_cols - g * 32;
+    if (n >= 32) return ~0u;
+    uint32_t m = 0;
+#pragma unroll 1  // once per work item and only in the last column group: keep it out of the instruction cache
+    for (int q = 0; q < 32; q++)
+        if (column_of_bit(q) < n) m |= 1u << q;
+    return m;
+}
+
+// Work item = (chunk, column tile of 256 groups).  One launch per pass: persistent CTAs claim items from a global
+// counter in plan order (bottom-up: chunk height ascending; top-down: chunk depth ascending), so everything an item
+// depends on has a smaller index and was claimed earlier by a CTA that is already running -- waiting on it cannot
+// deadlock, whatever the number of resident CTAs.  Dependencies are per column tile (tile t of a chunk needs only tile
+// t of its child chunks / its parent chunk), tracked by one counter per (chunk, tile); there is no grid-wide barrier
+// and no per-level launch, so narrow levels near the root overlap with wide ones instead of leaving the GPU idle.
+//
+// Inside a CTA the producer warp runs AHEAD of the four walking warps, across item boundaries: while they finish item
+// n it has already claimed item n+1, waited for its dependencies, staged its program and started filling the rings
+// with its operands, so the walkers go from one item to the next without seeing the claim / dependency / staging
+// latencies.  Item descriptors and programs are double buffered; all hand-overs are mbarriers, the kernels contain no
+// CTA-wide barrier after set-up.
+
+template <int RING>
+__device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars) {
+    using M = SmemMap<RING>;
+    Ring r;
+    r.smem = (uint32_t)__cvta_generic_to_shared(smem);
+    r.bars = (uint32_t)__cvta_generic_to_shared(bars);
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < M::kLeafRing; i++) {
+            mbar_init(r.bars + (M::bLeafFull + i) * 8, 1);           // one arrive.expect_tx by the producer
+            mbar_init(r.bars + (M::bLeafEmpty + i) * 8, kTPB / 32);  // one arrive per walking warp
+        }
+        for (int i = 0; i < M::SETS; i++) {
+            mbar_init(r.bars + (M::bSetFull + i) * 8, 1);
+            mbar_init(r.bars + (M::bSetEmpty + i) * 8, kTPB / 32);
+        }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(r.bars + (M::bProg + i) * 8, 1);
+            mbar_init(r.bars + (M::bDescFull + i) * 8, 1);
+            mbar_init(r.bars + (M::bDescEmpty + i) * 8, kTPB / 32);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    return r;
+}
+
+// Producer warp: claim -> item record -> (program copy, stream window) -> dependency -> descriptor -> operand stream,
+// item after item.  Everything that does not need the dependency is started before it is polled, the item record is
+// one 32-byte load, and the claim for the NEXT item is issued before this one is produced, so that per item only the
+// record load and the dependency poll remain on the producer's critical path.
+template <int RING>
+__device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r) {
+    const int lane = threadIdx.x & 31;
+    uint32_t n_leaf = 0, n_set = 0;
+    NextItem h = {};
+    if (lane == 0) {
+        h.begin(0, 1, 0);
+        h.fetch(p);
+        header_step<RING>(p, r, h, true);
+    }
+    for (uint32_t n = 0;; n++) {
+        // item n: descriptor posted; broadcast what the stream needs
+        const int32_t chunk = __shfl_sync(0xffffffffu, h.valid ? h.a.x : -1, 0);
+        if (chunk < 0) return;
+        const int32_t tile = __shfl_sync(0xffffffffu, h.tile, 0);
+        const int32_t slen = __shfl_sync(0xffffffffu, h.a.w, 0);
+        const int32_t stream_off = __shfl_sync(0xffffffffu, h.b.y, 0);
+        WarpWords w;
+        w.init(p.stream + stream_off, slen, lane);
+        if (lane == 0) h.begin(n + 1, slen, p.claim_lead);
+        produce_stream<RING>(p, r, w, slen, tile, n_leaf, n_set, h);
+        if (lane == 0 && !h.posted) {
+            if (!h.fetched) h.fetch(p);
+            header_step<RING>(p, r, h, true);
+        }
+    }
+}
+
+// Walking warps: take the next descriptor; returns false when there is no more work.
+template <int RING>
+__device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d) {
+    using M = SmemMap<RING>;
+    const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
+    {
+        PMFS_WP(0);
+        mbar_wait(r.bars + (M::bDescFull + slot) * 8, phase);
+    }
+    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(d.chunk), "=r"(d.tile), "=r"(d.plen), "=r"(d.parent)
+                 : "r"(r.smem + M::kDesc + slot * 16)
+                 : "memory");
+    return d.chunk >= 0;
+}
+// Item finished: publish it to dependants (all walkers' stores first), then free the descriptor/program slot.
+__device__ __forceinline__ void finish_item(int* counter, uint32_t desc_empty_bar) {
+    {
+        PMFS_WP(4);
+        asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // the four walking warps only
+    }
+    if (threadIdx.x == 0 && counter) {
+        __threadfence();
+        atomicAdd(counter, 1);
+    }
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(desc_empty_bar);
+}
+
+template <int ALGO, bool POLY>
+__global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
+    using M = SmemMap<kSetRingFwd>;
+    extern __shared__ uint4 smem[];
+    __shared__ __align__(8) unsigned long long bars[M::kBars];
+    const Ring ring = ring_setup<kSetRingFwd>(smem, bars);
+    if (threadIdx.x >= kTPB) {
+        PMFS_WP(10);
+        producer_loop<kSetRingFwd>(p, ring);
+        return;
+    }
+    PMFS_WP(5);
+    uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
+    ItemDesc d;
+    for (uint32_t n = 0; next_item<kSetRingFwd>(ring, n, d); n++) {
+        const uint32_t slot = n & 1u;
+        PMFS_TRACE_BEGIN
+        {
+            DevEnv<false, kSetRingFwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            Code4 forced[kNG];
+            const Code4* fp = nullptr;
+            if (ALGO == kAlgoFitch && p.forced_planes) {
+#pragma unroll
+                for (int j = 0; j < kNG; j++) {
+                    const uint4 v = __ldg(p.forced_planes + env.g[j]);
+                    forced[j].b[0] = v.x; forced[j].b[1] = v.y; forced[j].b[2] = v.z; forced[j].b[3] = v.w;
+                }
+                fp = forced;
+            }
+            forward_walk<ALGO, POLY>(env, nullptr, d.plen, fp);
+        }
+        if (d.plen <= kProgWords) staged[slot]++;
+        finish_item(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr,
+                    ring.bars + (M::bDescEmpty + slot) * 8);
+        PMFS_TRACE_END(d.chunk, d.tile)
+    }
+}
+
+template <int ALGO>
+__global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 3) bwd_kernel(const WalkParams p) {
+    using M = SmemMap<kSetRingBwd>;
+    extern __shared__ uint4 smem[];
+    __shared__ __align__(8) unsigned long long bars[M::kBars];
+    const Ring ring = ring_setup<kSetRingBwd>(smem, bars);
+    if (threadIdx.x >= kTPB) {
+        PMFS_WP(10);
+        producer_loop<kSetRingBwd>(p, ring);
+        return;
+    }
+    PMFS_WP(5);
+    uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
+    ItemDesc d;
+    for (uint32_t n = 0; next_item<kSetRingBwd>(ring, n, d); n++) {
+        const uint32_t slot = n & 1u;
+        uint32_t err;
+        PMFS_TRACE_BEGIN
+        {
+            DevEnv<true, kSetRingBwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            if (p.cell_count) env.reserve_blocks();
+            Code4 P[kNG], forced[kNG];
+            uint32_t pv[kNG], colmask[kNG];
+            const Code4* fp = nullptr;
+#pragma unroll
+            for (int j = 0; j < kNG; j++) {
+                pv[j] = ~0u;
+                if (d.chunk == 0) {
+                    const uint4 v = __ldg(p.cons_planes + env.g[j]);
+                    P[j].b[0] = v.x; P[j].b[1] = v.y; P[j].b[2] = v.z; P[j].b[3] = v.w;
+                    if (ALGO == kAlgoSankoff && p.forced_planes) {
+                        const uint4 f = __ldg(p.forced_planes + env.g[j]);
+                        forced[j].b[0] = f.x; forced[j].b[1] = f.y; forced[j].b[2] = f.z; forced[j].b[3] = f.w;
+                        fp = forced;
+                    }
+                } else {  // written by another SM during this launch: read through L2
+                    const uint4 v = __ldcg(p.xcode + (int64_t)d.chunk * p.G + env.g[j]);
+                    P[j].b[0] = v.x; P[j].b[1] = v.y; P[j].b[2] = v.z; P[j].b[3] = v.w;
+                    pv[j] = __ldcg(p.xvalid + (int64_t)d.chunk * p.G + env.g[j]);
+                }
+                colmask[j] = env.active[j] ? real_column_mask(env.g[j], p.tile_cols) : 0u;
+            }
+            err = backward_walk<ALGO>(env, nullptr, d.plen, P, pv, fp, colmask);
+        }
+        if (err) atomicOr(p.err_flag, 1u);
+        if (d.plen <= kProgWords) staged[slot]++;
+        finish_item(p.ready + (int64_t)d.chunk * p.ctas_per_chunk + d.tile, ring.bars + (M::bDescEmpty + slot) * 8);
+        PMFS_TRACE_END(d.chunk, d.tile)
+    }
+}
+
+}  // namespace pmfs
