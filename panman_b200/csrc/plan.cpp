@@ -230,6 +230,12 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
             if (f.i < 0) {
                 P.bwd_prog.push_back(v == 0 ? op(B_ENTER_ROOT, 0) : op(B_ENTER, (uint32_t)P.int_id[v]));
                 P.bwd_stream.push_back(kStreamSet | (uint32_t)P.int_id[v]);
+                // child chunks first: XCHILD releases the child chunk (its tile can start at once), so it comes before
+                // anything that takes time at this node
+                for (int32_t k = b; k < e; k++) {
+                    int32_t c = t.child_idx[k];
+                    if (P.int_id[c] >= 0 && cut[c]) P.bwd_prog.push_back(op(B_XCHILD, (uint32_t)chunk_of_root[c]));
+                }
                 for (int32_t k = b; k < e; k++) {
                     int32_t c = t.child_idx[k];
                     if (P.int_id[c] < 0) {
@@ -237,9 +243,7 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
                             P.bwd_prog.push_back(op(B_LEAF, (uint32_t)t.leaf_row[c]));
                             P.bwd_stream.push_back((uint32_t)t.leaf_row[c]);
                         }
-                    } else if (cut[c]) {
-                        P.bwd_prog.push_back(op(B_XCHILD, (uint32_t)chunk_of_root[c]));
-                    } else {
+                    } else if (!cut[c]) {
                         f.subs.push_back(c);
                     }
                 }

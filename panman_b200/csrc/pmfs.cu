@@ -190,9 +190,10 @@ static int upload_plan(pmfs_ctx* c) {
             }
             items[2 * k] = make_int4(order[k], ch.parent, pass == 0 ? ch.fwd_len : ch.bwd_len,
                                      pass == 0 ? ch.fwd_stream_len : ch.bwd_stream_len);
-            // bottom-up: wait for all child chunks on my own counter; top-down: for the parent chunk on its counter
+            // both passes wait on the chunk's OWN counter: bottom-up it counts finished child chunks, top-down it is set
+            // by the parent chunk the moment that has stored this chunk's parent state (XCHILD), not when it finishes
             const int need = pass == 0 ? ch.n_child : (ch.parent < 0 ? 0 : 1);
-            const int dep = (pass == 0 || ch.parent < 0) ? order[k] : ch.parent;
+            const int dep = order[k];
             items[2 * k + 1] = make_int4((int)(poff / 4), (int)soff, need, dep);
         }
         if ((rc = up(pass == 0 ? c->d_fwd_items : c->d_bwd_items, items))) return rc;

@@ -374,6 +374,7 @@ struct DevEnv {
     int64_t gwarp;       // (unclamped) column group of this warp's lane 0, first group slot
     int64_t set_tile;    // uint4 offset of this tile inside one node's set row: tile * 1024
     int32_t tile_w;      // column groups of this tile (256, less for the last tile): stride between the 4 quarters
+    int32_t item_tile;   // column tile of this work item
     uint32_t& n_leaf;    // running ring entry numbers of this CTA (same sequences as the producer's)
     uint32_t& n_set;
     uint4* fstk;         // [depth][kNG][4][kTPB]
@@ -391,6 +392,7 @@ struct DevEnv {
                       uint32_t& n_leaf_, uint32_t& n_set_, void* smem_generic)
         : p(p_), ring(r), gwarp((int64_t)d.tile * kTileGroups + (threadIdx.x & ~31)), set_tile((int64_t)d.tile * (kSetBytes / 16)),
           tile_w((int32_t)min((int64_t)kTileGroups, p_.G - (int64_t)d.tile * kTileGroups)),
+          item_tile(d.tile),
           n_leaf(n_leaf_), n_set(n_set_), fstk((uint4*)((char*)smem_generic + M::kStack)),
           bstk((uint32_t*)((char*)smem_generic + M::kStack)), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords),
           gprog(nullptr), sprog(r.smem + M::kProg + slot * (kProgWords * 4)) {
@@ -519,12 +521,19 @@ struct DevEnv {
             pv[j] = q[(j * 5 + 4) * kTPB];
         }
     }
+    // The parent state of a child chunk, and -- top-down dependencies are per chunk, not per finished item -- the go-ahead
+    // for it: the child chunk's tile can start while this item is still walking the rest of its own nodes.
     __device__ __forceinline__ void store_x(uint32_t chunk, const Code4 (&c)[kNG], const uint32_t (&pv)[kNG]) const {
 #pragma unroll
         for (int j = 0; j < kNG; j++) {
             if (!active[j]) continue;
             p.xcode[(int64_t)chunk * p.G + g[j]] = make_uint4(c[j].b[0], c[j].b[1], c[j].b[2], c[j].b[3]);
             p.xvalid[(int64_t)chunk * p.G + g[j]] = pv[j];
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // all four walking warps have stored their part
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(p.ready + (int64_t)chunk * p.ctas_per_chunk + item_tile, 1);
         }
     }
     __device__ __forceinline__ bool any(bool x) const { return __any_sync(0xffffffffu, x); }
@@ -845,7 +854,7 @@ __global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 3) bwd_kern
         }
         if (err) atomicOr(p.err_flag, 1u);
         if (d.plen <= kProgWords) staged[slot]++;
-        finish_item(p.ready + (int64_t)d.chunk * p.ctas_per_chunk + d.tile, ring.bars + (M::bDescEmpty + slot) * 8);
+        finish_item(nullptr, ring.bars + (M::bDescEmpty + slot) * 8);  // (child chunks were released by store_x)
         PMFS_TRACE_END(d.chunk, d.tile)
     }
 }
