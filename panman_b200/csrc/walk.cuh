@@ -378,8 +378,38 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
             } else if (code == F_JOIN_IMM) {
                 load_operand(env, env.word(prog, pc++), A);
             } else {  // F_JOIN_IMM2
-                load_operand(env, env.word(prog, pc++), A);
-                load_operand(env, env.word(prog, pc++), T);
+                const uint32_t o1 = env.word(prog, pc++), o2 = env.word(prog, pc++);
+                if (!((o1 | o2) & kOperandSet) && o1 != kAbsentLeaf && o2 != kAbsentLeaf) {
+                    // a cherry (two leaves, a third of the internal nodes of a random binary tree): two one-element sets
+                    // meet only if equal, and then their union is the same set -- S = {a} | {b} without a join;
+                    // Sankoff's D1 is everything else where a != b and empty where a == b
+                    uint4 wa[NG], wb[NG];
+                    env.leaf(o1, wa);
+                    env.leaf(o2, wb);
+#pragma unroll
+                    for (int j = 0; j < NG; j++) {
+                        Code4 a, b;
+                        transpose_nibbles(wa[j], a);
+                        transpose_nibbles(wb[j], b);
+                        uint32_t la[4], ha[4], lb[4], hb[4];
+                        la[0] = ~a.b[1] & ~a.b[0]; la[1] = ~a.b[1] & a.b[0]; la[2] = a.b[1] & ~a.b[0]; la[3] = a.b[1] & a.b[0];
+                        ha[0] = ~a.b[3] & ~a.b[2]; ha[1] = ~a.b[3] & a.b[2]; ha[2] = a.b[3] & ~a.b[2]; ha[3] = a.b[3] & a.b[2];
+                        lb[0] = ~b.b[1] & ~b.b[0]; lb[1] = ~b.b[1] & b.b[0]; lb[2] = b.b[1] & ~b.b[0]; lb[3] = b.b[1] & b.b[0];
+                        hb[0] = ~b.b[3] & ~b.b[2]; hb[1] = ~b.b[3] & b.b[2]; hb[2] = b.b[3] & ~b.b[2]; hb[3] = b.b[3] & b.b[2];
+#pragma unroll
+                        for (int s_ = 0; s_ < 16; s_++) T[j].p[s_] = (ha[s_ >> 2] & la[s_ & 3]) | (hb[s_ >> 2] & lb[s_ & 3]);
+                        if (ALGO == kAlgoSankoff) {
+                            const uint32_t ne = code_ne(a, b);
+#pragma unroll
+                            for (int s_ = 0; s_ < 16; s_++) D1[j].p[s_] = ~T[j].p[s_] & ne;
+                        }
+                    }
+                    finish_node<ALGO>(env, id, T, forced);
+                    if (ALGO == kAlgoSankoff) env.store_d(id, D1);
+                    continue;
+                }
+                load_operand(env, o1, A);
+                load_operand(env, o2, T);
             }
 #pragma unroll
             for (int j = 0; j < NG; j++) {
