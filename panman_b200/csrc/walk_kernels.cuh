@@ -758,13 +758,15 @@ __device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d
 }
 // Item finished: publish it to dependants (all walkers' stores first), then free the descriptor/program slot.
 __device__ __forceinline__ void finish_item(int* counter, uint32_t desc_empty_bar) {
-    {
-        PMFS_WP(4);
-        asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // the four walking warps only
-    }
-    if (threadIdx.x == 0 && counter) {
-        __threadfence();
-        atomicAdd(counter, 1);
+    if (counter) {  // (uniform; the top-down pass publishes per child chunk in store_x and has nothing to say here)
+        {
+            PMFS_WP(4);
+            asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // the four walking warps only
+        }
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(counter, 1);
+        }
     }
     __syncwarp();
     if ((threadIdx.x & 31) == 0) mbar_arrive(desc_empty_bar);
