@@ -583,6 +583,15 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     unsigned long long* const d_off = d_stats + 16;
     if (!c->h_stats) PMFS_CUDA(cudaMallocHost(&c->h_stats, 16 * sizeof(unsigned long long)));
     size_t cap = std::max<size_t>(c->d_keys.cap, 1 << 20);  // total records; one region is cap / n_owners
+    if (use_cells && c->d_keys.cap == 0) {
+        // First call: every (chunk, column region) reserves output blocks of 256 records (DevEnv::emit_cells); two
+        // blocks each covers the usual mutation densities, so that the passes need not be run twice to find the size.
+        // Bounded by what is free on the device; denser data still takes the grow-and-redo path below.
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        const size_t guess = (size_t)NC * (size_t)W * 512;
+        if (guess * sizeof(unsigned long long) < free_b / 4) cap = std::max(cap, guess);
+    }
 
     pmfs_timing& tm = c->timing;
     const float h2d_keep = tm.h2d_ms;
