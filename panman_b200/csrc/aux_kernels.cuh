@@ -6,8 +6,12 @@
 namespace pmfs {
 
 // codes[col_base .. col_base+tile_cols) -> planes[G] in the bit order of transpose_nibbles
-__global__ void prep_planes_kernel(const uint8_t* __restrict__ codes, int64_t tile_cols, int64_t G, uint4* __restrict__ planes) {
+// (also clears up to two small word arrays -- the step's counters -- so that they need no launches of their own)
+__global__ void prep_planes_kernel(const uint8_t* __restrict__ codes, int64_t tile_cols, int64_t G, uint4* __restrict__ planes,
+                                   uint32_t* zero_a = nullptr, int64_t n_a = 0, uint32_t* zero_b = nullptr, int64_t n_b = 0) {
     int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (int64_t i = g; i < n_a; i += (int64_t)gridDim.x * blockDim.x) zero_a[i] = 0;
+    for (int64_t i = g; i < n_b; i += (int64_t)gridDim.x * blockDim.x) zero_b[i] = 0;
     if (g >= G) return;
     uint32_t b[4] = {0, 0, 0, 0};
     for (int q = 0; q < 32; q++) {
@@ -174,7 +178,7 @@ __device__ __forceinline__ int kth_set_bit(uint32_t mask, uint32_t k) {  // posi
     }
     return pos;
 }
-__global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, unsigned long long cap, const uint32_t* __restrict__ cnt,
+__global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, unsigned long long cap, uint32_t* __restrict__ cnt,
                                    const uint32_t* __restrict__ start, const uint32_t* __restrict__ prefix, int64_t cells, int32_t W,
                                    int pos_bits, const unsigned long long* __restrict__ stats, unsigned long long out_cap,
                                    pmfs_mut* __restrict__ out) {
@@ -194,6 +198,7 @@ __global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, 
     }
     for (; c0 < cells; c0 += stride) {
         const uint32_t n_l = n_nx, s_l = s_nx, e_l = e_nx;
+        if (n_l) cnt[c0 + lane] = 0;  // leaves the matrix clear for the next run (no 12-bytes-per-cell memset per step)
         n_nx = 0;
         if (c0 + stride + lane < cells) {
             n_nx = cnt[c0 + stride + lane];

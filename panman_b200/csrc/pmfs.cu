@@ -100,6 +100,7 @@ struct pmfs_ctx {
     cudaEvent_t ev_slab[2] = {};        // pmfs_run: upload slab 0 / 1 complete (recorded on copy_stream)
     cudaStream_t copy_stream = nullptr;
     int64_t slab_split = 0;             // > 0 while pmfs_run pipelines: first column group of the second slab
+    int64_t cells_clean_n = 0;          // d_cell_count holds this many zeroed cells (0: unknown, clear before use)
     // plan on device
     DevBuf<uint32_t> d_fwd_prog, d_bwd_prog, d_fwd_stream, d_bwd_stream;
     DevBuf<int64_t> d_fwd_off, d_bwd_off, d_fwd_soff, d_bwd_soff;
@@ -384,7 +385,7 @@ static size_t sync_ints(const Plan& P, int64_t groups) {
 // One launch per pass over all chunks (the name is historical: the first version launched once per chunk level).
 // wp.ready must point to sync_ints() ints of device memory.
 template <int ALGO>
-static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches) {
+static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches, bool sync_cleared = false) {
     const Plan& P = c->plan;
     wp.prog = fwd ? c->d_fwd_prog.ptr : c->d_bwd_prog.ptr;
     wp.chunk_off = fwd ? c->d_fwd_off.ptr : c->d_bwd_off.ptr;
@@ -432,7 +433,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     if (c->n_sms == 0) PMFS_CUDA(cudaDeviceGetAttribute(&c->n_sms, cudaDevAttrMultiProcessorCount, c->device));
     const unsigned grid = (unsigned)std::min<int64_t>(n_items, (int64_t)c->n_sms * per_sm);
     // claim counters and dependency counters of BOTH passes are cleared once, ahead of the bottom-up pass
-    if (fwd) PMFS_CUDA(cudaMemsetAsync(sync, 0, (64 + 2 * per_pass) * sizeof(int), c->stream));
+    if (fwd && !sync_cleared) PMFS_CUDA(cudaMemsetAsync(sync, 0, (64 + 2 * per_pass) * sizeof(int), c->stream));
     void* args[] = {&wp};
 #ifdef PMFS_WAITPROF
     {
@@ -605,8 +606,11 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     for (int attempt = 0; attempt < 2; attempt++) {
         if ((rc = c->d_keys.ensure(cap))) return rc;
         region = c->d_keys.cap / (size_t)n_owners;
-        PMFS_CUDA(cudaMemsetAsync(c->d_count.ptr, 0, (n_ctr + 16) * sizeof(unsigned long long), c->stream));
-        if (use_cells) PMFS_CUDA(cudaMemsetAsync(c->d_cell_count.ptr, 0, (size_t)cells * sizeof(uint32_t), c->stream));
+        // (the area counters and the walk kernels' claim / dependency counters are cleared by the prep kernel below; the
+        // cell matrix is left clear by order_cells_kernel and only needs a memset after a run that did not get there)
+        if (use_cells && c->cells_clean_n != cells)
+            PMFS_CUDA(cudaMemsetAsync(c->d_cell_count.ptr, 0, (size_t)cells * sizeof(uint32_t), c->stream));
+        c->cells_clean_n = 0;
         fwd_ms = bwd_ms = 0;
         tm.n_launches = 0;
         // column segments: the memory tiles, cut once more where pmfs_run's second upload slab begins
@@ -647,14 +651,20 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             wp.ready = c->d_sync.ptr;
             const unsigned pg = (unsigned)((wp.G + 127) / 128);
             PMFS_CUDA(cudaEventRecord(c->ev[0], c->stream));
-            prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_cons + wp.col_base, wp.tile_cols, wp.G, c->d_cons_planes.ptr);
+            {
+                const int64_t seg_items = (int64_t)P->chunks.size() * ((wp.G + kTileGroups - 1) / kTileGroups);
+                prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_cons + wp.col_base, wp.tile_cols, wp.G, c->d_cons_planes.ptr,
+                                                             (uint32_t*)c->d_sync.ptr, 64 + 2 * seg_items,
+                                                             g0 == 0 ? (uint32_t*)c->d_count.ptr : nullptr,
+                                                             g0 == 0 ? (int64_t)(n_ctr + 16) * 2 : 0);
+            }
             tm.n_launches++;
             if (d_forced) {
                 prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_forced + wp.col_base, wp.tile_cols, wp.G, c->d_forced_planes.ptr);
                 tm.n_launches++;
             }
-            rc = algo == PMFS_FITCH ? launch_levels<kAlgoFitch>(c, wp, true, &tm.n_launches)
-                                    : launch_levels<kAlgoSankoff>(c, wp, true, &tm.n_launches);
+            rc = algo == PMFS_FITCH ? launch_levels<kAlgoFitch>(c, wp, true, &tm.n_launches, true)
+                                    : launch_levels<kAlgoSankoff>(c, wp, true, &tm.n_launches, true);
             if (rc) return rc;
             PMFS_CUDA(cudaEventRecord(c->ev[1], c->stream));
             rc = algo == PMFS_FITCH ? launch_levels<kAlgoFitch>(c, wp, false, &tm.n_launches)
@@ -816,6 +826,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         PMFS_CUDA(cudaGetLastError());
         tm.n_launches += 1;
     }
+    if (use_cells) c->cells_clean_n = cells;  // order_cells_kernel ran to the end (or nothing was emitted): the matrix is clear
     if (use_cells && ordered_cap > 0 && (size_t)n <= ordered_cap) {
         // the ordering was queued before the one synchronisation of the step and has finished with it
         cudaEventElapsedTime(&tm.sort_ms, c->ev[3], c->ev[7]);
