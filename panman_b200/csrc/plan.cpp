@@ -97,6 +97,53 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
         if (!any_new || rem[0] < 32 || thr <= 8) break;
         thr = std::max<int64_t>(8, thr / 8);
     }
+    // ---- walk-stack depth.  Every stack level costs shared memory per CTA (16 KB bottom-up, 5 KB top-down) and with it
+    // resident CTAs per SM, which is what the latency-bound walks live on; so a chunk may nest at most kMaxWalkStack
+    // saved states.  Bottom-up a binary node with two in-chunk internal children saves the first one's set while it
+    // walks the second; top-down every in-chunk internal child but the last saves the parent state.  Where that would
+    // nest deeper, the child that would be walked with the stack already full is cut off as a chunk of its own.
+    {
+        constexpr int kMaxWalkStack = 2;
+        std::vector<int32_t> remf(V, 1);
+        std::vector<uint8_t> need_f(V, 0), need_b(V, 0);
+        for (int32_t v = V - 1; v >= 0; v--) {
+            if (P.int_id[v] < 0) continue;
+            const int32_t b = t.child_off[v], e = t.child_off[v + 1];
+            for (;;) {
+                int32_t first = -1, last = -1, nsub = 0;  // the generators' orders: stable sorts on rem (see below)
+                for (int32_t k = b; k < e; k++) {
+                    const int32_t c = t.child_idx[k];
+                    if (P.int_id[c] < 0 || cut[c]) continue;
+                    nsub++;
+                    if (first < 0 || remf[c] > remf[first]) first = c;
+                    if (last < 0 || remf[c] >= remf[last]) last = c;
+                }
+                bool changed = false;
+                int nf = 0, nb = 0;
+                for (int32_t k = b; k < e; k++) {
+                    const int32_t c = t.child_idx[k];
+                    if (P.int_id[c] < 0 || cut[c]) continue;
+                    const bool pushed_f = (e - b) == 2 && nsub == 2 && c != first;
+                    const bool pushed_b = c != last;
+                    if ((pushed_f && need_f[c] + 1 > kMaxWalkStack) || (pushed_b && need_b[c] + 1 > kMaxWalkStack)) {
+                        cut[c] = 1;
+                        changed = true;
+                        break;
+                    }
+                    nf = std::max(nf, need_f[c] + (pushed_f ? 1 : 0));
+                    nb = std::max(nb, need_b[c] + (pushed_b ? 1 : 0));
+                }
+                if (changed) continue;
+                need_f[v] = (uint8_t)nf;
+                need_b[v] = (uint8_t)nb;
+                break;
+            }
+            for (int32_t k = b; k < e; k++) {
+                const int32_t c = t.child_idx[k];
+                remf[v] += (P.int_id[c] < 0 || cut[c]) ? 1 : remf[c];
+            }
+        }
+    }
     // rem[] must describe the final cut set (the walk orders children by it)
     std::fill(rem.begin(), rem.end(), 1);
     for (int32_t v = V - 1; v >= 1; v--) rem[t.parent[v]] += cut[v] ? 1 : rem[v];

@@ -237,14 +237,15 @@ static int replan(pmfs_ctx* c, int32_t chunk_nodes) {
     return upload_plan(c);
 }
 
-// Chunk size.  At BASELINE-config-2 scale a pass is (chain of dependent items near the root) + (bulk throughput); the
-// chain costs about 6 us per chunk level plus 0.4 us per node on the longest path, so chunks are kept small as long as
-// an item still amortises its fixed cost -- measured optimum on config 2: 12-14 nodes (sweeps in profiles/).
+// Chunk size.  At BASELINE-config-2 scale a pass is (chain of dependent items near the root) + (bulk throughput).  With
+// the walk stack capped by the plan (plan.cpp: kMaxWalkStack, so that chunk size no longer costs resident CTAs) and child
+// chunks released per XCHILD, the fixed cost per item is what is left to amortise: measured on config 2 the step is flat
+// between 24 and 64 nodes (0.71-0.72 ms) and 4 % slower at 14 (sweeps in profiles/README.md).
 static int32_t auto_chunk_nodes(int32_t n_nodes, int64_t groups) {
     int64_t ctas_per_chunk = (groups + kTileGroups - 1) / kTileGroups;
     int64_t want_chunks = std::max<int64_t>(1, (148 * 48 + ctas_per_chunk - 1) / ctas_per_chunk);
     int64_t cn = n_nodes / (want_chunks * 2);  // chunks end up between cn and 2*cn nodes
-    return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 14), 1 << 16);
+    return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 24), 1 << 16);
 }
 
 extern "C" {
