@@ -97,12 +97,29 @@ def test_emul_ladder_and_balanced_stack_depth(emul):
         assert plan[3] <= 1 and plan[4] <= 1  # a ladder needs no stack at all: the heavy child is walked in place
         got = run_emul(emul, algo, ladder, msa, cons, None, 100)
         assert G.same_muts(got, want)
-    # perfectly balanced tree: stack depth stays logarithmic
+    # perfectly balanced tree in ONE chunk request: the plan cuts wherever a walk would nest more than two saved states
+    # (every stack level costs shared memory per CTA, i.e. resident CTAs), and the result does not change
     def bal(lo, hi):
         return lo if hi - lo == 1 else [bal(lo, (lo + hi) // 2), bal((lo + hi) // 2, hi)]
     tree = synth._flatten(bal(0, 256))
-    _, plan = run_emul(emul, 0, tree, synth.simulate_msa(tree, 8, rng), np.ones(8, np.uint8), None, 1 << 30, want_plan=True)
-    assert plan[3] <= 8 and plan[4] <= 8
+    msa = synth.simulate_msa(tree, 40, rng, p_sub=0.05)
+    cons = synth.consensus_first_nongap(msa)
+    for algo in (0, 1):
+        got, plan = run_emul(emul, algo, tree, msa, cons, None, 1 << 30, want_plan=True)
+        assert plan[3] <= 2 and plan[4] <= 2 and plan[0] > 1
+        assert G.same_muts(got, O.run_port(algo, tree, msa, cons, None))
+
+
+def test_emul_walk_stack_is_capped_on_random_trees(emul):
+    rng = np.random.default_rng(17)
+    for trial in range(8):
+        tree = synth.random_tree(int(rng.integers(200, 1500)), rng, max_arity=2 if trial % 2 else 5)
+        msa = synth.simulate_msa(tree, 33, rng, p_sub=0.05, p_del=0.02, p_ins=0.05)
+        cons = synth.consensus_first_nongap(msa)
+        for chunk in (24, 200, 1 << 30):
+            got, plan = run_emul(emul, trial % 2, tree, msa, cons, None, chunk, want_plan=True)
+            assert plan[3] <= 2 and plan[4] <= 2, (trial, chunk, plan)
+            assert G.same_muts(got, O.run_port(trial % 2, tree, msa, cons, None)), (trial, chunk)
 
 
 def test_emul_sankoff_invalid_root(emul):
