@@ -213,3 +213,25 @@ def test_block_level_passes_through_run_codes():
         with api.Context(t2) as ctx:
             got = O.blocks_from_nuc(ctx.run_codes(api.SANKOFF, st2, cons, forced))
         assert G.same_muts(got, want), (trial, "sankoff")
+
+
+def test_large_polytomies():
+    """Nodes with tens to hundreds of children (outbreak trees are full of them): the any-arity joins of both
+    algorithms, with Sankoff's counters rippling through several bit planes, against the plain-C oracle."""
+    rng = np.random.default_rng(29)
+    star = synth._flatten(list(range(300)))
+    two_level, nxt = [], 0
+    for _ in range(6):
+        k = int(rng.integers(40, 70))
+        two_level.append(list(range(nxt, nxt + k)))
+        nxt += k
+    two_level += list(range(nxt, nxt + 25))
+    for tree in (star, synth._flatten(two_level)):
+        L = 1100
+        msa = synth.simulate_msa(tree, L, rng, p_sub=0.3, p_del=0.1, p_ins=0.2, p_n=0.05, p_amb=0.05)
+        cons = synth.consensus_first_nongap(msa)
+        for algo in (0, 1):
+            for forced in (None, msa[3]):
+                want = O.run_port(algo, tree, msa, cons, forced, threads=4)
+                got = run_gpu(tree, algo, msa, cons, forced)
+                assert G.same_muts(got, want), (tree.n_nodes, algo, forced is not None)

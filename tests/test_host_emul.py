@@ -128,3 +128,29 @@ def test_emul_sankoff_invalid_root(emul):
         run_emul(emul, 1, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), None, 1 << 30)
     assert run_emul(emul, 0, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), None, 1 << 30).shape[0] == 0
     assert run_emul(emul, 1, tree, np.zeros((0, 3), np.uint8), np.zeros(3, np.uint8), np.array([1, 0, 2], np.uint8), 1 << 30).shape[0] == 2
+
+
+def test_emul_large_polytomies(emul):
+    """Any-arity joins far beyond what the random trees reach: a star of 300 leaves, a two-level tree with nodes of 40-70
+    children, and polytomies made by collapsing the edges of a binary tree (Sankoff's counters need up to 9 bits here,
+    i.e. the flush of the 2-bit register counters into the full-width ones ripples through several planes)."""
+    rng = np.random.default_rng(23)
+    star = synth._flatten(list(range(300)))
+    two_level, nxt = [], 0
+    for _ in range(6):
+        k = int(rng.integers(40, 70))
+        two_level.append(list(range(nxt, nxt + k)))
+        nxt += k
+    two_level += list(range(nxt, nxt + 25))
+    trees_ = [star, synth._flatten(two_level)]
+    for tree in trees_:
+        L = 70
+        msa = synth.simulate_msa(tree, L, rng, p_sub=0.3, p_del=0.1, p_ins=0.2, p_n=0.05, p_amb=0.05)
+        cons = synth.consensus_first_nongap(msa)
+        forced = msa[3]
+        for algo in (0, 1):
+            for frc in (None, forced):
+                want = O.run_port(algo, tree, msa, cons, frc)
+                for chunk in (24, 1 << 30):
+                    got = run_emul(emul, algo, tree, msa, cons, frc, chunk)
+                    assert G.same_muts(got, want), (tree.n_nodes, algo, chunk)
