@@ -235,3 +235,21 @@ def test_large_polytomies():
                 want = O.run_port(algo, tree, msa, cons, forced, threads=4)
                 got = run_gpu(tree, algo, msa, cons, forced)
                 assert G.same_muts(got, want), (tree.n_nodes, algo, forced is not None)
+
+
+def test_record_buffer_grows_and_passes_are_redone():
+    """Far more mutations than the first call's record buffer is sized for (random codes in every cell: most cells
+    mutate): the overflow is detected on the device, the buffer grows, the passes run again -- same records."""
+    rng = np.random.default_rng(31)
+    tree = synth.random_tree(48, rng, max_arity=2)
+    L = 40000
+    msa = rng.integers(0, 16, (synth.n_rows(tree), L)).astype(np.uint8)
+    cons = np.maximum(msa[0], 1).astype(np.uint8)
+    for algo in (0, 1):
+        want = O.run_port(algo, tree, msa, cons, None, threads=4)
+        assert want.shape[0] > (1 << 20)
+        with api.Context(tree) as ctx:
+            nib = api.pack_nibbles(msa)
+            got = ctx.run(algo, nib, L, cons)
+            again = ctx.run(algo, nib, L, cons)  # second call: the grown buffer is kept
+        assert G.same_muts(got, want) and G.same_muts(again, want), algo
