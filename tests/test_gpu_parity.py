@@ -253,3 +253,22 @@ def test_record_buffer_grows_and_passes_are_redone():
             got = ctx.run(algo, nib, L, cons)
             again = ctx.run(algo, nib, L, cons)  # second call: the grown buffer is kept
         assert G.same_muts(got, want) and G.same_muts(again, want), algo
+
+
+def test_no_records_then_records_on_one_context():
+    """A run that emits nothing (all rows equal to the consensus), then one that does, then nothing again, on the same
+    context: the per-run state that is only cleared lazily (cell counts, output buffer of the previous run) must not leak."""
+    rng = np.random.default_rng(37)
+    tree = synth.random_tree(200, rng, max_arity=3)
+    L = 3000
+    rows = synth.n_rows(tree)
+    same = np.tile(rng.integers(1, 16, L).astype(np.uint8), (rows, 1))
+    varied = synth.simulate_msa(tree, L, rng, p_sub=0.05, p_del=0.02, p_ins=0.05, p_n=0.02)
+    with api.Context(tree) as ctx:
+        for algo in (0, 1):
+            for msa in (same, varied, same, varied):
+                cons = msa[0].copy() if msa is same else synth.consensus_first_nongap(msa)
+                want = O.run_port(algo, tree, msa, cons, None, threads=4)
+                got = ctx.run(algo, api.pack_nibbles(msa), L, cons)
+                assert (want.shape[0] == 0) == (msa is same)
+                assert G.same_muts(got, want), (algo, msa is same)
