@@ -126,9 +126,9 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
                     const bool pushed_f = (e - b) == 2 && nsub == 2 && c != first;
                     const bool pushed_b = c != last;
                     if ((pushed_f && need_f[c] + 1 > kMaxWalkStack) || (pushed_b && need_b[c] + 1 > kMaxWalkStack)) {
-                        cut[c] = 1;
+                        cut[c] = 1;  // (all offenders of this scan at once: a node may have 10^5 children)
                         changed = true;
-                        break;
+                        continue;
                     }
                     nf = std::max(nf, need_f[c] + (pushed_f ? 1 : 0));
                     nb = std::max(nb, need_b[c] + (pushed_b ? 1 : 0));
