@@ -90,6 +90,19 @@ void pmfs_destroy(pmfs_ctx* ctx);
  * (0 = automatic from free HBM).  Results never depend on either. */
 int pmfs_set_tuning(pmfs_ctx* ctx, int32_t chunk_nodes, int64_t tile_cols);
 
+/* Column-tile shape of the walk kernels' work items: `walking_warps` x 32 threads, each walking `groups_per_thread`
+ * groups of 32 columns.  Built shapes: 4x2 (256 groups per item), 2x2 and 4x1 (128), 1x2 and 2x1 (64), 1x1 (32).
+ * 0 = automatic: the widest shape that does not idle lanes on the column range, the narrowest one on ladder-like trees
+ * (there the column tiles are the only independent work).  Results never depend on it.  No counterpart in the
+ * reference. */
+int pmfs_set_tile(pmfs_ctx* ctx, int32_t walking_warps, int32_t groups_per_thread);
+
+/* Every wait inside the walk kernels gives up after `seconds` (default 10; 0 = never) and the run fails with
+ * PMFS_ERR_CUDA and a message naming the watchdog: a bookkeeping bug must not hang a GPU, but a debugger, a sanitizer
+ * or a time-sliced GPU can make legitimate waits long.  A tripped watchdog leaves the CUDA context unusable, like any
+ * device-side trap.  No counterpart in the reference. */
+int pmfs_set_watchdog(pmfs_ctx* ctx, double seconds);
+
 /* Run all of the context's work on `cuda_stream` (a cudaStream_t of the context's device; NULL restores the context's
  * own stream).  Lets a caller order the passes after its own producers and time them with its own events. */
 int pmfs_set_stream(pmfs_ctx* ctx, void* cuda_stream);
@@ -143,6 +156,25 @@ static inline int pmfs_block_inverted(const pmfs_mut* m) { return m->type == 2 ?
 int pmfs_run_device(pmfs_ctx* ctx, int algo, const uint8_t* d_msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
                     int64_t n_cols, const uint8_t* d_consensus_code, const uint8_t* d_root_forced_code,
                     pmfs_mut** d_out, int64_t* n_out);
+/* ---- column batches --------------------------------------------------------------------------------------------------
+ * The same pass over [n_cols] columns in batches of `batch_cols` columns (a multiple of 32; 0 = automatic: as many as
+ * the per-node set arrays of one batch fit in free device memory, halved again if one batch would exceed 2^31
+ * records).  The reference batches columns the same way when memory is short: --low-mem-mode reads and processes
+ * 20 000 columns at a time and appends every batch's tuples to the per-node lists (src/panman.cpp:1503-1514, :1597-1601).
+ * After each batch `consumer` (may be NULL) is called with the batch's records ON THE DEVICE, sorted by (node,pos),
+ * positions global; the buffer is reused by the next batch, so the consumer must be done with it -- or have queued
+ * its copy on the context's stream -- when it returns; a non-zero return value aborts the run.  A node's complete list
+ * is the concatenation of its slices from all batches in batch order.  This is how an 8 M-taxon x 30 000-column
+ * alignment (2.4 x 10^9 records, 120 GB of nibbles) runs on one GPU.  pmfs_get_timing reports the sums over batches. */
+typedef int (*pmfs_batch_fn)(void* user, int64_t col_begin, int64_t n_cols, const pmfs_mut* d_records, int64_t n_records);
+int pmfs_run_batched(pmfs_ctx* ctx, int algo, const uint8_t* d_msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
+                     int64_t n_cols, const uint8_t* d_consensus_code, const uint8_t* d_root_forced_code, int64_t batch_cols,
+                     pmfs_batch_fn consumer, void* user, int64_t* n_total, int32_t* n_batches);
+/* Batch size used by pmfs_run_batched when its batch_cols is 0, and by pmfs_run / pmfs_run_chars / pmfs_run_codes, which
+ * stream an alignment that does not fit on the device next to its set arrays through the GPU in column batches
+ * (0 = automatic). */
+int pmfs_set_batch_cols(pmfs_ctx* ctx, int64_t batch_cols);
+
 /* ---- column shards across GPUs (one context per GPU; no counterpart in the reference, which is single-process) ------
  * pmfs_set_shard puts a context in shard mode: its columns are [pos_offset, pos_offset+n_cols) of a total_cols-wide
  * alignment, and node ids [node_bounds[r], node_bounds[r+1]) are owned by rank r (n_parts <= 16; n_parts = 0 leaves
@@ -175,9 +207,13 @@ int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);
  * static storage duration in device memory, which every GPU that loads this library keeps until the process exits.
  *   inputs   device pointers as for pmfs_run_device (all columns are processed in one pass, no tiling)
  *   outputs  d_out: caller's device buffer of out_capacity records, filled sorted by (node,pos); *n_out: record count
- * Limits: the call is rejected with PMFS_ERR_ARG and an explanatory pmfs_last_error() when
- *   256-byte-rounded (n_internal*ceil(n_cols/32)*64 + n_chunks*ceil(n_cols/32)*20 + out_capacity*16 + sort workspace)
- * exceeds 32 MiB, and when more than out_capacity records are produced (*n_out then holds the number needed).
+ * Limits: the call is rejected with PMFS_ERR_ARG and an explanatory pmfs_last_error() when the pieces carved out of
+ * the array, each rounded up to 256 bytes -- with G = ceil(n_cols/32): the set array n_internal*G*64, the chunk parent
+ * states n_chunks*G*20, two bit-sliced code arrays G*16 each, two record buffers out_capacity*8 each, the radix sort's
+ * workspace (about 1/16 of a record buffer) and the walk kernels' counters (64 + 2*n_chunks*tiles)*4 -- exceed 32 MiB,
+ * and when more than out_capacity records are produced (*n_out then holds the number needed).  A context in
+ * column-shard mode is refused with PMFS_ERR_STATE.  The call returns after the context's stream has been
+ * synchronised; pmfs_download and pmfs_pack_last do not apply to its result (it is in the caller's buffer).
  * The first call on a device looks up the array's address on that device; make that first call before any CUDA stream
  * capture begins.  All calls share the array: it keeps the previous call's contents (the call clears the two words
  * that must start at zero), and two calls whose GPU work overlaps -- different contexts or streams, same device --

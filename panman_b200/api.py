@@ -70,10 +70,12 @@ class SynthSpec:
     accessory_frac: float = 0.0
 
 
+BATCH_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int64)  # pmfs_batch_fn
+
 _lib = None
 
-EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_codes",
-           "pmfs_result_free", "pmfs_run_device", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
+EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_tile", "pmfs_set_watchdog", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_codes",
+           "pmfs_result_free", "pmfs_run_device", "pmfs_run_batched", "pmfs_set_batch_cols", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
 
@@ -92,6 +94,8 @@ def lib():
         L.pmfs_destroy.argtypes = [C.c_void_p]
         L.pmfs_destroy.restype = None
         L.pmfs_set_tuning.argtypes = [C.c_void_p, C.c_int32, C.c_int64]
+        L.pmfs_set_tile.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+        L.pmfs_set_watchdog.argtypes = [C.c_void_p, C.c_double]
         L.pmfs_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.pmfs_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
@@ -100,6 +104,9 @@ def lib():
         L.pmfs_result_free.argtypes = [C.c_void_p, C.c_void_p]
         L.pmfs_result_free.restype = None
         L.pmfs_run_device.argtypes = L.pmfs_run.argtypes
+        L.pmfs_run_batched.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
+                                       C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
+        L.pmfs_set_batch_cols.argtypes = [C.c_void_p, C.c_int64]
         L.pmfs_run_fitch_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
         L.pmfs_set_shard.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
@@ -177,9 +184,23 @@ class Context:
     def set_tuning(self, chunk_nodes: int = 0, tile_cols: int = 0):
         _check(self._L.pmfs_set_tuning(self._h, chunk_nodes, tile_cols))
 
-    def set_stream(self, cuda_stream: int = 0):
-        """Run on the given cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream); 0 = the context's own."""
-        _check(self._L.pmfs_set_stream(self._h, cuda_stream or None))
+    def set_tile(self, walking_warps: int = 0, groups_per_thread: int = 0):
+        """Column-tile shape of the work items (pmfs_set_tile); 0 = automatic."""
+        _check(self._L.pmfs_set_tile(self._h, walking_warps, groups_per_thread))
+
+    def set_watchdog(self, seconds: float):
+        _check(self._L.pmfs_set_watchdog(self._h, seconds))
+
+    def set_stream(self, cuda_stream=None):
+        """Run on the given cudaStream_t handle (e.g. torch.cuda.current_stream().cuda_stream); None = the context's own
+        stream.  Handle 0 is CUDA's legacy default stream -- what torch's default stream is -- and is passed on as
+        cudaStreamLegacy, NOT taken as "no stream": work queued by torch on its default stream and the library's work
+        must stay ordered with each other."""
+        if cuda_stream is None:
+            h = None
+        else:
+            h = int(cuda_stream) or 1  # cudaStreamLegacy == (cudaStream_t)0x1
+        _check(self._L.pmfs_set_stream(self._h, h))
 
     def run(self, algo: int, msa_nibbles: np.ndarray, n_cols: int, consensus: np.ndarray, forced=None,
             copy: bool = True) -> np.ndarray:
@@ -229,6 +250,25 @@ class Context:
         _check(self._L.pmfs_run_device(self._h, algo, d_msa, row_stride, n_rows, n_cols, d_cons, d_forced or None,
                                        C.byref(out), C.byref(n)))
         return out.value, n.value
+
+    def set_batch_cols(self, batch_cols: int = 0):
+        _check(self._L.pmfs_set_batch_cols(self._h, batch_cols))
+
+    def run_batched(self, algo: int, d_msa: int, row_stride: int, n_rows: int, n_cols: int, d_cons: int, d_forced: int = 0,
+                    batch_cols: int = 0, consumer=None):
+        """pmfs_run_batched: the pass in column batches.  consumer(col_begin, n_cols, device pointer, n_records) is called
+        after every batch (records on the device, (node,pos)-ordered, global positions; valid until it returns).
+        Returns (total records, number of batches)."""
+        total, nb = C.c_int64(), C.c_int32()
+        cb = None
+        if consumer is not None:
+            def _cb(_user, col_begin, ncols, ptr, n):
+                consumer(col_begin, ncols, ptr or 0, n)
+                return 0
+            cb = BATCH_FN(_cb)
+        _check(self._L.pmfs_run_batched(self._h, algo, d_msa, row_stride, n_rows, n_cols, d_cons, d_forced or None, batch_cols,
+                                        C.cast(cb, C.c_void_p) if cb is not None else None, None, C.byref(total), C.byref(nb)))
+        return total.value, nb.value
 
     def run_fitch_static(self, d_msa: int, row_stride: int, n_rows: int, n_cols: int, d_cons: int, d_forced: int,
                          d_out: int, out_capacity: int) -> int:

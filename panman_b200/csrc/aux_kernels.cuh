@@ -164,6 +164,7 @@ __global__ void compact_areas_kernel(const unsigned long long* __restrict__ src,
 // stats = {records, largest region count}: on overflow of a region or of `out` nothing is written (the host redoes it).
 __global__ void cells_total_kernel(const uint32_t* __restrict__ cnt, const uint32_t* __restrict__ prefix, int64_t cells,
                                    unsigned long long* __restrict__ stats) {
+    stats[3] = stats[0];  // record slots reserved (area_stats_kernel's sum: an upper bound that cannot wrap)
     stats[0] = (unsigned long long)prefix[cells - 1] + cnt[cells - 1];
 }
 __device__ __forceinline__ int kth_set_bit(uint32_t mask, uint32_t k) {  // position of the k-th (from 0) set bit
@@ -182,7 +183,7 @@ __global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, 
                                    const uint32_t* __restrict__ start, const uint32_t* __restrict__ prefix, int64_t cells, int32_t W,
                                    int pos_bits, const unsigned long long* __restrict__ stats, unsigned long long out_cap,
                                    pmfs_mut* __restrict__ out) {
-    if (stats[1] > cap || stats[0] > out_cap) return;
+    if (stats[1] > cap || stats[0] > out_cap || (stats[3] >> 32)) return;  // (32-bit prefix sums: see cells_total_kernel)
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int64_t stride = (((int64_t)gridDim.x * blockDim.x) >> 5) * 32;

@@ -1,11 +1,14 @@
 // libpmfs: context, pipeline and C ABI (include/pmfs.h) around the CUDA kernels (sm_100a).
 //
-// Device code lives in two headers included below:
-//   walk_kernels.cuh  fwd_kernel<ALGO,POLY>  bottom-up walk, ONE launch: persistent CTAs claim (chunk, column tile) items
-//                     bwd_kernel<ALGO>       top-down walk + mutation emission (warp-cooperative stream compaction)
-//   aux_kernels.cuh   prep_planes_kernel (codes -> bit-sliced planes), order_cells_kernel + helpers (ordering without a
-//                     sort), compact/assemble (radix path), pack_* (<=6-run packing), pack_chars_kernel, synth_* kernels
-// and run walk.cuh's interpreter (shared with the host emulation in tests/).
+// Device code:
+//   walk_kernels.cuh  fwd_kernel<CFG,ALGO,POLY>  bottom-up walk, ONE launch: persistent CTAs claim (chunk, column tile) items
+//                     bwd_kernel<CFG,ALGO>       top-down walk + mutation emission (warp-cooperative stream compaction)
+//                     templates on the tile shape CFG, instantiated once per shape in walk_inst_*.cu and reached from
+//                     here through walk_params.hpp's WalkKernelSet; they run walk.cuh's interpreter (shared with the
+//                     host emulation in tests/)
+//   aux_kernels.cuh   (included below) prep_planes_kernel (codes -> bit-sliced planes), order_cells_kernel + helpers
+//                     (ordering without a sort), compact/assemble (radix path), pack_* (<=6-run packing),
+//                     pack_chars_kernel, synth_* kernels
 // HBM layout: MSA rows of packed nibbles (16 B per thread per leaf); set arrays S (and D1 for Sankoff)
 // tile-major, i.e. one node's set for one column tile is one contiguous block of up to 16 KB (a single TMA copy).
 #include <cuda_runtime.h>
@@ -24,14 +27,13 @@
 #include "../../include/pmfs.h"
 #include "plan.hpp"
 #include "walk.cuh"
+#include "walk_params.hpp"
 
 namespace pmfs {
 
-constexpr int kTPB = 128;  // walking threads per CTA; each walks 2 column groups (kNG), so a CTA tile is 256 groups
-// A mutation record is ONE 64-bit word: sort key (node, column) in the high bits, payload in the low 10 bits
-// (type 2 bits, node state 4, parent state 4), so ordering the records is a keys-only radix sort over exactly the
-// key bits that can be set, and the multi-GPU exchange moves 8 bytes per record.
-constexpr int kPayloadBits = 10;
+// A mutation record is ONE 64-bit word: sort key (node, column) in the high bits, payload in the low kPayloadBits = 10
+// bits (type 2 bits, node state 4, parent state 4; walk_params.hpp), so ordering the records is a keys-only radix sort
+// over exactly the key bits that can be set, and the multi-GPU exchange moves 8 bytes per record.
 
 static thread_local std::string g_error;
 
@@ -46,8 +48,35 @@ static thread_local std::string g_error;
 
 }  // namespace pmfs
 
-#include "walk_kernels.cuh"
 #include "aux_kernels.cuh"
+
+// ---- tile shapes (walk_inst_*.cu: one translation unit per shape) ------------------------------------------------------
+namespace pmfs {
+const WalkKernelSet* walk_kernel_set_4x2();
+const WalkKernelSet* walk_kernel_set_2x2();
+const WalkKernelSet* walk_kernel_set_1x2();
+const WalkKernelSet* walk_kernel_set_4x1();
+const WalkKernelSet* walk_kernel_set_2x1();
+const WalkKernelSet* walk_kernel_set_1x1();
+const WalkKernelSet* walk_kernel_set_by_index(int i) {
+    switch (i) {
+        case 0: return walk_kernel_set_4x2();  // 256 column groups per work item
+        case 1: return walk_kernel_set_2x2();  // 128
+        case 2: return walk_kernel_set_4x1();  // 128, one group per thread
+        case 3: return walk_kernel_set_1x2();  // 64
+        case 4: return walk_kernel_set_2x1();  // 64, one group per thread
+        case 5: return walk_kernel_set_1x1();  // 32
+        default: return nullptr;
+    }
+}
+const WalkKernelSet* walk_kernel_set(int nw, int ng) {
+    for (int i = 0; i < kNumTileShapes; i++) {
+        const WalkKernelSet* s = walk_kernel_set_by_index(i);
+        if (s->shape.nw == nw && s->shape.ng == ng) return s;
+    }
+    return nullptr;
+}
+}  // namespace pmfs
 
 namespace pmfs {
 
@@ -94,6 +123,10 @@ struct pmfs_ctx {
     std::vector<int32_t> parent, child_off, child_idx, leaf_row;  // kept for re-planning and synth
     int32_t tune_chunk_nodes = 0;
     int64_t tune_tile_cols = 0;
+    int tune_nw = 0, tune_ng = 0;          // pmfs_set_tile: forced tile shape (0 = automatic)
+    const WalkKernelSet* ks = nullptr;     // tile shape of the current run
+    int32_t tree_height = 0;               // internal nodes on the longest root-to-leaf path
+    long long watchdog_ns = 10000000000ll; // device-side wait limit (pmfs_set_watchdog)
     cudaStream_t stream = nullptr;      // stream in use
     cudaStream_t own_stream = nullptr;  // created by pmfs_create
     cudaEvent_t ev[8] = {};
@@ -115,6 +148,8 @@ struct pmfs_ctx {
     };
     std::vector<Occ> occ_cache;
     float host_ms = 0;  // wall time of the last run_device_impl call
+    bool too_many_records = false;  // the last run failed only because one call may not produce that many records
+    int64_t tune_batch_cols = 0;    // pmfs_set_batch_cols
     // column-shard mode (pmfs_set_shard)
     int64_t shard_pos_offset = 0, shard_total_cols = 0;
     PartBounds parts = {};
@@ -148,6 +183,7 @@ struct pmfs_ctx {
     size_t h_pk_out_cap = 0, h_pk_off_cap = 0;
     pmfs_mut* h_out = nullptr;  // pinned
     size_t h_out_cap = 0;
+    std::vector<pmfs_mut> h_acc, h_big;  // pmfs_run in column batches: per-batch records, and the stitched result
     int64_t last_n_out = 0;
     pmfs_timing timing = {};
     // synth
@@ -241,11 +277,41 @@ static int replan(pmfs_ctx* c, int32_t chunk_nodes) {
 // the walk stack capped by the plan (plan.cpp: kMaxWalkStack, so that chunk size no longer costs resident CTAs) and child
 // chunks released per XCHILD, the fixed cost per item is what is left to amortise: measured on config 2 the step is flat
 // between 24 and 64 nodes (0.71-0.72 ms) and 4 % slower at 14 (sweeps in profiles/README.md).
-static int32_t auto_chunk_nodes(int32_t n_nodes, int64_t groups) {
-    int64_t ctas_per_chunk = (groups + kTileGroups - 1) / kTileGroups;
+static int32_t auto_chunk_nodes(int32_t n_nodes, int64_t groups, int tile_groups) {
+    int64_t ctas_per_chunk = (groups + tile_groups - 1) / tile_groups;
     int64_t want_chunks = std::max<int64_t>(1, (148 * 48 + ctas_per_chunk - 1) / ctas_per_chunk);
     int64_t cn = n_nodes / (want_chunks * 2);  // chunks end up between cn and 2*cn nodes
     return (int32_t)std::min<int64_t>(std::max<int64_t>(cn, 24), 1 << 16);
+}
+
+// Tile shape of a run over `groups` column groups (per memory tile).  Wide tiles amortise per-item and per-op
+// bookkeeping and are what BASELINE config 2 was tuned on; narrow ones are for (1) trees that offer no chunk-level
+// parallelism -- on a ladder the column tiles are the only independent work, so the narrowest tile gives the most
+// chains --, and (2) narrow column ranges (column shards of a wide tree, memory-limited column batches), where a wide
+// tile would idle most of its lanes.  PMFS_TILE_SHAPE=NWxNG (environment) and pmfs_set_tile override the choice.
+static const WalkKernelSet* choose_shape(const pmfs_ctx* c, int64_t groups) {
+    if (c->tune_nw > 0)
+        if (const WalkKernelSet* s = walk_kernel_set(c->tune_nw, c->tune_ng)) return s;
+    if (const char* e = getenv("PMFS_TILE_SHAPE")) {
+        int nw = 0, ng = 0;
+        if (sscanf(e, "%dx%d", &nw, &ng) == 2)
+            if (const WalkKernelSet* s = walk_kernel_set(nw, ng)) return s;
+    }
+    const int64_t I = c->plan.n_internal;
+    static const int wide_first[4][2] = {{4, 2}, {2, 2}, {1, 2}, {1, 1}};
+    if ((int64_t)c->tree_height * 4 > I) {  // ladder-like: tiles are the parallelism
+        for (auto& s : wide_first) {
+            const WalkKernelSet* k = walk_kernel_set(s[0], s[1]);
+            if ((groups + k->shape.groups() - 1) / k->shape.groups() >= 2 * 148) return k;
+        }
+        return walk_kernel_set(1, 1);
+    }
+    for (auto& s : wide_first) {  // widest shape that pads the column range by at most a tenth
+        const WalkKernelSet* k = walk_kernel_set(s[0], s[1]);
+        const int64_t w = k->shape.groups(), padded = (groups + w - 1) / w * w;
+        if (padded * 10 <= groups * 11) return k;
+    }
+    return walk_kernel_set(1, 1);
 }
 
 extern "C" {
@@ -294,10 +360,28 @@ int pmfs_create(pmfs_ctx** out, const pmfs_tree* tree, int device) {
         return PMFS_ERR_CUDA;
     }
     c->own_stream = c->stream;
-    for (auto& ev : c->ev) cudaEventCreate(&ev);
-    for (auto& ev : c->ev_slab) cudaEventCreate(&ev);
-    cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
-    int rc = replan(c, auto_chunk_nodes(V, 1024));
+    {
+        cudaError_t ce = cudaSuccess;
+        for (auto& ev : c->ev)
+            if (ce == cudaSuccess) ce = cudaEventCreate(&ev);
+        for (auto& ev : c->ev_slab)
+            if (ce == cudaSuccess) ce = cudaEventCreate(&ev);
+        if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+        if (ce != cudaSuccess) {
+            g_error = std::string("pmfs_create: event / stream creation: ") + cudaGetErrorString(ce);
+            pmfs_destroy(c);
+            return PMFS_ERR_CUDA;
+        }
+    }
+    {
+        std::vector<int32_t> depth((size_t)V, 0);  // internal nodes above a node, itself included
+        for (int32_t v = 0; v < V; v++) {
+            const bool internal = tree->child_off[v + 1] > tree->child_off[v];
+            depth[v] = (v == 0 ? 0 : depth[tree->parent[v]]) + (internal ? 1 : 0);
+            c->tree_height = std::max(c->tree_height, depth[v]);
+        }
+    }
+    int rc = replan(c, auto_chunk_nodes(V, 1024, 256));
     if (rc) {
         pmfs_destroy(c);
         return rc;
@@ -349,6 +433,25 @@ int pmfs_set_tuning(pmfs_ctx* c, int32_t chunk_nodes, int64_t tile_cols) {
     return PMFS_OK;
 }
 
+int pmfs_set_tile(pmfs_ctx* c, int32_t walking_warps, int32_t groups_per_thread) {
+    if (!c || (walking_warps != 0 && !walk_kernel_set(walking_warps, groups_per_thread))) {
+        g_error = "pmfs_set_tile: shapes are (walking warps x column groups per thread) 4x2, 2x2, 4x1, 1x2, 2x1, 1x1; 0 = automatic";
+        return PMFS_ERR_ARG;
+    }
+    c->tune_nw = walking_warps;
+    c->tune_ng = walking_warps ? groups_per_thread : 0;
+    return PMFS_OK;
+}
+
+int pmfs_set_watchdog(pmfs_ctx* c, double seconds) {
+    if (!c || seconds < 0) {
+        g_error = "pmfs_set_watchdog: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    c->watchdog_ns = (long long)(seconds * 1e9);
+    return PMFS_OK;
+}
+
 int pmfs_set_stream(pmfs_ctx* c, void* cuda_stream) {
     if (!c) return PMFS_ERR_ARG;
     c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
@@ -379,8 +482,8 @@ int pmfs_get_timing(pmfs_ctx* c, pmfs_timing* t) {
 
 // ---------------------------------------------------------------------------------------------------- the pipeline
 // ints of synchronisation scratch a pass needs for `groups` column groups: claim counters + per-(chunk,tile) counters
-static size_t sync_ints(const Plan& P, int64_t groups) {
-    return 64 + 2 * P.chunks.size() * (size_t)((groups + kTileGroups - 1) / kTileGroups);
+static size_t sync_ints(const Plan& P, int64_t groups, int tile_groups) {
+    return 64 + 2 * P.chunks.size() * (size_t)((groups + tile_groups - 1) / tile_groups);
 }
 
 // One launch per pass over all chunks (the name is historical: the first version launched once per chunk level).
@@ -398,8 +501,11 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     wp.items = fwd ? c->d_fwd_items.ptr : c->d_bwd_items.ptr;
     wp.chunk_parent = c->d_chunk_parent.ptr;
     wp.chunk_nchild = c->d_chunk_nchild.ptr;
-    wp.ctas_per_chunk = (int32_t)((wp.G + kTileGroups - 1) / kTileGroups);
+    const WalkKernelSet& ks = *c->ks;
+    const int tile_groups = ks.shape.groups(), threads = ks.shape.threads();
+    wp.ctas_per_chunk = (int32_t)((wp.G + tile_groups - 1) / tile_groups);
     wp.stack_depth = fwd ? P.fwd_stack_depth : P.bwd_stack_depth;
+    wp.spin_limit_ns = c->watchdog_ns;
     {
         static const int lead = getenv("PMFS_CLAIM_LEAD") ? atoi(getenv("PMFS_CLAIM_LEAD")) : 4;
         wp.claim_lead = lead;
@@ -414,20 +520,22 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     const size_t per_pass = (size_t)n_items;
     wp.next_item = sync + (fwd ? 0 : 32);
     wp.ready = sync + 64 + (fwd ? 0 : per_pass);
-    const size_t smem = fwd ? (size_t)SmemMap<kSetRingFwd>::kStack + (size_t)P.fwd_stack_depth * kNG * 4 * kTPB * sizeof(uint4)
-                            : (size_t)SmemMap<kSetRingBwd>::kStack + (size_t)P.bwd_stack_depth * kNG * 5 * kTPB * sizeof(uint32_t);
+    const size_t smem = fwd ? ks.fwd_smem_fixed + (size_t)P.fwd_stack_depth * ks.fwd_smem_per_level
+                            : ks.bwd_smem_fixed + (size_t)P.bwd_stack_depth * ks.bwd_smem_per_level;
     if (smem > 200 * 1024) {
         g_error = "walk stack does not fit in shared memory (tree too unbalanced for this chunk size)";
         return PMFS_ERR_ARG;
     }
-    const void* k = fwd ? (c->has_poly ? (const void*)fwd_kernel<ALGO, true> : (const void*)fwd_kernel<ALGO, false>)
-                        : (const void*)bwd_kernel<ALGO>;
-    if (smem > 40 * 1024) PMFS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const void* k = fwd ? ks.fwd[ALGO][c->has_poly ? 1 : 0] : ks.bwd[ALGO];
     int per_sm = 0;
     for (auto& e : c->occ_cache)
         if (e.k == k && e.smem == smem) per_sm = e.per_sm;
     if (per_sm == 0) {
-        PMFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kThreads, smem));
+        size_t allowed = 40 * 1024;  // the attribute is a maximum: only ever raise it
+        for (auto& e : c->occ_cache)
+            if (e.k == k) allowed = std::max(allowed, e.smem);
+        if (smem > allowed) PMFS_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PMFS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, threads, smem));
         if (per_sm < 1) per_sm = 1;
         c->occ_cache.push_back({k, smem, per_sm});
     }
@@ -436,39 +544,15 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     // claim counters and dependency counters of BOTH passes are cleared once, ahead of the bottom-up pass
     if (fwd && !sync_cleared) PMFS_CUDA(cudaMemsetAsync(sync, 0, (64 + 2 * per_pass) * sizeof(int), c->stream));
     void* args[] = {&wp};
-#ifdef PMFS_WAITPROF
-    {
-        unsigned long long z[16] = {0};
+    if (ks.prof_reset) {  // -DPMFS_WAITPROF builds only
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
-        PMFS_CUDA(cudaMemcpyToSymbol(g_waitprof, z, sizeof(z)));
-        PMFS_CUDA(cudaMemcpyToSymbol(g_trace_n, z, sizeof(unsigned int)));
+        ks.prof_reset();
     }
-#endif
-    PMFS_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kThreads), args, smem, c->stream));
-#ifdef PMFS_WAITPROF
-    {
-        unsigned long long z[16];
+    PMFS_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(threads), args, smem, c->stream));
+    if (ks.prof_dump) {
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
-        PMFS_CUDA(cudaMemcpyFromSymbol(z, g_waitprof, sizeof(z)));
-        const double W = (double)z[5], Pr = (double)z[10];
-        fprintf(stderr, "[waitprof %s grid %u per_sm %d items %d] walkers: desc %.1f%% prog %.1f%% leaf %.1f%% set %.1f%% barsync %.1f%% | "
-                "producer: dep %.1f%% desc_empty %.1f%% leaf_empty %.1f%% set_empty %.1f%% | walker warp-cycles %.3g\n",
-                fwd ? "fwd" : "bwd", grid, per_sm, wp.n_items, 100 * z[0] / W, 100 * z[1] / W, 100 * z[2] / W, 100 * z[3] / W, 100 * z[4] / W,
-                100 * z[6] / Pr, 100 * z[7] / Pr, 100 * z[8] / Pr, 100 * z[9] / Pr, W);
-        if (const char* dir = getenv("PMFS_TRACE_DIR")) {
-            unsigned int tn = 0;
-            PMFS_CUDA(cudaMemcpyFromSymbol(&tn, g_trace_n, sizeof(tn)));
-            tn = std::min<unsigned int>(tn, kTraceCap);
-            std::vector<ulonglong4> tr(tn);
-            if (tn) PMFS_CUDA(cudaMemcpyFromSymbol(tr.data(), g_trace, (size_t)tn * sizeof(ulonglong4)));
-            const std::string path = std::string(dir) + (fwd ? "/trace_fwd.bin" : "/trace_bwd.bin");
-            if (FILE* fp = fopen(path.c_str(), "wb")) {
-                fwrite(tr.data(), sizeof(ulonglong4), tn, fp);
-                fclose(fp);
-            }
-        }
+        ks.prof_dump(fwd, grid, per_sm, wp.n_items);
     }
-#endif
     (*launches)++;
     return PMFS_OK;
 }
@@ -479,6 +563,23 @@ static int launch_order_cells(pmfs_ctx* c, size_t region_cap, int64_t cells, int
     order_cells_kernel<<<grid, 256, 0, c->stream>>>(c->d_keys.ptr, region_cap, c->d_cell_count.ptr, c->d_cell_start.ptr, c->d_cell_prefix.ptr,
                                                     cells, (int32_t)W, pos_bits, d_stats, out_cap, c->d_out.ptr);
     PMFS_CUDA(cudaGetLastError());
+    return PMFS_OK;
+}
+
+// Column groups whose set arrays (S, and D1 for Sankoff) fit in the device memory that is free now (what the context
+// already holds for them counts as free), leaving `reserve_bytes` and 15 % aside for records, cells and the caller.
+static int mem_limited_groups(pmfs_ctx* c, int algo, int64_t G_all, size_t reserve_bytes, int64_t* groups) {
+    const int64_t I = c->plan.n_internal;
+    const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64;
+    const size_t need = (size_t)I * 4 * (size_t)G_all;
+    *groups = G_all;
+    if (reserve_bytes == 0 && c->d_S.cap >= need && (algo != PMFS_SANKOFF || c->d_D.cap >= need)) return PMFS_OK;
+    // (cudaMemGetInfo costs a fraction of a millisecond: only asked when buffers may have to grow)
+    size_t free_b = 0, total_b = 0;
+    PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);  // reusable
+    free_b = free_b > reserve_bytes ? free_b - reserve_bytes : 0;
+    *groups = std::min<int64_t>(G_all, std::max<int64_t>(1, (int64_t)(free_b * 0.85) / per_group));
     return PMFS_OK;
 }
 
@@ -501,30 +602,29 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         return PMFS_ERR_ARG;
     }
     PMFS_CUDA(cudaSetDevice(c->device));
+    c->too_many_records = false;
     const auto host_t0 = std::chrono::steady_clock::now();
     const Plan* P = &c->plan;
     const int64_t G_all = (n_cols + 31) / 32;
     const int64_t I = P->n_internal;
 
     // column tile so that the set arrays fit in HBM
-    const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64;
     int64_t tile_groups = G_all;
     auto set_elems = [&](int64_t groups) {  // uint4 elements of one tile-major set array for `groups` column groups
         return (size_t)I * 4 * (size_t)groups;
     };
-    const bool fits_already = c->d_S.cap >= set_elems(G_all) && (algo != PMFS_SANKOFF || c->d_D.cap >= set_elems(G_all));
-    if (!fits_already) {  // (cudaMemGetInfo costs a fraction of a millisecond: only ask when buffers have to grow)
-        size_t free_b = 0, total_b = 0;
-        PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
-        free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);  // reusable
-        tile_groups = std::max<int64_t>(1, (int64_t)(free_b * 0.85) / per_group);
+    {
+        int rc = mem_limited_groups(c, algo, G_all, 0, &tile_groups);
+        if (rc) return rc;
     }
     if (c->tune_tile_cols > 0) tile_groups = std::min<int64_t>(tile_groups, (c->tune_tile_cols + 31) / 32);
     tile_groups = std::min(tile_groups, G_all);
-    if (tile_groups < G_all) tile_groups = std::max<int64_t>(kTileGroups, tile_groups / kTileGroups * kTileGroups);
+    c->ks = choose_shape(c, tile_groups);
+    const int TG = c->ks->shape.groups();  // column groups per work item
+    if (tile_groups < G_all) tile_groups = std::max<int64_t>(TG, tile_groups / TG * TG);
     tile_groups = std::min(tile_groups, G_all);
 
-    const int32_t want_chunk = c->tune_chunk_nodes > 0 ? c->tune_chunk_nodes : auto_chunk_nodes(P->n_nodes, tile_groups);
+    const int32_t want_chunk = c->tune_chunk_nodes > 0 ? c->tune_chunk_nodes : auto_chunk_nodes(P->n_nodes, tile_groups, TG);
     if (want_chunk != c->chunk_nodes_used) {
         int rc = replan(c, want_chunk);
         if (rc) return rc;
@@ -551,7 +651,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     if (d_forced && (rc = c->d_forced_planes.ensure(tile_groups))) return rc;
     if ((rc = c->d_xcode.ensure((size_t)NC * tile_groups))) return rc;
     if ((rc = c->d_xvalid.ensure((size_t)NC * tile_groups))) return rc;
-    if ((rc = c->d_sync.ensure(sync_ints(*P, tile_groups)))) return rc;
+    if ((rc = c->d_sync.ensure(sync_ints(*P, tile_groups, TG)))) return rc;
     // output regions: per owning rank in shard mode, else one per 32 column groups (see DevEnv::emit)
     const int64_t W = (G_all + 31) / 32;
     const int n_parts = std::max(1, c->parts.n_parts);
@@ -653,7 +753,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
             const unsigned pg = (unsigned)((wp.G + 127) / 128);
             PMFS_CUDA(cudaEventRecord(c->ev[0], c->stream));
             {
-                const int64_t seg_items = (int64_t)P->chunks.size() * ((wp.G + kTileGroups - 1) / kTileGroups);
+                const int64_t seg_items = (int64_t)P->chunks.size() * ((wp.G + TG - 1) / TG);
                 prep_planes_kernel<<<pg, 128, 0, c->stream>>>(d_cons + wp.col_base, wp.tile_cols, wp.G, c->d_cons_planes.ptr,
                                                              (uint32_t*)c->d_sync.ptr, 64 + 2 * seg_items,
                                                              g0 == 0 ? (uint32_t*)c->d_count.ptr : nullptr,
@@ -701,7 +801,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                 // (the region counters include the unused ends of the warps' output blocks: the record count is the cells')
                 cells_total_kernel<<<1, 1, 0, c->stream>>>(c->d_cell_count.ptr, c->d_cell_prefix.ptr, cells, d_stats);
                 tm.n_launches++;
-                PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+                PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
                 ordered_cap = c->d_out.cap;
                 if (ordered_cap > 0) {
                     rc = launch_order_cells(c, region, cells, W, pos_bits, d_stats, ordered_cap);
@@ -727,6 +827,14 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         }
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
         const unsigned int err = (unsigned int)stats[2];
+        if (use_cells && stats[3] >> 32) {
+            // the cells' prefix sums are 32-bit: with 2^32 or more record slots reserved they could wrap (the ordering
+            // kernel has refused to run on the device for the same reason)
+            c->too_many_records = true;
+            g_error = "pmfs_run: too many records for one call (2^32 record slots reserved): run fewer columns per call -- "
+                      "pmfs_run_batched does that";
+            return PMFS_ERR_ARG;
+        }
         if (!multi) {
             cudaEventElapsedTime(&fwd_ms, c->ev[0], c->ev[1]);
             cudaEventElapsedTime(&bwd_ms, c->ev[1], c->ev[2]);
@@ -760,7 +868,8 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
 
     const int64_t n = (int64_t)count;
     if (n > 0x7fffffffll) {
-        g_error = "pmfs_run: more than 2^31 records in one call: run fewer columns per call";
+        c->too_many_records = true;
+        g_error = "pmfs_run: more than 2^31 records in one call: run fewer columns per call -- pmfs_run_batched does that";
         return PMFS_ERR_ARG;
     }
     if (c->parts.n_parts > 0) {
@@ -850,6 +959,98 @@ int pmfs_run_device(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
                     const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut** d_out, int64_t* n_out) {
     if (c) c->timing.h2d_ms = 0;
     return run_device_impl(c, algo, d_msa, row_stride, n_rows, n_cols, d_cons, d_forced, d_out, n_out);
+}
+
+int pmfs_set_batch_cols(pmfs_ctx* c, int64_t batch_cols) {
+    if (!c || batch_cols < 0) {
+        g_error = "pmfs_set_batch_cols: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    c->tune_batch_cols = batch_cols;
+    return PMFS_OK;
+}
+
+// Columns per batch: what the caller asked for, else as many as the set arrays of one batch fit in free device memory,
+// in equal batches whose size is a multiple of 32 column groups (whole output regions and tile shapes).
+static int batch_groups_for(pmfs_ctx* c, int algo, int64_t n_cols, int64_t batch_cols, size_t reserve_bytes, int64_t* out) {
+    const int64_t G_all = (n_cols + 31) / 32;
+    if (batch_cols <= 0) batch_cols = c->tune_batch_cols;
+    if (batch_cols > 0) {
+        *out = std::min(G_all, (batch_cols + 31) / 32);
+        return PMFS_OK;
+    }
+    int64_t gmax = 0;
+    int rc = mem_limited_groups(c, algo, G_all, reserve_bytes, &gmax);
+    if (rc) return rc;
+    // (a batch is ordered through 32-bit cell prefix sums and 2^30 cells at most: bound the cell matrix as well)
+    const int64_t max_regions = std::max<int64_t>(1, ((int64_t)1 << 30) / std::max(1, c->plan.n_nodes));
+    gmax = std::min(gmax, max_regions * 32);
+    if (gmax >= G_all) {
+        *out = G_all;
+        return PMFS_OK;
+    }
+    const int64_t n_b = (G_all + gmax - 1) / gmax;
+    int64_t gb = ((G_all + n_b - 1) / n_b + 31) / 32 * 32;
+    if (gb > gmax) gb = gmax >= 32 ? gmax / 32 * 32 : gmax;
+    *out = std::max<int64_t>(1, gb);
+    return PMFS_OK;
+}
+
+int pmfs_run_batched(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                     const uint8_t* d_cons, const uint8_t* d_forced, int64_t batch_cols, pmfs_batch_fn consumer, void* user,
+                     int64_t* n_total, int32_t* n_batches) {
+    if (!c || !d_msa || !d_cons || n_cols <= 0 || batch_cols < 0) {
+        g_error = "pmfs_run_batched: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    if (c->parts.n_parts > 0) {
+        g_error = "pmfs_run_batched: not available while pmfs_set_shard node ranges are set (use pmfs_comm_run)";
+        return PMFS_ERR_STATE;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    const bool fixed = batch_cols > 0 || c->tune_batch_cols > 0;
+    int64_t gb = 0;
+    int rc = batch_groups_for(c, algo, n_cols, batch_cols, 0, &gb);
+    if (rc) return rc;
+    const int64_t base_off = c->shard_total_cols > 0 ? c->shard_pos_offset : 0, base_total = c->shard_total_cols;
+    int64_t total = 0;
+    int32_t batches = 0;
+    pmfs_timing sum = {};
+    for (int64_t b0 = 0; b0 < n_cols;) {
+        const int64_t nb = std::min(n_cols - b0, gb * 32);
+        // a batch is a column shard that keeps its output: global positions, ordered by (node,pos) on its own
+        c->shard_pos_offset = base_off + b0;
+        c->shard_total_cols = base_total > 0 ? base_total : n_cols;
+        pmfs_mut* d_out = nullptr;
+        int64_t n = 0;
+        c->timing.h2d_ms = 0;
+        rc = run_device_impl(c, algo, d_msa + b0 / 2, row_stride, n_rows, nb, d_cons + b0, d_forced ? d_forced + b0 : nullptr, &d_out, &n);
+        c->shard_pos_offset = base_off;
+        c->shard_total_cols = base_total;
+        if (rc == PMFS_ERR_ARG && c->too_many_records && !fixed && gb > 32) {
+            gb = std::max<int64_t>(32, gb / 2 / 32 * 32);  // automatic batch size: halve it and run this batch again
+            continue;
+        }
+        if (rc) return rc;
+        const pmfs_timing& t = c->timing;
+        sum.forward_ms += t.forward_ms; sum.backward_ms += t.backward_ms; sum.sort_ms += t.sort_ms; sum.total_ms += t.total_ms;
+        sum.wall_ms += t.wall_ms; sum.n_launches += t.n_launches; sum.forward_bytes += t.forward_bytes;
+        sum.backward_bytes += t.backward_bytes;
+        if (consumer) {
+            const int crc = consumer(user, base_off + b0, nb, d_out, n);
+            if (crc != 0) {
+                g_error = "pmfs_run_batched: the consumer returned " + std::to_string(crc);
+                return PMFS_ERR_STATE;
+            }
+        }
+        total += n;
+        batches++;
+        b0 += nb;
+    }
+    c->timing = sum;
+    if (n_total) *n_total = total;
+    if (n_batches) *n_batches = batches;
+    return PMFS_OK;
 }
 
 int pmfs_set_shard(pmfs_ctx* c, int64_t pos_offset, int64_t total_cols, int32_t n_parts, const int32_t* node_bounds) {
@@ -994,13 +1195,9 @@ int pmfs_download(pmfs_ctx* c, pmfs_mut* host_out, int64_t n) {
     return PMFS_OK;
 }
 
-int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
-             const uint8_t* cons, const uint8_t* forced, pmfs_mut** out, int64_t* n_out) {
-    if (!c || !msa || !cons || !out || !n_out || n_cols <= 0 || n_rows < 0 || row_stride * 2 < n_cols) {
-        g_error = "pmfs_run: bad argument";
-        return PMFS_ERR_ARG;
-    }
-    PMFS_CUDA(cudaSetDevice(c->device));
+// pmfs_run when the whole alignment fits on the device next to (tiles of) its set arrays: one upload, one pass.
+static int run_host_whole(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                          const uint8_t* cons, const uint8_t* forced, pmfs_mut** out, int64_t* n_out) {
     const int64_t dstride = ((n_cols + 31) / 32) * 16;
     int rc;
     if ((rc = c->d_msa.ensure((size_t)std::max<int64_t>(1, n_rows) * dstride))) return rc;
@@ -1009,11 +1206,12 @@ int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int3
     const int64_t used = (n_cols + 1) / 2;
     // Wide alignments go up in two column slabs on a copy stream and the passes of the first slab (all column tiles but
     // the last) run while the second is still on the bus: only the last tile's passes are left after the upload.
-    const int64_t G_all = (n_cols + 31) / 32, tiles = (G_all + kTileGroups - 1) / kTileGroups;
+    constexpr int64_t kSlabGroups = 256;  // slab boundary granularity (a multiple of every tile shape and of an output region)
+    const int64_t G_all = (n_cols + 31) / 32, tiles = (G_all + kSlabGroups - 1) / kSlabGroups;
     const bool slabs = n_rows > 0 && tiles >= 2 && (size_t)n_rows * (size_t)used >= ((size_t)32 << 20);
     pmfs_mut* d_out = nullptr;
     if (slabs) {
-        const int64_t split = (tiles - 1) * kTileGroups;  // column groups in slab 0
+        const int64_t split = (tiles - 1) * kSlabGroups;  // column groups in slab 0
         const size_t w0 = (size_t)split * 16, w1 = (size_t)(row_stride >= dstride ? dstride : used) - w0;
         cudaStream_t cs = c->copy_stream;
         PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));  // whatever the caller's stream still does with these buffers
@@ -1075,6 +1273,138 @@ int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int3
     c->timing.total_ms += c->timing.d2h_ms;
     *out = h;
     return PMFS_OK;
+}
+
+// pmfs_run when it does not: the alignment goes through the GPU in column batches, batch b+1 on the bus while batch b is
+// in the passes (two device buffers), every batch's ordered records come back to the host and are stitched into one
+// (node,pos)-ordered array at the end -- a node's list is the concatenation of its slices in batch order.  The
+// reference's --low-mem-mode has the same shape (src/panman.cpp:1503-1514: read 20 000 columns, process, append).
+static int run_host_streaming(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                              const uint8_t* cons, const uint8_t* forced, pmfs_mut** out, int64_t* n_out) {
+    const int64_t G_all = (n_cols + 31) / 32, used = (n_cols + 1) / 2;
+    int rc;
+    if ((rc = c->d_cons.ensure((size_t)n_cols))) return rc;
+    if (forced && (rc = c->d_forced.ensure((size_t)n_cols))) return rc;
+    c->d_msa.release();  // sized per batch below; what it held counts as free memory
+    int64_t gb = 0;
+    if (c->tune_batch_cols > 0) {
+        gb = std::min(G_all, (c->tune_batch_cols + 31) / 32);
+    } else {
+        // a column group costs its share of the set arrays plus two staged MSA segments of 16 B per row
+        size_t free_b = 0, total_b = 0;
+        PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);
+        const int64_t per_group = (int64_t)c->plan.n_internal * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64 + 2 * 16 * (int64_t)n_rows;
+        int64_t gmax = std::max<int64_t>(1, (int64_t)(free_b * 0.8) / per_group);
+        const int64_t max_regions = std::max<int64_t>(1, ((int64_t)1 << 30) / std::max(1, c->plan.n_nodes));
+        gmax = std::min(gmax, max_regions * 32);
+        const int64_t n_b = (G_all + gmax - 1) / gmax;
+        gb = ((G_all + n_b - 1) / n_b + 31) / 32 * 32;
+        if (gb > gmax) gb = gmax >= 32 ? gmax / 32 * 32 : gmax;
+        gb = std::min(G_all, std::max<int64_t>(1, gb));
+    }
+    const int64_t bstride = gb * 16;  // device row stride of a staged batch
+    if ((rc = c->d_msa.ensure((size_t)2 * (size_t)std::max<int32_t>(1, n_rows) * (size_t)bstride))) return rc;
+    uint8_t* const buf[2] = {c->d_msa.ptr, c->d_msa.ptr + (size_t)std::max<int32_t>(1, n_rows) * (size_t)bstride};
+    cudaStream_t cs = c->copy_stream;
+    PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));  // whatever the caller's stream still does with these buffers
+    PMFS_CUDA(cudaStreamWaitEvent(cs, c->ev[6], 0));
+    PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons, (size_t)n_cols, cudaMemcpyHostToDevice, cs));
+    if (forced) PMFS_CUDA(cudaMemcpyAsync(c->d_forced.ptr, forced, (size_t)n_cols, cudaMemcpyHostToDevice, cs));
+    const int64_t n_batches = (G_all + gb - 1) / gb;
+    auto upload = [&](int64_t b) -> int {
+        const int64_t g0 = b * gb, w = std::min<int64_t>(bstride, used - g0 * 16);  // bytes of a host row in this batch
+        if (n_rows == 0) return PMFS_OK;
+        if (w < bstride) PMFS_CUDA(cudaMemsetAsync(buf[b & 1], 0, (size_t)n_rows * bstride, cs));
+        PMFS_CUDA(cudaMemcpy2DAsync(buf[b & 1], (size_t)bstride, msa + g0 * 16, (size_t)row_stride, (size_t)w, (size_t)n_rows,
+                                    cudaMemcpyHostToDevice, cs));
+        return PMFS_OK;
+    };
+    std::vector<pmfs_mut>& acc = c->h_acc;
+    std::vector<int64_t> batch_end;
+    acc.clear();
+    const int64_t base_off = c->shard_total_cols > 0 ? c->shard_pos_offset : 0, base_total = c->shard_total_cols;
+    pmfs_timing sum = {};
+    const auto t0 = std::chrono::steady_clock::now();
+    if ((rc = upload(0))) return rc;
+    PMFS_CUDA(cudaEventRecord(c->ev_slab[0], cs));
+    for (int64_t b = 0; b < n_batches; b++) {
+        if (b + 1 < n_batches) {  // (its buffer is free: batch b-1 has been through the passes and its records are on the host)
+            if ((rc = upload(b + 1))) return rc;
+            PMFS_CUDA(cudaEventRecord(c->ev_slab[(b + 1) & 1], cs));
+        }
+        PMFS_CUDA(cudaStreamWaitEvent(c->stream, c->ev_slab[b & 1], 0));
+        const int64_t g0 = b * gb, nb = std::min(n_cols - g0 * 32, gb * 32);
+        c->shard_pos_offset = base_off + g0 * 32;
+        c->shard_total_cols = base_total > 0 ? base_total : n_cols;
+        pmfs_mut* d_out = nullptr;
+        int64_t n = 0;
+        c->timing.h2d_ms = 0;
+        rc = run_device_impl(c, algo, buf[b & 1], bstride, n_rows, nb, c->d_cons.ptr + g0 * 32, forced ? c->d_forced.ptr + g0 * 32 : nullptr,
+                             &d_out, &n);
+        c->shard_pos_offset = base_off;
+        c->shard_total_cols = base_total;
+        if (rc) {
+            cudaStreamSynchronize(cs);
+            return rc;
+        }
+        const size_t at = acc.size();
+        acc.resize(at + (size_t)n);
+        if (n > 0) PMFS_CUDA(cudaMemcpyAsync(acc.data() + at, d_out, (size_t)n * sizeof(pmfs_mut), cudaMemcpyDeviceToHost, c->stream));
+        PMFS_CUDA(cudaStreamSynchronize(c->stream));
+        batch_end.push_back((int64_t)acc.size());
+        const pmfs_timing& t = c->timing;
+        sum.forward_ms += t.forward_ms; sum.backward_ms += t.backward_ms; sum.sort_ms += t.sort_ms;
+        sum.n_launches += t.n_launches; sum.forward_bytes += t.forward_bytes; sum.backward_bytes += t.backward_bytes;
+    }
+    // stitch by node: count per node, prefix, then the batches in order (each is sorted by (node,pos))
+    const size_t V = (size_t)c->plan.n_nodes, total = acc.size();
+    std::vector<pmfs_mut>& res = c->h_big;
+    if (n_batches == 1) {
+        res.swap(acc);
+    } else {
+        std::vector<int64_t> at(V + 1, 0);
+        for (size_t i = 0; i < total; i++) at[(size_t)acc[i].node + 1]++;
+        for (size_t v = 0; v < V; v++) at[v + 1] += at[v];
+        res.resize(total);
+        for (size_t i = 0; i < total; i++) res[(size_t)at[(size_t)acc[i].node]++] = acc[i];
+        std::vector<pmfs_mut>().swap(acc);
+    }
+    sum.wall_ms = sum.total_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    c->timing = sum;
+    c->last_n_out = 0;  // the device only holds the last batch: pmfs_download / pmfs_pack_last do not apply
+    *out = res.data();
+    *n_out = (int64_t)total;
+    return PMFS_OK;
+}
+
+int pmfs_run(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+             const uint8_t* cons, const uint8_t* forced, pmfs_mut** out, int64_t* n_out) {
+    if (!c || !msa || !cons || !out || !n_out || n_cols <= 0 || n_rows < 0 || row_stride * 2 < n_cols ||
+        (algo != PMFS_FITCH && algo != PMFS_SANKOFF)) {
+        g_error = "pmfs_run: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    if ((int64_t)c->plan.row_to_node.size() > (int64_t)n_rows) {
+        g_error = "pmfs_run: a leaf refers to an MSA row >= n_rows";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    bool streaming = c->tune_batch_cols > 0 && c->tune_batch_cols < n_cols;
+    if (!streaming && c->parts.n_parts == 0) {
+        // whole upload unless the nibbles alone would take more than half of what is free (what the context holds counts)
+        const size_t need = (size_t)std::max<int32_t>(1, n_rows) * (size_t)(((n_cols + 31) / 32) * 16);
+        if (need > c->d_msa.cap) {
+            size_t free_b = 0, total_b = 0;
+            PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
+            streaming = need > (free_b + c->d_msa.cap) / 2;
+        }
+    }
+    if (!streaming) {
+        const int rc = run_host_whole(c, algo, msa, row_stride, n_rows, n_cols, cons, forced, out, n_out);
+        if (!(rc == PMFS_ERR_ARG && c->too_many_records && c->parts.n_parts == 0)) return rc;
+    }
+    return run_host_streaming(c, algo, msa, row_stride, n_rows, n_cols, cons, forced, out, n_out);
 }
 
 static uint8_t host_code_of_char(char ch) {  // src/panman.cpp:83-118
@@ -1154,6 +1484,10 @@ static int run_bytes(pmfs_ctx* c, int algo, bool raw, const char* msa_chars, int
 void pmfs_result_free(pmfs_ctx* c, pmfs_mut* out) {
     // results live in the context's pinned buffer, which is reused by the next pmfs_run and released by pmfs_destroy;
     // releasing early only matters for very large results
+    if (c && out && out == c->h_big.data()) {
+        std::vector<pmfs_mut>().swap(c->h_big);
+        return;
+    }
     if (!c || !out || out != c->h_out) return;
     if (c->h_out_cap > ((size_t)64 << 20) / sizeof(pmfs_mut)) {
         cudaFreeHost(c->h_out);
@@ -1224,7 +1558,8 @@ int pmfs_synth_msa(pmfs_ctx* c, const pmfs_synth_spec* spec, int64_t col_begin, 
         if ((rc = c->d_synth_state[0].ensure((size_t)c->synth_max_slots * s.words))) return rc;
         if ((rc = c->d_synth_state[1].ensure((size_t)c->synth_max_slots * s.words))) return rc;
     }
-    PMFS_CUDA(cudaMemsetAsync(d_msa, 0, (size_t)n_rows * row_stride, c->stream));
+    // (only this column window of the rows: the caller may be filling a wider alignment window by window)
+    PMFS_CUDA(cudaMemset2DAsync(d_msa, (size_t)row_stride, 0, (size_t)s.words * 4, (size_t)n_rows, c->stream));
     for (size_t d = 0; d + 1 < c->synth_lvl_off.size(); d++) {
         const int64_t b0 = c->synth_lvl_off[d], e0 = c->synth_lvl_off[d + 1];
         s.node = c->d_synth_node.ptr + b0;
@@ -1240,6 +1575,10 @@ int pmfs_synth_msa(pmfs_ctx* c, const pmfs_synth_spec* spec, int64_t col_begin, 
     if (d_cons) synth_consensus_kernel<<<(unsigned)((n_cols + 255) / 256), 256, 0, c->stream>>>(d_msa, row_stride, n_rows, n_cols, d_cons);
     PMFS_CUDA(cudaGetLastError());
     PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->d_synth_state[0].cap * sizeof(uint32_t) > ((size_t)256 << 20)) {  // big trees: do not sit on gigabytes of scratch
+        c->d_synth_state[0].release();
+        c->d_synth_state[1].release();
+    }
     return PMFS_OK;
 }
 
@@ -1319,7 +1658,12 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
         g_error = "pmfs_run_fitch_static: a leaf refers to an MSA row >= n_rows";
         return PMFS_ERR_ARG;
     }
+    if (c->parts.n_parts > 0 || c->shard_total_cols > 0) {
+        g_error = "pmfs_run_fitch_static: not available on a context in column-shard mode (pmfs_set_shard)";
+        return PMFS_ERR_STATE;
+    }
     *n_out = 0;
+    c->last_n_out = 0;  // the result goes to the caller's buffer: pmfs_download / pmfs_pack_last have nothing to work on
     unsigned char* scratch = nullptr;
     int rc = static_scratch_on(c->device, &scratch);  // first call on a device: resolves the array's address there
     if (rc) return rc;
@@ -1355,7 +1699,8 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     unsigned long long* keys = cv.take<unsigned long long>(cap);
     unsigned long long* keys_alt = cv.take<unsigned long long>(cap);
     uint8_t* tmp = cv.take<uint8_t>(sort_tmp);
-    int* sync = cv.take<int>(sync_ints(P, G));
+    c->ks = choose_shape(c, G);
+    int* sync = cv.take<int>(sync_ints(P, G, c->ks->shape.groups()));
     if (cv.used > kStaticScratchBytes) {
         g_error = "pmfs_run_fitch_static: this problem needs " + std::to_string(cv.used) + " bytes of scratch (" +
                   std::to_string(I) + " internal nodes x " + std::to_string(G) + " column groups x 64 B, plus 16 B per record "

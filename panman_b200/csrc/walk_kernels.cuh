@@ -1,55 +1,17 @@
 // libpmfs device code, part 1: the two walk kernels and everything they are made of -- work-item scheduling, the producer
 // warp with its TMA rings, the per-thread view of an item (DevEnv) that walk.cuh's interpreter runs on, emission.
-// Included by pmfs.cu only (after its constants, WalkParams comes first here).
+// Everything is a template on the tile shape CFG (walk_params.hpp: TileShape); one translation unit per shape
+// (walk_inst.cuh) instantiates the kernels.
 #pragma once
 
-namespace pmfs {
+#include <cuda_runtime.h>
 
-// ------------------------------------------------------------------------------------------------ device environment
-struct WalkParams {
-    const uint32_t* prog;       // fwd or bwd program words
-    const int64_t* chunk_off;   // [NC] offset of each chunk's program
-    const int32_t* chunk_len;   // [NC]
-    const int32_t* order;       // chunk ids in execution order of this pass
-    const int4* items;          // [2*NC] per chunk IN EXECUTION ORDER: {chunk, parent, plen, slen}, {prog_off/4, stream_off, need, dep chunk}
-    const int32_t* chunk_parent;  // [NC] parent chunk, -1 for the chunk that holds the tree root
-    const int32_t* chunk_nchild;  // [NC] number of child chunks
-    int* ready;                 // [NC][ctas_per_chunk] dependency counters of this pass (zeroed before the launch)
-    int* next_item;             // work-item claim counter of this pass (zeroed before the launch)
-    int32_t n_items;
-    const uint32_t* stream;     // load streams (plan.hpp)
-    const int64_t* stream_off;  // [NC]
-    const int32_t* stream_len;  // [NC]
-    int32_t ctas_per_chunk;
-    int32_t stack_depth;
-    int32_t claim_lead;         // stream entries before the end of an item at which the producer claims the next one
-    const uint4* msa;           // first group of this column tile
-    int64_t msa_stride16;       // uint4 per MSA row
-    uint4* S;                   // [I][4][G]
-    uint4* D;                   // Sankoff only
-    int64_t G;                  // column groups in this tile
-    int64_t tile_cols;          // real columns in this tile
-    int64_t col_base;           // global column of the tile's first column
-    const uint4* cons_planes;   // [G]
-    const uint4* forced_planes; // [G] or null
-    uint4* xcode;               // [NC][G] parent state per chunk root
-    uint32_t* xvalid;           // [NC][G]
-    const int32_t* int_to_node;
-    const int32_t* row_to_node;
-    unsigned long long* out_keys;   // [n_owners][out_cap] packed records (see kPayloadBits)
-    unsigned long long* out_count;  // [n_owners]
-    unsigned long long out_cap;     // capacity of one owner's region
-    int32_t n_regions;              // > 0: one output region per 32 column groups (see emit); 0: regions per owner
-    uint32_t bucket_mask;           // single-GPU runs: regions are further split by (node & bucket_mask), bucket-major
-    uint32_t* cell_count;           // [n_nodes][n_regions] or null: records of (node, region) -- see order_cells_kernel
-    uint32_t* cell_start;           // [n_nodes][n_regions]: where they start inside the region
-    int64_t region_base;            // region index of this column tile's first 32 groups
-    int32_t n_owners;               // 1, or the number of ranks in column-shard mode
-    int32_t owner_bound[17];        // nodes [owner_bound[r], owner_bound[r+1]) are owned by rank r
-    unsigned int* err_flag;
-    int64_t pos_offset;         // global column of this context's first column (column shards); 0 otherwise
-    int pos_bits;               // record = ((node << pos_bits | column) << kPayloadBits) | payload
-};
+#include "../../include/pmfs.h"
+#include "plan.hpp"
+#include "walk.cuh"
+#include "walk_params.hpp"
+
+namespace pmfs {
 
 // 64-word sliding window over a word array that every lane of the warp reads at the same, never decreasing index
 // (load streams): lane l holds words base+l and base+32+l in two registers, a read is one shuffle, and the next 32
@@ -74,13 +36,20 @@ struct WarpWords {
     }
 };
 
-constexpr int kNG = 2;                    // column groups per walking thread (walk.cuh: Env::kGroups)
-constexpr int kTileGroups = kTPB * kNG;   // column groups per work item (256 groups = 8 192 columns)
-constexpr int kThreads = kTPB + 32;       // 4 walking warps + 1 producer warp
-// Operand rings of a CTA, per pass: leaf-row units in flight (4 KB each: 16 B for each group of the tile) and set slots in
-// flight (16 KB each: 64 B for each group).  One int encodes both (leaf * 16 + sets) so that it can be a template argument.
-// Bottom-up: mostly leaves, and its 32 KB walk stack + 128 registers cap it at 3 CTAs per SM anyway.  Top-down: every
-// internal node is one set; 2 + 2 keeps a CTA under 57 KB, which lets 4 CTAs share an SM (measured: 0.41 -> 0.36 ms).
+// Tile shape as a type: NW walking warps + 1 producer warp per CTA, NG column groups per walking thread.
+template <int NW_, int NG_>
+struct TileCfg {
+    static constexpr int NW = NW_, NG = NG_;
+    static constexpr int TPB = 32 * NW_;          // walking threads per CTA
+    static constexpr int Groups = TPB * NG_;      // column groups per work item (x 32 columns)
+    static constexpr int Threads = TPB + 32;      // + the producer warp
+    static constexpr int UnitBytes = Groups * 16; // one MSA row segment of the tile
+    static constexpr int SetBytes = Groups * 64;  // one node's set for the tile
+};
+// Operand rings of a CTA, per pass: leaf-row units in flight (16 B for each group of the tile) and set slots in flight
+// (64 B for each group).  One int encodes both (leaf * 16 + sets) so that it can be a template argument.
+// Bottom-up: mostly leaves, and its walk stack + 128 registers cap the resident CTAs anyway.  Top-down: every
+// internal node is one set; 2 + 2 keeps a 256-group CTA under 57 KB, which lets 4 CTAs share an SM (0.41 -> 0.36 ms).
 #ifndef PMFS_RING_FWD
 #define PMFS_RING_FWD (4 * 16 + 1)
 #define PMFS_RING_BWD (2 * 16 + 2)
@@ -88,8 +57,6 @@ constexpr int kThreads = kTPB + 32;       // 4 walking warps + 1 producer warp
 constexpr int kSetRingFwd = PMFS_RING_FWD;
 constexpr int kSetRingBwd = PMFS_RING_BWD;
 constexpr int kProgWords = 256;           // walk programs up to this many words are staged in shared memory
-constexpr int kUnitBytes = kTileGroups * 16;
-constexpr int kSetBytes = kTileGroups * 64;
 
 // ---- mbarrier / bulk-copy (TMA) primitives, sm_90+ PTX ------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -129,20 +96,25 @@ __device__ __forceinline__ bool mbar_try_park(uint32_t bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// A wait that can never be satisfied (a bug in the producer/consumer bookkeeping) must not hang the GPU: after about
-// ten seconds of spinning the kernel traps and the host sees a CUDA error.
-constexpr long long kSpinLimitCycles = 20000000000ll;  // ~10 s
-__device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
-    const long long t0 = clock64();
-    for (uint32_t it = 1; !mbar_try_park(bar, parity); it++)
-        if ((it & 255u) == 0 && clock64() - t0 > kSpinLimitCycles) __trap();
+// A wait that can never be satisfied (a bug in the producer/consumer bookkeeping) must not hang the GPU: after
+// WalkParams::spin_limit_ns of waiting (wall clock of the GPU, %globaltimer; default 10 s, pmfs_set_watchdog; 0 = wait
+// forever, e.g. under a debugger or on a time-sliced GPU) the kernel traps and the host reports a watchdog error.
+__device__ __forceinline__ long long timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return (long long)t;
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity);
+static __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity, long long limit_ns) {
+    const long long t0 = timer_ns();
+    for (uint32_t it = 1; !mbar_try_park(bar, parity); it++)
+        if ((it & 255u) == 0 && limit_ns > 0 && timer_ns() - t0 > limit_ns) __trap();
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, long long limit_ns) {
+    if (!mbar_try(bar, parity)) mbar_wait_slow(bar, parity, limit_ns);
 }
 // -DPMFS_WAITPROF (never in the shipped library): cycles spent per wait kind, summed over warps, printed per launch
 #ifdef PMFS_WAITPROF
-__device__ unsigned long long g_waitprof[16];
+static __device__ unsigned long long g_waitprof[16];  // (per translation unit = per tile shape)
 __device__ __forceinline__ long long wp_now() { return clock64(); }
 __device__ __forceinline__ void wp_add(int k, long long t0) {
     if ((threadIdx.x & 31) == 0) atomicAdd(&g_waitprof[k], (unsigned long long)(clock64() - t0));
@@ -160,8 +132,8 @@ struct WaitProf {
 #endif
 // per-item timeline: {start ns, end ns, chunk, tile | smid << 16}
 constexpr int kTraceCap = 1 << 17;
-__device__ ulonglong4 g_trace[kTraceCap];
-__device__ unsigned int g_trace_n;
+static __device__ ulonglong4 g_trace[kTraceCap];
+static __device__ unsigned int g_trace_n;
 __device__ __forceinline__ unsigned long long trace_now() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -205,21 +177,22 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 // quarter-sets of all 256 groups, a single contiguous copy).  Per ring entry: `full` flips when its bytes have
 // landed, `empty` when all 4 walking warps have read it.  Entry numbers keep counting across the work items of a
 // persistent CTA, so phases never need resetting.
-template <int RING>
+template <class CFG, int RING>
 struct SmemMap {
     static constexpr int kLeafRing = RING >> 4, SETS = RING & 15;
     static constexpr int kProg = 0;                                 // 2 staged programs
     static constexpr int kDesc = 2 * kProgWords * 4;                // 2 item descriptors (16 B each, 64 B reserved)
     static constexpr int kLeaf = kDesc + 64;                        // leaf ring
-    static constexpr int kSet = kLeaf + kLeafRing * kUnitBytes;     // set ring
-    static constexpr int kStack = kSet + SETS * kSetBytes;          // walk stack (dynamic size)
+    static constexpr int kSet = kLeaf + kLeafRing * CFG::UnitBytes;     // set ring
+    static constexpr int kStack = kSet + SETS * CFG::SetBytes;          // walk stack (dynamic size)
     // barriers (static shared array), 8 bytes each
     static constexpr int bLeafFull = 0, bLeafEmpty = kLeafRing, bSetFull = 2 * kLeafRing, bSetEmpty = 2 * kLeafRing + SETS,
                          bProg = 2 * kLeafRing + 2 * SETS, bDescFull = bProg + 2, bDescEmpty = bProg + 4, kBars = bProg + 6;
 };
 struct Ring {
-    uint32_t smem;  // shared address of the dynamic shared memory
-    uint32_t bars;  // shared address of the barrier array
+    uint32_t smem;       // shared address of the dynamic shared memory
+    uint32_t bars;       // shared address of the barrier array
+    long long limit_ns;  // watchdog of every wait (WalkParams::spin_limit_ns)
 };
 
 // What the producer tells the walkers about a work item (one int4 in shared memory).
@@ -267,15 +240,15 @@ struct NextItem {
         fetched = true;
     }
 };
-template <int RING>
+template <class CFG, int RING>
 __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, NextItem& h, bool block) {
-    using M = SmemMap<RING>;
+    using M = SmemMap<CFG, RING>;
     const uint32_t slot = h.ordinal & 1u, phase = (h.ordinal >> 1) & 1u;
     if (!h.slot_free) {  // the walkers are done with the item two before this one
         const uint32_t bar = r.bars + (M::bDescEmpty + slot) * 8;
         if (block) {
             PMFS_WP(7);
-            mbar_wait(bar, phase ^ 1u);
+            mbar_wait(bar, phase ^ 1u, r.limit_ns);
         } else if (!mbar_test(bar, phase ^ 1u)) {
             return;
         }
@@ -293,10 +266,10 @@ __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, 
         if (*f < h.b.z) {
             if (!block) return;
             PMFS_WP(6);
-            const long long t0 = clock64();
+            const long long t0 = timer_ns();
             while (*f < h.b.z) {
                 __nanosleep(32);
-                if (clock64() - t0 > kSpinLimitCycles) __trap();
+                if (r.limit_ns > 0 && timer_ns() - t0 > r.limit_ns) __trap();
             }
         }
         __threadfence();
@@ -312,23 +285,23 @@ __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, 
 
 // Producer side of one item: walk the chunk's load stream and keep both rings full.  Called by the whole producer warp
 // (the stream words are read warp-wide); lane 0 drives TMA and, in passing, the header of the next item.
-template <int RING>
+template <class CFG, int RING>
 __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& r, WarpWords& w, int32_t slen, int tile,
                                                uint32_t& n_leaf, uint32_t& n_set, NextItem& h) {
-    using M = SmemMap<RING>;
+    using M = SmemMap<CFG, RING>;
     const int lane = threadIdx.x & 31;
-    const int64_t g0 = (int64_t)tile * kTileGroups;
-    const uint32_t leaf_bytes = (uint32_t)min((int64_t)kTileGroups, p.G - g0) * 16u;
+    const int64_t g0 = (int64_t)tile * CFG::Groups;
+    const uint32_t leaf_bytes = (uint32_t)min((int64_t)CFG::Groups, p.G - g0) * 16u;
     for (int32_t j = 0; j < slen; j++) {
         const uint32_t e = w.get(j, lane);
         if (e & kStreamSet) {
             if (lane == 0) {
                 const uint32_t u = n_set % M::SETS, par = (n_set / M::SETS) & 1u;
                 PMFS_WP(9);
-                mbar_wait(r.bars + (M::bSetEmpty + u) * 8, par ^ 1u);  // all walkers are done with the slot's previous set
+                mbar_wait(r.bars + (M::bSetEmpty + u) * 8, par ^ 1u, r.limit_ns);  // all walkers are done with the slot's previous set
                 // one node's set for this tile: 4 quarters of `tile_w` groups, contiguous (leaf_bytes = tile_w * 16)
                 mbar_arrive_expect_tx(r.bars + (M::bSetFull + u) * 8, 4 * leaf_bytes);
-                bulk_g2s(r.smem + M::kSet + u * kSetBytes, p.S + (int64_t)(e & ~kStreamSet) * (4 * p.G) + g0 * 4, 4 * leaf_bytes,
+                bulk_g2s(r.smem + M::kSet + u * CFG::SetBytes, p.S + (int64_t)(e & ~kStreamSet) * (4 * p.G) + g0 * 4, 4 * leaf_bytes,
                          r.bars + (M::bSetFull + u) * 8);
             }
             n_set++;
@@ -336,9 +309,9 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
             if (lane == 0) {
                 const uint32_t u = n_leaf % M::kLeafRing, par = (n_leaf / M::kLeafRing) & 1u;
                 PMFS_WP(8);
-                mbar_wait(r.bars + (M::bLeafEmpty + u) * 8, par ^ 1u);
+                mbar_wait(r.bars + (M::bLeafEmpty + u) * 8, par ^ 1u, r.limit_ns);
                 mbar_arrive_expect_tx(r.bars + (M::bLeafFull + u) * 8, leaf_bytes);
-                bulk_g2s(r.smem + M::kLeaf + u * kUnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
+                bulk_g2s(r.smem + M::kLeaf + u * CFG::UnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
                          r.bars + (M::bLeafFull + u) * 8);
             }
             n_leaf++;
@@ -350,7 +323,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
             const int32_t left = slen - 1 - j;
             if (left == h.t_claim) h.claim(p);
             else if (left == h.t_fetch) h.fetch(p);
-            else if (left < h.t_fetch && !h.posted && (left & 1) == 0) header_step<RING>(p, r, h, false);
+            else if (left < h.t_fetch && !h.posted && (left & 1) == 0) header_step<CFG, RING>(p, r, h, false);
         }
     }
 }
@@ -363,49 +336,49 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
 // Set arrays are TILE-MAJOR: S[internal id][tile][quarter][groups of the tile] (uint4; 256 groups per tile, fewer in
 // the last one), so one node's set for one tile is a single contiguous block of up to 16 KB (one TMA copy) and a
 // warp's 128-bit stores are 512-byte segments.  A node's row is exactly 4*G uint4: no padding.
-template <bool READONLY_SETS, int RING>
+template <class CFG, bool READONLY_SETS, int RING>
 struct DevEnv {
-    static constexpr int kGroups = kNG;
-    using M = SmemMap<RING>;
+    static constexpr int kGroups = CFG::NG;
+    using M = SmemMap<CFG, RING>;
     const WalkParams& p;
     const Ring& ring;
-    int64_t g[kNG];      // clamped column groups
-    bool active[kNG];
+    int64_t g[CFG::NG];      // clamped column groups
+    bool active[CFG::NG];
     int64_t gwarp;       // (unclamped) column group of this warp's lane 0, first group slot
     int64_t set_tile;    // uint4 offset of this tile inside one node's set row: tile * 1024
     int32_t tile_w;      // column groups of this tile (256, less for the last tile): stride between the 4 quarters
     int32_t item_tile;   // column tile of this work item
     uint32_t& n_leaf;    // running ring entry numbers of this CTA (same sequences as the producer's)
     uint32_t& n_set;
-    uint4* fstk;         // [depth][kNG][4][kTPB]
-    uint32_t* bstk;      // [depth][kNG][5][kTPB]
+    uint4* fstk;         // [depth][CFG::NG][4][CFG::TPB]
+    uint32_t* bstk;      // [depth][CFG::NG][5][CFG::TPB]
     int sp = 0;
     int lane;
     bool prog_staged;
     const uint32_t* gprog;
     uint32_t sprog;      // shared address of this item's staged program
     uint32_t ltmask;     // bits of a group word whose column is smaller than the column of bit `lane`
-    mutable unsigned long long blk_base[kNG];  // lane 0, cell mode: the warp's current output block per group slot
-    mutable uint32_t blk_used[kNG], blk_size[kNG];
+    mutable unsigned long long blk_base[CFG::NG];  // lane 0, cell mode: the warp's current output block per group slot
+    mutable uint32_t blk_used[CFG::NG], blk_size[CFG::NG];
 
     __device__ DevEnv(const WalkParams& p_, const Ring& r, const ItemDesc& d, uint32_t slot, uint32_t prog_parity,
                       uint32_t& n_leaf_, uint32_t& n_set_, void* smem_generic)
-        : p(p_), ring(r), gwarp((int64_t)d.tile * kTileGroups + (threadIdx.x & ~31)), set_tile((int64_t)d.tile * (kSetBytes / 16)),
-          tile_w((int32_t)min((int64_t)kTileGroups, p_.G - (int64_t)d.tile * kTileGroups)),
+        : p(p_), ring(r), gwarp((int64_t)d.tile * CFG::Groups + (threadIdx.x & ~31)), set_tile((int64_t)d.tile * (CFG::SetBytes / 16)),
+          tile_w((int32_t)min((int64_t)CFG::Groups, p_.G - (int64_t)d.tile * CFG::Groups)),
           item_tile(d.tile),
           n_leaf(n_leaf_), n_set(n_set_), fstk((uint4*)((char*)smem_generic + M::kStack)),
           bstk((uint32_t*)((char*)smem_generic + M::kStack)), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords),
           gprog(nullptr), sprog(r.smem + M::kProg + slot * (kProgWords * 4)) {
 #pragma unroll
-        for (int j = 0; j < kNG; j++) {
-            const int64_t gj = (int64_t)d.tile * kTileGroups + j * kTPB + threadIdx.x;
+        for (int j = 0; j < CFG::NG; j++) {
+            const int64_t gj = (int64_t)d.tile * CFG::Groups + j * CFG::TPB + threadIdx.x;
             active[j] = gj < p_.G;
             g[j] = active[j] ? gj : p_.G - 1;
         }
         // bit q is column 8*(q&3) + (q>>2): smaller residues q&3 come first as a whole, then smaller q>>2 of this lane's own
         ltmask = 0x11111111u * ((1u << (lane & 3)) - 1u) | ((0x11111111u << (lane & 3)) & ((1u << (4 * (lane >> 2))) - 1u));
         PMFS_WP(1);
-        if (prog_staged) mbar_wait(r.bars + (M::bProg + slot) * 8, prog_parity);
+        if (prog_staged) mbar_wait(r.bars + (M::bProg + slot) * 8, prog_parity, r.limit_ns);
         else gprog = p_.prog + p_.chunk_off[d.chunk];
     }
 
@@ -419,28 +392,28 @@ struct DevEnv {
     }
 
     // next leaf unit: wait until the TMA copy has landed, read this thread's 16 bytes per group, hand the unit back
-    __device__ __forceinline__ void leaf(uint32_t, uint4 (&w)[kNG]) {
+    __device__ __forceinline__ void leaf(uint32_t, uint4 (&w)[CFG::NG]) {
         const uint32_t u = n_leaf % M::kLeafRing, par = (n_leaf / M::kLeafRing) & 1u;
         PMFS_WP(2);
-        mbar_wait(ring.bars + (M::bLeafFull + u) * 8, par);
-        const uint32_t base = ring.smem + M::kLeaf + u * kUnitBytes + threadIdx.x * 16;
+        mbar_wait(ring.bars + (M::bLeafFull + u) * 8, par, ring.limit_ns);
+        const uint32_t base = ring.smem + M::kLeaf + u * CFG::UnitBytes + threadIdx.x * 16;
 #pragma unroll
-        for (int j = 0; j < kNG; j++) w[j] = lds128(base + j * (kTPB * 16));
+        for (int j = 0; j < CFG::NG; j++) w[j] = lds128(base + j * (CFG::TPB * 16));
         __syncwarp();
         if (lane == 0) mbar_arrive(ring.bars + (M::bLeafEmpty + u) * 8);
         n_leaf++;
     }
-    // next set slot (a set written by an earlier work item): 4 quarters x kNG groups
-    __device__ __forceinline__ void load_x(uint32_t, Planes16 (&s)[kNG]) {
+    // next set slot (a set written by an earlier work item): 4 quarters x CFG::NG groups
+    __device__ __forceinline__ void load_x(uint32_t, Planes16 (&s)[CFG::NG]) {
         const uint32_t u = n_set % M::SETS, par = (n_set / M::SETS) & 1u;
         PMFS_WP(3);
-        mbar_wait(ring.bars + (M::bSetFull + u) * 8, par);
-        const uint32_t base = ring.smem + M::kSet + u * kSetBytes + threadIdx.x * 16;
+        mbar_wait(ring.bars + (M::bSetFull + u) * 8, par, ring.limit_ns);
+        const uint32_t base = ring.smem + M::kSet + u * CFG::SetBytes + threadIdx.x * 16;
 #pragma unroll
-        for (int j = 0; j < kNG; j++)
+        for (int j = 0; j < CFG::NG; j++)
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const uint4 v = lds128(base + (i * tile_w + j * kTPB) * 16);
+                const uint4 v = lds128(base + (i * tile_w + j * CFG::TPB) * 16);
                 s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
             }
         __syncwarp();
@@ -450,11 +423,11 @@ struct DevEnv {
 
     // direct access to the set arrays (sets of this work item itself; Sankoff D1 on the slow path)
     __device__ __forceinline__ int64_t set_index(uint32_t id, int j, int i) const {
-        return (int64_t)id * (4 * p.G) + set_tile + i * tile_w + j * kTPB + threadIdx.x;
+        return (int64_t)id * (4 * p.G) + set_tile + i * tile_w + j * CFG::TPB + threadIdx.x;
     }
-    __device__ __forceinline__ void load_arr(const uint4* base, uint32_t id, Planes16 (&s)[kNG]) const {
+    __device__ __forceinline__ void load_arr(const uint4* base, uint32_t id, Planes16 (&s)[CFG::NG]) const {
 #pragma unroll
-        for (int j = 0; j < kNG; j++) {
+        for (int j = 0; j < CFG::NG; j++) {
             if (!active[j]) {  // padding lane of the last tile: its slot lies outside this tile's block
                 zero16(s[j]);
                 continue;
@@ -467,70 +440,70 @@ struct DevEnv {
             }
         }
     }
-    __device__ __forceinline__ void store_arr(uint4* base, uint32_t id, const Planes16 (&s)[kNG]) const {
+    __device__ __forceinline__ void store_arr(uint4* base, uint32_t id, const Planes16 (&s)[CFG::NG]) const {
 #pragma unroll
-        for (int j = 0; j < kNG; j++) {
+        for (int j = 0; j < CFG::NG; j++) {
             if (!active[j]) continue;
 #pragma unroll
             for (int i = 0; i < 4; i++)
                 base[set_index(id, j, i)] = make_uint4(s[j].p[4 * i], s[j].p[4 * i + 1], s[j].p[4 * i + 2], s[j].p[4 * i + 3]);
         }
     }
-    __device__ __forceinline__ void load_s(uint32_t id, Planes16 (&s)[kNG]) const { load_arr(p.S, id, s); }
-    __device__ __forceinline__ void load_d(uint32_t id, Planes16 (&s)[kNG]) const { load_arr(p.D, id, s); }
-    __device__ __forceinline__ void store_s(uint32_t id, const Planes16 (&s)[kNG]) const { store_arr(p.S, id, s); }
-    __device__ __forceinline__ void store_d(uint32_t id, const Planes16 (&s)[kNG]) const { store_arr(p.D, id, s); }
+    __device__ __forceinline__ void load_s(uint32_t id, Planes16 (&s)[CFG::NG]) const { load_arr(p.S, id, s); }
+    __device__ __forceinline__ void load_d(uint32_t id, Planes16 (&s)[CFG::NG]) const { load_arr(p.D, id, s); }
+    __device__ __forceinline__ void store_s(uint32_t id, const Planes16 (&s)[CFG::NG]) const { store_arr(p.S, id, s); }
+    __device__ __forceinline__ void store_d(uint32_t id, const Planes16 (&s)[CFG::NG]) const { store_arr(p.D, id, s); }
 
-    __device__ __forceinline__ void push(const Planes16 (&s)[kNG]) {
-        uint4* q = fstk + (sp * kNG * 4) * kTPB + threadIdx.x;
+    __device__ __forceinline__ void push(const Planes16 (&s)[CFG::NG]) {
+        uint4* q = fstk + (sp * CFG::NG * 4) * CFG::TPB + threadIdx.x;
 #pragma unroll
-        for (int j = 0; j < kNG; j++)
+        for (int j = 0; j < CFG::NG; j++)
 #pragma unroll
             for (int i = 0; i < 4; i++)
-                q[(j * 4 + i) * kTPB] = make_uint4(s[j].p[4 * i], s[j].p[4 * i + 1], s[j].p[4 * i + 2], s[j].p[4 * i + 3]);
+                q[(j * 4 + i) * CFG::TPB] = make_uint4(s[j].p[4 * i], s[j].p[4 * i + 1], s[j].p[4 * i + 2], s[j].p[4 * i + 3]);
         sp++;
     }
-    __device__ __forceinline__ void pop(Planes16 (&s)[kNG]) {
+    __device__ __forceinline__ void pop(Planes16 (&s)[CFG::NG]) {
         sp--;
-        const uint4* q = fstk + (sp * kNG * 4) * kTPB + threadIdx.x;
+        const uint4* q = fstk + (sp * CFG::NG * 4) * CFG::TPB + threadIdx.x;
 #pragma unroll
-        for (int j = 0; j < kNG; j++)
+        for (int j = 0; j < CFG::NG; j++)
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const uint4 v = q[(j * 4 + i) * kTPB];
+                const uint4 v = q[(j * 4 + i) * CFG::TPB];
                 s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
             }
     }
-    __device__ __forceinline__ void pushp(const Code4 (&c)[kNG], const uint32_t (&pv)[kNG]) {
-        uint32_t* q = bstk + (sp * kNG * 5) * kTPB + threadIdx.x;
+    __device__ __forceinline__ void pushp(const Code4 (&c)[CFG::NG], const uint32_t (&pv)[CFG::NG]) {
+        uint32_t* q = bstk + (sp * CFG::NG * 5) * CFG::TPB + threadIdx.x;
 #pragma unroll
-        for (int j = 0; j < kNG; j++) {
+        for (int j = 0; j < CFG::NG; j++) {
 #pragma unroll
-            for (int i = 0; i < 4; i++) q[(j * 5 + i) * kTPB] = c[j].b[i];
-            q[(j * 5 + 4) * kTPB] = pv[j];
+            for (int i = 0; i < 4; i++) q[(j * 5 + i) * CFG::TPB] = c[j].b[i];
+            q[(j * 5 + 4) * CFG::TPB] = pv[j];
         }
         sp++;
     }
-    __device__ __forceinline__ void popp(Code4 (&c)[kNG], uint32_t (&pv)[kNG]) {
+    __device__ __forceinline__ void popp(Code4 (&c)[CFG::NG], uint32_t (&pv)[CFG::NG]) {
         sp--;
-        const uint32_t* q = bstk + (sp * kNG * 5) * kTPB + threadIdx.x;
+        const uint32_t* q = bstk + (sp * CFG::NG * 5) * CFG::TPB + threadIdx.x;
 #pragma unroll
-        for (int j = 0; j < kNG; j++) {
+        for (int j = 0; j < CFG::NG; j++) {
 #pragma unroll
-            for (int i = 0; i < 4; i++) c[j].b[i] = q[(j * 5 + i) * kTPB];
-            pv[j] = q[(j * 5 + 4) * kTPB];
+            for (int i = 0; i < 4; i++) c[j].b[i] = q[(j * 5 + i) * CFG::TPB];
+            pv[j] = q[(j * 5 + 4) * CFG::TPB];
         }
     }
     // The parent state of a child chunk, and -- top-down dependencies are per chunk, not per finished item -- the go-ahead
     // for it: the child chunk's tile can start while this item is still walking the rest of its own nodes.
-    __device__ __forceinline__ void store_x(uint32_t chunk, const Code4 (&c)[kNG], const uint32_t (&pv)[kNG]) const {
+    __device__ __forceinline__ void store_x(uint32_t chunk, const Code4 (&c)[CFG::NG], const uint32_t (&pv)[CFG::NG]) const {
 #pragma unroll
-        for (int j = 0; j < kNG; j++) {
+        for (int j = 0; j < CFG::NG; j++) {
             if (!active[j]) continue;
             p.xcode[(int64_t)chunk * p.G + g[j]] = make_uint4(c[j].b[0], c[j].b[1], c[j].b[2], c[j].b[3]);
             p.xvalid[(int64_t)chunk * p.G + g[j]] = pv[j];
         }
-        asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // all four walking warps have stored their part
+        asm volatile("bar.sync 1, %0;" ::"n"(CFG::TPB) : "memory");  // all four walking warps have stored their part
         if (threadIdx.x == 0) {
             __threadfence();
             atomicAdd(p.ready + (int64_t)chunk * p.ctas_per_chunk + item_tile, 1);
@@ -586,20 +559,20 @@ struct DevEnv {
     __device__ __forceinline__ void reserve_blocks() const {
         if (lane != 0) return;
 #pragma unroll
-        for (int j = 0; j < kNG; j++) {
+        for (int j = 0; j < CFG::NG; j++) {
             blk_used[j] = blk_size[j] = 0;
-            if (gwarp + j * kTPB < p.G) {
-                blk_base[j] = atomicAdd(p.out_count + p.region_base + ((gwarp + j * kTPB) >> 5), (unsigned long long)kEmitBlock);
+            if (gwarp + j * CFG::TPB < p.G) {
+                blk_base[j] = atomicAdd(p.out_count + p.region_base + ((gwarp + j * CFG::TPB) >> 5), (unsigned long long)kEmitBlock);
                 blk_size[j] = kEmitBlock;
             }
         }
     }
-    __device__ void emit_cells(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+    __device__ void emit_cells(uint32_t node, const uint32_t (&m)[CFG::NG], const Code4 (&G)[CFG::NG], const Code4 (&P)[CFG::NG]) const {
 #pragma unroll
-        for (int j = 0; j < kNG; j++) {
+        for (int j = 0; j < CFG::NG; j++) {
             if (!__any_sync(0xffffffffu, m[j] != 0)) continue;
             const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
-            const int64_t region = p.region_base + ((gwarp + j * kTPB) >> 5);
+            const int64_t region = p.region_base + ((gwarp + j * CFG::TPB) >> 5);
             unsigned long long base = 0;
             if (lane == 0) {
                 if (total > blk_size[j] - blk_used[j]) {  // block used up (or a node with more records than a block holds)
@@ -614,10 +587,10 @@ struct DevEnv {
                 p.cell_start[cell] = (uint32_t)base;
             }
             base = __shfl_sync(0xffffffffu, base, 0);
-            emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * kTPB);
+            emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * CFG::TPB);
         }
     }
-    __device__ void emit(uint32_t node, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+    __device__ void emit(uint32_t node, const uint32_t (&m)[CFG::NG], const Code4 (&G)[CFG::NG], const Code4 (&P)[CFG::NG]) const {
         if (p.cell_count) {
             emit_cells(node, m, G, P);
             return;
@@ -627,20 +600,20 @@ struct DevEnv {
 #pragma unroll 1  // (unrolled 16-fold this loop was a fifth of the kernel's code)
             for (int r = 1; r < p.n_owners; r++) own_base += (int32_t)node >= p.owner_bound[r] ? p.n_regions : 0;
 #pragma unroll
-            for (int j = 0; j < kNG; j++) {
+            for (int j = 0; j < CFG::NG; j++) {
                 if (!__any_sync(0xffffffffu, m[j] != 0)) continue;
                 const uint32_t total = __reduce_add_sync(0xffffffffu, (uint32_t)__popc(m[j]));
-                const int64_t region = own_base + (int64_t)(node & p.bucket_mask) * p.n_regions + p.region_base + ((gwarp + j * kTPB) >> 5);
+                const int64_t region = own_base + (int64_t)(node & p.bucket_mask) * p.n_regions + p.region_base + ((gwarp + j * CFG::TPB) >> 5);
                 unsigned long long base = 0;
                 if (lane == 0) base = atomicAdd(p.out_count + region, (unsigned long long)total);
                 base = __shfl_sync(0xffffffffu, base, 0);
-                emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * kTPB);
+                emit1(node, p.out_keys + (unsigned long long)region * p.out_cap, base, m[j], G[j], P[j], gwarp + j * CFG::TPB);
             }
             return;
         }
         uint32_t cnt = 0;
 #pragma unroll
-        for (int j = 0; j < kNG; j++) cnt += __popc(m[j]);
+        for (int j = 0; j < CFG::NG; j++) cnt += __popc(m[j]);
         const uint32_t total = __reduce_add_sync(0xffffffffu, cnt);
         int own = 0;  // owner of this node's list (column shards); uniform across the warp
 #pragma unroll 1
@@ -650,12 +623,12 @@ struct DevEnv {
         base = __shfl_sync(0xffffffffu, base, 0);
         unsigned long long* out = p.out_keys + (unsigned long long)own * p.out_cap;
 #pragma unroll
-        for (int j = 0; j < kNG; j++) emit1(node, out, base, m[j], G[j], P[j], gwarp + j * kTPB);
+        for (int j = 0; j < CFG::NG; j++) emit1(node, out, base, m[j], G[j], P[j], gwarp + j * CFG::TPB);
     }
-    __device__ __forceinline__ void emit_internal(uint32_t id, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+    __device__ __forceinline__ void emit_internal(uint32_t id, const uint32_t (&m)[CFG::NG], const Code4 (&G)[CFG::NG], const Code4 (&P)[CFG::NG]) const {
         emit((uint32_t)__ldg(p.int_to_node + id), m, G, P);
     }
-    __device__ __forceinline__ void emit_leaf(uint32_t row, const uint32_t (&m)[kNG], const Code4 (&G)[kNG], const Code4 (&P)[kNG]) const {
+    __device__ __forceinline__ void emit_leaf(uint32_t row, const uint32_t (&m)[CFG::NG], const Code4 (&G)[CFG::NG], const Code4 (&P)[CFG::NG]) const {
         emit((uint32_t)__ldg(p.row_to_node + row), m, G, P);
     }
 };
@@ -683,25 +656,26 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
 // latencies.  Item descriptors and programs are double buffered; all hand-overs are mbarriers, the kernels contain no
 // CTA-wide barrier after set-up.
 
-template <int RING>
-__device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars) {
-    using M = SmemMap<RING>;
+template <class CFG, int RING>
+__device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars, long long limit_ns) {
+    using M = SmemMap<CFG, RING>;
     Ring r;
     r.smem = (uint32_t)__cvta_generic_to_shared(smem);
     r.bars = (uint32_t)__cvta_generic_to_shared(bars);
+    r.limit_ns = limit_ns;
     if (threadIdx.x == 0) {
         for (int i = 0; i < M::kLeafRing; i++) {
             mbar_init(r.bars + (M::bLeafFull + i) * 8, 1);           // one arrive.expect_tx by the producer
-            mbar_init(r.bars + (M::bLeafEmpty + i) * 8, kTPB / 32);  // one arrive per walking warp
+            mbar_init(r.bars + (M::bLeafEmpty + i) * 8, CFG::NW);  // one arrive per walking warp
         }
         for (int i = 0; i < M::SETS; i++) {
             mbar_init(r.bars + (M::bSetFull + i) * 8, 1);
-            mbar_init(r.bars + (M::bSetEmpty + i) * 8, kTPB / 32);
+            mbar_init(r.bars + (M::bSetEmpty + i) * 8, CFG::NW);
         }
         for (int i = 0; i < 2; i++) {
             mbar_init(r.bars + (M::bProg + i) * 8, 1);
             mbar_init(r.bars + (M::bDescFull + i) * 8, 1);
-            mbar_init(r.bars + (M::bDescEmpty + i) * 8, kTPB / 32);
+            mbar_init(r.bars + (M::bDescEmpty + i) * 8, CFG::NW);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -713,7 +687,7 @@ __device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars)
 // item after item.  Everything that does not need the dependency is started before it is polled, the item record is
 // one 32-byte load, and the claim for the NEXT item is issued before this one is produced, so that per item only the
 // record load and the dependency poll remain on the producer's critical path.
-template <int RING>
+template <class CFG, int RING>
 __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r) {
     const int lane = threadIdx.x & 31;
     uint32_t n_leaf = 0, n_set = 0;
@@ -721,7 +695,7 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
     if (lane == 0) {
         h.begin(0, 1, 0);
         h.fetch(p);
-        header_step<RING>(p, r, h, true);
+        header_step<CFG, RING>(p, r, h, true);
     }
     for (uint32_t n = 0;; n++) {
         // item n: descriptor posted; broadcast what the stream needs
@@ -733,22 +707,22 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
         WarpWords w;
         w.init(p.stream + stream_off, slen, lane);
         if (lane == 0) h.begin(n + 1, slen, p.claim_lead);
-        produce_stream<RING>(p, r, w, slen, tile, n_leaf, n_set, h);
+        produce_stream<CFG, RING>(p, r, w, slen, tile, n_leaf, n_set, h);
         if (lane == 0 && !h.posted) {
             if (!h.fetched) h.fetch(p);
-            header_step<RING>(p, r, h, true);
+            header_step<CFG, RING>(p, r, h, true);
         }
     }
 }
 
 // Walking warps: take the next descriptor; returns false when there is no more work.
-template <int RING>
+template <class CFG, int RING>
 __device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d) {
-    using M = SmemMap<RING>;
+    using M = SmemMap<CFG, RING>;
     const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
     {
         PMFS_WP(0);
-        mbar_wait(r.bars + (M::bDescFull + slot) * 8, phase);
+        mbar_wait(r.bars + (M::bDescFull + slot) * 8, phase, r.limit_ns);
     }
     asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(d.chunk), "=r"(d.tile), "=r"(d.plen), "=r"(d.parent)
@@ -757,11 +731,12 @@ __device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d
     return d.chunk >= 0;
 }
 // Item finished: publish it to dependants (all walkers' stores first), then free the descriptor/program slot.
+template <class CFG>
 __device__ __forceinline__ void finish_item(int* counter, uint32_t desc_empty_bar) {
     if (counter) {  // (uniform; the top-down pass publishes per child chunk in store_x and has nothing to say here)
         {
             PMFS_WP(4);
-            asm volatile("bar.sync 1, %0;" ::"n"(kTPB) : "memory");  // the four walking warps only
+            asm volatile("bar.sync 1, %0;" ::"n"(CFG::TPB) : "memory");  // the four walking warps only
         }
         if (threadIdx.x == 0) {
             __threadfence();
@@ -772,30 +747,30 @@ __device__ __forceinline__ void finish_item(int* counter, uint32_t desc_empty_ba
     if ((threadIdx.x & 31) == 0) mbar_arrive(desc_empty_bar);
 }
 
-template <int ALGO, bool POLY>
-__global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
-    using M = SmemMap<kSetRingFwd>;
+template <class CFG, int ALGO, bool POLY>
+__global__ void __launch_bounds__(CFG::Threads) fwd_kernel(const WalkParams p) {
+    using M = SmemMap<CFG, kSetRingFwd>;
     extern __shared__ uint4 smem[];
     __shared__ __align__(8) unsigned long long bars[M::kBars];
-    const Ring ring = ring_setup<kSetRingFwd>(smem, bars);
-    if (threadIdx.x >= kTPB) {
+    const Ring ring = ring_setup<CFG, kSetRingFwd>(smem, bars, p.spin_limit_ns);
+    if (threadIdx.x >= CFG::TPB) {
         PMFS_WP(10);
-        producer_loop<kSetRingFwd>(p, ring);
+        producer_loop<CFG, kSetRingFwd>(p, ring);
         return;
     }
     PMFS_WP(5);
     uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
     ItemDesc d;
-    for (uint32_t n = 0; next_item<kSetRingFwd>(ring, n, d); n++) {
+    for (uint32_t n = 0; next_item<CFG, kSetRingFwd>(ring, n, d); n++) {
         const uint32_t slot = n & 1u;
         PMFS_TRACE_BEGIN
         {
-            DevEnv<false, kSetRingFwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
-            Code4 forced[kNG];
+            DevEnv<CFG, false, kSetRingFwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            Code4 forced[CFG::NG];
             const Code4* fp = nullptr;
             if (ALGO == kAlgoFitch && p.forced_planes) {
 #pragma unroll
-                for (int j = 0; j < kNG; j++) {
+                for (int j = 0; j < CFG::NG; j++) {
                     const uint4 v = __ldg(p.forced_planes + env.g[j]);
                     forced[j].b[0] = v.x; forced[j].b[1] = v.y; forced[j].b[2] = v.z; forced[j].b[3] = v.w;
                 }
@@ -804,38 +779,45 @@ __global__ void __launch_bounds__(kThreads) fwd_kernel(const WalkParams p) {
             forward_walk<ALGO, POLY>(env, nullptr, d.plen, fp);
         }
         if (d.plen <= kProgWords) staged[slot]++;
-        finish_item(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr,
+        finish_item<CFG>(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr,
                     ring.bars + (M::bDescEmpty + slot) * 8);
         PMFS_TRACE_END(d.chunk, d.tile)
     }
 }
 
-template <int ALGO>
-__global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 3) bwd_kernel(const WalkParams p) {
-    using M = SmemMap<kSetRingBwd>;
+// Resident CTAs the top-down kernel is compiled for: 96 registers per thread for Fitch (4 CTAs of the 160-thread shape
+// share an SM: +13 % over 3), 128 for Sankoff, whatever the number of threads of the shape.
+template <class CFG, int ALGO>
+constexpr int bwd_min_ctas() {
+    // (registers are per SM sub-partition: 16 384 each, warps are spread over the four of them)
+    return 4 * (16384 / ((ALGO == kAlgoFitch ? 96 : 128) * 32)) / (CFG::Threads / 32);
+}
+template <class CFG, int ALGO>
+__global__ void __launch_bounds__(CFG::Threads, bwd_min_ctas<CFG, ALGO>()) bwd_kernel(const WalkParams p) {
+    using M = SmemMap<CFG, kSetRingBwd>;
     extern __shared__ uint4 smem[];
     __shared__ __align__(8) unsigned long long bars[M::kBars];
-    const Ring ring = ring_setup<kSetRingBwd>(smem, bars);
-    if (threadIdx.x >= kTPB) {
+    const Ring ring = ring_setup<CFG, kSetRingBwd>(smem, bars, p.spin_limit_ns);
+    if (threadIdx.x >= CFG::TPB) {
         PMFS_WP(10);
-        producer_loop<kSetRingBwd>(p, ring);
+        producer_loop<CFG, kSetRingBwd>(p, ring);
         return;
     }
     PMFS_WP(5);
     uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
     ItemDesc d;
-    for (uint32_t n = 0; next_item<kSetRingBwd>(ring, n, d); n++) {
+    for (uint32_t n = 0; next_item<CFG, kSetRingBwd>(ring, n, d); n++) {
         const uint32_t slot = n & 1u;
         uint32_t err;
         PMFS_TRACE_BEGIN
         {
-            DevEnv<true, kSetRingBwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            DevEnv<CFG, true, kSetRingBwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
             if (p.cell_count) env.reserve_blocks();
-            Code4 P[kNG], forced[kNG];
-            uint32_t pv[kNG], colmask[kNG];
+            Code4 P[CFG::NG], forced[CFG::NG];
+            uint32_t pv[CFG::NG], colmask[CFG::NG];
             const Code4* fp = nullptr;
 #pragma unroll
-            for (int j = 0; j < kNG; j++) {
+            for (int j = 0; j < CFG::NG; j++) {
                 pv[j] = ~0u;
                 if (d.chunk == 0) {
                     const uint4 v = __ldg(p.cons_planes + env.g[j]);
@@ -856,7 +838,7 @@ __global__ void __launch_bounds__(kThreads, ALGO == kAlgoFitch ? 4 : 3) bwd_kern
         }
         if (err) atomicOr(p.err_flag, 1u);
         if (d.plen <= kProgWords) staged[slot]++;
-        finish_item(nullptr, ring.bars + (M::bDescEmpty + slot) * 8);  // (child chunks were released by store_x)
+        finish_item<CFG>(nullptr, ring.bars + (M::bDescEmpty + slot) * 8);  // (child chunks were released by store_x)
         PMFS_TRACE_END(d.chunk, d.tile)
     }
 }

@@ -5,8 +5,9 @@ that may not stall the device (cudaMalloc / cudaFree synchronise it), a process 
 or code running where the allocator is off limits.  For them the library keeps a fixed 32 MiB array in device memory and
 carves every intermediate of the Fitch pass out of it.  Because the array is shared by all calls and keeps the previous
 call's contents, this test runs the entry point twice in a row on DIFFERENT alignments and requires each result to be
-identical, record for record, to what the ordinary entry point (pmfs_run_device) returns for the same input.  It also
-checks that a problem beyond the fixed size is refused with a message instead of being attempted.
+identical, record for record, to what the ordinary entry point (pmfs_run_device) returns for the same input and to what
+the reference's own CPU code (oracle/_ref) computes.  It also checks that a problem beyond the fixed size is refused
+with a message instead of being attempted.
 
 The file name sorts last on purpose: with `pytest -x` every other test has already run if this one fails."""
 import numpy as np
@@ -14,6 +15,7 @@ import pytest
 
 import golden_util as G
 import synth
+from oracle import oracle_api as O
 from panman_b200 import api, trees
 
 pytestmark = pytest.mark.gpu
@@ -53,6 +55,11 @@ def test_static_scratch_entry_point_matches_run_device_twice_in_a_row():
             assert n == n_ref and n > 1000, (call, n, n_ref)
             assert G.same_muts(got, want), call
             assert (got["parent_code"] == want["parent_code"]).all(), call
+            # ... and to what the reference's CPU code computes (both entry points share kernels: agreeing with each
+            # other is not enough)
+            ref = O.run_ref_columns(api.FITCH, tree, O.codes_to_chars(msa), O.codes_to_chars(cons),
+                                    None if forced is None else O.codes_to_chars(forced), threads=4)
+            assert G.same_muts(got, ref), call
 
 
 def test_static_scratch_entry_point_rejects_what_does_not_fit():
