@@ -1,17 +1,24 @@
 #!/usr/bin/env python
-"""bench.py -- column.node updates/s of the Fitch / Sankoff pass on BASELINE config 2, one JSON line on rank 0.
+"""bench.py -- column.node updates/s of the Fitch / Sankoff pass, one JSON line on rank 0.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--algo fitch|sankoff] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--algo fitch|sankoff] [--impl ours|reference] [--workload c3|c2]
 
-A step = one full pass of the hot path (bottom-up sets, top-down assignment, mutation emission, ordering by (node,pos))
-over one synthetic SARS-CoV-2-shaped alignment of 20 000 taxa x 30 000 columns on a random binary tree (39 999 nodes),
-already resident in HBM.  With N GPUs every rank owns its own 30 000-column shard of a 20 000 x (30 000*N) alignment
-(weak scaling; columns are independent: every rank runs the whole step on its shard and keeps its (node,pos)-ordered
-records with global positions -- no data-path collective; a node's complete list is the concatenation of the ranks'
-slices, panman_b200/shard.py stitch_by_node).  The variant in which an NCCL all-to-all leaves every rank with the
-complete lists of a node range ON THE DEVICE is timed after the main loop and reported as config.gathered_by_node.
-`value` counts all ranks' updates over the max-over-ranks device time; `e2e` is the same metric through the
-host-buffer C-ABI call (pmfs_run: H2D of the nibble-packed MSA and D2H of the records inside the timed region).
+Workload (default, every N): BASELINE config 3 -- the 8 000 000-taxon x 30 000-column SARS-CoV-2-shaped alignment
+(random binary tree, 15 999 999 nodes), COLUMN-SHARDED over the N GPUs, strong scaling: the same 30 000 columns whatever
+N.  A step = one full pass of the hot path over all 30 000 columns: bottom-up sets, top-down assignment, mutation
+emission, ordering by (node,pos) and -- for N > 1 -- the gather of the per-node lists by node range with NCCL
+(pmfs_comm_run: every rank ends up owning the complete (node,pos)-ordered lists of its node range, in HBM), all inside
+the timed region.  The alignment is resident in HBM when the timed region starts (120 GB on one GPU, 15 GB per GPU on
+eight).  The per-node set arrays of 8 M internal nodes take 0.5 GB per 32 columns, so the columns go through in
+ascending windows (one window = N x the columns that fit per GPU); each window's result is complete and ordered, and a
+node's list is the concatenation over windows -- the shape of the reference's own --low-mem-mode batch loop
+(src/panman.cpp:1503-1514).  `--workload c2` is BASELINE config 2 (20 000 taxa x 30 000 columns per GPU); on one GPU it
+is also measured next to the main workload and reported as `c2_single_gpu`.
+
+`value` counts all ranks' updates over the max-over-ranks device time; `e2e` is the same metric through host buffers
+(N = 1: pmfs_run; N > 1: H2D of the rank's columns + pmfs_comm_run + D2H of the rank's node range) on a column batch of
+the workload; `cpu_baseline` / `--impl reference` time the reference's own fitchSankoff.cpp (oracle/_ref) on the host
+cores on a column sample of the same workload.
 """
 import argparse
 import json
@@ -27,16 +34,20 @@ sys.path.insert(0, ROOT)
 if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
     del os.environ["NCCL_DEBUG"]
 
-N_TAXA = 20000
-N_COLS = 30000
 B_CONTRACT = {"fitch": 4.25, "sankoff": 6.25}  # level-sweep bytes per column.node update
+WORKLOADS = {
+    # name: (taxa, columns, tree, description)
+    "c3": (8_000_000, 30_000, "random binary tree", "c3: synthetic SARS-CoV-2-shaped MSA, 8000000 taxa x 30000 columns"),
+    "c2": (20_000, 30_000, "random binary tree", "c2: synthetic SARS-CoV-2-shaped MSA, 20000 taxa x 30000 columns per GPU"),
+}
 
 
-def ncu_traffic(algo):
-    """DRAM bytes per step of fwd_kernel + bwd_kernel from the committed `ncu --set full` capture (profiles/)."""
+def ncu_traffic(workload, algo):
+    """DRAM bytes of fwd_kernel + bwd_kernel from the committed `ncu --set full` capture (profiles/traffic_r2.json),
+    with the commit and tile shape it was taken at; None when there is no capture for this workload."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "traffic_r1.json")))
-        return float(t[algo]["traffic_bytes_per_step"])
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic_r2.json")))
+        return t[workload][algo]
     except Exception:
         return None
 
@@ -94,38 +105,89 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference_sample(tree, host_codes, cons, algo, threads):
-    """Times the reference's CPU path on a column sample.  oracle/_ref (the reference's own fitchSankoff.cpp) when its
-    prebuilt library is present, else the plain-C port."""
+def ref_threads(n_nodes, ncpu):
+    """Threads for the reference's CPU code: each holds one column's node-name-keyed hash maps (~200 B per node)."""
+    try:
+        avail = int([l for l in open("/proc/meminfo") if l.startswith("MemAvailable")][0].split()[1]) * 1024
+    except Exception:
+        avail = 32 << 30
+    return max(1, min(ncpu, int(0.4 * avail / (n_nodes * 200 + 1))))
+
+
+class CpuReference:
+    """The reference's CPU path on column samples: oracle/_ref (the reference's own fitchSankoff.cpp) when its prebuilt
+    library is present, else the plain-C port.  The Node graph is built once; only the column loop is timed."""
+
+    def __init__(self, tree, ncpu):
+        from oracle import oracle_api as O
+        self.O, self.tree = O, tree
+        self.threads = ref_threads(tree.n_nodes, ncpu)
+        self.kind = "reference" if (O.ref_available() and os.path.exists(O.REF_SO)) else "port"
+        self.graph = O.RefGraph(tree) if self.kind == "reference" else None
+
+    def run(self, algo_name, codes, cons):
+        """-> (records, seconds of the column loop)"""
+        O, a = self.O, 0 if algo_name == "fitch" else 1
+        if self.graph is not None:
+            rec = self.graph.columns(a, O.codes_to_chars(codes), O.codes_to_chars(cons), None, threads=self.threads)
+            return rec, O.last_ref_loop_seconds()
+        t0 = time.perf_counter()
+        rec = O.run_port(a, self.tree, codes, cons, None, threads=self.threads)
+        return rec, time.perf_counter() - t0
+
+
+def consensus_of(codes):
+    """First non-gap code per column in row order (the rule the device generator applies, src/panman.cpp:1326-1340)."""
+    import numpy as np
+    nz = codes != 0
+    return codes[nz.argmax(0), np.arange(codes.shape[1])]
+
+
+def reference_arm(args, tree, spec, workload, n_taxa, n_cols, ncpu):
+    """bench.py --impl reference: the reference's CPU code alone -- no GPU, no product library.  Input: the CPU twin of
+    the synthetic alignment generator (oracle/synth_twin.c), a fresh random column sample per step."""
+    import numpy as np
     from oracle import oracle_api as O
-    a = 0 if algo == "fitch" else 1
-    if O.ref_available() and os.path.exists(O.REF_SO):
-        kind = "reference"
-        chars, cchars = O.codes_to_chars(host_codes), O.codes_to_chars(cons)
-        t0 = time.perf_counter()
-        rec = O.run_ref_columns(a, tree, chars, cchars, None, threads=threads)
-        dt = time.perf_counter() - t0
-    else:
-        kind = "port"
-        t0 = time.perf_counter()
-        rec = O.run_port(a, tree, host_codes, cons, None, threads=threads)
-        dt = time.perf_counter() - t0
-    return kind, dt, rec
+    V = tree.n_nodes
+    cols_per_step = args.cpu_cols or max(8, min(2048, int(1.3e8 / V)))  # a few seconds of CPU work per step
+    ref = CpuReference(tree, ncpu)
+    rng = np.random.default_rng(0)
+    times = []
+    for it in range(args.warmup + args.steps):
+        cols = np.sort(rng.choice(n_cols, size=cols_per_step, replace=False))
+        codes = O.synth_columns(tree, spec, cols, n_taxa, threads=ncpu)
+        _, dt = ref.run(args.algo, codes, consensus_of(codes))
+        if it >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    val = V * cols_per_step * len(times) / total
+    line = {"metric": "column.node updates/sec", "value": val, "unit": "updates/s", "impl": "reference",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
+            "higher_is_better": True, "scaling": "strong" if args.workload == "c3" else "weak", "vs_baseline": None,
+            "dtype": "u16 bitsets / int32 costs", "data": "synthetic", "config": {"workload": workload},
+            "cpu_baseline": {"value": val, "unit": "updates/s", "cores": ref.threads, "kind": ref.kind,
+                             "sample": f"{cols_per_step} random columns of the workload per step, all {V} nodes, "
+                                       f"{ref.threads} threads over columns, g++ -O2; the Node graph is built once, the column "
+                                       "loop alone is timed"},
+            "e2e": {"value": val, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--algo", choices=["fitch", "sankoff"], default="fitch")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", choices=["c3", "c2"], default="c3")
     ap.add_argument("--cpu-cols", type=int, default=0, help="columns of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--chunk-nodes", type=int, default=0, help="plan tuning: nodes per chunk (0 = automatic)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (tuning sweeps)")
-    ap.add_argument("--no-exchange", action="store_true", help="N > 1: skip the extra gathered-by-node leg")
-    ap.add_argument("--p-n-block", type=float, default=None, help="experiment: override the N-block rate of the synthetic MSA")
+    ap.add_argument("--no-c2", action="store_true", help="N = 1: skip the extra config-2 measurement")
+    ap.add_argument("--chunk-nodes", type=int, default=0, help="plan tuning: nodes per chunk (0 = automatic)")
+    ap.add_argument("--window-cols", type=int, default=0, help="columns per GPU and window (0 = as many as fit)")
+    ap.add_argument("--taxa", type=int, default=0, help="experiment: override the number of taxa")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -135,204 +197,326 @@ def main():
         return 0
 
     import numpy as np
-    import torch
 
-    from panman_b200 import api, trees
-
-    algo = api.FITCH if args.algo == "fitch" else api.SANKOFF
-    tree = trees.random_binary_tree(N_TAXA)
-    V = tree.n_nodes
+    from panman_b200 import trees
+    n_taxa, n_cols, _, wl_text = WORKLOADS[args.workload]
+    if args.taxa:
+        n_taxa = args.taxa
+        wl_text = wl_text.replace(str(WORKLOADS[args.workload][0]), str(n_taxa))
     ncpu = os.cpu_count() or 1
-    workload = (f"c2: synthetic SARS-CoV-2-shaped MSA, {N_TAXA} taxa x {N_COLS} columns per GPU, "
-                f"random binary tree ({V} nodes), algo={args.algo}")
-    hbm_peak, peak_src = peaks()
+    t_setup = time.time()
+    tree = trees.random_binary_tree(n_taxa)
+    V = tree.n_nodes
+    strong = args.workload == "c3"
+    workload = f"{wl_text}, random binary tree ({V} nodes), algo={args.algo}" + (f", column-sharded x{world}" if strong else "")
 
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (the synthetic MSA is generated on the GPU)")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    ctx = api.Context(tree, device=local_rank)
-    if args.chunk_nodes:
-        ctx.set_tuning(chunk_nodes=args.chunk_nodes)
-    stride = ((N_COLS + 31) // 32) * 16
-    d_msa = torch.zeros((N_TAXA, stride), dtype=torch.uint8, device=dev)
-    d_cons = torch.zeros(N_COLS, dtype=torch.uint8, device=dev)
-    torch.cuda.synchronize()
-    spec = api.SynthSpec()
-    if args.p_n_block is not None:
-        spec.p_n_block = args.p_n_block
-    ctx.synth_msa(spec, rank * N_COLS, N_COLS, d_msa.data_ptr(), stride, d_cons.data_ptr())
-
-    # ------------------------------------------------------------------ reference arm: the CPU path on the host cores
     if args.impl == "reference":
-        cols_per_step = args.cpu_cols or max(64, min(2048, 32 * ncpu))
-        rng = np.random.default_rng(0)
-        cons_h = d_cons.cpu().numpy()
-        times = []
-        full = api.unpack_nibbles(d_msa.cpu().numpy(), N_COLS)
-        for it in range(args.warmup + args.steps):
-            cols = np.sort(rng.choice(N_COLS, size=cols_per_step, replace=False))
-            sub = full[:, cols]
-            kind, dt, _ = cpu_reference_sample(tree, np.ascontiguousarray(sub), cons_h[cols], args.algo, ncpu)
-            if it >= args.warmup:
-                times.append(dt)
-        total = sum(times)
-        val = V * cols_per_step * len(times) / total
-        line = {"metric": "column.node updates/sec", "value": val, "unit": "updates/s", "impl": "reference",
-                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u16 bitsets / int32 costs",
-                "data": "synthetic", "config": {"workload": workload},
-                "cpu_baseline": {"value": val, "unit": "updates/s", "cores": ncpu, "kind": kind,
-                                 "sample": f"{cols_per_step} random columns of the workload per step, all {V} nodes, "
-                                           f"{ncpu} threads over columns, g++ -O2"},
-                "e2e": {"value": val, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        from panman_b200.api import SynthSpec  # (a dataclass: the product library is NOT loaded by this arm)
+        reference_arm(args, tree, SynthSpec(), workload, n_taxa, n_cols, ncpu)
         return 0
 
-    # ------------------------------------------------------------------ our arm
+    import torch
+
+    from panman_b200 import api, shard
+    algo = api.FITCH if args.algo == "fitch" else api.SANKOFF
+    hbm_peak, peak_src = peaks()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
-    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
-    if world > 1:
-        ctx.set_shard(rank * N_COLS, world * N_COLS, None)  # a column shard that keeps its output: global positions
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    from panman_b200 import shard
+    def allmax(x):
+        t = torch.tensor(x, device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t]
 
-    def step(exchange=False):
-        ptr, n = ctx.run_device(algo, d_msa.data_ptr(), stride, N_TAXA, N_COLS, d_cons.data_ptr())
-        if exchange:  # every rank ends up owning the complete, ordered lists of its node range
-            shard.exchange_parts(ctx, rank, world, dev)
-        return n
+    ctx = api.Context(tree, device=local_rank)
+    if args.chunk_nodes:
+        ctx.set_tuning(chunk_nodes=args.chunk_nodes)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)  # torch's stream: its events and NCCL work order with ours
+    comm = None
+    if world > 1 and strong:
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(api.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        comm = api.Comm(ctx, idt.cpu().numpy().tobytes(), rank, world)
+    spec = api.SynthSpec()
 
+    # ---- column layout.  c3: the G column groups go through in windows; in window w rank r owns the groups
+    # [w*world*gb + r*gb, +gb): its local alignment is the concatenation of its shares, window after window.
+    # c2: every rank has its own 30 000 columns of a 20 000 x (30 000*world) alignment (weak scaling, no gather).
+    G = (n_cols + 31) // 32
+    if strong:
+        share = (G + world - 1) // world                   # groups per rank if everything went in one window
+        local_groups_max = share
+    else:
+        share = local_groups_max = G
+    stride = local_groups_max * 16
+    # (allocate the alignment first: what fits per window is measured against what is free afterwards)
+    d_msa = torch.zeros((n_taxa, stride), dtype=torch.uint8, device=dev)
+    d_cons = torch.zeros(local_groups_max * 32, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+    if not strong:
+        gb, n_win = G, 1
+    else:
+        if args.window_cols:
+            gb = max(1, min(share, (args.window_cols + 31) // 32))
+        elif comm is not None:
+            gb = max(1, (comm.batch_cols(algo, share * 32) + 31) // 32)
+        else:
+            gb = min(share, 64)  # one GPU: 2 048 columns per batch leave room for the record buffers next to 120 GB of nibbles
+        n_win = (share + gb - 1) // gb
+
+    def window(w):
+        """(local group offset, global first column, columns) of this rank's share of window w.  Windows are ascending
+        column ranges; inside a window the ranks' shares are ascending with the rank; every rank's shares, window after
+        window, tile its local alignment [0, share) (the last window is narrower)."""
+        if not strong:
+            return 0, rank * n_cols, n_cols
+        width = gb if w < n_win - 1 else share - (n_win - 1) * gb
+        g_lo = min(G, w * world * gb + rank * width)
+        g_hi = min(G, g_lo + width)
+        c0 = min(n_cols, g_lo * 32)
+        return w * gb, c0, max(0, min(n_cols, g_hi * 32) - c0)
+
+    # the synthetic alignment, generated on the device window by window (a pure function of (seed, node, column))
+    for w in range(n_win):
+        lg, c0, nc = window(w)
+        for o in range(0, nc, 2048):
+            m = min(2048, nc - o)
+            ctx.synth_msa(spec, c0 + o, m, d_msa.data_ptr() + lg * 16 + o // 2, stride, d_cons.data_ptr() + lg * 32 + o)
+    torch.cuda.synchronize()
+    setup_s = time.time() - t_setup
+
+    totals = {"fwd": 0.0, "bwd": 0.0, "sort": 0.0, "xchg": 0.0, "stitch": 0.0, "launches": 0, "design_bytes": 0, "records": 0, "batches": 0}
+
+    def account(t, n):
+        totals["fwd"] += t["forward_ms"]; totals["bwd"] += t["backward_ms"]; totals["sort"] += t["sort_ms"]
+        totals["xchg"] += t["exchange_ms"]; totals["stitch"] += t["stitch_ms"]; totals["launches"] += t["n_launches"]
+        totals["design_bytes"] += t["forward_bytes"] + t["backward_bytes"]
+        totals["records"] += n
+
+    def step():
+        if not strong:
+            _, n = ctx.run_device(algo, d_msa.data_ptr(), stride, n_taxa, n_cols, d_cons.data_ptr())
+            account(ctx.timing(), n)
+            totals["batches"] += 1
+        elif comm is None:
+            n, nb = ctx.run_batched(algo, d_msa.data_ptr(), stride, n_taxa, n_cols, d_cons.data_ptr(), batch_cols=gb * 32)
+            account(ctx.timing(), n)
+            totals["batches"] += nb
+        else:
+            for w in range(n_win):
+                lg, c0, nc = window(w)
+                _, n = comm.run(algo, d_msa.data_ptr() + lg * 16, stride, n_taxa, nc, c0, n_cols, d_cons.data_ptr() + lg * 32)
+                account(ctx.timing(), n)
+                totals["batches"] += 1
+
+    if not strong and world > 1:
+        ctx.set_shard(rank * n_cols, world * n_cols, None)  # a column shard that keeps its output: global positions
     sampler = ClockSampler(local_rank)
     sampler.start()  # started before the warm-up so that nvidia-smi is already sampling when the timed region begins
     for _ in range(args.warmup):
-        n_rec = step()
+        step()
     barrier()
     sampler.mark()
+    for k in totals:
+        totals[k] = 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    pass_ms, launches = 0.0, 0
     e0.record()
     for _ in range(args.steps):
-        n_rec = step()
-        t = ctx.timing()
-        pass_ms += t["forward_ms"] + t["backward_ms"]
-        launches += t["n_launches"]
+        step()
     e1.record()
     barrier()
     clocks = sampler.stop()
-    ms = torch.tensor([e0.elapsed_time(e1), pass_ms], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    total_ms, pass_ms = float(ms[0]), float(ms[1])
-    updates_per_step = V * N_COLS * world
+    total_ms, pass_ms, xchg_ms, stitch_ms, sort_ms = allmax([e0.elapsed_time(e1), totals["fwd"] + totals["bwd"], totals["xchg"],
+                                                            totals["stitch"], totals["sort"]])
+    updates_per_step = V * n_cols * (1 if strong else world)
     value = updates_per_step * args.steps / (total_ms * 1e-3)
-    tinfo = ctx.timing()
     plan = ctx.plan_info()
-
-    # the same step followed by the all-to-all by node range (lists complete on the device of the owning rank)
-    gathered = None
-    if world > 1 and not args.no_exchange:
-        ctx.set_shard(rank * N_COLS, world * N_COLS, [b for b, _ in shard.node_ranges(V, world)] + [V])
-        xsteps = max(1, min(args.steps, 50))
-        for _ in range(3):
-            step(True)
-        barrier()
-        x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        x0.record()
-        for _ in range(xsteps):
-            step(True)
-        x1.record()
-        barrier()
-        xms = torch.tensor([x0.elapsed_time(x1)], device=dev, dtype=torch.float64)
-        dist.all_reduce(xms, op=dist.ReduceOp.MAX)
-        gathered = {"ms_per_step": float(xms[0]) / xsteps, "value": updates_per_step * xsteps / (float(xms[0]) * 1e-3),
-                    "steps": xsteps, "what": "step + NCCL all-to-all of the 8-byte records by node range + owner-side ordering"}
-        ctx.set_shard(0, 0, None)
-
-    # end to end: pinned host buffers through pmfs_run (H2D + passes + sort + D2H of the records), every step
-    h_msa = torch.empty((N_TAXA, stride), dtype=torch.uint8, pin_memory=True)
-    h_msa.copy_(d_msa)
-    h_cons = torch.empty(N_COLS, dtype=torch.uint8, pin_memory=True)
-    h_cons.copy_(d_cons)
-    torch.cuda.synchronize()
-    h_msa_np, h_cons_np = h_msa.numpy(), h_cons.numpy()
-    ctx.set_stream(0)
+    rec_all = torch.tensor([totals["records"]], device=dev, dtype=torch.float64)
     if world > 1:
-        ctx.set_shard(rank * N_COLS, world * N_COLS, None)
-    for _ in range(max(1, min(args.warmup, 2))):
-        rec = ctx.run(algo, h_msa_np, N_COLS, h_cons_np, copy=False)
-    e2e_steps = 0 if args.no_e2e else max(1, min(args.steps, 10))
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        rec = ctx.run(algo, h_msa_np, N_COLS, h_cons_np, copy=False)  # view of the context's pinned result buffer
-    torch.cuda.synchronize()
-    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_val = updates_per_step * e2e_steps / float(e2e_s[0]) if e2e_steps else None
-    e2e_phases = ctx.timing()
-    h2d = int(N_TAXA * stride + N_COLS)
-    d2h = int(rec.shape[0] * 12)
+        dist.all_reduce(rec_all)
+    records_per_step = int(float(rec_all[0]) / args.steps)
+    mine = dict(totals)
+
+    # ---- end to end through host buffers, on a column batch of the workload
+    e2e = None
+    if not args.no_e2e:
+        lg, c0, nc = window(0)
+        e_cols = min(nc, 1024 if n_taxa > 1_000_000 else n_cols)
+        e_groups = (e_cols + 31) // 32
+        h_msa = torch.empty((n_taxa, e_groups * 16), dtype=torch.uint8, pin_memory=True)
+        h_msa.copy_(d_msa[:, lg * 16: lg * 16 + e_groups * 16])
+        h_cons = torch.empty(e_cols, dtype=torch.uint8, pin_memory=True)
+        h_cons.copy_(d_cons[lg * 32: lg * 32 + e_cols])
+        torch.cuda.synchronize()
+        e_steps = max(1, min(args.steps, 3 if n_taxa > 1_000_000 else 10))
+        if comm is None:
+            if world > 1:
+                ctx.set_shard(rank * n_cols, world * n_cols, None)
+            h_msa_np, h_cons_np = h_msa.numpy(), h_cons.numpy()
+
+            def e_step():
+                return ctx.run(algo, h_msa_np, e_cols, h_cons_np, copy=False).shape[0]
+        else:
+            dd_msa = torch.empty((n_taxa, e_groups * 16), dtype=torch.uint8, device=dev)
+            dd_cons = torch.empty(e_cols, dtype=torch.uint8, device=dev)
+            h_out = torch.empty(0, dtype=torch.uint8, pin_memory=True)
+            e_total = e_cols * world  # every rank brings e_cols columns: one window of the job
+
+            def e_step():
+                nonlocal h_out
+                dd_msa.copy_(h_msa, non_blocking=True)
+                dd_cons.copy_(h_cons, non_blocking=True)
+                _, n = comm.run(algo, dd_msa.data_ptr(), e_groups * 16, n_taxa, e_cols, rank * e_cols, e_total, dd_cons.data_ptr())
+                if h_out.numel() < n * 12:
+                    h_out = torch.empty(int(n * 12 * 1.25) + 1024, dtype=torch.uint8, pin_memory=True)
+                ctx.download_into(h_out.data_ptr(), n)
+                return n
+        for _ in range(2):
+            n_e = e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            n_e = e_step()
+        torch.cuda.synchronize()
+        (e_s,) = allmax([time.perf_counter() - t0])
+        e_updates = V * e_cols * world
+        e2e = {"value": e_updates * e_steps / e_s, "unit": "updates/s", "h2d_bytes_per_step": int(n_taxa * e_groups * 16 + e_cols),
+               "d2h_bytes_per_step": int(n_e * 12), "steps": e_steps,
+               "what": (f"host buffers in, host records out on a {e_cols}-column batch per GPU of the workload "
+                        + ("(pmfs_run, pinned buffers)" if comm is None else
+                           "(H2D of the rank's columns, pmfs_comm_run with the NCCL gather, D2H of the rank's node range)")
+                        + "; bytes are per rank"),
+               "phases_ms_last_step": {k: ctx.timing()[k] for k in ("h2d_ms", "forward_ms", "backward_ms", "sort_ms", "d2h_ms",
+                                                                     "exchange_ms", "stitch_ms")}}
+        del h_msa
+        if world > 1 and not strong:
+            ctx.set_shard(0, 0, None)
 
     if rank == 0:
         b = B_CONTRACT[args.algo]
-        per_step_pass_s = pass_ms * 1e-3 / args.steps
-        achieved = V * N_COLS * b / per_step_pass_s / 1e9  # per GPU
-        design_bytes = tinfo["forward_bytes"] + tinfo["backward_bytes"]
+        pass_s = pass_ms * 1e-3 / args.steps                 # fwd + bwd kernel time of one step on the slowest rank
+        design = mine["design_bytes"] / args.steps + 8.0 * mine["records"] / args.steps   # this rank's bytes per step
+        per_gpu_updates = V * n_cols / (world if strong else 1)
+        achieved = design / pass_s / 1e9
+        step_s = total_ms * 1e-3 / args.steps
+        traffic = ncu_traffic(args.workload, args.algo)
         line = {
             "metric": "column.node updates/sec", "value": value, "unit": "updates/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "strong" if strong else "weak",
             "vs_baseline": None, "dtype": "u32 bit-planes (16-state sets, 4-bit codes)", "data": "synthetic",
-            "config": {"workload": workload, "l2": "inputs larger than L2 (MSA 300 MB + set array 1.2 GB touched per step)",
-                       "parallelism": (f"column shards x{world}, no data-path collective: every rank keeps the (node,pos)-ordered "
-                                       "records of its own columns (global positions); a node's list is the concatenation "
-                                       "over ranks") if world > 1 else "1 GPU",
-                       "gathered_by_node": gathered,
-                       "records_per_step": int(n_rec), "plan": plan},
+            "config": {"workload": workload,
+                       "l2": "inputs larger than L2 (alignment and set arrays are tens of GB per GPU)" if strong else
+                             "inputs larger than L2 (MSA 300 MB + set array 1.2 GB touched per step)",
+                       "parallelism": (f"column shards x{world}; per window every rank runs the whole tree over its columns, then the "
+                                       "per-node lists are gathered by node range with NCCL (pmfs_comm_run) inside the timed step"
+                                       if comm is not None else
+                                       (f"column shards x{world}, no data-path collective (weak scaling)" if world > 1 else "1 GPU")),
+                       "windows_per_step": mine["batches"] // args.steps, "columns_per_gpu_and_window": gb * 32,
+                       "records_per_step": records_per_step, "plan": plan, "setup_s": round(setup_s, 1)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                         "traffic": ncu_traffic(args.algo), "peak_source": peak_src,
-                         "traffic_note": "dram__bytes_read+write of fwd_kernel+bwd_kernel per step, ncu --set full capture of "
-                                         "this workload (profiles/traffic_r1.json); algorithmic bytes at the contract "
-                                         "figure: %.3e" % (V * N_COLS * b),
-                         "kernel": "fwd_kernel + bwd_kernel (all chunk levels of one step)",
-                         "bytes_per_update_contract": b, "pass_ms_per_step": 1e3 * per_step_pass_s,
-                         "frac_whole_step": V * N_COLS * b / (total_ms * 1e-3 / args.steps) / 1e9 / hbm_peak / world,
-                         "bytes_per_update_design": design_bytes / (V * N_COLS),
-                         "achieved_design_gbs": design_bytes / per_step_pass_s / 1e9},
-            "e2e": {"value": e2e_val, "unit": "updates/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps, "phases_ms_last_step": {k: e2e_phases[k] for k in
-                                                                ("h2d_ms", "forward_ms", "backward_ms", "sort_ms", "d2h_ms")}},
-            "gpu_launches": int(launches), "clocks": clocks,
-            "phases_ms_last_step": {k: tinfo[k] for k in ("forward_ms", "backward_ms", "sort_ms", "wall_ms")},
+                         "kernel": "fwd_kernel + bwd_kernel (every work item of one step, per GPU)",
+                         "bytes": "design bytes: what the walk kernels must move (leaf nibbles once per pass, every internal "
+                                  "node's set written once and read once, D1 for Sankoff, 8 B per record), DESIGN.md §5",
+                         "bytes_per_update_design": design / per_gpu_updates, "pass_ms_per_step": 1e3 * pass_s,
+                         "peak_source": peak_src, "traffic": None if traffic is None else traffic.get("traffic_bytes_per_step"),
+                         "traffic_source": None if traffic is None else traffic.get("source"),
+                         "frac_contract": per_gpu_updates * b / pass_s / 1e9 / hbm_peak, "bytes_per_update_contract": b,
+                         "frac_whole_step": design / step_s / 1e9 / hbm_peak},
+            "e2e": e2e, "gpu_launches": int(mine["launches"]), "clocks": clocks,
+            "phases_ms_per_step": {"forward+backward": pass_ms / args.steps, "ordering": sort_ms / args.steps,
+                                   "exchange": xchg_ms / args.steps, "stitch": stitch_ms / args.steps},
         }
         if world == 1 and not args.no_cpu_baseline:
-            cols_n = args.cpu_cols or 8192  # about 10 s (Fitch) to 30 s (Sankoff) of CPU work on 16 cores
-            cols = np.sort(np.random.default_rng(0).choice(N_COLS, size=cols_n, replace=False))
-            full = api.unpack_nibbles(h_msa_np, N_COLS)
-            sub = np.ascontiguousarray(full[:, cols])
-            kind, dt, want = cpu_reference_sample(tree, sub, h_cons_np[cols], args.algo, ncpu)
-            # the sample doubles as a parity check of the benchmarked run
-            sel = np.isin(rec["pos"], cols)
-            mine = rec[sel].copy()
-            mine["pos"] = np.searchsorted(cols, mine["pos"])
-            mine = mine[np.lexsort((mine["pos"], mine["node"]))]
-            exact = mine.shape == want.shape and all((mine[k] == want[k]).all() for k in ("node", "pos", "type", "code"))
-            line["cpu_baseline"] = {"value": V * cols_n / dt, "unit": "updates/s", "cores": ncpu, "kind": kind,
-                                    "sample": f"{cols_n} random columns of the workload, all {V} nodes, {ncpu} threads over "
-                                              f"columns, g++ -O2, {dt:.2f} s", "bit_exact_on_sample": bool(exact)}
+            line["cpu_baseline"] = cpu_baseline(args, ctx, tree, algo, d_msa, d_cons, stride, n_taxa, n_cols, ncpu)
+        if world == 1 and strong and not args.no_c2:
+            line["c2_single_gpu"] = c2_leg(args, algo, hbm_peak)
         print(json.dumps(line))
+    if comm is not None:
+        comm.close()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
     ctx.close()
     return 0
+
+
+def cpu_baseline(args, ctx, tree, algo, d_msa, d_cons, stride, n_taxa, n_cols, ncpu):
+    """The reference's CPU code on a random column sample of the benchmarked alignment (rank 0, N = 1), doubling as a
+    bit-exactness check of the benchmarked path."""
+    import numpy as np
+    import torch
+
+    from panman_b200 import shard
+    V = tree.n_nodes
+    span = min(n_cols, 2048)  # sample inside the first columns: one device run of `span` columns gives the CUDA records
+    cols_n = args.cpu_cols or max(8, min(8192, int(6e8 / V)))
+    cols = np.sort(np.random.default_rng(0).choice(span, size=min(cols_n, span), replace=False))
+    byte_cols = torch.from_numpy(cols // 2).to(d_msa.device)
+    sub_bytes = d_msa[:, byte_cols].cpu().numpy()
+    sub = np.ascontiguousarray(np.where(cols % 2 == 0, sub_bytes & 15, sub_bytes >> 4).astype(np.uint8))
+    cons = d_cons[:span].cpu().numpy()[cols]
+    ref = CpuReference(tree, ncpu)
+    want, dt = ref.run(args.algo, sub, cons)
+    ptr, n = ctx.run_device(algo, d_msa.data_ptr(), stride, n_taxa, span, d_cons.data_ptr())
+    t = shard.records_as_tensor(ptr, n, d_msa.device)
+    sel = torch.isin(t[:, 1], torch.from_numpy(cols.astype(np.int32)).to(d_msa.device))
+    mine = shard.records_to_numpy(t[sel])
+    mine["pos"] = np.searchsorted(cols, mine["pos"])
+    mine = mine[np.lexsort((mine["pos"], mine["node"]))]
+    exact = mine.shape == want.shape and all((mine[k] == want[k]).all() for k in ("node", "pos", "type", "code"))
+    return {"value": V * cols.size / dt, "unit": "updates/s", "cores": ref.threads, "kind": ref.kind,
+            "sample": f"{cols.size} random columns of the workload, all {V} nodes, {ref.threads} threads over columns, "
+                      f"g++ -O2, {dt:.2f} s (column loop; the Node graph is built once, untimed)",
+            "bit_exact_on_sample": bool(exact)}
+
+
+def c2_leg(args, algo, hbm_peak):
+    """BASELINE config 2 (20 000 taxa x 30 000 columns, one GPU, everything in one pass) measured in the same run."""
+    import torch
+
+    from panman_b200 import api, trees
+    n_taxa, n_cols = WORKLOADS["c2"][:2]
+    tree = trees.random_binary_tree(n_taxa)
+    V = tree.n_nodes
+    stride = ((n_cols + 31) // 32) * 16
+    with api.Context(tree) as ctx:
+        ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+        d_msa = torch.zeros((n_taxa, stride), dtype=torch.uint8, device="cuda")
+        d_cons = torch.zeros(n_cols, dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        ctx.synth_msa(api.SynthSpec(), 0, n_cols, d_msa.data_ptr(), stride, d_cons.data_ptr())
+        for _ in range(5):
+            ctx.run_device(algo, d_msa.data_ptr(), stride, n_taxa, n_cols, d_cons.data_ptr())
+        torch.cuda.synchronize()
+        steps, pass_ms, design, n = 50, 0.0, 0, 0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            _, n = ctx.run_device(algo, d_msa.data_ptr(), stride, n_taxa, n_cols, d_cons.data_ptr())
+            t = ctx.timing()
+            pass_ms += t["forward_ms"] + t["backward_ms"]
+            design = t["forward_bytes"] + t["backward_bytes"] + 8 * n
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        return {"workload": "c2: 20000 taxa x 30000 columns, random binary tree (39999 nodes), one pass",
+                "value": V * n_cols / (ms * 1e-3), "ms_per_step": ms, "steps": steps, "records_per_step": int(n),
+                "roofline_frac": design / (pass_ms / steps * 1e-3) / 1e9 / hbm_peak,
+                "frac_whole_step": design / (ms * 1e-3) / 1e9 / hbm_peak, "pass_ms_per_step": pass_ms / steps}
 
 
 if __name__ == "__main__":

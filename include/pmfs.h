@@ -75,6 +75,8 @@ typedef struct {
     int64_t forward_bytes;  /* design-level HBM bytes of the forward pass ("bytes per update") */
     int64_t backward_bytes; /* same for the backward pass, excluding emitted records */
     float wall_ms;          /* host wall clock of the device-resident part of the call (launch + sync overheads included) */
+    float exchange_ms;      /* pmfs_comm_run: cut points + NCCL exchange of the records by node range */
+    float stitch_ms;        /* pmfs_comm_run: owner-side merge of the received slices */
 } pmfs_timing;
 
 const char* pmfs_last_error(void);
@@ -194,7 +196,49 @@ int pmfs_set_shard(pmfs_ctx* ctx, int64_t pos_offset, int64_t total_cols, int32_
 int pmfs_get_parts(pmfs_ctx* ctx, const void** d_records, int64_t* offsets, int64_t* counts, int* column_ordered);
 int pmfs_sort_records(pmfs_ctx* ctx, void* d_records, int64_t n, int column_ordered, pmfs_mut** d_out);
 
-/* Copies device records of the last pmfs_run_device / pmfs_sort_records to a caller buffer of at least n records. */
+/* ---- column shards gathered by node range with NCCL (BASELINE north_star: "Each GPU runs the full tree over its column
+ * range, and the per-node mutation lists are gathered with NCCL over NVLink").  No counterpart in the reference, which
+ * is a single process on host cores.
+ * A pmfs_comm joins one context (= one GPU) to `world` ranks.  Multi-process use (one process per GPU, e.g. under
+ * torchrun or MPI): rank 0 calls pmfs_comm_unique_id and ships the 128 bytes to the others by whatever means the job
+ * has, then every rank calls pmfs_comm_create (ncclCommInitRank underneath; NCCL is loaded at run time, world = 1 needs
+ * none).  Node ids are split evenly: rank r owns nodes [V*r/world, V*(r+1)/world) (pmfs_comm_node_range).
+ * pmfs_comm_run is collective: every rank runs the pass over ITS columns [col_offset, col_offset+n_cols) of a
+ * total_cols-wide alignment (n_cols = 0 is allowed: the rank only receives), the (node,pos)-ordered 64-bit records are
+ * cut at the owners' node boundaries, exchanged in one NCCL group (8 bytes per record) and stitched by the owner: the
+ * ranks' column ranges must be disjoint and ascending with the rank, so a node's list is the concatenation of its runs in
+ * rank order -- no sort.  On return *d_out (device, owned by the context, valid until the next run) holds the COMPLETE
+ * lists of the rank's node range over all ranks' columns, ordered by (node,pos), global positions; pmfs_download and
+ * pmfs_pack_last apply to it (the <=6-run packing must come after the gather: runs straddle shard boundaries).  An
+ * alignment that does not fit is run as several calls over ascending column windows, each window split over the ranks
+ * (pmfs_comm_batch_cols gives the columns per rank and call that fit on every GPU); a node's list is then the
+ * concatenation over the calls.  If a rank fails, the others may block in NCCL: treat an error as fatal for the job. */
+typedef struct pmfs_comm pmfs_comm;
+int pmfs_comm_unique_id(void* id128);
+int pmfs_comm_create(pmfs_comm** comm, pmfs_ctx* ctx, const void* id128, int rank, int world);
+void pmfs_comm_destroy(pmfs_comm* comm);
+int pmfs_comm_node_range(pmfs_comm* comm, int rank, int32_t* node_begin, int32_t* node_end);
+int pmfs_comm_batch_cols(pmfs_comm* comm, int algo, int64_t cols_per_rank, int64_t bytes_per_col, int64_t* batch_cols);
+int pmfs_comm_run(pmfs_comm* comm, int algo, const uint8_t* d_msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
+                  int64_t n_cols, int64_t col_offset, int64_t total_cols, const uint8_t* d_consensus_code,
+                  const uint8_t* d_root_forced_code, pmfs_mut** d_out, int64_t* n_out);
+/* The same ranks as contexts of ONE process (same or different GPUs), exchanging by device-to-device copies at host
+ * barriers instead of NCCL: every rank must then be driven by its own host thread. */
+int pmfs_comm_create_local(pmfs_comm** comms, pmfs_ctx* const* ctxs, int world);
+
+/* One process, several GPUs -- what a C++ panmanUtils links against (src/panman.cpp:1264, :1457: the MSA-driven Tree
+ * constructors): same contract as pmfs_run (host alignment in, ONE (node,pos)-ordered host array out, valid until the
+ * next call), with the columns spread over n_gpus devices (devices = NULL: 0 .. n_gpus-1), one host thread and one
+ * context per device, ncclCommInitAll underneath.  window_cols > 0 caps the columns in flight over all GPUs
+ * (0 = as many as fit). */
+typedef struct pmfs_multi pmfs_multi;
+int pmfs_multi_create(pmfs_multi** m, const pmfs_tree* tree, int n_gpus, const int* devices);
+void pmfs_multi_destroy(pmfs_multi* m);
+int pmfs_multi_run(pmfs_multi* m, int algo, const uint8_t* msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
+                   int64_t n_cols, const uint8_t* consensus_code, const uint8_t* root_forced_code, int64_t window_cols,
+                   pmfs_mut** out, int64_t* n_out);
+
+/* Copies device records of the last pmfs_run_device / pmfs_sort_records / pmfs_comm_run to a caller buffer of at least n records. */
 int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);
 
 /* Fitch pass that allocates nothing.  This entry point has no counterpart in the reference.

@@ -115,6 +115,33 @@ def run_port(algo: int, tree: FlatTree, msa_codes: np.ndarray, consensus: np.nda
     return _take(lib.pmo_free, out, n.value, MUT_DTYPE)
 
 
+class _SynthSpec(C.Structure):
+    _fields_ = [("seed", C.c_uint64), ("p_sub", C.c_float), ("p_del", C.c_float), ("p_ins", C.c_float),
+                ("p_n_block", C.c_float), ("p_amb", C.c_float), ("accessory_frac", C.c_float)]
+
+
+def synth_columns(tree: FlatTree, spec, cols: np.ndarray, n_rows: int, threads: int = 1) -> np.ndarray:
+    """CPU twin of the product's device-side synthetic alignment generator (oracle/synth_twin.c): codes
+    [n_rows, len(cols)] of the given GLOBAL columns.  spec: any object with the pmfs_synth_spec fields."""
+    lib = port_lib()
+    s = _SynthSpec(spec.seed, spec.p_sub, spec.p_del, spec.p_ins, spec.p_n_block, spec.p_amb, spec.accessory_frac)
+    c = np.ascontiguousarray(cols, dtype=np.int64)
+    out = np.zeros((n_rows, c.shape[0]), np.uint8)
+    par, lrow = _i32(tree.parent), _i32(tree.leaf_row)
+    rc = lib.pmo_synth(C.c_int32(tree.n_nodes), _ptr(par, C.c_int32), _ptr(lrow, C.c_int32), C.c_int32(n_rows), C.byref(s),
+                       _ptr(c, C.c_int64), C.c_int64(c.shape[0]), C.c_int(threads), _ptr(out, C.c_uint8))
+    if rc != 0:
+        raise RuntimeError(f"pmo_synth rc={rc}")
+    return out
+
+
+def last_ref_loop_seconds() -> float:
+    """Wall time of the column loop of the last run_ref_columns call (graph construction excluded)."""
+    lib = ref_lib()
+    lib.pmref_last_loop_seconds.restype = C.c_double
+    return float(lib.pmref_last_loop_seconds())
+
+
 def codes_to_chars(codes: np.ndarray) -> np.ndarray:
     lut = np.frombuffer(CODE_CHARS.encode(), dtype=np.uint8)
     return lut[np.asarray(codes, dtype=np.uint8)]
@@ -146,6 +173,36 @@ def run_ref_columns(algo: int, tree: FlatTree, msa_chars: np.ndarray, consensus_
     if rc != 0:
         raise RuntimeError(f"pmref_columns rc={rc}")
     return _take(lib.pmref_free, out, n.value, MUT_DTYPE)
+
+
+class RefGraph:
+    """The reference's Node graph for a flat tree, built once (oracle/ref_driver.cpp: pmref_graph_new) so that repeated
+    column samples on a big tree do not pay the graph construction every time."""
+
+    def __init__(self, tree: FlatTree):
+        self._lib = ref_lib()
+        self._lib.pmref_graph_new.restype = C.c_void_p
+        self._lib.pmref_graph_free.argtypes = [C.c_void_p]
+        par, coff, cidx, lrow = _i32(tree.parent), _i32(tree.child_off), _i32(tree.child_idx), _i32(tree.leaf_row)
+        self._h = C.c_void_p(self._lib.pmref_graph_new(C.c_int32(tree.n_nodes), _ptr(par, C.c_int32), _ptr(coff, C.c_int32),
+                                                       _ptr(cidx, C.c_int32), _ptr(lrow, C.c_int32)))
+
+    def columns(self, algo: int, msa_chars: np.ndarray, consensus_chars: np.ndarray, forced_chars=None, threads: int = 1):
+        msa = np.ascontiguousarray(msa_chars, dtype=np.uint8)
+        cons = np.ascontiguousarray(consensus_chars, dtype=np.uint8)
+        frc = None if forced_chars is None else np.ascontiguousarray(forced_chars, dtype=np.uint8)
+        out, n = C.c_void_p(), C.c_int64()
+        rc = self._lib.pmref_columns_g(self._h, C.c_int(algo), C.c_int32(msa.shape[0]), C.c_int64(cons.shape[0]), _ptr(msa, C.c_char),
+                                       _ptr(cons, C.c_char), None if frc is None else _ptr(frc, C.c_char), C.c_int(threads),
+                                       C.byref(out), C.byref(n))
+        if rc != 0:
+            raise RuntimeError(f"pmref_columns_g rc={rc}")
+        return _take(self._lib.pmref_free, out, n.value, MUT_DTYPE)
+
+    def close(self):
+        if self._h:
+            self._lib.pmref_graph_free(self._h)
+            self._h = None
 
 
 def run_ref_blocks(algo: int, tree: FlatTree, states: np.ndarray, forced=None):

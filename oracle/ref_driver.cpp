@@ -27,6 +27,7 @@
 
 #include <atomic>
 #include <cctype>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -275,6 +276,7 @@ struct ColumnJob {
     const char* forced = nullptr;  // reference row chars or nullptr
     int64_t nCols = 0;
     std::atomic<int64_t> next{0};
+    int64_t chunk = 16;  // columns a thread takes at a time (smaller for small samples, so that every thread gets work)
     std::mutex outMutex;
     std::vector<RefMut>* out = nullptr;
 };
@@ -284,9 +286,9 @@ void runColumns(ColumnJob* job) {
     std::vector<RefMut> local;
     Tree& T = *job->tree;
     for (;;) {
-        int64_t begin = job->next.fetch_add(16);
+        int64_t begin = job->next.fetch_add(job->chunk);
         if (begin >= job->nCols) break;
-        int64_t end = std::min(begin + 16, job->nCols);
+        int64_t end = std::min(begin + job->chunk, job->nCols);
         for (int64_t i = begin; i < end; i++) {
             std::unordered_map<std::string, std::pair<panmanUtils::NucMutationType, char>> mutations;
             if (job->algo == 0) {
@@ -342,9 +344,15 @@ size_t maxLevel(const NodeGraph& g) {
     return m;
 }
 
+// Wall time of the last column loop (threads + the final sort), excluding the construction of the Node graph and of the
+// row table around it -- those are one-off set-up in the reference too (createTreeFromNewickString, the FASTA read).
+double g_lastLoopSeconds = 0;
+
 // Runs the column loop on `nThreads` big-stack threads; output sorted by (node, pos) == per-node std::sort order.
 void runAllColumns(ColumnJob& job, int nThreads, size_t depth) {
+    const auto loopT0 = std::chrono::steady_clock::now();
     if (nThreads < 1) nThreads = 1;
+    job.chunk = std::max<int64_t>(1, std::min<int64_t>(16, job.nCols / (4 * (int64_t)nThreads)));
     size_t stackBytes = (size_t)64 << 20;
     stackBytes += depth * 2048;  // Sankoff frames hold vector<vector<int>>; generous per-level allowance
     std::vector<pthread_t> th(nThreads);
@@ -357,6 +365,7 @@ void runAllColumns(ColumnJob& job, int nThreads, size_t depth) {
     std::sort(job.out->begin(), job.out->end(), [](const RefMut& a, const RefMut& b) {
         return a.node != b.node ? a.node < b.node : a.pos < b.pos;
     });
+    g_lastLoopSeconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - loopT0).count();
 }
 
 bool anyLeafPresent(const NodeGraph& g, const std::vector<std::pair<std::string, const char*>>& rows) {
@@ -421,15 +430,22 @@ typedef RefMut pmref_mut;
 typedef RefNucMut pmref_nucmut;
 
 void pmref_free(void* p) { free(p); }
+double pmref_last_loop_seconds(void) { return g_lastLoopSeconds; }
 
 // Column loop over a flat tree.  Node i is named "node_<k>" if internal (k = 1 + number of internal nodes before it in
 // pre-order, i.e. the reference's numbering), "r<row>" if leaf_row[i] >= 0, "absent_<i>" if leaf_row[i] == -2.  MSA rows
 // are keyed "r<row>" and inserted in row order.  msa is [n_rows][n_cols] CHARACTERS; consensus/forced are characters.
 // Returns 0, -4 (Sankoff with no tree leaf present in the MSA and no forced root: the reference asserts).
-int pmref_columns(int algo, int32_t n_nodes, const int32_t* parent, const int32_t* child_off, const int32_t* child_idx,
-                  const int32_t* leaf_row, int32_t n_rows, int64_t n_cols, const char* msa, const char* consensus,
-                  const char* forced, int n_threads, pmref_mut** out, int64_t* n_out) {
+struct RefGraph {  // a flat tree turned into the reference's Node graph, kept across calls
     NodeGraph g;
+    Tree tree;
+    size_t depth = 1;
+};
+
+void* pmref_graph_new(int32_t n_nodes, const int32_t* parent, const int32_t* child_off, const int32_t* child_idx,
+                      const int32_t* leaf_row) {
+    RefGraph* R = new RefGraph();
+    NodeGraph& g = R->g;
     g.nodes.resize(n_nodes);
     int internal = 0;
     for (int i = 0; i < n_nodes; i++) {
@@ -450,26 +466,43 @@ int pmref_columns(int algo, int32_t n_nodes, const int32_t* parent, const int32_
         Node* n = g.nodes[i];
         n->level = n->parent ? n->parent->level + 1 : 1;
     }
-    Tree tree;
-    tree.root = g.nodes[0];
-    std::vector<std::string> rowIds(n_rows);
+    R->tree.root = g.nodes[0];
+    R->depth = maxLevel(g);
+    return R;
+}
+
+void pmref_graph_free(void* graph) { delete static_cast<RefGraph*>(graph); }
+
+// The column loop on a graph built by pmref_graph_new (bench.py's reference arm calls it once per step).
+int pmref_columns_g(void* graph, int algo, int32_t n_rows, int64_t n_cols, const char* msa, const char* consensus,
+                    const char* forced, int n_threads, pmref_mut** out, int64_t* n_out) {
+    RefGraph* R = static_cast<RefGraph*>(graph);
     std::vector<std::pair<std::string, const char*>> rows;
     for (int r = 0; r < n_rows; r++) rows.emplace_back("r" + std::to_string(r), msa + (size_t)r * n_cols);
-    if (algo == 1 && !forced && !anyLeafPresent(g, rows)) return -4;
+    if (algo == 1 && !forced && !anyLeafPresent(R->g, rows)) return -4;
     std::vector<RefMut> muts;
     ColumnJob job;
     job.algo = algo;
-    job.tree = &tree;
-    job.graph = &g;
+    job.tree = &R->tree;
+    job.graph = &R->g;
     job.rows = &rows;
     job.consensus = consensus;
     job.forced = forced;
     job.nCols = n_cols;
     job.out = &muts;
-    runAllColumns(job, n_threads, maxLevel(g));
+    runAllColumns(job, n_threads, R->depth);
     *out = dupArray(muts);
     *n_out = (int64_t)muts.size();
     return 0;
+}
+
+int pmref_columns(int algo, int32_t n_nodes, const int32_t* parent, const int32_t* child_off, const int32_t* child_idx,
+                  const int32_t* leaf_row, int32_t n_rows, int64_t n_cols, const char* msa, const char* consensus,
+                  const char* forced, int n_threads, pmref_mut** out, int64_t* n_out) {
+    void* graph = pmref_graph_new(n_nodes, parent, child_off, child_idx, leaf_row);
+    const int rc = pmref_columns_g(graph, algo, n_rows, n_cols, msa, consensus, forced, n_threads, out, n_out);
+    pmref_graph_free(graph);
+    return rc;
 }
 
 // Block-level passes (the per-block loop of the PanGraph branch, src/panman.cpp:865-950, restated; its callers build

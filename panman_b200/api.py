@@ -44,7 +44,7 @@ class _Tree(C.Structure):
 class _Timing(C.Structure):
     _fields_ = [("h2d_ms", C.c_float), ("forward_ms", C.c_float), ("backward_ms", C.c_float), ("sort_ms", C.c_float),
                 ("d2h_ms", C.c_float), ("total_ms", C.c_float), ("n_launches", C.c_int64), ("forward_bytes", C.c_int64),
-                ("backward_bytes", C.c_int64), ("wall_ms", C.c_float)]
+                ("backward_bytes", C.c_int64), ("wall_ms", C.c_float), ("exchange_ms", C.c_float), ("stitch_ms", C.c_float)]
 
 
 class _PlanInfo(C.Structure):
@@ -75,7 +75,7 @@ BATCH_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.
 _lib = None
 
 EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_tile", "pmfs_set_watchdog", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_codes",
-           "pmfs_result_free", "pmfs_run_device", "pmfs_run_batched", "pmfs_set_batch_cols", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
+           "pmfs_result_free", "pmfs_run_device", "pmfs_run_batched", "pmfs_set_batch_cols", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_comm_unique_id", "pmfs_comm_create", "pmfs_comm_create_local", "pmfs_comm_destroy", "pmfs_comm_node_range", "pmfs_comm_batch_cols", "pmfs_comm_run", "pmfs_multi_create", "pmfs_multi_destroy", "pmfs_multi_run", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
 
@@ -112,6 +112,20 @@ def lib():
         L.pmfs_set_shard.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]
         L.pmfs_get_parts.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]
         L.pmfs_sort_records.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.POINTER(C.c_void_p)]
+        L.pmfs_comm_unique_id.argtypes = [C.c_void_p]
+        L.pmfs_comm_create.argtypes = [C.POINTER(C.c_void_p), C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        L.pmfs_comm_create_local.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int]
+        L.pmfs_comm_destroy.argtypes = [C.c_void_p]
+        L.pmfs_comm_destroy.restype = None
+        L.pmfs_comm_node_range.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        L.pmfs_comm_batch_cols.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]
+        L.pmfs_comm_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_int64, C.c_int64,
+                                    C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+        L.pmfs_multi_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(_Tree), C.c_int, C.c_void_p]
+        L.pmfs_multi_destroy.argtypes = [C.c_void_p]
+        L.pmfs_multi_destroy.restype = None
+        L.pmfs_multi_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
+                                     C.c_int64, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
         L.pmfs_pack_last.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_void_p)]
         L.pmfs_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.pmfs_get_timing.argtypes = [C.c_void_p, C.POINTER(_Timing)]
@@ -326,6 +340,10 @@ class Context:
         _check(self._L.pmfs_download(self._h, res.ctypes.data, n))
         return res
 
+    def download_into(self, host_ptr: int, n: int):
+        """pmfs_download into a caller buffer (e.g. pinned memory) of at least n records."""
+        _check(self._L.pmfs_download(self._h, host_ptr, n))
+
     def timing(self) -> dict:
         t = _Timing()
         _check(self._L.pmfs_get_timing(self._h, C.byref(t)))
@@ -339,3 +357,91 @@ class Context:
     def synth_msa(self, spec: SynthSpec, col_begin: int, n_cols: int, d_msa: int, row_stride: int, d_cons: int = 0):
         s = _Synth(spec.seed, spec.p_sub, spec.p_del, spec.p_ins, spec.p_n_block, spec.p_amb, spec.accessory_frac)
         _check(self._L.pmfs_synth_msa(self._h, C.byref(s), col_begin, n_cols, d_msa, row_stride, d_cons or None))
+
+
+def comm_unique_id() -> bytes:
+    """pmfs_comm_unique_id: the 128 bytes rank 0 creates and every rank passes to Comm (ship them as you like)."""
+    buf = C.create_string_buffer(128)
+    _check(lib().pmfs_comm_unique_id(buf))
+    return buf.raw
+
+
+class Comm:
+    """One rank of a group of contexts (one GPU each) whose per-node lists are gathered by node range (pmfs_comm_*)."""
+
+    def __init__(self, ctx: Context, unique_id: bytes | None, rank: int, world: int, _handle=None):
+        self._L = lib()
+        self.ctx, self.rank, self.world = ctx, rank, world
+        if _handle is not None:
+            self._h = _handle
+            return
+        self._h = C.c_void_p()
+        idbuf = C.create_string_buffer(unique_id, 128) if unique_id is not None else None
+        _check(self._L.pmfs_comm_create(C.byref(self._h), ctx._h, idbuf, rank, world))
+
+    @staticmethod
+    def local_group(ctxs):
+        """Communicators over contexts of THIS process that exchange by device copies (pmfs_comm_create_local); every
+        rank must be driven by its own host thread."""
+        n = len(ctxs)
+        hs = (C.c_void_p * n)()
+        cs = (C.c_void_p * n)(*[c._h for c in ctxs])
+        _check(lib().pmfs_comm_create_local(hs, cs, n))
+        return [Comm(ctxs[r], None, r, n, _handle=C.c_void_p(hs[r])) for r in range(n)]
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.pmfs_comm_destroy(self._h)
+            self._h = None
+
+    def node_range(self, rank: int | None = None):
+        b, e = C.c_int32(), C.c_int32()
+        _check(self._L.pmfs_comm_node_range(self._h, self.rank if rank is None else rank, C.byref(b), C.byref(e)))
+        return b.value, e.value
+
+    def batch_cols(self, algo: int, cols_per_rank: int, bytes_per_col: int = 0) -> int:
+        out = C.c_int64()
+        _check(self._L.pmfs_comm_batch_cols(self._h, algo, cols_per_rank, bytes_per_col, C.byref(out)))
+        return out.value
+
+    def run(self, algo: int, d_msa: int, row_stride: int, n_rows: int, n_cols: int, col_offset: int, total_cols: int,
+            d_cons: int, d_forced: int = 0):
+        """Collective.  -> (device pointer to this rank's node range of pmfs_mut records, count)."""
+        out, n = C.c_void_p(), C.c_int64()
+        _check(self._L.pmfs_comm_run(self._h, algo, d_msa or None, row_stride, n_rows, n_cols, col_offset, total_cols,
+                                     d_cons or None, d_forced or None, C.byref(out), C.byref(n)))
+        return out.value or 0, n.value
+
+
+class Multi:
+    """One process, several GPUs (pmfs_multi_*): host alignment in, one (node,pos)-ordered host array out."""
+
+    def __init__(self, tree, n_gpus: int, devices=None):
+        self._L = lib()
+        self._keep = [_i32(tree.parent), _i32(tree.child_off), _i32(tree.child_idx), _i32(tree.leaf_row)]
+        t = _Tree(int(self._keep[0].shape[0]), *[a.ctypes.data_as(C.POINTER(C.c_int32)) for a in self._keep])
+        self._h = C.c_void_p()
+        dev = None if devices is None else np.ascontiguousarray(devices, dtype=np.int32)
+        _check(self._L.pmfs_multi_create(C.byref(self._h), C.byref(t), n_gpus, None if dev is None else dev.ctypes.data))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.pmfs_multi_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def run(self, algo: int, msa_nibbles: np.ndarray, n_cols: int, consensus: np.ndarray, forced=None, window_cols: int = 0):
+        msa = np.ascontiguousarray(msa_nibbles, dtype=np.uint8)
+        cons = np.ascontiguousarray(consensus, dtype=np.uint8)
+        frc = None if forced is None else np.ascontiguousarray(forced, dtype=np.uint8)
+        out, n = C.c_void_p(), C.c_int64()
+        _check(self._L.pmfs_multi_run(self._h, algo, msa.ctypes.data, msa.shape[1], msa.shape[0], n_cols, cons.ctypes.data,
+                                      None if frc is None else frc.ctypes.data, window_cols, C.byref(out), C.byref(n)))
+        if not n.value:
+            return np.zeros(0, MUT_DTYPE)
+        return np.frombuffer((C.c_char * (n.value * MUT_DTYPE.itemsize)).from_address(out.value), dtype=MUT_DTYPE).copy()

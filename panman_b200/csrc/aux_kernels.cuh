@@ -42,10 +42,6 @@ __global__ void assemble_kernel(const unsigned long long* __restrict__ recs, int
 // the greedy rule of the reference cuts every run into pieces of 6 from its start, so a packed record starts at every
 // record whose index inside its run is a multiple of 6.  run_start[i] = index of the first record of i's run
 // (max-scan of "i if a run starts here"), starts are counted by a prefix sum, and each start packs up to 6 records.
-struct PackedNucMut {  // pmfs_host_nucmut (include/pmfs_host.h)
-    int32_t nucPosition, nucGapPosition, primaryBlockId, secondaryBlockId;
-    uint32_t mutInfo, nucs;
-};
 __global__ void pack_runstart_kernel(const pmfs_mut* __restrict__ m, int64_t n, int32_t* __restrict__ run_start) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -179,16 +175,20 @@ __device__ __forceinline__ int kth_set_bit(uint32_t mask, uint32_t k) {  // posi
     }
     return pos;
 }
+// KEYS: the ordered records stay 64-bit words (column shards whose lists are gathered by node range: 8 bytes per record
+// cross NVLink and the owner converts, comm.cu); else they become pmfs_mut.
+template <bool KEYS>
 __global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, unsigned long long cap, uint32_t* __restrict__ cnt,
                                    const uint32_t* __restrict__ start, const uint32_t* __restrict__ prefix, int64_t cells, int32_t W,
                                    int pos_bits, const unsigned long long* __restrict__ stats, unsigned long long out_cap,
-                                   pmfs_mut* __restrict__ out) {
+                                   void* __restrict__ out) {
     if (stats[1] > cap || stats[0] > out_cap || (stats[3] >> 32)) return;  // (32-bit prefix sums: see cells_total_kernel)
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int64_t stride = (((int64_t)gridDim.x * blockDim.x) >> 5) * 32;
     const unsigned long long pos_mask = (1ull << pos_bits) - 1;
     uint32_t* const out32 = (uint32_t*)out;
+    unsigned long long* const out64 = (unsigned long long*)out;
     int64_t c0 = (((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32;
     // the three per-cell words of the NEXT block are fetched while the current one is copied
     uint32_t n_nx = 0, s_nx = 0, e_nx = 0;
@@ -216,12 +216,16 @@ __global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, 
             uint32_t* o = out32 + (size_t)e_l * 3;
             unsigned long long r = n_l ? src[0] : 0ull;
             for (uint32_t i = 0; i < n_l; i++, o += 3) {
-                const unsigned long long key = r >> kPayloadBits;
+                const unsigned long long cur = r, key = r >> kPayloadBits;
                 const uint32_t pay = (uint32_t)r;
                 if (i + 1 < n_l) r = src[i + 1];  // next record in flight while this one is stored
-                o[0] = (uint32_t)(key >> pos_bits);
-                o[1] = (uint32_t)(key & pos_mask);
-                o[2] = (pay & 3) | (((pay >> 2) & 15) << 8) | (((pay >> 6) & 15) << 16);
+                if (KEYS) {
+                    out64[(size_t)e_l + i] = cur;
+                } else {
+                    o[0] = (uint32_t)(key >> pos_bits);
+                    o[1] = (uint32_t)(key & pos_mask);
+                    o[2] = (pay & 3) | (((pay >> 2) & 15) << 8) | (((pay >> 6) & 15) << 16);
+                }
             }
             continue;
         }
@@ -241,13 +245,45 @@ __global__ void order_cells_kernel(const unsigned long long* __restrict__ keys, 
             const uint32_t rel_src = __shfl_sync(full, rel_l, src_lane);
             if (t < total) {
                 const unsigned long long r = src_t[t - rel_src], key = r >> kPayloadBits;
-                uint32_t* o = out32 + ((size_t)e0 + t) * 3;
-                o[0] = (uint32_t)(key >> pos_bits);
-                o[1] = (uint32_t)(key & pos_mask);
-                o[2] = (uint32_t)(r & 3) | ((uint32_t)((r >> 2) & 15) << 8) | ((uint32_t)((r >> 6) & 15) << 16);
+                if (KEYS) {
+                    out64[(size_t)e0 + t] = r;
+                } else {
+                    uint32_t* o = out32 + ((size_t)e0 + t) * 3;
+                    o[0] = (uint32_t)(key >> pos_bits);
+                    o[1] = (uint32_t)(key & pos_mask);
+                    o[2] = (uint32_t)(r & 3) | ((uint32_t)((r >> 2) & 15) << 8) | ((uint32_t)((r >> 6) & 15) << 16);
+                }
             }
         }
     }
+}
+
+// Per-node offsets into the ordered records, from the cell prefix sums: noff[v] = first record of node v, noff[V] = n;
+// cut[r] = first record of the node range owned by rank r (cut[n_parts] = n).
+__global__ void node_offsets_kernel(const uint32_t* __restrict__ prefix, int32_t W, int32_t n_nodes, const unsigned long long* __restrict__ stats,
+                                    uint32_t* __restrict__ noff, PartBounds parts, unsigned long long* __restrict__ cut) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n_nodes) noff[v] = prefix[v * W];
+    if (v == n_nodes) noff[v] = (uint32_t)stats[0];
+    if (v <= parts.n_parts) {
+        const int32_t b = parts.bound[v];
+        cut[v] = b >= n_nodes ? stats[0] : (unsigned long long)prefix[(int64_t)b * W];
+    }
+}
+// The same from the ordered 64-bit records themselves (radix path: no cell matrix): lower bound of each node id.
+__global__ void node_lower_bound_kernel(const unsigned long long* __restrict__ recs, int64_t n, int shift, int32_t n_nodes,
+                                        uint32_t* __restrict__ noff, PartBounds parts, unsigned long long* __restrict__ cut) {
+    const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v > n_nodes) return;
+    int64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if ((int64_t)(recs[mid] >> shift) < v) lo = mid + 1;
+        else hi = mid;
+    }
+    noff[v] = (uint32_t)lo;
+    for (int r = 0; r <= parts.n_parts; r++)
+        if (parts.bound[r] == v || (v == n_nodes && parts.bound[r] > n_nodes)) cut[r] = (unsigned long long)lo;
 }
 
 // region r's records (count[r] of them at src + r*cap) -> dst + offset[r]: makes the per-region output contiguous

@@ -28,6 +28,7 @@
 #include "plan.hpp"
 #include "walk.cuh"
 #include "walk_params.hpp"
+#include "ctx.hpp"
 
 namespace pmfs {
 
@@ -35,16 +36,7 @@ namespace pmfs {
 // bits (type 2 bits, node state 4, parent state 4; walk_params.hpp), so ordering the records is a keys-only radix sort
 // over exactly the key bits that can be set, and the multi-GPU exchange moves 8 bytes per record.
 
-static thread_local std::string g_error;
-
-#define PMFS_CUDA(call)                                                                             \
-    do {                                                                                            \
-        cudaError_t e_ = (call);                                                                    \
-        if (e_ != cudaSuccess) {                                                                    \
-            g_error = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
-            return e_ == cudaErrorMemoryAllocation ? PMFS_ERR_NOMEM : PMFS_ERR_CUDA;                \
-        }                                                                                           \
-    } while (0)
+thread_local std::string g_error;
 
 }  // namespace pmfs
 
@@ -77,122 +69,6 @@ const WalkKernelSet* walk_kernel_set(int nw, int ng) {
     return nullptr;
 }
 }  // namespace pmfs
-
-namespace pmfs {
-
-// ------------------------------------------------------------------------------------------------ context
-template <class T>
-struct DevBuf {
-    T* ptr = nullptr;
-    size_t cap = 0;  // elements
-    int ensure(size_t n) {
-        if (n <= cap) return PMFS_OK;
-        if (ptr) cudaFree(ptr);
-        ptr = nullptr;
-        cap = 0;
-        cudaError_t e = cudaMalloc(&ptr, std::max<size_t>(n, 1) * sizeof(T));
-        if (e != cudaSuccess) {
-            g_error = std::string("cudaMalloc(") + std::to_string(n * sizeof(T)) + " B): " + cudaGetErrorString(e);
-            cudaGetLastError();
-            return PMFS_ERR_NOMEM;
-        }
-        cap = n;
-        return PMFS_OK;
-    }
-    void release() {
-        if (ptr) cudaFree(ptr);
-        ptr = nullptr;
-        cap = 0;
-    }
-};
-
-}  // namespace pmfs
-
-using namespace pmfs;
-
-struct PartBounds {
-    int32_t n_parts;
-    int32_t bound[17];  // nodes [bound[r], bound[r+1]) belong to rank r
-};
-
-struct pmfs_ctx {
-    int device = 0;
-    Plan plan;
-    bool has_poly = false;
-    int32_t chunk_nodes_used = 0;
-    std::vector<int32_t> parent, child_off, child_idx, leaf_row;  // kept for re-planning and synth
-    int32_t tune_chunk_nodes = 0;
-    int64_t tune_tile_cols = 0;
-    int tune_nw = 0, tune_ng = 0;          // pmfs_set_tile: forced tile shape (0 = automatic)
-    const WalkKernelSet* ks = nullptr;     // tile shape of the current run
-    int32_t tree_height = 0;               // internal nodes on the longest root-to-leaf path
-    long long watchdog_ns = 10000000000ll; // device-side wait limit (pmfs_set_watchdog)
-    cudaStream_t stream = nullptr;      // stream in use
-    cudaStream_t own_stream = nullptr;  // created by pmfs_create
-    cudaEvent_t ev[8] = {};
-    cudaEvent_t ev_slab[2] = {};        // pmfs_run: upload slab 0 / 1 complete (recorded on copy_stream)
-    cudaStream_t copy_stream = nullptr;
-    int64_t slab_split = 0;             // > 0 while pmfs_run pipelines: first column group of the second slab
-    int64_t cells_clean_n = 0;          // d_cell_count holds this many zeroed cells (0: unknown, clear before use)
-    // plan on device
-    DevBuf<uint32_t> d_fwd_prog, d_bwd_prog, d_fwd_stream, d_bwd_stream;
-    DevBuf<int64_t> d_fwd_off, d_bwd_off, d_fwd_soff, d_bwd_soff;
-    DevBuf<int32_t> d_fwd_slen, d_bwd_slen, d_chunk_parent, d_chunk_nchild;
-    DevBuf<int4> d_fwd_items, d_bwd_items;
-    DevBuf<int> d_sync;
-    int n_sms = 0;
-    struct Occ {
-        const void* k;
-        size_t smem;
-        int per_sm;
-    };
-    std::vector<Occ> occ_cache;
-    float host_ms = 0;  // wall time of the last run_device_impl call
-    bool too_many_records = false;  // the last run failed only because one call may not produce that many records
-    int64_t tune_batch_cols = 0;    // pmfs_set_batch_cols
-    // column-shard mode (pmfs_set_shard)
-    int64_t shard_pos_offset = 0, shard_total_cols = 0;
-    PartBounds parts = {};
-    int64_t part_counts[16] = {};
-    unsigned long long* parts_keys = nullptr;
-    int64_t part_offsets[16] = {};
-    bool parts_by_columns = false;
-    DevBuf<unsigned long long> d_rkeys_alt;
-    DevBuf<uint8_t> d_sort_tmp2;
-    DevBuf<int32_t> d_fwd_len, d_bwd_len, d_fwd_order, d_bwd_order, d_int_to_node, d_row_to_node;
-    // per-run state
-    DevBuf<uint4> d_S, d_D, d_cons_planes, d_forced_planes, d_xcode;
-    DevBuf<uint32_t> d_xvalid;
-    DevBuf<unsigned long long> d_keys, d_keys_alt;
-
-    DevBuf<unsigned long long> d_count;
-    DevBuf<uint8_t> d_sort_tmp, d_scan_tmp;
-    DevBuf<uint32_t> d_cell_count, d_cell_start, d_cell_prefix;  // per (node, column region), see order_cells_kernel
-    unsigned long long* h_stats = nullptr;  // pinned: {records, largest area, error flag} of the last run
-    DevBuf<pmfs_mut> d_out;
-    // host-path staging
-    DevBuf<uint8_t> d_msa, d_cons, d_forced, d_chars;
-    std::vector<unsigned long long> h_counts, h_offsets;
-    // device-side packing (pmfs_pack_last)
-    DevBuf<int32_t> d_pk_run, d_pk_idx, d_pk_node;
-    DevBuf<PackedNucMut> d_pk_out;
-    DevBuf<int64_t> d_pk_off;
-    DevBuf<uint8_t> d_pk_tmp;
-    PackedNucMut* h_pk_out = nullptr;  // pinned
-    int64_t* h_pk_off = nullptr;       // pinned
-    size_t h_pk_out_cap = 0, h_pk_off_cap = 0;
-    pmfs_mut* h_out = nullptr;  // pinned
-    size_t h_out_cap = 0;
-    std::vector<pmfs_mut> h_acc, h_big;  // pmfs_run in column batches: per-batch records, and the stitched result
-    int64_t last_n_out = 0;
-    pmfs_timing timing = {};
-    // synth
-    DevBuf<int32_t> d_synth_node, d_synth_pslot, d_synth_mslot;
-    DevBuf<uint32_t> d_synth_state[2];
-    std::vector<int64_t> synth_lvl_off;
-    int64_t synth_max_slots = 1;
-    bool synth_ready = false;
-};
 
 static int upload_plan(pmfs_ctx* c) {
     const Plan& P = c->plan;
@@ -414,6 +290,8 @@ void pmfs_destroy(pmfs_ctx* c) {
     if (c->h_pk_off) cudaFreeHost(c->h_pk_off);
     c->d_pk_run.release(); c->d_pk_idx.release(); c->d_pk_node.release(); c->d_pk_out.release(); c->d_pk_off.release();
     c->d_pk_tmp.release();
+    c->d_skeys.release(); c->d_noff.release(); c->d_cuts.release();
+    if (c->h_cuts) cudaFreeHost(c->h_cuts);
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : c->ev_slab)
@@ -560,31 +438,40 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
 static int launch_order_cells(pmfs_ctx* c, size_t region_cap, int64_t cells, int64_t W, int pos_bits, const unsigned long long* d_stats,
                               size_t out_cap) {
     const unsigned grid = (unsigned)std::max<int64_t>(1, std::min<int64_t>((int64_t)c->n_sms * 8, (cells + 255) / 256));
-    order_cells_kernel<<<grid, 256, 0, c->stream>>>(c->d_keys.ptr, region_cap, c->d_cell_count.ptr, c->d_cell_start.ptr, c->d_cell_prefix.ptr,
-                                                    cells, (int32_t)W, pos_bits, d_stats, out_cap, c->d_out.ptr);
+    if (c->keys_out)
+        order_cells_kernel<true><<<grid, 256, 0, c->stream>>>(c->d_keys.ptr, region_cap, c->d_cell_count.ptr, c->d_cell_start.ptr,
+                                                              c->d_cell_prefix.ptr, cells, (int32_t)W, pos_bits, d_stats, out_cap, c->d_skeys.ptr);
+    else
+        order_cells_kernel<false><<<grid, 256, 0, c->stream>>>(c->d_keys.ptr, region_cap, c->d_cell_count.ptr, c->d_cell_start.ptr,
+                                                               c->d_cell_prefix.ptr, cells, (int32_t)W, pos_bits, d_stats, out_cap, c->d_out.ptr);
     PMFS_CUDA(cudaGetLastError());
     return PMFS_OK;
 }
 
 // Column groups whose set arrays (S, and D1 for Sankoff) fit in the device memory that is free now (what the context
-// already holds for them counts as free), leaving `reserve_bytes` and 15 % aside for records, cells and the caller.
-static int mem_limited_groups(pmfs_ctx* c, int algo, int64_t G_all, size_t reserve_bytes, int64_t* groups) {
+// already holds for them counts as free), with `extra_per_group` bytes per group for whatever else the caller allocates
+// per column group, and 30 % left aside for records and cells (on a 16 M-node tree the record buffers of a column
+// group -- emitted, ordered, received, converted -- come to a fifth of its set arrays).
+namespace pmfs {
+int mem_limited_groups(pmfs_ctx* c, int algo, int64_t G_all, size_t extra_per_group, int64_t* groups) {
     const int64_t I = c->plan.n_internal;
-    const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64;
+    const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64 + (int64_t)extra_per_group;
     const size_t need = (size_t)I * 4 * (size_t)G_all;
     *groups = G_all;
-    if (reserve_bytes == 0 && c->d_S.cap >= need && (algo != PMFS_SANKOFF || c->d_D.cap >= need)) return PMFS_OK;
+    if (extra_per_group == 0 && c->d_S.cap >= need && (algo != PMFS_SANKOFF || c->d_D.cap >= need)) return PMFS_OK;
     // (cudaMemGetInfo costs a fraction of a millisecond: only asked when buffers may have to grow)
     size_t free_b = 0, total_b = 0;
     PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
     free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);  // reusable
-    free_b = free_b > reserve_bytes ? free_b - reserve_bytes : 0;
-    *groups = std::min<int64_t>(G_all, std::max<int64_t>(1, (int64_t)(free_b * 0.85) / per_group));
+    *groups = std::min<int64_t>(G_all, std::max<int64_t>(1, (int64_t)(free_b * 0.7) / per_group));
     return PMFS_OK;
 }
 
-static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
-                           const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut** d_out, int64_t* n_out) {
+}  // namespace pmfs
+
+namespace pmfs {
+int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_stride, int32_t n_rows, int64_t n_cols,
+                    const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut** d_out, int64_t* n_out) {
     if (!c || (algo != PMFS_FITCH && algo != PMFS_SANKOFF) || !d_msa || !d_cons || !n_out || n_cols <= 0) {
         g_error = "pmfs_run: bad argument";
         return PMFS_ERR_ARG;
@@ -802,7 +689,16 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
                 cells_total_kernel<<<1, 1, 0, c->stream>>>(c->d_cell_count.ptr, c->d_cell_prefix.ptr, cells, d_stats);
                 tm.n_launches++;
                 PMFS_CUDA(cudaMemcpyAsync(stats, d_stats, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-                ordered_cap = c->d_out.cap;
+                if (c->keys_out) {  // per-node offsets and the owners' cut points only need the prefix sums: queue them now
+                    if ((rc = c->d_noff.ensure((size_t)P->n_nodes + 1))) return rc;
+                    if ((rc = c->d_cuts.ensure(32))) return rc;
+                    if (!c->h_cuts) PMFS_CUDA(cudaMallocHost(&c->h_cuts, 32 * sizeof(unsigned long long)));
+                    node_offsets_kernel<<<(unsigned)((P->n_nodes + 256) / 256), 256, 0, c->stream>>>(c->d_cell_prefix.ptr, (int32_t)W, P->n_nodes, d_stats,
+                                                                                                   c->d_noff.ptr, c->xparts, c->d_cuts.ptr);
+                    tm.n_launches++;
+                    PMFS_CUDA(cudaMemcpyAsync(c->h_cuts, c->d_cuts.ptr, 17 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+                }
+                ordered_cap = c->keys_out ? c->d_skeys.cap : c->d_out.cap;
                 if (ordered_cap > 0) {
                     rc = launch_order_cells(c, region, cells, W, pos_bits, d_stats, ordered_cap);
                     if (rc) return rc;
@@ -914,14 +810,18 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     }
     if (n > 0 && use_cells) {
         if ((size_t)n > ordered_cap) {  // first run, or more records than ever before: now the count is known
-            if ((rc = c->d_out.ensure((size_t)n + (size_t)n / 8))) return rc;
-            rc = launch_order_cells(c, region, cells, W, pos_bits, d_stats, c->d_out.cap);
+            if (c->keys_out) {
+                if ((rc = c->d_skeys.ensure((size_t)n + (size_t)n / 8))) return rc;
+            } else {
+                if ((rc = c->d_out.ensure((size_t)n + (size_t)n / 8))) return rc;
+            }
+            rc = launch_order_cells(c, region, cells, W, pos_bits, d_stats, c->keys_out ? c->d_skeys.cap : c->d_out.cap);
             if (rc) return rc;
             tm.n_launches++;
         }
     } else if (n > 0) {  // order by (node,pos): keys-only radix sort over exactly the key bits that can be set
         if ((rc = c->d_keys_alt.ensure(c->d_keys.cap))) return rc;
-        if ((rc = c->d_out.ensure((size_t)n))) return rc;
+        if (!c->keys_out && (rc = c->d_out.ensure((size_t)n))) return rc;
         cub::DoubleBuffer<unsigned long long> kb(c->d_keys.ptr, c->d_keys_alt.ptr);
         const int lo = by_columns ? kPayloadBits + pos_bits + bucket_bits : kPayloadBits;
         const int hi = kPayloadBits + pos_bits + node_bits;
@@ -932,9 +832,23 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
         // 2^bucket_bits nodes)
         if (by_columns) kb = cub::DoubleBuffer<unsigned long long>(c->d_keys_alt.ptr, c->d_keys.ptr);
         if (lo < hi) PMFS_CUDA(cub::DeviceRadixSort::SortKeys(c->d_sort_tmp.ptr, tmp_bytes, kb, (int)n, lo, hi, c->stream));
-        assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), n, pos_bits, c->d_out.ptr);
+        if (c->keys_out) {
+            c->skeys_view = kb.Current();  // the ordered 64-bit records, in one of the two sort buffers
+        } else {
+            assemble_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(kb.Current(), n, pos_bits, c->d_out.ptr);
+        }
         PMFS_CUDA(cudaGetLastError());
         tm.n_launches += 1;
+    }
+    if (c->keys_out && !use_cells) {  // per-node offsets by binary search in the ordered records
+        if ((rc = c->d_noff.ensure((size_t)P->n_nodes + 1))) return rc;
+        if ((rc = c->d_cuts.ensure(32))) return rc;
+        if (!c->h_cuts) PMFS_CUDA(cudaMallocHost(&c->h_cuts, 32 * sizeof(unsigned long long)));
+        node_lower_bound_kernel<<<(unsigned)((P->n_nodes + 256) / 256), 256, 0, c->stream>>>(c->skeys_view, n, kPayloadBits + pos_bits, P->n_nodes,
+                                                                                           c->d_noff.ptr, c->xparts, c->d_cuts.ptr);
+        PMFS_CUDA(cudaMemcpyAsync(c->h_cuts, c->d_cuts.ptr, 17 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    } else if (c->keys_out) {
+        c->skeys_view = c->d_skeys.ptr;
     }
     if (use_cells) c->cells_clean_n = cells;  // order_cells_kernel ran to the end (or nothing was emitted): the matrix is clear
     if (use_cells && ordered_cap > 0 && (size_t)n <= ordered_cap) {
@@ -952,6 +866,7 @@ static int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t 
     if (d_out) *d_out = c->d_out.ptr;
     return PMFS_OK;
 }
+}  // namespace pmfs
 
 extern "C" {
 
@@ -972,7 +887,7 @@ int pmfs_set_batch_cols(pmfs_ctx* c, int64_t batch_cols) {
 
 // Columns per batch: what the caller asked for, else as many as the set arrays of one batch fit in free device memory,
 // in equal batches whose size is a multiple of 32 column groups (whole output regions and tile shapes).
-static int batch_groups_for(pmfs_ctx* c, int algo, int64_t n_cols, int64_t batch_cols, size_t reserve_bytes, int64_t* out) {
+static int batch_groups_for(pmfs_ctx* c, int algo, int64_t n_cols, int64_t batch_cols, size_t extra_per_group, int64_t* out) {
     const int64_t G_all = (n_cols + 31) / 32;
     if (batch_cols <= 0) batch_cols = c->tune_batch_cols;
     if (batch_cols > 0) {
@@ -980,7 +895,7 @@ static int batch_groups_for(pmfs_ctx* c, int algo, int64_t n_cols, int64_t batch
         return PMFS_OK;
     }
     int64_t gmax = 0;
-    int rc = mem_limited_groups(c, algo, G_all, reserve_bytes, &gmax);
+    int rc = mem_limited_groups(c, algo, G_all, extra_per_group, &gmax);
     if (rc) return rc;
     // (a batch is ordered through 32-bit cell prefix sums and 2^30 cells at most: bound the cell matrix as well)
     const int64_t max_regions = std::max<int64_t>(1, ((int64_t)1 << 30) / std::max(1, c->plan.n_nodes));
@@ -1295,7 +1210,7 @@ static int run_host_streaming(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t
         PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
         free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);
         const int64_t per_group = (int64_t)c->plan.n_internal * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64 + 2 * 16 * (int64_t)n_rows;
-        int64_t gmax = std::max<int64_t>(1, (int64_t)(free_b * 0.8) / per_group);
+        int64_t gmax = std::max<int64_t>(1, (int64_t)(free_b * 0.65) / per_group);
         const int64_t max_regions = std::max<int64_t>(1, ((int64_t)1 << 30) / std::max(1, c->plan.n_nodes));
         gmax = std::min(gmax, max_regions * 32);
         const int64_t n_b = (G_all + gmax - 1) / gmax;

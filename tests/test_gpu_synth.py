@@ -46,6 +46,28 @@ def test_synth_is_a_pure_function_of_seed_node_column():
         assert {0, 1, 2, 4, 8, 15} <= codes
 
 
+def test_cpu_twin_of_the_generator_matches_the_device_cell_for_cell():
+    """oracle/synth_twin.c (what bench.py's reference arm generates its input with, without a GPU) against the device
+    generator: every cell of a 700-taxon alignment with all event kinds, of a polytomy tree with absent leaves, and of
+    column windows far from 0 (the hash takes the GLOBAL column)."""
+    import synth as S
+    specs = [api.SynthSpec(seed=7, p_sub=0.01, p_del=0.01, p_ins=0.05, p_n_block=0.02, p_amb=0.01, accessory_frac=0.3),
+             api.SynthSpec()]
+    rng = np.random.default_rng(3)
+    for tree in (trees.random_binary_tree(700, seed=2), S.random_tree(400, rng, max_arity=5, absent_frac=0.05),
+                 trees.caterpillar_tree(300)):
+        rows = S.n_rows(tree)
+        with api.Context(tree) as ctx:
+            for spec in specs:
+                for col0, L in ((0, 4096), (29984, 16), (1 << 20, 1000)):
+                    d_msa, d_cons, _ = synth_on_device(ctx, spec, rows, col0, L)
+                    dev = api.unpack_nibbles(d_msa.cpu().numpy(), L)
+                    twin = O.synth_columns(tree, spec, np.arange(col0, col0 + L), rows, threads=4)
+                    assert (dev == twin).all(), (tree.n_nodes, col0, L)
+                    nz = twin != 0
+                    assert (d_cons.cpu().numpy() == twin[nz.argmax(0), np.arange(L)]).all()
+
+
 @pytest.mark.parametrize("algo", [api.FITCH, api.SANKOFF])
 def test_config2_full_size_properties_and_subsample_parity(algo):
     """BASELINE config 2 (20 000 taxa x 30 000 columns, random binary tree) at full size:
