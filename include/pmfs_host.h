@@ -35,6 +35,20 @@ int pmfs_host_build(const char* msa_path, const char* nwk_path, const char* refe
 int pmfs_host_pack(const pmfs_mut* muts, int64_t n_muts, int32_t n_nodes, int64_t** nuc_off, pmfs_host_nucmut** nuc,
                    int64_t* n_nuc);
 
+/* .panman output: writePanMAN (src/panmanUtils.cpp:269-297) over TreeGroup::writeToFile (src/panman.cpp:7027-7161) and
+ * Tree::getNodesPreorder (:2868-2943) for a tree of this path: Cap'n Proto message per panman.capnp (hand-encoded: one
+ * segment, standard stream framing), LZMA level 9 around it when compress != 0 (/usr/bin/xz).
+ * pmfs_host_write_panman needs no device: tree in pre-order (parent[], '\n'-joined identifiers, branch lengths or NULL
+ * for 0.0), per-node packed NucMut lists as a CSR (as pmfs_host_build / pmfs_pack_last return them), Block consensus
+ * words.  pmfs_host_build_panman is the whole `panmanUtils -M msa -N nwk [--reference id] [--low-mem-mode] -o out`
+ * (src/panmanUtils.cpp:1487-1543) on CUDA device `device`. */
+const char* pmfs_host_writer_last_error(void);
+int pmfs_host_write_panman(int32_t n_nodes, const int32_t* parent, const char* names_joined, const float* branch_length,
+                           const int64_t* nuc_off, const pmfs_host_nucmut* nuc, const uint32_t* block_words,
+                           int64_t n_block_words, const char* out_path, int compress);
+int pmfs_host_build_panman(const char* msa_path, const char* nwk_path, const char* reference, int low_mem, int device,
+                           const char* out_path, int compress);
+
 #ifdef __cplusplus
 }
 #endif

@@ -370,6 +370,28 @@ int pmfs_host_parse_newick(const char* newick, int32_t* parent, int32_t* n_child
 
 void pmfs_host_free(void* p) { free(p); }
 
+// `panmanUtils -M msa -N nwk [--reference id] [--low-mem-mode] -o out` (src/panmanUtils.cpp:1487-1543): build, then
+// writePanMAN.
+int pmfs_host_build_panman(const char* msa_path, const char* nwk_path, const char* reference, int low_mem, int device,
+                           const char* out_path, int compress) {
+    try {
+        std::ifstream fin(msa_path), nwk(nwk_path);
+        if (!fin.good() || !nwk.good() || !out_path) {
+            g_host_error = "cannot open input file";
+            return -15;
+        }
+        Tree T(fin, nwk, low_mem ? pmfs_host::MSA_OPTIMIZE : pmfs_host::MSA, reference ? reference : "", device);
+        pmfs_host::writePanMAN(T, out_path, compress != 0);
+        return 0;
+    } catch (const BuildError& e) {
+        g_host_error = e.what();
+        return e.status;
+    } catch (const std::exception& e) {
+        g_host_error = e.what();
+        return -19;
+    }
+}
+
 typedef struct {  // NucMut (src/panman.hpp:55-61) with mutInfo widened so the layout has no padding
     int32_t nucPosition, nucGapPosition, primaryBlockId, secondaryBlockId;
     uint32_t mutInfo, nucs;

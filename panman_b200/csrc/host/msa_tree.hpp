@@ -67,6 +67,8 @@ class Tree {
 
     // Same signature as the reference constructor plus the CUDA device to run on.
     Tree(std::istream& fin, std::istream& secondFin, FILE_TYPE ftype, std::string reference = "", int device = 0);
+    // An empty tree for code that fills the fields itself (the writer's array entry point).
+    explicit Tree(std::nullptr_t) {}
 
     // Pieces, exposed so each can be tested against the reference behaviour on its own
     static void createTreeFromNewickString(std::string newick, std::vector<Node>& nodes,
@@ -78,5 +80,14 @@ class Tree {
     static void packNucMutations(const std::vector<pmfs_mut>& sortedMuts, std::vector<Node>& nodes);
     static std::vector<uint32_t> packBlockConsensus(const std::string& seq);
 };
+
+// ---- .panman output (panman_writer.cpp) ----
+// Tree::getNewickString (src/panman.cpp:1923-2030) of the whole tree.
+std::string getNewickString(const Tree& tree);
+// The Cap'n Proto stream TreeGroup::writeToFile (src/panman.cpp:7027-7161) produces for a TreeGroup holding this tree.
+std::vector<uint8_t> encodePanMAN(const Tree& tree);
+// writePanMAN (src/panmanUtils.cpp:269-297): the stream through LZMA level 9 (xz) into `path`; compress = false leaves
+// it bare.
+void writePanMAN(const Tree& tree, const std::string& path, bool compress = true);
 
 }  // namespace pmfs_host

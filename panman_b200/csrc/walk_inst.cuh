@@ -51,8 +51,9 @@ static WalkKernelSet make_kernel_set() {
     s.fwd[kAlgoSankoff][1] = (const void*)fwd_kernel<CFG, kAlgoSankoff, true>;
     s.bwd[kAlgoFitch] = (const void*)bwd_kernel<CFG, kAlgoFitch>;
     s.bwd[kAlgoSankoff] = (const void*)bwd_kernel<CFG, kAlgoSankoff>;
-    s.fwd_smem_fixed = SmemMap<CFG, kSetRingFwd>::kStack;
-    s.bwd_smem_fixed = SmemMap<CFG, kSetRingBwd>::kStack;
+    s.smem_fixed = kSmemLeaf;
+    s.leaf_unit_bytes = CFG::UnitBytes;
+    s.set_slot_bytes = CFG::SetBytes;
     s.fwd_smem_per_level = (size_t)CFG::NG * 4 * CFG::TPB * sizeof(uint4);
     s.bwd_smem_per_level = (size_t)CFG::NG * 5 * CFG::TPB * sizeof(uint32_t);
 #ifdef PMFS_WAITPROF

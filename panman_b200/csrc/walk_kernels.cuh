@@ -46,16 +46,12 @@ struct TileCfg {
     static constexpr int UnitBytes = Groups * 16; // one MSA row segment of the tile
     static constexpr int SetBytes = Groups * 64;  // one node's set for the tile
 };
-// Operand rings of a CTA, per pass: leaf-row units in flight (16 B for each group of the tile) and set slots in flight
-// (64 B for each group).  One int encodes both (leaf * 16 + sets) so that it can be a template argument.
-// Bottom-up: mostly leaves, and its walk stack + 128 registers cap the resident CTAs anyway.  Top-down: every
-// internal node is one set; 2 + 2 keeps a 256-group CTA under 57 KB, which lets 4 CTAs share an SM (0.41 -> 0.36 ms).
-#ifndef PMFS_RING_FWD
-#define PMFS_RING_FWD (4 * 16 + 1)
-#define PMFS_RING_BWD (2 * 16 + 2)
-#endif
-constexpr int kSetRingFwd = PMFS_RING_FWD;
-constexpr int kSetRingBwd = PMFS_RING_BWD;
+// Operand rings of a CTA: leaf-row units in flight (16 B for each group of the tile) and set slots in flight (64 B for each
+// group).  Their depths are powers of two chosen per launch (WalkParams::leaf_ring_log2 / set_ring_log2, pmfs.cu
+// ring_depths): bottom-up is mostly leaves, top-down needs one set per internal node; narrow tiles have small units, so
+// the same bytes in flight need deeper rings, and on a ladder-like tree -- one chain of dependent nodes per column tile --
+// the ring depth IS the number of operands in flight per chain.
+constexpr int kMaxLeafRing = 32, kMaxSetRing = 16;
 constexpr int kProgWords = 256;           // walk programs up to this many words are staged in shared memory
 
 // ---- mbarrier / bulk-copy (TMA) primitives, sm_90+ PTX ------------------------------------------------------------
@@ -172,29 +168,24 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 }
 
 // Shared-memory layout of one CTA (addresses in the shared window).  Two operand rings, both filled by the producer
-// warp with TMA bulk copies and drained by the 4 walking warps: LEAF units (one 4 KB segment of an MSA row: 16 bytes
-// for each of the tile's 256 column groups) and SET slots (one 16 KB block of the tile-major set array: the 4
-// quarter-sets of all 256 groups, a single contiguous copy).  Per ring entry: `full` flips when its bytes have
-// landed, `empty` when all 4 walking warps have read it.  Entry numbers keep counting across the work items of a
-// persistent CTA, so phases never need resetting.
-template <class CFG, int RING>
-struct SmemMap {
-    static constexpr int kLeafRing = RING >> 4, SETS = RING & 15;
-    static constexpr int kProg = 0;                                 // 2 staged programs
-    static constexpr int kDesc = 2 * kProgWords * 4;                // 2 item descriptors (16 B each, 64 B reserved)
-    static constexpr int kLeaf = kDesc + 64;                        // leaf ring
-    static constexpr int kSet = kLeaf + kLeafRing * CFG::UnitBytes;     // set ring
-    static constexpr int kStack = kSet + SETS * CFG::SetBytes;          // walk stack (dynamic size)
-    // barriers (static shared array), 8 bytes each
-    static constexpr int bLeafFull = 0, bLeafEmpty = kLeafRing, bSetFull = 2 * kLeafRing, bSetEmpty = 2 * kLeafRing + SETS,
-                         bProg = 2 * kLeafRing + 2 * SETS, bDescFull = bProg + 2, bDescEmpty = bProg + 4, kBars = bProg + 6;
-};
+// warp with TMA bulk copies and drained by the walking warps: LEAF units (one segment of an MSA row: 16 bytes for each
+// of the tile's column groups) and SET slots (one block of the tile-major set array: the 4 quarter-sets of all groups
+// of the tile, a single contiguous copy).  Per ring entry: `full` flips when its bytes have landed, `empty` when all
+// walking warps have read it.  Entry numbers keep counting across the work items of a persistent CTA, so phases never
+// need resetting.
+constexpr int kSmemProg = 0;                      // 2 staged programs
+constexpr int kSmemDesc = 2 * kProgWords * 4;     // 2 item descriptors (16 B each, 64 B reserved)
+constexpr int kSmemLeaf = kSmemDesc + 64;         // leaf ring, then the set ring, then the walk stack (dynamic sizes)
+// barriers (static shared array), 8 bytes each
+constexpr int kBarLeafFull = 0, kBarLeafEmpty = kMaxLeafRing, kBarSetFull = 2 * kMaxLeafRing, kBarSetEmpty = 2 * kMaxLeafRing + kMaxSetRing,
+              kBarProg = 2 * kMaxLeafRing + 2 * kMaxSetRing, kBarDescFull = kBarProg + 2, kBarDescEmpty = kBarProg + 4, kBars = kBarProg + 6;
 struct Ring {
     uint32_t smem;       // shared address of the dynamic shared memory
     uint32_t bars;       // shared address of the barrier array
     long long limit_ns;  // watchdog of every wait (WalkParams::spin_limit_ns)
+    uint32_t leaf_log2, leaf_mask, set_log2, set_mask;  // ring depths (powers of two)
+    uint32_t off_set, off_stack;                        // byte offsets of the set ring and the walk stack
 };
-
 // What the producer tells the walkers about a work item (one int4 in shared memory).
 struct ItemDesc {
     int32_t chunk;   // -1: no more items
@@ -240,12 +231,10 @@ struct NextItem {
         fetched = true;
     }
 };
-template <class CFG, int RING>
 __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, NextItem& h, bool block) {
-    using M = SmemMap<CFG, RING>;
     const uint32_t slot = h.ordinal & 1u, phase = (h.ordinal >> 1) & 1u;
     if (!h.slot_free) {  // the walkers are done with the item two before this one
-        const uint32_t bar = r.bars + (M::bDescEmpty + slot) * 8;
+        const uint32_t bar = r.bars + (kBarDescEmpty + slot) * 8;
         if (block) {
             PMFS_WP(7);
             mbar_wait(bar, phase ^ 1u, r.limit_ns);
@@ -256,8 +245,8 @@ __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, 
         if (h.valid && h.a.z <= kProgWords) {
             // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
             const uint32_t bytes = (uint32_t)((h.a.z + 3) / 4) * 16u;
-            mbar_arrive_expect_tx(r.bars + (M::bProg + slot) * 8, bytes);
-            bulk_g2s(r.smem + M::kProg + slot * (kProgWords * 4), p.prog + (int64_t)h.b.x * 4, bytes, r.bars + (M::bProg + slot) * 8);
+            mbar_arrive_expect_tx(r.bars + (kBarProg + slot) * 8, bytes);
+            bulk_g2s(r.smem + kSmemProg + slot * (kProgWords * 4), p.prog + (int64_t)h.b.x * 4, bytes, r.bars + (kBarProg + slot) * 8);
         }
     }
     if (h.valid && !h.dep_ok) {
@@ -276,19 +265,18 @@ __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, 
         asm volatile("fence.proxy.async;" ::: "memory");  // data written by other CTAs is read by the TMA engine
         h.dep_ok = true;
     }
-    asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.smem + M::kDesc + slot * 16), "r"(h.valid ? h.a.x : -1), "r"(h.tile),
+    asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(r.smem + kSmemDesc + slot * 16), "r"(h.valid ? h.a.x : -1), "r"(h.tile),
                  "r"(h.a.z), "r"(h.a.y)
                  : "memory");
-    mbar_arrive(r.bars + (M::bDescFull + slot) * 8);
+    mbar_arrive(r.bars + (kBarDescFull + slot) * 8);
     h.posted = true;
 }
 
 // Producer side of one item: walk the chunk's load stream and keep both rings full.  Called by the whole producer warp
 // (the stream words are read warp-wide); lane 0 drives TMA and, in passing, the header of the next item.
-template <class CFG, int RING>
+template <class CFG>
 __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& r, WarpWords& w, int32_t slen, int tile,
                                                uint32_t& n_leaf, uint32_t& n_set, NextItem& h) {
-    using M = SmemMap<CFG, RING>;
     const int lane = threadIdx.x & 31;
     const int64_t g0 = (int64_t)tile * CFG::Groups;
     const uint32_t leaf_bytes = (uint32_t)min((int64_t)CFG::Groups, p.G - g0) * 16u;
@@ -296,23 +284,23 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
         const uint32_t e = w.get(j, lane);
         if (e & kStreamSet) {
             if (lane == 0) {
-                const uint32_t u = n_set % M::SETS, par = (n_set / M::SETS) & 1u;
+                const uint32_t u = n_set & r.set_mask, par = (n_set >> r.set_log2) & 1u;
                 PMFS_WP(9);
-                mbar_wait(r.bars + (M::bSetEmpty + u) * 8, par ^ 1u, r.limit_ns);  // all walkers are done with the slot's previous set
+                mbar_wait(r.bars + (kBarSetEmpty + u) * 8, par ^ 1u, r.limit_ns);  // all walkers are done with the slot's previous set
                 // one node's set for this tile: 4 quarters of `tile_w` groups, contiguous (leaf_bytes = tile_w * 16)
-                mbar_arrive_expect_tx(r.bars + (M::bSetFull + u) * 8, 4 * leaf_bytes);
-                bulk_g2s(r.smem + M::kSet + u * CFG::SetBytes, p.S + (int64_t)(e & ~kStreamSet) * (4 * p.G) + g0 * 4, 4 * leaf_bytes,
-                         r.bars + (M::bSetFull + u) * 8);
+                mbar_arrive_expect_tx(r.bars + (kBarSetFull + u) * 8, 4 * leaf_bytes);
+                bulk_g2s(r.smem + r.off_set + u * CFG::SetBytes, p.S + (int64_t)(e & ~kStreamSet) * (4 * p.G) + g0 * 4, 4 * leaf_bytes,
+                         r.bars + (kBarSetFull + u) * 8);
             }
             n_set++;
         } else {
             if (lane == 0) {
-                const uint32_t u = n_leaf % M::kLeafRing, par = (n_leaf / M::kLeafRing) & 1u;
+                const uint32_t u = n_leaf & r.leaf_mask, par = (n_leaf >> r.leaf_log2) & 1u;
                 PMFS_WP(8);
-                mbar_wait(r.bars + (M::bLeafEmpty + u) * 8, par ^ 1u, r.limit_ns);
-                mbar_arrive_expect_tx(r.bars + (M::bLeafFull + u) * 8, leaf_bytes);
-                bulk_g2s(r.smem + M::kLeaf + u * CFG::UnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
-                         r.bars + (M::bLeafFull + u) * 8);
+                mbar_wait(r.bars + (kBarLeafEmpty + u) * 8, par ^ 1u, r.limit_ns);
+                mbar_arrive_expect_tx(r.bars + (kBarLeafFull + u) * 8, leaf_bytes);
+                bulk_g2s(r.smem + kSmemLeaf + u * CFG::UnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
+                         r.bars + (kBarLeafFull + u) * 8);
             }
             n_leaf++;
         }
@@ -323,7 +311,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
             const int32_t left = slen - 1 - j;
             if (left == h.t_claim) h.claim(p);
             else if (left == h.t_fetch) h.fetch(p);
-            else if (left < h.t_fetch && !h.posted && (left & 1) == 0) header_step<CFG, RING>(p, r, h, false);
+            else if (left < h.t_fetch && !h.posted && (left & 1) == 0) header_step(p, r, h, false);
         }
     }
 }
@@ -336,10 +324,9 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
 // Set arrays are TILE-MAJOR: S[internal id][tile][quarter][groups of the tile] (uint4; 256 groups per tile, fewer in
 // the last one), so one node's set for one tile is a single contiguous block of up to 16 KB (one TMA copy) and a
 // warp's 128-bit stores are 512-byte segments.  A node's row is exactly 4*G uint4: no padding.
-template <class CFG, bool READONLY_SETS, int RING>
+template <class CFG, bool READONLY_SETS>
 struct DevEnv {
     static constexpr int kGroups = CFG::NG;
-    using M = SmemMap<CFG, RING>;
     const WalkParams& p;
     const Ring& ring;
     int64_t g[CFG::NG];      // clamped column groups
@@ -366,9 +353,9 @@ struct DevEnv {
         : p(p_), ring(r), gwarp((int64_t)d.tile * CFG::Groups + (threadIdx.x & ~31)), set_tile((int64_t)d.tile * (CFG::SetBytes / 16)),
           tile_w((int32_t)min((int64_t)CFG::Groups, p_.G - (int64_t)d.tile * CFG::Groups)),
           item_tile(d.tile),
-          n_leaf(n_leaf_), n_set(n_set_), fstk((uint4*)((char*)smem_generic + M::kStack)),
-          bstk((uint32_t*)((char*)smem_generic + M::kStack)), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords),
-          gprog(nullptr), sprog(r.smem + M::kProg + slot * (kProgWords * 4)) {
+          n_leaf(n_leaf_), n_set(n_set_), fstk((uint4*)((char*)smem_generic + r.off_stack)),
+          bstk((uint32_t*)((char*)smem_generic + r.off_stack)), lane(threadIdx.x & 31), prog_staged(d.plen <= kProgWords),
+          gprog(nullptr), sprog(r.smem + kSmemProg + slot * (kProgWords * 4)) {
 #pragma unroll
         for (int j = 0; j < CFG::NG; j++) {
             const int64_t gj = (int64_t)d.tile * CFG::Groups + j * CFG::TPB + threadIdx.x;
@@ -378,7 +365,7 @@ struct DevEnv {
         // bit q is column 8*(q&3) + (q>>2): smaller residues q&3 come first as a whole, then smaller q>>2 of this lane's own
         ltmask = 0x11111111u * ((1u << (lane & 3)) - 1u) | ((0x11111111u << (lane & 3)) & ((1u << (4 * (lane >> 2))) - 1u));
         PMFS_WP(1);
-        if (prog_staged) mbar_wait(r.bars + (M::bProg + slot) * 8, prog_parity, r.limit_ns);
+        if (prog_staged) mbar_wait(r.bars + (kBarProg + slot) * 8, prog_parity, r.limit_ns);
         else gprog = p_.prog + p_.chunk_off[d.chunk];
     }
 
@@ -393,22 +380,22 @@ struct DevEnv {
 
     // next leaf unit: wait until the TMA copy has landed, read this thread's 16 bytes per group, hand the unit back
     __device__ __forceinline__ void leaf(uint32_t, uint4 (&w)[CFG::NG]) {
-        const uint32_t u = n_leaf % M::kLeafRing, par = (n_leaf / M::kLeafRing) & 1u;
+        const uint32_t u = n_leaf & ring.leaf_mask, par = (n_leaf >> ring.leaf_log2) & 1u;
         PMFS_WP(2);
-        mbar_wait(ring.bars + (M::bLeafFull + u) * 8, par, ring.limit_ns);
-        const uint32_t base = ring.smem + M::kLeaf + u * CFG::UnitBytes + threadIdx.x * 16;
+        mbar_wait(ring.bars + (kBarLeafFull + u) * 8, par, ring.limit_ns);
+        const uint32_t base = ring.smem + kSmemLeaf + u * CFG::UnitBytes + threadIdx.x * 16;
 #pragma unroll
         for (int j = 0; j < CFG::NG; j++) w[j] = lds128(base + j * (CFG::TPB * 16));
         __syncwarp();
-        if (lane == 0) mbar_arrive(ring.bars + (M::bLeafEmpty + u) * 8);
+        if (lane == 0) mbar_arrive(ring.bars + (kBarLeafEmpty + u) * 8);
         n_leaf++;
     }
     // next set slot (a set written by an earlier work item): 4 quarters x CFG::NG groups
     __device__ __forceinline__ void load_x(uint32_t, Planes16 (&s)[CFG::NG]) {
-        const uint32_t u = n_set % M::SETS, par = (n_set / M::SETS) & 1u;
+        const uint32_t u = n_set & ring.set_mask, par = (n_set >> ring.set_log2) & 1u;
         PMFS_WP(3);
-        mbar_wait(ring.bars + (M::bSetFull + u) * 8, par, ring.limit_ns);
-        const uint32_t base = ring.smem + M::kSet + u * CFG::SetBytes + threadIdx.x * 16;
+        mbar_wait(ring.bars + (kBarSetFull + u) * 8, par, ring.limit_ns);
+        const uint32_t base = ring.smem + ring.off_set + u * CFG::SetBytes + threadIdx.x * 16;
 #pragma unroll
         for (int j = 0; j < CFG::NG; j++)
 #pragma unroll
@@ -417,7 +404,7 @@ struct DevEnv {
                 s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
             }
         __syncwarp();
-        if (lane == 0) mbar_arrive(ring.bars + (M::bSetEmpty + u) * 8);
+        if (lane == 0) mbar_arrive(ring.bars + (kBarSetEmpty + u) * 8);
         n_set++;
     }
 
@@ -656,26 +643,31 @@ __device__ __forceinline__ uint32_t real_column_mask(int64_t g, int64_t tile_col
 // latencies.  Item descriptors and programs are double buffered; all hand-overs are mbarriers, the kernels contain no
 // CTA-wide barrier after set-up.
 
-template <class CFG, int RING>
-__device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars, long long limit_ns) {
-    using M = SmemMap<CFG, RING>;
+template <class CFG>
+__device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars, const WalkParams& p) {
     Ring r;
     r.smem = (uint32_t)__cvta_generic_to_shared(smem);
     r.bars = (uint32_t)__cvta_generic_to_shared(bars);
-    r.limit_ns = limit_ns;
+    r.limit_ns = p.spin_limit_ns;
+    r.leaf_log2 = (uint32_t)p.leaf_ring_log2;
+    r.leaf_mask = (1u << r.leaf_log2) - 1u;
+    r.set_log2 = (uint32_t)p.set_ring_log2;
+    r.set_mask = (1u << r.set_log2) - 1u;
+    r.off_set = kSmemLeaf + (CFG::UnitBytes << r.leaf_log2);
+    r.off_stack = r.off_set + (CFG::SetBytes << r.set_log2);
     if (threadIdx.x == 0) {
-        for (int i = 0; i < M::kLeafRing; i++) {
-            mbar_init(r.bars + (M::bLeafFull + i) * 8, 1);           // one arrive.expect_tx by the producer
-            mbar_init(r.bars + (M::bLeafEmpty + i) * 8, CFG::NW);  // one arrive per walking warp
+        for (uint32_t i = 0; i <= r.leaf_mask; i++) {
+            mbar_init(r.bars + (kBarLeafFull + i) * 8, 1);           // one arrive.expect_tx by the producer
+            mbar_init(r.bars + (kBarLeafEmpty + i) * 8, CFG::NW);    // one arrive per walking warp
         }
-        for (int i = 0; i < M::SETS; i++) {
-            mbar_init(r.bars + (M::bSetFull + i) * 8, 1);
-            mbar_init(r.bars + (M::bSetEmpty + i) * 8, CFG::NW);
+        for (uint32_t i = 0; i <= r.set_mask; i++) {
+            mbar_init(r.bars + (kBarSetFull + i) * 8, 1);
+            mbar_init(r.bars + (kBarSetEmpty + i) * 8, CFG::NW);
         }
         for (int i = 0; i < 2; i++) {
-            mbar_init(r.bars + (M::bProg + i) * 8, 1);
-            mbar_init(r.bars + (M::bDescFull + i) * 8, 1);
-            mbar_init(r.bars + (M::bDescEmpty + i) * 8, CFG::NW);
+            mbar_init(r.bars + (kBarProg + i) * 8, 1);
+            mbar_init(r.bars + (kBarDescFull + i) * 8, 1);
+            mbar_init(r.bars + (kBarDescEmpty + i) * 8, CFG::NW);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -687,7 +679,7 @@ __device__ __forceinline__ Ring ring_setup(void* smem, unsigned long long* bars,
 // item after item.  Everything that does not need the dependency is started before it is polled, the item record is
 // one 32-byte load, and the claim for the NEXT item is issued before this one is produced, so that per item only the
 // record load and the dependency poll remain on the producer's critical path.
-template <class CFG, int RING>
+template <class CFG>
 __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r) {
     const int lane = threadIdx.x & 31;
     uint32_t n_leaf = 0, n_set = 0;
@@ -695,7 +687,7 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
     if (lane == 0) {
         h.begin(0, 1, 0);
         h.fetch(p);
-        header_step<CFG, RING>(p, r, h, true);
+        header_step(p, r, h, true);
     }
     for (uint32_t n = 0;; n++) {
         // item n: descriptor posted; broadcast what the stream needs
@@ -707,26 +699,24 @@ __device__ __forceinline__ void producer_loop(const WalkParams& p, const Ring& r
         WarpWords w;
         w.init(p.stream + stream_off, slen, lane);
         if (lane == 0) h.begin(n + 1, slen, p.claim_lead);
-        produce_stream<CFG, RING>(p, r, w, slen, tile, n_leaf, n_set, h);
+        produce_stream<CFG>(p, r, w, slen, tile, n_leaf, n_set, h);
         if (lane == 0 && !h.posted) {
             if (!h.fetched) h.fetch(p);
-            header_step<CFG, RING>(p, r, h, true);
+            header_step(p, r, h, true);
         }
     }
 }
 
 // Walking warps: take the next descriptor; returns false when there is no more work.
-template <class CFG, int RING>
 __device__ __forceinline__ bool next_item(const Ring& r, uint32_t n, ItemDesc& d) {
-    using M = SmemMap<CFG, RING>;
     const uint32_t slot = n & 1u, phase = (n >> 1) & 1u;
     {
         PMFS_WP(0);
-        mbar_wait(r.bars + (M::bDescFull + slot) * 8, phase, r.limit_ns);
+        mbar_wait(r.bars + (kBarDescFull + slot) * 8, phase, r.limit_ns);
     }
     asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];"
                  : "=r"(d.chunk), "=r"(d.tile), "=r"(d.plen), "=r"(d.parent)
-                 : "r"(r.smem + M::kDesc + slot * 16)
+                 : "r"(r.smem + kSmemDesc + slot * 16)
                  : "memory");
     return d.chunk >= 0;
 }
@@ -749,23 +739,22 @@ __device__ __forceinline__ void finish_item(int* counter, uint32_t desc_empty_ba
 
 template <class CFG, int ALGO, bool POLY>
 __global__ void __launch_bounds__(CFG::Threads) fwd_kernel(const WalkParams p) {
-    using M = SmemMap<CFG, kSetRingFwd>;
     extern __shared__ uint4 smem[];
-    __shared__ __align__(8) unsigned long long bars[M::kBars];
-    const Ring ring = ring_setup<CFG, kSetRingFwd>(smem, bars, p.spin_limit_ns);
+    __shared__ __align__(8) unsigned long long bars[kBars];
+    const Ring ring = ring_setup<CFG>(smem, bars, p);
     if (threadIdx.x >= CFG::TPB) {
         PMFS_WP(10);
-        producer_loop<CFG, kSetRingFwd>(p, ring);
+        producer_loop<CFG>(p, ring);
         return;
     }
     PMFS_WP(5);
     uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
     ItemDesc d;
-    for (uint32_t n = 0; next_item<CFG, kSetRingFwd>(ring, n, d); n++) {
+    for (uint32_t n = 0; next_item(ring, n, d); n++) {
         const uint32_t slot = n & 1u;
         PMFS_TRACE_BEGIN
         {
-            DevEnv<CFG, false, kSetRingFwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            DevEnv<CFG, false> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
             Code4 forced[CFG::NG];
             const Code4* fp = nullptr;
             if (ALGO == kAlgoFitch && p.forced_planes) {
@@ -780,7 +769,7 @@ __global__ void __launch_bounds__(CFG::Threads) fwd_kernel(const WalkParams p) {
         }
         if (d.plen <= kProgWords) staged[slot]++;
         finish_item<CFG>(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr,
-                    ring.bars + (M::bDescEmpty + slot) * 8);
+                    ring.bars + (kBarDescEmpty + slot) * 8);
         PMFS_TRACE_END(d.chunk, d.tile)
     }
 }
@@ -794,24 +783,23 @@ constexpr int bwd_min_ctas() {
 }
 template <class CFG, int ALGO>
 __global__ void __launch_bounds__(CFG::Threads, bwd_min_ctas<CFG, ALGO>()) bwd_kernel(const WalkParams p) {
-    using M = SmemMap<CFG, kSetRingBwd>;
     extern __shared__ uint4 smem[];
-    __shared__ __align__(8) unsigned long long bars[M::kBars];
-    const Ring ring = ring_setup<CFG, kSetRingBwd>(smem, bars, p.spin_limit_ns);
+    __shared__ __align__(8) unsigned long long bars[kBars];
+    const Ring ring = ring_setup<CFG>(smem, bars, p);
     if (threadIdx.x >= CFG::TPB) {
         PMFS_WP(10);
-        producer_loop<CFG, kSetRingBwd>(p, ring);
+        producer_loop<CFG>(p, ring);
         return;
     }
     PMFS_WP(5);
     uint32_t n_leaf = 0, n_set = 0, staged[2] = {0, 0};
     ItemDesc d;
-    for (uint32_t n = 0; next_item<CFG, kSetRingBwd>(ring, n, d); n++) {
+    for (uint32_t n = 0; next_item(ring, n, d); n++) {
         const uint32_t slot = n & 1u;
         uint32_t err;
         PMFS_TRACE_BEGIN
         {
-            DevEnv<CFG, true, kSetRingBwd> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
+            DevEnv<CFG, true> env(p, ring, d, slot, staged[slot] & 1u, n_leaf, n_set, smem);
             if (p.cell_count) env.reserve_blocks();
             Code4 P[CFG::NG], forced[CFG::NG];
             uint32_t pv[CFG::NG], colmask[CFG::NG];
@@ -838,7 +826,7 @@ __global__ void __launch_bounds__(CFG::Threads, bwd_min_ctas<CFG, ALGO>()) bwd_k
         }
         if (err) atomicOr(p.err_flag, 1u);
         if (d.plen <= kProgWords) staged[slot]++;
-        finish_item<CFG>(nullptr, ring.bars + (M::bDescEmpty + slot) * 8);  // (child chunks were released by store_x)
+        finish_item<CFG>(nullptr, ring.bars + (kBarDescEmpty + slot) * 8);  // (child chunks were released by store_x)
         PMFS_TRACE_END(d.chunk, d.tile)
     }
 }

@@ -28,6 +28,8 @@ struct WalkParams {
     int32_t ctas_per_chunk;
     int32_t stack_depth;
     int32_t claim_lead;         // stream entries before the end of an item at which the producer claims the next one
+    int32_t leaf_ring_log2;     // operand rings of a CTA: 2^n leaf-row units and 2^n set slots in flight (walk_kernels.cuh)
+    int32_t set_ring_log2;
     const uint4* msa;           // first group of this column tile
     int64_t msa_stride16;       // uint4 per MSA row
     uint4* S;                   // [I][4][G]
@@ -72,7 +74,8 @@ struct WalkKernelSet {
     TileShape shape;
     const void* fwd[2][2];  // [algo][poly]
     const void* bwd[2];     // [algo]
-    size_t fwd_smem_fixed, bwd_smem_fixed;          // dynamic shared memory without the walk stack
+    size_t smem_fixed;                              // dynamic shared memory without rings and walk stack
+    size_t leaf_unit_bytes, set_slot_bytes;         // one ring entry of each kind
     size_t fwd_smem_per_level, bwd_smem_per_level;  // walk stack bytes per saved state
     // -DPMFS_WAITPROF builds only (null otherwise): clear / print the wait-time counters and dump the item timelines
     void (*prof_reset)();

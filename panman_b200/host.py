@@ -7,7 +7,8 @@ import numpy as np
 
 from .api import MUT_DTYPE, NUCMUT_DTYPE, PmfsError, lib
 
-HOST_EXPORTS = ["pmfs_host_last_error", "pmfs_host_free", "pmfs_host_parse_newick", "pmfs_host_build", "pmfs_host_pack"]
+HOST_EXPORTS = ["pmfs_host_last_error", "pmfs_host_free", "pmfs_host_parse_newick", "pmfs_host_build", "pmfs_host_pack",
+                "pmfs_host_writer_last_error", "pmfs_host_write_panman", "pmfs_host_build_panman"]
 
 
 def _L():
@@ -77,3 +78,31 @@ def pack(muts: np.ndarray, n_nodes: int):
     if rc != 0:
         _err(rc)
     return _take(off, n_nodes + 1, np.dtype("<i8")), _take(nuc, n.value, NUCMUT_DTYPE)
+
+
+def write_panman(parent, names, nuc_off, nuc, block_words, out_path: str, compress: bool = True, branch_length=None):
+    """pmfs_host_write_panman: the .panman writer alone (no device): tree in pre-order + per-node packed NucMut CSR."""
+    L = _L()
+    L.pmfs_host_writer_last_error.restype = C.c_char_p
+    par = np.ascontiguousarray(parent, dtype=np.int32)
+    off = np.ascontiguousarray(nuc_off, dtype=np.int64)
+    nm = np.ascontiguousarray(nuc, dtype=NUCMUT_DTYPE)
+    bw = np.ascontiguousarray(block_words, dtype=np.uint32)
+    bl = None if branch_length is None else np.ascontiguousarray(branch_length, dtype=np.float32)
+    joined = "".join(n + "\n" for n in names).encode()
+    rc = L.pmfs_host_write_panman(C.c_int32(par.shape[0]), C.c_void_p(par.ctypes.data), joined,
+                                  None if bl is None else C.c_void_p(bl.ctypes.data), C.c_void_p(off.ctypes.data),
+                                  C.c_void_p(nm.ctypes.data) if nm.shape[0] else None, C.c_void_p(bw.ctypes.data) if bw.shape[0] else None,
+                                  C.c_int64(bw.shape[0]), out_path.encode(), C.c_int(int(compress)))
+    if rc != 0:
+        raise PmfsError(rc, L.pmfs_host_writer_last_error().decode())
+
+
+def build_panman(msa_path: str, nwk_path: str, out_path: str, reference: str = "", low_mem: bool = False, device: int = 0,
+                 compress: bool = True):
+    """pmfs_host_build_panman: `panmanUtils -M msa -N nwk [--reference id] [--low-mem-mode] -o out` on a CUDA device."""
+    L = _L()
+    rc = L.pmfs_host_build_panman(msa_path.encode(), nwk_path.encode(), reference.encode(), int(low_mem), device,
+                                  out_path.encode(), int(compress))
+    if rc != 0:
+        _err(rc)

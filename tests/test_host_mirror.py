@@ -73,7 +73,7 @@ def test_pack_matches_oracle_rule(small_cases):
             assert (off == z[f"{name}/nuc_off{algo}"]).all() and G.same_nuc(nuc, z[f"{name}/nuc{algo}"]), (name, algo)
 
 
-def _write_c1(c1, tmp_path, crlf=False):
+def _write_c1(c1, tmp_path, crlf=False, description=" padded"):
     L = int(c1["n_cols"])
     msa = G.unpack_nibbles(c1["msa_nibbles"], L)
     rows = {str(k): i for i, k in enumerate(c1["row_ids"])}
@@ -81,7 +81,7 @@ def _write_c1(c1, tmp_path, crlf=False):
     eol = "\r\n" if crlf else "\n"
     with open(fa, "w", newline="") as f:
         for k in c1["fasta_order"]:
-            f.write(">" + str(k) + " padded" + eol + O.codes_to_chars(msa[rows[str(k)]]).tobytes().decode() + eol)
+            f.write(">" + str(k) + description + eol + O.codes_to_chars(msa[rows[str(k)]]).tobytes().decode() + eol)
     nw = tmp_path / "sars_20.nwk"
     nw.write_text(str(c1["newick"]) + "\n")
     return str(fa), str(nw)
@@ -116,3 +116,45 @@ def test_build_input_errors(c1, tmp_path):
     with pytest.raises(api.PmfsError) as e:
         host.build(fa, nw, "no_such_id", True)
     assert e.value.status == -13  # low-mem mode: "Reference not found" (src/panman.cpp:1582-1585)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not (O.ref_available() and os.path.exists(O.REF_SO)), reason="oracle/_ref absent")
+@pytest.mark.parametrize("low", [0, 1])
+@pytest.mark.parametrize("description", [" padded", ""])
+def test_build_c1_with_crlf_line_ends(c1, tmp_path, low, description):
+    """CRLF input.  The default reader strips '\\r' from rows and from every id but the LAST sequence's
+    (src/panman.cpp:1291-1302: with no description after the id that sequence then matches no tree leaf); the low-mem
+    reader (:667-714) strips nothing, so every row carries one more, all-'\\r' column.  Whatever the reference's driver
+    makes of it (oracle/ref_driver.cpp restates it), the mirror must make the same."""
+    fa, nw = _write_c1(c1, tmp_path, crlf=True, description=description)
+    try:
+        ref = O.ref_build(fa, nw, "", bool(low), threads=4)
+    except RuntimeError as e:  # the reference's driver gives up on this input: so must the mirror
+        with pytest.raises(api.PmfsError):
+            host.build(fa, nw, "", bool(low))
+        assert "rc=" in str(e)
+        return
+    r = host.build(fa, nw, "", bool(low))
+    assert r["names"] == ref["names"] and r["consensus"] == ref["consensus"]
+    assert G.same_muts(r["muts"], ref["muts"])
+    assert (r["nuc_off"] == ref["nuc_off"]).all() and G.same_nuc(r["nuc"], ref["nuc"])
+    assert (r["block_words"] == ref["block_words"]).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("low,with_ref", [(0, 0), (1, 1)])
+def test_build_panman_file_c1(c1, tmp_path, low, with_ref):
+    """The whole `panmanUtils -M .. -N .. [--reference id] [--low-mem-mode] -o out` on the GPU, .panman file included: what
+    an independent reader decodes from the file is the golden per-node NucMut CSR."""
+    from panman_reader import nuc_csr, read_panman
+    key = f"v{low}{with_ref}_"
+    fa, nw = _write_c1(c1, tmp_path)
+    out = str(tmp_path / "c1.panman")
+    host.build_panman(fa, nw, out, str(c1[key + "reference"]), bool(low))
+    d = read_panman(out)
+    off, nuc = nuc_csr(d)
+    assert nuc.shape[0] == int(c1[key + "n_nuc"]) and G.digest_nuc(off, nuc) == str(c1[key + "nuc_sha256"])
+    assert hashlib.sha256(d["consensusSeqMap"][0]["consensusSeq"].astype("<u4").tobytes()).hexdigest() == str(c1[key + "block_words_sha256"])
+    names, parent, _ = host.parse_newick(d["newick"])
+    assert names == [str(x) for x in c1["names"]] and (parent == c1["parent"]).all()
