@@ -133,6 +133,13 @@ int pmfs_run_chars(pmfs_ctx* ctx, int algo, const char* msa_chars, int64_t row_s
                    int64_t n_cols, const char* consensus_chars, const char* root_forced_chars, pmfs_mut** out,
                    int64_t* n_out);
 
+/* The same on rows that are NOT contiguous: rows[r] points to the n_cols characters of sequence r, wherever the caller
+ * keeps them -- the reference keeps a std::map<std::string, std::string> (src/panman.cpp:1271-1315), so a caller can pass
+ * the map's strings as they are.  The rows go through two pinned staging buffers: every character is touched once on the
+ * host, the upload of one chunk of rows overlaps the staging of the next, and the device keeps packed codes only. */
+int pmfs_run_char_rows(pmfs_ctx* ctx, int algo, const char* const* rows, int32_t n_rows, int64_t n_cols,
+                       const char* consensus_chars, const char* root_forced_chars, pmfs_mut** out, int64_t* n_out);
+
 /* Same call on unpacked STATE CODES, one byte per cell (low 4 bits used): for the callers of the path that do not come
  * from alignment characters.  The reference's block-level passes are this call on three states:
  * blockFitchForwardPassNew / BackwardPassNew / AssignMutationsNew (src/fitchSankoff.cpp:224-308, driven per block at

@@ -74,7 +74,7 @@ BATCH_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.
 
 _lib = None
 
-EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_tile", "pmfs_set_watchdog", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_codes",
+EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_tile", "pmfs_set_watchdog", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_char_rows", "pmfs_run_codes",
            "pmfs_result_free", "pmfs_run_device", "pmfs_run_batched", "pmfs_set_batch_cols", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_comm_unique_id", "pmfs_comm_create", "pmfs_comm_create_local", "pmfs_comm_destroy", "pmfs_comm_node_range", "pmfs_comm_batch_cols", "pmfs_comm_run", "pmfs_multi_create", "pmfs_multi_destroy", "pmfs_multi_run", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 

@@ -143,6 +143,8 @@ struct pmfs_ctx {
     size_t h_pk_out_cap = 0, h_pk_off_cap = 0;
     pmfs_mut* h_out = nullptr;  // pinned
     size_t h_out_cap = 0;
+    uint8_t* h_stage = nullptr;  // pinned: two staging buffers of pmfs_run_char_rows
+    size_t h_stage_cap = 0;
     std::vector<pmfs_mut> h_acc, h_big;  // pmfs_run in column batches: per-batch records, and the stitched result
     int64_t last_n_out = 0;
     pmfs_timing timing = {};

@@ -296,11 +296,11 @@ Tree::Tree(std::istream& fin, std::istream& secondFin, FILE_TYPE ftype, std::str
         }
     }
     if (L > 0) {
-        // rows as contiguous characters, in map order; the character -> code conversion of :1398-1406 / :1565-1571 and
-        // the nibble packing happen on the device (pmfs_run_chars)
-        std::vector<char> chars((size_t)std::max<size_t>(1, seqs.size()) * (size_t)L);
-        size_t row = 0;
-        for (const auto& u : seqs) memcpy(chars.data() + row++ * (size_t)L, u.second.data(), (size_t)L);
+        // the map's strings as they are, in map order: staged, uploaded and converted to packed codes chunk by chunk
+        // (pmfs_run_char_rows; the character -> code conversion of :1398-1406 / :1565-1571 happens on the device)
+        std::vector<const char*> rowPtrs;
+        rowPtrs.reserve(seqs.size());
+        for (const auto& u : seqs) rowPtrs.push_back(u.second.data());
         const char* forcedChars = nullptr;
         if (!reference.empty()) forcedChars = seqs.at(reference).data();  // refState (:1409) / defaultState (:1573-1580)
         pmfs_tree t = {V, parent.data(), childOff.data(), childIdx.data(), leafRow.data()};
@@ -309,8 +309,8 @@ Tree::Tree(std::istream& fin, std::istream& secondFin, FILE_TYPE ftype, std::str
         if (rc) throw BuildError(rc, pmfs_last_error());
         pmfs_mut* out = nullptr;
         int64_t n = 0;
-        rc = pmfs_run_chars(ctx, ftype == FILE_TYPE::MSA ? PMFS_FITCH : PMFS_SANKOFF, chars.data(), L, (int32_t)seqs.size(), L,
-                            consensusSeq.data(), forcedChars, &out, &n);
+        rc = pmfs_run_char_rows(ctx, ftype == FILE_TYPE::MSA ? PMFS_FITCH : PMFS_SANKOFF, rowPtrs.data(), (int32_t)seqs.size(), L,
+                                consensusSeq.data(), forcedChars, &out, &n);
         if (rc) {
             std::string msg = pmfs_last_error();
             pmfs_destroy(ctx);

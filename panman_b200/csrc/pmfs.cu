@@ -292,6 +292,7 @@ void pmfs_destroy(pmfs_ctx* c) {
     c->d_pk_tmp.release();
     c->d_skeys.release(); c->d_noff.release(); c->d_cuts.release();
     if (c->h_cuts) cudaFreeHost(c->h_cuts);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
     for (auto& ev : c->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto& ev : c->ev_slab)
@@ -1417,6 +1418,71 @@ static int run_bytes(pmfs_ctx* c, int algo, bool raw, const char* msa_chars, int
     }
     if (*n_out > 0)
         PMFS_CUDA(cudaMemcpyAsync(c->h_out, d_out, (size_t)*n_out * sizeof(pmfs_mut), cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    *out = c->h_out;
+    return PMFS_OK;
+}
+
+// Characters row by row, straight from wherever the caller keeps its sequences (the reference keeps a std::map of
+// std::strings, src/panman.cpp:1271-1315): the rows are staged through two pinned buffers, so the host touches every
+// character once (no contiguous second copy of the alignment), the upload of one chunk of rows overlaps the staging of
+// the next, the device converts to packed codes chunk by chunk, and only 0.5 B per cell stays resident.
+int pmfs_run_char_rows(pmfs_ctx* c, int algo, const char* const* rows, int32_t n_rows, int64_t n_cols, const char* consensus_chars,
+                       const char* forced_chars, pmfs_mut** out, int64_t* n_out) {
+    if (!c || (!rows && n_rows > 0) || !consensus_chars || !out || !n_out || n_cols <= 0 || n_rows < 0) {
+        g_error = "pmfs_run_char_rows: bad argument";
+        return PMFS_ERR_ARG;
+    }
+    PMFS_CUDA(cudaSetDevice(c->device));
+    const int64_t dstride = ((n_cols + 31) / 32) * 16;
+    const int64_t cstride = ((n_cols + 15) / 16) * 16;
+    const int64_t chunk_rows = std::max<int64_t>(1, std::min<int64_t>(std::max<int32_t>(1, n_rows), ((int64_t)32 << 20) / cstride));
+    int rc;
+    if ((rc = c->d_msa.ensure((size_t)std::max<int32_t>(1, n_rows) * dstride))) return rc;
+    if ((rc = c->d_chars.ensure((size_t)2 * chunk_rows * cstride + 16))) return rc;
+    if ((rc = c->d_cons.ensure((size_t)n_cols))) return rc;
+    if (forced_chars && (rc = c->d_forced.ensure((size_t)n_cols))) return rc;
+    const size_t stage_bytes = (size_t)chunk_rows * cstride;
+    if (c->h_stage_cap < 2 * stage_bytes) {
+        if (c->h_stage) cudaFreeHost(c->h_stage);
+        c->h_stage = nullptr;
+        c->h_stage_cap = 0;
+        PMFS_CUDA(cudaMallocHost(&c->h_stage, 2 * stage_bytes));
+        c->h_stage_cap = 2 * stage_bytes;
+    }
+    std::vector<uint8_t> cons((size_t)n_cols), forced(forced_chars ? (size_t)n_cols : 0);
+    for (int64_t i = 0; i < n_cols; i++) cons[i] = host_code_of_char(consensus_chars[i]);
+    for (size_t i = 0; i < forced.size(); i++) forced[i] = host_code_of_char(forced_chars[i]);
+    PMFS_CUDA(cudaEventRecord(c->ev[5], c->stream));
+    for (int64_t r0 = 0, k = 0; r0 < n_rows; r0 += chunk_rows, k++) {
+        const int64_t nr = std::min<int64_t>(chunk_rows, n_rows - r0);
+        uint8_t* h = c->h_stage + (k & 1) * stage_bytes;
+        uint8_t* d = c->d_chars.ptr + (k & 1) * stage_bytes;
+        if (k >= 2) PMFS_CUDA(cudaEventSynchronize(c->ev_slab[k & 1]));  // the copy out of this staging buffer has finished
+        for (int64_t r = 0; r < nr; r++) memcpy(h + r * cstride, rows[r0 + r], (size_t)n_cols);
+        PMFS_CUDA(cudaMemcpyAsync(d, h, (size_t)nr * cstride, cudaMemcpyHostToDevice, c->stream));
+        PMFS_CUDA(cudaEventRecord(c->ev_slab[k & 1], c->stream));
+        const int64_t total = (dstride / 4) * nr;
+        pack_chars_kernel<false><<<(unsigned)((total + 255) / 256), 256, 0, c->stream>>>(d, cstride, (int32_t)nr, n_cols, c->d_msa.ptr + r0 * dstride, dstride);
+        PMFS_CUDA(cudaGetLastError());
+    }
+    PMFS_CUDA(cudaMemcpyAsync(c->d_cons.ptr, cons.data(), (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
+    if (forced_chars) PMFS_CUDA(cudaMemcpyAsync(c->d_forced.ptr, forced.data(), (size_t)n_cols, cudaMemcpyHostToDevice, c->stream));
+    PMFS_CUDA(cudaEventRecord(c->ev[6], c->stream));
+    PMFS_CUDA(cudaEventSynchronize(c->ev[6]));
+    cudaEventElapsedTime(&c->timing.h2d_ms, c->ev[5], c->ev[6]);
+    pmfs_mut* d_out = nullptr;
+    rc = run_device_impl(c, algo, c->d_msa.ptr, dstride, n_rows, n_cols, c->d_cons.ptr, forced_chars ? c->d_forced.ptr : nullptr, &d_out, n_out);
+    if (rc) return rc;
+    if ((size_t)*n_out > c->h_out_cap || !c->h_out) {
+        if (c->h_out) cudaFreeHost(c->h_out);
+        c->h_out = nullptr;
+        c->h_out_cap = 0;
+        const size_t want = std::max<size_t>(1024, (size_t)*n_out + (size_t)*n_out / 4);
+        PMFS_CUDA(cudaMallocHost(&c->h_out, want * sizeof(pmfs_mut)));
+        c->h_out_cap = want;
+    }
+    if (*n_out > 0) PMFS_CUDA(cudaMemcpyAsync(c->h_out, d_out, (size_t)*n_out * sizeof(pmfs_mut), cudaMemcpyDeviceToHost, c->stream));
     PMFS_CUDA(cudaStreamSynchronize(c->stream));
     *out = c->h_out;
     return PMFS_OK;

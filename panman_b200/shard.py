@@ -130,13 +130,61 @@ def _as_tensor(ptr: int, n: int, dtype_str: str, device):
 _xbuf = {}
 
 
-def exchange_parts(ctx, rank: int, world: int, device, group=None, same_stream: bool = True):
+def gather_slices_by_node_range(rec, rank: int, world: int, n_nodes: int, group=None):
+    """The protocol of pmfs_comm_run (panman_b200/csrc/comm.cu) restated on torch tensors, for the CPU / gloo tests of the
+    multi-GPU host logic: rec is this rank's int32 [n,3] records (node, GLOBAL pos, payload) ordered by (node,pos); the
+    ranks' column ranges are disjoint and ascending with the rank.
+      1. noff[v] = first record of node v (the library gets it from the prefix sums that ordered the records),
+         cut[r] = noff[first node of rank r]: rank r's records are one contiguous slice of every source;
+      2. all-gather of the cut points; 3. all-to-all of the slices and of the matching noff ranges;
+      4. stitch: node v's list is the concatenation of its runs in source order -- no sort.
+    Returns this rank's node range [n_nodes*rank/world, n_nodes*(rank+1)/world) of the unsharded result."""
+    import torch
+    import torch.distributed as dist
+
+    bounds = [(n_nodes * r) // world for r in range(world + 1)]
+    nodes = rec[:, 0].contiguous()
+    noff = torch.searchsorted(nodes, torch.arange(n_nodes + 1, dtype=nodes.dtype)).to(torch.int64)
+    cuts = noff[torch.tensor(bounds)]
+    all_cuts = [torch.empty_like(cuts) for _ in range(world)]
+    dist.all_gather(all_cuts, cuts, group=group)
+    send_n = [int(cuts[p + 1] - cuts[p]) for p in range(world)]
+    recv_n = [int(all_cuts[s][rank + 1] - all_cuts[s][rank]) for s in range(world)]
+    inbox = torch.empty((sum(recv_n), 3), dtype=rec.dtype)
+    # (the slices are contiguous and in owner order: this rank's records ARE the send buffer)
+    dist.all_to_all_single(inbox, rec[int(cuts[0]):int(cuts[world])].contiguous(), output_split_sizes=recv_n, input_split_sizes=send_n,
+                           group=group)
+    recv = list(torch.split(inbox, recv_n))
+    n_own = bounds[rank + 1] - bounds[rank]
+    send_off = torch.cat([noff[bounds[p]:bounds[p + 1] + 1] for p in range(world)])
+    off_in = torch.empty(world * (n_own + 1), dtype=torch.int64)
+    dist.all_to_all_single(off_in, send_off, output_split_sizes=[n_own + 1] * world,
+                           input_split_sizes=[bounds[p + 1] - bounds[p] + 1 for p in range(world)], group=group)
+    recv_off = list(torch.split(off_in, n_own + 1))
+    runs = torch.stack([o[1:] - o[:-1] for o in recv_off])           # [source, owned node] run lengths
+    total = runs.sum(0)
+    start = torch.cumsum(total, 0) - total
+    out = torch.empty((int(total.sum()), 3), dtype=rec.dtype)
+    before = torch.cumsum(runs, 0) - runs                             # records of that node from lower ranks
+    for s in range(world):
+        rel = recv_off[s] - recv_off[s][0]
+        node_l = torch.repeat_interleave(torch.arange(n_own), runs[s])
+        idx = torch.arange(recv[s].shape[0]) - rel[node_l]
+        out[start[node_l] + before[s][node_l] + idx] = recv[s]
+    return out
+
+
+def exchange_parts(ctx, rank: int, world: int, device, group=None, same_stream: bool = False):
     """The data path's single exchange on GPUs, after a shard-mode pmfs_run_device on every rank: all-to-all of the
     64-bit records (already grouped by owning rank when they were emitted) over NCCL, then each rank orders what it
     received with the library's radix sort.  Returns (device pointer to this rank's pmfs_mut records, count).
 
-    same_stream: the context runs on torch's current stream (pmfs_set_stream), so the sort is ordered after the
-    all-to-all without a host synchronisation.  Small tensors and the inbox are reused across calls."""
+    (The first, radix-sorting form of the exchange, kept for the shard-mode entry points pmfs_set_shard / pmfs_get_parts /
+    pmfs_sort_records; bench.py and C++ callers use pmfs_comm_run, which needs no sort.)
+    same_stream: pass True only when the context was told to run on torch's current stream (Context.set_stream with that
+    stream's handle): the sort is then ordered after the all-to-all on the device.  Otherwise the all-to-all is
+    synchronised on the host first -- NCCL's work.wait() orders torch's stream, not the context's.  Small tensors and the
+    inbox are reused across calls."""
     import torch
     import torch.distributed as dist
 

@@ -272,3 +272,30 @@ def test_no_records_then_records_on_one_context():
                 got = ctx.run(algo, api.pack_nibbles(msa), L, cons)
                 assert (want.shape[0] == 0) == (msa is same)
                 assert G.same_muts(got, want), (algo, msa is same)
+
+
+def test_replaying_the_emitted_mutations_reproduces_every_leaf_row(c1):
+    """Semantic round trip of the CUDA path's output, independent of any oracle (tests/replay.py): config 1 in two CLI
+    variants with the device-side packing, and random polytomy trees with absent leaves and forced roots."""
+    import replay
+    tree = G.c1_tree(c1)
+    L = int(c1["n_cols"])
+    msa = G.unpack_nibbles(c1["msa_nibbles"], L)
+    for low, with_ref in ((0, 0), (1, 1)):
+        key = f"v{low}{with_ref}_"
+        forced = msa[list(c1["row_ids"]).index(str(c1[key + "reference"]))] if with_ref else None
+        with api.Context(tree) as ctx:
+            ctx.run(low, api.pack_nibbles(msa), L, c1[key + "consensus"], forced)
+            off, nuc = ctx.pack_last()
+        replay.assert_replay_reproduces_msa(tree, msa, c1[key + "consensus"], off, nuc)
+    rng = np.random.default_rng(18)
+    for trial in range(8):
+        t = synth.random_tree(int(rng.integers(3, 200)), rng, max_arity=6, absent_frac=0.1 if trial % 2 else 0.0)
+        m = synth.simulate_msa(t, 700, rng, p_sub=0.08, p_del=0.05, p_ins=0.2, p_n=0.05, p_amb=0.05)
+        cons = synth.consensus_first_nongap(m)
+        forced = m[0] if trial % 3 == 0 else None
+        for algo in (0, 1):
+            with api.Context(t) as ctx:
+                ctx.run(algo, api.pack_nibbles(m), 700, cons, forced)
+                off, nuc = ctx.pack_last()
+            replay.assert_replay_reproduces_msa(t, m, cons, off, nuc)

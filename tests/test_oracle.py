@@ -108,3 +108,33 @@ def test_block_passes_are_the_nucleotide_passes_on_three_states():
                 st2 = np.vstack([states, np.zeros((n_abs, B), np.uint8)])
             got = O.blocks_from_nuc(O.run_port(algo, t2, st2, cons, forced, threads=1))
             assert G.same_muts(got, want), (trial, algo)
+
+
+def test_replaying_the_mutations_reproduces_every_leaf_row(c1):
+    """The emitted mutations are a lossless encoding of the alignment given the tree and the consensus: replaying them
+    from the root (the rule the reference rebuilds sequences with, src/fasta.cpp:545-657) yields every leaf's row.  Checked
+    here on the oracle's output (config 1 in all four CLI variants, random polytomy trees with absent leaves and forced
+    roots) -- tests/test_gpu_parity.py runs the same check on the CUDA path's output."""
+    import golden_util as G
+    import replay
+    import synth
+    tree = G.c1_tree(c1)
+    L = int(c1["n_cols"])
+    msa = G.unpack_nibbles(c1["msa_nibbles"], L)
+    for low in (0, 1):
+        for with_ref in (0, 1):
+            key = f"v{low}{with_ref}_"
+            forced = msa[list(c1["row_ids"]).index(str(c1[key + "reference"]))] if with_ref else None
+            muts = O.run_port(low, tree, msa, c1[key + "consensus"], forced, threads=4)
+            off, nuc = O.pack_port(muts, tree.n_nodes)
+            replay.assert_replay_reproduces_msa(tree, msa, c1[key + "consensus"], off, nuc)
+    rng = np.random.default_rng(8)
+    for trial in range(6):
+        t = synth.random_tree(int(rng.integers(3, 120)), rng, max_arity=5, absent_frac=0.1 if trial % 2 else 0.0)
+        m = synth.simulate_msa(t, 300, rng, p_sub=0.08, p_del=0.05, p_ins=0.2, p_n=0.05, p_amb=0.05)
+        cons = synth.consensus_first_nongap(m)
+        forced = m[0] if trial % 3 == 0 else None
+        for algo in (0, 1):
+            muts = O.run_port(algo, t, m, cons, forced, threads=2)
+            off, nuc = O.pack_port(muts, t.n_nodes)
+            replay.assert_replay_reproduces_msa(t, m, cons, off, nuc)

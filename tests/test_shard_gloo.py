@@ -49,6 +49,11 @@ def _worker(rank, world, port, seed, q):
     nb, ne = shard.node_ranges(tree.n_nodes, world)[rank]
     sel = (want_all["node"] >= nb) & (want_all["node"] < ne)
     q.put(("x", rank, G.same_muts(shard.records_to_numpy(owned), want_all[sel]), int(sel.sum())))
+    # the protocol of pmfs_comm_run (ordered slices cut at the node boundaries, stitched without a sort)
+    g = shard.numpy_to_records(_to_mut12(mine))
+    g[:, 1] += b
+    sl = shard.gather_slices_by_node_range(g, rank, world, tree.n_nodes)
+    q.put(("s", rank, G.same_muts(shard.records_to_numpy(sl), want_all[sel]), int(sel.sum())))
     merged = shard.gather_records(shard.numpy_to_records(_to_mut12(mine)), b, rank, world)
     if rank == 0:
         got = shard.records_to_numpy(merged)
@@ -88,10 +93,12 @@ def test_gather_merge_pack_world2():
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
-    got = [q.get(timeout=10) for _ in range(3)]
+    got = [q.get(timeout=10) for _ in range(5)]
     ex = [g for g in got if g[0] == "x"]
     assert len(ex) == 2 and all(g[2] for g in ex) and all(g[3] > 0 for g in ex), ex  # all-to-all by node range
-    ok, straddle = [g for g in got if g[0] != "x"][0]
+    sl = [g for g in got if g[0] == "s"]
+    assert len(sl) == 2 and all(g[2] for g in sl), sl                                # pmfs_comm_run's protocol
+    ok, straddle = [g for g in got if g[0] not in ("x", "s")][0]
     assert ok
     assert straddle, "test input should contain a run of consecutive positions across the shard boundary"
 
