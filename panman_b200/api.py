@@ -25,7 +25,8 @@ class PmfsError(RuntimeError):
 
 
 def library_path() -> str:
-    return os.path.join(HERE, "libpmfs.so")
+    # PMFS_LIB: another build of the library (profiling / debugging variants, e.g. -DPMFS_WAITPROF)
+    return os.environ.get("PMFS_LIB") or os.path.join(HERE, "libpmfs.so")
 
 
 def build_library(force: bool = False) -> str:

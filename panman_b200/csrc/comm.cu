@@ -342,12 +342,7 @@ int pmfs_comm_batch_cols(pmfs_comm* m, int algo, int64_t cols_per_rank, int64_t 
         PMFS_CUDA(cudaStreamSynchronize(c->stream));
         g = m->h_red[0];
     }
-    if (g < G_all) {
-        const int64_t n_b = (G_all + g - 1) / g;
-        int64_t gb = ((G_all + n_b - 1) / n_b + 31) / 32 * 32;
-        if (gb > g) gb = g >= 32 ? g / 32 * 32 : g;
-        g = std::max<int64_t>(1, gb);
-    }
+    g = balanced_batch_groups(G_all, g);
     *batch_cols = std::min(cols_per_rank, g * 32);
     return PMFS_OK;
 }

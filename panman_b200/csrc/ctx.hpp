@@ -72,6 +72,7 @@ struct pmfs_ctx {
     Plan plan;
     bool has_poly = false;
     int32_t chunk_nodes_used = 0;
+    bool chunk_nodes_auto = false;  // the plan in use was made for an automatic (not a caller-given) chunk size
     std::vector<int32_t> parent, child_off, child_idx, leaf_row;  // kept for re-planning and synth
     int32_t tune_chunk_nodes = 0;
     int64_t tune_tile_cols = 0;
@@ -166,5 +167,7 @@ int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
                     const uint8_t* d_cons, const uint8_t* d_forced, pmfs_mut** d_out, int64_t* n_out);
 // Column groups whose set arrays fit in the device memory that is free now.
 int mem_limited_groups(pmfs_ctx* c, int algo, int64_t G_all, size_t extra_per_group, int64_t* groups);
+// Equal batches of at most gmax column groups, sized in multiples of a wide tile shape.
+int64_t balanced_batch_groups(int64_t G_all, int64_t gmax);
 
 }  // namespace pmfs

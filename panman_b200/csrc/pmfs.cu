@@ -174,16 +174,23 @@ static const WalkKernelSet* choose_shape(const pmfs_ctx* c, int64_t groups) {
             if (const WalkKernelSet* s = walk_kernel_set(nw, ng)) return s;
     }
     const int64_t I = c->plan.n_internal;
-    static const int wide_first[4][2] = {{4, 2}, {2, 2}, {1, 2}, {1, 1}};
+    // Measured on one B200 (profiles/r2_a_sweep_*.jsonl): binary trees -- 256 groups: 4x2; 128: 2x2; 64: 2x1 (7 % ahead of 1x2
+    // on the 16 M-node tree, 30 % on 1 000 taxa x 5 M columns); 32: 1x1.  Trees with polytomies: one group per thread at every
+    // width (the any-arity joins keep their counters in registers: half the state per thread; 4x1 is 15 % / 50 % ahead of 4x2
+    // for Fitch / Sankoff on a 20 000-taxon tree with 60 % of its edges collapsed).
+    static const int binary_first[4][2] = {{4, 2}, {2, 2}, {2, 1}, {1, 1}};
+    static const int poly_first[3][2] = {{4, 1}, {2, 1}, {1, 1}};
+    const int (*order)[2] = c->has_poly ? poly_first : binary_first;
+    const int n_order = c->has_poly ? 3 : 4;
     if ((int64_t)c->tree_height * 4 > I) {  // ladder-like: tiles are the parallelism
-        for (auto& s : wide_first) {
-            const WalkKernelSet* k = walk_kernel_set(s[0], s[1]);
+        for (int i = 0; i < n_order; i++) {
+            const WalkKernelSet* k = walk_kernel_set(order[i][0], order[i][1]);
             if ((groups + k->shape.groups() - 1) / k->shape.groups() >= 2 * 148) return k;
         }
         return walk_kernel_set(1, 1);
     }
-    for (auto& s : wide_first) {  // widest shape that pads the column range by at most a tenth
-        const WalkKernelSet* k = walk_kernel_set(s[0], s[1]);
+    for (int i = 0; i < n_order; i++) {  // widest shape that pads the column range by at most a tenth
+        const WalkKernelSet* k = walk_kernel_set(order[i][0], order[i][1]);
         const int64_t w = k->shape.groups(), padded = (groups + w - 1) / w * w;
         if (padded * 10 <= groups * 11) return k;
     }
@@ -262,6 +269,7 @@ int pmfs_create(pmfs_ctx** out, const pmfs_tree* tree, int device) {
         pmfs_destroy(c);
         return rc;
     }
+    c->chunk_nodes_auto = true;
     *out = c;
     return PMFS_OK;
 }
@@ -539,9 +547,15 @@ int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
     tile_groups = std::min(tile_groups, G_all);
 
     const int32_t want_chunk = c->tune_chunk_nodes > 0 ? c->tune_chunk_nodes : auto_chunk_nodes(P->n_nodes, tile_groups, TG);
-    if (want_chunk != c->chunk_nodes_used) {
+    // (an automatic target within 4x of the plan in use keeps that plan: column batches of different widths -- the ragged
+    // last batch of a run -- would otherwise re-plan back and forth, seconds each on a 16 M-node tree, for chunk sizes
+    // that the walk-stack cap decides anyway)
+    const bool close_enough = c->tune_chunk_nodes == 0 && c->chunk_nodes_used > 0 && want_chunk <= 4 * (int64_t)c->chunk_nodes_used &&
+                              c->chunk_nodes_used <= 4 * (int64_t)want_chunk && c->chunk_nodes_auto;
+    if (want_chunk != c->chunk_nodes_used && !close_enough) {
         int rc = replan(c, want_chunk);
         if (rc) return rc;
+        c->chunk_nodes_auto = c->tune_chunk_nodes == 0;
         P = &c->plan;
     }
     const int64_t NC = (int64_t)P->chunks.size();
@@ -912,6 +926,24 @@ int pmfs_set_batch_cols(pmfs_ctx* c, int64_t batch_cols) {
     return PMFS_OK;
 }
 
+}  // extern "C"
+
+// Equal batches of at most gmax column groups whose size is a multiple of a wide tile shape (128 groups when there is room
+// for two of them, else 64, else 32): a batch of, say, 157 groups would run on the narrowest shape or idle a fifth of a
+// wider one.
+namespace pmfs {
+int64_t balanced_batch_groups(int64_t G_all, int64_t gmax) {
+    if (gmax >= G_all) return G_all;
+    const int64_t q = gmax >= 256 ? 128 : (gmax >= 64 ? 64 : (gmax >= 32 ? 32 : 1));
+    const int64_t n_b = (G_all + gmax - 1) / gmax;
+    int64_t gb = ((G_all + n_b - 1) / n_b + q - 1) / q * q;
+    if (gb > gmax) gb = gmax / q * q;
+    return std::max<int64_t>(1, gb);
+}
+}  // namespace pmfs
+
+extern "C" {
+
 // Columns per batch: what the caller asked for, else as many as the set arrays of one batch fit in free device memory,
 // in equal batches whose size is a multiple of 32 column groups (whole output regions and tile shapes).
 static int batch_groups_for(pmfs_ctx* c, int algo, int64_t n_cols, int64_t batch_cols, size_t extra_per_group, int64_t* out) {
@@ -931,10 +963,7 @@ static int batch_groups_for(pmfs_ctx* c, int algo, int64_t n_cols, int64_t batch
         *out = G_all;
         return PMFS_OK;
     }
-    const int64_t n_b = (G_all + gmax - 1) / gmax;
-    int64_t gb = ((G_all + n_b - 1) / n_b + 31) / 32 * 32;
-    if (gb > gmax) gb = gmax >= 32 ? gmax / 32 * 32 : gmax;
-    *out = std::max<int64_t>(1, gb);
+    *out = balanced_batch_groups(G_all, gmax);
     return PMFS_OK;
 }
 
@@ -1240,10 +1269,7 @@ static int run_host_streaming(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t
         int64_t gmax = std::max<int64_t>(1, (int64_t)(free_b * 0.65) / per_group);
         const int64_t max_regions = std::max<int64_t>(1, ((int64_t)1 << 30) / std::max(1, c->plan.n_nodes));
         gmax = std::min(gmax, max_regions * 32);
-        const int64_t n_b = (G_all + gmax - 1) / gmax;
-        gb = ((G_all + n_b - 1) / n_b + 31) / 32 * 32;
-        if (gb > gmax) gb = gmax >= 32 ? gmax / 32 * 32 : gmax;
-        gb = std::min(G_all, std::max<int64_t>(1, gb));
+        gb = balanced_batch_groups(G_all, gmax);
     }
     const int64_t bstride = gb * 16;  // device row stride of a staged batch
     if ((rc = c->d_msa.ensure((size_t)2 * (size_t)std::max<int32_t>(1, n_rows) * (size_t)bstride))) return rc;

@@ -379,7 +379,11 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
                 load_operand(env, env.word(prog, pc++), A);
             } else {  // F_JOIN_IMM2
                 const uint32_t o1 = env.word(prog, pc++), o2 = env.word(prog, pc++);
+#ifdef PMFS_DBG_NO_CHERRY
+                if (false) {
+#else
                 if (!((o1 | o2) & kOperandSet) && o1 != kAbsentLeaf && o2 != kAbsentLeaf) {
+#endif
                     // a cherry (two leaves, a third of the internal nodes of a random binary tree): two one-element sets
                     // meet only if equal, and then their union is the same set -- S = {a} | {b} without a join;
                     // Sankoff's D1 is everything else where a != b and empty where a == b

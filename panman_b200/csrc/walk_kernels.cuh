@@ -287,6 +287,9 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
                 const uint32_t u = n_set & r.set_mask, par = (n_set >> r.set_log2) & 1u;
                 PMFS_WP(9);
                 mbar_wait(r.bars + (kBarSetEmpty + u) * 8, par ^ 1u, r.limit_ns);  // all walkers are done with the slot's previous set
+#ifdef PMFS_DBG_PROXY_FENCE
+                asm volatile("fence.proxy.async;" ::: "memory");
+#endif
                 // one node's set for this tile: 4 quarters of `tile_w` groups, contiguous (leaf_bytes = tile_w * 16)
                 mbar_arrive_expect_tx(r.bars + (kBarSetFull + u) * 8, 4 * leaf_bytes);
                 bulk_g2s(r.smem + r.off_set + u * CFG::SetBytes, p.S + (int64_t)(e & ~kStreamSet) * (4 * p.G) + g0 * 4, 4 * leaf_bytes,
@@ -298,6 +301,9 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
                 const uint32_t u = n_leaf & r.leaf_mask, par = (n_leaf >> r.leaf_log2) & 1u;
                 PMFS_WP(8);
                 mbar_wait(r.bars + (kBarLeafEmpty + u) * 8, par ^ 1u, r.limit_ns);
+#ifdef PMFS_DBG_PROXY_FENCE
+                asm volatile("fence.proxy.async;" ::: "memory");
+#endif
                 mbar_arrive_expect_tx(r.bars + (kBarLeafFull + u) * 8, leaf_bytes);
                 bulk_g2s(r.smem + kSmemLeaf + u * CFG::UnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
                          r.bars + (kBarLeafFull + u) * 8);
