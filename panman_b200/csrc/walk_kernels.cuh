@@ -155,6 +155,13 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+// Before the TMA engine may overwrite shared memory that the walking warps have been reading with ordinary loads (a ring
+// entry or a program buffer handed back through its `empty` mbarrier): the hand-back orders the walkers' reads before this
+// thread's later accesses in the GENERIC proxy only; the refill is a write through the ASYNC proxy, and without this
+// fence it can overtake reads that are still in flight.  Seen as one stale operand in ~10^7 (a whole leaf unit of the
+// wrong row, almost always in the two back-to-back leaf reads of a cherry), only with one column group per thread,
+// where the walkers outrun the producer -- profiles/r2_c_race_hunt.log.
+__device__ __forceinline__ void reuse_fence() { asm volatile("fence.proxy.async;" ::: "memory"); }
 // one contiguous global->shared copy by the TMA engine; completion is counted in bytes on `bar`
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
@@ -243,6 +250,7 @@ __device__ __forceinline__ void header_step(const WalkParams& p, const Ring& r, 
         }
         h.slot_free = true;
         if (h.valid && h.a.z <= kProgWords) {
+            reuse_fence();  // (the walkers read the program of two items ago out of this buffer)
             // (16-byte granularity: programs start at multiples of 4 words and the buffer is padded, see plan.cpp)
             const uint32_t bytes = (uint32_t)((h.a.z + 3) / 4) * 16u;
             mbar_arrive_expect_tx(r.bars + (kBarProg + slot) * 8, bytes);
@@ -287,9 +295,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
                 const uint32_t u = n_set & r.set_mask, par = (n_set >> r.set_log2) & 1u;
                 PMFS_WP(9);
                 mbar_wait(r.bars + (kBarSetEmpty + u) * 8, par ^ 1u, r.limit_ns);  // all walkers are done with the slot's previous set
-#ifdef PMFS_DBG_PROXY_FENCE
-                asm volatile("fence.proxy.async;" ::: "memory");
-#endif
+                reuse_fence();
                 // one node's set for this tile: 4 quarters of `tile_w` groups, contiguous (leaf_bytes = tile_w * 16)
                 mbar_arrive_expect_tx(r.bars + (kBarSetFull + u) * 8, 4 * leaf_bytes);
                 bulk_g2s(r.smem + r.off_set + u * CFG::SetBytes, p.S + (int64_t)(e & ~kStreamSet) * (4 * p.G) + g0 * 4, 4 * leaf_bytes,
@@ -301,9 +307,7 @@ __device__ __forceinline__ void produce_stream(const WalkParams& p, const Ring& 
                 const uint32_t u = n_leaf & r.leaf_mask, par = (n_leaf >> r.leaf_log2) & 1u;
                 PMFS_WP(8);
                 mbar_wait(r.bars + (kBarLeafEmpty + u) * 8, par ^ 1u, r.limit_ns);
-#ifdef PMFS_DBG_PROXY_FENCE
-                asm volatile("fence.proxy.async;" ::: "memory");
-#endif
+                reuse_fence();
                 mbar_arrive_expect_tx(r.bars + (kBarLeafFull + u) * 8, leaf_bytes);
                 bulk_g2s(r.smem + kSmemLeaf + u * CFG::UnitBytes, p.msa + (int64_t)e * p.msa_stride16 + g0, leaf_bytes,
                          r.bars + (kBarLeafFull + u) * 8);

@@ -108,6 +108,27 @@ def test_config4_bacterial_shape_full_size(algo):
         assert n > 50_000_000
 
 
+def test_config4_every_record_identical_across_tile_shapes_and_runs():
+    """All 71.6 M records of config 4 from the narrow-tile shapes, run several times each, against the 256-group shape:
+    identical down to the last record.  (This comparison is what exposed a one-in-10^7 stale operand in the shapes whose
+    walking warps outrun the producer warp: a TMA refill of a ring entry overtaking the walkers' reads of it, see
+    walk_kernels.cuh reuse_fence.  A column sample against the oracle cannot see a defect that rare.)"""
+    torch = _torch()
+    N, L = 1000, 5_000_000
+    tree = trees.random_binary_tree(N)
+    spec = api.SynthSpec(p_sub=2e-3, p_del=5e-3, p_ins=5e-3, p_n_block=1e-3, p_amb=1e-4, accessory_frac=0.35)
+    with api.Context(tree) as ctx:
+        d_msa, d_cons, stride = _synth(ctx, spec, N, L)
+        for algo in (api.FITCH, api.SANKOFF):
+            ctx.set_tile(4, 2)
+            want = shard.records_as_tensor(*ctx.run_device(algo, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr()), "cuda").clone()
+            for shape in ((4, 1), (2, 1), (1, 1), (2, 2)):
+                ctx.set_tile(*shape)
+                for rep in range(3):
+                    got = shard.records_as_tensor(*ctx.run_device(algo, d_msa.data_ptr(), stride, N, L, d_cons.data_ptr()), "cuda")
+                    assert got.shape == want.shape and bool((got == want).all()), (algo, shape, rep, got.shape, want.shape)
+
+
 @pytest.mark.parametrize("algo,n_sample", [(api.FITCH, 4096), (api.SANKOFF, 4096)])
 def test_config5_ladder_full_size(algo, n_sample):
     """BASELINE config 5: a 100 000-taxon caterpillar x 100 000 columns (serial depth 100 000: the reference's recursion
