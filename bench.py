@@ -143,32 +143,68 @@ def consensus_of(codes):
     return codes[nz.argmax(0), np.arange(codes.shape[1])]
 
 
+def subtree_sample(tree, max_nodes):
+    """A subtree of at most max_nodes nodes (ids are pre-order, so a subtree is the id range [v, v + size)), as a tree of
+    its own with its leaves' MSA rows renumbered -> (FlatTree, rows of the full alignment its leaves use)."""
+    import numpy as np
+    from panman_b200.trees import FlatTree
+    V = tree.n_nodes
+    size = np.ones(V, np.int64)
+    par = tree.parent
+    for v in range(V - 1, 0, -1):
+        size[par[v]] += size[v]
+    cand = np.nonzero((size <= max_nodes) & (size >= max_nodes // 4) & (tree.leaf_row == -1))[0]
+    v = int(cand[np.argmax(size[cand])]) if cand.size else 0
+    n = int(size[v])
+    ids = np.arange(v, v + n)
+    parent = (par[ids] - v).astype(np.int32)
+    parent[0] = -1
+    off = tree.child_off[v:v + n + 1].astype(np.int64)
+    child_idx = (tree.child_idx[off[0]:off[-1]] - v).astype(np.int32)
+    child_off = (off - off[0]).astype(np.int32)
+    rows_full = tree.leaf_row[ids].copy()
+    used = rows_full[rows_full >= 0]
+    remap = -np.ones(int(used.max()) + 1 if used.size else 1, np.int64)
+    remap[used] = np.arange(used.size)
+    leaf_row = np.where(rows_full >= 0, remap[np.maximum(rows_full, 0)], rows_full).astype(np.int32)
+    return FlatTree(parent, child_off, child_idx, leaf_row), used
+
+
 def reference_arm(args, tree, spec, workload, n_taxa, n_cols, ncpu):
     """bench.py --impl reference: the reference's CPU code alone -- no GPU, no product library.  Input: the CPU twin of
-    the synthetic alignment generator (oracle/synth_twin.c), a fresh random column sample per step."""
+    the synthetic alignment generator (oracle/synth_twin.c), a fresh random column sample per step.  On the 16 M-node tree
+    one column costs the reference's node-name-keyed hash maps about half a minute of one core, so a step of K-step runs
+    would take hours: there the sample of column.node updates is (random columns) x (one subtree of ~1 M nodes) -- the
+    reference's own code on a real part of the workload; its smaller hash maps make it, if anything, faster per update
+    than on the whole tree (the cpu_baseline of the main arm times whole columns once)."""
     import numpy as np
     from oracle import oracle_api as O
-    V = tree.n_nodes
-    cols_per_step = args.cpu_cols or max(8, min(2048, int(1.3e8 / V)))  # a few seconds of CPU work per step
-    ref = CpuReference(tree, ncpu)
+    V_full = tree.n_nodes
+    sub, sub_rows = (tree, None) if V_full <= 2_000_000 else subtree_sample(tree, 1_000_000)
+    V = sub.n_nodes
+    ref = CpuReference(sub, ncpu)
+    cols_per_step = args.cpu_cols or max(ref.threads, min(2048, int(4e7 / V)))  # a few seconds of CPU work per step
     rng = np.random.default_rng(0)
     times = []
     for it in range(args.warmup + args.steps):
         cols = np.sort(rng.choice(n_cols, size=cols_per_step, replace=False))
         codes = O.synth_columns(tree, spec, cols, n_taxa, threads=ncpu)
+        if sub_rows is not None:
+            codes = np.ascontiguousarray(codes[sub_rows])
         _, dt = ref.run(args.algo, codes, consensus_of(codes))
         if it >= args.warmup:
             times.append(dt)
     total = sum(times)
     val = V * cols_per_step * len(times) / total
+    what = (f"{cols_per_step} random columns of the workload per step x all {V} nodes" if sub_rows is None else
+            f"{cols_per_step} random columns of the workload per step x one subtree of {V} of the {V_full} nodes")
     line = {"metric": "column.node updates/sec", "value": val, "unit": "updates/s", "impl": "reference",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
             "higher_is_better": True, "scaling": "strong" if args.workload == "c3" else "weak", "vs_baseline": None,
             "dtype": "u16 bitsets / int32 costs", "data": "synthetic", "config": {"workload": workload},
             "cpu_baseline": {"value": val, "unit": "updates/s", "cores": ref.threads, "kind": ref.kind,
-                             "sample": f"{cols_per_step} random columns of the workload per step, all {V} nodes, "
-                                       f"{ref.threads} threads over columns, g++ -O2; the Node graph is built once, the column "
-                                       "loop alone is timed"},
+                             "sample": what + f", {ref.threads} threads over columns, g++ -O2; the Node graph is built once, the "
+                                              "column loop alone is timed"},
             "e2e": {"value": val, "unit": "updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
@@ -463,7 +499,8 @@ def cpu_baseline(args, ctx, tree, algo, d_msa, d_cons, stride, n_taxa, n_cols, n
     from panman_b200 import shard
     V = tree.n_nodes
     span = min(n_cols, 2048)  # sample inside the first columns: one device run of `span` columns gives the CUDA records
-    cols_n = args.cpu_cols or max(8, min(8192, int(6e8 / V)))
+    # (on the 16 M-node tree one column costs the reference ~30 s of one core: one column per host thread there)
+    cols_n = args.cpu_cols or max(min(ncpu, 16), min(8192, int(3e8 / V)))
     cols = np.sort(np.random.default_rng(0).choice(span, size=min(cols_n, span), replace=False))
     byte_cols = torch.from_numpy(cols // 2).to(d_msa.device)
     sub_bytes = d_msa[:, byte_cols].cpu().numpy()
