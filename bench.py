@@ -278,7 +278,10 @@ def main():
     ctx = api.Context(tree, device=local_rank)
     if args.chunk_nodes:
         ctx.set_tuning(chunk_nodes=args.chunk_nodes)
-    ctx.set_stream(torch.cuda.current_stream().cuda_stream)  # torch's stream: its events and NCCL work order with ours
+    # one stream for everything that is timed: the library's kernels, its NCCL exchange and torch's events and copies
+    bench_stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(bench_stream)
+    ctx.set_stream(bench_stream.cuda_stream)
     comm = None
     if world > 1 and strong:
         idt = torch.zeros(128, dtype=torch.uint8, device=dev)

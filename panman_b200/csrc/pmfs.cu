@@ -376,26 +376,32 @@ static size_t sync_ints(const Plan& P, int64_t groups, int tile_groups) {
 // Operand ring depths of a pass (log2 of leaf-row units / set slots in flight per CTA, walk_kernels.cuh).  The 256-group
 // shape keeps what BASELINE config 2 was tuned with (bottom-up 4 + 1: mostly leaves, and its walk stack and registers cap
 // the resident CTAs anyway; top-down 2 + 2: under 57 KB, so 4 CTAs share an SM).  Narrower tiles have smaller units: about
-// the same bytes in flight per SM need deeper rings.  On a ladder-like tree every column tile is ONE chain of dependent
-// nodes, its CTA is alone on its SM, and the ring depth is the number of operands in flight for the chain: as deep as
-// the barrier array allows.  PMFS_RINGS="fl,fs,bl,bs" (environment, log2 values) overrides, for sweeps.
-static void ring_depths(const pmfs_ctx* c, const WalkKernelSet& ks, bool fwd, int32_t* leaf_log2, int32_t* set_log2) {
+// the same bytes in flight per SM need deeper rings -- but not deeper than that: more shared memory per CTA costs
+// resident CTAs, and on the 16 M-node tree 16 + 4 / 8 + 8 entries ran 40 % slower than 8 + 2 / 4 + 4
+// (profiles/r2_b_ring_sweep.log; a ladder, one chain of dependent nodes per column tile, does not care either way: its
+// walkers wait for instructions, not for operands).  PMFS_RINGS="fl,fs,bl,bs" (environment, log2 values) overrides.
+static void ring_depths(const pmfs_ctx* c, const WalkKernelSet& ks, bool fwd, int stack_depth, int32_t* leaf_log2, int32_t* set_log2) {
     const int groups = ks.shape.groups();
     int fl, fs, bl, bs;
     if (groups >= 256) { fl = 2; fs = 0; bl = 1; bs = 1; }
     else if (groups >= 128) { fl = 2; fs = 1; bl = 2; bs = 1; }
     else if (groups >= 64) { fl = 3; fs = 1; bl = 2; bs = 2; }
     else { fl = 3; fs = 2; bl = 3; bs = 2; }
-    if ((int64_t)c->tree_height * 4 > c->plan.n_internal) {  // ladder-like
-        fl = 5; fs = 0; bl = 4; bs = 4;
-    }
     if (const char* e = getenv("PMFS_RINGS")) {
         int a, b, d, f;
         if (sscanf(e, "%d,%d,%d,%d", &a, &b, &d, &f) == 4) { fl = a; fs = b; bl = d; bs = f; }
     }
     auto clamp = [](int v, int hi) { return v < 0 ? 0 : (v > hi ? hi : v); };
-    *leaf_log2 = clamp(fwd ? fl : bl, 5);  // kMaxLeafRing = 32
-    *set_log2 = clamp(fwd ? fs : bs, 4);   // kMaxSetRing = 16
+    int l = clamp(fwd ? fl : bl, 5), t = clamp(fwd ? fs : bs, 4);  // kMaxLeafRing = 32, kMaxSetRing = 16
+    // (whatever was asked for: the rings and the walk stack have to fit in one CTA's shared memory)
+    const size_t stack = (size_t)stack_depth * (fwd ? ks.fwd_smem_per_level : ks.bwd_smem_per_level);
+    while (ks.smem_fixed + (ks.leaf_unit_bytes << l) + (ks.set_slot_bytes << t) + stack > 160 * 1024 && (l > 0 || t > 0)) {
+        if ((ks.leaf_unit_bytes << l) >= (ks.set_slot_bytes << t) && l > 0) l--;
+        else if (t > 0) t--;
+        else l--;
+    }
+    *leaf_log2 = l;
+    *set_log2 = t;
 }
 
 // One launch per pass over all chunks (the name is historical: the first version launched once per chunk level).
@@ -432,7 +438,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     const size_t per_pass = (size_t)n_items;
     wp.next_item = sync + (fwd ? 0 : 32);
     wp.ready = sync + 64 + (fwd ? 0 : per_pass);
-    ring_depths(c, ks, fwd, &wp.leaf_ring_log2, &wp.set_ring_log2);
+    ring_depths(c, ks, fwd, fwd ? P.fwd_stack_depth : P.bwd_stack_depth, &wp.leaf_ring_log2, &wp.set_ring_log2);
     const size_t smem = ks.smem_fixed + (ks.leaf_unit_bytes << wp.leaf_ring_log2) + (ks.set_slot_bytes << wp.set_ring_log2) +
                         (fwd ? (size_t)P.fwd_stack_depth * ks.fwd_smem_per_level : (size_t)P.bwd_stack_depth * ks.bwd_smem_per_level);
     if (smem > 200 * 1024) {

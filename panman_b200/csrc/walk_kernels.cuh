@@ -161,7 +161,32 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 // fence it can overtake reads that are still in flight.  Seen as one stale operand in ~10^7 (a whole leaf unit of the
 // wrong row, almost always in the two back-to-back leaf reads of a cherry), only with one column group per thread,
 // where the walkers outrun the producer -- profiles/r2_c_race_hunt.log.
-__device__ __forceinline__ void reuse_fence() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// PMFS_REUSE_MODE (build variants kept for the record of how this was settled, profiles/README.md):
+//   1  fence.proxy.async in the producer before every refill: correct, but the fence also waits for the producer's own
+//      copies still in flight, which serialises the ring (config 2 +14 %, config 3 +40 %)
+//   2  the same fence restricted to shared memory (.shared::cta)
+//   3  no fence; the walkers hand an entry back only after its data has ARRIVED in their registers (the hand-back takes a
+//      value that depends on the loaded words), so no read of the old contents can still be in flight when the refill
+//      is issued
+#ifndef PMFS_REUSE_MODE
+#define PMFS_REUSE_MODE 3
+#endif
+__device__ __forceinline__ void reuse_fence() {
+#if PMFS_REUSE_MODE == 1
+    asm volatile("fence.proxy.async;" ::: "memory");
+#elif PMFS_REUSE_MODE == 2
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
+}
+// Zero at run time, but only computable once `loaded` -- XOR of one word of every ld.shared of the entry being handed
+// back -- has been delivered: added to the address of the hand-back arrive.  (__shfl_sync of a lane's own value.)
+__device__ __forceinline__ uint32_t after_loads(uint32_t loaded) {
+#if PMFS_REUSE_MODE == 3
+    return __shfl_sync(0xffffffffu, loaded, threadIdx.x & 31) ^ loaded;
+#else
+    return 0u;
+#endif
+}
 // one contiguous global->shared copy by the TMA engine; completion is counted in bytes on `bar`
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
@@ -394,10 +419,15 @@ struct DevEnv {
         PMFS_WP(2);
         mbar_wait(ring.bars + (kBarLeafFull + u) * 8, par, ring.limit_ns);
         const uint32_t base = ring.smem + kSmemLeaf + u * CFG::UnitBytes + threadIdx.x * 16;
+        uint32_t loaded = 0;
 #pragma unroll
-        for (int j = 0; j < CFG::NG; j++) w[j] = lds128(base + j * (CFG::TPB * 16));
+        for (int j = 0; j < CFG::NG; j++) {
+            w[j] = lds128(base + j * (CFG::TPB * 16));
+            loaded ^= w[j].x;
+        }
+        const uint32_t zero = after_loads(loaded);
         __syncwarp();
-        if (lane == 0) mbar_arrive(ring.bars + (kBarLeafEmpty + u) * 8);
+        if (lane == 0) mbar_arrive(ring.bars + (kBarLeafEmpty + u) * 8 + zero);
         n_leaf++;
     }
     // next set slot (a set written by an earlier work item): 4 quarters x CFG::NG groups
@@ -406,15 +436,18 @@ struct DevEnv {
         PMFS_WP(3);
         mbar_wait(ring.bars + (kBarSetFull + u) * 8, par, ring.limit_ns);
         const uint32_t base = ring.smem + ring.off_set + u * CFG::SetBytes + threadIdx.x * 16;
+        uint32_t loaded = 0;
 #pragma unroll
         for (int j = 0; j < CFG::NG; j++)
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 const uint4 v = lds128(base + (i * tile_w + j * CFG::TPB) * 16);
                 s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
+                loaded ^= v.x;
             }
+        const uint32_t zero = after_loads(loaded);
         __syncwarp();
-        if (lane == 0) mbar_arrive(ring.bars + (kBarSetEmpty + u) * 8);
+        if (lane == 0) mbar_arrive(ring.bars + (kBarSetEmpty + u) * 8 + zero);
         n_set++;
     }
 
@@ -508,20 +541,57 @@ struct DevEnv {
     }
     __device__ __forceinline__ bool any(bool x) const { return __any_sync(0xffffffffu, x); }
 
-    // Stream compaction of one node's mutations, warp-cooperative.  Called by all 32 lanes (the caller branches on a
-    // warp vote).  One REDUX gives the warp's record count, ONE atomic reserves the slots; then, for every lane that has
-    // mutations, its mask and planes are broadcast and each lane of the warp writes the record of "its" bit -- a block of
-    // 32 N's costs the same ~40 instructions as a single substitution, and the stores are coalesced.  The order inside
-    // the buffer depends on scheduling; the final radix sort by (node,pos) makes the result deterministic.
+    // Stream compaction of one node's mutations.  Called by all 32 lanes (the caller branches on a warp vote); the slots
+    // [base, base + total) were reserved by the caller, `base` is advanced past them.  A warp prefix sum over the lanes'
+    // record counts gives every lane the place of its own records (lane order = column-group order, so ranks are column
+    // order).  Lanes with a few mutations -- the common case away from blocks of N: single substitutions and indels
+    // scattered over the lanes -- write their own records, one loop over their set bits in column order.  Lanes with MANY
+    // (a 32-column block of N, a long insertion) are served by the whole warp instead: mask and planes are broadcast and
+    // each lane writes the record of "its" bit, so that such a block costs ~40 instructions, with coalesced stores.
+    // (Before the per-lane path every lane with mutations was served cooperatively: on the bacterial-shaped config 4,
+    // where the average call has seven lanes with one mutation each, emission was most of the top-down pass.)
+    static constexpr uint32_t kDenseLane = 4;
+    __device__ __forceinline__ unsigned long long make_record(uint32_t node, unsigned long long pos, uint32_t cg, uint32_t cp) const {
+        // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
+        const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
+        const unsigned long long key = ((unsigned long long)node << p.pos_bits) | pos;
+        return (key << kPayloadBits) | type | (cg << 2) | (cp << 6);
+    }
     __device__ void emit1(uint32_t node, unsigned long long* out, unsigned long long& base, uint32_t m, const Code4& G,
                           const Code4& P, int64_t gw) const {
         const unsigned full = 0xffffffffu;
-        uint32_t srcs = __ballot_sync(full, m != 0);
-        const unsigned long long pos0 = (unsigned long long)(p.pos_offset + p.col_base + gw * 32 + column_of_bit(lane));
+        const uint32_t cnt = __popc(m);
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(full, incl, d);
+            if (lane >= d) incl += t;
+        }
+        const uint32_t excl = incl - cnt, total = __shfl_sync(full, incl, 31);
+        const unsigned long long col0 = (unsigned long long)(p.pos_offset + p.col_base + gw * 32);  // first column of lane 0's group
+        if (cnt != 0 && cnt <= kDenseLane) {
+            unsigned long long idx = base + excl;
+            const unsigned long long mine = col0 + (unsigned long long)lane * 32;
+#pragma unroll 1
+            for (int r = 0; r < 4; r++) {  // bit q is column 8*(q&3) + (q>>2): residue by residue, ascending q inside
+                uint32_t mr = m & (0x11111111u << r);
+                while (mr) {
+                    const int q = __ffs(mr) - 1;
+                    mr &= mr - 1;
+                    const uint32_t cg = ((G.b[0] >> q) & 1u) | (((G.b[1] >> q) & 1u) << 1) | (((G.b[2] >> q) & 1u) << 2) | (((G.b[3] >> q) & 1u) << 3);
+                    const uint32_t cp = ((P.b[0] >> q) & 1u) | (((P.b[1] >> q) & 1u) << 1) | (((P.b[2] >> q) & 1u) << 2) | (((P.b[3] >> q) & 1u) << 3);
+                    if (idx < p.out_cap) out[idx] = make_record(node, mine + (unsigned long long)(8 * r + (q >> 2)), cg, cp);
+                    idx++;
+                }
+            }
+        }
+        uint32_t srcs = __ballot_sync(full, cnt > kDenseLane);
+        const unsigned long long pos0 = col0 + (unsigned long long)column_of_bit(lane);
         while (srcs) {
             const int src = __ffs(srcs) - 1;
             srcs &= srcs - 1;
             const uint32_t mm = __shfl_sync(full, m, src);
+            const unsigned long long at = base + __shfl_sync(full, excl, src);
             uint32_t cg = 0, cp = 0;
 #pragma unroll
             for (int i = 0; i < 4; i++) {
@@ -529,16 +599,11 @@ struct DevEnv {
                 cp |= ((__shfl_sync(full, P.b[i], src) >> lane) & 1u) << i;
             }
             if ((mm >> lane) & 1u) {
-                const unsigned long long idx = base + __popc(mm & ltmask);  // rank in COLUMN order
-                if (idx < p.out_cap) {
-                    // parent gap -> insertion; node gap -> deletion; else substitution (fitchSankoff.cpp:139-167, :683-698)
-                    const uint32_t type = cp == 0 ? PMFS_NI : (cg == 0 ? PMFS_ND : PMFS_NS);
-                    const unsigned long long key = ((unsigned long long)node << p.pos_bits) | (pos0 + (unsigned long long)src * 32);
-                    out[idx] = (key << kPayloadBits) | type | (cg << 2) | (cp << 6);
-                }
+                const unsigned long long idx = at + __popc(mm & ltmask);  // rank in COLUMN order
+                if (idx < p.out_cap) out[idx] = make_record(node, pos0 + (unsigned long long)src * 32, cg, cp);
             }
-            base += __popc(mm);
         }
+        base += total;
     }
     // Two output layouts.  Regions per 32 column groups (single-GPU runs): the records of one (node, region) pair come
     // from exactly one call, are written contiguously in column order, and regions are laid out in column order -- so a

@@ -1,5 +1,6 @@
-"""Per-kernel metrics out of `ncu --set full` reports -> profiles/<tag>_ncu_full_c2_<algo>.csv and profiles/traffic_r1.json
-(the DRAM bytes bench.py reports as roofline.traffic).  usage: python profiles/ncu_extract.py <tag> fitch=<rep> sankoff=<rep>"""
+"""Per-kernel metrics out of `ncu --set full` reports -> profiles/<tag>_ncu_full_<workload>_<algo>.csv and
+profiles/traffic_<round>.json (DRAM bytes per launch of the walk kernels, with the commit they were captured at).
+usage: python profiles/ncu_extract.py <tag> <workload>:<algo>=<rep> ...   (tag e.g. r2_c)"""
 import csv
 import io
 import json
@@ -24,13 +25,15 @@ METRICS = ["launch__grid_size", "launch__block_size", "launch__registers_per_thr
            "smsp__average_warps_issue_stalled_sleeping_per_issue_active.ratio"]
 tag = sys.argv[1]
 traffic = {}
+commit = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True, cwd=HERE).stdout.strip()
 for arg in sys.argv[2:]:
-    algo, rep = arg.split("=")
+    wa, rep = arg.split("=")
+    workload, algo = wa.split(":")
     out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     hdr, units, data = rows[0], rows[1], rows[2:]
     cols = [hdr.index("Kernel Name")] + [hdr.index(m) for m in METRICS if m in hdr]
-    with open(os.path.join(HERE, f"{tag}_ncu_full_c2_{algo}.csv"), "w", newline="") as f:
+    with open(os.path.join(HERE, f"{tag}_ncu_full_{workload}_{algo}.csv"), "w", newline="") as f:
         w = csv.writer(f)
         w.writerow([hdr[i] for i in cols])
         w.writerow([units[i] for i in cols])
@@ -53,9 +56,15 @@ for arg in sys.argv[2:]:
         ks.append(k)
         if "fwd_kernel" in name or "bwd_kernel" in name:
             total += k["dram_read_bytes"] + k["dram_write_bytes"]
-    traffic[algo] = {"kernels": ks, "traffic_bytes_per_step": total}
-json.dump(traffic, open(os.path.join(HERE, "traffic_r1.json"), "w"), indent=1)
-print(json.dumps({a: t["traffic_bytes_per_step"] for a, t in traffic.items()}))
-for a, t in traffic.items():
-    for k in t["kernels"]:
-        print(a, k)
+    traffic.setdefault(workload, {})[algo] = {"kernels": ks, "traffic_bytes_per_step": total,
+                                              "source": f"ncu --set full --clock-control none, {os.path.basename(rep)}, capture {tag} at commit {commit}"}
+out_path = os.path.join(HERE, "traffic_" + tag.split("_")[0] + ".json")
+old = json.load(open(out_path)) if os.path.exists(out_path) else {}
+for w, d in traffic.items():
+    old.setdefault(w, {}).update(d)
+json.dump(old, open(out_path, "w"), indent=1)
+for w, d in traffic.items():
+    for a, t in d.items():
+        print(w, a, t["traffic_bytes_per_step"])
+        for k in t["kernels"]:
+            print("  ", k)
