@@ -161,15 +161,16 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 // fence it can overtake reads that are still in flight.  Seen as one stale operand in ~10^7 (a whole leaf unit of the
 // wrong row, almost always in the two back-to-back leaf reads of a cherry), only with one column group per thread,
 // where the walkers outrun the producer -- profiles/r2_c_race_hunt.log.
-// PMFS_REUSE_MODE (build variants kept for the record of how this was settled, profiles/README.md):
-//   1  fence.proxy.async in the producer before every refill: correct, but the fence also waits for the producer's own
-//      copies still in flight, which serialises the ring (config 2 +14 %, config 3 +40 %)
-//   2  the same fence restricted to shared memory (.shared::cta)
+// PMFS_REUSE_MODE (build variants kept for the record of how this was settled, profiles/r2_e_reuse_hunt.log: all three
+// give identical records on all of config 4; times are config 2 / config 3's 2 048-column slice):
+//   1  fence.proxy.async in the producer before every refill: 0.814 / 26.4 ms -- the unqualified fence also orders the
+//      producer's global-memory accesses, which stalls the ring
+//   2  the same fence restricted to shared memory (.shared::cta), the state space the hazard is in: 0.730 / 18.7 ms.  DEFAULT
 //   3  no fence; the walkers hand an entry back only after its data has ARRIVED in their registers (the hand-back takes a
-//      value that depends on the loaded words), so no read of the old contents can still be in flight when the refill
-//      is issued
+//      value that depends on the loaded words), so no read of the old contents can be in flight when the refill is
+//      issued: 0.741 / 19.0 ms
 #ifndef PMFS_REUSE_MODE
-#define PMFS_REUSE_MODE 3
+#define PMFS_REUSE_MODE 2
 #endif
 __device__ __forceinline__ void reuse_fence() {
 #if PMFS_REUSE_MODE == 1
@@ -560,6 +561,30 @@ struct DevEnv {
     __device__ void emit1(uint32_t node, unsigned long long* out, unsigned long long& base, uint32_t m, const Code4& G,
                           const Code4& P, int64_t gw) const {
         const unsigned full = 0xffffffffu;
+        const unsigned long long col0 = (unsigned long long)(p.pos_offset + p.col_base + gw * 32);  // first column of lane 0's group
+        const unsigned long long pos0 = col0 + (unsigned long long)column_of_bit(lane);
+        uint32_t srcs = __ballot_sync(full, m != 0);
+        if (__popc(srcs) <= 2) {
+            // one or two lanes with mutations (a block of N at a leaf, a lone substitution: nearly every call on
+            // SARS-CoV-2-shaped data): serve them cooperatively right away, without the prefix sum
+            while (srcs) {
+                const int src = __ffs(srcs) - 1;
+                srcs &= srcs - 1;
+                const uint32_t mm = __shfl_sync(full, m, src);
+                uint32_t cg = 0, cp = 0;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    cg |= ((__shfl_sync(full, G.b[i], src) >> lane) & 1u) << i;
+                    cp |= ((__shfl_sync(full, P.b[i], src) >> lane) & 1u) << i;
+                }
+                if ((mm >> lane) & 1u) {
+                    const unsigned long long idx = base + __popc(mm & ltmask);  // rank in COLUMN order
+                    if (idx < p.out_cap) out[idx] = make_record(node, pos0 + (unsigned long long)src * 32, cg, cp);
+                }
+                base += __popc(mm);
+            }
+            return;
+        }
         const uint32_t cnt = __popc(m);
         uint32_t incl = cnt;
 #pragma unroll
@@ -568,7 +593,6 @@ struct DevEnv {
             if (lane >= d) incl += t;
         }
         const uint32_t excl = incl - cnt, total = __shfl_sync(full, incl, 31);
-        const unsigned long long col0 = (unsigned long long)(p.pos_offset + p.col_base + gw * 32);  // first column of lane 0's group
         if (cnt != 0 && cnt <= kDenseLane) {
             unsigned long long idx = base + excl;
             const unsigned long long mine = col0 + (unsigned long long)lane * 32;
@@ -585,8 +609,7 @@ struct DevEnv {
                 }
             }
         }
-        uint32_t srcs = __ballot_sync(full, cnt > kDenseLane);
-        const unsigned long long pos0 = col0 + (unsigned long long)column_of_bit(lane);
+        srcs = __ballot_sync(full, cnt > kDenseLane);
         while (srcs) {
             const int src = __ffs(srcs) - 1;
             srcs &= srcs - 1;
