@@ -356,9 +356,21 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
     Planes16 T[NG];
 #pragma unroll
     for (int j = 0; j < NG; j++) zero16(T[j]);
+    // Program words are fetched three ahead of their use (an op has at most two operand words): the load of a word --
+    // shared memory for staged programs, L1/L2 for long ones -- is then never waited for.  (Reading up to three words past
+    // the end of a program is harmless: programs are padded, see plan.cpp.)
     int32_t pc = 0;
+    uint32_t q0 = env.word(prog, 0), q1 = env.word(prog, 1), q2 = env.word(prog, 2);
+    auto take = [&]() {
+        const uint32_t r = q0;
+        q0 = q1;
+        q1 = q2;
+        q2 = env.word(prog, pc + 3);
+        pc++;
+        return r;
+    };
     while (pc < len) {
-        const uint32_t w = env.word(prog, pc++);
+        const uint32_t w = take();
         const uint32_t code = w & ((1u << kOpBits) - 1), id = w >> kOpBits;
         if (code == F_PUSH) {
             env.push(T);
@@ -367,18 +379,19 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
         Planes16 D1[NG];
         if (code == F_POLY) {
             if (POLY) {
-                const uint32_t k = env.word(prog, pc++);
+                const uint32_t k = take();
                 poly_join<ALGO>(env, prog, pc, k, T, D1);
                 pc += (int32_t)k;
+                q0 = env.word(prog, pc); q1 = env.word(prog, pc + 1); q2 = env.word(prog, pc + 2);
             }
         } else {
             Planes16 A[NG];
             if (code == F_JOIN_POP) {
                 env.pop(A);
             } else if (code == F_JOIN_IMM) {
-                load_operand(env, env.word(prog, pc++), A);
+                load_operand(env, take(), A);
             } else {  // F_JOIN_IMM2
-                const uint32_t o1 = env.word(prog, pc++), o2 = env.word(prog, pc++);
+                const uint32_t o1 = take(), o2 = take();
 #ifdef PMFS_DBG_NO_CHERRY
                 if (false) {
 #else
@@ -441,8 +454,10 @@ PMFS_HD uint32_t backward_walk(Env& env, const uint32_t* prog, int32_t len, Code
     constexpr int NG = Env::kGroups;
     uint32_t err = 0;
     int32_t pc = 0;
+    uint32_t w_next = env.word(prog, 0);  // every op is one word: fetched one op ahead
     while (pc < len) {
-        const uint32_t w = env.word(prog, pc++);
+        const uint32_t w = w_next;
+        w_next = env.word(prog, ++pc);
         const uint32_t code = w & ((1u << kOpBits) - 1), arg = w >> kOpBits;
         if (code == B_ENTER) {
             Planes16 S[NG];
