@@ -378,8 +378,13 @@ def main():
     e1.record()
     barrier()
     clocks = sampler.stop()
-    total_ms, pass_ms, xchg_ms, stitch_ms, sort_ms = allmax([e0.elapsed_time(e1), totals["fwd"] + totals["bwd"], totals["xchg"],
-                                                            totals["stitch"], totals["sort"]])
+    mine_ms = [e0.elapsed_time(e1), totals["fwd"] + totals["bwd"], totals["xchg"], totals["stitch"], totals["sort"]]
+    total_ms, pass_ms, xchg_ms, stitch_ms, sort_ms = allmax(mine_ms)
+    per_rank = None
+    if world > 1:  # every rank's own phase times (the maxima above hide how much of `exchange` is waiting for the slowest rank)
+        g = torch.zeros((world, 5), device=dev, dtype=torch.float64)
+        dist.all_gather_into_tensor(g.view(-1), torch.tensor(mine_ms, device=dev, dtype=torch.float64))
+        per_rank = [[round(float(v) / args.steps, 3) for v in row] for row in g.cpu()]
     updates_per_step = V * n_cols * (1 if strong else world)
     value = updates_per_step * args.steps / (total_ms * 1e-3)
     plan = ctx.plan_info()
@@ -477,7 +482,9 @@ def main():
                          "frac_whole_step": design / step_s / 1e9 / hbm_peak},
             "e2e": e2e, "gpu_launches": int(mine["launches"]), "clocks": clocks,
             "phases_ms_per_step": {"forward+backward": pass_ms / args.steps, "ordering": sort_ms / args.steps,
-                                   "exchange": xchg_ms / args.steps, "stitch": stitch_ms / args.steps},
+                                   "exchange": xchg_ms / args.steps, "stitch": stitch_ms / args.steps,
+                                   "note": "maxima over ranks; exchange includes waiting for the slowest rank",
+                                   "per_rank_step_pass_exchange_stitch_order": per_rank},
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args, ctx, tree, algo, d_msa, d_cons, stride, n_taxa, n_cols, ncpu)
