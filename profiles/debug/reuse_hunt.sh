@@ -1,9 +1,10 @@
 #!/bin/bash
-# correctness (all records of config 4, narrow shapes vs 4x2) and speed of the three ring hand-back variants
+# correctness (all records of config 4, narrow shapes vs 4x2) and speed of ring hand-back variants: libpmfs.so (default
+# mode) against libpmfs_reuse<N>.so builds
 cd /root/repo
 L=$PWD/panman_b200
-for v in "" reuse1 reuse2; do
-  name=${v:-mode3_default}
+for v in "" $*; do
+  name=${v:-default}
   lib=$L/libpmfs${v:+_$v}.so
   echo "===== $name"
   PMFS_LIB=$lib TAG=$name timeout 200 python profiles/debug/count_diff.py 4x1 2x1 1x1 2>&1 | tail -6
@@ -12,4 +13,8 @@ for v in "" reuse1 reuse2; do
 import sys, json
 for l in sys.stdin:
     d = json.loads(l); print('c3', d['algo'], d['columns'], d['ms'])"
+  PMFS_LIB=$lib timeout 100 python profiles/sweep_shapes.py c4 c5 2>&1 | grep auto | python -c "
+import sys, json
+for l in sys.stdin:
+    d = json.loads(l); print(d['config'], d['algo'], d['columns'], d['ms'])"
 done
