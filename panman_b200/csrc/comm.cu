@@ -11,8 +11,14 @@
 //   4. the owner stitches: every source's slice is (node,pos)-ordered and the sources' columns are disjoint and
 //      rank-ordered, so node v's list is the concatenation of its runs in source order -- per-node totals, one prefix sum,
 //      one copy kernel that also turns the records into pmfs_mut.  No sort anywhere.
-// Each GPU only touches its own memory and NCCL's buffers.  NCCL is loaded at run time (dlopen), so single-GPU users of
-// the library do not need it installed.
+// Step 3 has two transports.  NCCL send/recv (PMFS_COMM_TRANSPORT=nccl) moved 250 GB/s between two B200s and less with
+// more peers -- a third of a step at 8 GPUs.  The default for ranks in different processes of one box is therefore
+// PEER COPIES: every rank's inbox is exported once with CUDA IPC, and a source copies each slice straight into its
+// owner's inbox at the place the gathered cut points assign to it (copy engines over NVLink, no SMs, no staging); a tiny
+// NCCL all-reduce after the copies is the stream-ordered barrier that tells every owner its inbox is complete.  NCCL
+// stays the control plane (cut points, barriers, handle exchange).  Inboxes grow collectively (every rank derives every
+// rank's need from the same cut points), so an exported buffer is never freed while a peer has it mapped.
+// NCCL is loaded at run time (dlopen), so single-GPU users of the library do not need it installed.
 #include <cuda_runtime.h>
 #include <dlfcn.h>
 #include <nccl.h>
@@ -188,7 +194,16 @@ struct pmfs_comm {
     long long* h_red = nullptr;  // pinned
     cudaEvent_t ev[3] = {};
     float exchange_ms = 0, stitch_ms = 0;
+    // peer-copy transport
+    bool p2p = false;
+    size_t inbox_cap_all[kMaxRanks] = {};        // every rank's inbox capacity in records (the same on all ranks)
+    unsigned long long* peer_inbox[kMaxRanks] = {};  // IPC mappings of the peers' inboxes / node-offset tables
+    uint32_t* peer_noff_in[kMaxRanks] = {};
+    DevBuf<unsigned long long> d_hand;           // handle exchange: [world][8] words
+    unsigned long long* h_hand = nullptr;        // pinned
 };
+
+static int p2p_setup(pmfs_comm* m);
 
 static int comm_finish_create(pmfs_comm* m) {
     pmfs_ctx* c = m->ctx;
@@ -202,6 +217,90 @@ static int comm_finish_create(pmfs_comm* m) {
     int rc;
     if ((rc = m->d_allcuts.ensure((size_t)kMaxRanks * (kMaxRanks + 1)))) return rc;
     if ((rc = m->d_red.ensure(8))) return rc;
+    return PMFS_OK;
+}
+
+// ---- peer-copy transport: CUDA IPC mappings of the peers' buffers, exchanged through NCCL -----------------------------
+// All ranks gather everybody's handle for one buffer (`mine`, or nothing for ranks not in `mask`) and map the ones in mask.
+static int exchange_handles(pmfs_comm* m, void* mine, uint32_t mask, void** mapped) {
+    pmfs_ctx* c = m->ctx;
+    NcclApi& A = nccl_api();
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    const int W = m->world, me = m->rank;
+    int rc;
+    if ((rc = m->d_hand.ensure((size_t)kMaxRanks * 8 + 8))) return rc;
+    if (!m->h_hand) PMFS_CUDA(cudaMallocHost(&m->h_hand, ((size_t)kMaxRanks * 8 + 8) * sizeof(unsigned long long)));
+    cudaIpcMemHandle_t h = {};
+    if (mine && ((mask >> me) & 1u)) PMFS_CUDA(cudaIpcGetMemHandle(&h, mine));
+    memcpy(m->h_hand + (size_t)kMaxRanks * 8, &h, 64);
+    PMFS_CUDA(cudaMemcpyAsync(m->d_hand.ptr + (size_t)kMaxRanks * 8, m->h_hand + (size_t)kMaxRanks * 8, 64, cudaMemcpyHostToDevice, c->stream));
+    PMFS_NCCL(A.AllGather(m->d_hand.ptr + (size_t)kMaxRanks * 8, m->d_hand.ptr, 8, ncclUint64, m->comm, c->stream));
+    PMFS_CUDA(cudaMemcpyAsync(m->h_hand, m->d_hand.ptr, (size_t)W * 64, cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    for (int r = 0; r < W; r++) {
+        if (r == me || !((mask >> r) & 1u)) continue;
+        cudaIpcMemHandle_t hr;
+        memcpy(&hr, m->h_hand + (size_t)r * 8, 64);
+        void* ptr = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, hr, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            g_error = std::string("pmfs_comm: cudaIpcOpenMemHandle (rank ") + std::to_string(r) + "): " + cudaGetErrorString(e) +
+                      " -- set PMFS_COMM_TRANSPORT=nccl where the GPUs cannot map each other's memory";
+            cudaGetLastError();
+            return PMFS_ERR_CUDA;
+        }
+        mapped[r] = ptr;
+    }
+    return PMFS_OK;
+}
+
+// stream-ordered barrier over the ranks (a one-word all-reduce); host_sync: also wait for it on the host
+static int comm_barrier(pmfs_comm* m, bool host_sync) {
+    pmfs_ctx* c = m->ctx;
+    PMFS_NCCL(nccl_api().AllReduce(m->d_red.ptr, m->d_red.ptr, 1, ncclInt64, ncclSum, m->comm, c->stream));
+    if (host_sync) PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    return PMFS_OK;
+}
+
+static int p2p_setup(pmfs_comm* m) {
+    // the node-offset tables never change size: W x (owned nodes + 1) words, exported once
+    const int W = m->world, me = m->rank;
+    const int32_t n_own = m->parts.bound[me + 1] - m->parts.bound[me];
+    int rc;
+    if ((rc = m->d_noff_in.ensure((size_t)W * ((size_t)n_own + 1)))) return rc;
+    PMFS_CUDA(cudaMemsetAsync(m->d_red.ptr, 0, 8 * sizeof(long long), m->ctx->stream));
+    return exchange_handles(m, m->d_noff_in.ptr, (1u << W) - 1u, (void**)m->peer_noff_in);
+}
+
+// Every rank's inbox must hold what the gathered cut points say it will receive.  Inboxes that have to grow do so
+// collectively: everybody unmaps them, a barrier, the owners reallocate and re-export, everybody maps the new ones.
+static int p2p_grow_inboxes(pmfs_comm* m, const unsigned long long* all) {
+    const int W = m->world, me = m->rank;
+    uint32_t grow = 0;
+    size_t newcap[kMaxRanks] = {};
+    for (int p = 0; p < W; p++) {
+        unsigned long long need = 0;
+        for (int s = 0; s < W; s++) need += all[s * (W + 1) + p + 1] - all[s * (W + 1) + p];
+        if (need > m->inbox_cap_all[p]) {
+            grow |= 1u << p;
+            newcap[p] = (size_t)need + (size_t)need / 4 + 1024;
+        }
+    }
+    if (!grow) return PMFS_OK;
+    for (int p = 0; p < W; p++)
+        if (((grow >> p) & 1u) && p != me && m->peer_inbox[p]) {
+            PMFS_CUDA(cudaIpcCloseMemHandle(m->peer_inbox[p]));
+            m->peer_inbox[p] = nullptr;
+        }
+    int rc = comm_barrier(m, true);  // nobody has the old buffers mapped any more
+    if (rc) return rc;
+    if ((grow >> me) & 1u) {
+        m->d_inbox.release();
+        if ((rc = m->d_inbox.ensure(newcap[me]))) return rc;
+    }
+    if ((rc = exchange_handles(m, m->d_inbox.ptr, grow, (void**)m->peer_inbox))) return rc;
+    for (int p = 0; p < W; p++)
+        if ((grow >> p) & 1u) m->inbox_cap_all[p] = newcap[p];
     return PMFS_OK;
 }
 
@@ -248,6 +347,11 @@ int pmfs_comm_create(pmfs_comm** out, pmfs_ctx* ctx, const void* id128, int rank
         }
     }
     int rc = comm_finish_create(m);
+    if (!rc && world > 1) {
+        const char* tr = getenv("PMFS_COMM_TRANSPORT");
+        m->p2p = !(tr && std::string(tr) == "nccl");
+        if (m->p2p) rc = p2p_setup(m);
+    }
     if (rc) {
         pmfs_comm_destroy(m);
         return rc;
@@ -260,6 +364,12 @@ void pmfs_comm_destroy(pmfs_comm* m) {
     if (!m) return;
     cudaSetDevice(m->ctx->device);
     cudaStreamSynchronize(m->ctx->stream);
+    for (int r = 0; r < kMaxRanks; r++) {
+        if (m->peer_inbox[r]) cudaIpcCloseMemHandle(m->peer_inbox[r]);
+        if (m->peer_noff_in[r]) cudaIpcCloseMemHandle(m->peer_noff_in[r]);
+    }
+    if (m->h_hand) cudaFreeHost(m->h_hand);
+    m->d_hand.release();
     if (m->comm) nccl_api().CommDestroy(m->comm);
     if (m->group && --m->group->refs == 0) delete m->group;  // (destroy the members from one thread)
     m->d_allcuts.release(); m->d_inbox.release(); m->d_noff_in.release(); m->d_total.release(); m->d_start.release();
@@ -414,7 +524,12 @@ int pmfs_comm_run(pmfs_comm* m, int algo, const uint8_t* d_msa, int64_t row_stri
         return PMFS_ERR_ARG;
     }
     const int32_t n_own = m->parts.bound[me + 1] - m->parts.bound[me];
-    if ((rc = m->d_inbox.ensure((size_t)total + (size_t)total / 8 + 16))) return rc;
+    const bool p2p = m->p2p && !G && W > 1;
+    if (p2p) {
+        if ((rc = p2p_grow_inboxes(m, all))) return rc;
+    } else {
+        if ((rc = m->d_inbox.ensure((size_t)total + (size_t)total / 8 + 16))) return rc;
+    }
     if ((rc = m->d_noff_in.ensure((size_t)W * ((size_t)n_own + 1)))) return rc;
     if ((rc = m->d_total.ensure((size_t)n_own + 1))) return rc;
     if ((rc = m->d_start.ensure((size_t)n_own + 1))) return rc;
@@ -422,7 +537,7 @@ int pmfs_comm_run(pmfs_comm* m, int algo, const uint8_t* d_msa, int64_t row_stri
     // 3. slices and node offsets to their owners: one NCCL group; this rank's own slice by a device copy
     const unsigned long long* mine = c->skeys_view;
     const unsigned long long* my_cuts = all + (size_t)me * (W + 1);
-    if (W > 1 && !G) PMFS_NCCL(A.GroupStart());
+    if (W > 1 && !G && !p2p) PMFS_NCCL(A.GroupStart());
     for (int p = 0; p < W; p++) {
         const unsigned long long sc = my_cuts[p + 1] - my_cuts[p];            // what I send to p
         const unsigned long long rcn = all[p * (W + 1) + me + 1] - all[p * (W + 1) + me];  // what p sends to me
@@ -441,12 +556,21 @@ int pmfs_comm_run(pmfs_comm* m, int algo, const uint8_t* d_msa, int64_t row_stri
                                       ((size_t)n_own + 1) * sizeof(uint32_t), cudaMemcpyDefault, c->stream));
             continue;
         }
+        if (p2p) {  // push: my slice for p goes to the place in p's inbox that the cut points give it
+            unsigned long long at = 0;
+            for (int s2 = 0; s2 < me; s2++) at += all[s2 * (W + 1) + p + 1] - all[s2 * (W + 1) + p];
+            if (sc) PMFS_CUDA(cudaMemcpyAsync(m->peer_inbox[p] + at, mine + my_cuts[p], sc * sizeof(unsigned long long), cudaMemcpyDefault, c->stream));
+            PMFS_CUDA(cudaMemcpyAsync(m->peer_noff_in[p] + (size_t)me * ((size_t)own_p + 1), c->d_noff.ptr + m->parts.bound[p],
+                                      ((size_t)own_p + 1) * sizeof(uint32_t), cudaMemcpyDefault, c->stream));
+            continue;
+        }
         if (sc) PMFS_NCCL(A.Send(mine + my_cuts[p], (size_t)sc, ncclUint64, p, m->comm, c->stream));
         if (rcn) PMFS_NCCL(A.Recv(m->d_inbox.ptr + sp.roff[p], (size_t)rcn, ncclUint64, p, m->comm, c->stream));
         PMFS_NCCL(A.Send(c->d_noff.ptr + m->parts.bound[p], (size_t)own_p + 1, ncclUint32, p, m->comm, c->stream));
         PMFS_NCCL(A.Recv(m->d_noff_in.ptr + (size_t)p * (n_own + 1), (size_t)n_own + 1, ncclUint32, p, m->comm, c->stream));
     }
-    if (W > 1 && !G) PMFS_NCCL(A.GroupEnd());
+    if (W > 1 && !G && !p2p) PMFS_NCCL(A.GroupEnd());
+    if (p2p && (rc = comm_barrier(m, false))) return rc;  // everybody's copies into everybody's inbox are complete
     PMFS_CUDA(cudaEventRecord(m->ev[1], c->stream));
     // 4. stitch
     int pos_bits = 1;

@@ -189,32 +189,38 @@ dist.broadcast(idt, 0)
 ctx = api.Context(tree, device=rank)
 comm = api.Comm(ctx, bytes(idt.cpu().numpy().tobytes()), rank, world)
 b, e = shard.column_shards(L, world)[rank]
+nb, ne = comm.node_range()
 for algo in (0, 1):
-    nib = api.pack_nibbles(msa[:, b:e], row_stride=((e - b + 31) // 32) * 16)
-    d_msa, d_cons = torch.from_numpy(nib).cuda(), torch.from_numpy(np.ascontiguousarray(cons[b:e])).cuda()
-    torch.cuda.synchronize()
-    for rep in range(2):
-        ptr, n = comm.run(algo, d_msa.data_ptr(), nib.shape[1], synth.n_rows(tree), e - b, b, L, d_cons.data_ptr(), 0)
-    got = ctx.download(n)
-    want = O.run_port(algo, tree, msa, cons, None, threads=2)
-    nb, ne = comm.node_range()
-    sel = (want["node"] >= nb) & (want["node"] < ne)
-    assert G.same_muts(got, want[sel]), (rank, algo)
+    # a narrow call first, then the full width twice: the inboxes have to grow between calls
+    for lo, hi in ((0, 640), (0, L), (0, L)):
+        bb, ee = shard.column_shards(hi - lo, world)[rank]
+        nib = api.pack_nibbles(msa[:, bb:ee], row_stride=((ee - bb + 31) // 32) * 16)
+        d_msa, d_cons = torch.from_numpy(nib).cuda(), torch.from_numpy(np.ascontiguousarray(cons[bb:ee])).cuda()
+        torch.cuda.synchronize()
+        ptr, n = comm.run(algo, d_msa.data_ptr(), nib.shape[1], synth.n_rows(tree), ee - bb, bb, hi, d_cons.data_ptr(), 0)
+        got = ctx.download(n)
+        want = O.run_port(algo, tree, msa[:, :hi], cons[:hi], None, threads=2)
+        sel = (want["node"] >= nb) & (want["node"] < ne)
+        assert G.same_muts(got, want[sel]), (rank, algo, hi)
 comm.close(); ctx.close()
 dist.barrier(); dist.destroy_process_group()
 print("rank", rank, "ok")
 """
 
 
-def test_gather_over_nccl_two_processes(tmp_path):
-    """The NCCL transport: one process per GPU under torch.distributed.run, the unique id shipped by a torch broadcast."""
+@pytest.mark.parametrize("transport", ["p2p", "nccl"])
+def test_gather_two_processes(tmp_path, transport):
+    """One process per GPU under torch.distributed.run, the NCCL unique id shipped by a torch broadcast; the records
+    travel by peer copies into IPC-mapped inboxes (the default) or by ncclSend / ncclRecv."""
     torch = _torch()
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     script = tmp_path / "worker.py"
     script.write_text(_NCCL_WORKER)
+    env = dict(os.environ, PMFS_COMM_TRANSPORT=transport)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-                        "127.0.0.1", "--master-port", "29731", str(script), ROOT], capture_output=True, text=True, timeout=600)
+                        "127.0.0.1", "--master-port", "29731" if transport == "p2p" else "29732", str(script), ROOT],
+                       capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0 and r.stdout.count("ok") == 2, r.stdout[-3000:] + r.stderr[-3000:]
 
 
