@@ -169,8 +169,8 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 //   3  no fence; the walkers hand an entry back only after its data has ARRIVED in their registers (the hand-back takes a
 //      value that depends on the loaded words), so no read of the old contents can be in flight when the refill is
 //      issued: 0.741 / 19.0 ms
-//   4  no fence; an entry is handed back when the walker asks for its NEXT operand from either ring (or at the end of the
-//      item): the instructions issued in between have consumed its words
+// Tried and removed: handing an entry back only when the walker asks for its NEXT operand, without a fence -- slower, and
+// records still differed (profiles/r2_f_reuse_hunt_mode4.log): consuming the loaded words orders nothing between the proxies.
 #ifndef PMFS_REUSE_MODE
 #define PMFS_REUSE_MODE 2
 #endif
@@ -378,7 +378,6 @@ struct DevEnv {
     uint4* fstk;         // [depth][CFG::NG][4][CFG::TPB]
     uint32_t* bstk;      // [depth][CFG::NG][5][CFG::TPB]
     int sp = 0;
-    uint32_t pend = 0;   // PMFS_REUSE_MODE 4: ring entries read but not handed back yet (bit 0 leaf unit, bit 1 set slot)
     int lane;
     bool prog_staged;
     const uint32_t* gprog;
@@ -419,7 +418,6 @@ struct DevEnv {
 
     // next leaf unit: wait until the TMA copy has landed, read this thread's 16 bytes per group, hand the unit back
     __device__ __forceinline__ void leaf(uint32_t, uint4 (&w)[CFG::NG]) {
-        flush();
         const uint32_t u = n_leaf & ring.leaf_mask, par = (n_leaf >> ring.leaf_log2) & 1u;
         PMFS_WP(2);
         mbar_wait(ring.bars + (kBarLeafFull + u) * 8, par, ring.limit_ns);
@@ -430,19 +428,13 @@ struct DevEnv {
             w[j] = lds128(base + j * (CFG::TPB * 16));
             loaded ^= w[j].x;
         }
-#if PMFS_REUSE_MODE == 4
-        (void)loaded;
-        pend |= 1u;  // handed back when the next unit is asked for (or at the end of the item): its words are used by then
-#else
         const uint32_t zero = after_loads(loaded);
         __syncwarp();
         if (lane == 0) mbar_arrive(ring.bars + (kBarLeafEmpty + u) * 8 + zero);
-#endif
         n_leaf++;
     }
     // next set slot (a set written by an earlier work item): 4 quarters x CFG::NG groups
     __device__ __forceinline__ void load_x(uint32_t, Planes16 (&s)[CFG::NG]) {
-        flush();
         const uint32_t u = n_set & ring.set_mask, par = (n_set >> ring.set_log2) & 1u;
         PMFS_WP(3);
         mbar_wait(ring.bars + (kBarSetFull + u) * 8, par, ring.limit_ns);
@@ -456,41 +448,11 @@ struct DevEnv {
                 s[j].p[4 * i] = v.x; s[j].p[4 * i + 1] = v.y; s[j].p[4 * i + 2] = v.z; s[j].p[4 * i + 3] = v.w;
                 loaded ^= v.x;
             }
-#if PMFS_REUSE_MODE == 4
-        (void)loaded;
-        pend |= 2u;
-#else
         const uint32_t zero = after_loads(loaded);
         __syncwarp();
         if (lane == 0) mbar_arrive(ring.bars + (kBarSetEmpty + u) * 8 + zero);
-#endif
         n_set++;
     }
-    // PMFS_REUSE_MODE 4: hand back the previous entry of a ring (its ld.shared results have been consumed by the
-    // instructions issued since, so no read of it can be in flight any more)
-    __device__ __forceinline__ void release_leaf() {
-#if PMFS_REUSE_MODE == 4
-        if (pend & 1u) {
-            __syncwarp();
-            if (lane == 0) mbar_arrive(ring.bars + (kBarLeafEmpty + ((n_leaf - 1u) & ring.leaf_mask)) * 8);
-            pend &= ~1u;
-        }
-#endif
-    }
-    __device__ __forceinline__ void release_set() {
-#if PMFS_REUSE_MODE == 4
-        if (pend & 2u) {
-            __syncwarp();
-            if (lane == 0) mbar_arrive(ring.bars + (kBarSetEmpty + ((n_set - 1u) & ring.set_mask)) * 8);
-            pend &= ~2u;
-        }
-#endif
-    }
-    __device__ __forceinline__ void flush() {
-        release_leaf();
-        release_set();
-    }
-
     // direct access to the set arrays (sets of this work item itself; Sankoff D1 on the slow path)
     __device__ __forceinline__ int64_t set_index(uint32_t id, int j, int i) const {
         return (int64_t)id * (4 * p.G) + set_tile + i * tile_w + j * CFG::TPB + threadIdx.x;
@@ -903,7 +865,6 @@ __global__ void __launch_bounds__(CFG::Threads) fwd_kernel(const WalkParams p) {
                 fp = forced;
             }
             forward_walk<ALGO, POLY>(env, nullptr, d.plen, fp);
-            env.flush();
         }
         if (d.plen <= kProgWords) staged[slot]++;
         finish_item<CFG>(d.parent >= 0 ? p.ready + (int64_t)d.parent * p.ctas_per_chunk + d.tile : nullptr,
@@ -961,7 +922,6 @@ __global__ void __launch_bounds__(CFG::Threads, bwd_min_ctas<CFG, ALGO>()) bwd_k
                 colmask[j] = env.active[j] ? real_column_mask(env.g[j], p.tile_cols) : 0u;
             }
             err = backward_walk<ALGO>(env, nullptr, d.plen, P, pv, fp, colmask);
-            env.flush();
         }
         if (err) atomicOr(p.err_flag, 1u);
         if (d.plen <= kProgWords) staged[slot]++;

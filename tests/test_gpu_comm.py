@@ -188,7 +188,6 @@ if rank == 0:
 dist.broadcast(idt, 0)
 ctx = api.Context(tree, device=rank)
 comm = api.Comm(ctx, bytes(idt.cpu().numpy().tobytes()), rank, world)
-b, e = shard.column_shards(L, world)[rank]
 nb, ne = comm.node_range()
 for algo in (0, 1):
     # a narrow call first, then the full width twice: the inboxes have to grow between calls
