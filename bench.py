@@ -6,7 +6,7 @@
 Workload (default, every N): BASELINE config 3 -- the 8 000 000-taxon x 30 000-column SARS-CoV-2-shaped alignment
 (random binary tree, 15 999 999 nodes), COLUMN-SHARDED over the N GPUs, strong scaling: the same 30 000 columns whatever
 N.  A step = one full pass of the hot path over all 30 000 columns: bottom-up sets, top-down assignment, mutation
-emission, ordering by (node,pos) and -- for N > 1 -- the gather of the per-node lists by node range with NCCL
+emission, ordering by (node,pos) and -- for N > 1 -- the gather of the per-node lists by node range over NVLink
 (pmfs_comm_run: every rank ends up owning the complete (node,pos)-ordered lists of its node range, in HBM), all inside
 the timed region.  The alignment is resident in HBM when the timed region starts (120 GB on one GPU, 15 GB per GPU on
 eight).  The per-node set arrays of 8 M internal nodes take 0.5 GB per 32 columns, so the columns go through in
@@ -102,7 +102,7 @@ class ClockSampler:
                     reasons.add(name)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "sm_min_mhz": sm[0] if sm else None}
 
 
 def ref_threads(n_nodes, ncpu):
@@ -385,6 +385,15 @@ def main():
         g = torch.zeros((world, 5), device=dev, dtype=torch.float64)
         dist.all_gather_into_tensor(g.view(-1), torch.tensor(mine_ms, device=dev, dtype=torch.float64))
         per_rank = [[round(float(v) / args.steps, 3) for v in row] for row in g.cpu()]
+        # every rank samples its own GPU: median / lowest SM clock and a bit mask of the throttle reasons it saw
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        ck = torch.tensor([clocks["sm_mhz"] or 0, clocks.get("sm_min_mhz") or 0,
+                           sum(1 << i for i, nm in enumerate(names) if nm in clocks["reasons"])], device=dev, dtype=torch.float64)
+        gk = torch.zeros((world, 3), device=dev, dtype=torch.float64)
+        dist.all_gather_into_tensor(gk.view(-1), ck)
+        clocks["per_rank_median_min_reasons"] = [[float(a), float(b), [nm for i, nm in enumerate(names) if int(c) >> i & 1]]
+                                                 for a, b, c in gk.cpu().tolist()]
+        clocks["reasons"] = sorted({nm for row in clocks["per_rank_median_min_reasons"] for nm in row[2]})
     updates_per_step = V * n_cols * (1 if strong else world)
     value = updates_per_step * args.steps / (total_ms * 1e-3)
     plan = ctx.plan_info()
@@ -441,7 +450,7 @@ def main():
                "d2h_bytes_per_step": int(n_e * 12), "steps": e_steps,
                "what": (f"host buffers in, host records out on a {e_cols}-column batch per GPU of the workload "
                         + ("(pmfs_run, pinned buffers)" if comm is None else
-                           "(H2D of the rank's columns, pmfs_comm_run with the NCCL gather, D2H of the rank's node range)")
+                           "(H2D of the rank's columns, pmfs_comm_run with the gather by node range, D2H of the rank's node range)")
                         + "; bytes are per rank"),
                "phases_ms_last_step": {k: ctx.timing()[k] for k in ("h2d_ms", "forward_ms", "backward_ms", "sort_ms", "d2h_ms",
                                                                      "exchange_ms", "stitch_ms")}}
@@ -466,7 +475,7 @@ def main():
                        "l2": "inputs larger than L2 (alignment and set arrays are tens of GB per GPU)" if strong else
                              "inputs larger than L2 (MSA 300 MB + set array 1.2 GB touched per step)",
                        "parallelism": (f"column shards x{world}; per window every rank runs the whole tree over its columns, then the "
-                                       "per-node lists are gathered by node range with NCCL (pmfs_comm_run) inside the timed step"
+                                       f"per-node lists are gathered by node range (pmfs_comm_run, transport: {comm.transport}) inside the timed step"
                                        if comm is not None else
                                        (f"column shards x{world}, no data-path collective (weak scaling)" if world > 1 else "1 GPU")),
                        "windows_per_step": mine["batches"] // args.steps, "columns_per_gpu_and_window": gb * 32,

@@ -226,6 +226,11 @@ int pmfs_comm_create(pmfs_comm** comm, pmfs_ctx* ctx, const void* id128, int ran
 void pmfs_comm_destroy(pmfs_comm* comm);
 int pmfs_comm_node_range(pmfs_comm* comm, int rank, int32_t* node_begin, int32_t* node_end);
 int pmfs_comm_batch_cols(pmfs_comm* comm, int algo, int64_t cols_per_rank, int64_t bytes_per_col, int64_t* batch_cols);
+/* How the records travel between the ranks of this communicator: 0 = ncclSend / ncclRecv, 1 = device-to-device copies
+ * into the owners' inboxes mapped through CUDA IPC (the default where every rank can map every peer; NCCL then only
+ * carries cut points and barriers; PMFS_COMM_TRANSPORT=nccl forces 0), 2 = copies inside one process
+ * (pmfs_comm_create_local).  -1: null communicator. */
+int pmfs_comm_transport(pmfs_comm* comm);
 int pmfs_comm_run(pmfs_comm* comm, int algo, const uint8_t* d_msa_nibbles, int64_t row_stride_bytes, int32_t n_rows,
                   int64_t n_cols, int64_t col_offset, int64_t total_cols, const uint8_t* d_consensus_code,
                   const uint8_t* d_root_forced_code, pmfs_mut** d_out, int64_t* n_out);

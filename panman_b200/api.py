@@ -76,7 +76,7 @@ BATCH_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.
 _lib = None
 
 EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_tile", "pmfs_set_watchdog", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_char_rows", "pmfs_run_codes",
-           "pmfs_result_free", "pmfs_run_device", "pmfs_run_batched", "pmfs_set_batch_cols", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_comm_unique_id", "pmfs_comm_create", "pmfs_comm_create_local", "pmfs_comm_destroy", "pmfs_comm_node_range", "pmfs_comm_batch_cols", "pmfs_comm_run", "pmfs_multi_create", "pmfs_multi_destroy", "pmfs_multi_run", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
+           "pmfs_result_free", "pmfs_run_device", "pmfs_run_batched", "pmfs_set_batch_cols", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_comm_unique_id", "pmfs_comm_create", "pmfs_comm_create_local", "pmfs_comm_destroy", "pmfs_comm_node_range", "pmfs_comm_batch_cols", "pmfs_comm_transport", "pmfs_comm_run", "pmfs_multi_create", "pmfs_multi_destroy", "pmfs_multi_run", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
 
@@ -120,6 +120,7 @@ def lib():
         L.pmfs_comm_destroy.restype = None
         L.pmfs_comm_node_range.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.pmfs_comm_batch_cols.argtypes = [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]
+        L.pmfs_comm_transport.argtypes = [C.c_void_p]
         L.pmfs_comm_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_int64, C.c_int64,
                                     C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
         L.pmfs_multi_create.argtypes = [C.POINTER(C.c_void_p), C.POINTER(_Tree), C.c_int, C.c_void_p]
@@ -399,6 +400,11 @@ class Comm:
         b, e = C.c_int32(), C.c_int32()
         _check(self._L.pmfs_comm_node_range(self._h, self.rank if rank is None else rank, C.byref(b), C.byref(e)))
         return b.value, e.value
+
+    @property
+    def transport(self) -> str:
+        """How records travel between the ranks ("nccl", "peer-copy" through CUDA IPC, "local" inside one process)."""
+        return {0: "nccl", 1: "peer-copy", 2: "local"}.get(self._L.pmfs_comm_transport(self._h), "?")
 
     def batch_cols(self, algo: int, cols_per_rank: int, bytes_per_col: int = 0) -> int:
         out = C.c_int64()

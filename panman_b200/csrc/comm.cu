@@ -231,7 +231,13 @@ static int exchange_handles(pmfs_comm* m, void* mine, uint32_t mask, void** mapp
     if ((rc = m->d_hand.ensure((size_t)kMaxRanks * 8 + 8))) return rc;
     if (!m->h_hand) PMFS_CUDA(cudaMallocHost(&m->h_hand, ((size_t)kMaxRanks * 8 + 8) * sizeof(unsigned long long)));
     cudaIpcMemHandle_t h = {};
-    if (mine && ((mask >> me) & 1u)) PMFS_CUDA(cudaIpcGetMemHandle(&h, mine));
+    bool exported = true;  // a rank that cannot export still takes part in the gather (an all-zero handle maps nowhere)
+    if (mine && ((mask >> me) & 1u) && cudaIpcGetMemHandle(&h, mine) != cudaSuccess) {
+        g_error = "pmfs_comm: cudaIpcGetMemHandle failed -- set PMFS_COMM_TRANSPORT=nccl";
+        cudaGetLastError();
+        memset(&h, 0, sizeof(h));
+        exported = false;
+    }
     memcpy(m->h_hand + (size_t)kMaxRanks * 8, &h, 64);
     PMFS_CUDA(cudaMemcpyAsync(m->d_hand.ptr + (size_t)kMaxRanks * 8, m->h_hand + (size_t)kMaxRanks * 8, 64, cudaMemcpyHostToDevice, c->stream));
     PMFS_NCCL(A.AllGather(m->d_hand.ptr + (size_t)kMaxRanks * 8, m->d_hand.ptr, 8, ncclUint64, m->comm, c->stream));
@@ -251,7 +257,7 @@ static int exchange_handles(pmfs_comm* m, void* mine, uint32_t mask, void** mapp
         }
         mapped[r] = ptr;
     }
-    return PMFS_OK;
+    return exported ? PMFS_OK : PMFS_ERR_CUDA;
 }
 
 // stream-ordered barrier over the ranks (a one-word all-reduce); host_sync: also wait for it on the host
@@ -264,12 +270,28 @@ static int comm_barrier(pmfs_comm* m, bool host_sync) {
 
 static int p2p_setup(pmfs_comm* m) {
     // the node-offset tables never change size: W x (owned nodes + 1) words, exported once
+    pmfs_ctx* c = m->ctx;
     const int W = m->world, me = m->rank;
     const int32_t n_own = m->parts.bound[me + 1] - m->parts.bound[me];
     int rc;
     if ((rc = m->d_noff_in.ensure((size_t)W * ((size_t)n_own + 1)))) return rc;
-    PMFS_CUDA(cudaMemsetAsync(m->d_red.ptr, 0, 8 * sizeof(long long), m->ctx->stream));
-    return exchange_handles(m, m->d_noff_in.ptr, (1u << W) - 1u, (void**)m->peer_noff_in);
+    const int mapped = exchange_handles(m, m->d_noff_in.ptr, (1u << W) - 1u, (void**)m->peer_noff_in);
+    // Either every rank has mapped every peer, or nobody uses the mappings: agree on it (the ranks must not part ways).
+    m->h_red[0] = mapped == PMFS_OK ? 0 : 1;
+    PMFS_CUDA(cudaMemcpyAsync(m->d_red.ptr, m->h_red, sizeof(long long), cudaMemcpyHostToDevice, c->stream));
+    PMFS_NCCL(nccl_api().AllReduce(m->d_red.ptr, m->d_red.ptr, 1, ncclInt64, ncclSum, m->comm, c->stream));
+    PMFS_CUDA(cudaMemcpyAsync(m->h_red, m->d_red.ptr, sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+    PMFS_CUDA(cudaStreamSynchronize(c->stream));
+    if (m->h_red[0] != 0) {  // some rank cannot map a peer (no peer access, separate IPC namespaces): ncclSend / ncclRecv
+        for (int r = 0; r < W; r++)
+            if (r != me && m->peer_noff_in[r]) {
+                cudaIpcCloseMemHandle(m->peer_noff_in[r]);
+                m->peer_noff_in[r] = nullptr;
+            }
+        cudaGetLastError();
+        m->p2p = false;
+    }
+    return PMFS_OK;
 }
 
 // Every rank's inbox must hold what the gathered cut points say it will receive.  Inboxes that have to grow do so
@@ -426,6 +448,11 @@ int pmfs_comm_node_range(pmfs_comm* m, int rank, int32_t* node_begin, int32_t* n
 // Columns per rank and call such that every rank's set arrays fit in what its GPU has free: the minimum over ranks
 // (one small all-reduce), a multiple of 32 column groups where possible.  `bytes_per_col`: device memory the caller will
 // still allocate per column of a call (e.g. n_rows / 2 for a staged alignment window).
+int pmfs_comm_transport(pmfs_comm* m) {
+    if (!m) return -1;
+    return m->group ? 2 : (m->p2p ? 1 : 0);
+}
+
 int pmfs_comm_batch_cols(pmfs_comm* m, int algo, int64_t cols_per_rank, int64_t bytes_per_col, int64_t* batch_cols) {
     if (!m || cols_per_rank <= 0 || !batch_cols || bytes_per_col < 0) {
         g_error = "pmfs_comm_batch_cols: bad argument";
