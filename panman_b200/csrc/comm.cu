@@ -565,7 +565,10 @@ int pmfs_comm_run(pmfs_comm* m, int algo, const uint8_t* d_msa, int64_t row_stri
     const unsigned long long* mine = c->skeys_view;
     const unsigned long long* my_cuts = all + (size_t)me * (W + 1);
     if (W > 1 && !G && !p2p) PMFS_NCCL(A.GroupStart());
-    for (int p = 0; p < W; p++) {
+    for (int k = 0; k < W; k++) {
+        // peers in rotated order: in "phase" k every rank writes to a different owner (rank + k), so no owner's NVLink
+        // ingress has all the ranks' slices queued up on it at once
+        const int p = (me + k) % W;
         const unsigned long long sc = my_cuts[p + 1] - my_cuts[p];            // what I send to p
         const unsigned long long rcn = all[p * (W + 1) + me + 1] - all[p * (W + 1) + me];  // what p sends to me
         const int32_t own_p = m->parts.bound[p + 1] - m->parts.bound[p];

@@ -189,12 +189,29 @@ static const WalkKernelSet* choose_shape(const pmfs_ctx* c, int64_t groups) {
         }
         return walk_kernel_set(1, 1);
     }
-    for (int i = 0; i < n_order; i++) {  // widest shape that pads the column range by at most a tenth
+    // Otherwise: estimated time = (cost of a tile) x (rounds of work items over the CTA slots).  A tile's cost grows
+    // sub-linearly with its width and hardly shrinks when the tile is partly empty (per-op bookkeeping, program and
+    // descriptor traffic do not depend on the fill): cost(tile) = c_shape * (0.7 + 0.3 * fill), c_shape relative to
+    // 1x1 = 1 from the sweeps on the 16 M-node tree (Fitch 1 : 1.72 : 2.94 : 4.4, Sankoff 1 : 1.89 : 2.7 : 4.8 for
+    // 1x1 : 2x1 : 2x2 : 4x2; 4x1 3.2).  With more items than slots (~5 CTAs on each of 148 SMs) the run costs the sum
+    // of its tiles: 112 groups of the 16 M-node tree are one 2x2 tile (2.74) rather than four 1x1 tiles (3.85) -- a
+    // rule on padding alone picked the latter and made the rank with the narrowest column shard the slowest.  With
+    // fewer (a small tree over few columns) the narrowest tile that keeps the item count under the slots wins.
+    auto tile_cost = [](int nw, int ng) { return nw * ng == 8 ? 4.5 : nw * ng == 4 ? (ng == 2 ? 2.85 : 3.2) : nw * ng == 2 ? 1.78 : 1.0; };
+    const double chunks = std::max<double>(1.0, (double)c->plan.n_nodes / 36.0), slots = 740.0;
+    const WalkKernelSet* best = walk_kernel_set(1, 1);
+    double best_cost = 1e300;
+    for (int i = 0; i < n_order; i++) {
         const WalkKernelSet* k = walk_kernel_set(order[i][0], order[i][1]);
-        const int64_t w = k->shape.groups(), padded = (groups + w - 1) / w * w;
-        if (padded * 10 <= groups * 11) return k;
+        const int64_t w = k->shape.groups(), tiles = (groups + w - 1) / w;
+        const double fill = (double)groups / (double)(w * tiles);
+        const double cost = tile_cost(order[i][0], order[i][1]) * (0.7 + 0.3 * fill) * std::max(1.0, chunks * (double)tiles / slots);
+        if (cost < best_cost) {
+            best_cost = cost;
+            best = k;
+        }
     }
-    return walk_kernel_set(1, 1);
+    return best;
 }
 
 extern "C" {

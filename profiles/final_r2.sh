@@ -1,0 +1,35 @@
+#!/bin/bash
+# Round-2 evidence run on one B200: the GPU test suite, smoke, the bench lines, the ncu launch list of the bench command
+# and the `--set full` captures of the walk kernels.  Everything lands under gpurun_out/<tag>/; what is to be judged is
+# copied into profiles/ afterwards (profiles/ncu_extract.py turns the .ncu-rep files into csv + traffic_r2.json).
+# usage: bash profiles/final_r2.sh <tag> [skip-tests]
+tag=${1:-r2l}
+out=gpurun_out/$tag
+mkdir -p $out
+cd "$(dirname "$0")/.."
+nvidia-smi --query-gpu=name,memory.total,clocks.max.sm,power.limit --format=csv > $out/gpu.txt 2>&1
+nproc >> $out/gpu.txt; free -g >> $out/gpu.txt
+
+if [ "$2" != "skip-tests" ]; then
+  timeout 1500 python -m pytest tests -m gpu -x -q --durations=15 > $out/pytest_gpu.log 2>&1; echo "rc=$?" >> $out/pytest_gpu.log
+fi
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 2>&1; echo "rc=$?" >> $out/smoke.log
+
+# the driver's own command lines, with wall time
+( time timeout 900 python bench.py --gpus 1 --steps 20 --warmup 5 ) > $out/bench_c3_fitch.json 2> $out/bench_c3_fitch.err
+( time timeout 900 python bench.py --impl reference --gpus 1 --steps 20 --warmup 5 ) > $out/bench_ref.json 2> $out/bench_ref.err
+timeout 600 python bench.py --algo sankoff --steps 5 --warmup 3 --no-e2e --no-c2 --cpu-cols 16 > $out/bench_c3_sankoff.json 2> $out/bench_c3_sankoff.err
+
+# launch list of the bench command (one pass of ncu, no replay): our kernels only -- the synthetic generator's launches
+# before the timed region would fill the list otherwise
+KERN='regex:fwd_kernel|bwd_kernel|order_cells_kernel|prep_planes_kernel|area_stats_kernel|cells_total_kernel|node_offsets_kernel|node_lower_bound_kernel|DeviceScan'
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name "$KERN" -c 600 --csv \
+  --log-file $out/launches_bench_c3.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --no-c2 > $out/ncu_bench.log 2>&1
+
+# full captures: config 2 (one pass over everything) and a 1 M-taxon tree of config 3's shape (the 8 M-taxon one makes
+# ncu save and restore 60 GB of set arrays around each of its ~40 replays)
+timeout 600 ncu --set full --clock-control none --import-source on -k 'regex:fwd_kernel|bwd_kernel|order_cells_kernel' -c 6 -f \
+  -o $out/ncu_c2_fitch python profiles/prof_cfg.py c2 fitch 0 0 2 > $out/ncu_c2_fitch.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k 'regex:fwd_kernel|bwd_kernel|order_cells_kernel' -c 6 -f \
+  -o $out/ncu_c3_fitch python profiles/prof_cfg.py c3 fitch 2048 1000000 2 > $out/ncu_c3_fitch.log 2>&1
+ls -la $out > $out/listing.txt
