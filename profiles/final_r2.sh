@@ -18,7 +18,6 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $out/smoke.log 
 # the driver's own command lines, with wall time
 ( time timeout 900 python bench.py --gpus 1 --steps 20 --warmup 5 ) > $out/bench_c3_fitch.json 2> $out/bench_c3_fitch.err
 ( time timeout 900 python bench.py --impl reference --gpus 1 --steps 20 --warmup 5 ) > $out/bench_ref.json 2> $out/bench_ref.err
-timeout 600 python bench.py --algo sankoff --steps 5 --warmup 3 --no-e2e --no-c2 --cpu-cols 16 > $out/bench_c3_sankoff.json 2> $out/bench_c3_sankoff.err
 
 # launch list of the bench command (one pass of ncu, no replay): our kernels only -- the synthetic generator's launches
 # before the timed region would fill the list otherwise
@@ -32,4 +31,6 @@ timeout 600 ncu --set full --clock-control none --import-source on -k 'regex:fwd
   -o $out/ncu_c2_fitch python profiles/prof_cfg.py c2 fitch 0 0 2 > $out/ncu_c2_fitch.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k 'regex:fwd_kernel|bwd_kernel|order_cells_kernel' -c 6 -f \
   -o $out/ncu_c3_fitch python profiles/prof_cfg.py c3 fitch 2048 1000000 2 > $out/ncu_c3_fitch.log 2>&1
+# Sankoff on the same workload (the reference's 8 M-taxon run is --low-mem-mode, i.e. Sankoff)
+timeout 600 python bench.py --algo sankoff --steps 4 --warmup 3 --no-e2e --no-c2 --cpu-cols 16 > $out/bench_c3_sankoff.json 2> $out/bench_c3_sankoff.err
 ls -la $out > $out/listing.txt
