@@ -99,6 +99,15 @@ int pmfs_set_tuning(pmfs_ctx* ctx, int32_t chunk_nodes, int64_t tile_cols);
  * reference. */
 int pmfs_set_tile(pmfs_ctx* ctx, int32_t walking_warps, int32_t groups_per_thread);
 
+/* Polytomies: a node with MORE than `min_arity` children (default 128; 0 = never) is split -- its children are dealt
+ * out, `part_children` at a time (default and maximum 63; 0 = default), to work items of their own that fold them side
+ * by side into partial results (Fitch: the AND and the OR of the children's sets, the two things src/fitchSankoff.cpp:39-55
+ * needs of them; Sankoff: bit-sliced counts of the children whose set holds each state, :372-403), which the node then
+ * combines; the same items walk their children top-down.  Without it a node with thousands of children -- common in
+ * outbreak trees -- is one serial stretch per column tile.  The next run re-plans.  Results never depend on it.  No
+ * counterpart in the reference. */
+int pmfs_set_poly_split(pmfs_ctx* ctx, int32_t min_arity, int32_t part_children);
+
 /* Every wait inside the walk kernels gives up after `seconds` (default 10; 0 = never) and the run fails with
  * PMFS_ERR_CUDA and a message naming the watchdog: a bookkeeping bug must not hang a GPU, but a debugger, a sanitizer
  * or a time-sliced GPU can make legitimate waits long.  A tripped watchdog leaves the CUDA context unusable, like any
@@ -301,6 +310,8 @@ typedef struct {
     int64_t program_words;
     int64_t edges_leaf;     /* parent->leaf edges */
     int64_t edges_internal; /* parent->internal edges */
+    int32_t n_parts;        /* part chunks of split polytomies (counted in n_chunks) */
+    int32_t n_set_rows;     /* rows of the set arrays: n_internal + the parts' partial results */
 } pmfs_plan_info;
 int pmfs_get_plan_info(pmfs_ctx* ctx, pmfs_plan_info* info);
 

@@ -52,7 +52,7 @@ class _PlanInfo(C.Structure):
     _fields_ = [("n_nodes", C.c_int32), ("n_internal", C.c_int32), ("n_leaves", C.c_int32), ("n_chunks", C.c_int32),
                 ("n_fwd_levels", C.c_int32), ("n_bwd_levels", C.c_int32), ("fwd_stack_depth", C.c_int32),
                 ("bwd_stack_depth", C.c_int32), ("max_arity", C.c_int32), ("program_words", C.c_int64),
-                ("edges_leaf", C.c_int64), ("edges_internal", C.c_int64)]
+                ("edges_leaf", C.c_int64), ("edges_internal", C.c_int64), ("n_parts", C.c_int32), ("n_set_rows", C.c_int32)]
 
 
 class _Synth(C.Structure):
@@ -75,7 +75,7 @@ BATCH_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.
 
 _lib = None
 
-EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_tile", "pmfs_set_watchdog", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_char_rows", "pmfs_run_codes",
+EXPORTS = ["pmfs_last_error", "pmfs_version", "pmfs_create", "pmfs_destroy", "pmfs_set_tuning", "pmfs_set_tile", "pmfs_set_poly_split", "pmfs_set_watchdog", "pmfs_set_stream", "pmfs_run", "pmfs_run_chars", "pmfs_run_char_rows", "pmfs_run_codes",
            "pmfs_result_free", "pmfs_run_device", "pmfs_run_batched", "pmfs_set_batch_cols", "pmfs_run_fitch_static", "pmfs_set_shard", "pmfs_get_parts", "pmfs_sort_records", "pmfs_comm_unique_id", "pmfs_comm_create", "pmfs_comm_create_local", "pmfs_comm_destroy", "pmfs_comm_node_range", "pmfs_comm_batch_cols", "pmfs_comm_transport", "pmfs_comm_run", "pmfs_multi_create", "pmfs_multi_destroy", "pmfs_multi_run", "pmfs_pack_last", "pmfs_download", "pmfs_get_timing", "pmfs_get_plan_info",
            "pmfs_synth_msa"]
 
@@ -96,6 +96,7 @@ def lib():
         L.pmfs_destroy.restype = None
         L.pmfs_set_tuning.argtypes = [C.c_void_p, C.c_int32, C.c_int64]
         L.pmfs_set_tile.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+        L.pmfs_set_poly_split.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
         L.pmfs_set_watchdog.argtypes = [C.c_void_p, C.c_double]
         L.pmfs_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.pmfs_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
@@ -203,6 +204,10 @@ class Context:
     def set_tile(self, walking_warps: int = 0, groups_per_thread: int = 0):
         """Column-tile shape of the work items (pmfs_set_tile); 0 = automatic."""
         _check(self._L.pmfs_set_tile(self._h, walking_warps, groups_per_thread))
+
+    def set_poly_split(self, min_arity: int = 128, part_children: int = 0):
+        """Split nodes with more than `min_arity` children into parts of `part_children` (pmfs_set_poly_split); 0 = never / default."""
+        _check(self._L.pmfs_set_poly_split(self._h, min_arity, part_children))
 
     def set_watchdog(self, seconds: float):
         _check(self._L.pmfs_set_watchdog(self._h, seconds))

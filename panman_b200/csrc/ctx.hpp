@@ -75,6 +75,7 @@ struct pmfs_ctx {
     bool chunk_nodes_auto = false;  // the plan in use was made for an automatic (not a caller-given) chunk size
     std::vector<int32_t> parent, child_off, child_idx, leaf_row;  // kept for re-planning and synth
     int32_t tune_chunk_nodes = 0;
+    int32_t tune_split_arity = 128, tune_part_children = 63;  // split polytomies (PlanOptions)
     int64_t tune_tile_cols = 0;
     int tune_nw = 0, tune_ng = 0;          // pmfs_set_tile: forced tile shape (0 = automatic)
     const WalkKernelSet* ks = nullptr;     // tile shape of the current run

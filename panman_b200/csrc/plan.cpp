@@ -12,7 +12,9 @@ inline uint32_t op(uint32_t code, uint32_t arg) { return code | (arg << kOpBits)
 
 }  // namespace
 
-std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
+std::string build_plan(const pmfs_tree& t, const PlanOptions& opt, Plan& P) {
+    int32_t chunk_nodes = opt.chunk_nodes;
+    const int32_t PCH = std::min(std::max(opt.part_children, 1), kPartChildren);  // children per part of a split polytomy
     const int32_t V = t.n_nodes;
     if (V < 2) return "tree needs at least a root and one child";
     if (!t.parent || !t.child_off || !t.child_idx || !t.leaf_row) return "null tree array";
@@ -97,6 +99,19 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
         if (!any_new || rem[0] < 32 || thr <= 8) break;
         thr = std::max<int64_t>(8, thr / 8);
     }
+    // ---- split polytomies.  A node with more than split_arity children would be one serial stretch of one work item per
+    // column tile (0.4 us per leaf child for Fitch, 2 us for Sankoff's counters): its children are dealt out, PCH
+    // at a time in child-list order, to PART chunks that fold them into partial results side by side; the node's own
+    // chunk only combines those.  Every internal child of such a node roots a chunk of its own, so that a part's
+    // operands are leaves and finished sets only.
+    std::vector<uint8_t> split(V, 0);
+    if (opt.split_arity > 0)
+        for (int32_t v = 0; v < V; v++)
+            if (t.child_off[v + 1] - t.child_off[v] > opt.split_arity) {
+                split[v] = 1;
+                for (int32_t k = t.child_off[v]; k < t.child_off[v + 1]; k++)
+                    if (P.int_id[t.child_idx[k]] >= 0) cut[t.child_idx[k]] = 1;
+            }
     // ---- walk-stack depth.  Every stack level costs shared memory per CTA (16 KB bottom-up, 5 KB top-down) and with it
     // resident CTAs per SM, which is what the latency-bound walks live on; so a chunk may nest at most kMaxWalkStack
     // saved states.  Bottom-up a binary node with two in-chunk internal children saves the first one's set while it
@@ -148,8 +163,10 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
     std::fill(rem.begin(), rem.end(), 1);
     for (int32_t v = V - 1; v >= 1; v--) rem[t.parent[v]] += cut[v] ? 1 : rem[v];
     cut[0] = 1;
-    std::vector<int32_t> chunk_of_root(V, -1);
-    for (int32_t v = 0; v < V; v++)
+    // chunk ids follow the pre-order node ids (a split node's own chunk, then its parts, then everything below): a chunk's
+    // parent always has a smaller id
+    std::vector<int32_t> chunk_of_root(V, -1), part_first(V, -1);
+    for (int32_t v = 0; v < V; v++) {
         if (cut[v]) {
             chunk_of_root[v] = (int32_t)P.chunks.size();
             Chunk c;
@@ -157,17 +174,47 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
             c.root_int = P.int_id[v];
             P.chunks.push_back(c);
         }
+        if (split[v]) {
+            part_first[v] = (int32_t)P.chunks.size();
+            const int32_t k = t.child_off[v + 1] - t.child_off[v];
+            for (int32_t p = 0; p * PCH < k; p++) {
+                Chunk c;
+                c.root_node = v;
+                c.root_int = P.int_id[v];
+                c.part_row = P.n_internal + (P.n_parts++) * opt.part_rows;
+                P.chunks.push_back(c);
+            }
+        }
+    }
+    P.part_rows = P.n_parts ? opt.part_rows : 0;
+    P.n_set_rows = P.n_internal + P.n_parts * P.part_rows;
+    if ((int64_t)P.n_internal + (int64_t)P.n_parts * opt.part_rows >= (int64_t)kOperandIdMask) return "too many set rows";
     const int32_t NC = (int32_t)P.chunks.size();
     // owner[v]: chunk whose program visits v as a member (a chunk root is a member of its own chunk)
     std::vector<int32_t> owner(V, 0);
     for (int32_t v = 1; v < V; v++) owner[v] = cut[v] ? chunk_of_root[v] : owner[t.parent[v]];
+    // the chunk that hands a chunk its parent state (and consumes its result): the owner of the root's parent -- or,
+    // below a split node, the part that holds the root; a part hangs off the split node's own chunk
+    std::vector<int32_t> child_pos;
+    if (P.n_parts) {
+        child_pos.assign(V, 0);
+        for (int32_t v = 0; v < V; v++)
+            if (split[v])
+                for (int32_t k = t.child_off[v]; k < t.child_off[v + 1]; k++) child_pos[t.child_idx[k]] = k - t.child_off[v];
+    }
     for (int32_t c = 1; c < NC; c++) {
-        P.chunks[c].parent = owner[t.parent[P.chunks[c].root_node]];
-        P.chunks[P.chunks[c].parent].n_child++;
-        P.chunks[c].depth = P.chunks[P.chunks[c].parent].depth + 1;
+        Chunk& ch = P.chunks[c];
+        if (ch.part_row >= 0) {
+            ch.parent = owner[ch.root_node];
+        } else {
+            const int32_t tp = t.parent[ch.root_node];
+            ch.parent = split[tp] ? part_first[tp] + child_pos[ch.root_node] / PCH : owner[tp];
+        }
+        P.chunks[ch.parent].n_child++;
+        ch.depth = P.chunks[ch.parent].depth + 1;
     }
     for (int32_t c = NC - 1; c >= 1; c--) {
-        Chunk& par = P.chunks[owner[t.parent[P.chunks[c].root_node]]];
+        Chunk& par = P.chunks[P.chunks[c].parent];
         par.height = std::max(par.height, P.chunks[c].height + 1);
     }
 
@@ -202,10 +249,30 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
         ch.fwd_stream_off = (int64_t)P.fwd_stream.size();
         int32_t depth = 0;
         st.clear();
-        st.push_back({ch.root_node, -1, false, {}});
+        if (ch.part_row >= 0) {  // a part: one fold over its share of the split node's children
+            const int32_t v = ch.root_node, p = ci - part_first[v];
+            const int32_t b = t.child_off[v] + p * PCH, e = std::min(t.child_off[v + 1], b + PCH);
+            P.fwd_prog.push_back(op(F_PART, (uint32_t)ch.part_row));
+            P.fwd_prog.push_back((uint32_t)(e - b));
+            for (int32_t k = b; k < e; k++) push_operand(t.child_idx[k]);
+        } else {
+            st.push_back({ch.root_node, -1, false, {}});
+        }
         while (!st.empty()) {
             Frame& f = st.back();
             const int32_t v = f.v, b = t.child_off[v], e = t.child_off[v + 1];
+            if (split[v]) {  // the parts have folded the children: combine their partial results
+                const int32_t m = (e - b + PCH - 1) / PCH;
+                P.fwd_prog.push_back(op(F_COMBINE, (uint32_t)P.int_id[v]));
+                P.fwd_prog.push_back((uint32_t)m);
+                for (int32_t p = 0; p < m; p++) {
+                    const uint32_t row = (uint32_t)P.chunks[part_first[v] + p].part_row;
+                    P.fwd_prog.push_back(kOperandSet | kOperandExt | row);
+                    for (int32_t r = 0; r < P.part_rows; r++) P.fwd_stream.push_back(kStreamSet | (row + (uint32_t)r));
+                }
+                st.pop_back();
+                continue;
+            }
             if (f.i < 0) {
                 for (int32_t k = b; k < e; k++)
                     if (is_sub(t.child_idx[k])) f.subs.push_back(t.child_idx[k]);
@@ -270,10 +337,36 @@ std::string build_plan(const pmfs_tree& t, int32_t chunk_nodes, Plan& P) {
         ch.bwd_stream_off = (int64_t)P.bwd_stream.size();
         int32_t depth = 0;
         st.clear();
-        st.push_back({ch.root_node, -1, false, {}});
+        if (ch.part_row >= 0) {  // a part starts from the split node's state: its share of the children, child chunks first
+            const int32_t v = ch.root_node, p = ci - part_first[v];
+            const int32_t b = t.child_off[v] + p * PCH, e = std::min(t.child_off[v + 1], b + PCH);
+            for (int32_t k = b; k < e; k++)
+                if (P.int_id[t.child_idx[k]] >= 0) P.bwd_prog.push_back(op(B_XCHILD, (uint32_t)chunk_of_root[t.child_idx[k]]));
+            for (int32_t k = b; k < e; k++) {
+                const int32_t c = t.child_idx[k];
+                if (P.int_id[c] < 0 && t.leaf_row[c] >= 0) {
+                    P.bwd_prog.push_back(op(B_LEAF, (uint32_t)t.leaf_row[c]));
+                    P.bwd_stream.push_back((uint32_t)t.leaf_row[c]);
+                }
+            }
+            if (ch.bwd_off == (int64_t)P.bwd_prog.size()) {  // (absent leaves only: nothing to do, but no item is empty)
+                P.bwd_prog.push_back(op(B_PUSHP, 0));
+                P.bwd_prog.push_back(op(B_POPP, 0));
+                P.bwd_stack_depth = std::max(P.bwd_stack_depth, 1);
+            }
+        } else {
+            st.push_back({ch.root_node, -1, false, {}});
+        }
         while (!st.empty()) {
             Frame& f = st.back();
             const int32_t v = f.v, b = t.child_off[v], e = t.child_off[v + 1];
+            if (split[v]) {  // resolve the node, hand its state to the parts
+                P.bwd_prog.push_back(v == 0 ? op(B_ENTER_ROOT, 0) : op(B_ENTER, (uint32_t)P.int_id[v]));
+                P.bwd_stream.push_back(kStreamSet | (uint32_t)P.int_id[v]);
+                for (int32_t p = 0; p * PCH < e - b; p++) P.bwd_prog.push_back(op(B_XCHILD, (uint32_t)(part_first[v] + p)));
+                st.pop_back();
+                continue;
+            }
             if (f.i < 0) {
                 P.bwd_prog.push_back(v == 0 ? op(B_ENTER_ROOT, 0) : op(B_ENTER, (uint32_t)P.int_id[v]));
                 P.bwd_stream.push_back(kStreamSet | (uint32_t)P.int_id[v]);

@@ -37,6 +37,13 @@ enum FwdOp : uint32_t {
     F_JOIN_IMM = 2,   // arg = v, 1 operand:   T = join(T, operand);          store set[v]
     F_JOIN_IMM2 = 3,  // arg = v, 2 operands:  T = join(operand0, operand1);  store set[v]
     F_POLY = 4,       // arg = v, next word = k, then k operands: any arity (1, >=3); children re-read from memory
+    // Split polytomies (arity > PlanOptions::split_arity): the children are dealt out to PART chunks, each of which
+    // folds its share into a partial result -- Fitch: the pair (AND, OR) of the children's sets; Sankoff: the bit-sliced
+    // counters h[s] of its children (row b holds bit b of all 16 counters) -- kept in `part_rows` extra rows of the set
+    // array; the node itself only combines the partial results.  fitchSankoff.cpp:39-55 (AND else OR over all
+    // children) and :372-403 (sums over all children) are associative in exactly these partial forms.
+    F_PART = 5,       // arg = first extra row, next word = k, then k operands: fold and store the partial result
+    F_COMBINE = 6,    // arg = v, next word = m, then m operands (first extra row of each part): combine; store set[v]
 };
 
 enum BwdOp : uint32_t {
@@ -59,11 +66,26 @@ struct Chunk {
     int32_t n_child = 0;   // chunks rooted directly below this one
     int32_t height = 0;  // 0 = no child chunks
     int32_t depth = 0;   // 0 = contains the tree root
+    int32_t part_row = -1;  // >= 0: a PART chunk (some children of root_node, a split polytomy); its first extra set row
+};
+
+// Children per part of a split polytomy (both algorithms), and the set rows a part's partial result takes: Fitch the
+// pair (AND, OR); Sankoff 6 counter bits (at most 63 children are counted per part).
+constexpr int32_t kPartChildren = 63;  // the most a part may hold (6-bit counters)
+constexpr int32_t kPartRowsFitch = 2, kPartRowsSankoff = 6;
+
+struct PlanOptions {
+    int32_t chunk_nodes = 64;  // cut a subtree off as its own chunk once it holds at least this many not-yet-cut nodes
+    int32_t split_arity = 128; // nodes with MORE children than this are split into parts (0: never)
+    int32_t part_children = kPartChildren;  // children per part, 1..kPartChildren (smaller values are for tests)
+    int32_t part_rows = kPartRowsFitch;  // rows per partial result: the programs of split nodes depend on the algorithm
 };
 
 struct Plan {
     int32_t n_nodes = 0, n_internal = 0, n_leaves = 0, n_rows_used = 0;
     int32_t max_arity = 0;
+    int32_t n_parts = 0, part_rows = 0;  // part chunks of split polytomies; rows per partial result (0 without parts)
+    int32_t n_set_rows = 0;              // rows of the set arrays: n_internal + n_parts * part_rows
     std::vector<int32_t> int_id;       // [V] internal id or -1
     std::vector<int32_t> int_to_node;  // [I]
     std::vector<int32_t> row_to_node;  // [max row + 1] node id or -1
@@ -81,6 +103,11 @@ struct Plan {
 // many not-yet-cut nodes.  The part of the tree left above those chunks is cut again with a threshold 8x smaller, and so
 // on: chunks shrink towards the root, where few chunks run side by side and the length of one chunk's walk is the
 // critical path.  Returns an empty string or an error description.
-std::string build_plan(const pmfs_tree& tree, int32_t chunk_nodes, Plan& plan);
+std::string build_plan(const pmfs_tree& tree, const PlanOptions& opt, Plan& plan);
+inline std::string build_plan(const pmfs_tree& tree, int32_t chunk_nodes, Plan& plan) {
+    PlanOptions o;
+    o.chunk_nodes = chunk_nodes;
+    return build_plan(tree, o, plan);
+}
 
 }  // namespace pmfs

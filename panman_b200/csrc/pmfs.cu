@@ -130,14 +130,21 @@ static int upload_plan(pmfs_ctx* c) {
     return PMFS_OK;
 }
 
-static int replan(pmfs_ctx* c, int32_t chunk_nodes) {
+static int replan(pmfs_ctx* c, int32_t chunk_nodes, int algo = -1) {
     pmfs_tree t;
     t.n_nodes = (int32_t)c->parent.size();
     t.parent = c->parent.data();
     t.child_off = c->child_off.data();
     t.child_idx = c->child_idx.data();
     t.leaf_row = c->leaf_row.data();
-    std::string err = build_plan(t, chunk_nodes, c->plan);
+    // (the programs of split polytomies depend on the algorithm: a part's partial result is 2 set rows for Fitch, 6 for
+    // Sankoff; without an algorithm given, the one the current plan was built for)
+    PlanOptions po;
+    po.chunk_nodes = chunk_nodes;
+    po.split_arity = c->tune_split_arity;
+    po.part_children = c->tune_part_children;
+    po.part_rows = algo == PMFS_SANKOFF || (algo < 0 && c->plan.part_rows == kPartRowsSankoff) ? kPartRowsSankoff : kPartRowsFitch;
+    std::string err = build_plan(t, po, c->plan);
     if (!err.empty()) {
         g_error = "pmfs_create: " + err;
         return PMFS_ERR_ARG;
@@ -337,6 +344,18 @@ int pmfs_set_tuning(pmfs_ctx* c, int32_t chunk_nodes, int64_t tile_cols) {
     return PMFS_OK;
 }
 
+int pmfs_set_poly_split(pmfs_ctx* c, int32_t min_arity, int32_t part_children) {
+    if (!c || min_arity < 0 || part_children < 0 || part_children > kPartChildren) {
+        g_error = "pmfs_set_poly_split: bad argument (at most 63 children per part)";
+        return PMFS_ERR_ARG;
+    }
+    c->tune_split_arity = min_arity;
+    c->tune_part_children = part_children ? part_children : kPartChildren;
+    c->chunk_nodes_used = 0;  // the next run builds its plan anew
+    c->chunk_nodes_auto = false;
+    return PMFS_OK;
+}
+
 int pmfs_set_tile(pmfs_ctx* c, int32_t walking_warps, int32_t groups_per_thread) {
     if (!c || (walking_warps != 0 && !walk_kernel_set(walking_warps, groups_per_thread))) {
         g_error = "pmfs_set_tile: shapes are (walking warps x column groups per thread) 4x2, 2x2, 4x1, 1x2, 2x1, 1x1; 0 = automatic";
@@ -373,6 +392,7 @@ int pmfs_get_plan_info(pmfs_ctx* c, pmfs_plan_info* info) {
     info->max_arity = P.max_arity;
     info->program_words = (int64_t)P.fwd_prog.size() + (int64_t)P.bwd_prog.size();
     info->edges_leaf = P.edges_leaf; info->edges_internal = P.edges_internal;
+    info->n_parts = P.n_parts; info->n_set_rows = P.n_set_rows;
     return PMFS_OK;
 }
 
@@ -512,7 +532,7 @@ static int launch_order_cells(pmfs_ctx* c, size_t region_cap, int64_t cells, int
 // group -- emitted, ordered, received, converted -- come to a fifth of its set arrays).
 namespace pmfs {
 int mem_limited_groups(pmfs_ctx* c, int algo, int64_t G_all, size_t extra_per_group, int64_t* groups) {
-    const int64_t I = c->plan.n_internal;
+    const int64_t I = c->plan.n_set_rows;
     const int64_t per_group = I * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64 + (int64_t)extra_per_group;
     const size_t need = (size_t)I * 4 * (size_t)G_all;
     *groups = G_all;
@@ -549,6 +569,10 @@ int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
     PMFS_CUDA(cudaSetDevice(c->device));
     c->too_many_records = false;
     const auto host_t0 = std::chrono::steady_clock::now();
+    if (c->plan.n_parts > 0 && c->chunk_nodes_used > 0 && c->plan.part_rows != (algo == PMFS_SANKOFF ? kPartRowsSankoff : kPartRowsFitch)) {
+        int rc = replan(c, c->chunk_nodes_used, algo);  // split polytomies: the other algorithm's partial results
+        if (rc) return rc;
+    }
     const Plan* P = &c->plan;
     const int64_t G_all = (n_cols + 31) / 32;
     const int64_t I = P->n_internal;
@@ -556,7 +580,7 @@ int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
     // column tile so that the set arrays fit in HBM
     int64_t tile_groups = G_all;
     auto set_elems = [&](int64_t groups) {  // uint4 elements of one tile-major set array for `groups` column groups
-        return (size_t)I * 4 * (size_t)groups;
+        return (size_t)c->plan.n_set_rows * 4 * (size_t)groups;  // (n_set_rows does not depend on the chunk size)
     };
     {
         int rc = mem_limited_groups(c, algo, G_all, 0, &tile_groups);
@@ -576,7 +600,7 @@ int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
     const bool close_enough = c->tune_chunk_nodes == 0 && c->chunk_nodes_used > 0 && want_chunk <= 4 * (int64_t)c->chunk_nodes_used &&
                               c->chunk_nodes_used <= 4 * (int64_t)want_chunk && c->chunk_nodes_auto;
     if (want_chunk != c->chunk_nodes_used && !close_enough) {
-        int rc = replan(c, want_chunk);
+        int rc = replan(c, want_chunk, algo);
         if (rc) return rc;
         c->chunk_nodes_auto = c->tune_chunk_nodes == 0;
         P = &c->plan;
@@ -1288,7 +1312,7 @@ static int run_host_streaming(pmfs_ctx* c, int algo, const uint8_t* msa, int64_t
         size_t free_b = 0, total_b = 0;
         PMFS_CUDA(cudaMemGetInfo(&free_b, &total_b));
         free_b += c->d_S.cap * sizeof(uint4) + c->d_D.cap * sizeof(uint4);
-        const int64_t per_group = (int64_t)c->plan.n_internal * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64 + 2 * 16 * (int64_t)n_rows;
+        const int64_t per_group = (int64_t)c->plan.n_set_rows * 64 * (algo == PMFS_SANKOFF ? 2 : 1) + 64 + 2 * 16 * (int64_t)n_rows;
         int64_t gmax = std::max<int64_t>(1, (int64_t)(free_b * 0.65) / per_group);
         const int64_t max_regions = std::max<int64_t>(1, ((int64_t)1 << 30) / std::max(1, c->plan.n_nodes));
         gmax = std::min(gmax, max_regions * 32);
@@ -1725,9 +1749,15 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
     if (rc) return rc;
     PMFS_CUDA(cudaSetDevice(c->device));
 
+    if (c->plan.n_parts > 0 && c->plan.part_rows != kPartRowsFitch) {
+        // (re-planning would allocate; this entry point never does)
+        g_error = "pmfs_run_fitch_static: the tree has split polytomies and the context's plan was last built for Sankoff: "
+                  "run pmfs_run_device(PMFS_FITCH) once first";
+        return PMFS_ERR_ARG;
+    }
     const Plan& P = c->plan;
     const int64_t G = (n_cols + 31) / 32;
-    const size_t I = (size_t)P.n_internal, NC = P.chunks.size(), cap = (size_t)out_capacity;
+    const size_t I = (size_t)P.n_set_rows, NC = P.chunks.size(), cap = (size_t)out_capacity;
     int node_bits = 1, pos_bits = 1;
     while ((1ll << node_bits) < P.n_nodes) node_bits++;
     while ((1ll << pos_bits) < n_cols) pos_bits++;

@@ -195,29 +195,56 @@ PMFS_HD void finish_node(Env& env, uint32_t id, Planes16 (&S)[Env::kGroups], con
 }
 
 // Any-arity join (unary nodes and polytomies); children are re-read from memory, so nothing is live across them.
-template <int ALGO, class Env>
-PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, Planes16 (&S)[Env::kGroups],
+// mode 0 (F_POLY): all k children of node `id`.  mode 1 (F_PART): fold the k children of one part of a split polytomy and
+// store the partial result in the extra set rows from `id` on; S / D1 are not touched.  mode 2 (F_COMBINE): the k
+// operands are parts (first extra row of each); combine their partial results into S / D1 of the node.
+// (The mode is a template parameter: with a run-time mode the three variants' live ranges add up -- +30 registers on the
+// kernels of every tree with a polytomy, split or not.)
+template <int ALGO, int MODE, class Env>
+PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, uint32_t id, Planes16 (&S)[Env::kGroups],
                        Planes16 (&D1)[Env::kGroups]) {
     constexpr int NG = Env::kGroups;
+    constexpr int mode = MODE;
     if (ALGO == kAlgoFitch) {
+        // S = AND of the children's sets if that is not empty, else their OR (fitchSankoff.cpp:39-55): (AND, OR) of a
+        // subset of the children is all a part has to hand on
         Planes16 A[NG], O[NG];
 #pragma unroll
         for (int j = 0; j < NG; j++)
 #pragma unroll
             for (int i = 0; i < 16; i++) { A[j].p[i] = ~0u; O[j].p[i] = 0; }
         for (uint32_t c = 0; c < k; c++) {
+            const uint32_t o = env.word(prog, pc + (int32_t)c);
             Planes16 B[NG];
-            load_operand(env, env.word(prog, pc + (int32_t)c), B);
+            if (mode == 2) {
+                env.load_x(o & kOperandIdMask, B);
+#pragma unroll
+                for (int j = 0; j < NG; j++)
+#pragma unroll
+                    for (int i = 0; i < 16; i++) A[j].p[i] &= B[j].p[i];
+                env.load_x((o & kOperandIdMask) + 1, B);
+#pragma unroll
+                for (int j = 0; j < NG; j++)
+#pragma unroll
+                    for (int i = 0; i < 16; i++) O[j].p[i] |= B[j].p[i];
+                continue;
+            }
+            load_operand(env, o, B);
 #pragma unroll
             for (int j = 0; j < NG; j++)
 #pragma unroll
                 for (int i = 0; i < 16; i++) { A[j].p[i] &= B[j].p[i]; O[j].p[i] |= B[j].p[i]; }
         }
+        if constexpr (MODE == 1) {
+            env.store_s(id, A);
+            env.store_s(id + 1, O);
+        } else {
 #pragma unroll
-        for (int j = 0; j < NG; j++) {
-            const uint32_t any = or16(A[j]);
+            for (int j = 0; j < NG; j++) {
+                const uint32_t any = or16(A[j]);
 #pragma unroll
-            for (int i = 0; i < 16; i++) S[j].p[i] = A[j].p[i] | (O[j].p[i] & ~any);
+                for (int i = 0; i < 16; i++) S[j].p[i] = A[j].p[i] | (O[j].p[i] & ~any);
+            }
         }
     } else {
         // h[s] = number of valid children whose S contains s, as bit-sliced counters; S = argmax h, D1 = {h = max-1}.
@@ -226,8 +253,12 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
         // increments cannot overflow it.  Arity <= 3 needs nothing else.  For larger arities the register counters are
         // added into full-width counters in a per-thread array after every third child (only the states some column of
         // the warp has seen; the carry ripples two bits on average), and read back from there at the end.
+        // A part counts at most 63 children: its 16 counters are 6 bits, handed on as 6 set rows (row b = bit b of all
+        // counters); the combine adds the parts' counters up.  (A valid child is in at least one counter, so "some child
+        // is valid" is handed on with them.)
+        const uint32_t k_all = mode == 2 ? k * 63u : k;  // what the counters must be able to hold
         int nb = 1;
-        while ((k >> nb) != 0) nb++;
+        while ((k_all >> nb) != 0) nb++;
         const int nhi = nb > 2 ? nb - 2 : 0;
         uint32_t lo0[NG][16], lo1[NG][16], full[NG][16][kPolyBits];
         uint32_t any_valid[NG];
@@ -244,6 +275,40 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
         }
         uint32_t pending = 0;  // children counted in lo0/lo1 since the last flush
         for (uint32_t c = 0; c < k; c++) {
+            if (mode == 2) {  // full += the 6-bit counters of part c (ripple-carry over the bit rows, then into the high bits)
+                const uint32_t row = env.word(prog, pc + (int32_t)c) & kOperandIdMask;
+                uint32_t cy[NG][16];
+#pragma unroll
+                for (int j = 0; j < NG; j++)
+#pragma unroll
+                    for (int s_ = 0; s_ < 16; s_++) cy[j][s_] = 0;
+                for (int b_ = 0; b_ < kPartRowsSankoff; b_++) {
+                    Planes16 R[NG];
+                    env.load_x(row + (uint32_t)b_, R);
+#pragma unroll
+                    for (int j = 0; j < NG; j++) {
+                        any_valid[j] |= or16(R[j]);
+#pragma unroll
+                        for (int s_ = 0; s_ < 16; s_++) {
+                            const uint32_t x = full[j][s_][b_], r = R[j].p[s_], c_in = cy[j][s_];
+                            full[j][s_][b_] = x ^ r ^ c_in;
+                            cy[j][s_] = (x & r) | (c_in & (x ^ r));
+                        }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < NG; j++)
+#pragma unroll
+                    for (int s_ = 0; s_ < 16; s_++) {
+                        uint32_t carry = cy[j][s_];
+                        for (int b_ = kPartRowsSankoff; b_ < nb && env.any(carry != 0); b_++) {
+                            const uint32_t x = full[j][s_][b_];
+                            full[j][s_][b_] = x ^ carry;
+                            carry &= x;
+                        }
+                    }
+                continue;
+            }
             Planes16 B[NG];
             load_operand(env, env.word(prog, pc + (int32_t)c), B);
 #pragma unroll
@@ -289,6 +354,17 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
                     lo1[j][s_] = full[j][s_][1];
                 }
         }
+        if constexpr (MODE == 1) {
+            for (int b_ = 0; b_ < kPartRowsSankoff; b_++) {
+                Planes16 R[NG];
+#pragma unroll
+                for (int j = 0; j < NG; j++)
+#pragma unroll
+                    for (int s_ = 0; s_ < 16; s_++)
+                        R[j].p[s_] = b_ == 0 ? lo0[j][s_] : b_ == 1 ? lo1[j][s_] : (b_ < nb ? full[j][s_][b_] : 0u);
+                env.store_s(id + (uint32_t)b_, R);
+            }
+        } else {
 #pragma unroll
         for (int j = 0; j < NG; j++) {
             // argmax over the 16 counters, most significant bit first: `cand` keeps the states that can still be maximal,
@@ -346,6 +422,7 @@ PMFS_HD void poly_join(Env& env, const uint32_t* prog, int32_t pc, uint32_t k, P
                 D1[j].p[s_] = eq[s_];
             }
         }
+        }
     }
 }
 
@@ -377,12 +454,15 @@ PMFS_HD void forward_walk(Env& env, const uint32_t* prog, int32_t len, const Cod
             continue;
         }
         Planes16 D1[NG];
-        if (code == F_POLY) {
+        if (code >= F_POLY) {  // F_POLY, F_PART, F_COMBINE
             if (POLY) {
                 const uint32_t k = take();
-                poly_join<ALGO>(env, prog, pc, k, T, D1);
+                if (code == F_POLY) poly_join<ALGO, 0>(env, prog, pc, k, id, T, D1);
+                else if (code == F_PART) poly_join<ALGO, 1>(env, prog, pc, k, id, T, D1);
+                else poly_join<ALGO, 2>(env, prog, pc, k, id, T, D1);
                 pc += (int32_t)k;
                 q0 = env.word(prog, pc); q1 = env.word(prog, pc + 1); q2 = env.word(prog, pc + 2);
+                if (code == F_PART) continue;  // a part stores its partial result itself; no node is finished here
             }
         } else {
             Planes16 A[NG];

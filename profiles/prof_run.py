@@ -1,5 +1,6 @@
 """Minimal driver for ncu captures: BASELINE config 2, `--steps` device-resident passes, nothing else.
-usage: python profiles/prof_run.py [fitch|sankoff] [steps] [taxa] [columns] [fraction of internal edges collapsed]"""
+usage: python profiles/prof_run.py [fitch|sankoff] [steps] [taxa] [columns] [fraction of internal edges collapsed] [split arity]
+(split arity: nodes with more children are split into parts, pmfs_set_poly_split; default 128, 0 = never)"""
 import os
 import sys
 
@@ -16,6 +17,8 @@ tree = trees.random_binary_tree(N)
 if len(sys.argv) > 5 and float(sys.argv[5]) > 0:
     tree = trees.collapse_edges(tree, float(sys.argv[5]))  # polytomies
 ctx = api.Context(tree)
+if len(sys.argv) > 6:
+    ctx.set_poly_split(int(sys.argv[6]), 0)
 stride = ((L + 31) // 32) * 16
 d_msa = torch.zeros((N, stride), dtype=torch.uint8, device="cuda")
 d_cons = torch.zeros(L, dtype=torch.uint8, device="cuda")

@@ -130,7 +130,7 @@ int run(const Plan& P, const uint8_t* msa, int64_t row_stride, int64_t n_cols, c
         std::vector<Rec>& out) {
     const int64_t G = (n_cols + 31) / 32;
     const int64_t H = (G + NG - 1) / NG;  // "threads": thread t walks groups t, t+H, ...
-    std::vector<uint32_t> S((size_t)P.n_internal * 16 * G), D(ALGO ? S.size() : 0);
+    std::vector<uint32_t> S((size_t)P.n_set_rows * 16 * G), D(ALGO ? (size_t)P.n_internal * 16 * G : 0);
     std::vector<uint32_t> xcode(P.chunks.size() * 4 * G), xv(P.chunks.size() * G);
     uint32_t err = 0;
     for (int pass = 0; pass < 2; pass++) {
@@ -190,9 +190,17 @@ int run(const Plan& P, const uint8_t* msa, int64_t row_stride, int64_t n_cols, c
 
 }  // namespace
 
+static int32_t g_split_arity = 128, g_part_children = kPartChildren;
+
 extern "C" {
 
 void emul_free(void* p) { free(p); }
+
+// plan options for split polytomies (PlanOptions::split_arity / part_children) of the following emul_run calls
+void emul_set_split(int32_t split_arity, int32_t part_children) {
+    g_split_arity = split_arity;
+    g_part_children = part_children;
+}
 
 // same contract as pmfs_run (include/pmfs.h) + an explicit chunk size and the number of column groups per thread; plan_out (optional) receives
 // {n_chunks, fwd_levels, bwd_levels, fwd_stack, bwd_stack, program_words}
@@ -202,7 +210,12 @@ int emul_run(int algo, int32_t n_nodes, const int32_t* parent, const int32_t* ch
              int64_t* plan_out) {
     pmfs_tree t = {n_nodes, parent, child_off, child_idx, leaf_row};
     Plan P;
-    std::string e = build_plan(t, chunk_nodes, P);
+    PlanOptions po;
+    po.chunk_nodes = chunk_nodes;
+    po.split_arity = g_split_arity;
+    po.part_children = g_part_children;
+    po.part_rows = algo == 0 ? kPartRowsFitch : kPartRowsSankoff;
+    std::string e = build_plan(t, po, P);
     if (!e.empty()) return PMFS_ERR_ARG;
     if (plan_out) {
         plan_out[0] = (int64_t)P.chunks.size();
@@ -211,6 +224,7 @@ int emul_run(int algo, int32_t n_nodes, const int32_t* parent, const int32_t* ch
         plan_out[3] = P.fwd_stack_depth;
         plan_out[4] = P.bwd_stack_depth;
         plan_out[5] = (int64_t)(P.fwd_prog.size() + P.bwd_prog.size());
+        plan_out[6] = P.n_parts;
     }
     // rows padded to whole groups, as the library does on upload
     const int64_t dstride = ((n_cols + 31) / 32) * 16;

@@ -237,6 +237,54 @@ def test_large_polytomies():
                 assert G.same_muts(got, want), (tree.n_nodes, algo, forced is not None)
 
 
+def test_split_polytomies():
+    """Nodes with more children than a threshold are dealt out to part work items (partial AND / OR pairs for Fitch,
+    partial bit-sliced counters for Sankoff) that the node combines; the parts also walk their children top-down.
+    Small thresholds and parts so that small trees have many parts, nested splits, split roots, absent leaves; both
+    algorithms alternate on ONE context (the programs of split nodes differ per algorithm: the context re-plans)."""
+    rng = np.random.default_rng(31)
+    for trial in range(10):
+        tree = synth.random_tree(int(rng.integers(100, 1500)), rng, max_arity=int(rng.integers(4, 40)),
+                                 absent_frac=0.0 if trial % 3 else 0.1)
+        L = int(rng.integers(40, 900))
+        msa = synth.simulate_msa(tree, L, rng, p_sub=0.1, p_del=0.05, p_ins=0.2, p_n=0.05, p_amb=0.05)
+        cons = synth.consensus_first_nongap(msa)
+        forced = msa[int(rng.integers(0, msa.shape[0]))] if trial % 2 else None
+        nib = api.pack_nibbles(msa)
+        want = [O.run_port(algo, tree, msa, cons, forced, threads=4) for algo in (0, 1)]
+        with api.Context(tree) as ctx:
+            ctx.set_poly_split(int(rng.choice([2, 5, 9])), int(rng.choice([1, 3, 7, 63])))
+            if trial % 4 == 1:
+                ctx.set_tile(1, 1)
+            elif trial % 4 == 2:
+                ctx.set_tile(4, 2)
+            for algo in (0, 1, 1, 0):
+                got = ctx.run(algo, nib, L, cons, forced)
+                assert ctx.plan_info()["n_parts"] > 0
+                assert G.same_muts(got, want[algo]), (trial, algo)
+    # production thresholds (more than 128 children, 63 per part): a star of 20 000 and an outbreak-like tree -- a
+    # backbone whose nodes each carry hundreds of identical-looking leaves
+    star = synth._flatten(list(range(20000)))
+    backbone, nxt = [], 0
+    node = list(range(nxt, nxt + 400)); nxt += 400
+    for _ in range(12):
+        k = int(rng.integers(100, 700))
+        node = [node] + list(range(nxt, nxt + k)); nxt += k
+    for tree in (star, synth._flatten(node)):
+        L = 2048 + 37
+        msa = synth.simulate_msa(tree, L, rng, p_sub=0.02, p_del=0.01, p_ins=0.02, p_n=0.01, p_amb=0.01)
+        cons = synth.consensus_first_nongap(msa)
+        nib = api.pack_nibbles(msa)
+        with api.Context(tree) as ctx, api.Context(tree) as whole:
+            whole.set_poly_split(0, 0)  # never split: the any-arity join walks all children in one work item
+            for algo in (0, 1):
+                got = ctx.run(algo, nib, L, cons)
+                assert ctx.plan_info()["n_parts"] >= 100
+                assert G.same_muts(got, O.run_port(algo, tree, msa, cons, None, threads=8)), (tree.n_nodes, algo)
+                ref = whole.run(algo, nib, L, cons)
+                assert whole.plan_info()["n_parts"] == 0 and G.same_muts(got, ref)
+
+
 def test_record_buffer_grows_and_passes_are_redone():
     """Far more mutations than the first call's record buffer is sized for (random codes in every cell: most cells
     mutate): the overflow is detected on the device, the buffer grows, the passes run again -- same records."""

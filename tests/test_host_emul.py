@@ -26,6 +26,7 @@ def emul():
                         "-I/usr/local/cuda/include", "-o", SO] + srcs, check=True)
     lib = C.CDLL(SO)
     lib.emul_free.argtypes = [C.c_void_p]
+    lib.emul_set_split.argtypes = [C.c_int32, C.c_int32]
     return lib
 
 
@@ -36,7 +37,7 @@ def run_emul(lib, algo, tree, msa_codes, cons, forced, chunk_nodes, want_plan=Fa
     cons = np.ascontiguousarray(cons, np.uint8)
     frc = None if forced is None else np.ascontiguousarray(forced, np.uint8)
     out, n = C.c_void_p(), C.c_int64()
-    plan = (C.c_int64 * 6)()
+    plan = (C.c_int64 * 8)()
     rc = lib.emul_run(C.c_int(algo), C.c_int32(tree.n_nodes), *[C.c_void_p(a.ctypes.data) for a in arrs],
                       C.c_void_p(nib.ctypes.data), C.c_int64(nib.shape[1]), C.c_int64(n_cols), C.c_void_p(cons.ctypes.data),
                       None if frc is None else C.c_void_p(frc.ctypes.data), C.c_int32(chunk_nodes), C.c_int32(groups), C.byref(out), C.byref(n), plan)
@@ -154,3 +155,44 @@ def test_emul_large_polytomies(emul):
                 for chunk in (24, 1 << 30):
                     got = run_emul(emul, algo, tree, msa, cons, frc, chunk)
                     assert G.same_muts(got, want), (tree.n_nodes, algo, chunk)
+
+
+def test_emul_split_polytomies(emul):
+    """Nodes with more children than the threshold are dealt out to part chunks (partial AND / OR pairs, partial
+    counters) that the node's own chunk combines; the parts also walk their children top-down.  Small thresholds and
+    parts here so that small trees have many parts, mixed leaf / absent / internal children, split roots and nested splits."""
+    rng = np.random.default_rng(23)
+    try:
+        for trial in range(36):
+            arity = int(rng.integers(3, 40))
+            tree = synth.random_tree(int(rng.integers(5, 400)), rng, max_arity=arity, absent_frac=0.0 if trial % 3 else 0.15)
+            L = int(rng.integers(1, 100))
+            msa = synth.simulate_msa(tree, L, rng, p_sub=0.1, p_del=0.05, p_ins=0.2, p_n=0.05, p_amb=0.05)
+            cons = synth.consensus_first_nongap(msa)
+            forced = msa[int(rng.integers(0, msa.shape[0]))] if trial % 2 else None
+            chunk = int(rng.choice([2, 8, 32, 1 << 30]))
+            split, part = int(rng.choice([2, 3, 5, 9])), int(rng.choice([1, 2, 3, 7, 63]))
+            emul.emul_set_split(split, part)
+            n_parts = 0
+            for algo in (0, 1):
+                want = O.run_port(algo, tree, msa, cons, forced, threads=2)
+                got, plan = run_emul(emul, algo, tree, msa, cons, forced, chunk, want_plan=True, groups=1 + trial % 2)
+                assert G.same_muts(got, want), (trial, algo, chunk, split, part, plan)
+                n_parts = plan[6]
+            arities = np.diff(tree.child_off)
+            assert (n_parts > 0) == bool((arities > split).any())
+        # a star and a star of stars with the production thresholds (more than 128 children, 63 per part)
+        emul.emul_set_split(128, 63)
+        for shape in ("star", "nested"):
+            if shape == "star":
+                tree = synth._flatten(list(range(700)))
+            else:
+                tree = synth._flatten([list(range(i * 150, (i + 1) * 150)) for i in range(4)] + list(range(600, 900)))
+            msa = synth.simulate_msa(tree, 70, rng, p_sub=0.05, p_del=0.02, p_ins=0.05, p_n=0.02, p_amb=0.02)
+            cons = synth.consensus_first_nongap(msa)
+            for algo in (0, 1):
+                got, plan = run_emul(emul, algo, tree, msa, cons, None, 64, want_plan=True)
+                assert plan[6] == (12 if shape == "star" else 4 * 3 + 5), plan
+                assert G.same_muts(got, O.run_port(algo, tree, msa, cons, None)), (shape, algo)
+    finally:
+        emul.emul_set_split(128, 63)
