@@ -428,10 +428,14 @@ def main():
             h_out = torch.empty(0, dtype=torch.uint8, pin_memory=True)
             e_total = e_cols * world  # every rank brings e_cols columns: one window of the job
 
+            ev_h = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
             def e_step():
                 nonlocal h_out
+                ev_h[0].record()
                 dd_msa.copy_(h_msa, non_blocking=True)
                 dd_cons.copy_(h_cons, non_blocking=True)
+                ev_h[1].record()
                 _, n = comm.run(algo, dd_msa.data_ptr(), e_groups * 16, n_taxa, e_cols, rank * e_cols, e_total, dd_cons.data_ptr())
                 if h_out.numel() < n * 12:
                     h_out = torch.empty(int(n * 12 * 1.25) + 1024, dtype=torch.uint8, pin_memory=True)
@@ -454,6 +458,15 @@ def main():
                         + "; bytes are per rank"),
                "phases_ms_last_step": {k: ctx.timing()[k] for k in ("h2d_ms", "forward_ms", "backward_ms", "sort_ms", "d2h_ms",
                                                                      "exchange_ms", "stitch_ms")}}
+        if comm is not None:
+            # what the host side delivers with all ranks uploading at once (they share the host's memory and PCIe
+            # root complexes): this, not the GPUs, bounds the end-to-end figure at N > 1
+            torch.cuda.synchronize()
+            gbs = torch.tensor([h_msa.numel() / (ev_h[0].elapsed_time(ev_h[1]) * 1e-3) / 1e9], device=dev, dtype=torch.float64)
+            allg = torch.zeros(world, device=dev, dtype=torch.float64)
+            dist.all_gather_into_tensor(allg, gbs)
+            e2e["h2d_gbs_per_rank_last_step"] = [round(float(x), 1) for x in allg.cpu()]
+            e2e["h2d_gbs_all_ranks"] = round(float(allg.sum()), 1)
         del h_msa
         if world > 1 and not strong:
             ctx.set_shard(0, 0, None)
