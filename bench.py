@@ -47,7 +47,7 @@ def ncu_traffic(workload, algo):
     with the commit and tile shape it was taken at; None when there is no capture for this workload."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic_r2.json")))
-        return t[workload][algo]
+        return t[{"c3": "c3_8m_taxa_2048col_batch"}.get(workload, workload)][algo]
     except Exception:
         return None
 
@@ -313,7 +313,15 @@ def main():
         elif comm is not None:
             gb = max(1, (comm.batch_cols(algo, share * 32) + 31) // 32)
         else:
-            gb = min(share, 64)  # one GPU: 2 048 columns per batch leave room for the record buffers next to 120 GB of nibbles
+            # one GPU: the widest power-of-two batch whose set arrays (0.5 GB per column group on the 8 M-taxon tree, twice
+            # that for Sankoff) take at most 0.62 of what the resident alignment leaves free -- the record buffers need
+            # the rest.  Config 3: 64 groups (2 048 columns) for Fitch, 32 for Sankoff.
+            free_b = torch.cuda.mem_get_info(dev)[0]
+            per_group = (V // 2) * 64 * (2 if args.algo == "sankoff" else 1)
+            gb = 128
+            while gb > 1 and gb * per_group > 0.62 * free_b:
+                gb //= 2
+            gb = min(share, gb)
         n_win = (share + gb - 1) // gb
 
     def window(w):

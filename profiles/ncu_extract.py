@@ -25,7 +25,7 @@ METRICS = ["launch__grid_size", "launch__block_size", "launch__registers_per_thr
            "smsp__average_warps_issue_stalled_sleeping_per_issue_active.ratio"]
 tag = sys.argv[1]
 traffic = {}
-commit = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True, cwd=HERE).stdout.strip()
+commit = os.environ.get("CAPTURE_COMMIT") or subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True, cwd=HERE).stdout.strip()
 for arg in sys.argv[2:]:
     wa, rep = arg.split("=")
     workload, algo = wa.split(":")
@@ -44,7 +44,7 @@ for arg in sys.argv[2:]:
         x = float(r[i])
         u = units[i].lower()
         return x * {"gbyte": 1e9, "mbyte": 1e6, "kbyte": 1e3, "byte": 1}.get(u, 1)
-    ks, total = [], 0.0
+    ks, per_kernel = [], {}
     for r in data:
         name = r[hdr.index("Kernel Name")].split("(")[0]
         k = {"kernel": name, "dram_read_bytes": val(r, "dram__bytes_read.sum"), "dram_write_bytes": val(r, "dram__bytes_write.sum"),
@@ -55,7 +55,9 @@ for arg in sys.argv[2:]:
              "warps_active_pct": float(r[hdr.index("sm__warps_active.avg.pct_of_peak_sustained_active")])}
         ks.append(k)
         if "fwd_kernel" in name or "bwd_kernel" in name:
-            total += k["dram_read_bytes"] + k["dram_write_bytes"]
+            per_kernel.setdefault(name, []).append(k["dram_read_bytes"] + k["dram_write_bytes"])
+    # one step launches each walk kernel once: average over the captured launches of each (a capture may hold several steps)
+    total = sum(sum(v) / len(v) for v in per_kernel.values())
     traffic.setdefault(workload, {})[algo] = {"kernels": ks, "traffic_bytes_per_step": total,
                                               "source": f"ncu --set full --clock-control none, {os.path.basename(rep)}, capture {tag} at commit {commit}"}
 out_path = os.path.join(HERE, "traffic_" + tag.split("_")[0] + ".json")
