@@ -517,7 +517,7 @@ def main():
                                    "per_rank_step_pass_exchange_stitch_order": per_rank},
         }
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(args, ctx, tree, algo, d_msa, d_cons, stride, n_taxa, n_cols, ncpu)
+            line["cpu_baseline"] = cpu_baseline(args, ctx, tree, algo, d_msa, d_cons, stride, n_taxa, min(n_cols, gb * 32), ncpu)
         if world == 1 and strong and not args.no_c2:
             line["c2_single_gpu"] = c2_leg(args, algo, hbm_peak)
         print(json.dumps(line))
