@@ -411,6 +411,32 @@ def main():
     records_per_step = int(float(rec_all[0]) / args.steps)
     mine = dict(totals)
 
+    # ---- N > 1, untimed: the gathered result of a narrow window against the same columns run unsharded on this GPU,
+    # restricted to the rank's node range -- record for record (every rank generates all the window's columns itself)
+    gather_ok = None
+    if comm is not None:
+        try:
+            from panman_b200 import shard
+            vc = 128
+            tot = vc * world
+            v_msa = torch.zeros((n_taxa, tot // 2), dtype=torch.uint8, device=dev)
+            v_cons = torch.zeros(tot, dtype=torch.uint8, device=dev)
+            ctx.synth_msa(spec, 0, tot, v_msa.data_ptr(), tot // 2, v_cons.data_ptr())
+            torch.cuda.synchronize()
+            ptr, n = comm.run(algo, v_msa.data_ptr() + rank * (vc // 2), tot // 2, n_taxa, vc, rank * vc, tot, v_cons.data_ptr() + rank * vc)
+            got = shard.records_as_tensor(ptr, n, dev).clone()
+            ptr2, n2 = ctx.run_device(algo, v_msa.data_ptr(), tot // 2, n_taxa, tot, v_cons.data_ptr())
+            whole = shard.records_as_tensor(ptr2, n2, dev)
+            nb_, ne_ = comm.node_range()
+            sel = (whole[:, 0] >= nb_) & (whole[:, 0] < ne_)
+            ok = torch.tensor([1 if (n > 0 and torch.equal(got, whole[sel])) else 0], device=dev, dtype=torch.int32)
+            del v_msa, got, whole
+        except Exception as e:  # (the check must not cost the measurement its line)
+            ok = torch.tensor([0], device=dev, dtype=torch.int32)
+            print(f"rank {rank}: gather check failed to run: {e}", file=sys.stderr)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        gather_ok = bool(int(ok[0]))
+
     # ---- end to end through host buffers, on a column batch of the workload
     e2e = None
     if not args.no_e2e:
@@ -511,6 +537,7 @@ def main():
                          "frac_contract": per_gpu_updates * b / pass_s / 1e9 / hbm_peak, "bytes_per_update_contract": b,
                          "frac_whole_step": design / step_s / 1e9 / hbm_peak},
             "e2e": e2e, "gpu_launches": int(mine["launches"]), "clocks": clocks,
+            "gather_bit_exact_vs_unsharded": gather_ok,
             "phases_ms_per_step": {"forward+backward": pass_ms / args.steps, "ordering": sort_ms / args.steps,
                                    "exchange": xchg_ms / args.steps, "stitch": stitch_ms / args.steps,
                                    "note": "maxima over ranks; exchange includes waiting for the slowest rank",
