@@ -94,9 +94,10 @@ int pmfs_set_tuning(pmfs_ctx* ctx, int32_t chunk_nodes, int64_t tile_cols);
 
 /* Column-tile shape of the walk kernels' work items: `walking_warps` x 32 threads, each walking `groups_per_thread`
  * groups of 32 columns.  Built shapes: 4x2 (256 groups per item), 2x2 and 4x1 (128), 1x2 and 2x1 (64), 1x1 (32).
- * 0 = automatic: the widest shape that does not idle lanes on the column range, the narrowest one on ladder-like trees
- * (there the column tiles are the only independent work).  Results never depend on it.  No counterpart in the
- * reference. */
+ * 0 = automatic: the shape with the smallest estimated time for the tree and the column range (a tile's cost grows
+ * sub-linearly with its width and hardly shrinks when it is partly empty), the narrowest one that still fills the GPU
+ * on ladder-like trees (there the column tiles are the only independent work), one group per thread on trees with
+ * polytomies.  Results never depend on it.  No counterpart in the reference. */
 int pmfs_set_tile(pmfs_ctx* ctx, int32_t walking_warps, int32_t groups_per_thread);
 
 /* Polytomies: a node with MORE than `min_arity` children (default 128; 0 = never) is split -- its children are dealt

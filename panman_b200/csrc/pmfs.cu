@@ -172,7 +172,9 @@ static int32_t auto_chunk_nodes(int32_t n_nodes, int64_t groups, int tile_groups
 // parallelism -- on a ladder the column tiles are the only independent work, so the narrowest tile gives the most
 // chains --, and (2) narrow column ranges (column shards of a wide tree, memory-limited column batches), where a wide
 // tile would idle most of its lanes.  PMFS_TILE_SHAPE=NWxNG (environment) and pmfs_set_tile override the choice.
-static const WalkKernelSet* choose_shape(const pmfs_ctx* c, int64_t groups) {
+// max_tile_groups > 0: the set arrays only fit that many column groups per pass, and a pass is a whole number of tiles --
+// shapes wider than that are out (rounding the pass up to one tile would allocate more than what fits).
+static const WalkKernelSet* choose_shape(const pmfs_ctx* c, int64_t groups, int64_t max_tile_groups = 0) {
     if (c->tune_nw > 0)
         if (const WalkKernelSet* s = walk_kernel_set(c->tune_nw, c->tune_ng)) return s;
     if (const char* e = getenv("PMFS_TILE_SHAPE")) {
@@ -192,6 +194,7 @@ static const WalkKernelSet* choose_shape(const pmfs_ctx* c, int64_t groups) {
     if ((int64_t)c->tree_height * 4 > I) {  // ladder-like: tiles are the parallelism
         for (int i = 0; i < n_order; i++) {
             const WalkKernelSet* k = walk_kernel_set(order[i][0], order[i][1]);
+            if (max_tile_groups > 0 && k->shape.groups() > max_tile_groups && k->shape.groups() > 32) continue;
             if ((groups + k->shape.groups() - 1) / k->shape.groups() >= 2 * 148) return k;
         }
         return walk_kernel_set(1, 1);
@@ -211,6 +214,7 @@ static const WalkKernelSet* choose_shape(const pmfs_ctx* c, int64_t groups) {
     for (int i = 0; i < n_order; i++) {
         const WalkKernelSet* k = walk_kernel_set(order[i][0], order[i][1]);
         const int64_t w = k->shape.groups(), tiles = (groups + w - 1) / w;
+        if (max_tile_groups > 0 && w > max_tile_groups && w > 32) continue;
         const double fill = (double)groups / (double)(w * tiles);
         const double cost = tile_cost(order[i][0], order[i][1]) * (0.7 + 0.3 * fill) * std::max(1.0, chunks * (double)tiles / slots);
         if (cost < best_cost) {
@@ -588,7 +592,7 @@ int run_device_impl(pmfs_ctx* c, int algo, const uint8_t* d_msa, int64_t row_str
     }
     if (c->tune_tile_cols > 0) tile_groups = std::min<int64_t>(tile_groups, (c->tune_tile_cols + 31) / 32);
     tile_groups = std::min(tile_groups, G_all);
-    c->ks = choose_shape(c, tile_groups);
+    c->ks = choose_shape(c, tile_groups, tile_groups < G_all ? tile_groups : 0);
     const int TG = c->ks->shape.groups();  // column groups per work item
     if (tile_groups < G_all) tile_groups = std::max<int64_t>(TG, tile_groups / TG * TG);
     tile_groups = std::min(tile_groups, G_all);
