@@ -274,11 +274,13 @@ int pmfs_download(pmfs_ctx* ctx, pmfs_mut* host_out, int64_t n);
  *   inputs   device pointers as for pmfs_run_device (all columns are processed in one pass, no tiling)
  *   outputs  d_out: caller's device buffer of out_capacity records, filled sorted by (node,pos); *n_out: record count
  * Limits: the call is rejected with PMFS_ERR_ARG and an explanatory pmfs_last_error() when the pieces carved out of
- * the array, each rounded up to 256 bytes -- with G = ceil(n_cols/32): the set array n_internal*G*64, the chunk parent
+ * the array, each rounded up to 256 bytes -- with G = ceil(n_cols/32): the set array n_set_rows*G*64 (n_set_rows = n_internal, plus 2 rows per part of a split polytomy,
+ * pmfs_get_plan_info), the chunk parent
  * states n_chunks*G*20, two bit-sliced code arrays G*16 each, two record buffers out_capacity*8 each, the radix sort's
  * workspace (about 1/16 of a record buffer) and the walk kernels' counters (64 + 2*n_chunks*tiles)*4 -- exceed 32 MiB,
  * and when more than out_capacity records are produced (*n_out then holds the number needed).  A context in
- * column-shard mode is refused with PMFS_ERR_STATE.  The call returns after the context's stream has been
+ * column-shard mode is refused with PMFS_ERR_STATE, and so is one whose tree has split polytomies and whose plan was
+ * last built for Sankoff (re-planning would allocate: run pmfs_run_device(PMFS_FITCH) once first).  The call returns after the context's stream has been
  * synchronised; pmfs_download and pmfs_pack_last do not apply to its result (it is in the caller's buffer).
  * The first call on a device looks up the array's address on that device; make that first call before any CUDA stream
  * capture begins.  All calls share the array: it keeps the previous call's contents (the call clears the two words

@@ -1757,7 +1757,7 @@ extern "C" int pmfs_run_fitch_static(pmfs_ctx* c, const uint8_t* d_msa, int64_t 
         // (re-planning would allocate; this entry point never does)
         g_error = "pmfs_run_fitch_static: the tree has split polytomies and the context's plan was last built for Sankoff: "
                   "run pmfs_run_device(PMFS_FITCH) once first";
-        return PMFS_ERR_ARG;
+        return PMFS_ERR_STATE;
     }
     const Plan& P = c->plan;
     const int64_t G = (n_cols + 31) / 32;

@@ -86,3 +86,31 @@ def test_static_scratch_entry_point_rejects_what_does_not_fit():
         with pytest.raises(api.PmfsError) as e:
             ctx.run_fitch_static(d_msa.data_ptr(), d_msa.shape[1], 50, 640, d_cons.data_ptr(), 0, d_out.data_ptr(), 16)
         assert e.value.status == -1 and e.value.n_out > 16
+
+
+def test_static_scratch_entry_point_on_a_split_polytomy():
+    """A tree with a split polytomy (more than 128 children): the static entry point runs the part / combine programs
+    out of its fixed array; and it refuses -- instead of re-planning, which would allocate -- when the context's plan was
+    last built for Sankoff, whose partial results have another layout."""
+    import torch
+
+    tree = synth._flatten([list(range(200)), list(range(200, 230))])
+    L = 700
+    rng = np.random.default_rng(3)
+    msa = synth.simulate_msa(tree, L, rng, p_sub=0.05, p_del=0.01, p_ins=0.02, p_n=0.01, p_amb=0.01)
+    cons = synth.consensus_first_nongap(msa)
+    d_msa, d_cons = _device_inputs(torch, msa, cons)
+    stride, cap = d_msa.shape[1], 200000
+    d_out = torch.zeros(cap * 12, dtype=torch.uint8, device="cuda")
+    want = O.run_port(api.FITCH, tree, msa, cons, None, threads=2)
+    with api.Context(tree) as ctx:
+        n = ctx.run_fitch_static(d_msa.data_ptr(), stride, 230, L, d_cons.data_ptr(), 0, d_out.data_ptr(), cap)
+        assert ctx.plan_info()["n_parts"] == 4
+        assert G.same_muts(d_out[: n * 12].cpu().numpy().view(api.MUT_DTYPE).copy(), want)
+        ctx.run_device(api.SANKOFF, d_msa.data_ptr(), stride, 230, L, d_cons.data_ptr())
+        with pytest.raises(api.PmfsError) as e:
+            ctx.run_fitch_static(d_msa.data_ptr(), stride, 230, L, d_cons.data_ptr(), 0, d_out.data_ptr(), cap)
+        assert e.value.status == -5 and "Sankoff" in str(e.value)
+        ctx.run_device(api.FITCH, d_msa.data_ptr(), stride, 230, L, d_cons.data_ptr())
+        n = ctx.run_fitch_static(d_msa.data_ptr(), stride, 230, L, d_cons.data_ptr(), 0, d_out.data_ptr(), cap)
+        assert G.same_muts(d_out[: n * 12].cpu().numpy().view(api.MUT_DTYPE).copy(), want)
