@@ -421,13 +421,17 @@ static size_t sync_ints(const Plan& P, int64_t groups, int tile_groups) {
 // resident CTAs, and on the 16 M-node tree 16 + 4 / 8 + 8 entries ran 40 % slower than 8 + 2 / 4 + 4
 // (profiles/r2_b_ring_sweep.log; a ladder, one chain of dependent nodes per column tile, does not care either way: its
 // walkers wait for instructions, not for operands).  PMFS_RINGS="fl,fs,bl,bs" (environment, log2 values) overrides.
-static void ring_depths(const pmfs_ctx* c, const WalkKernelSet& ks, bool fwd, int stack_depth, int32_t* leaf_log2, int32_t* set_log2) {
+static void ring_depths(const pmfs_ctx* c, const WalkKernelSet& ks, bool fwd, int algo, int stack_depth, int32_t* leaf_log2, int32_t* set_log2) {
     const int groups = ks.shape.groups();
     int fl, fs, bl, bs;
     if (groups >= 256) { fl = 2; fs = 0; bl = 1; bs = 1; }
     else if (groups >= 128) { fl = 2; fs = 1; bl = 2; bs = 1; }
     else if (groups >= 64) { fl = 3; fs = 1; bl = 2; bs = 2; }
     else { fl = 3; fs = 2; bl = 3; bs = 2; }
+    // The 2x1 top-down Fitch kernel is compiled for 64 registers (walk_kernels.cuh bwd_min_ctas): 10 CTAs per SM by
+    // registers, which shared memory only lets in with a two-slot set ring (8.88 -> 8.40 ms per 2 048-column batch of the
+    // 16 M-node tree; with the four-slot ring 64 registers gain nothing, profiles/r2_x_regs64.log)
+    if (algo == PMFS_FITCH && ks.shape.nw == 2 && ks.shape.ng == 1) bs = 1;
     if (const char* e = getenv("PMFS_RINGS")) {
         int a, b, d, f;
         if (sscanf(e, "%d,%d,%d,%d", &a, &b, &d, &f) == 4) { fl = a; fs = b; bl = d; bs = f; }
@@ -479,7 +483,7 @@ static int launch_levels(pmfs_ctx* c, WalkParams wp, bool fwd, int64_t* launches
     const size_t per_pass = (size_t)n_items;
     wp.next_item = sync + (fwd ? 0 : 32);
     wp.ready = sync + 64 + (fwd ? 0 : per_pass);
-    ring_depths(c, ks, fwd, fwd ? P.fwd_stack_depth : P.bwd_stack_depth, &wp.leaf_ring_log2, &wp.set_ring_log2);
+    ring_depths(c, ks, fwd, ALGO, fwd ? P.fwd_stack_depth : P.bwd_stack_depth, &wp.leaf_ring_log2, &wp.set_ring_log2);
     const size_t smem = ks.smem_fixed + (ks.leaf_unit_bytes << wp.leaf_ring_log2) + (ks.set_slot_bytes << wp.set_ring_log2) +
                         (fwd ? (size_t)P.fwd_stack_depth * ks.fwd_smem_per_level : (size_t)P.bwd_stack_depth * ks.bwd_smem_per_level);
     if (smem > 200 * 1024) {

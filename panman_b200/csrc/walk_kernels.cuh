@@ -875,14 +875,18 @@ __global__ void __launch_bounds__(CFG::Threads) fwd_kernel(const WalkParams p) {
 
 // Resident CTAs the top-down kernel is compiled for: 96 registers per thread for Fitch (4 CTAs of the 160-thread shape
 // share an SM: +13 % over 3), 128 for Sankoff, whatever the number of threads of the shape.  The 2x1 shape -- what the
-// 2 048-column batches of an 8 M-taxon tree on one GPU run -- fits 80 registers without spilling (86 when left alone):
-// 8 CTAs = 24 warps per SM instead of 6 = 18, top-down pass 10.2 -> 8.9 ms per batch.  Not the 1x1 shape: 12 CTAs of two
-// warps each are slower than 10 (5.6 -> 6.0 ms; every CTA brings a producer warp and its rings) --
-// profiles/r2_v_regs80.log.
+// 2 048-column batches of an 8 M-taxon tree on one GPU run -- fits 64 registers without spilling (it takes 86 when left
+// alone): top-down pass per batch 10.2 ms at 6 CTAs per SM (18 warps), 8.9 at 8 (80 registers), 8.4 at 10 (64 registers
+// and a two-slot set ring, which is what lets them in: pmfs.cu ring_depths).  Not the 1x1 shape: 12 CTAs of two warps
+// are slower than 10 (5.6 -> 6.0 ms; every CTA brings a producer warp and its rings).  profiles/r2_v_regs80.log,
+// profiles/r2_x_regs64.log.
+#ifndef PMFS_R21
+#define PMFS_R21 64
+#endif
 template <class CFG, int ALGO>
 constexpr int bwd_min_ctas() {
     // (registers are per SM sub-partition: 16 384 each, warps are spread over the four of them)
-    constexpr int regs = ALGO == kAlgoFitch ? (CFG::NW == 2 && CFG::NG == 1 ? 80 : 96) : 128;
+    constexpr int regs = ALGO == kAlgoFitch ? (CFG::NW == 2 && CFG::NG == 1 ? PMFS_R21 : 96) : 128;
     return 4 * (16384 / (regs * 32)) / (CFG::Threads / 32);
 }
 template <class CFG, int ALGO>
