@@ -194,5 +194,8 @@ def test_emul_split_polytomies(emul):
                 got, plan = run_emul(emul, algo, tree, msa, cons, None, 64, want_plan=True)
                 assert plan[6] == (12 if shape == "star" else 4 * 3 + 5), plan
                 assert G.same_muts(got, O.run_port(algo, tree, msa, cons, None)), (shape, algo)
+                if O.ref_available():  # ... and against the reference's own fitchSankoff.cpp, not only its restatement
+                    ref = O.run_ref_columns(algo, tree, O.codes_to_chars(msa), O.codes_to_chars(cons), None, threads=2)
+                    assert G.same_muts(got, ref), (shape, algo, "ref")
     finally:
         emul.emul_set_split(128, 63)
