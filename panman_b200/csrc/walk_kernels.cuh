@@ -880,7 +880,7 @@ __global__ void __launch_bounds__(CFG::Threads) fwd_kernel(const WalkParams p) {
 // and a two-slot set ring, which is what lets them in: pmfs.cu ring_depths).  Not the 1x1 shape: 12 CTAs of two warps
 // are slower than 10 (5.6 -> 6.0 ms; every CTA brings a producer warp and its rings).  profiles/r2_v_regs80.log,
 // profiles/r2_x_regs64.log.
-#ifndef PMFS_R21
+#ifndef PMFS_R21  // registers per thread the 2x1 Fitch instance is compiled for (build variants: -DPMFS_R21=80, 96)
 #define PMFS_R21 64
 #endif
 template <class CFG, int ALGO>
