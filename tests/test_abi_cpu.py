@@ -68,3 +68,41 @@ def test_nibble_packing_roundtrip():
         assert p.shape == (3, (cols + 1) // 2)
         assert (api.unpack_nibbles(p, cols) == codes).all()
         assert (p[:, 0] & 15 == codes[:, 0]).all()  # column 0 in the LOW nibble
+
+
+def _build_c_example(tmp_path):
+    """examples/fitch_from_c.c: the headers as C99 (-pedantic), linked against libpmfs.so only."""
+    import subprocess
+    exe = str(tmp_path / "fitch_from_c")
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                        os.path.join(ROOT, "examples", "fitch_from_c.c"), "-L" + os.path.join(ROOT, "panman_b200"), "-lpmfs",
+                        "-Wl,-rpath," + os.path.join(ROOT, "panman_b200"), "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_headers_are_c99_and_cxx17_and_the_c_example_links(lib, tmp_path):
+    import subprocess
+    inc = "-I" + os.path.join(ROOT, "include")
+    for cmd in (["gcc", "-std=c99", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", inc, os.path.join(ROOT, "include", "pmfs_host.h")],
+                ["g++", "-std=c++17", "-Werror", "-fsyntax-only", "-x", "c++", inc, os.path.join(ROOT, "include", "pmfs_host.h")]):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    exe = _build_c_example(tmp_path)
+    if not _has_gpu():  # no device: the product fails loudly instead of falling back to anything
+        r = subprocess.run([exe], capture_output=True, text=True)
+        assert r.returncode == 2 and "no CPU path" in r.stderr
+
+
+@pytest.mark.gpu
+def test_c_example_prints_the_oracles_records(lib, tmp_path):
+    import subprocess
+    from oracle import oracle_api as O
+    exe = _build_c_example(tmp_path)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    tree = synth._flatten([[0, 1], 2])
+    msa = np.array([[1, 2, 4, 8], [1, 2, 8, 8], [1, 4, 4, 0]], np.uint8)
+    want = O.run_port(0, tree, msa, np.array([1, 2, 4, 8], np.uint8), None)
+    lines = [f"node {m['node']} pos {m['pos']} type {m['type']} code {m['code']}" for m in want]
+    assert r.stdout.strip().splitlines() == lines and len(lines) > 0
