@@ -88,6 +88,9 @@ def test_headers_are_c99_and_cxx17_and_the_c_example_links(lib, tmp_path):
                 ["g++", "-std=c++17", "-Werror", "-fsyntax-only", "-x", "c++", inc, os.path.join(ROOT, "include", "pmfs_host.h")]):
         r = subprocess.run(cmd, capture_output=True, text=True)
         assert r.returncode == 0, r.stderr
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", inc, os.path.join(ROOT, "examples", "msa_to_panman.c"),
+                        "-L" + os.path.join(ROOT, "panman_b200"), "-lpmfs", "-o", str(tmp_path / "msa_to_panman")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
     exe = _build_c_example(tmp_path)
     if not _has_gpu():  # no device: the product fails loudly instead of falling back to anything
         r = subprocess.run([exe], capture_output=True, text=True)

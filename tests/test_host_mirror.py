@@ -12,6 +12,8 @@ import synth
 from oracle import oracle_api as O
 from panman_b200 import api, host
 
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
 
 @pytest.fixture(scope="module", autouse=True)
 def _lib():
@@ -158,3 +160,28 @@ def test_build_panman_file_c1(c1, tmp_path, low, with_ref):
     assert hashlib.sha256(d["consensusSeqMap"][0]["consensusSeq"].astype("<u4").tobytes()).hexdigest() == str(c1[key + "block_words_sha256"])
     names, parent, _ = host.parse_newick(d["newick"])
     assert names == [str(x) for x in c1["names"]] and (parent == c1["parent"]).all()
+
+
+@pytest.mark.gpu
+def test_command_line_example_writes_the_same_panman(c1, tmp_path):
+    """examples/msa_to_panman.c -- the C program a user would build against libpmfs.so -- on BASELINE config 1 with
+    --reference and --low-mem-mode: the file it writes decodes to the golden NucMut lists; and it reports the
+    reference's own complaint (unequal row lengths) instead of writing anything."""
+    import subprocess
+    from panman_reader import nuc_csr, read_panman
+    exe = str(tmp_path / "msa_to_panman")
+    r = subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                        os.path.join(ROOT, "examples", "msa_to_panman.c"), "-L" + os.path.join(ROOT, "panman_b200"), "-lpmfs",
+                        "-Wl,-rpath," + os.path.join(ROOT, "panman_b200"), "-o", exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    key = "v11_"
+    fa, nw = _write_c1(c1, tmp_path)
+    out = str(tmp_path / "cli")
+    r = subprocess.run([exe, fa, nw, out, "--reference", str(c1[key + "reference"]), "--low-mem-mode"], capture_output=True, text=True)
+    assert r.returncode == 0 and "wrote" in r.stdout, r.stdout + r.stderr
+    off, nuc = nuc_csr(read_panman(out + ".panman"))
+    assert nuc.shape[0] == int(c1[key + "n_nuc"]) and G.digest_nuc(off, nuc) == str(c1[key + "nuc_sha256"])
+    with open(fa, "a") as f:
+        f.write(">short\nACGT\n")
+    r = subprocess.run([exe, fa, nw, str(tmp_path / "bad")], capture_output=True, text=True)
+    assert r.returncode == 1 and "lengths" in r.stderr and not os.path.exists(str(tmp_path / "bad.panman"))
